@@ -1,0 +1,361 @@
+"""CPU oracle for the latent + loss hot path of bplaut/PyTorch-VAE.
+
+TEST INFRASTRUCTURE ONLY.  Nothing under ``oracle/`` is part of the product:
+only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s CPU-baseline /
+``--impl reference`` legs may import it, and only as the checker.  The product
+(``pytorch-vae_b200/vaekit``) never imports this file and has no CPU fallback.
+
+Where the arithmetic lives: the reference contains no native code; every
+operation on the path is a call into **PyTorch** (``requirements.txt:4`` pins
+``torch>=1.6.1``; this image has torch 2.11.0+cu128).  The functions below restate the
+reference's formulas with the same ATen operators, in the same order, as plain
+functions that take the *noise as an explicit argument* (the reference draws it
+with ``torch.randn_like``).  Each function cites the reference lines it follows.
+
+Parity pinning: the reference's own tests hold no golden vectors (print-only
+smoke tests), so the oracle is pinned against the reference
+itself, imported live from ``/root/reference`` in the build container
+(``tests/test_oracle_pin.py``), and against fixtures generated from it by
+``tests/golden/make_golden.py`` (committed as ``tests/golden/*.npz``).
+
+All functions are dtype-generic: feed ``.double()`` inputs for the fp64
+yard-stick.
+"""
+from __future__ import annotations
+
+import math
+from typing import Dict, Optional, Tuple
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+Tensor = torch.Tensor
+
+# --------------------------------------------------------------------------
+# Philox4x32-10 counter RNG + Box-Muller: the *product's* noise stream
+# (include/vaekit.h "RNG contract").  Integer part is bit-exact by definition;
+# checked against the Random123 known-answer vectors in tests/test_philox.py.
+# --------------------------------------------------------------------------
+_PHILOX_M0 = np.uint64(0xD2511F53)
+_PHILOX_M1 = np.uint64(0xCD9E8D57)
+_PHILOX_W0 = np.uint32(0x9E3779B9)
+_PHILOX_W1 = np.uint32(0xBB67AE85)
+
+
+def philox4x32_10(counter: np.ndarray, key: np.ndarray) -> np.ndarray:
+    """counter: [..., 4] uint32, key: [..., 2] uint32 (broadcastable) -> [..., 4] uint32."""
+    c = np.array(counter, dtype=np.uint32, copy=True)
+    k = np.array(np.broadcast_to(key, c.shape[:-1] + (2,)), dtype=np.uint32, copy=True)
+    mask = np.uint64(0xFFFFFFFF)
+    with np.errstate(over="ignore"):
+        for _ in range(10):
+            p0 = _PHILOX_M0 * c[..., 0].astype(np.uint64)
+            p1 = _PHILOX_M1 * c[..., 2].astype(np.uint64)
+            hi0 = (p0 >> np.uint64(32)).astype(np.uint32)
+            lo0 = (p0 & mask).astype(np.uint32)
+            hi1 = (p1 >> np.uint64(32)).astype(np.uint32)
+            lo1 = (p1 & mask).astype(np.uint32)
+            n0 = hi1 ^ c[..., 1] ^ k[..., 0]
+            n1 = lo1
+            n2 = hi0 ^ c[..., 3] ^ k[..., 1]
+            n3 = lo0
+            c = np.stack([n0, n1, n2, n3], axis=-1)
+            k = np.stack([k[..., 0] + _PHILOX_W0, k[..., 1] + _PHILOX_W1], axis=-1)
+    return c
+
+
+def philox_uint32(seed: int, offset: int, n_quads: int, first_quad: int = 0) -> np.ndarray:
+    """The product's stream: quad q (elements 4q..4q+3) = Philox(ctr=(lo(q+offset),
+    hi(q+offset), 0, 0), key=(lo(seed), hi(seed))).  Returns [n_quads, 4] uint32."""
+    q = np.arange(first_quad, first_quad + n_quads, dtype=np.uint64) + np.uint64(offset)
+    ctr = np.zeros((n_quads, 4), dtype=np.uint32)
+    ctr[:, 0] = (q & np.uint64(0xFFFFFFFF)).astype(np.uint32)
+    ctr[:, 1] = (q >> np.uint64(32)).astype(np.uint32)
+    key = np.array([seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF], dtype=np.uint32)
+    return philox4x32_10(ctr, key)
+
+
+def philox_normal(seed: int, offset: int, numel: int) -> np.ndarray:
+    """fp32 standard normals for elements [0, numel): element 4q+c uses words of
+    quad q; Box-Muller pairs (w0,w1)->(n0,n1), (w2,w3)->(n2,n3) with
+    u = (w + 0.5) * 2^-32 in (0,1), r = sqrt(-2 ln u_a), theta = 2 pi u_b.
+    Float part is evaluated in float64 then rounded: the CUDA kernel's fp32
+    intrinsics agree to a few ulp, so compare with a tolerance, not bit-wise."""
+    nq = (numel + 3) // 4
+    w = philox_uint32(seed, offset, nq).astype(np.float64)
+    u = (w + 0.5) * (2.0 ** -32)
+    r0 = np.sqrt(-2.0 * np.log(u[:, 0]))
+    r1 = np.sqrt(-2.0 * np.log(u[:, 2]))
+    t0 = 2.0 * np.pi * u[:, 1]
+    t1 = 2.0 * np.pi * u[:, 3]
+    out = np.stack([r0 * np.cos(t0), r0 * np.sin(t0), r1 * np.cos(t1), r1 * np.sin(t1)], axis=1)
+    return out.reshape(-1)[:numel].astype(np.float32)
+
+
+# --------------------------------------------------------------------------
+# K1: reparameterisation + Gaussian KL
+# --------------------------------------------------------------------------
+def reparameterize(mu: Tensor, logvar: Tensor, eps: Tensor) -> Tensor:
+    """vanilla_vae.py:115-117 (same body: beta_vae.py:120-122, logcosh_vae.py:116-118,
+    iwae.py:117-119, miwae.py:120-122, betatc_vae.py:123-125); eps replaces randn_like."""
+    std = torch.exp(0.5 * logvar)
+    return eps * std + mu
+
+
+def kld_rows(mu: Tensor, log_var: Tensor) -> Tensor:
+    """Row-wise -1/2 sum_d(1 + lv - mu^2 - e^lv) over the last dim
+    (vanilla_vae.py:143 inner expression; iwae.py:150; miwae.py:155)."""
+    return -0.5 * torch.sum(1 + log_var - mu ** 2 - log_var.exp(), dim=-1)
+
+
+# --------------------------------------------------------------------------
+# K2: ELBO-style losses
+# --------------------------------------------------------------------------
+def vanilla_loss(recons: Tensor, input: Tensor, mu: Tensor, log_var: Tensor, M_N: float) -> Dict[str, Tensor]:
+    """vanilla_vae.py:134-146."""
+    recons_loss = F.mse_loss(recons, input)
+    kld_loss = torch.mean(kld_rows(mu, log_var), dim=0)
+    loss = recons_loss + M_N * kld_loss
+    return {"loss": loss, "Reconstruction_Loss": recons_loss.detach(), "KLD": -kld_loss.detach()}
+
+
+def beta_loss(recons: Tensor, input: Tensor, mu: Tensor, log_var: Tensor, M_N: float, *,
+              loss_type: str, beta: float, gamma: float, C_max: float, C_stop_iter: float,
+              num_iter: int) -> Dict[str, Tensor]:
+    """beta_vae.py:129-152.  ``num_iter`` is the value *after* the increment at :132."""
+    recons_loss = F.mse_loss(recons, input)
+    kld_loss = torch.mean(kld_rows(mu, log_var), dim=0)
+    if loss_type == "H":
+        loss = recons_loss + beta * M_N * kld_loss
+    elif loss_type == "B":
+        cmax = torch.tensor([C_max], dtype=torch.float32)  # torch.Tensor([max_capacity]), beta_vae.py:28
+        C = torch.clamp(cmax / C_stop_iter * num_iter, 0, cmax.data[0])
+        loss = recons_loss + gamma * M_N * (kld_loss - C.to(kld_loss.dtype)).abs()
+    else:
+        raise ValueError("Undefined loss type.")
+    return {"loss": loss, "Reconstruction_Loss": recons_loss, "KLD": kld_loss}
+
+
+def logcosh_loss(recons: Tensor, input: Tensor, mu: Tensor, log_var: Tensor, M_N: float, *,
+                 alpha: float, beta: float) -> Dict[str, Tensor]:
+    """logcosh_vae.py:141-155 (literal, unstabilised form; log(2) is an fp32 constant)."""
+    t = recons - input
+    r = alpha * t + torch.log(1.0 + torch.exp(-2 * alpha * t)) - torch.log(torch.tensor(2.0))
+    recons_loss = (1.0 / alpha) * r.mean()
+    kld_loss = torch.mean(kld_rows(mu, log_var), dim=0)
+    loss = recons_loss + beta * M_N * kld_loss
+    return {"loss": loss, "Reconstruction_Loss": recons_loss, "KLD": -kld_loss}
+
+
+# --------------------------------------------------------------------------
+# K3: IWAE / MIWAE bound
+# --------------------------------------------------------------------------
+def iw_bound_loss(recons: Tensor, input: Tensor, mu: Tensor, log_var: Tensor, M_N: float) -> Dict[str, Tensor]:
+    """iwae.py:145-160 (recons [B,S,C,H,W]) and miwae.py:148-164 (recons [B,M,S,C,H,W]).
+    The input image is broadcast (the reference materialises a repeat, iwae.py:145)."""
+    nd = recons.dim() - input.dim()          # 1 for IWAE, 2 for MIWAE
+    x = input.view(input.shape[0], *([1] * nd), *input.shape[1:])
+    log_p_x_z = ((recons - x) ** 2).flatten(1 + nd).mean(-1)
+    kld = kld_rows(mu, log_var)
+    log_weight = log_p_x_z + M_N * kld
+    weight = F.softmax(log_weight, dim=-1)
+    s = torch.sum(weight * log_weight, dim=-1)
+    if nd == 1:
+        loss = torch.mean(s, dim=0)
+    else:
+        loss = torch.mean(torch.mean(s, dim=-2), dim=0)
+    return {"loss": loss, "Reconstruction_Loss": log_p_x_z.mean(), "KLD": -kld.mean()}
+
+
+# --------------------------------------------------------------------------
+# K4: WAE-MMD
+# --------------------------------------------------------------------------
+def _pair_views(x1: Tensor, x2: Tensor) -> Tuple[Tensor, Tensor]:
+    """wae_mmd.py:129-141."""
+    n, d = x1.shape
+    return x1.unsqueeze(-2).expand(n, n, d), x2.unsqueeze(-3).expand(n, n, d)
+
+
+def rbf_kernel_matrix(x1: Tensor, x2: Tensor, z_var: float) -> Tensor:
+    """wae_mmd.py:164-168: exp(-mean_d (x1-x2)^2 / (2 D z_var)) as an [N,N] matrix."""
+    a, b = _pair_views(x1, x2)
+    sigma = 2.0 * a.size(-1) * z_var
+    return torch.exp(-((a - b).pow(2).mean(-1) / sigma))
+
+
+def imq_kernel_offdiag_sum(x1: Tensor, x2: Tensor, z_var: float, eps: float = 1e-7) -> Tensor:
+    """wae_mmd.py:183-191: C/(eps + C + ||x1-x2||^2), summed minus its diagonal (a scalar)."""
+    a, b = _pair_views(x1, x2)
+    C = 2 * a.size(-1) * z_var
+    k = C / (eps + C + (a - b).pow(2).sum(dim=-1))
+    return k.sum() - k.diag().sum()
+
+
+def mmd_terms(z: Tensor, prior_z: Tensor, kernel_type: str, z_var: float) -> Tuple[Tensor, Tensor, Tensor]:
+    """The three ``.mean()`` operands of wae_mmd.py:197-203 (pp, zz, pz)."""
+    if kernel_type == "rbf":
+        f = lambda a, b: rbf_kernel_matrix(a, b, z_var).mean()
+    elif kernel_type == "imq":
+        f = lambda a, b: imq_kernel_offdiag_sum(a, b, z_var).mean()
+    else:
+        raise ValueError("Undefined kernel type.")
+    return f(prior_z, prior_z), f(z, z), f(prior_z, z)
+
+
+def mmd(z: Tensor, prior_z: Tensor, reg_weight: float, kernel_type: str, z_var: float) -> Tensor:
+    """wae_mmd.py:193-204 with prior_z injected."""
+    pp, zz, pz = mmd_terms(z, prior_z, kernel_type, z_var)
+    return reg_weight * pp + reg_weight * zz - 2 * reg_weight * pz
+
+
+def mmd_terms_chunked(z: Tensor, prior_z: Tensor, kernel_type: str, z_var: float,
+                      block: int = 1024) -> Tuple[Tensor, Tensor, Tensor]:
+    """Row-blocked restatement of the same three terms for N where the reference's
+    [N,N,D] broadcast cannot be materialised.  Uses the literal
+    (x-y)^2 form per block, so it is the same arithmetic, just tiled; the sums
+    are accumulated in float64.  Not differentiable (use torch.autograd on
+    ``mmd`` at small N for gradients)."""
+    n, d = z.shape
+
+    def term(a: Tensor, b: Tensor) -> Tensor:
+        tot = torch.zeros((), dtype=torch.float64)
+        for i in range(0, n, block):
+            diff = a[i:i + block, None, :] - b[None, :, :]
+            if kernel_type == "rbf":
+                k = torch.exp(-(diff.pow(2).mean(-1) / (2.0 * d * z_var)))
+                tot += k.double().sum()
+            elif kernel_type == "imq":
+                C = 2 * d * z_var
+                k = C / (1e-7 + C + diff.pow(2).sum(-1))
+                tot += k.double().sum() - k[:, i:i + block].diag().double().sum()
+            else:
+                raise ValueError("Undefined kernel type.")
+        return tot / (n * n) if kernel_type == "rbf" else tot
+
+    with torch.no_grad():
+        return term(prior_z, prior_z), term(z, z), term(prior_z, z)
+
+
+def wae_loss(recons: Tensor, input: Tensor, z: Tensor, prior_z: Tensor, *, reg_weight: float,
+             kernel_type: str, z_var: float) -> Dict[str, Tensor]:
+    """wae_mmd.py:107-123."""
+    b = input.size(0)
+    reg = reg_weight / (b * (b - 1))
+    recons_loss = F.mse_loss(recons, input)
+    mmd_loss = mmd(z, prior_z, reg, kernel_type, z_var)
+    return {"loss": recons_loss + mmd_loss, "Reconstruction_Loss": recons_loss, "MMD": mmd_loss}
+
+
+# --------------------------------------------------------------------------
+# K5: Beta-TC-VAE
+# --------------------------------------------------------------------------
+def log_density_gaussian(x: Tensor, mu: Tensor, logvar: Tensor) -> Tensor:
+    """betatc_vae.py:140-142."""
+    norm = -0.5 * (math.log(2 * math.pi) + logvar)
+    return norm - 0.5 * ((x - mu) ** 2 * torch.exp(-logvar))
+
+
+def betatc_loss(recons: Tensor, input: Tensor, mu: Tensor, log_var: Tensor, z: Tensor, M_N: float, *,
+                alpha: float, beta: float, gamma: float, anneal_rate: float) -> Dict[str, Tensor]:
+    """betatc_vae.py:155-211.  ``anneal_rate`` is what :196-200 computes from
+    num_iter / training mode (host logic, tested separately)."""
+    recons_loss = F.mse_loss(recons, input, reduction="sum")
+    log_q_zx = log_density_gaussian(z, mu, log_var).sum(dim=1)
+    zeros = torch.zeros_like(z)
+    log_p_z = log_density_gaussian(z, zeros, zeros).sum(dim=1)
+    bsz, d = z.shape
+    mat = log_density_gaussian(z.view(bsz, 1, d), mu.view(1, bsz, d), log_var.view(1, bsz, d))
+    dataset_size = (1 / M_N) * bsz
+    strat = (dataset_size - bsz + 1) / (dataset_size * (bsz - 1))
+    w = torch.Tensor(bsz, bsz).fill_(1 / (bsz - 1))           # fp32 table, as the reference builds it
+    w.view(-1)[::bsz] = 1 / dataset_size
+    w.view(-1)[1::bsz] = strat
+    w[bsz - 2, 0] = strat
+    mat = mat + w.log().to(mat.dtype).view(bsz, bsz, 1)
+    log_q_z = torch.logsumexp(mat.sum(2), dim=1)
+    log_prod_q_z = torch.logsumexp(mat, dim=1).sum(1)
+    mi = (log_q_zx - log_q_z).mean()
+    tc = (log_q_z - log_prod_q_z).mean()
+    kld = (log_prod_q_z - log_p_z).mean()
+    loss = recons_loss / bsz + alpha * mi + (beta * tc + anneal_rate * gamma * kld)
+    return {"loss": loss, "Reconstruction_Loss": recons_loss, "KLD": kld, "TC_Loss": tc, "MI_Loss": mi}
+
+
+# --------------------------------------------------------------------------
+# K6: SWAE
+# --------------------------------------------------------------------------
+def random_projections(latent_dim: int, num_samples: int, proj_dist: str = "normal") -> Tensor:
+    """swae.py:139-148: consumes the *CPU* default generator."""
+    if proj_dist == "normal":
+        r = torch.randn(num_samples, latent_dim)
+    elif proj_dist == "cauchy":
+        r = torch.distributions.Cauchy(torch.tensor([0.0]), torch.tensor([1.0])).sample(
+            (num_samples, latent_dim)).squeeze()
+    else:
+        raise ValueError("Unknown projection distribution.")
+    return r / r.norm(dim=1).view(-1, 1)
+
+
+def swd(z: Tensor, prior_z: Tensor, proj: Tensor, p: float, reg_weight: float) -> Tensor:
+    """swae.py:165-179; ``proj`` is the [S,D] matrix of swae.py:168 (before transpose)."""
+    pm = proj.transpose(0, 1).to(z.dtype)
+    lat = z.matmul(pm)
+    pri = prior_z.matmul(pm)
+    w = torch.sort(lat.t(), dim=1)[0] - torch.sort(pri.t(), dim=1)[0]
+    return reg_weight * w.pow(p).mean()
+
+
+def swae_loss(recons: Tensor, input: Tensor, z: Tensor, prior_z: Tensor, proj: Tensor, *,
+              reg_weight: float, p: float) -> Dict[str, Tensor]:
+    """swae.py:110-127."""
+    b = input.size(0)
+    reg = reg_weight / (b * (b - 1))
+    l2 = F.mse_loss(recons, input)
+    l1 = F.l1_loss(recons, input)
+    s = swd(z, prior_z, proj, p, reg)
+    return {"loss": l2 + l1 + s, "Reconstruction_Loss": l2 + l1, "SWD": s}
+
+
+# --------------------------------------------------------------------------
+# K7: VQ-VAE vector quantiser
+# --------------------------------------------------------------------------
+def vq_distances(flat: Tensor, codebook: Tensor) -> Tensor:
+    """vq_vae.py:30-32, same association: (|x|^2 + |e|^2) - 2 x.e^T."""
+    return torch.sum(flat ** 2, dim=1, keepdim=True) + torch.sum(codebook ** 2, dim=1) - \
+        2 * torch.matmul(flat, codebook.t())
+
+
+def vq_forward(latents: Tensor, codebook: Tensor, beta: float) -> Tuple[Tensor, Tensor, Tensor]:
+    """vq_vae.py:24-55.  Returns (quantised NCHW, vq_loss, indices[R]); the
+    reference does not return the indices, the oracle exposes them for the
+    bit-exactness check."""
+    k, d = codebook.shape
+    nhwc = latents.permute(0, 2, 3, 1).contiguous()
+    flat = nhwc.view(-1, d)
+    dist = vq_distances(flat, codebook)
+    inds = torch.argmin(dist, dim=1).unsqueeze(1)
+    one_hot = torch.zeros(inds.size(0), k, dtype=latents.dtype)
+    one_hot.scatter_(1, inds, 1)
+    q = torch.matmul(one_hot, codebook).view(nhwc.shape)
+    commitment = F.mse_loss(q.detach(), nhwc)
+    embedding = F.mse_loss(q, nhwc.detach())
+    vq_loss = commitment * beta + embedding
+    q = nhwc + (q - nhwc).detach()
+    return q.permute(0, 3, 1, 2).contiguous(), vq_loss, inds.view(-1)
+
+
+def vqvae_loss(recons: Tensor, input: Tensor, vq_loss: Tensor) -> Dict[str, Tensor]:
+    """vq_vae.py:194-211."""
+    recons_loss = F.mse_loss(recons, input)
+    return {"loss": recons_loss + vq_loss, "Reconstruction_Loss": recons_loss, "VQ_Loss": vq_loss}
+
+
+def vq_gap(flat: Tensor, codebook: Tensor) -> Tuple[Tensor, Tensor]:
+    """Per-row (best index in float64, relative best-vs-second gap of the fp32
+    distances) used to decide where indices must be bit-exact (north star)."""
+    d32 = vq_distances(flat, codebook)
+    top2 = torch.topk(d32, 2, dim=1, largest=False).values
+    gap = (top2[:, 1] - top2[:, 0]) / top2[:, 0].abs().clamp_min(1e-30)
+    d64 = vq_distances(flat.double(), codebook.double())
+    return torch.argmin(d64, dim=1), gap
