@@ -1,0 +1,404 @@
+#!/usr/bin/env python
+"""Benchmark of the latent + loss hot path (BASELINE.json metric: samples/s fwd+bwd).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload iwae|miwae|vanilla] [--impl reference]
+
+Default workload = BASELINE.json configs[1]: IWAE K=5, batch 4096, latent 128, 64x64 RGB --
+reparameterize + importance-weighted bound, forward + backward, on synthetic tensors.
+One JSON line on stdout (rank 0).  Under torchrun each rank owns its own batch of 4096
+(weak scaling, no data-path collective: the op is batch-local).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (os.path.join(ROOT, "pytorch-vae_b200"),):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import torch  # noqa: E402
+
+P_IMG = 3 * 64 * 64
+WORKLOADS = {
+    # name: (B, G, K, D, M_N)
+    "iwae": dict(B=4096, G=1, K=5, D=128, M_N=0.00025, desc="IWAE K=5, batch 4096, latent 128, 3x64x64 (BASELINE configs[1])"),
+    "miwae": dict(B=4096, G=3, K=5, D=128, M_N=0.00025, desc="MIWAE K=5 M=3, batch 4096, latent 128, 3x64x64 (BASELINE configs[1])"),
+    "vanilla": dict(B=65536, G=0, K=0, D=128, M_N=0.005, desc="VanillaVAE loss, batch 65536, latent 128, 3x64x64 (config 1 at streaming size)"),
+}
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (measured)"
+    except Exception:
+        return 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons while the timed region runs."""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0])); mx = float(f[1])
+            except ValueError:
+                continue
+            for n, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        med = sm[len(sm) // 2] if sm else None
+        return {"sm_mhz": med, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+# ---------------------------------------------------------------------------
+# workloads
+# ---------------------------------------------------------------------------
+def sample_shape(wl, B):
+    if wl["K"] == 0:
+        return (B,)
+    return (B, wl["G"], wl["K"]) if wl["G"] > 1 else (B, wl["K"])
+
+
+def make_host_inputs(wl, B, seed, pin):
+    g = torch.Generator().manual_seed(seed)
+    ss = sample_shape(wl, B)
+    t = {
+        "recons": torch.tanh(torch.randn(*ss, 3, 64, 64, generator=g)),       # decoder ends in Tanh
+        "input": torch.rand(B, 3, 64, 64, generator=g),                       # ToTensor range
+        "mu0": torch.randn(B, wl["D"], generator=g),
+        "lv0": 0.5 * torch.randn(B, wl["D"], generator=g) - 1.0,
+        "gz": 1e-3 * torch.randn(*ss, wl["D"], generator=g),                  # upstream grad of z (decoder bwd)
+    }
+    if pin:
+        t = {k: v.pin_memory() for k, v in t.items()}
+    return t
+
+
+def make_device_inputs(wl, B, seed, dev):
+    """Synthetic tensors generated on the device (fast for 1-3 GB), same distributions."""
+    g = torch.Generator(device=dev).manual_seed(seed)
+    ss = sample_shape(wl, B)
+    return {
+        "recons": torch.tanh(torch.randn(*ss, 3, 64, 64, device=dev, generator=g)),
+        "input": torch.rand(B, 3, 64, 64, device=dev, generator=g),
+        "mu0": torch.randn(B, wl["D"], device=dev, generator=g),
+        "lv0": 0.5 * torch.randn(B, wl["D"], device=dev, generator=g) - 1.0,
+        "gz": 1e-3 * torch.randn(*ss, wl["D"], device=dev, generator=g),
+    }
+
+
+def expand_latents(wl, mu0, lv0):
+    if wl["K"] == 0:
+        return mu0, lv0
+    if wl["G"] > 1:
+        shp = (-1, wl["G"], wl["K"], -1)
+        return mu0.view(mu0.size(0), 1, 1, -1).expand(*shp), lv0.view(lv0.size(0), 1, 1, -1).expand(*shp)
+    return mu0.unsqueeze(1).expand(-1, wl["K"], -1), lv0.unsqueeze(1).expand(-1, wl["K"], -1)
+
+
+def hot_path_step(model, wl, t):
+    """One pass of the hot path through the public model API: reparameterize -> loss_function -> backward."""
+    recons = t["recons"].requires_grad_(True)
+    mu0 = t["mu0"].requires_grad_(True)
+    lv0 = t["lv0"].requires_grad_(True)
+    recons.grad = mu0.grad = lv0.grad = None
+    mu, lv = expand_latents(wl, mu0, lv0)
+    z = model.reparameterize(mu, lv)
+    if wl["K"] == 0:
+        d = model.loss_function(recons, t["input"], mu, lv, M_N=wl["M_N"])
+    else:
+        d = model.loss_function(recons, t["input"], mu, lv, z, None, M_N=wl["M_N"])
+    torch.autograd.backward([d["loss"], z], [None, t["gz"]])
+    return d
+
+
+def algorithmic_bytes(wl, B):
+    """bytes one step must move (fp32)."""
+    D = wl["D"]
+    if wl["K"] == 0:
+        return B * (5 * P_IMG * 4 + 8 * D * 4)
+    GK = max(wl["G"], 1) * wl["K"]
+    recon = B * ((GK * P_IMG + P_IMG) * 4 * 2 + GK * P_IMG * 4)          # fwd read, bwd read + write g_recons
+    lat = B * (2 * D * 4 * 2 + GK * D * 4 * 4)                           # mu0/lv0 read twice; z, g_z, g_mu, g_lv rows
+    return recon + lat
+
+
+def build_model(name):
+    from vaekit.models import vae_models
+    if name == "iwae":
+        return vae_models["IWAE"](3, 128, num_samples=5)
+    if name == "miwae":
+        return vae_models["MIWAE"](3, 128, num_samples=5, num_estimates=3)
+    return vae_models["VanillaVAE"](3, 128)
+
+
+KERNEL_BYTES = {
+    # kernel -> algorithmic bytes per launch as a function of the workload (fp32), SURVEY.md 8(d) / DESIGN.md
+    "iw_bound_fwd": lambda B, GK, D: B * (GK * P_IMG + P_IMG) * 4 + B * GK * 8,
+    "iw_bound_bwd": lambda B, GK, D: B * (2 * GK * P_IMG + P_IMG) * 4 + B * GK * 12,
+    "elbo_fwd": lambda B, GK, D: B * 2 * P_IMG * 4 + B * 4,
+    "elbo_bwd": lambda B, GK, D: B * 3 * P_IMG * 4 + B * 4,
+    "reparam_kl_fwd": lambda B, GK, D: B * 2 * D * 4 + B * max(GK, 1) * (D * 4 + 4),
+    "reparam_kl_bwd": lambda B, GK, D: B * 2 * D * 4 + B * max(GK, 1) * (3 * D * 4 + 4),
+}
+
+
+def roofline_from_events(wl, B, log):
+    """Per-kernel average duration from the CUDA events recorded around every libvaekit launch
+    inside the timed region (same stream), turned into achieved GB/s on algorithmic bytes."""
+    peak, peak_src = peaks()
+    GK = max(wl["G"], 1) * wl["K"]
+    acc = {}
+    for name, e0, e1 in log:
+        acc.setdefault(name, []).append(e0.elapsed_time(e1))
+    res, total = {}, 0.0
+    for name, ts in acc.items():
+        ms = sum(ts) / len(ts)
+        nbytes = KERNEL_BYTES[name](B, GK, wl["D"]) if name in KERNEL_BYTES else 0
+        res[name] = {"ms": round(ms, 4), "launches": len(ts), "bytes": nbytes, "GBps": round(nbytes / ms / 1e6, 1)}
+        total += ms
+    dom = max(res, key=lambda k: res[k]["ms"])
+    for k in res:
+        res[k]["share_of_kernel_time"] = round(res[k]["ms"] / total, 4)
+    d = res[dom]
+    return {"bound": "hbm", "kernel": dom + "_kernel", "achieved": d["GBps"], "peak": peak, "unit": "GB/s",
+            "frac": round(d["GBps"] / peak, 4), "traffic": None, "peak_source": peak_src,
+            "algorithmic_bytes_per_launch": d["bytes"], "ms_per_launch": d["ms"], "kernels": res}
+
+
+# ---------------------------------------------------------------------------
+# CPU baseline: the oracle port of the reference's torch code, on the host cores
+# ---------------------------------------------------------------------------
+def cpu_reference_step(wl, t):
+    """reparameterize + loss_function + backward exactly as the reference composes them
+    (iwae.py:121-160 / miwae.py:124-164 / vanilla_vae.py:119-146), via oracle/vae_oracle.py."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import vae_oracle as O
+    recons = t["recons"].detach().requires_grad_(True)
+    mu0 = t["mu0"].detach().requires_grad_(True)
+    lv0 = t["lv0"].detach().requires_grad_(True)
+    if wl["K"] == 0:
+        mu, lv = mu0, lv0
+    elif wl["G"] > 1:
+        mu = mu0.repeat(wl["G"], wl["K"], 1, 1).permute(2, 0, 1, 3)
+        lv = lv0.repeat(wl["G"], wl["K"], 1, 1).permute(2, 0, 1, 3)
+    else:
+        mu = mu0.repeat(wl["K"], 1, 1).permute(1, 0, 2)
+        lv = lv0.repeat(wl["K"], 1, 1).permute(1, 0, 2)
+    z = O.reparameterize(mu, lv, torch.randn_like(mu))
+    if wl["K"] == 0:
+        d = O.vanilla_loss(recons, t["input"], mu, lv, wl["M_N"])
+    else:
+        d = O.iw_bound_loss(recons, t["input"], mu, lv, wl["M_N"])
+    torch.autograd.backward([d["loss"], z], [None, t["gz"]])
+    return d
+
+
+def cpu_baseline(wl, sample_B, iters, warmup=1):
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    t = make_host_inputs(wl, sample_B, 1265, pin=False)
+    for _ in range(warmup):
+        cpu_reference_step(wl, t)
+    ts = []
+    for _ in range(iters):
+        t0 = time.perf_counter()
+        cpu_reference_step(wl, t)
+        ts.append(time.perf_counter() - t0)
+    return ts, cores
+
+
+def run_reference_arm(args, wl):
+    """--impl reference: the reference's CPU path (oracle port of its torch code; the Python reference
+    itself cannot travel to the GPU box) on all host cores, bounded sample of the same workload."""
+    rank, world, _ = dist_env()
+    if rank != 0:
+        return
+    sample_B = args.cpu_sample or (1024 if wl["K"] else 4096)
+    ts, cores = cpu_baseline(wl, sample_B, args.steps, warmup=max(1, min(args.warmup, 2)))
+    total = sum(ts)
+    value = sample_B * len(ts) / total
+    line = {
+        "impl": "reference", "metric": "latent+loss samples/s fwd+bwd", "value": round(value, 2), "unit": "samples/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(1e3 * total / len(ts), 3),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl["desc"], "sample": "batch %d of %d per step" % (sample_B, wl["B"])},
+        "cpu_baseline": {"value": round(value, 2), "unit": "samples/s", "cores": cores, "kind": "port",
+                         "sample": "batch %d of the %d-sample workload per step, torch CPU %d threads" % (sample_B, wl["B"], cores)},
+        "e2e": {"value": round(value, 2), "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------
+def run_gpu_arm(args, wl):
+    import torch.distributed as dist
+    rank, world, local = dist_env()
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    import vaekit
+    from vaekit import _lib as L
+    vaekit.lib()
+    model = build_model(args.workload)
+    B = wl["B"]
+    t = make_device_inputs(wl, B, 1265 + rank, dev)
+    torch.manual_seed(1265)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    # ---- device-resident timing (value) ----
+    for _ in range(args.warmup):
+        hot_path_step(model, wl, t)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    L.EVENT_LOG = []
+    launches0 = L.LAUNCHES
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        d = hot_path_step(model, wl, t)
+    e1.record()
+    barrier()
+    log, L.EVENT_LOG = L.EVENT_LOG, None
+    launches = L.LAUNCHES - launches0
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop() if rank == 0 else None
+    if world > 1:
+        tms = torch.tensor([ms], device=dev)
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+        ms = tms.item()
+    value = world * B * args.steps / (ms / 1e3)
+    roof = roofline_from_events(wl, B, log)
+    loss_val = d["loss"].item()
+
+    # ---- end-to-end: pinned host tensors in, loss out, every step ----
+    host = make_host_inputs(wl, B, 99 + rank, pin=True) if not args.no_e2e else None
+    e2e = None
+    if host is not None:
+        h2d = sum(v.numel() * 4 for v in host.values())
+
+        def e2e_step():
+            td = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
+            dd = hot_path_step(model, wl, td)
+            return [dd[k].item() for k in dd]          # the caller's .item() per dict key (experiment.py:55)
+
+        for _ in range(min(args.warmup, 3)):
+            e2e_step()
+        barrier()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record()
+        for _ in range(args.steps):
+            vals = e2e_step()
+        f1.record()
+        barrier()
+        ems = f0.elapsed_time(f1)
+        if world > 1:
+            tms = torch.tensor([ems], device=dev)
+            dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+            ems = tms.item()
+        e2e = {"value": round(world * B * args.steps / (ems / 1e3), 1), "unit": "samples/s",
+               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4 * len(vals), "ms_per_step": round(ems / args.steps, 3)}
+
+    if rank == 0:
+        cpu = None
+        if world == 1 and not args.no_cpu:
+            sample_B = args.cpu_sample or (1024 if wl["K"] else 4096)
+            ts, cores = cpu_baseline(wl, sample_B, 3)
+            v = sample_B * len(ts) / sum(ts)
+            cpu = {"value": round(v, 2), "unit": "samples/s", "cores": cores, "kind": "port",
+                   "sample": "batch %d of the %d-sample workload, 3 iterations after 1 warm-up, torch CPU %d threads"
+                             % (sample_B, B, cores)}
+        alg = algorithmic_bytes(wl, B)
+        line = {
+            "metric": "latent+loss samples/s fwd+bwd", "value": round(value, 1), "unit": "samples/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 4),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": wl["desc"], "per_gpu_batch": B, "global_batch": B * world,
+                       "l2_policy": "inputs (%.2f GB/step) larger than L2, no flush" % (alg / 1e9),
+                       "parallelism": "batch-sharded, no data-path collective" if world > 1 else "single GPU",
+                       "step": "reparameterize + loss_function + backward through the drop-in model API"},
+            "step_GBps_algorithmic": round(alg / (ms / args.steps) / 1e6, 1),
+            "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+            "loss": loss_val,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default="iwae", choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="vaekit", choices=["vaekit", "reference"])
+    ap.add_argument("--cpu-sample", type=int, default=0, help="batch of the bounded CPU-baseline sample")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    wl = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        run_reference_arm(args, wl)
+    else:
+        run_gpu_arm(args, wl)
+
+
+if __name__ == "__main__":
+    main()

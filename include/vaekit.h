@@ -1,0 +1,144 @@
+/*
+ * vaekit.h -- C ABI of libvaekit.so: the B200 (sm_100a) kernels behind the
+ * stochastic-latent + loss hot path of bplaut/PyTorch-VAE.
+ *
+ * The reference has no FFI of its own (it is pure Python over torch); the
+ * boundary it offers is the method surface of its BaseVAE subclasses
+ * (models/base.py:5-28).  Each entry point below replaces the ATen call
+ * sequence of the cited reference lines; the Python host layer
+ * (pytorch-vae_b200/vaekit) binds them with ctypes and exposes the reference's
+ * method names on top.
+ *
+ * Conventions (all entry points):
+ *   - plain C types only; every pointer is a DEVICE pointer to fp32 data
+ *     unless the parameter name ends in _host;
+ *   - returns 0 on success, a negative VK_ERR_* otherwise; never throws,
+ *     never allocates, never synchronises the stream;
+ *   - `stream` is a cudaStream_t passed as void*; work is enqueued on it;
+ *   - workspaces are caller-provided; vk_workspace_bytes() gives the size.  The
+ *     first VK_WS_HEADER_BYTES of a workspace must be ZERO on first use and are
+ *     left zero by every call (self-resetting tickets), so one zero-initialised
+ *     buffer per stream can be reused for all calls;
+ *   - tensors are dense row-major unless strides are passed explicitly.
+ *
+ * RNG contract: noise is a pure function of (seed, offset, element index):
+ *   quad q = element/4 draws Philox4x32-10 with counter (lo32(q+offset),
+ *   hi32(q+offset), 0, 0) and key (lo32(seed), hi32(seed)); the four words give
+ *   four normals by Box-Muller on 23-bit uniforms (oracle/vae_oracle.py
+ *   philox_normal is the CPU statement of the same stream).  The result does
+ *   not depend on launch geometry or on how a batch is sharded over GPUs.
+ */
+#ifndef VAEKIT_H_
+#define VAEKIT_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VK_OK                 0
+#define VK_ERR_BAD_ARG       -1   /* null pointer, negative size, misaligned, unknown mode */
+#define VK_ERR_UNSUPPORTED   -2   /* shape outside what the kernel was built for */
+#define VK_ERR_WORKSPACE     -3   /* workspace too small */
+#define VK_ERR_CUDA          -4   /* launch / runtime error, see vk_last_error_string() */
+
+#define VK_WS_HEADER_BYTES   256
+
+int         vk_version(void);             /* major*10000 + minor*100 + patch */
+const char* vk_last_error_string(void);   /* thread-local, valid until the next failing call */
+/* Generic upper bound for the reduction workspaces of the streaming ops. */
+int64_t     vk_workspace_bytes(void);
+
+/* ---------------------------------------------------------------------------
+ * K1  reparameterize + Gaussian KL          (reference: models/vanilla_vae.py:107-117,
+ *     beta_vae.py:112-122, logcosh_vae.py:108-118, iwae.py:111-119, miwae.py:114-122,
+ *     betatc_vae.py:115-125; KL rows: vanilla_vae.py:143 inner sum, iwae.py:150)
+ *
+ * mu / log_var are addressed as rows of D contiguous floats; row r of the
+ * logical [n0,n1,n2] outer grid (r = (i0*n1 + i1)*n2 + i2) starts at element
+ * i0*s[0] + i1*s[1] + i2*s[2]  (this covers the IWAE/MIWAE repeat().permute()
+ * views, iwae.py:123-124, without materialising them).
+ *   z        [rows, D] dense, or NULL      z = eps * exp(0.5*log_var) + mu
+ *   kl_rows  [rows]    or NULL             -0.5 * sum_d(1 + lv - mu^2 - exp(lv))
+ *   eps_out  [rows, D] dense, or NULL      the noise used (for oracle injection)
+ * If z and eps_out are both NULL no noise is generated (KL-only mode).
+ * -------------------------------------------------------------------------*/
+int vk_reparam_kl_fwd(const float* mu, const float* log_var,
+                      const int64_t* outer_host /*[3]*/, const int64_t* mu_strides_host /*[3]*/,
+                      const int64_t* lv_strides_host /*[3]*/, int64_t D,
+                      uint64_t seed, uint64_t offset,
+                      float* z, float* kl_rows, float* eps_out, void* stream);
+
+/* Backward of the above.  g_z [rows,D] dense or NULL; g_kl [rows] or NULL.
+ *   g_mu = g_z + g_kl * mu ;  g_lv = g_z * eps * 0.5 * exp(0.5 lv) - 0.5 * g_kl * (1 - exp(lv))
+ * eps is regenerated from (seed, offset).  g_mu / g_lv are dense [rows, D]. */
+int vk_reparam_kl_bwd(const float* g_z, const float* g_kl, const float* mu, const float* log_var,
+                      const int64_t* outer_host, const int64_t* mu_strides_host,
+                      const int64_t* lv_strides_host, int64_t D,
+                      uint64_t seed, uint64_t offset,
+                      float* g_mu, float* g_lv, void* stream);
+
+/* Standard-normal fill with the contract stream (prior_z of wae_mmd.py:195 / swae.py:165). */
+int vk_philox_normal(float* out, int64_t numel, uint64_t seed, uint64_t offset, void* stream);
+/* Raw Philox words, [n_quads,4] uint32 -- for the bit-exact stream test. */
+int vk_philox_raw(uint32_t* out, int64_t n_quads, uint64_t seed, uint64_t offset, void* stream);
+
+/* ---------------------------------------------------------------------------
+ * K2  reconstruction term + KL combine       (reference: vanilla_vae.py:134-146,
+ *     beta_vae.py:129-152, logcosh_vae.py:125-155, betatc_vae.py:163,
+ *     swae.py:121-122, wae_mmd.py:118, vq_vae.py:205)
+ *
+ * recon_mode: what out[1] is
+ *   VK_RECON_MSE_MEAN     mean((r-x)^2)
+ *   VK_RECON_MSE_SUM      sum((r-x)^2)
+ *   VK_RECON_LOGCOSH      (1/alpha) * mean(alpha*t + log(1+exp(-2 alpha t)) - log 2), t = r-x
+ *   VK_RECON_MSE_L1_MEAN  mean((r-x)^2) + mean(|r-x|)
+ * combine_mode: what out[0] is (kld = mean(kl_rows); ignored when kl_rows is NULL)
+ *   VK_COMBINE_NONE       out[0] = out[1]
+ *   VK_COMBINE_LINEAR     out[0] = out[1] + w * kld
+ *   VK_COMBINE_ABS        out[0] = out[1] + w * |kld - C|
+ * out[4] = { loss, recon_loss, kld, -kld }.
+ * -------------------------------------------------------------------------*/
+enum { VK_RECON_MSE_MEAN = 0, VK_RECON_MSE_SUM = 1, VK_RECON_LOGCOSH = 2, VK_RECON_MSE_L1_MEAN = 3 };
+enum { VK_COMBINE_NONE = 0, VK_COMBINE_LINEAR = 1, VK_COMBINE_ABS = 2 };
+
+int vk_elbo_fwd(const float* recons, const float* input, int64_t numel,
+                const float* kl_rows, int64_t rows,
+                int recon_mode, float alpha, int combine_mode, float w, float C,
+                float* out /*[4]*/, void* workspace, int64_t workspace_bytes, void* stream);
+
+/* Backward.  g_loss/g_recon/g_kld/g_negkld: device pointers to the upstream
+ * scalar gradients of out[0..3], each may be NULL (= 0).  `out` is the forward
+ * result (sign of kld - C).  g_recons [numel] and g_kl_rows [rows] may be NULL. */
+int vk_elbo_bwd(const float* recons, const float* input, int64_t numel, int64_t rows,
+                int recon_mode, float alpha, int combine_mode, float w, float C,
+                const float* out, const float* g_loss, const float* g_recon,
+                const float* g_kld, const float* g_negkld,
+                float* g_recons, float* g_kl_rows, void* stream);
+
+/* ---------------------------------------------------------------------------
+ * K3  IWAE / MIWAE importance-weighted bound   (reference: iwae.py:129-160,
+ *     miwae.py:132-164; closed-form backward: SURVEY.md A.2)
+ *
+ * recons [B, G, K, P] dense (G = num_estimates, 1 for IWAE), input [B, P] is
+ * broadcast over (G, K) in-kernel (the reference materialises the repeat,
+ * iwae.py:145).  kl [B*G*K] are the KL rows of K1.
+ *   lp[b,g,k] = mean_P (r - x)^2 ;  lw = lp + M_N*kl ;  w = softmax_k(lw)
+ *   out[4] = { mean_{b,g} sum_k w*lw,  mean(lp),  mean(kl),  -mean(kl) }
+ * lp_out [B*G*K] is saved for the backward.
+ * -------------------------------------------------------------------------*/
+int vk_iw_bound_fwd(const float* recons, const float* input, const float* kl,
+                    int64_t B, int64_t G, int64_t K, int64_t P, float M_N,
+                    float* lp_out, float* out /*[4]*/,
+                    void* workspace, int64_t workspace_bytes, void* stream);
+
+int vk_iw_bound_bwd(const float* recons, const float* input, const float* lp, const float* kl,
+                    int64_t B, int64_t G, int64_t K, int64_t P, float M_N,
+                    const float* g_loss, const float* g_recon, const float* g_kld, const float* g_negkld,
+                    float* g_recons /*[B,G,K,P] or NULL*/, float* g_kl /*[B*G*K] or NULL*/, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VAEKIT_H_ */

@@ -77,14 +77,15 @@ def philox_uint32(seed: int, offset: int, n_quads: int, first_quad: int = 0) -> 
 
 
 def philox_normal(seed: int, offset: int, numel: int) -> np.ndarray:
-    """fp32 standard normals for elements [0, numel): element 4q+c uses words of
-    quad q; Box-Muller pairs (w0,w1)->(n0,n1), (w2,w3)->(n2,n3) with
-    u = (w + 0.5) * 2^-32 in (0,1), r = sqrt(-2 ln u_a), theta = 2 pi u_b.
-    Float part is evaluated in float64 then rounded: the CUDA kernel's fp32
-    intrinsics agree to a few ulp, so compare with a tolerance, not bit-wise."""
+    """fp32 standard normals for elements [0, numel): element 4q+c uses the words of
+    quad q; Box-Muller pairs (w0,w1)->(n0,n1), (w2,w3)->(n2,n3) with the 23-bit
+    uniform u = ((w >> 9) + 0.5) * 2^-23 in (0,1) (exactly representable in
+    fp32), r = sqrt(-2 ln u_a), (n_even, n_odd) = r * (cos, sin)(2 pi u_b).
+    Evaluated in float64 then rounded: the CUDA kernel's fp32 logf/sincospif
+    agree to a few ulp, so compare with a small tolerance, not bit-wise."""
     nq = (numel + 3) // 4
-    w = philox_uint32(seed, offset, nq).astype(np.float64)
-    u = (w + 0.5) * (2.0 ** -32)
+    w = philox_uint32(seed, offset, nq)
+    u = ((w >> np.uint32(9)).astype(np.float64) + 0.5) * (2.0 ** -23)
     r0 = np.sqrt(-2.0 * np.log(u[:, 0]))
     r1 = np.sqrt(-2.0 * np.log(u[:, 2]))
     t0 = 2.0 * np.pi * u[:, 1]
@@ -153,9 +154,12 @@ def logcosh_loss(recons: Tensor, input: Tensor, mu: Tensor, log_var: Tensor, M_N
 # --------------------------------------------------------------------------
 def iw_bound_loss(recons: Tensor, input: Tensor, mu: Tensor, log_var: Tensor, M_N: float) -> Dict[str, Tensor]:
     """iwae.py:145-160 (recons [B,S,C,H,W]) and miwae.py:148-164 (recons [B,M,S,C,H,W]).
-    The input image is broadcast (the reference materialises a repeat, iwae.py:145)."""
+    input is [B,C,H,W]."""
     nd = recons.dim() - input.dim()          # 1 for IWAE, 2 for MIWAE
-    x = input.view(input.shape[0], *([1] * nd), *input.shape[1:])
+    if nd == 1:                              # iwae.py:145 (materialised repeat, as the reference does)
+        x = input.repeat(recons.shape[1], 1, 1, 1, 1).permute(1, 0, 2, 3, 4)
+    else:                                    # miwae.py:148-149
+        x = input.repeat(recons.shape[1], recons.shape[2], 1, 1, 1, 1).permute(2, 0, 1, 3, 4, 5)
     log_p_x_z = ((recons - x) ** 2).flatten(1 + nd).mean(-1)
     kld = kld_rows(mu, log_var)
     log_weight = log_p_x_z + M_N * kld

@@ -1,0 +1,122 @@
+"""ctypes binding of libvaekit.so (include/vaekit.h).  There is NO fallback: if the
+library is missing or a call fails, a RuntimeError is raised."""
+import ctypes as C
+import os
+import threading
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "_lib", "libvaekit.so")
+
+_p = C.c_void_p
+_i64 = C.c_int64
+_u64 = C.c_uint64
+_f = C.c_float
+_i = C.c_int
+
+_SIGNATURES = {
+    "vk_version": ([], _i),
+    "vk_last_error_string": ([], C.c_char_p),
+    "vk_workspace_bytes": ([], _i64),
+    "vk_reparam_kl_fwd": ([_p, _p, _p, _p, _p, _i64, _u64, _u64, _p, _p, _p, _p], _i),
+    "vk_reparam_kl_bwd": ([_p, _p, _p, _p, _p, _p, _p, _i64, _u64, _u64, _p, _p, _p], _i),
+    "vk_philox_normal": ([_p, _i64, _u64, _u64, _p], _i),
+    "vk_philox_raw": ([_p, _i64, _u64, _u64, _p], _i),
+    "vk_elbo_fwd": ([_p, _p, _i64, _p, _i64, _i, _f, _i, _f, _f, _p, _p, _i64, _p], _i),
+    "vk_elbo_bwd": ([_p, _p, _i64, _i64, _i, _f, _i, _f, _f, _p, _p, _p, _p, _p, _p, _p, _p], _i),
+    "vk_iw_bound_fwd": ([_p, _p, _p, _i64, _i64, _i64, _i64, _f, _p, _p, _p, _i64, _p], _i),
+    "vk_iw_bound_bwd": ([_p, _p, _p, _p, _i64, _i64, _i64, _i64, _f, _p, _p, _p, _p, _p, _p, _p], _i),
+}
+
+_lib = None
+_lock = threading.Lock()
+
+
+def lib():
+    """The loaded shared library (loads on first use; raises if it was never built)."""
+    global _lib
+    if _lib is None:
+        with _lock:
+            if _lib is None:
+                if not os.path.exists(LIB_PATH):
+                    raise RuntimeError(
+                        "vaekit: %s not found -- build it with `python pytorch-vae_b200/build.py` "
+                        "(there is no CPU or eager fallback)" % LIB_PATH)
+                handle = C.CDLL(LIB_PATH)
+                for name, (args, res) in _SIGNATURES.items():
+                    fn = getattr(handle, name)      # AttributeError if the symbol is missing
+                    fn.argtypes = args
+                    fn.restype = res
+                _lib = handle
+    return _lib
+
+
+def declared_symbols():
+    return sorted(_SIGNATURES)
+
+
+def check(rc, what):
+    if rc != 0:
+        msg = lib().vk_last_error_string().decode("utf-8", "replace")
+        raise RuntimeError("vaekit %s failed (%d): %s" % (what, rc, msg))
+
+
+EVENT_LOG = None      # set to a list to get (name, start_event, end_event) per kernel launch
+LAUNCHES = 0          # number of libvaekit kernel launches made by this process
+
+
+def call(name, *args):
+    """Invoke vk_<name>(*args) on the current device/stream; raises on a non-zero return code."""
+    global LAUNCHES
+    fn = getattr(lib(), "vk_" + name)
+    if EVENT_LOG is None:
+        rc = fn(*args)
+    else:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        rc = fn(*args)
+        e1.record()
+        EVENT_LOG.append((name, e0, e1))
+    LAUNCHES += 1
+    check(rc, name)
+
+
+def ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def stream_ptr():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def require(t, name, dims=None):
+    """Host-side argument policy (SURVEY 8(b) 'Errors'): CUDA fp32 tensors only."""
+    if not isinstance(t, torch.Tensor):
+        raise RuntimeError("vaekit: %s must be a tensor" % name)
+    if not t.is_cuda:
+        raise RuntimeError("vaekit: %s must be a CUDA tensor (no CPU fallback), got %s" % (name, t.device))
+    if t.dtype != torch.float32:
+        raise RuntimeError("vaekit: %s must be float32, got %s" % (name, t.dtype))
+    if dims is not None and t.dim() not in dims:
+        raise RuntimeError("vaekit: %s must have %s dims, got %d" % (name, dims, t.dim()))
+    return t
+
+
+_workspaces = {}
+
+
+def workspace(device, min_bytes=0):
+    """Zero-initialised scratch buffer, one per (device, stream); kernels leave the
+    ticket header zeroed, so it is reused across calls without a memset."""
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    need = max(int(lib().vk_workspace_bytes()), int(min_bytes))
+    ws = _workspaces.get(key)
+    if ws is None or ws.numel() < need:
+        ws = torch.zeros(need, dtype=torch.uint8, device=device)
+        _workspaces[key] = ws
+    return ws
+
+
+def i64x3(vals):
+    return (C.c_int64 * 3)(*[int(v) for v in vals])

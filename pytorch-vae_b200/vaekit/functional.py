@@ -1,0 +1,213 @@
+"""torch.autograd glue over the C-ABI kernels.  Each Function enqueues exactly one
+kernel forward and one backward; nothing here computes on the CPU."""
+import torch
+
+from . import _lib as L
+
+RECON_MSE_MEAN, RECON_MSE_SUM, RECON_LOGCOSH, RECON_MSE_L1_MEAN = 0, 1, 2, 3
+COMBINE_NONE, COMBINE_LINEAR, COMBINE_ABS = 0, 1, 2
+
+
+# ---------------------------------------------------------------------------
+# RNG: (seed, offset) drawn from torch's CUDA generator so torch.manual_seed
+# governs the noise; the stream itself is vaekit's own (include/vaekit.h).
+# ---------------------------------------------------------------------------
+def next_philox(device, numel):
+    """Reserve ceil(numel/4) Philox quads on `device`'s default generator."""
+    gen = torch.cuda.default_generators[device.index if device.index is not None else torch.cuda.current_device()]
+    seed, offset = gen.initial_seed(), gen.get_offset()
+    quads = (int(numel) + 3) // 4
+    gen.set_offset(offset + ((quads + 3) // 4) * 4)     # torch requires multiples of 4
+    return seed & 0xFFFFFFFFFFFFFFFF, offset
+
+
+def _row_layout(t):
+    """(outer[3], strides[3], D, tensor) for a tensor addressed as rows of D contiguous floats."""
+    if t.dim() == 0:
+        t = t.reshape(1, 1)
+    if t.dim() == 1:
+        t = t.unsqueeze(0)
+    if t.dim() > 4 or (t.shape[-1] > 1 and t.stride(-1) != 1):
+        t = t.contiguous()
+    outer = list(t.shape[:-1])
+    strides = list(t.stride()[:-1])
+    pad = 3 - len(outer)
+    return [1] * pad + outer, [0] * pad + strides, t.shape[-1], t
+
+
+class _ReparamKL(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, mu, log_var, seed, offset, want_z, want_kl, want_eps):
+        L.require(mu, "mu"); L.require(log_var, "logvar")
+        if mu.shape != log_var.shape:
+            raise RuntimeError("vaekit: mu %s and logvar %s differ in shape" % (tuple(mu.shape), tuple(log_var.shape)))
+        outer, ms, D, mu_v = _row_layout(mu)
+        _, ls, _, lv_v = _row_layout(log_var)
+        rows = outer[0] * outer[1] * outer[2]
+        dev = mu.device
+        z = torch.empty(mu.shape, dtype=torch.float32, device=dev) if want_z else None
+        kl = torch.empty(mu.shape[:-1], dtype=torch.float32, device=dev) if want_kl else None
+        eps = torch.empty(mu.shape, dtype=torch.float32, device=dev) if want_eps else None
+        if rows * D > 0:
+            with torch.cuda.device(dev):
+                L.call("reparam_kl_fwd", L.ptr(mu_v), L.ptr(lv_v), L.i64x3(outer), L.i64x3(ms), L.i64x3(ls), D,
+                                               seed, offset, L.ptr(z), L.ptr(kl), L.ptr(eps), L.stream_ptr())
+        ctx.save_for_backward(mu, log_var)
+        ctx.rng = (seed, offset)
+        ctx.had_z = want_z
+        ctx.set_materialize_grads(False)
+        if eps is not None:
+            ctx.mark_non_differentiable(eps)
+        return z, kl, eps
+
+    @staticmethod
+    def backward(ctx, g_z, g_kl, _g_eps):
+        mu, log_var = ctx.saved_tensors
+        outer, ms, D, mu_v = _row_layout(mu)
+        _, ls, _, lv_v = _row_layout(log_var)
+        dev = mu.device
+        g_mu = torch.empty(mu.shape, dtype=torch.float32, device=dev)
+        g_lv = torch.empty(mu.shape, dtype=torch.float32, device=dev)
+        if g_z is not None:
+            g_z = g_z.contiguous()
+        if g_kl is not None:
+            g_kl = g_kl.contiguous()
+        if g_mu.numel() > 0:
+            with torch.cuda.device(dev):
+                L.call("reparam_kl_bwd", L.ptr(g_z), L.ptr(g_kl), L.ptr(mu_v), L.ptr(lv_v), L.i64x3(outer),
+                                               L.i64x3(ms), L.i64x3(ls), D, ctx.rng[0], ctx.rng[1], L.ptr(g_mu),
+                                               L.ptr(g_lv), L.stream_ptr())
+        return g_mu, g_lv, None, None, None, None, None
+
+
+def reparam_kl(mu, log_var, *, rng=None, want_kl=True, want_eps=False):
+    """z = eps*exp(0.5*logvar)+mu with the KL rows as a fused second output.
+    Returns (z, kl_rows, eps_or_None); rng = (seed, offset) or None to draw from torch's generator."""
+    if rng is None:
+        rng = next_philox(mu.device, mu.numel())
+    return _ReparamKL.apply(mu, log_var, rng[0], rng[1], True, want_kl, want_eps)
+
+
+def kl_rows(mu, log_var):
+    """-0.5*sum_d(1+lv-mu^2-exp(lv)) per row (no noise drawn)."""
+    return _ReparamKL.apply(mu, log_var, 0, 0, False, True, False)[1]
+
+
+def philox_normal(shape, device, rng=None):
+    """Standard normals from the contract stream (the prior_z draws of WAE / SWAE)."""
+    out = torch.empty(shape, dtype=torch.float32, device=device)
+    if rng is None:
+        rng = next_philox(out.device, out.numel())
+    with torch.cuda.device(out.device):
+        L.call("philox_normal", L.ptr(out), out.numel(), rng[0], rng[1], L.stream_ptr())
+    return out
+
+
+def philox_raw(n_quads, device, seed, offset):
+    out = torch.empty((n_quads, 4), dtype=torch.int32, device=device)
+    with torch.cuda.device(out.device):
+        L.call("philox_raw", L.ptr(out), n_quads, seed, offset, L.stream_ptr())
+    return out
+
+
+# ---------------------------------------------------------------------------
+# K2
+# ---------------------------------------------------------------------------
+class _Elbo(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, recons, input, kl, recon_mode, alpha, combine_mode, w, C):
+        L.require(recons, "recons"); L.require(input, "input")
+        if recons.shape != input.shape:
+            raise RuntimeError("vaekit: recons %s and input %s differ in shape" % (tuple(recons.shape), tuple(input.shape)))
+        if recons.numel() == 0:
+            raise RuntimeError("vaekit: empty reconstruction tensor")
+        r, x = recons.contiguous(), input.contiguous()
+        klc = None
+        if kl is not None:
+            klc = L.require(kl, "kl_rows").contiguous()
+        dev = recons.device
+        out = torch.empty(4, dtype=torch.float32, device=dev)
+        ws = L.workspace(dev)
+        with torch.cuda.device(dev):
+            L.call("elbo_fwd", L.ptr(r), L.ptr(x), r.numel(), L.ptr(klc), 0 if klc is None else klc.numel(),
+                                     recon_mode, alpha, combine_mode, w, C, L.ptr(out), L.ptr(ws), ws.numel(),
+                                     L.stream_ptr())
+        ctx.save_for_backward(r, x, out)
+        ctx.cfg = (recon_mode, alpha, combine_mode, w, C, None if klc is None else tuple(kl.shape))
+        ctx.set_materialize_grads(False)
+        return out[0], out[1], out[2], out[3]
+
+    @staticmethod
+    def backward(ctx, g0, g1, g2, g3):
+        r, x, out = ctx.saved_tensors
+        recon_mode, alpha, combine_mode, w, C, kl_shape = ctx.cfg
+        dev = r.device
+        need_r, need_x, need_kl = ctx.needs_input_grad[0], ctx.needs_input_grad[1], ctx.needs_input_grad[2]
+        g_rec = torch.empty_like(r) if (need_r or need_x) else None
+        g_kl = torch.empty(kl_shape, dtype=torch.float32, device=dev) if (need_kl and kl_shape is not None) else None
+        gs = [None if g is None else g.contiguous() for g in (g0, g1, g2, g3)]
+        rows = 0 if kl_shape is None else max(1, int(torch.Size(kl_shape).numel()))
+        with torch.cuda.device(dev):
+            L.call("elbo_bwd", L.ptr(r), L.ptr(x), r.numel(), rows, recon_mode, alpha, combine_mode, w, C,
+                                     L.ptr(out), L.ptr(gs[0]), L.ptr(gs[1]), L.ptr(gs[2]), L.ptr(gs[3]),
+                                     L.ptr(g_rec), L.ptr(g_kl), L.stream_ptr())
+        return (g_rec if need_r else None, (-g_rec) if need_x else None, g_kl, None, None, None, None, None)
+
+
+def elbo(recons, input, kl=None, *, recon_mode=RECON_MSE_MEAN, alpha=1.0, combine_mode=COMBINE_NONE, w=0.0, C=0.0):
+    """Returns (loss, recon_loss, kld, -kld) as 0-dim tensors sharing one 16-byte buffer."""
+    return _Elbo.apply(recons, input, kl, int(recon_mode), float(alpha), int(combine_mode), float(w), float(C))
+
+
+# ---------------------------------------------------------------------------
+# K3
+# ---------------------------------------------------------------------------
+class _IwBound(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, recons, input, kl, M_N):
+        L.require(recons, "recons"); L.require(input, "input"); L.require(kl, "kl_rows")
+        nd = recons.dim() - input.dim()
+        if nd not in (1, 2) or recons.shape[0] != input.shape[0] or recons.shape[1 + nd:] != input.shape[1:]:
+            raise RuntimeError("vaekit: recons %s is not input %s with 1 or 2 sample dims" %
+                               (tuple(recons.shape), tuple(input.shape)))
+        if tuple(kl.shape) != tuple(recons.shape[:1 + nd]):
+            raise RuntimeError("vaekit: kl rows %s do not match recons sample dims %s" %
+                               (tuple(kl.shape), tuple(recons.shape[:1 + nd])))
+        B = recons.shape[0]
+        G = recons.shape[1] if nd == 2 else 1
+        K = recons.shape[nd]
+        P = input[0].numel() if B > 0 else 0
+        if B * G * K * P == 0:
+            raise RuntimeError("vaekit: empty input to the importance-weighted bound")
+        r, x, klc = recons.contiguous(), input.contiguous(), kl.contiguous()
+        dev = recons.device
+        lp = torch.empty(kl.shape, dtype=torch.float32, device=dev)
+        out = torch.empty(4, dtype=torch.float32, device=dev)
+        ws = L.workspace(dev, 256 + 24 * B)
+        with torch.cuda.device(dev):
+            L.call("iw_bound_fwd", L.ptr(r), L.ptr(x), L.ptr(klc), B, G, K, P, M_N, L.ptr(lp), L.ptr(out),
+                                         L.ptr(ws), ws.numel(), L.stream_ptr())
+        ctx.save_for_backward(r, x, klc, lp)
+        ctx.cfg = (B, G, K, P, M_N)
+        ctx.set_materialize_grads(False)
+        return out[0], out[1], out[2], out[3]
+
+    @staticmethod
+    def backward(ctx, g0, g1, g2, g3):
+        r, x, klc, lp = ctx.saved_tensors
+        B, G, K, P, M_N = ctx.cfg
+        if ctx.needs_input_grad[1]:
+            raise RuntimeError("vaekit: gradient w.r.t. the input image of the IW bound is not provided")
+        g_rec = torch.empty_like(r) if ctx.needs_input_grad[0] else None
+        g_kl = torch.empty_like(klc) if ctx.needs_input_grad[2] else None
+        gs = [None if g is None else g.contiguous() for g in (g0, g1, g2, g3)]
+        with torch.cuda.device(r.device):
+            L.call("iw_bound_bwd", L.ptr(r), L.ptr(x), L.ptr(lp), L.ptr(klc), B, G, K, P, M_N, L.ptr(gs[0]),
+                                         L.ptr(gs[1]), L.ptr(gs[2]), L.ptr(gs[3]), L.ptr(g_rec), L.ptr(g_kl),
+                                         L.stream_ptr())
+        return g_rec, None, g_kl, None
+
+
+def iw_bound(recons, input, kl, M_N):
+    """(loss, mean log_p_x_z, mean kl, -mean kl) of iwae.py:145-160 / miwae.py:148-164."""
+    return _IwBound.apply(recons, input, kl, float(M_N))

@@ -1,0 +1,19 @@
+"""Model registry with the reference's keys (models/__init__.py:65-91) for the classes on the
+hot path; the remaining reference variants are out of scope."""
+from .base import BaseVAE
+from .vanilla_vae import VanillaVAE
+from .beta_vae import BetaVAE
+from .logcosh_vae import LogCoshVAE
+from .iwae import IWAE
+from .miwae import MIWAE
+
+VAE = VanillaVAE
+GaussianVAE = VanillaVAE
+
+vae_models = {
+    'IWAE': IWAE,
+    'MIWAE': MIWAE,
+    'BetaVAE': BetaVAE,
+    'LogCoshVAE': LogCoshVAE,
+    'VanillaVAE': VanillaVAE,
+}
