@@ -2,7 +2,7 @@
 // Replaces models/iwae.py:145-158 and models/miwae.py:148-162: the reference
 // materialises input.repeat(K) (1 GB at B=4096,K=5), then makes >= 4 passes over
 // the [B,K,P] tensors.  Here one CTA owns one batch item: the input image is
-// staged once in shared memory and every one of its G*K reconstructions is
+// held in registers column by column and every one of its G*K reconstructions is
 // streamed past it exactly once (forward: read-only; backward: read + write
 // g_recons).  softmax over K and the closed-form backward run in
 // registers of a few threads; there is no [B,K,P] temporary at all.
@@ -14,52 +14,6 @@ struct IwParams {
   int64_t B, G, K, P;
   float M_N;
 };
-
-// sum over one reconstruction of (r - x)^2, x from shared memory (or global when it does not fit)
-template <bool XS>
-__device__ __forceinline__ float sq_diff_partial(const float* __restrict__ r, const float* __restrict__ xg,
-                                                 const float* xs, int64_t P, bool vec) {
-  float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-  const int t = threadIdx.x, nt = blockDim.x;
-  const int64_t nvec = vec ? (P >> 2) : 0;
-  const float4* r4 = reinterpret_cast<const float4*>(r);
-  const float4* x4 = reinterpret_cast<const float4*>(XS ? xs : xg);
-  int64_t i = t;
-  for (; i + 3 * nt < nvec; i += 4 * nt) {
-    float4 rv[4];
-#pragma unroll
-    for (int u = 0; u < 4; ++u) rv[u] = ldg_stream(r4 + i + u * nt);
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const float4 x = x4[i + u * nt];
-      const float d0 = rv[u].x - x.x, d1 = rv[u].y - x.y, d2 = rv[u].z - x.z, d3 = rv[u].w - x.w;
-      a0 += d0 * d0; a1 += d1 * d1; a2 += d2 * d2; a3 += d3 * d3;
-    }
-  }
-  for (; i < nvec; i += nt) {
-    const float4 rv = ldg_stream(r4 + i);
-    const float4 x = x4[i];
-    const float d0 = rv.x - x.x, d1 = rv.y - x.y, d2 = rv.z - x.z, d3 = rv.w - x.w;
-    a0 += d0 * d0; a1 += d1 * d1; a2 += d2 * d2; a3 += d3 * d3;
-  }
-  const float* xsrc = XS ? xs : xg;
-  for (int64_t j = 4 * nvec + t; j < P; j += nt) {
-    const float d = r[j] - xsrc[j];
-    a0 += d * d;
-  }
-  return (a0 + a1) + (a2 + a3);
-}
-
-template <bool XS>
-__device__ __forceinline__ void stage_input(const float* __restrict__ xg, float* xs, int64_t P, bool vec) {
-  if (!XS) return;
-  const int t = threadIdx.x, nt = blockDim.x;
-  const int64_t nvec = vec ? (P >> 2) : 0;
-  for (int64_t i = t; i < nvec; i += nt)
-    reinterpret_cast<float4*>(xs)[i] = ldg_stream(reinterpret_cast<const float4*>(xg) + i);
-  for (int64_t j = 4 * nvec + t; j < P; j += nt) xs[j] = xg[j];
-  __syncthreads();
-}
 
 // softmax statistics of one (b,g) row held by one thread
 __device__ __forceinline__ void row_stats(const float* lp, const float* kl, int64_t K, float M_N, float& mx,
@@ -77,9 +31,13 @@ __device__ __forceinline__ void row_stats(const float* lp, const float* kl, int6
   S = num / denom;
 }
 
-// dynamic smem: [P floats input (if XS)] [GK * nwarps floats warp partials] [GK floats lp]
-template <bool XS>
-__global__ void __launch_bounds__(256)
+constexpr int kSC = 8;   // reconstructions processed together per pixel column (independent loads in flight)
+
+// Column-major traversal: a thread owns pixel columns i = t, t+nt, ...; for each column the input pixel
+// quad is loaded ONCE into registers and the same column of up to kSC reconstructions is streamed past it,
+// so kSC independent 128-bit loads are in flight per thread and nothing is staged in shared memory.
+// dynamic smem: [GK * nwarps floats warp partials] [GK floats lp]
+__global__ void __launch_bounds__(256, 3)
 iw_bound_fwd_kernel(const float* __restrict__ recons, const float* __restrict__ input, const float* __restrict__ kl,
                     IwParams p, float* __restrict__ lp_out, float* __restrict__ out,
                     unsigned int* __restrict__ ticket, double* __restrict__ partials) {
@@ -88,26 +46,65 @@ iw_bound_fwd_kernel(const float* __restrict__ recons, const float* __restrict__ 
   const int64_t b = blockIdx.x;
   const int64_t GK = p.G * p.K;
   const int nw = blockDim.x >> 5, wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int64_t Ppad = XS ? ((p.P + 3) & ~(int64_t)3) : 0;
-  float* xs = smem;
-  float* wpart = smem + Ppad;
+  const int t = threadIdx.x, nt = blockDim.x;
+  float* wpart = smem;
   float* lps = wpart + GK * nw;
   const float* xg = input + b * p.P;
   const float* rb = recons + b * GK * p.P;
   const bool vec = (p.P % 4 == 0) &&
                    (((reinterpret_cast<uintptr_t>(recons) | reinterpret_cast<uintptr_t>(input)) & 15) == 0);
-  stage_input<XS>(xg, xs, p.P, vec);
-  for (int64_t s = 0; s < GK; ++s) {
-    float v = sq_diff_partial<XS>(rb + s * p.P, xg, xs, p.P, vec);
-    v = warp_sum(v);
-    if (lane == 0) wpart[s * nw + wid] = v;
+  const int64_t nvec = vec ? (p.P >> 2) : 0;
+  const float4* x4 = reinterpret_cast<const float4*>(xg);
+  for (int64_t s0 = 0; s0 < GK; s0 += kSC) {
+    const int ns = (int)((GK - s0 < kSC) ? (GK - s0) : kSC);
+    float acc[kSC];
+#pragma unroll
+    for (int j = 0; j < kSC; ++j) acc[j] = 0.f;
+    if (ns == kSC) {
+      for (int64_t i = t; i < nvec; i += nt) {
+        const float4 x = __ldg(x4 + i);
+        float4 rv[kSC];
+#pragma unroll
+        for (int j = 0; j < kSC; ++j) rv[j] = ldg_stream(reinterpret_cast<const float4*>(rb + (s0 + j) * p.P) + i);
+#pragma unroll
+        for (int j = 0; j < kSC; ++j) {
+          const float d0 = rv[j].x - x.x, d1 = rv[j].y - x.y, d2 = rv[j].z - x.z, d3 = rv[j].w - x.w;
+          acc[j] += (d0 * d0 + d1 * d1) + (d2 * d2 + d3 * d3);
+        }
+      }
+    } else {
+      for (int64_t i = t; i < nvec; i += nt) {
+        const float4 x = __ldg(x4 + i);
+        float4 rv[kSC];
+#pragma unroll
+        for (int j = 0; j < kSC; ++j)
+          if (j < ns) rv[j] = ldg_stream(reinterpret_cast<const float4*>(rb + (s0 + j) * p.P) + i);
+#pragma unroll
+        for (int j = 0; j < kSC; ++j)
+          if (j < ns) {
+            const float d0 = rv[j].x - x.x, d1 = rv[j].y - x.y, d2 = rv[j].z - x.z, d3 = rv[j].w - x.w;
+            acc[j] += (d0 * d0 + d1 * d1) + (d2 * d2 + d3 * d3);
+          }
+      }
+    }
+    for (int64_t i = 4 * nvec + t; i < p.P; i += nt) {     // scalar tail / unaligned path
+      const float x = xg[i];
+#pragma unroll
+      for (int j = 0; j < kSC; ++j)
+        if (j < ns) { const float d = rb[(s0 + j) * p.P + i] - x; acc[j] += d * d; }
+    }
+#pragma unroll
+    for (int j = 0; j < kSC; ++j) {
+      const float v = warp_sum(acc[j]);
+      if (lane == 0 && j < ns) wpart[(s0 + j) * nw + wid] = v;
+    }
   }
   __syncthreads();
   const float invP = 1.0f / (float)p.P;
   for (int64_t s = threadIdx.x; s < GK; s += blockDim.x) {
-    float t = 0.f;
-    for (int w = 0; w < nw; ++w) t += wpart[s * nw + w];
-    const float lp = t * invP;
+    float tt = 0.f;
+    for (int w = 0; w < nw; ++w) tt += wpart[s * nw + w];
+    const float lp = tt * invP;
     lps[s] = lp;
     lp_out[b * GK + s] = lp;
   }
@@ -129,28 +126,27 @@ iw_bound_fwd_kernel(const float* __restrict__ recons, const float* __restrict__ 
     partials[3 * b + 2] = v[2];
   }
   if (last_block_ticket(ticket, gridDim.x)) {
-    double t[3] = {0.0, 0.0, 0.0};
+    double tt[3] = {0.0, 0.0, 0.0};
     for (int64_t i = threadIdx.x; i < p.B; i += blockDim.x) {
-      t[0] += partials[3 * i + 0];
-      t[1] += partials[3 * i + 1];
-      t[2] += partials[3 * i + 2];
+      tt[0] += partials[3 * i + 0];
+      tt[1] += partials[3 * i + 1];
+      tt[2] += partials[3 * i + 2];
     }
     __syncthreads();
-    block_sum<3>(t, red);
+    block_sum<3>(tt, red);
     if (threadIdx.x == 0) {
       const double rows = (double)(p.B * p.G), all = (double)(p.B * GK);
-      out[0] = (float)(t[0] / rows);
-      out[1] = (float)(t[1] / all);
-      out[2] = (float)(t[2] / all);
-      out[3] = -(float)(t[2] / all);
+      out[0] = (float)(tt[0] / rows);
+      out[1] = (float)(tt[1] / all);
+      out[2] = (float)(tt[2] / all);
+      out[3] = -(float)(tt[2] / all);
     }
   }
 }
 
 // grid = (B, splits): block (b, y) handles pixels [y*chunk, (y+1)*chunk) of every reconstruction of item b.
-// dynamic smem: [chunk floats input (if XS)] [GK floats coefficient]
-template <bool XS>
-__global__ void __launch_bounds__(256)
+// dynamic smem: [GK floats coefficient]
+__global__ void __launch_bounds__(256, 3)
 iw_bound_bwd_kernel(const float* __restrict__ recons, const float* __restrict__ input, const float* __restrict__ lp,
                     const float* __restrict__ kl, IwParams p, int64_t chunk, const float* __restrict__ g_loss,
                     const float* __restrict__ g_recon, const float* __restrict__ g_kld,
@@ -160,9 +156,7 @@ iw_bound_bwd_kernel(const float* __restrict__ recons, const float* __restrict__ 
   const int64_t GK = p.G * p.K;
   const int64_t p0 = (int64_t)blockIdx.y * chunk;
   const int64_t plen = (p.P - p0 < chunk) ? (p.P - p0) : chunk;
-  const int64_t cpad = XS ? ((chunk + 3) & ~(int64_t)3) : 0;
-  float* xs = smem;
-  float* coef = smem + cpad;
+  float* coef = smem;
   const float gl = g_loss ? *g_loss : 0.f;
   const float gr = g_recon ? *g_recon : 0.f;
   const float gk = (g_kld ? *g_kld : 0.f) - (g_negkld ? *g_negkld : 0.f);
@@ -180,44 +174,45 @@ iw_bound_bwd_kernel(const float* __restrict__ recons, const float* __restrict__ 
       if (g_kl && blockIdx.y == 0) g_kl[(b * p.G + g) * p.K + k] = gl * c * p.M_N + gk * inv_all;
     }
   }
+  __syncthreads();
   if (!g_recons || plen <= 0) return;
   const float* xg = input + b * p.P + p0;
   const bool vec = (p.P % 4 == 0) && (chunk % 4 == 0) &&
                    (((reinterpret_cast<uintptr_t>(recons) | reinterpret_cast<uintptr_t>(input) |
                       reinterpret_cast<uintptr_t>(g_recons)) & 15) == 0);
-  if (XS) stage_input<true>(xg, xs, plen, vec); else __syncthreads();
   const int t = threadIdx.x, nt = blockDim.x;
   const int64_t nvec = vec ? (plen >> 2) : 0;
-  const float4* x4 = reinterpret_cast<const float4*>(XS ? xs : xg);
-  const float* xsrc = XS ? xs : xg;
-  for (int64_t s = 0; s < GK; ++s) {
-    const float c = coef[s];
-    const float* r = recons + (b * GK + s) * p.P + p0;
-    float* go = g_recons + (b * GK + s) * p.P + p0;
-    const float4* r4 = reinterpret_cast<const float4*>(r);
-    float4* g4 = reinterpret_cast<float4*>(go);
-    int64_t i = t;
-    for (; i + 3 * nt < nvec; i += 4 * nt) {
-      float4 rv[4];
+  const float4* x4 = reinterpret_cast<const float4*>(xg);
+  const float* rb = recons + b * GK * p.P + p0;
+  float* gb = g_recons + b * GK * p.P + p0;
+  for (int64_t s0 = 0; s0 < GK; s0 += kSC) {
+    const int ns = (int)((GK - s0 < kSC) ? (GK - s0) : kSC);
+    float c[kSC];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) rv[u] = ldg_stream(r4 + i + u * nt);
+    for (int j = 0; j < kSC; ++j) c[j] = (j < ns) ? coef[s0 + j] : 0.f;
+    for (int64_t i = t; i < nvec; i += nt) {
+      const float4 x = __ldg(x4 + i);
+      float4 rv[kSC];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const float4 x = x4[i + u * nt];
-        stg_stream(g4 + i + u * nt, make_float4(c * (rv[u].x - x.x), c * (rv[u].y - x.y), c * (rv[u].z - x.z),
-                                                c * (rv[u].w - x.w)));
-      }
+      for (int j = 0; j < kSC; ++j)
+        if (j < ns) rv[j] = ldg_stream(reinterpret_cast<const float4*>(rb + (s0 + j) * p.P) + i);
+#pragma unroll
+      for (int j = 0; j < kSC; ++j)
+        if (j < ns)
+          stg_stream(reinterpret_cast<float4*>(gb + (s0 + j) * p.P) + i,
+                     make_float4(c[j] * (rv[j].x - x.x), c[j] * (rv[j].y - x.y), c[j] * (rv[j].z - x.z),
+                                 c[j] * (rv[j].w - x.w)));
     }
-    for (; i < nvec; i += nt) {
-      const float4 rv = ldg_stream(r4 + i);
-      const float4 x = x4[i];
-      stg_stream(g4 + i, make_float4(c * (rv.x - x.x), c * (rv.y - x.y), c * (rv.z - x.z), c * (rv.w - x.w)));
+    for (int64_t i = 4 * nvec + t; i < plen; i += nt) {
+      const float x = xg[i];
+#pragma unroll
+      for (int j = 0; j < kSC; ++j)
+        if (j < ns) gb[(s0 + j) * p.P + i] = c[j] * (rb[(s0 + j) * p.P + i] - x);
     }
-    for (int64_t j = 4 * nvec + t; j < plen; j += nt) go[j] = c * (r[j] - xsrc[j]);
   }
 }
 
-constexpr int64_t kIwMaxSmemInput = 160 * 1024;  // bytes of input image staged per CTA
+constexpr int64_t kIwMaxSmem = 200 * 1024;
 
 }  // namespace vk
 
@@ -233,19 +228,14 @@ extern "C" int vk_iw_bound_fwd(const float* recons, const float* input, const fl
   VK_REQUIRE(workspace_bytes >= need_ws, VK_ERR_WORKSPACE, "iw_bound_fwd: workspace needs %lld bytes", (long long)need_ws);
   const int64_t GK = G * K;
   IwParams p{B, G, K, P, M_N};
-  const bool xs = P * 4 <= kIwMaxSmemInput;
-  const int64_t smem = ((xs ? ((P + 3) & ~(int64_t)3) : 0) + GK * 8 + GK) * 4;
-  VK_REQUIRE(smem <= 220 * 1024, VK_ERR_UNSUPPORTED, "iw_bound_fwd: G*K=%lld too large for shared memory", (long long)GK);
+  const int64_t smem = (GK * 8 + GK) * 4;
+  VK_REQUIRE(smem <= kIwMaxSmem, VK_ERR_UNSUPPORTED, "iw_bound_fwd: G*K=%lld too large for shared memory", (long long)GK);
   unsigned int* ticket = reinterpret_cast<unsigned int*>(workspace);
   double* partials = reinterpret_cast<double*>(reinterpret_cast<char*>(workspace) + kWsHeader);
   cudaStream_t s = (cudaStream_t)stream;
-  if (xs) {
-    cudaFuncSetAttribute(iw_bound_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    iw_bound_fwd_kernel<true><<<(unsigned)B, 256, smem, s>>>(recons, input, kl, p, lp_out, out, ticket, partials);
-  } else {
-    cudaFuncSetAttribute(iw_bound_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    iw_bound_fwd_kernel<false><<<(unsigned)B, 256, smem, s>>>(recons, input, kl, p, lp_out, out, ticket, partials);
-  }
+  if (smem > 48 * 1024)
+    cudaFuncSetAttribute(iw_bound_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  iw_bound_fwd_kernel<<<(unsigned)B, 256, smem, s>>>(recons, input, kl, p, lp_out, out, ticket, partials);
   return check_launch("iw_bound_fwd");
 }
 
@@ -271,17 +261,12 @@ extern "C" int vk_iw_bound_bwd(const float* recons, const float* input, const fl
   chunk = (chunk + 3) & ~(int64_t)3;
   splits = (P + chunk - 1) / chunk;
   VK_REQUIRE(splits <= 65535, VK_ERR_UNSUPPORTED, "iw_bound_bwd: P too large");
-  const bool xs = chunk * 4 <= kIwMaxSmemInput;
-  const int64_t smem = ((xs ? chunk : 0) + GK) * 4;
-  VK_REQUIRE(smem <= 220 * 1024, VK_ERR_UNSUPPORTED, "iw_bound_bwd: G*K=%lld too large for shared memory", (long long)GK);
+  const int64_t smem = GK * 4;
+  VK_REQUIRE(smem <= kIwMaxSmem, VK_ERR_UNSUPPORTED, "iw_bound_bwd: G*K=%lld too large for shared memory", (long long)GK);
   dim3 grid((unsigned)B, (unsigned)splits);
   cudaStream_t s = (cudaStream_t)stream;
-  if (xs) {
-    cudaFuncSetAttribute(iw_bound_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    iw_bound_bwd_kernel<true><<<grid, 256, smem, s>>>(recons, input, lp, kl, p, chunk, g_loss, g_recon, g_kld, g_negkld, g_recons, g_kl);
-  } else {
-    cudaFuncSetAttribute(iw_bound_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    iw_bound_bwd_kernel<false><<<grid, 256, smem, s>>>(recons, input, lp, kl, p, chunk, g_loss, g_recon, g_kld, g_negkld, g_recons, g_kl);
-  }
+  if (smem > 48 * 1024)
+    cudaFuncSetAttribute(iw_bound_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  iw_bound_bwd_kernel<<<grid, 256, smem, s>>>(recons, input, lp, kl, p, chunk, g_loss, g_recon, g_kld, g_negkld, g_recons, g_kl);
   return check_launch("iw_bound_bwd");
 }

@@ -241,8 +241,8 @@ def test_iw_shapes_vs_oracle(vk, B, G, K, P):
     F, _ = vk
     gen = torch.Generator().manual_seed(B * 100 + K)
     shape = (B, G, K) if G > 1 else (B, K)
-    r = torch.tanh(torch.randn(*shape, P, generator=gen))
-    x = torch.rand(B, P, generator=gen)
+    r = torch.tanh(torch.randn(*shape, 1, 1, P, generator=gen))      # [B,(G,)K,C,H,W] with C=H=1
+    x = torch.rand(B, 1, 1, P, generator=gen)
     mu = torch.randn(*shape, 8, generator=gen)
     lv = 0.5 * torch.randn(*shape, 8, generator=gen)
     rc, muc, lvc = leaf(r), leaf(mu), leaf(lv)
