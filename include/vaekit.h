@@ -138,6 +138,27 @@ int vk_iw_bound_bwd(const float* recons, const float* input, const float* lp, co
                     const float* g_loss, const float* g_recon, const float* g_kld, const float* g_negkld,
                     float* g_recons /*[B,G,K,P] or NULL*/, float* g_kl /*[B*G*K] or NULL*/, void* stream);
 
+/* ---------------------------------------------------------------------------
+ * K7  VQ-VAE VectorQuantizer               (reference: models/vq_vae.py:24-55)
+ *
+ * latents [B, D, H*W] (NCHW, read in place -- no NHWC copy), codebook [K, D].
+ *   idx[r]  = argmin_k (|x_r|^2 + |e_k|^2) - 2 x_r.e_k   (first index on ties), r = b*HW + hw
+ *   q_out   = x + (e_idx - x)                            (straight-through value, vq_vae.py:51), NCHW
+ *   out[2]  = { vq_loss = beta*mse + mse,  mse = mean (e_idx - x)^2 }
+ * The distance GEMM runs on tcgen05 tensor cores as three bf16 passes (hi*hi + lo*hi + hi*lo, fp32
+ * accumulation in TMEM): |error| on x.e is ~2^-17 |x||e| sqrt(D).
+ * Backward (g_q upstream of q_out or NULL, g_loss upstream of vq_loss or NULL):
+ *   g_latents  = g_q + g_loss * (2 beta / numel) (x - q)
+ *   g_codebook[k] = sum_{r: idx_r = k} g_loss * (2 / numel) (q_r - x_r)      (overwritten, not accumulated)
+ * -------------------------------------------------------------------------*/
+int64_t vk_vq_workspace_bytes(int64_t D, int64_t K);
+int vk_vq_fwd(const float* latents, const float* codebook, int64_t B, int64_t D, int64_t HW, int64_t K,
+              float beta, float* q_out, int32_t* idx_out, float* out /*[2]*/,
+              void* workspace, int64_t workspace_bytes, void* stream);
+int vk_vq_bwd(const float* g_q, const float* g_loss, const float* latents, const float* codebook,
+              const int32_t* idx, int64_t B, int64_t D, int64_t HW, int64_t K, float beta,
+              float* g_latents /*or NULL*/, float* g_codebook /*or NULL*/, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

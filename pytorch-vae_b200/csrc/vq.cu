@@ -1,0 +1,402 @@
+// K7: VQ-VAE VectorQuantizer forward / backward (reference: models/vq_vae.py:24-55).
+//
+// The reference permutes NCHW -> NHWC, builds the [R,K] distance matrix with two SGEMM-class calls,
+// argmin, a [R,K] one-hot, one-hot @ codebook, two mse_loss, the straight-through add and permutes back
+// (about 1 GB of temporaries at R = 262144, K = 512).  Here one persistent warp-specialised kernel does all
+// of it in a single pass over the latents:
+//
+//   producer warps (4)  read a 128-row tile of x straight from NCHW (coalesced along h*w), compute |x|^2,
+//                       split every value into bf16 hi + lo and write the UMMA operand image to shared memory
+//   MMA warp (1 thread) tcgen05.mma  dot[128, 256-code chunk] = x . e^T  as hi*hi + lo*hi + hi*lo
+//                       (3 bf16 passes, fp32 accumulate in TMEM: ~2^-17 relative, enough for the argmin to
+//                       agree with the fp32 reference wherever its best-vs-second gap exceeds 1e-5)
+//   epilogue warps (4)  tcgen05.ld the accumulators, dist = (|x|^2 + |e|^2) - 2 dot  in the reference's
+//                       association (vq_vae.py:30-32), running first-index argmin, then gather the fp32 code,
+//                       q_out = x + (q - x) (vq_vae.py:51), indices, and the squared-error partial sum
+//
+// The bf16 hi/lo image of the codebook (built once per call by a tiny pack kernel) is brought into shared
+// memory with one 1-D bulk TMA copy and stays resident; TMEM holds two 256-column accumulator buffers so the
+// MMA of the next chunk overlaps the argmin of the current one.
+#include "common.cuh"
+#include "tc.cuh"
+
+namespace vk {
+using namespace tc;
+
+namespace {
+
+constexpr int kTileRows = 128;
+constexpr int kProducerWarps = 4, kEpilogueWarps = 4;
+constexpr int kVqThreads = 32 * (kProducerWarps + kEpilogueWarps + 1);   // warps 0-3 producer, 4-7 epilogue, 8 MMA
+
+struct VqShape {
+  int64_t B, D, HW, K, R;
+  int Dp;       // D padded to a multiple of 16 (MMA K step)
+  int NC;       // codes per MMA chunk (<= 256, multiple of 32)
+  int Kp;       // K padded to a multiple of NC
+  int nch;      // chunks
+  int64_t tiles;
+};
+
+__host__ __device__ inline int round_up(int x, int m) { return (x + m - 1) / m * m; }
+
+// workspace layout (after the 256-byte ticket header)
+struct VqWs {
+  size_t partials, image, ee, total;
+};
+inline VqWs vq_ws(const VqShape& s) {
+  VqWs w;
+  w.partials = kWsHeader;
+  w.image = w.partials + (size_t)kMaxReduceBlocks * sizeof(double);
+  w.ee = w.image + (size_t)2 * s.Kp * s.Dp * 2;
+  w.total = w.ee + (size_t)s.Kp * 4;
+  return w;
+}
+
+// smem layout of the forward kernel
+struct VqSmem {
+  uint32_t cb, x[2], ee, xx, bars, tmem, total;
+};
+__host__ __device__ inline VqSmem vq_smem(int Dp, int Kp) {
+  VqSmem m;
+  uint32_t o = 0;
+  m.cb = o;            o += 2u * Kp * Dp * 2;            // hi image then lo image
+  m.x[0] = o;          o += 2u * kTileRows * Dp * 2;
+  m.x[1] = o;          o += 2u * kTileRows * Dp * 2;
+  m.ee = o;            o += Kp * 4u;
+  m.xx = o;            o += 4u * kTileRows * 4;          // |x|^2, 4 slots (producer runs <= 3 tiles ahead of the epilogue)
+  m.bars = o;          o += 16 * 8;
+  m.tmem = o;          o += 16;
+  m.total = o;
+  return m;
+}
+
+// ---- codebook pack: fp32 [K,D] -> bf16 hi/lo operand images [Dp/8][Kp][8] + |e|^2 ---------------------------
+__global__ void vq_pack_codebook_kernel(const float* __restrict__ E, int K, int D, int Kp, int Dp,
+                                        __nv_bfloat16* __restrict__ img, float* __restrict__ ee) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= Kp) return;
+  __nv_bfloat16* hi = img;
+  __nv_bfloat16* lo = img + (size_t)Kp * Dp;
+  float s = 0.f;
+  for (int d = 0; d < Dp; ++d) {
+    const float v = (k < K && d < D) ? E[(size_t)k * D + d] : 0.f;
+    s += v * v;
+    __nv_bfloat16 h, l;
+    split_bf16(v, h, l);
+    const size_t a = ((size_t)(d >> 3) * Kp + k) * 8 + (d & 7);
+    hi[a] = h;
+    lo[a] = l;
+  }
+  ee[k] = (k < K) ? s : INFINITY;          // padded codes can never win the argmin
+}
+
+// ---- forward -------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kVqThreads, 1)
+vq_fwd_kernel(const float* __restrict__ X, const float* __restrict__ E, const uint8_t* __restrict__ cb_image,
+              const float* __restrict__ ee_g, VqShape s, float beta, float* __restrict__ q_out,
+              int32_t* __restrict__ idx_out, float* __restrict__ out, unsigned int* ticket, double* partials) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const VqSmem L = vq_smem(s.Dp, s.Kp);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t sbase = smem_u32(smem);
+  // barriers: 0 cb_full | 1,2 x_full | 3,4 x_empty | 5,6 tmem_full | 7,8 tmem_empty
+  auto bar = [&](int i) { return sbase + L.bars + 8u * i; };
+  float* ee_s = reinterpret_cast<float*>(smem + L.ee);
+  float* xx_s = reinterpret_cast<float*>(smem + L.xx);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + L.tmem);
+
+  if (threadIdx.x == 0) {
+    mbar_init(bar(0), 1);
+    mbar_init(bar(1), 32 * kProducerWarps); mbar_init(bar(2), 32 * kProducerWarps);
+    mbar_init(bar(3), 1); mbar_init(bar(4), 1);
+    mbar_init(bar(5), 1); mbar_init(bar(6), 1);
+    mbar_init(bar(7), 32 * kEpilogueWarps); mbar_init(bar(8), 32 * kEpilogueWarps);
+    mbar_fence_init();
+  }
+  if (warp == 8) tmem_alloc(smem_u32(tmem_slot), 512);
+  for (int k = threadIdx.x; k < s.Kp; k += blockDim.x) ee_s[k] = ee_g[k];
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tmem = *tmem_slot;
+  const uint32_t img_bytes = 2u * kTileRows * s.Dp;        // one x image (hi or lo)
+  const uint32_t cb_img_bytes = 2u * s.Kp * s.Dp;          // one codebook image (hi or lo)
+
+  if (warp < kProducerWarps) {
+    // ===== producers: NCHW fp32 -> bf16 hi/lo operand image, |x|^2 =====
+    const int t = threadIdx.x;                               // row within the tile
+    int it = 0;
+    for (int64_t tile = blockIdx.x; tile < s.tiles; tile += gridDim.x, ++it) {
+      const int st = it & 1;
+      if (it >= 2) mbar_wait(bar(3 + st), ((it >> 1) - 1) & 1);
+      const int64_t r = tile * kTileRows + t;
+      const bool live = r < s.R;
+      const int64_t b = live ? r / s.HW : 0, hw = live ? r % s.HW : 0;
+      const float* xp = X + (b * s.D) * s.HW + hw;
+      uint8_t* hi = smem + L.x[st];
+      uint8_t* lo = hi + img_bytes;
+      float xx = 0.f;
+      for (int d0 = 0; d0 < s.Dp; d0 += 8) {
+        float v[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[e] = (live && d0 + e < s.D) ? __ldg(xp + (int64_t)(d0 + e) * s.HW) : 0.f;
+        uint32_t ph[4], pl[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          __nv_bfloat16 h0, l0, h1, l1;
+          split_bf16(v[2 * e], h0, l0);
+          split_bf16(v[2 * e + 1], h1, l1);
+          ph[e] = pack2(h0, h1);
+          pl[e] = pack2(l0, l1);
+          xx += v[2 * e] * v[2 * e];
+          xx += v[2 * e + 1] * v[2 * e + 1];
+        }
+        const uint32_t off = ((uint32_t)(d0 >> 3) * kTileRows + t) * 16;
+        *reinterpret_cast<uint4*>(hi + off) = make_uint4(ph[0], ph[1], ph[2], ph[3]);
+        *reinterpret_cast<uint4*>(lo + off) = make_uint4(pl[0], pl[1], pl[2], pl[3]);
+      }
+      xx_s[(it & 3) * kTileRows + t] = xx;
+      fence_proxy_async();
+      mbar_arrive(bar(1 + st));
+    }
+  } else if (warp == 8) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      mbar_expect_tx(bar(0), 2 * cb_img_bytes);
+      bulk_g2s(sbase + L.cb, cb_image, 2 * cb_img_bytes, bar(0));
+      mbar_wait(bar(0), 0);
+      const uint32_t idesc = idesc_bf16(128, s.NC, 0, 0);
+      const uint32_t a_lbo = kTileRows * 16, b_lbo = (uint32_t)s.Kp * 16;
+      int it = 0;
+      uint32_t c = 0;                                       // global chunk counter -> TMEM buffer c & 1
+      for (int64_t tile = blockIdx.x; tile < s.tiles; tile += gridDim.x, ++it) {
+        const int st = it & 1;
+        mbar_wait(bar(1 + st), (it >> 1) & 1);
+        fence_after_sync();
+        const uint32_t a_hi = sbase + L.x[st], a_lo = a_hi + img_bytes;
+        for (int ch = 0; ch < s.nch; ++ch, ++c) {
+          const uint32_t buf = c & 1;
+          if (c >= 2) mbar_wait(bar(7 + buf), ((c >> 1) - 1) & 1);
+          fence_after_sync();
+          const uint32_t b_hi = sbase + L.cb + (uint32_t)ch * s.NC * 16, b_lo = b_hi + cb_img_bytes;
+          const uint32_t d = tmem + buf * 256;
+          uint32_t acc = 0;
+          for (int pass = 0; pass < 3; ++pass) {
+            const uint32_t a0 = pass == 1 ? a_lo : a_hi, b0 = pass == 2 ? b_lo : b_hi;
+            for (int k = 0; k < s.Dp / 16; ++k) {
+              mma_bf16(d, smem_desc(a0 + k * 2 * a_lbo, a_lbo, 128), smem_desc(b0 + k * 2 * b_lbo, b_lbo, 128), idesc, acc);
+              acc = 1;
+            }
+          }
+          mma_commit(bar(5 + buf));
+        }
+        mma_commit(bar(3 + st));                            // x stage free once every MMA of this tile has run
+      }
+    }
+  } else {
+    // ===== epilogue: distances, argmin, gather, straight-through output, loss partial =====
+    const int ew = warp - kProducerWarps;                    // == warp % 4 -> TMEM lanes 32*ew .. 32*ew+31
+    const int t = ew * 32 + lane;
+    double sq = 0.0;
+    int it = 0;
+    uint32_t c = 0;
+    for (int64_t tile = blockIdx.x; tile < s.tiles; tile += gridDim.x, ++it) {
+      const int st = it & 1;
+      float best = INFINITY;
+      int bi = 0;
+      float xx = 0.f;
+      for (int ch = 0; ch < s.nch; ++ch, ++c) {
+        const uint32_t buf = c & 1;
+        mbar_wait(bar(5 + buf), (c >> 1) & 1);
+        fence_after_sync();
+        if (ch == 0) xx = xx_s[(it & 3) * kTileRows + t];    // written before x_full, which precedes tmem_full
+        for (int c0 = 0; c0 < s.NC; c0 += 32) {
+          uint32_t r[32];
+          tmem_ld32(tmem + ((uint32_t)(ew * 32) << 16) + buf * 256 + c0, r);
+          tmem_ld_wait();
+          const int kb = ch * s.NC + c0;
+#pragma unroll
+          for (int i = 0; i < 32; i += 4) {
+            const float4 e4 = *reinterpret_cast<const float4*>(ee_s + kb + i);
+            const float ee[4] = {e4.x, e4.y, e4.z, e4.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const float dist = fmaf(-2.f, __uint_as_float(r[i + j]), xx + ee[j]);   // (|x|^2+|e|^2) - 2 x.e
+              if (dist < best) { best = dist; bi = kb + i + j; }
+            }
+          }
+        }
+        fence_before_sync();
+        mbar_arrive(bar(7 + buf));
+      }
+      const int64_t r = tile * kTileRows + t;
+      if (r < s.R) {
+        idx_out[r] = bi;
+        const int64_t b = r / s.HW, hw = r % s.HW;
+        const float* xp = X + (b * s.D) * s.HW + hw;
+        float* qp = q_out + (b * s.D) * s.HW + hw;
+        const float* ep = E + (size_t)bi * s.D;
+        float acc = 0.f;
+        if ((s.D & 3) == 0) {
+          for (int d = 0; d < s.D; d += 4) {
+            const float4 e4 = __ldg(reinterpret_cast<const float4*>(ep + d));
+            const float ev[4] = {e4.x, e4.y, e4.z, e4.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const float x = __ldg(xp + (int64_t)(d + j) * s.HW);
+              const float df = ev[j] - x;
+              qp[(int64_t)(d + j) * s.HW] = x + df;          // latents + (quantized - latents).detach()
+              acc = fmaf(df, df, acc);
+            }
+          }
+        } else {
+          for (int d = 0; d < s.D; ++d) {
+            const float x = __ldg(xp + (int64_t)d * s.HW);
+            const float df = __ldg(ep + d) - x;
+            qp[(int64_t)d * s.HW] = x + df;
+            acc = fmaf(df, df, acc);
+          }
+        }
+        sq += (double)acc;
+      }
+    }
+    // block partial of sum (q-x)^2 over the epilogue warps, then the last-block combine
+    double v[1] = {sq};
+    __shared__ double red[kEpilogueWarps];
+    v[0] = warp_sum(v[0]);
+    if (lane == 0) red[ew] = v[0];
+    asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpilogueWarps));
+    if (ew == 0 && lane == 0) {
+      double tot = 0;
+      for (int i = 0; i < kEpilogueWarps; ++i) tot += red[i];
+      partials[blockIdx.x] = tot;
+      __threadfence();
+      const unsigned int tk = atomicAdd(ticket, 1u);
+      if (tk == gridDim.x - 1) {
+        __threadfence();
+        double all = 0;
+        for (unsigned int i = 0; i < gridDim.x; ++i) all += ((volatile double*)partials)[i];
+        const float m = (float)(all / ((double)s.R * (double)s.D));   // mse_loss(q, x): commitment == embedding in value
+        out[0] = m * beta + m;                                         // vq_vae.py:50
+        out[1] = m;
+        *ticket = 0u;
+      }
+    }
+  }
+  fence_before_sync();
+  __syncthreads();
+  if (warp == 8) tmem_dealloc(tmem, 512);
+}
+
+// ---- backward ------------------------------------------------------------------------------------------------
+// g_x = g_q + g_loss * (2 beta / numel) (x - q);   g_E[idx] += g_loss * (2 / numel) (q - x)   (vq_vae.py:47-51)
+__global__ void __launch_bounds__(256)
+vq_bwd_kernel(const float* __restrict__ g_q, const float* __restrict__ g_loss, const float* __restrict__ X,
+              const float* __restrict__ E, const int32_t* __restrict__ idx, VqShape s, float beta,
+              float* __restrict__ g_x, float* __restrict__ g_E) {
+  extern __shared__ float acc_s[];                           // [K][D+1] per-CTA codebook-gradient accumulator
+  const int ld = (int)s.D + 1;
+  const bool want_e = g_E != nullptr;
+  if (want_e) for (int i = threadIdx.x; i < s.K * ld; i += blockDim.x) acc_s[i] = 0.f;
+  __syncthreads();
+  const float gl = g_loss ? *g_loss : 0.f;
+  const float cx = gl * 2.f * beta / (float)((double)s.R * (double)s.D);
+  const float ce = gl * 2.f / (float)((double)s.R * (double)s.D);
+  for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < s.R; r += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t b = r / s.HW, hw = r % s.HW;
+    const int k = idx[r];
+    const float* xp = X + (b * s.D) * s.HW + hw;
+    const float* gp = g_q ? g_q + (b * s.D) * s.HW + hw : nullptr;
+    float* op = g_x ? g_x + (b * s.D) * s.HW + hw : nullptr;
+    const float* ep = E + (size_t)k * s.D;
+#pragma unroll 8
+    for (int d = 0; d < s.D; ++d) {
+      const float x = __ldg(xp + (int64_t)d * s.HW);
+      const float df = __ldg(ep + d) - x;                    // q - x
+      if (op) op[(int64_t)d * s.HW] = (gp ? __ldg(gp + (int64_t)d * s.HW) : 0.f) - cx * df;
+      if (want_e) atomicAdd(&acc_s[k * ld + d], ce * df);
+    }
+  }
+  if (want_e) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < s.K * s.D; i += blockDim.x) {
+      const float v = acc_s[(i / s.D) * ld + (i % s.D)];
+      if (v != 0.f) atomicAdd(&g_E[i], v);
+    }
+  }
+}
+
+__global__ void zero_kernel(float* p, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = 0.f;
+}
+
+int make_shape(int64_t B, int64_t D, int64_t HW, int64_t K, VqShape& s) {
+  VK_REQUIRE(B > 0 && D > 0 && HW > 0 && K > 0, VK_ERR_BAD_ARG, "vq: empty shape B=%lld D=%lld HW=%lld K=%lld",
+             (long long)B, (long long)D, (long long)HW, (long long)K);
+  VK_REQUIRE(D <= 256 && K <= 4096, VK_ERR_UNSUPPORTED, "vq: D=%lld (max 256) or K=%lld (max 4096) too large",
+             (long long)D, (long long)K);
+  s.B = B; s.D = D; s.HW = HW; s.K = K; s.R = B * HW;
+  s.Dp = round_up((int)D, 16);
+  s.NC = K >= 256 ? 256 : round_up((int)K, 32);
+  s.Kp = round_up((int)K, s.NC);
+  s.nch = s.Kp / s.NC;
+  s.tiles = (s.R + kTileRows - 1) / kTileRows;
+  return VK_OK;
+}
+
+}  // namespace
+}  // namespace vk
+
+using namespace vk;
+
+extern "C" int64_t vk_vq_workspace_bytes(int64_t D, int64_t K) {
+  VqShape s;
+  if (make_shape(1, D, 1, K, s) != VK_OK) return -1;
+  return (int64_t)vq_ws(s).total;
+}
+
+extern "C" int vk_vq_fwd(const float* latents, const float* codebook, int64_t B, int64_t D, int64_t HW, int64_t K,
+                         float beta, float* q_out, int32_t* idx_out, float* out, void* workspace,
+                         int64_t workspace_bytes, void* stream) {
+  VK_REQUIRE(latents && codebook && q_out && idx_out && out && workspace, VK_ERR_BAD_ARG, "vq_fwd: null pointer");
+  VqShape s;
+  int rc = make_shape(B, D, HW, K, s);
+  if (rc != VK_OK) return rc;
+  const VqWs w = vq_ws(s);
+  VK_REQUIRE(workspace_bytes >= (int64_t)w.total, VK_ERR_WORKSPACE, "vq_fwd: workspace %lld < %lld",
+             (long long)workspace_bytes, (long long)w.total);
+  const VqSmem L = vq_smem(s.Dp, s.Kp);
+  VK_REQUIRE(L.total + 256 <= 227 * 1024, VK_ERR_UNSUPPORTED,
+             "vq_fwd: codebook %lldx%lld needs %u bytes of shared memory (max 232192)", (long long)K, (long long)D, L.total);
+  cudaStream_t st = (cudaStream_t)stream;
+  uint8_t* ws = (uint8_t*)workspace;
+  vq_pack_codebook_kernel<<<(s.Kp + 127) / 128, 128, 0, st>>>(codebook, (int)K, (int)D, s.Kp, s.Dp,
+                                                              (__nv_bfloat16*)(ws + w.image), (float*)(ws + w.ee));
+  if (cudaFuncSetAttribute(vq_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total) != cudaSuccess)
+    return check_launch("vq_fwd (shared memory attribute)");
+  const int grid = (int)(s.tiles < sm_count() ? s.tiles : sm_count());
+  vq_fwd_kernel<<<grid, kVqThreads, L.total, st>>>(latents, codebook, ws + w.image, (const float*)(ws + w.ee), s,
+                                                          beta, q_out, idx_out, out, (unsigned int*)ws,
+                                                          (double*)(ws + w.partials));
+  return check_launch("vq_fwd");
+}
+
+extern "C" int vk_vq_bwd(const float* g_q, const float* g_loss, const float* latents, const float* codebook,
+                         const int32_t* idx, int64_t B, int64_t D, int64_t HW, int64_t K, float beta,
+                         float* g_latents, float* g_codebook, void* stream) {
+  VK_REQUIRE(latents && codebook && idx, VK_ERR_BAD_ARG, "vq_bwd: null pointer");
+  VqShape s;
+  int rc = make_shape(B, D, HW, K, s);
+  if (rc != VK_OK) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t sm = g_codebook ? (size_t)K * (D + 1) * 4 : 0;
+  VK_REQUIRE(sm <= 226 * 1024, VK_ERR_UNSUPPORTED, "vq_bwd: codebook gradient tile needs %zu bytes of shared memory", sm);
+  if (sm > 48 * 1024 && cudaFuncSetAttribute(vq_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm) != cudaSuccess)
+    return check_launch("vq_bwd (shared memory attribute)");
+  if (g_codebook) zero_kernel<<<64, 256, 0, st>>>(g_codebook, K * D);
+  int64_t blocks = (s.R + 255) / 256;
+  if (blocks > sm_count()) blocks = sm_count();
+  vq_bwd_kernel<<<(int)blocks, 256, sm, st>>>(g_q, g_loss, latents, codebook, idx, s, beta, g_latents, g_codebook);
+  return check_launch("vq_bwd");
+}

@@ -211,3 +211,55 @@ class _IwBound(torch.autograd.Function):
 def iw_bound(recons, input, kl, M_N):
     """(loss, mean log_p_x_z, mean kl, -mean kl) of iwae.py:145-160 / miwae.py:148-164."""
     return _IwBound.apply(recons, input, kl, float(M_N))
+
+
+# ---------------------------------------------------------------------------
+# K7
+# ---------------------------------------------------------------------------
+class _VectorQuantize(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, latents, codebook, beta):
+        L.require(latents, "latents", dims=(3, 4)); L.require(codebook, "codebook", dims=(2,))
+        if latents.shape[1] != codebook.shape[1]:
+            raise RuntimeError("vaekit: latents have %d channels but the codebook has embedding_dim %d" %
+                               (latents.shape[1], codebook.shape[1]))
+        if latents.numel() == 0:
+            raise RuntimeError("vaekit: empty latents")
+        x, e = latents.contiguous(), codebook.contiguous()
+        B, D = x.shape[0], x.shape[1]
+        HW = x[0, 0].numel()
+        K = e.shape[0]
+        dev = x.device
+        q = torch.empty_like(x)
+        idx = torch.empty(B * HW, dtype=torch.int32, device=dev)
+        out = torch.empty(2, dtype=torch.float32, device=dev)
+        need = int(L.lib().vk_vq_workspace_bytes(D, K))
+        if need < 0:
+            raise RuntimeError("vaekit: VectorQuantizer shape D=%d K=%d is not supported" % (D, K))
+        ws = L.workspace(dev, need)
+        with torch.cuda.device(dev):
+            L.call("vq_fwd", L.ptr(x), L.ptr(e), B, D, HW, K, beta, L.ptr(q), L.ptr(idx), L.ptr(out), L.ptr(ws),
+                   ws.numel(), L.stream_ptr())
+        ctx.save_for_backward(x, e, idx)
+        ctx.cfg = (B, D, HW, K, beta)
+        ctx.set_materialize_grads(False)
+        ctx.mark_non_differentiable(idx)
+        return q, out[0], idx
+
+    @staticmethod
+    def backward(ctx, g_q, g_loss, _g_idx):
+        x, e, idx = ctx.saved_tensors
+        B, D, HW, K, beta = ctx.cfg
+        g_x = torch.empty_like(x) if ctx.needs_input_grad[0] else None
+        g_e = torch.empty_like(e) if ctx.needs_input_grad[1] else None
+        g_q = None if g_q is None else g_q.contiguous()
+        g_loss = None if g_loss is None else g_loss.contiguous()
+        with torch.cuda.device(x.device):
+            L.call("vq_bwd", L.ptr(g_q), L.ptr(g_loss), L.ptr(x), L.ptr(e), L.ptr(idx), B, D, HW, K, beta,
+                   L.ptr(g_x), L.ptr(g_e), L.stream_ptr())
+        return g_x, g_e, None
+
+
+def vector_quantize(latents, codebook, beta):
+    """(quantized NCHW with straight-through gradient, vq_loss, indices[int32, B*H*W]) of vq_vae.py:24-55."""
+    return _VectorQuantize.apply(latents, codebook, float(beta))

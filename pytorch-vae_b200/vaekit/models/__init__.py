@@ -6,6 +6,7 @@ from .beta_vae import BetaVAE
 from .logcosh_vae import LogCoshVAE
 from .iwae import IWAE
 from .miwae import MIWAE
+from .vq_vae import VQVAE, VectorQuantizer
 
 VAE = VanillaVAE
 GaussianVAE = VanillaVAE
@@ -16,4 +17,5 @@ vae_models = {
     'BetaVAE': BetaVAE,
     'LogCoshVAE': LogCoshVAE,
     'VanillaVAE': VanillaVAE,
+    'VQVAE': VQVAE,
 }
