@@ -159,6 +159,30 @@ int vk_vq_bwd(const float* g_q, const float* g_loss, const float* latents, const
               const int32_t* idx, int64_t B, int64_t D, int64_t HW, int64_t K, float beta,
               float* g_latents /*or NULL*/, float* g_codebook /*or NULL*/, void* stream);
 
+/* ---------------------------------------------------------------------------
+ * K4  WAE-MMD                              (reference: models/wae_mmd.py:125-204)
+ *
+ * z, prior [N, D] fp32 (D <= 128).  kernel_type: VK_KERNEL_RBF  exp(-|x-y|^2 / (2 D^2 z_var)), full N x N sums
+ * (wae_mmd.py:164-167); VK_KERNEL_IMQ  C/(1e-7 + C + |x-y|^2), C = 2 D z_var, diagonal removed from all three
+ * sums (wae_mmd.py:185-191).  One sweep produces, for the row range [row_begin, row_end) (128-aligned; the
+ * whole matrix on one GPU, a row block per rank when sharded after an all-gather of z):
+ *   sums_out[3] (double, device) = { sum k(z_i,z_j), sum k(z_i,prior_j), sum k(prior_i,prior_j) } over the rows
+ *   grad_unscaled [(row_end-row_begin), D]:  G_i = sum_j dk/dd^2(z_i,z_j) (z_i-z_j) - sum_j dk/dd^2(z_i,p_j) (z_i-p_j)
+ *                 so that  d mmd / d z_i = 4 * reg * m * G_i,  m = 1/N^2 (rbf) or 1 (imq)
+ * x.y runs on tcgen05 tensor cores: passes = 3 -> bf16 hi/lo split (hi*hi + lo*hi + hi*lo, ~2^-17 relative,
+ * the parity mode), passes = 1 -> plain bf16 (reported separately; gradients lose ~3 digits).
+ * vk_mmd_combine: out[4] = { reg*pp + reg*zz - 2*reg*pz, pp, zz, pz } with pp = mean (rbf) / sum (imq) of the
+ * (all-reduced) sums, in the reference's fp32 association (wae_mmd.py:201-203).
+ * -------------------------------------------------------------------------*/
+enum { VK_KERNEL_RBF = 0, VK_KERNEL_IMQ = 1 };
+int64_t vk_mmd_workspace_bytes(int64_t N, int64_t D);
+int vk_mmd_fwd(const float* z, const float* prior, int64_t N, int64_t D, int kernel_type, float z_var, int passes,
+               int64_t row_begin, int64_t row_end, double* sums_out /*[3]*/, float* grad_unscaled,
+               void* workspace, int64_t workspace_bytes, void* stream);
+int vk_mmd_combine(const double* sums /*[3]*/, int64_t N, int kernel_type, float reg_weight, float* out /*[4]*/, void* stream);
+/* out[i] = in[i] * (*g) * factor  (g may be NULL = 1): backward of an op whose gradient was produced in the forward sweep */
+int vk_scale_by_scalar(const float* in, const float* g, float factor, int64_t n, float* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

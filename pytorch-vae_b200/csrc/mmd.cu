@@ -1,0 +1,590 @@
+// K4: WAE-MMD  compute_kernel / compute_rbf / compute_inv_mult_quad / compute_mmd
+// (reference: models/wae_mmd.py:125-204), forward value and d/dz in ONE sweep over the three Gram matrices.
+//
+// The reference materialises x1.expand(N,N,D) - x2.expand(N,N,D) (2.2 TB per temporary at N = 65536).  Here the
+// pairwise squared distance is  |x|^2 + |y|^2 - 2 x.y  with x.y on tcgen05 tensor cores:
+//
+//   pack kernels    z, prior_z (fp32 [N,D]) -> bf16 hi/lo operand images, 128-row tiles in the UMMA no-swizzle
+//                   canonical layout, + fp32 row norms.  The same image is a K-major operand (K = latent dim)
+//                   for the distance GEMM and an MN-major operand (K = sample index) for the gradient GEMM.
+//   main kernel     persistent, warp-specialised, one CTA per SM:
+//     TMA warp      1-D bulk copies (cp.async.bulk -> mbarrier) of the A row block and of 64-column B stages
+//     MMA warp      GEMM1  S[128,64]  = X_i . Y_j^T         (hi*hi + lo*hi + hi*lo, fp32 accumulate in TMEM)
+//                   GEMM2  O[128,D]  += C_ij . Y_j          (coefficient tile C written by the epilogue)
+//     epilogue (4w) tcgen05.ld S -> d^2 -> k (ex2 / rcp) -> running sum of k, c = dk/dd^2 (signed) ->
+//                   row sums of c, bf16 hi/lo of c into shared memory as the A operand of GEMM2
+//   finalize        dL/dz_i (unscaled) = z_i * sum_j c_ij - O_i ; per-CTA partial sums -> three kernel sums
+//
+// Gradient identity:  sum_j c_ij (z_i - y_j) = z_i * (sum_j c_ij) - (C Y)_i.
+// The prior-prior Gram needs no gradient: it is evaluated on a circulant half (each unordered tile pair once,
+// weight 2), which is also balanced when row blocks are sharded across GPUs.
+// Reference quirks kept: RBF = exp(-|x-y|^2 / (2 D^2 z_var)) averaged over the full N x N including the diagonal
+// (wae_mmd.py:164-167); IMQ = C / (1e-7 + C + |x-y|^2), C = 2 D z_var, summed with the diagonal removed from
+// all three terms, including k(prior_i, z_i) (wae_mmd.py:185-191).
+#include "common.cuh"
+#include "tc.cuh"
+
+namespace vk {
+using namespace tc;
+
+namespace {
+
+constexpr int kRows = 128;       // row block (MMA M)
+constexpr int kCols = 64;        // column tile (GEMM1 N, GEMM2 K)
+constexpr int kBStages = 3;
+constexpr int kNormRing = 8;
+constexpr int kMmdThreads = 32 * 6;   // warp 0 TMA, warp 1 MMA, warps 2-5 epilogue
+constexpr int kMaxQ = 8;
+
+struct MmdShape {
+  int64_t N;
+  int D, Dp, nkc;       // latent dim, padded to 16, number of 8-element K chunks
+  int T;                // 128-row tiles of the full matrix
+  int rb0, rb1;         // row-block range owned by this call
+  int Q;                // column chunks per row block (gradient items)
+  int kernel_type;      // 0 rbf, 1 imq
+  int passes;           // 3 (hi/lo split, fp32-grade) or 1 (plain bf16)
+  float a_exp;          // rbf: -log2(e) / (2 D^2 z_var)
+  float dk_scale;       // rbf: -1 / (2 D^2 z_var) ; imq: -1 / C
+  float C, Ceps;        // imq: C, fl32(1e-7 + C)
+};
+
+__host__ __device__ inline int rup(int x, int m) { return (x + m - 1) / m * m; }
+__host__ __device__ inline uint32_t tile_img_bytes(int Dp) { return 2u * kRows * Dp * 2u; }   // hi + lo of 128 rows
+
+struct MmdWs {
+  size_t cta_sums, imgZ, imgP, normZ, normP, Opart, rspart, total;
+};
+inline MmdWs mmd_ws(int64_t N, int D, int rows_local_blocks, int Q) {
+  const int Dp = rup(D, 16);
+  const int T = (int)((N + kRows - 1) / kRows);
+  MmdWs w;
+  size_t o = kWsHeader;
+  w.cta_sums = o; o += (size_t)256 * 3 * sizeof(double);
+  o = (o + 255) & ~(size_t)255;
+  w.imgZ = o; o += (size_t)T * tile_img_bytes(Dp);
+  w.imgP = o; o += (size_t)T * tile_img_bytes(Dp);
+  w.normZ = o; o += (size_t)T * kRows * 4;
+  w.normP = o; o += (size_t)T * kRows * 4;
+  w.Opart = o; o += (size_t)Q * rows_local_blocks * kRows * Dp * 4;
+  w.rspart = o; o += (size_t)Q * rows_local_blocks * kRows * 4;
+  w.total = o;
+  return w;
+}
+inline int pick_Q(int T, int row_blocks) {
+  // aim for >= 8 gradient items per SM so the static round-robin schedule balances
+  int q = (148 * 8 + row_blocks - 1) / row_blocks;
+  if (q > kMaxQ) q = kMaxQ;
+  if (q > 4 * T) q = 4 * T;
+  if (q < 1) q = 1;
+  const int n = 4 * T, len = (n + q - 1) / q;
+  return (n + len - 1) / len;                 // no empty chunk
+}
+
+struct MmdSmem {
+  uint32_t A, B[kBStages], Kmat[2], norms, bars, tmem, red, total;
+};
+__host__ __device__ inline MmdSmem mmd_smem(int Dp) {
+  MmdSmem m;
+  uint32_t o = 0;
+  m.A = o; o += tile_img_bytes(Dp);
+  for (int i = 0; i < kBStages; ++i) { m.B[i] = o; o += 2u * kCols * Dp * 2u; }
+  for (int i = 0; i < 2; ++i) { m.Kmat[i] = o; o += 2u * kRows * kCols * 2u; }
+  m.norms = o; o += kNormRing * kCols * 4u;   // deeper than the B ring: read by the epilogue after b_empty may have fired
+  m.bars = o; o += 24 * 8;
+  m.tmem = o; o += 16;
+  m.red = o; o += 4 * 3 * 8;
+  m.total = o;
+  return m;
+}
+
+// ---- pack: fp32 [N,D] -> image tiles [T][hi/lo][Dp/8][128][8] bf16 ; norms [T*128] fp32 ----------------------
+__global__ void mmd_pack_kernel(const float* __restrict__ X, int64_t N, int D, int Dp, uint8_t* __restrict__ img,
+                                float* __restrict__ norms, int T) {
+  const int nkc = Dp / 8;
+  const int64_t total = (int64_t)T * kRows * nkc;
+  for (int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t row = g / nkc;
+    const int kc = (int)(g % nkc);
+    float v[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int d = kc * 8 + e;
+      v[e] = (row < N && d < D) ? X[row * D + d] : 0.f;
+    }
+    uint32_t ph[4], pl[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      __nv_bfloat16 h0, l0, h1, l1;
+      split_bf16(v[2 * e], h0, l0);
+      split_bf16(v[2 * e + 1], h1, l1);
+      ph[e] = pack2(h0, h1);
+      pl[e] = pack2(l0, l1);
+    }
+    const int64_t tile = row / kRows;
+    const int r = (int)(row % kRows);
+    uint8_t* base = img + tile * tile_img_bytes(Dp);
+    *reinterpret_cast<uint4*>(base + ((size_t)kc * kRows + r) * 16) = make_uint4(ph[0], ph[1], ph[2], ph[3]);
+    *reinterpret_cast<uint4*>(base + ((size_t)(nkc + kc) * kRows + r) * 16) = make_uint4(pl[0], pl[1], pl[2], pl[3]);
+  }
+}
+// one warp per row, fixed summation order
+__global__ void mmd_norm_kernel(const float* __restrict__ X, int64_t N, int D, float* __restrict__ norms, int T) {
+  const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (row >= (int64_t)T * kRows) return;
+  float s = 0.f;
+  if (row < N) for (int d = lane; d < D; d += 32) { const float v = X[row * D + d]; s = fmaf(v, v, s); }
+  s = warp_sum(s);
+  if (lane == 0) norms[row] = s;
+}
+
+// ---- work items ---------------------------------------------------------------------------------------------
+// Item order: for each owned row block i: Q gradient items (i, q), then the prior-prior item of row block i.
+struct Item {
+  int i;          // row block (global index)
+  int grad;       // 1: rows = z, columns = [z tiles | prior tiles] chunk q ; 0: rows = prior, circulant half of prior
+  int u0, u1;     // tile sequence range
+};
+struct TileD {
+  int bm;         // column matrix: 0 z, 1 prior
+  int jt;         // 64-column tile index
+  int kind;       // 0 zz, 1 zp, 2 pp
+  float weight;
+  int diag;       // tile touches the main diagonal
+};
+__device__ __forceinline__ Item get_item(const MmdShape& s, int idx) {
+  Item it;
+  const int per = s.Q + 1;
+  it.i = s.rb0 + idx / per;
+  const int q = idx % per;
+  if (q < s.Q) {
+    it.grad = 1;
+    const int n = 4 * s.T, len = (n + s.Q - 1) / s.Q;
+    it.u0 = q * len;
+    it.u1 = it.u0 + len < n ? it.u0 + len : n;
+    if (it.u0 > n) it.u0 = n;
+  } else {
+    it.grad = 0;
+    const int noff = (s.T % 2 == 0) ? s.T / 2 + 1 : (s.T + 1) / 2;
+    it.u0 = 0;
+    it.u1 = 2 * noff;
+  }
+  return it;
+}
+__device__ __forceinline__ TileD get_tile(const MmdShape& s, const Item& it, int u) {
+  TileD t;
+  if (it.grad) {
+    const bool zside = u < 2 * s.T;
+    t.bm = zside ? 0 : 1;
+    t.jt = zside ? u : u - 2 * s.T;
+    t.kind = zside ? 0 : 1;
+    t.weight = 1.f;
+    t.diag = (t.jt >> 1) == it.i;
+  } else {
+    const int o = u >> 1;
+    const int j128 = (it.i + o) % s.T;
+    t.bm = 1;
+    t.jt = 2 * j128 + (u & 1);
+    t.kind = 2;
+    t.weight = (o == 0 || (s.T % 2 == 0 && o == s.T / 2)) ? 1.f : 2.f;
+    t.diag = o == 0;
+  }
+  return t;
+}
+__device__ __forceinline__ bool tile_live(const MmdShape& s, const TileD& t) { return (int64_t)t.jt * kCols < s.N; }
+
+// ---- main kernel ----------------------------------------------------------------------------------------------
+// barriers: 0 a_full | 1 a_empty | 2..4 b_full | 5..7 b_empty | 8,9 s_full | 10,11 s_empty | 12,13 k_full |
+//           14,15 k_empty | 16 o_full | 17 o_empty
+template <int PASSES>
+__global__ void __launch_bounds__(kMmdThreads, 1)
+mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ imgP, const float* __restrict__ normZ,
+                const float* __restrict__ normP, MmdShape s, int n_items, float* __restrict__ Opart,
+                float* __restrict__ rspart, double* __restrict__ cta_sums) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const MmdSmem L = mmd_smem(s.Dp);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t sbase = smem_u32(smem);
+  auto bar = [&](int i) { return sbase + L.bars + 8u * i; };
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + L.tmem);
+  if (threadIdx.x == 0) {
+    mbar_init(bar(0), 1); mbar_init(bar(1), 1);
+    for (int i = 0; i < kBStages; ++i) { mbar_init(bar(2 + i), 1); mbar_init(bar(5 + i), 1); }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(bar(8 + i), 1); mbar_init(bar(10 + i), 128);
+      mbar_init(bar(12 + i), 128); mbar_init(bar(14 + i), 1);
+    }
+    mbar_init(bar(16), 1); mbar_init(bar(17), 128);
+    mbar_fence_init();
+  }
+  if (warp == 1) tmem_alloc(smem_u32(tmem_slot), 512);
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tmem = *tmem_slot;
+  const uint32_t tmem_S = tmem, tmem_O = tmem + 128;        // S: 2 x 64 columns ; O: Dp (<=128) columns
+  const uint32_t a_bytes = tile_img_bytes(s.Dp);
+  const uint32_t b_half = (uint32_t)kCols * s.Dp * 2u;      // one hi (or lo) image of a 64-row stage
+  const uint32_t a_half = (uint32_t)kRows * s.Dp * 2u;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      uint32_t nb = 0;
+      int iter = 0;
+      for (int idx = blockIdx.x; idx < n_items; idx += gridDim.x, ++iter) {
+        const Item it = get_item(s, idx);
+        if (iter > 0) mbar_wait(bar(1), (iter - 1) & 1);
+        const uint8_t* aimg = (it.grad ? imgZ : imgP) + (size_t)it.i * a_bytes;
+        mbar_expect_tx(bar(0), a_bytes);
+        bulk_g2s(sbase + L.A, aimg, a_bytes, bar(0));
+        for (int u = it.u0; u < it.u1; ++u) {
+          const TileD t = get_tile(s, it, u);
+          if (!tile_live(s, t)) continue;
+          const uint32_t slot = nb % kBStages;
+          if (nb >= kBStages) mbar_wait(bar(5 + slot), ((nb / kBStages) - 1) & 1);
+          const uint8_t* bimg = (t.bm ? imgP : imgZ) + (size_t)(t.jt >> 1) * a_bytes + (size_t)(t.jt & 1) * kCols * 16;
+          const float* nrm = (t.bm ? normP : normZ) + (size_t)t.jt * kCols;
+          mbar_expect_tx(bar(2 + slot), 2 * b_half + kCols * 4);
+          for (int c = 0; c < 2 * s.nkc; ++c)               // hi chunks then lo chunks: 64 rows x 16 B each
+            bulk_g2s(sbase + L.B[slot] + c * kCols * 16, bimg + (size_t)c * kRows * 16, kCols * 16, bar(2 + slot));
+          bulk_g2s(sbase + L.norms + (nb % kNormRing) * kCols * 4, nrm, kCols * 4, bar(2 + slot));
+          ++nb;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      const uint32_t idesc1 = idesc_bf16(kRows, kCols, 0, 0);       // S = A(K-major) . B(K-major)^T
+      const uint32_t idesc2 = idesc_bf16(kRows, s.Dp, 0, 1);        // O += Kmat(K-major) . B(MN-major)
+      const uint32_t a_lbo = kRows * 16, b_lbo = kCols * 16;
+      uint32_t nb = 0, ns = 0, nk = 0, n_grad_items = 0;
+      int iter = 0;
+      auto gemm1 = [&](uint32_t slot) {
+        mbar_wait(bar(2 + slot), (nb / kBStages) & 1);
+        const uint32_t sb = ns & 1;
+        if (ns >= 2) mbar_wait(bar(10 + sb), ((ns >> 1) - 1) & 1);
+        fence_after_sync();
+        const uint32_t a_hi = sbase + L.A, a_lo = a_hi + a_half;
+        const uint32_t b_hi = sbase + L.B[slot], b_lo = b_hi + b_half;
+        uint32_t acc = 0;
+#pragma unroll
+        for (int pass = 0; pass < PASSES; ++pass) {
+          const uint32_t a0 = pass == 1 ? a_lo : a_hi, b0 = pass == 2 ? b_lo : b_hi;
+          for (int k = 0; k < s.Dp / 16; ++k) {
+            mma_bf16(tmem_S + sb * kCols, smem_desc(a0 + k * 2 * a_lbo, a_lbo, 128),
+                     smem_desc(b0 + k * 2 * b_lbo, b_lbo, 128), idesc1, acc);
+            acc = 1;
+          }
+        }
+        mma_commit(bar(8 + sb));
+        ++ns;
+      };
+      for (int idx = blockIdx.x; idx < n_items; idx += gridDim.x, ++iter) {
+        const Item it = get_item(s, idx);
+        mbar_wait(bar(0), iter & 1);
+        // live tiles of this item, in order
+        int live = 0;
+        for (int u = it.u0; u < it.u1; ++u) live += tile_live(s, get_tile(s, it, u)) ? 1 : 0;
+        const uint32_t nb0 = nb;
+        // software pipeline: G1(0), G1(1), then for each j: G2(j), G1(j+2)
+        int issued1 = 0;
+        for (; issued1 < 2 && issued1 < live; ++issued1) {
+          gemm1((nb0 + issued1) % kBStages);
+          if (!it.grad) mma_commit(bar(5 + (nb0 + issued1) % kBStages));
+          ++nb;
+        }
+        uint32_t oacc = 0;
+        for (int j = 0; j < live; ++j) {
+          if (it.grad) {
+            const uint32_t slot = (nb0 + j) % kBStages, kb = nk & 1;
+            mbar_wait(bar(12 + kb), (nk >> 1) & 1);
+            if (j == 0 && n_grad_items > 0) mbar_wait(bar(17), (n_grad_items - 1) & 1);
+            fence_after_sync();
+            const uint32_t k_hi = sbase + L.Kmat[kb], k_lo = k_hi + kRows * kCols * 2;
+            const uint32_t b_hi = sbase + L.B[slot], b_lo = b_hi + b_half;
+#pragma unroll
+            for (int pass = 0; pass < PASSES; ++pass) {
+              const uint32_t a0 = pass == 1 ? k_lo : k_hi, b0 = pass == 2 ? b_lo : b_hi;
+              for (int k = 0; k < kCols / 16; ++k) {
+                // A: K-major (K = column index), 128 rows ; B: MN-major (N = latent dim chunks, K = rows of the stage)
+                mma_bf16(tmem_O, smem_desc(a0 + k * 2 * a_lbo, a_lbo, 128),
+                         smem_desc(b0 + k * 16 * 16, 128, b_lbo), idesc2, oacc);
+                oacc = 1;
+              }
+            }
+            mma_commit(bar(5 + slot));
+            mma_commit(bar(14 + kb));
+            ++nk;
+          }
+          if (issued1 < live) {
+            gemm1((nb0 + issued1) % kBStages);
+            if (!it.grad) mma_commit(bar(5 + (nb0 + issued1) % kBStages));
+            ++nb;
+            ++issued1;
+          }
+        }
+        if (it.grad && live > 0) { mma_commit(bar(16)); ++n_grad_items; }
+        mma_commit(bar(1));
+      }
+    }
+  } else {
+    // ===== epilogue =====
+    const int ew = warp & 3;                                  // TMEM lane quadrant of this warp (warp id % 4)
+    const int t = ew * 32 + lane;                             // row within the block
+    double acc_sum[3] = {0.0, 0.0, 0.0};                      // zz, pz, pp
+    uint32_t ns = 0, nk = 0, nb = 0, n_grad_items = 0;
+    for (int idx = blockIdx.x; idx < n_items; idx += gridDim.x) {
+      const Item it = get_item(s, idx);
+      const int64_t grow = (int64_t)it.i * kRows + t;
+      const bool rvalid = grow < s.N;
+      const float nx = (it.grad ? normZ : normP)[grow];
+      float rs = 0.f;
+      int live = 0;
+      for (int u = it.u0; u < it.u1; ++u) {
+        const TileD td = get_tile(s, it, u);
+        if (!tile_live(s, td)) continue;
+        const uint32_t sb = ns & 1;
+        mbar_wait(bar(8 + sb), (ns >> 1) & 1);
+        fence_after_sync();
+        uint32_t ra[32], rb[32];
+        tmem_ld32(tmem_S + ((uint32_t)(ew * 32) << 16) + sb * kCols, ra);
+        tmem_ld32(tmem_S + ((uint32_t)(ew * 32) << 16) + sb * kCols + 32, rb);
+        tmem_ld_wait();
+        fence_before_sync();
+        mbar_arrive(bar(10 + sb));                            // S buffer free: the next GEMM1 may start
+        ++ns;
+        ++live;
+        const float* ny = reinterpret_cast<const float*>(smem + L.norms + (nb % kNormRing) * kCols * 4);
+        const int64_t gcol0 = (int64_t)td.jt * kCols;
+        const bool slow = td.diag || gcol0 + kCols > s.N || !rvalid;
+        const float sign = td.kind == 1 ? -1.f : 1.f;
+        float ksum = 0.f;
+        uint8_t* kh = smem + L.Kmat[nk & 1];
+        uint8_t* kl = kh + kRows * kCols * 2;
+        if (it.grad && nk >= 2) mbar_wait(bar(14 + (nk & 1)), ((nk >> 1) - 1) & 1);
+        auto half = [&](const uint32_t (&rr)[32], const int cbase) {
+#pragma unroll
+          for (int c8 = 0; c8 < 32; c8 += 8) {
+            float cv[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              const int c = cbase + c8 + e;
+              const float d2 = fmaxf(fmaf(-2.f, __uint_as_float(rr[c8 + e]), nx + ny[c]), 0.f);
+              float k, dk;
+              if (s.kernel_type == 0) {
+                k = exp2f(d2 * s.a_exp);
+                dk = k * s.dk_scale;
+              } else {
+                k = __fdividef(s.C, s.Ceps + d2);
+                dk = k * k * s.dk_scale;
+              }
+              if (slow) {
+                const bool ok = rvalid && (gcol0 + c < s.N) && !(s.kernel_type == 1 && td.diag && gcol0 + c == grow);
+                k = ok ? k : 0.f;
+                dk = ok ? dk : 0.f;
+              }
+              ksum += k;
+              cv[e] = dk * sign;
+              rs += cv[e];
+            }
+            if (it.grad) {
+              uint32_t ph[4], pl[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                __nv_bfloat16 h0, l0, h1, l1;
+                split_bf16(cv[2 * e], h0, l0);
+                split_bf16(cv[2 * e + 1], h1, l1);
+                ph[e] = pack2(h0, h1);
+                pl[e] = pack2(l0, l1);
+              }
+              const uint32_t off = ((uint32_t)((cbase + c8) >> 3) * kRows + t) * 16;
+              *reinterpret_cast<uint4*>(kh + off) = make_uint4(ph[0], ph[1], ph[2], ph[3]);
+              *reinterpret_cast<uint4*>(kl + off) = make_uint4(pl[0], pl[1], pl[2], pl[3]);
+            }
+          }
+        };
+        half(ra, 0);
+        half(rb, 32);
+        acc_sum[td.kind] += (double)(ksum * td.weight);
+        if (it.grad) {
+          fence_proxy_async();
+          mbar_arrive(bar(12 + (nk & 1)));
+          ++nk;
+        }
+        ++nb;
+      }
+      if (it.grad) {
+        const int q = (idx % (s.Q + 1));
+        const size_t lrow = (size_t)(it.i - s.rb0) * kRows + t;
+        const size_t nloc = (size_t)(s.rb1 - s.rb0) * kRows;
+        float* op = Opart + ((size_t)q * nloc + lrow) * s.Dp;
+        rspart[(size_t)q * nloc + lrow] = rs;
+        if (live == 0) {                                      // chunk made only of column tiles beyond N
+          for (int e = 0; e < s.Dp; ++e) op[e] = 0.f;
+          continue;
+        }
+        // O complete -> partial gradient rows to the workspace
+        mbar_wait(bar(16), n_grad_items & 1);
+        fence_after_sync();
+        for (int c0 = 0; c0 < s.Dp; c0 += 32) {
+          uint32_t o[32];
+          tmem_ld32(tmem_O + ((uint32_t)(ew * 32) << 16) + c0, o);
+          tmem_ld_wait();
+          if (c0 + 32 <= s.Dp) {
+#pragma unroll
+            for (int e = 0; e < 32; e += 4)
+              *reinterpret_cast<float4*>(op + c0 + e) = make_float4(__uint_as_float(o[e]), __uint_as_float(o[e + 1]),
+                                                                     __uint_as_float(o[e + 2]), __uint_as_float(o[e + 3]));
+          } else {
+            for (int e = 0; e < 32 && c0 + e < s.Dp; ++e) op[c0 + e] = __uint_as_float(o[e]);
+          }
+        }
+        fence_before_sync();
+        mbar_arrive(bar(17));
+        ++n_grad_items;
+      }
+    }
+    // per-CTA sums (fixed order) -> workspace
+    double* red = reinterpret_cast<double*>(smem + L.red);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) acc_sum[i] = warp_sum(acc_sum[i]);
+    if (lane == 0) for (int i = 0; i < 3; ++i) red[ew * 3 + i] = acc_sum[i];
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    if (t == 0) {
+      for (int i = 0; i < 3; ++i) cta_sums[blockIdx.x * 3 + i] = red[i] + red[3 + i] + red[6 + i] + red[9 + i];
+    }
+  }
+  fence_before_sync();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem, 512);
+}
+
+// ---- finalize: G_i = z_i * sum_q rs - sum_q O ; the three kernel sums ----------------------------------------
+__global__ void mmd_finalize_kernel(const float* __restrict__ Z, MmdShape s, const float* __restrict__ Opart,
+                                    const float* __restrict__ rspart, const double* __restrict__ cta_sums, int grid_main,
+                                    float* __restrict__ grad, double* __restrict__ sums) {
+  const int64_t row0 = (int64_t)s.rb0 * kRows;
+  const int64_t nloc_pad = (int64_t)(s.rb1 - s.rb0) * kRows;
+  int64_t nloc = s.N - row0;
+  if (nloc > nloc_pad) nloc = nloc_pad;
+  const int64_t total = nloc * s.D;
+  for (int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = g / s.D;
+    const int d = (int)(g % s.D);
+    float rs = 0.f, o = 0.f;
+    for (int q = 0; q < s.Q; ++q) {
+      rs += rspart[(size_t)q * nloc_pad + r];
+      o += Opart[((size_t)q * nloc_pad + r) * s.Dp + d];
+    }
+    grad[g] = fmaf(Z[(row0 + r) * s.D + d], rs, -o);
+  }
+  if (blockIdx.x == 0 && threadIdx.x < 3) {
+    double t = 0.0;
+    for (int c = 0; c < grid_main; ++c) t += cta_sums[c * 3 + threadIdx.x];
+    sums[threadIdx.x] = t;                       // order: zz, pz, pp
+  }
+}
+
+// out[4] = { mmd, term_pp, term_zz, term_pz } from the (all-reduced) sums {zz, pz, pp}; wae_mmd.py:197-203
+__global__ void mmd_combine_kernel(const double* __restrict__ sums, double n, int kernel_type, float reg, float* out) {
+  const double m = kernel_type == 0 ? 1.0 / (n * n) : 1.0;
+  const float zz = (float)(sums[0] * m), pz = (float)(sums[1] * m), pp = (float)(sums[2] * m);
+  out[0] = reg * pp + reg * zz - 2 * reg * pz;
+  out[1] = pp;
+  out[2] = zz;
+  out[3] = pz;
+}
+
+__global__ void scale_by_scalar_kernel(const float* __restrict__ in, const float* __restrict__ g, float factor, int64_t n,
+                                       float* __restrict__ out) {
+  const float f = (g ? *g : 1.f) * factor;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    out[i] = in[i] * f;
+}
+
+int make_shape(int64_t N, int64_t D, int kernel_type, float z_var, int passes, int64_t row_begin, int64_t row_end,
+               MmdShape& s) {
+  VK_REQUIRE(N >= 1 && D >= 1, VK_ERR_BAD_ARG, "mmd: empty z [%lld,%lld]", (long long)N, (long long)D);
+  VK_REQUIRE(D <= 128, VK_ERR_UNSUPPORTED, "mmd: latent dim %lld > 128 is not supported by the Gram tile kernel", (long long)D);
+  VK_REQUIRE(N <= (int64_t)1 << 24, VK_ERR_UNSUPPORTED, "mmd: N=%lld too large", (long long)N);
+  VK_REQUIRE(kernel_type == 0 || kernel_type == 1, VK_ERR_BAD_ARG, "mmd: unknown kernel type %d", kernel_type);
+  VK_REQUIRE(passes == 1 || passes == 3, VK_ERR_BAD_ARG, "mmd: passes must be 1 or 3");
+  VK_REQUIRE(row_begin >= 0 && row_begin < row_end && row_end <= N && row_begin % kRows == 0 &&
+             (row_end % kRows == 0 || row_end == N), VK_ERR_BAD_ARG,
+             "mmd: row range [%lld,%lld) must be 128-aligned inside [0,%lld)", (long long)row_begin, (long long)row_end, (long long)N);
+  s.N = N; s.D = (int)D; s.Dp = rup((int)D, 16); s.nkc = s.Dp / 8;
+  s.T = (int)((N + kRows - 1) / kRows);
+  s.rb0 = (int)(row_begin / kRows);
+  s.rb1 = (int)((row_end + kRows - 1) / kRows);
+  s.Q = pick_Q(s.T, s.rb1 - s.rb0);
+  s.kernel_type = kernel_type; s.passes = passes;
+  const double sp = 2.0 * (double)D * (double)D * (double)z_var;
+  s.a_exp = (float)(-1.4426950408889634 / sp);
+  s.C = (float)(2.0 * (double)D * (double)z_var);
+  s.Ceps = (float)(1e-7 + (double)s.C);
+  s.dk_scale = kernel_type == 0 ? (float)(-1.0 / sp) : -1.f / s.C;
+  return VK_OK;
+}
+
+}  // namespace
+}  // namespace vk
+
+using namespace vk;
+
+extern "C" int64_t vk_mmd_workspace_bytes(int64_t N, int64_t D) {
+  if (N < 1 || D < 1 || D > 128) return -1;
+  const int T = (int)((N + kRows - 1) / kRows);
+  return (int64_t)mmd_ws(N, (int)D, T, kMaxQ).total;
+}
+
+extern "C" int vk_mmd_fwd(const float* z, const float* prior, int64_t N, int64_t D, int kernel_type, float z_var,
+                          int passes, int64_t row_begin, int64_t row_end, double* sums_out, float* grad_unscaled,
+                          void* workspace, int64_t workspace_bytes, void* stream) {
+  VK_REQUIRE(z && prior && sums_out && grad_unscaled && workspace, VK_ERR_BAD_ARG, "mmd_fwd: null pointer");
+  MmdShape s;
+  int rc = make_shape(N, D, kernel_type, z_var, passes, row_begin, row_end, s);
+  if (rc != VK_OK) return rc;
+  const MmdWs w = mmd_ws(N, (int)D, s.rb1 - s.rb0, s.Q);
+  VK_REQUIRE(workspace_bytes >= (int64_t)w.total, VK_ERR_WORKSPACE, "mmd_fwd: workspace %lld < %lld",
+             (long long)workspace_bytes, (long long)w.total);
+  cudaStream_t st = (cudaStream_t)stream;
+  uint8_t* ws = (uint8_t*)workspace;
+  const int64_t pack_work = (int64_t)s.T * kRows * s.nkc;
+  const int pack_blocks = (int)((pack_work + 255) / 256 < 148 * 16 ? (pack_work + 255) / 256 : 148 * 16);
+  const int norm_blocks = (int)(((int64_t)s.T * kRows * 32 + 255) / 256);
+  mmd_pack_kernel<<<pack_blocks, 256, 0, st>>>(z, N, (int)D, s.Dp, ws + w.imgZ, (float*)(ws + w.normZ), s.T);
+  mmd_pack_kernel<<<pack_blocks, 256, 0, st>>>(prior, N, (int)D, s.Dp, ws + w.imgP, (float*)(ws + w.normP), s.T);
+  mmd_norm_kernel<<<norm_blocks, 256, 0, st>>>(z, N, (int)D, (float*)(ws + w.normZ), s.T);
+  mmd_norm_kernel<<<norm_blocks, 256, 0, st>>>(prior, N, (int)D, (float*)(ws + w.normP), s.T);
+  const MmdSmem L = mmd_smem(s.Dp);
+  const int n_items = (s.rb1 - s.rb0) * (s.Q + 1);
+  const int grid = n_items < sm_count() ? n_items : sm_count();
+  auto kern = passes == 3 ? mmd_main_kernel<3> : mmd_main_kernel<1>;
+  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total) != cudaSuccess)
+    return check_launch("mmd_fwd (shared memory attribute)");
+  kern<<<grid, kMmdThreads, L.total, st>>>(ws + w.imgZ, ws + w.imgP, (const float*)(ws + w.normZ),
+                                           (const float*)(ws + w.normP), s, n_items, (float*)(ws + w.Opart),
+                                           (float*)(ws + w.rspart), (double*)(ws + w.cta_sums));
+  rc = check_launch("mmd_main");
+  if (rc != VK_OK) return rc;
+  mmd_finalize_kernel<<<148 * 4, 256, 0, st>>>(z, s, (const float*)(ws + w.Opart), (const float*)(ws + w.rspart),
+                                               (const double*)(ws + w.cta_sums), grid, grad_unscaled, sums_out);
+  return check_launch("mmd_finalize");
+}
+
+extern "C" int vk_mmd_combine(const double* sums, int64_t N, int kernel_type, float reg_weight, float* out, void* stream) {
+  VK_REQUIRE(sums && out && N >= 1, VK_ERR_BAD_ARG, "mmd_combine: bad argument");
+  mmd_combine_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(sums, (double)N, kernel_type, reg_weight, out);
+  return check_launch("mmd_combine");
+}
+
+extern "C" int vk_scale_by_scalar(const float* in, const float* g, float factor, int64_t n, float* out, void* stream) {
+  VK_REQUIRE(in && out && n >= 0, VK_ERR_BAD_ARG, "scale_by_scalar: bad argument");
+  if (n == 0) return VK_OK;
+  const int blocks = (int)((n + 1023) / 1024 < 148 * 8 ? (n + 1023) / 1024 : 148 * 8);
+  scale_by_scalar_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(in, g, factor, n, out);
+  return check_launch("scale_by_scalar");
+}

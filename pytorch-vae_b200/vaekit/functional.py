@@ -263,3 +263,73 @@ class _VectorQuantize(torch.autograd.Function):
 def vector_quantize(latents, codebook, beta):
     """(quantized NCHW with straight-through gradient, vq_loss, indices[int32, B*H*W]) of vq_vae.py:24-55."""
     return _VectorQuantize.apply(latents, codebook, float(beta))
+
+
+# ---------------------------------------------------------------------------
+# K4
+# ---------------------------------------------------------------------------
+KERNEL_TYPES = {'rbf': 0, 'imq': 1}
+
+
+def mmd_sweep(z_all, prior_all, kernel_type, z_var, row_begin, row_end, passes=3):
+    """One Gram sweep (vk_mmd_fwd) over rows [row_begin,row_end) of the N x N kernel matrices.
+    Returns (sums[3] float64 device tensor {zz, pz, pp}, grad_unscaled [rows, D])."""
+    L.require(z_all, "z", dims=(2,)); L.require(prior_all, "prior_z", dims=(2,))
+    if z_all.shape != prior_all.shape:
+        raise RuntimeError("vaekit: z %s and prior_z %s differ in shape" % (tuple(z_all.shape), tuple(prior_all.shape)))
+    z, p = z_all.contiguous(), prior_all.contiguous()
+    N, D = z.shape
+    dev = z.device
+    need = int(L.lib().vk_mmd_workspace_bytes(N, D))
+    if need < 0:
+        raise RuntimeError("vaekit: MMD shape N=%d D=%d is not supported (latent dim must be <= 128)" % (N, D))
+    ws = L.workspace(dev, need)
+    sums = torch.empty(3, dtype=torch.float64, device=dev)
+    grad = torch.empty((row_end - row_begin, D), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        L.call("mmd_fwd", L.ptr(z), L.ptr(p), N, D, kernel_type, z_var, passes, row_begin, row_end, L.ptr(sums),
+               L.ptr(grad), L.ptr(ws), ws.numel(), L.stream_ptr())
+    return sums, grad
+
+
+def mmd_combine(sums, N, kernel_type, reg_weight):
+    out = torch.empty(4, dtype=torch.float32, device=sums.device)
+    with torch.cuda.device(sums.device):
+        L.call("mmd_combine", L.ptr(sums), N, kernel_type, reg_weight, L.ptr(out), L.stream_ptr())
+    return out
+
+
+def scale_by_scalar(t, g, factor):
+    out = torch.empty_like(t)
+    with torch.cuda.device(t.device):
+        L.call("scale_by_scalar", L.ptr(t), L.ptr(g), factor, t.numel(), L.ptr(out), L.stream_ptr())
+    return out
+
+
+class _Mmd(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, z, prior, kernel_type, z_var, reg_weight, passes):
+        N = z.shape[0]
+        sums, grad = mmd_sweep(z, prior, kernel_type, z_var, 0, N, passes)
+        out = mmd_combine(sums, N, kernel_type, reg_weight)
+        ctx.save_for_backward(grad)
+        ctx.factor = 4.0 * reg_weight * (1.0 / (float(N) * float(N)) if kernel_type == 0 else 1.0)
+        ctx.set_materialize_grads(False)
+        terms = out[1:].detach()
+        ctx.mark_non_differentiable(terms)
+        return out[0], terms
+
+    @staticmethod
+    def backward(ctx, g_mmd, _g_terms):
+        (grad,) = ctx.saved_tensors
+        if g_mmd is None:
+            return None, None, None, None, None, None
+        return scale_by_scalar(grad, g_mmd.contiguous(), ctx.factor), None, None, None, None, None
+
+
+def mmd(z, prior_z, reg_weight, kernel_type, z_var, passes=3):
+    """wae_mmd.py:193-204 with the prior sample given: returns (mmd, terms[3] = {pp, zz, pz} kernel means/sums).
+    Value and d mmd/d z come out of one tcgen05 Gram sweep; backward only rescales the saved gradient."""
+    if kernel_type not in KERNEL_TYPES:
+        raise ValueError('Undefined kernel type.')
+    return _Mmd.apply(z, prior_z, KERNEL_TYPES[kernel_type], float(z_var), float(reg_weight), int(passes))

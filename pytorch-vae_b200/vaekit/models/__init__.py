@@ -7,6 +7,7 @@ from .logcosh_vae import LogCoshVAE
 from .iwae import IWAE
 from .miwae import MIWAE
 from .vq_vae import VQVAE, VectorQuantizer
+from .wae_mmd import WAE_MMD
 
 VAE = VanillaVAE
 GaussianVAE = VanillaVAE
@@ -18,4 +19,5 @@ vae_models = {
     'LogCoshVAE': LogCoshVAE,
     'VanillaVAE': VanillaVAE,
     'VQVAE': VQVAE,
+    'WAE_MMD': WAE_MMD,
 }

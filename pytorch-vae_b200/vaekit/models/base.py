@@ -126,3 +126,38 @@ class GaussianConvVAE(BaseVAE):
 
     def generate(self, x: Tensor, **kwargs) -> Tensor:
         return self.forward(x)[0]
+
+
+class DeterministicConvAE(BaseVAE):
+    """Encoder -> z -> decoder skeleton shared by wae_mmd.py:10-105 and swae.py:10-108 (fc_z instead of
+    fc_mu / fc_var; the decoder reshape is hard-wired to 512 channels as in the reference)."""
+
+    def __init__(self, in_channels: int, latent_dim: int, hidden_dims: List = None) -> None:
+        super().__init__()
+        self.latent_dim = latent_dim
+        if hidden_dims is None:
+            hidden_dims = [32, 64, 128, 256, 512]
+        self.encoder = down_stack(in_channels, hidden_dims)
+        self.fc_z = nn.Linear(hidden_dims[-1] * 4, latent_dim)
+        self.decoder_input = nn.Linear(latent_dim, hidden_dims[-1] * 4)
+        hidden_dims.reverse()
+        self.decoder = up_stack(hidden_dims)
+        self.final_layer = output_head(hidden_dims[-1])
+
+    def encode(self, input: Tensor) -> Tensor:
+        return self.fc_z(torch.flatten(self.encoder(input), start_dim=1))
+
+    def decode(self, z: Tensor) -> Tensor:
+        h = self.decoder_input(z).view(-1, 512, 2, 2)
+        return self.final_layer(self.decoder(h))
+
+    def forward(self, input: Tensor, **kwargs) -> List[Tensor]:
+        z = self.encode(input)
+        return [self.decode(z), input, z]
+
+    def sample(self, num_samples: int, current_device: int, **kwargs) -> Tensor:
+        z = torch.randn(num_samples, self.latent_dim)
+        return self.decode(z.to(current_device))
+
+    def generate(self, x: Tensor, **kwargs) -> Tensor:
+        return self.forward(x)[0]
