@@ -33,7 +33,9 @@ constexpr int kRows = 128;       // row block (MMA M)
 constexpr int kCols = 64;        // column tile (GEMM1 N, GEMM2 K)
 constexpr int kBStages = 3;
 constexpr int kNormRing = 8;
-constexpr int kMmdThreads = 32 * 6;   // warp 0 TMA, warp 1 MMA, warps 2-5 epilogue
+constexpr int kEpiWarps = 8, kTmaWarp = 8, kMmaWarp = 9;
+constexpr int kEpiThreads = 32 * kEpiWarps;
+constexpr int kMmdThreads = 32 * 10;  // warps 0-7 epilogue, warp 8 TMA, warp 9 MMA
 constexpr int kMaxQ = 8;
 
 struct MmdShape {
@@ -53,7 +55,7 @@ __host__ __device__ inline int rup(int x, int m) { return (x + m - 1) / m * m; }
 __host__ __device__ inline uint32_t tile_img_bytes(int Dp) { return 2u * kRows * Dp * 2u; }   // hi + lo of 128 rows
 
 struct MmdWs {
-  size_t cta_sums, imgZ, imgP, normZ, normP, Opart, rspart, total;
+  size_t cta_sums, imgZ, imgP, imgZb, imgPb, normZ, normP, Opart, rspart, total;
 };
 inline MmdWs mmd_ws(int64_t N, int D, int rows_local_blocks, int Q) {
   const int Dp = rup(D, 16);
@@ -64,10 +66,12 @@ inline MmdWs mmd_ws(int64_t N, int D, int rows_local_blocks, int Q) {
   o = (o + 255) & ~(size_t)255;
   w.imgZ = o; o += (size_t)T * tile_img_bytes(Dp);
   w.imgP = o; o += (size_t)T * tile_img_bytes(Dp);
+  w.imgZb = o; o += (size_t)T * tile_img_bytes(Dp);      // same data as 64-row granules (B stages: one bulk copy each)
+  w.imgPb = o; o += (size_t)T * tile_img_bytes(Dp);
   w.normZ = o; o += (size_t)T * kRows * 4;
   w.normP = o; o += (size_t)T * kRows * 4;
   w.Opart = o; o += (size_t)Q * rows_local_blocks * kRows * Dp * 4;
-  w.rspart = o; o += (size_t)Q * rows_local_blocks * kRows * 4;
+  w.rspart = o; o += (size_t)2 * Q * rows_local_blocks * kRows * 4;   // two column halves per chunk
   w.total = o;
   return w;
 }
@@ -93,14 +97,14 @@ __host__ __device__ inline MmdSmem mmd_smem(int Dp) {
   m.norms = o; o += kNormRing * kCols * 4u;   // deeper than the B ring: read by the epilogue after b_empty may have fired
   m.bars = o; o += 24 * 8;
   m.tmem = o; o += 16;
-  m.red = o; o += 4 * 3 * 8;
+  m.red = o; o += kEpiWarps * 3 * 8;
   m.total = o;
   return m;
 }
 
 // ---- pack: fp32 [N,D] -> image tiles [T][hi/lo][Dp/8][128][8] bf16 ; norms [T*128] fp32 ----------------------
 __global__ void mmd_pack_kernel(const float* __restrict__ X, int64_t N, int D, int Dp, uint8_t* __restrict__ img,
-                                float* __restrict__ norms, int T) {
+                                uint8_t* __restrict__ imgB, int T) {
   const int nkc = Dp / 8;
   const int64_t total = (int64_t)T * kRows * nkc;
   for (int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (int64_t)gridDim.x * blockDim.x) {
@@ -126,6 +130,11 @@ __global__ void mmd_pack_kernel(const float* __restrict__ X, int64_t N, int D, i
     uint8_t* base = img + tile * tile_img_bytes(Dp);
     *reinterpret_cast<uint4*>(base + ((size_t)kc * kRows + r) * 16) = make_uint4(ph[0], ph[1], ph[2], ph[3]);
     *reinterpret_cast<uint4*>(base + ((size_t)(nkc + kc) * kRows + r) * 16) = make_uint4(pl[0], pl[1], pl[2], pl[3]);
+    // 64-row granule copy of the same data: [granule][hi/lo][Dp/8][64][8]
+    uint8_t* gb = imgB + (row / kCols) * (tile_img_bytes(Dp) / 2);
+    const int rb = (int)(row % kCols);
+    *reinterpret_cast<uint4*>(gb + ((size_t)kc * kCols + rb) * 16) = make_uint4(ph[0], ph[1], ph[2], ph[3]);
+    *reinterpret_cast<uint4*>(gb + ((size_t)(nkc + kc) * kCols + rb) * 16) = make_uint4(pl[0], pl[1], pl[2], pl[3]);
   }
 }
 // one warp per row, fixed summation order
@@ -192,14 +201,20 @@ __device__ __forceinline__ TileD get_tile(const MmdShape& s, const Item& it, int
   }
   return t;
 }
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 __device__ __forceinline__ bool tile_live(const MmdShape& s, const TileD& t) { return (int64_t)t.jt * kCols < s.N; }
 
 // ---- main kernel ----------------------------------------------------------------------------------------------
 // barriers: 0 a_full | 1 a_empty | 2..4 b_full | 5..7 b_empty | 8,9 s_full | 10,11 s_empty | 12,13 k_full |
 //           14,15 k_empty | 16 o_full | 17 o_empty
-template <int PASSES>
+template <int PASSES, int KT>
 __global__ void __launch_bounds__(kMmdThreads, 1)
-mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ imgP, const float* __restrict__ normZ,
+mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ imgP, const uint8_t* __restrict__ imgZb,
+                const uint8_t* __restrict__ imgPb, const float* __restrict__ normZ,
                 const float* __restrict__ normP, MmdShape s, int n_items, float* __restrict__ Opart,
                 float* __restrict__ rspart, double* __restrict__ cta_sums) {
   extern __shared__ __align__(128) uint8_t smem[];
@@ -212,13 +227,13 @@ mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ im
     mbar_init(bar(0), 1); mbar_init(bar(1), 1);
     for (int i = 0; i < kBStages; ++i) { mbar_init(bar(2 + i), 1); mbar_init(bar(5 + i), 1); }
     for (int i = 0; i < 2; ++i) {
-      mbar_init(bar(8 + i), 1); mbar_init(bar(10 + i), 128);
-      mbar_init(bar(12 + i), 128); mbar_init(bar(14 + i), 1);
+      mbar_init(bar(8 + i), 1); mbar_init(bar(10 + i), kEpiThreads);
+      mbar_init(bar(12 + i), kEpiThreads); mbar_init(bar(14 + i), 1);
     }
-    mbar_init(bar(16), 1); mbar_init(bar(17), 128);
+    mbar_init(bar(16), 1); mbar_init(bar(17), kEpiThreads);
     mbar_fence_init();
   }
-  if (warp == 1) tmem_alloc(smem_u32(tmem_slot), 512);
+  if (warp == kMmaWarp) tmem_alloc(smem_u32(tmem_slot), 512);
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
@@ -228,7 +243,7 @@ mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ im
   const uint32_t b_half = (uint32_t)kCols * s.Dp * 2u;      // one hi (or lo) image of a 64-row stage
   const uint32_t a_half = (uint32_t)kRows * s.Dp * 2u;
 
-  if (warp == 0) {
+  if (warp == kTmaWarp) {
     // ===== TMA producer =====
     if (lane == 0) {
       uint32_t nb = 0;
@@ -244,17 +259,16 @@ mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ im
           if (!tile_live(s, t)) continue;
           const uint32_t slot = nb % kBStages;
           if (nb >= kBStages) mbar_wait(bar(5 + slot), ((nb / kBStages) - 1) & 1);
-          const uint8_t* bimg = (t.bm ? imgP : imgZ) + (size_t)(t.jt >> 1) * a_bytes + (size_t)(t.jt & 1) * kCols * 16;
+          const uint8_t* bimg = (t.bm ? imgPb : imgZb) + (size_t)t.jt * (2 * b_half);
           const float* nrm = (t.bm ? normP : normZ) + (size_t)t.jt * kCols;
           mbar_expect_tx(bar(2 + slot), 2 * b_half + kCols * 4);
-          for (int c = 0; c < 2 * s.nkc; ++c)               // hi chunks then lo chunks: 64 rows x 16 B each
-            bulk_g2s(sbase + L.B[slot] + c * kCols * 16, bimg + (size_t)c * kRows * 16, kCols * 16, bar(2 + slot));
+          bulk_g2s(sbase + L.B[slot], bimg, 2 * b_half, bar(2 + slot));      // hi + lo images of 64 rows, one copy
           bulk_g2s(sbase + L.norms + (nb % kNormRing) * kCols * 4, nrm, kCols * 4, bar(2 + slot));
           ++nb;
         }
       }
     }
-  } else if (warp == 1) {
+  } else if (warp == kMmaWarp) {
     // ===== MMA issuer =====
     if (lane == 0) {
       const uint32_t idesc1 = idesc_bf16(kRows, kCols, 0, 0);       // S = A(K-major) . B(K-major)^T
@@ -331,10 +345,11 @@ mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ im
       }
     }
   } else {
-    // ===== epilogue =====
-    const int ew = warp & 3;                                  // TMEM lane quadrant of this warp (warp id % 4)
+    // ===== epilogue: 8 warps = 4 TMEM lane quadrants x 2 column halves (32 of the 64 tile columns each) =====
+    const int ew = warp & 3;                                  // TMEM lane quadrant (must equal warp id % 4)
+    const int h = warp >> 2;                                  // column half
     const int t = ew * 32 + lane;                             // row within the block
-    double acc_sum[3] = {0.0, 0.0, 0.0};                      // zz, pz, pp
+    double acc_zz = 0.0, acc_pz = 0.0, acc_pp = 0.0;
     uint32_t ns = 0, nk = 0, nb = 0, n_grad_items = 0;
     for (int idx = blockIdx.x; idx < n_items; idx += gridDim.x) {
       const Item it = get_item(s, idx);
@@ -349,66 +364,63 @@ mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ im
         const uint32_t sb = ns & 1;
         mbar_wait(bar(8 + sb), (ns >> 1) & 1);
         fence_after_sync();
-        uint32_t ra[32], rb[32];
-        tmem_ld32(tmem_S + ((uint32_t)(ew * 32) << 16) + sb * kCols, ra);
-        tmem_ld32(tmem_S + ((uint32_t)(ew * 32) << 16) + sb * kCols + 32, rb);
+        uint32_t rr[32];
+        tmem_ld32(tmem_S + ((uint32_t)(ew * 32) << 16) + sb * kCols + h * 32, rr);
         tmem_ld_wait();
         fence_before_sync();
         mbar_arrive(bar(10 + sb));                            // S buffer free: the next GEMM1 may start
         ++ns;
         ++live;
-        const float* ny = reinterpret_cast<const float*>(smem + L.norms + (nb % kNormRing) * kCols * 4);
-        const int64_t gcol0 = (int64_t)td.jt * kCols;
-        const bool slow = td.diag || gcol0 + kCols > s.N || !rvalid;
+        const float* ny = reinterpret_cast<const float*>(smem + L.norms + (nb % kNormRing) * kCols * 4) + h * 32;
+        const int64_t gcol0 = (int64_t)td.jt * kCols + h * 32;
+        const bool slow = td.diag || gcol0 + 32 > s.N || !rvalid;
         const float sign = td.kind == 1 ? -1.f : 1.f;
         float ksum = 0.f;
         uint8_t* kh = smem + L.Kmat[nk & 1];
         uint8_t* kl = kh + kRows * kCols * 2;
         if (it.grad && nk >= 2) mbar_wait(bar(14 + (nk & 1)), ((nk >> 1) - 1) & 1);
-        auto half = [&](const uint32_t (&rr)[32], const int cbase) {
+        const bool diag_excl = KT == 1 && td.diag;
 #pragma unroll
-          for (int c8 = 0; c8 < 32; c8 += 8) {
-            float cv[8];
+        for (int c8 = 0; c8 < 32; c8 += 8) {
+          float cv[8];
 #pragma unroll
-            for (int e = 0; e < 8; ++e) {
-              const int c = cbase + c8 + e;
-              const float d2 = fmaxf(fmaf(-2.f, __uint_as_float(rr[c8 + e]), nx + ny[c]), 0.f);
-              float k, dk;
-              if (s.kernel_type == 0) {
-                k = exp2f(d2 * s.a_exp);
-                dk = k * s.dk_scale;
-              } else {
-                k = __fdividef(s.C, s.Ceps + d2);
-                dk = k * k * s.dk_scale;
-              }
-              if (slow) {
-                const bool ok = rvalid && (gcol0 + c < s.N) && !(s.kernel_type == 1 && td.diag && gcol0 + c == grow);
-                k = ok ? k : 0.f;
-                dk = ok ? dk : 0.f;
-              }
-              ksum += k;
-              cv[e] = dk * sign;
-              rs += cv[e];
+          for (int e = 0; e < 8; ++e) {
+            const int c = c8 + e;
+            const float d2 = fmaxf(fmaf(-2.f, __uint_as_float(rr[c]), nx + ny[c]), 0.f);
+            float k, dk;
+            if (KT == 0) {
+              k = ex2_approx(d2 * s.a_exp);
+              dk = k * s.dk_scale;
+            } else {
+              k = __fdividef(s.C, s.Ceps + d2);
+              dk = k * k * s.dk_scale;
             }
-            if (it.grad) {
-              uint32_t ph[4], pl[4];
-#pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                __nv_bfloat16 h0, l0, h1, l1;
-                split_bf16(cv[2 * e], h0, l0);
-                split_bf16(cv[2 * e + 1], h1, l1);
-                ph[e] = pack2(h0, h1);
-                pl[e] = pack2(l0, l1);
-              }
-              const uint32_t off = ((uint32_t)((cbase + c8) >> 3) * kRows + t) * 16;
-              *reinterpret_cast<uint4*>(kh + off) = make_uint4(ph[0], ph[1], ph[2], ph[3]);
-              *reinterpret_cast<uint4*>(kl + off) = make_uint4(pl[0], pl[1], pl[2], pl[3]);
+            cv[e] = dk * sign;
+            if (slow) {                                       // warp-uniform except for rvalid (tail rows)
+              const bool ok = rvalid && (gcol0 + c < s.N) && !(diag_excl && gcol0 + c == grow);
+              k = ok ? k : 0.f;
+              cv[e] = ok ? cv[e] : 0.f;
             }
+            ksum += k;
+            rs += cv[e];
           }
-        };
-        half(ra, 0);
-        half(rb, 32);
-        acc_sum[td.kind] += (double)(ksum * td.weight);
+          if (it.grad) {
+            uint32_t ph[4], pl[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              __nv_bfloat16 h0, l0, h1, l1;
+              split_bf16(cv[2 * e], h0, l0);
+              split_bf16(cv[2 * e + 1], h1, l1);
+              ph[e] = pack2(h0, h1);
+              pl[e] = pack2(l0, l1);
+            }
+            const uint32_t off = ((uint32_t)((h * 32 + c8) >> 3) * kRows + t) * 16;
+            *reinterpret_cast<uint4*>(kh + off) = make_uint4(ph[0], ph[1], ph[2], ph[3]);
+            *reinterpret_cast<uint4*>(kl + off) = make_uint4(pl[0], pl[1], pl[2], pl[3]);
+          }
+        }
+        const double kw = (double)(ksum * td.weight);
+        if (td.kind == 0) acc_zz += kw; else if (td.kind == 1) acc_pz += kw; else acc_pp += kw;
         if (it.grad) {
           fence_proxy_async();
           mbar_arrive(bar(12 + (nk & 1)));
@@ -421,15 +433,15 @@ mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ im
         const size_t lrow = (size_t)(it.i - s.rb0) * kRows + t;
         const size_t nloc = (size_t)(s.rb1 - s.rb0) * kRows;
         float* op = Opart + ((size_t)q * nloc + lrow) * s.Dp;
-        rspart[(size_t)q * nloc + lrow] = rs;
+        rspart[((size_t)q * 2 + h) * nloc + lrow] = rs;
         if (live == 0) {                                      // chunk made only of column tiles beyond N
-          for (int e = 0; e < s.Dp; ++e) op[e] = 0.f;
+          for (int e = h; e < s.Dp; e += 2) op[e] = 0.f;
           continue;
         }
-        // O complete -> partial gradient rows to the workspace
+        // O complete -> partial gradient rows to the workspace (32-column chunks alternate between the halves)
         mbar_wait(bar(16), n_grad_items & 1);
         fence_after_sync();
-        for (int c0 = 0; c0 < s.Dp; c0 += 32) {
+        for (int c0 = h * 32; c0 < s.Dp; c0 += 64) {
           uint32_t o[32];
           tmem_ld32(tmem_O + ((uint32_t)(ew * 32) << 16) + c0, o);
           tmem_ld_wait();
@@ -439,7 +451,8 @@ mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ im
               *reinterpret_cast<float4*>(op + c0 + e) = make_float4(__uint_as_float(o[e]), __uint_as_float(o[e + 1]),
                                                                      __uint_as_float(o[e + 2]), __uint_as_float(o[e + 3]));
           } else {
-            for (int e = 0; e < 32 && c0 + e < s.Dp; ++e) op[c0 + e] = __uint_as_float(o[e]);
+#pragma unroll
+            for (int e = 0; e < 32; ++e) if (c0 + e < s.Dp) op[c0 + e] = __uint_as_float(o[e]);
           }
         }
         fence_before_sync();
@@ -449,17 +462,18 @@ mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ im
     }
     // per-CTA sums (fixed order) -> workspace
     double* red = reinterpret_cast<double*>(smem + L.red);
-#pragma unroll
-    for (int i = 0; i < 3; ++i) acc_sum[i] = warp_sum(acc_sum[i]);
-    if (lane == 0) for (int i = 0; i < 3; ++i) red[ew * 3 + i] = acc_sum[i];
-    asm volatile("bar.sync 1, 128;" ::: "memory");
-    if (t == 0) {
-      for (int i = 0; i < 3; ++i) cta_sums[blockIdx.x * 3 + i] = red[i] + red[3 + i] + red[6 + i] + red[9 + i];
+    acc_zz = warp_sum(acc_zz); acc_pz = warp_sum(acc_pz); acc_pp = warp_sum(acc_pp);
+    if (lane == 0) { red[warp * 3 + 0] = acc_zz; red[warp * 3 + 1] = acc_pz; red[warp * 3 + 2] = acc_pp; }
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    if (threadIdx.x < 3) {
+      double tot = 0.0;
+      for (int w = 0; w < kEpiWarps; ++w) tot += red[w * 3 + threadIdx.x];
+      cta_sums[blockIdx.x * 3 + threadIdx.x] = tot;
     }
   }
   fence_before_sync();
   __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem, 512);
+  if (warp == kMmaWarp) tmem_dealloc(tmem, 512);
 }
 
 // ---- finalize: G_i = z_i * sum_q rs - sum_q O ; the three kernel sums ----------------------------------------
@@ -476,7 +490,8 @@ __global__ void mmd_finalize_kernel(const float* __restrict__ Z, MmdShape s, con
     const int d = (int)(g % s.D);
     float rs = 0.f, o = 0.f;
     for (int q = 0; q < s.Q; ++q) {
-      rs += rspart[(size_t)q * nloc_pad + r];
+      rs += rspart[(size_t)(2 * q) * nloc_pad + r];
+      rs += rspart[(size_t)(2 * q + 1) * nloc_pad + r];
       o += Opart[((size_t)q * nloc_pad + r) * s.Dp + d];
     }
     grad[g] = fmaf(Z[(row0 + r) * s.D + d], rs, -o);
@@ -555,17 +570,18 @@ extern "C" int vk_mmd_fwd(const float* z, const float* prior, int64_t N, int64_t
   const int64_t pack_work = (int64_t)s.T * kRows * s.nkc;
   const int pack_blocks = (int)((pack_work + 255) / 256 < 148 * 16 ? (pack_work + 255) / 256 : 148 * 16);
   const int norm_blocks = (int)(((int64_t)s.T * kRows * 32 + 255) / 256);
-  mmd_pack_kernel<<<pack_blocks, 256, 0, st>>>(z, N, (int)D, s.Dp, ws + w.imgZ, (float*)(ws + w.normZ), s.T);
-  mmd_pack_kernel<<<pack_blocks, 256, 0, st>>>(prior, N, (int)D, s.Dp, ws + w.imgP, (float*)(ws + w.normP), s.T);
+  mmd_pack_kernel<<<pack_blocks, 256, 0, st>>>(z, N, (int)D, s.Dp, ws + w.imgZ, ws + w.imgZb, s.T);
+  mmd_pack_kernel<<<pack_blocks, 256, 0, st>>>(prior, N, (int)D, s.Dp, ws + w.imgP, ws + w.imgPb, s.T);
   mmd_norm_kernel<<<norm_blocks, 256, 0, st>>>(z, N, (int)D, (float*)(ws + w.normZ), s.T);
   mmd_norm_kernel<<<norm_blocks, 256, 0, st>>>(prior, N, (int)D, (float*)(ws + w.normP), s.T);
   const MmdSmem L = mmd_smem(s.Dp);
   const int n_items = (s.rb1 - s.rb0) * (s.Q + 1);
   const int grid = n_items < sm_count() ? n_items : sm_count();
-  auto kern = passes == 3 ? mmd_main_kernel<3> : mmd_main_kernel<1>;
+  auto kern = passes == 3 ? (kernel_type == 0 ? mmd_main_kernel<3, 0> : mmd_main_kernel<3, 1>)
+                          : (kernel_type == 0 ? mmd_main_kernel<1, 0> : mmd_main_kernel<1, 1>);
   if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total) != cudaSuccess)
     return check_launch("mmd_fwd (shared memory attribute)");
-  kern<<<grid, kMmdThreads, L.total, st>>>(ws + w.imgZ, ws + w.imgP, (const float*)(ws + w.normZ),
+  kern<<<grid, kMmdThreads, L.total, st>>>(ws + w.imgZ, ws + w.imgP, ws + w.imgZb, ws + w.imgPb, (const float*)(ws + w.normZ),
                                            (const float*)(ws + w.normP), s, n_items, (float*)(ws + w.Opart),
                                            (float*)(ws + w.rspart), (double*)(ws + w.cta_sums));
   rc = check_launch("mmd_main");

@@ -1,0 +1,38 @@
+"""Quick device timings of single ops (not the bench contract; used while tuning)."""
+import os, sys, time
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "pytorch-vae_b200"))
+import torch
+from vaekit import functional as F
+
+def timeit(fn, warm=2, it=5):
+    for _ in range(warm): fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(it): fn()
+    e1.record(); torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / it
+
+dev = torch.device("cuda")
+which = sys.argv[1:] or ["mmd", "vq"]
+if "mmd" in which:
+    for N in (8192, 65536):
+        z = torch.randn(N, 128, device=dev) + 0.25; p = torch.randn(N, 128, device=dev)
+        for kt in (0, 1):
+            for passes in (3, 1):
+                ms = timeit(lambda: F.mmd_sweep(z, p, kt, 2.0, 0, N, passes))
+                fl = 10.0 * N * N * 128
+                print("mmd N=%d kernel=%d passes=%d: %.3f ms  %.2f Msamples/s  algorithmic %.1f TFLOP/s" % (N, kt, passes, ms, N / ms / 1e3, fl / ms / 1e9), flush=True)
+if "vq" in which:
+    lat = torch.nn.functional.leaky_relu(torch.randn(1024, 64, 16, 16, device=dev)); cb = torch.randn(512, 64, device=dev)
+    ms = timeit(lambda: F.vector_quantize(lat, cb, 0.25), it=20)
+    print("vq fwd B=1024: %.4f ms  %.2f M images/s, %.1f GB/s on 135.4 MB" % (ms, 1024 / ms / 1e3, 135.4e6 / ms / 1e6))
+    latg = lat.clone().requires_grad_(True); cbg = cb.clone().requires_grad_(True)
+    gq = torch.randn_like(lat) * 1e-3
+    def step():
+        latg.grad = None; cbg.grad = None
+        q, l, _ = F.vector_quantize(latg, cbg, 0.25)
+        torch.autograd.backward([q, l], [gq, None])
+    ms = timeit(step, it=20)
+    print("vq fwd+bwd B=1024: %.4f ms  %.2f M images/s, %.1f GB/s on 337.9 MB" % (ms, 1024 / ms / 1e3, 337.9e6 / ms / 1e6))
