@@ -183,6 +183,28 @@ int vk_mmd_combine(const double* sums /*[3]*/, int64_t N, int kernel_type, float
 /* out[i] = in[i] * (*g) * factor  (g may be NULL = 1): backward of an op whose gradient was produced in the forward sweep */
 int vk_scale_by_scalar(const float* in, const float* g, float factor, int64_t n, float* out, void* stream);
 
+/* ---------------------------------------------------------------------------
+ * K6  SWAE sliced-Wasserstein distance       (reference: models/swae.py:151-179)
+ *
+ * z, prior [N, D]; proj [S, D] unit-norm projection directions (swae.py:129-148 builds them on the CPU generator;
+ * S may be one rank's shard of the model's projections).  One call produces
+ *   sum_out (double, device)      = sum_{s,i} (sort_i(z.theta_s) - sort_i(prior.theta_s))^p
+ *   grad_unscaled [N, D] or NULL  = d sum_out / d z          (through the sort permutation)
+ * so that  swd = reg * sum / (S_total N)  and  d swd / dz = reg / (S_total N) * grad_unscaled.
+ * Steps: fp32 projection GEMM stored projection-major, segmented LSD radix sort (8-bit digits; key + sample index
+ * for z, key-only for the prior), loss + scatter of d/dlat, fp32 GEMM back to [N, D].
+ * vk_mean_scale: out[0] = scale * (float)(sum / count)     (reg_weight * w_dist.mean(), swae.py:179)
+ * vk_seg_sort: the sort on its own -- keys [segments, n] fp32 ascending in place, perm_out (uint32 source index
+ * of every sorted element) or NULL.
+ * -------------------------------------------------------------------------*/
+int64_t vk_swd_workspace_bytes(int64_t N, int64_t S);
+int vk_swd_fwd(const float* z, const float* prior, const float* proj, int64_t N, int64_t D, int64_t S, float p,
+               double* sum_out, float* grad_unscaled, void* workspace, int64_t workspace_bytes, void* stream);
+int vk_mean_scale(const double* sum, double count, float scale, float* out, void* stream);
+int64_t vk_seg_sort_workspace_bytes(int64_t segments, int64_t n);
+int vk_seg_sort(float* keys, uint32_t* perm_out, int64_t segments, int64_t n, void* workspace,
+                int64_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -33,6 +33,11 @@ _SIGNATURES = {
     "vk_mmd_fwd": ([_p, _p, _i64, _i64, _i, _f, _i, _i64, _i64, _p, _p, _p, _i64, _p], _i),
     "vk_mmd_combine": ([_p, _i64, _i, _f, _p, _p], _i),
     "vk_scale_by_scalar": ([_p, _p, _f, _i64, _p, _p], _i),
+    "vk_swd_workspace_bytes": ([_i64, _i64], _i64),
+    "vk_swd_fwd": ([_p, _p, _p, _i64, _i64, _i64, _f, _p, _p, _p, _i64, _p], _i),
+    "vk_mean_scale": ([_p, C.c_double, _f, _p, _p], _i),
+    "vk_seg_sort_workspace_bytes": ([_i64, _i64], _i64),
+    "vk_seg_sort": ([_p, _p, _i64, _i64, _p, _i64, _p], _i),
     "vk_iw_bound_bwd": ([_p, _p, _p, _p, _i64, _i64, _i64, _i64, _f, _p, _p, _p, _p, _p, _p, _p], _i),
 }
 

@@ -333,3 +333,74 @@ def mmd(z, prior_z, reg_weight, kernel_type, z_var, passes=3):
     if kernel_type not in KERNEL_TYPES:
         raise ValueError('Undefined kernel type.')
     return _Mmd.apply(z, prior_z, KERNEL_TYPES[kernel_type], float(z_var), float(reg_weight), int(passes))
+
+
+# ---------------------------------------------------------------------------
+# K6
+# ---------------------------------------------------------------------------
+def swd_sweep(z, prior, proj, p, want_grad=True):
+    """Projection GEMM + segmented radix sorts + loss (+ d/dz) for the projections in `proj` [S, D] (vk_swd_fwd).
+    Returns (sum[1] float64 device tensor = sum (sorted diff)^p, grad_unscaled [N, D] or None)."""
+    L.require(z, "z", dims=(2,)); L.require(prior, "prior_z", dims=(2,)); L.require(proj, "projections", dims=(2,))
+    if z.shape != prior.shape or proj.shape[1] != z.shape[1]:
+        raise RuntimeError("vaekit: z %s, prior_z %s and projections %s do not fit together" %
+                           (tuple(z.shape), tuple(prior.shape), tuple(proj.shape)))
+    zc, pc, th = z.contiguous(), prior.contiguous(), proj.contiguous()
+    N, D = zc.shape
+    S = th.shape[0]
+    if N * S == 0:
+        raise RuntimeError("vaekit: empty input to the sliced-Wasserstein distance")
+    dev = zc.device
+    ws = L.workspace(dev, int(L.lib().vk_swd_workspace_bytes(N, S)))
+    total = torch.empty(1, dtype=torch.float64, device=dev)
+    grad = torch.empty((N, D), dtype=torch.float32, device=dev) if want_grad else None
+    with torch.cuda.device(dev):
+        L.call("swd_fwd", L.ptr(zc), L.ptr(pc), L.ptr(th), N, D, S, p, L.ptr(total), L.ptr(grad), L.ptr(ws), ws.numel(),
+               L.stream_ptr())
+    return total, grad
+
+
+def mean_scale(total, count, scale):
+    out = torch.empty(1, dtype=torch.float32, device=total.device)
+    with torch.cuda.device(total.device):
+        L.call("mean_scale", L.ptr(total), float(count), scale, L.ptr(out), L.stream_ptr())
+    return out[0]
+
+
+class _Swd(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, z, prior, proj, p, reg_weight):
+        total, grad = swd_sweep(z, prior, proj, p, want_grad=ctx.needs_input_grad[0])
+        count = float(z.shape[0]) * float(proj.shape[0])
+        if grad is not None:
+            ctx.save_for_backward(grad)
+        ctx.factor = reg_weight / count
+        ctx.set_materialize_grads(False)
+        return mean_scale(total, count, reg_weight)
+
+    @staticmethod
+    def backward(ctx, g):
+        if g is None or not ctx.saved_tensors:
+            return None, None, None, None, None
+        return scale_by_scalar(ctx.saved_tensors[0], g.contiguous(), ctx.factor), None, None, None, None
+
+
+def swd(z, prior_z, proj, p, reg_weight):
+    """swae.py:165-179 with the prior sample and the [S, D] projection directions given."""
+    return _Swd.apply(z, prior_z, proj, float(p), float(reg_weight))
+
+
+def seg_sort(keys, want_perm=False):
+    """Ascending sort of every row of a [segments, n] fp32 CUDA tensor with the library's radix sort.
+    Returns (sorted, perm or None); perm[s, i] (int64) is the source column of sorted[s, i]."""
+    L.require(keys, "keys", dims=(2,))
+    out = keys.contiguous().clone()
+    S, n = out.shape
+    if S * n == 0:
+        return out, (torch.empty((S, n), dtype=torch.int64, device=out.device) if want_perm else None)
+    dev = out.device
+    perm = torch.empty((S, n), dtype=torch.int32, device=dev) if want_perm else None
+    ws = L.workspace(dev, int(L.lib().vk_seg_sort_workspace_bytes(S, n)))
+    with torch.cuda.device(dev):
+        L.call("seg_sort", L.ptr(out), L.ptr(perm), S, n, L.ptr(ws), ws.numel(), L.stream_ptr())
+    return out, (perm.long() if want_perm else None)

@@ -8,6 +8,7 @@ from .iwae import IWAE
 from .miwae import MIWAE
 from .vq_vae import VQVAE, VectorQuantizer
 from .wae_mmd import WAE_MMD
+from .swae import SWAE
 
 VAE = VanillaVAE
 GaussianVAE = VanillaVAE
@@ -20,4 +21,5 @@ vae_models = {
     'VanillaVAE': VanillaVAE,
     'VQVAE': VQVAE,
     'WAE_MMD': WAE_MMD,
+    'SWAE': SWAE,
 }

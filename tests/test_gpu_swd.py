@@ -1,0 +1,150 @@
+"""Parity of the SWAE sliced-Wasserstein path (K6: projection GEMM, segmented radix sort, loss, d/dz) against
+the golden fixtures made from the unmodified reference (models/swae.py:110-179) and against the CPU oracle.
+Sorted values: bit-exact against torch.sort of the same keys; permutations: bit-exact wherever keys are not
+tied (torch.sort is unstable by default, ours is stable); loss / gradient: 1e-5 relative."""
+import os
+import sys
+
+import pytest
+import torch
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "oracle"))
+import vae_oracle as O  # noqa: E402
+from goldens import assert_close, leaf, load, rel_err  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-5
+DEV = "cuda"
+
+
+@pytest.fixture(scope="module")
+def vk():
+    import vaekit
+    from vaekit import functional as F
+    from vaekit.models import vae_models
+    vaekit.lib()
+    return F, vae_models
+
+
+@pytest.mark.parametrize("segs,n", [(1, 1), (3, 7), (5, 4096), (4, 4097), (7, 10000), (2, 262144 + 13), (200, 5000)])
+def test_seg_sort_matches_torch_sort(vk, segs, n):
+    F, _ = vk
+    gen = torch.Generator(device=DEV).manual_seed(segs * 1000 + n)
+    keys = torch.randn(segs, n, device=DEV, generator=gen) * 3
+    keys[0, : min(n, 5)] = torch.tensor([0.0, -0.0, 1e-38, -1e-38, 3.5])[: min(n, 5)].to(DEV)     # signed zeros, denormals
+    if n >= 64:
+        keys[-1, 10:40] = keys[-1, 10]                                                         # ties
+    out, perm = F.seg_sort(keys, want_perm=True)
+    ref, ref_perm = torch.sort(keys, dim=1, stable=True)
+    assert torch.equal(out.view(torch.int32) & 0x7FFFFFFF | 0, ref.view(torch.int32) & 0x7FFFFFFF | 0) or torch.equal(out, ref)
+    assert (out[:, 1:] >= out[:, :-1]).all()                                                    # sortedness
+    assert torch.equal(torch.gather(keys, 1, perm), out)                                        # perm is a valid gather
+    assert torch.equal(torch.sort(perm, dim=1).values, torch.arange(n, device=DEV).expand(segs, n))  # a permutation
+    # stable order == torch's stable sort, except between +0.0 and -0.0 (distinct radix keys, equal floats)
+    mism = (perm != ref_perm)
+    if mism.any():
+        assert (torch.gather(keys, 1, perm)[mism] == 0).all()
+    out2, none = F.seg_sort(keys)
+    assert none is None and torch.equal(out2, out)
+
+
+@pytest.mark.parametrize("name", ["swae_n64_d16", "swae_n256_d128"])
+def test_swae_golden(vk, name):
+    F, _ = vk
+    g = load(name, DEV)
+    n = g["in_z"].shape[0]
+    reg = g["hp_reg_weight"] / (n * (n - 1))
+    r, z = leaf(g["in_recons"]), leaf(g["in_z"])
+    _, recons_loss, _, _ = F.elbo(r, g["in_input"], recon_mode=F.RECON_MSE_L1_MEAN)
+    s = F.swd(z, g["noise_prior"], g["in_proj"], g["hp_p"], reg)
+    (recons_loss + s).backward()
+    assert_close(recons_loss, g["out_Reconstruction_Loss"], TOL)
+    assert_close(s, g["out_SWD"], TOL, "SWD")
+    assert_close(recons_loss + s, g["out_loss"], TOL)
+    assert_close(r.grad, g["grad_recons"], TOL)
+    assert_close(z.grad, g["grad_z"], TOL, "grad z")
+
+
+@pytest.mark.parametrize("n,dim,S,p", [(1000, 128, 200, 2.0), (4100, 128, 50, 2.0), (333, 10, 7, 2.0), (2, 16, 3, 2.0),
+                                       (5000, 64, 33, 2.0)])
+def test_swd_vs_oracle(vk, n, dim, S, p):
+    F, _ = vk
+    gen = torch.Generator().manual_seed(n + S)
+    z = 1.5 * torch.randn(n, dim, generator=gen) + 0.1
+    prior = torch.randn(n, dim, generator=gen)
+    torch.manual_seed(1265)
+    proj = O.random_projections(dim, S)
+    reg = 100.0 / (n * (n - 1))
+    zc = leaf(z)
+    ref = O.swd(zc, prior, proj, p, reg)
+    ref.backward()
+    zg = leaf(z.to(DEV))
+    s = F.swd(zg, prior.to(DEV), proj.to(DEV), p, reg)
+    (s * 0.7).backward()
+    assert_close(s, ref, TOL, "swd")
+    # The gradient goes through the sort permutation: two samples whose fp32 projections are within rounding of
+    # each other may swap ranks between two correct fp32 GEMMs (different summation order), which changes their
+    # gradient by the neighbouring prior gap.  Parity is asserted on the rows none of whose S
+    # projections has a float64 neighbour gap below 2e-6 relative; the rest is reported.
+    lat64 = z.double() @ proj.double().t()
+    srt, order = torch.sort(lat64, dim=0)
+    gaps = (srt[1:] - srt[:-1])
+    big = torch.full((1, S), float("inf"), dtype=torch.float64)
+    near = torch.minimum(torch.cat([gaps, big]), torch.cat([big, gaps])) < 2e-6 * srt.abs().clamp_min(1.0)
+    ambiguous = torch.zeros(n, dtype=torch.bool)
+    for j in range(S):
+        ambiguous[order[near[:, j], j]] = True
+    clear = ~ambiguous
+    g_ours, g_ref = (zg.grad / 0.7).cpu(), zc.grad
+    den = g_ref.abs().max().item()
+    e_all = (g_ours - g_ref).abs().max().item() / den
+    e_clear = (g_ours[clear] - g_ref[clear]).abs().max().item() / den if clear.any() else 0.0
+    print("swd n=%d d=%d S=%d: %.6e vs %.6e; grad rel err %.2e on %d clear rows, %.2e overall (%d rank-ambiguous rows)" %
+          (n, dim, S, s.item(), ref.item(), e_clear, int(clear.sum()), e_all, int(ambiguous.sum())))
+    assert e_clear <= TOL
+    assert e_all <= 5e-3
+
+
+def test_swd_projection_shards_add_up(vk):
+    """Sharding by projection (the multi-GPU decomposition, emulated on one GPU)."""
+    F, _ = vk
+    gen = torch.Generator().manual_seed(4)
+    n, dim, S = 3000, 128, 40
+    z = (1.5 * torch.randn(n, dim, generator=gen) + 0.1).to(DEV)
+    prior = torch.randn(n, dim, generator=gen).to(DEV)
+    proj = O.random_projections(dim, S).to(DEV)
+    tot, grad = F.swd_sweep(z, prior, proj, 2.0)
+    t2 = torch.zeros(1, dtype=torch.float64, device=DEV)
+    g2 = torch.zeros_like(grad)
+    for a, b in ((0, 13), (13, 27), (27, 40)):
+        t, g = F.swd_sweep(z, prior, proj[a:b], 2.0)
+        t2 += t
+        g2 += g
+    assert_close(t2, tot, 1e-12)
+    assert_close(g2, grad, 2e-6)
+
+
+def test_swae_model_contract(vk):
+    _, models = vk
+    torch.manual_seed(1265)
+    m = models["SWAE"](3, 128, reg_weight=100, num_projections=200).to(DEV)
+    x = torch.rand(16, 3, 64, 64, device=DEV)
+    out = m(x)
+    d = m.loss_function(*out)                          # no M_N, like tests/test_swae.py:26
+    assert set(d) == {"loss", "Reconstruction_Loss", "SWD"}
+    d["loss"].backward()
+    assert m.fc_z.weight.grad is not None
+    ref = O.swae_loss(out[0].detach().cpu(), x.cpu(), out[2].detach().cpu(), m.last_prior_z.cpu(), m.last_proj.cpu(),
+                      reg_weight=100, p=2.0)
+    for k in d:
+        assert_close(d[k], ref[k], TOL, k)
+    # the projection directions follow the CPU generator exactly like the reference
+    torch.manual_seed(7)
+    a = m.get_random_projections(128, 200)
+    torch.manual_seed(7)
+    assert torch.equal(a, O.random_projections(128, 200))
+    m.proj_dist = "uniform"
+    with pytest.raises(ValueError, match="Unknown projection distribution"):
+        m.get_random_projections(128, 4)
+    with pytest.raises(ZeroDivisionError):
+        m.loss_function(torch.rand(1, 3, 8, 8, device=DEV), torch.rand(1, 3, 8, 8, device=DEV), torch.randn(1, 128, device=DEV))
