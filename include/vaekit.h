@@ -205,6 +205,25 @@ int64_t vk_seg_sort_workspace_bytes(int64_t segments, int64_t n);
 int vk_seg_sort(float* keys, uint32_t* perm_out, int64_t segments, int64_t n, void* workspace,
                 int64_t workspace_bytes, void* stream);
 
+/* ---------------------------------------------------------------------------
+ * K5  Beta-TC-VAE latent terms             (reference: models/betatc_vae.py:132-142, 165-211)
+ *
+ * z, mu, log_var [B, D] (B >= 2).  ld_ijd = log N(z_id; mu_jd, exp(lv_jd)); the [B,B] log importance weights
+ * (columns 0 and 1 and entry [B-2,0] special, betatc_vae.py:179-182) are added to every latent dim before both
+ * logsumexps (betatc_vae.py:185).  gamma_anneal = anneal_rate * gamma (host state, betatc_vae.py:196-200).
+ *   out[4]   = { alpha*mi + (beta*tc + gamma_anneal*kld),  kld,  tc,  mi }       (means over the batch)
+ *   lqz_out [B], lse_out [B, D]: log_q_z[i] and LSE_j(ld_ijd + lw_ij), saved for the backward
+ * Backward: g_loss upstream of out[0] (NULL = 1); writes g_z, g_mu, g_lv [B, D] (overwritten).
+ * The B^2 D densities each need their own exp (per-dimension LSE), so the kernels are MUFU/FP32 bound.
+ * -------------------------------------------------------------------------*/
+int64_t vk_tc_workspace_bytes(int64_t B, int64_t D);
+int vk_tc_fwd(const float* z, const float* mu, const float* log_var, int64_t B, int64_t D, float M_N,
+              float alpha, float beta, float gamma_anneal, float* lqz_out, float* lse_out, float* out /*[4]*/,
+              void* workspace, int64_t workspace_bytes, void* stream);
+int vk_tc_bwd(const float* z, const float* mu, const float* log_var, const float* lqz, const float* lse,
+              int64_t B, int64_t D, float M_N, float alpha, float beta, float gamma_anneal, const float* g_loss,
+              float* g_z, float* g_mu, float* g_lv, void* workspace, int64_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

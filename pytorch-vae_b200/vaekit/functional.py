@@ -404,3 +404,54 @@ def seg_sort(keys, want_perm=False):
     with torch.cuda.device(dev):
         L.call("seg_sort", L.ptr(out), L.ptr(perm), S, n, L.ptr(ws), ws.numel(), L.stream_ptr())
     return out, (perm.long() if want_perm else None)
+
+
+# ---------------------------------------------------------------------------
+# K5
+# ---------------------------------------------------------------------------
+class _BetaTc(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, z, mu, log_var, M_N, alpha, beta, gamma_anneal):
+        for t, n in ((z, "z"), (mu, "mu"), (log_var, "log_var")):
+            L.require(t, n, dims=(2,))
+        if not (z.shape == mu.shape == log_var.shape):
+            raise RuntimeError("vaekit: z %s, mu %s and log_var %s differ in shape" %
+                               (tuple(z.shape), tuple(mu.shape), tuple(log_var.shape)))
+        B, D = z.shape
+        if B < 2:
+            raise RuntimeError("vaekit: the Beta-TC decomposition needs a batch of at least 2")
+        zc, mc, lc = z.contiguous(), mu.contiguous(), log_var.contiguous()
+        dev = z.device
+        lqz = torch.empty(B, dtype=torch.float32, device=dev)
+        lse = torch.empty((B, D), dtype=torch.float32, device=dev)
+        out = torch.empty(4, dtype=torch.float32, device=dev)
+        ws = L.workspace(dev, int(L.lib().vk_tc_workspace_bytes(B, D)))
+        with torch.cuda.device(dev):
+            L.call("tc_fwd", L.ptr(zc), L.ptr(mc), L.ptr(lc), B, D, M_N, alpha, beta, gamma_anneal, L.ptr(lqz), L.ptr(lse),
+                   L.ptr(out), L.ptr(ws), ws.numel(), L.stream_ptr())
+        ctx.save_for_backward(zc, mc, lc, lqz, lse)
+        ctx.cfg = (B, D, M_N, alpha, beta, gamma_anneal)
+        ctx.set_materialize_grads(False)
+        terms = out[1:].detach()
+        ctx.mark_non_differentiable(terms)
+        return out[0], terms
+
+    @staticmethod
+    def backward(ctx, g, _g_terms):
+        if g is None:
+            return (None,) * 7
+        zc, mc, lc, lqz, lse = ctx.saved_tensors
+        B, D, M_N, alpha, beta, gamma_anneal = ctx.cfg
+        dev = zc.device
+        g_z, g_mu, g_lv = torch.empty_like(zc), torch.empty_like(mc), torch.empty_like(lc)
+        ws = L.workspace(dev, int(L.lib().vk_tc_workspace_bytes(B, D)))
+        with torch.cuda.device(dev):
+            L.call("tc_bwd", L.ptr(zc), L.ptr(mc), L.ptr(lc), L.ptr(lqz), L.ptr(lse), B, D, M_N, alpha, beta, gamma_anneal,
+                   L.ptr(g.contiguous()), L.ptr(g_z), L.ptr(g_mu), L.ptr(g_lv), L.ptr(ws), ws.numel(), L.stream_ptr())
+        return g_z, g_mu, g_lv, None, None, None, None
+
+
+def betatc_terms(z, mu, log_var, M_N, alpha, beta, gamma_anneal):
+    """betatc_vae.py:165-205 without the reconstruction term: returns (alpha*mi + beta*tc + gamma_anneal*kld,
+    terms[3] = {kld, tc, mi})."""
+    return _BetaTc.apply(z, mu, log_var, float(M_N), float(alpha), float(beta), float(gamma_anneal))

@@ -9,6 +9,7 @@ from .miwae import MIWAE
 from .vq_vae import VQVAE, VectorQuantizer
 from .wae_mmd import WAE_MMD
 from .swae import SWAE
+from .betatc_vae import BetaTCVAE
 
 VAE = VanillaVAE
 GaussianVAE = VanillaVAE
@@ -22,4 +23,5 @@ vae_models = {
     'VQVAE': VQVAE,
     'WAE_MMD': WAE_MMD,
     'SWAE': SWAE,
+    'BetaTCVAE': BetaTCVAE,
 }

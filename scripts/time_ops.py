@@ -36,3 +36,21 @@ if "vq" in which:
         torch.autograd.backward([q, l], [gq, None])
     ms = timeit(step, it=20)
     print("vq fwd+bwd B=1024: %.4f ms  %.2f M images/s, %.1f GB/s on 337.9 MB" % (ms, 1024 / ms / 1e3, 337.9e6 / ms / 1e6))
+if "swd" in which:
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    from vaekit import _lib as L
+    N, D, S = 1 << 20, 128, 200
+    z = 1.5 * torch.randn(N, D, device=dev) + 0.1; p = torch.randn(N, D, device=dev)
+    th = torch.randn(S, D, device=dev); th = th / th.norm(dim=1, keepdim=True)
+    ms = timeit(lambda: F.swd_sweep(z, p, th, 2.0), warm=1, it=3)
+    print("swd N=%d S=%d fwd+grad: %.3f ms  %.1f Msamples/s  (model 28.8 GB -> %.0f GB/s)" % (N, S, ms, N / ms / 1e3, 28.8e9 / ms / 1e6), flush=True)
+    L.EVENT_LOG = []
+    F.swd_sweep(z, p, th, 2.0)
+    torch.cuda.synchronize()
+    keys = torch.randn(S, N, device=dev)
+    ms = timeit(lambda: F.seg_sort(keys), warm=1, it=3)
+    print("seg_sort key-only %dx%d (incl. clone): %.3f ms" % (S, N, ms))
+    ms = timeit(lambda: F.seg_sort(keys, want_perm=True), warm=1, it=3)
+    print("seg_sort key+perm %dx%d (incl. clone, perm.long()): %.3f ms" % (S, N, ms))
+    ms = timeit(lambda: torch.sort(keys, dim=1), warm=1, it=3)
+    print("torch.sort %dx%d: %.3f ms" % (S, N, ms))

@@ -1,0 +1,95 @@
+"""Parity of the Beta-TC-VAE latent-term kernels (K5, vk_tc_fwd / vk_tc_bwd) against the golden fixtures made
+from the unmodified reference (models/betatc_vae.py:144-211) and the CPU oracle.  Tolerance 1e-5 relative."""
+import os
+import sys
+
+import pytest
+import torch
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "oracle"))
+import vae_oracle as O  # noqa: E402
+from goldens import assert_close, leaf, load, rel_err  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-5
+DEV = "cuda"
+
+
+@pytest.fixture(scope="module")
+def vk():
+    import vaekit
+    from vaekit import functional as F
+    from vaekit.models import vae_models
+    vaekit.lib()
+    return F, vae_models
+
+
+@pytest.mark.parametrize("name", ["betatc_b16_d10", "betatc_b48_d32"])
+def test_betatc_golden(vk, name):
+    _, models = vk
+    g = load(name, DEV)
+    dim = g["in_mu"].shape[1]
+    m = models["BetaTCVAE"](3, dim, anneal_steps=100, alpha=1.0, beta=6.0, gamma=1.0)
+    # training mode, z produced by reparameterize from (mu, log_var): gradients flow into mu / log_var through z too
+    m.train()
+    r, mu, lv = leaf(g["in_recons"]), leaf(g["in_mu"]), leaf(g["in_log_var"])
+    z = O.reparameterize(mu, lv, g["noise_eps"])              # torch ops on the GPU with the fixture's noise
+    assert_close(z, g["out_z"], TOL)
+    d = m.loss_function(r, g["in_input"], mu, lv, z, M_N=g["hp_M_N"])
+    assert m.num_iter == 1
+    d["loss"].backward()
+    for k in ("loss", "Reconstruction_Loss", "KLD", "TC_Loss", "MI_Loss"):
+        assert_close(d[k], g["out_" + k], TOL, k)
+    assert_close(r.grad, g["grad_recons"], TOL)
+    assert_close(mu.grad, g["grad_mu"], TOL, "grad mu")
+    assert_close(lv.grad, g["grad_log_var"], TOL, "grad log_var")
+    # eval mode (anneal = 1, num_iter untouched), z as an independent leaf
+    m.eval()
+    r2, mu2, lv2, z2 = leaf(g["in_recons"]), leaf(g["in_mu"]), leaf(g["in_log_var"]), leaf(g["out_z"])
+    d2 = m.loss_function(r2, g["in_input"], mu2, lv2, z2, M_N=g["hp_M_N"])
+    assert m.num_iter == 1
+    d2["loss"].backward()
+    assert_close(d2["loss"], g["out_loss_eval"], TOL)
+    assert_close(mu2.grad, g["grad_eval_mu"], TOL)
+    assert_close(lv2.grad, g["grad_eval_log_var"], TOL)
+    assert_close(z2.grad, g["grad_eval_z"], TOL)
+
+
+@pytest.mark.parametrize("B,D", [(2, 3), (64, 10), (130, 128), (257, 33), (1024, 128)])
+def test_betatc_vs_oracle(vk, B, D):
+    F, _ = vk
+    gen = torch.Generator().manual_seed(B + D)
+    mu = torch.randn(B, D, generator=gen)
+    lv = 0.3 * torch.randn(B, D, generator=gen)
+    z = mu + torch.randn(B, D, generator=gen) * torch.exp(0.5 * lv)
+    rz = torch.zeros(B, 1, 1, 1)
+    zc, mc, lc = leaf(z), leaf(mu), leaf(lv)
+    ref = O.betatc_loss(rz, rz, mc, lc, zc, 0.00025, alpha=1.0, beta=6.0, gamma=1.0, anneal_rate=0.37)
+    ref["loss"].backward()
+    zg, mg, lg = leaf(z.to(DEV)), leaf(mu.to(DEV)), leaf(lv.to(DEV))
+    latent, terms = F.betatc_terms(zg, mg, lg, 0.00025, 1.0, 6.0, 0.37 * 1.0)
+    (latent * 2.0).backward()
+    assert_close(latent, ref["loss"], TOL, "latent loss")
+    assert_close(terms[0], ref["KLD"], TOL, "kld")
+    assert_close(terms[1], ref["TC_Loss"], TOL, "tc")
+    assert_close(terms[2], ref["MI_Loss"], TOL, "mi")
+    for a, b, n in ((zg, zc, "z"), (mg, mc, "mu"), (lg, lc, "log_var")):
+        e = rel_err(a.grad / 2.0, b.grad)
+        assert e <= 2e-5, "grad %s rel err %.2e" % (n, e)
+
+
+def test_betatc_model_contract(vk):
+    _, models = vk
+    torch.manual_seed(1265)
+    m = models["BetaTCVAE"](3, 64, anneal_steps=100).to(DEV)
+    x = torch.rand(16, 3, 64, 64, device=DEV)
+    out = m(x)
+    assert [tuple(t.shape) for t in out] == [(16, 3, 64, 64), (16, 3, 64, 64), (16, 64), (16, 64), (16, 64)]
+    d = m.loss_function(*out, M_N=0.005)
+    assert set(d) == {"loss", "Reconstruction_Loss", "KLD", "TC_Loss", "MI_Loss"} and m.num_iter == 1
+    d["loss"].backward()
+    assert m.fc_mu.weight.grad is not None and m.fc_var.weight.grad is not None
+    with pytest.raises(KeyError):
+        m.loss_function(*out)                                   # M_N is required (betatc_vae.py:177)
+    ld = m.log_density_gaussian(out[4], out[2], out[3])
+    assert_close(ld, O.log_density_gaussian(out[4].cpu(), out[2].cpu(), out[3].cpu()), TOL)
