@@ -385,17 +385,351 @@ def run_gpu_arm(args, wl):
         dist.destroy_process_group()
 
 
+# ---------------------------------------------------------------------------
+# op workloads: the other BASELINE.json configs (WAE-MMD, VQ, SWAE) and BetaTC, through the drop-in model API
+# ---------------------------------------------------------------------------
+def bf16_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["bf16_tflops_sustained"]), "MEASURED_PEAKS.json bf16_tflops_sustained (measured)"
+    except Exception:
+        return 1400.0, "fallback 1.4 PFLOP/s sustained (B200_PROFILING.md)"
+
+
+class OpWorkload:
+    """One hot-path op at a BASELINE.json size.  make() builds synthetic inputs, step() runs forward + backward through
+    the public model API, cpu_step() is the oracle port of the reference on a bounded sample."""
+    scaling = "weak"
+
+    def units(self, world):
+        return self.N * (world if self.scaling == "weak" else 1)
+
+
+class WaeMmd(OpWorkload):
+    scaling = "strong"          # fixed global batch, rows sharded after an all-gather of z (SURVEY 8(e))
+
+    def __init__(self, kt):
+        self.kt, self.N, self.D = kt, 65536, 128
+        self.reg = 5000.0 if kt == "rbf" else 100.0
+        self.desc = "WAE-MMD %s kernel, z batch 65536x128, value + d/dz in one tcgen05 Gram sweep (BASELINE configs[2])" % kt.upper()
+        self.cpu_sample, self.bound = 2048, "tensor"
+        self.dominant = "mmd_fwd"
+
+    def model(self):
+        from vaekit.models import vae_models
+        return vae_models["WAE_MMD"](3, self.D, reg_weight=self.reg, kernel_type=self.kt)
+
+    def make(self, dev, rank, world, n=None, generator_device=None):
+        n = n or self.N // world
+        g = torch.Generator(device=dev).manual_seed(1265 + rank)
+        return {"z": torch.randn(n, self.D, device=dev, generator=g) + 0.25}
+
+    def step(self, m, t, world=1):
+        z = t["z"].requires_grad_(True)
+        z.grad = None
+        n_glob = z.shape[0] * world
+        reg = m.reg_weight / (n_glob * (n_glob - 1))
+        if world > 1:
+            from vaekit import dist as vd
+            mmd, _ = vd.sharded_mmd(z, reg, m.kernel_type, m.z_var)
+        else:
+            mmd = m.compute_mmd(z, reg)
+        mmd.backward()
+        return {"MMD": mmd}
+
+    def work(self, world):
+        return {"mmd_fwd": 10.0 * self.N * self.N * self.D / world}, "TFLOP/s"
+
+    def cpu_step(self, t):
+        import vae_oracle as O
+        z = t["z"].detach().requires_grad_(True)
+        n = z.shape[0]
+        O.mmd(z, torch.randn_like(z), self.reg / (n * (n - 1)), self.kt, 2.0).backward()
+
+
+class VqWorkload(OpWorkload):
+    def __init__(self):
+        self.N, self.D, self.K, self.H = 1024, 64, 512, 16
+        self.desc = "VQ-VAE VectorQuantizer, codebook 512x64, 16x16 latent grid, batch 1024 (BASELINE configs[3])"
+        self.cpu_sample, self.bound = 128, "hbm"
+        self.dominant = "vq_fwd"
+
+    def model(self):
+        from vaekit.models.vq_vae import VectorQuantizer
+        m = VectorQuantizer(self.K, self.D, 0.25)
+        with torch.no_grad():
+            m.embedding.weight.normal_()
+        return m
+
+    def make(self, dev, rank, world, n=None):
+        n = n or self.N
+        g = torch.Generator(device=dev).manual_seed(1265 + rank)
+        return {"latents": torch.nn.functional.leaky_relu(torch.randn(n, self.D, self.H, self.H, device=dev, generator=g)),
+                "gq": 1e-3 * torch.randn(n, self.D, self.H, self.H, device=dev, generator=g)}
+
+    def step(self, m, t, world=1):
+        x = t["latents"].requires_grad_(True)
+        x.grad = None
+        m.embedding.weight.grad = None
+        q, vq_loss = m(x)
+        torch.autograd.backward([q, vq_loss], [t["gq"], None])
+        return {"VQ_Loss": vq_loss}
+
+    def work(self, world):
+        R = self.N * self.H * self.H
+        fwd = 2 * R * self.D * 4 + R * 4 + self.K * self.D * 4
+        bwd = 4 * R * self.D * 4 + R * 4 + 2 * self.K * self.D * 4
+        return {"vq_fwd": float(fwd), "vq_bwd": float(bwd)}, "GB/s"
+
+    def cpu_step(self, t):
+        import vae_oracle as O
+        x = t["latents"].detach().requires_grad_(True)
+        cb = torch.randn(self.K, self.D, requires_grad=True)
+        q, l, _ = O.vq_forward(x, cb, 0.25)
+        torch.autograd.backward([q, l], [t["gq"], None])
+
+
+class SwaeWorkload(OpWorkload):
+    scaling = "strong"          # fixed global batch, projections sharded across ranks (SURVEY 8(e))
+
+    def __init__(self):
+        self.N, self.D, self.S = 1 << 20, 128, 200
+        self.desc = "SWAE sliced-Wasserstein, 200 projections, batch 1048576x128, projection GEMM + radix sort (BASELINE configs[4])"
+        self.cpu_sample, self.bound = 1 << 16, "hbm"
+        self.dominant = "swd_fwd"
+
+    def model(self):
+        from vaekit.models import vae_models
+        return vae_models["SWAE"](3, self.D, reg_weight=100, num_projections=self.S)
+
+    def make(self, dev, rank, world, n=None):
+        n = n or self.N // world
+        g = torch.Generator(device=dev).manual_seed(1265 + rank)
+        return {"z": 1.5 * torch.randn(n, self.D, device=dev, generator=g) + 0.1}
+
+    def step(self, m, t, world=1):
+        z = t["z"].requires_grad_(True)
+        z.grad = None
+        n_glob = z.shape[0] * world
+        reg = m.reg_weight / (n_glob * (n_glob - 1))
+        if world > 1:
+            from vaekit import dist as vd
+            proj = vd.shared_tensor_(m.get_random_projections(self.D, self.S).to(z.device))
+            swd = vd.sharded_swd(z, proj, m.p, reg)
+        else:
+            swd = m.compute_swd(z, m.p, reg)
+        swd.backward()
+        return {"SWD": swd}
+
+    def work(self, world):
+        return {"swd_fwd": 27424.0 * self.N / world}, "GB/s"       # radix-sort traffic model of SURVEY 8(d)
+
+    def cpu_step(self, t):
+        import vae_oracle as O
+        z = t["z"].detach().requires_grad_(True)
+        n = z.shape[0]
+        O.swd(z, torch.randn_like(z), O.random_projections(self.D, self.S), 2.0, 100.0 / (n * (n - 1))).backward()
+
+
+class BetaTcWorkload(OpWorkload):
+    def __init__(self):
+        self.N, self.D = 4096, 128
+        self.desc = "BetaTC-VAE latent terms (log_q_z, per-dim LSE, MI/TC/KLD), batch 4096, latent 128 (SURVEY 8(d) extra)"
+        self.cpu_sample, self.bound = 1024, "mufu"
+        self.dominant = "tc_bwd"
+
+    def model(self):
+        from vaekit.models import vae_models
+        return vae_models["BetaTCVAE"](3, self.D).eval()
+
+    def make(self, dev, rank, world, n=None):
+        n = n or self.N
+        g = torch.Generator(device=dev).manual_seed(1265 + rank)
+        mu = torch.randn(n, self.D, device=dev, generator=g)
+        lv = 0.3 * torch.randn(n, self.D, device=dev, generator=g)
+        return {"mu": mu, "lv": lv, "eps": torch.randn(n, self.D, device=dev, generator=g)}
+
+    def step(self, m, t, world=1):
+        from vaekit import functional as F
+        mu, lv = t["mu"].requires_grad_(True), t["lv"].requires_grad_(True)
+        mu.grad = lv.grad = None
+        z = m.reparameterize(mu, lv)
+        latent, terms = F.betatc_terms(z, mu, lv, 0.00025, m.alpha, m.beta, m.gamma)
+        latent.backward()
+        return {"latent": latent}
+
+    def work(self, world):
+        return {"tc_fwd": float(self.N) * self.N * self.D, "tc_bwd": 2.0 * self.N * self.N * self.D}, "Gexp/s"
+
+    def cpu_step(self, t):
+        import vae_oracle as O
+        mu, lv = t["mu"].detach().requires_grad_(True), t["lv"].detach().requires_grad_(True)
+        z = O.reparameterize(mu, lv, t["eps"])
+        rz = torch.zeros(mu.shape[0], 1, 1, 1)
+        O.betatc_loss(rz, rz, mu, lv, z, 0.00025, alpha=1.0, beta=6.0, gamma=1.0, anneal_rate=1.0)["loss"].backward()
+
+
+OP_WORKLOADS = {"wae_mmd_rbf": lambda: WaeMmd("rbf"), "wae_mmd_imq": lambda: WaeMmd("imq"), "vq": VqWorkload,
+                "swae": SwaeWorkload, "betatc": BetaTcWorkload}
+
+
+def op_cpu_baseline(wl, iters, warmup=1):
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    t = wl.make(torch.device("cpu"), 0, 1, n=wl.cpu_sample)
+    for _ in range(warmup):
+        wl.cpu_step(t)
+    ts = []
+    for _ in range(iters):
+        t0 = time.perf_counter()
+        wl.cpu_step(t)
+        ts.append(time.perf_counter() - t0)
+    v = wl.cpu_sample * len(ts) / sum(ts)
+    return v, cores, ts
+
+
+def run_op_reference_arm(args, wl):
+    rank, _, _ = dist_env()
+    if rank != 0:
+        return
+    v, cores, ts = op_cpu_baseline(wl, max(1, min(args.steps, 3)), warmup=1)
+    sample = "batch %d of the %d-sample workload per step (the reference's broadcast formulation at that size), torch CPU %d threads" % (
+        wl.cpu_sample, wl.N, cores)
+    line = {"impl": "reference", "metric": "latent+loss samples/s fwd+bwd", "value": round(v, 2), "unit": "samples/s",
+            "n_gpus": args.gpus, "steps": len(ts), "warmup": 1, "ms_per_step": round(1e3 * sum(ts) / len(ts), 3),
+            "higher_is_better": True, "scaling": wl.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": wl.desc, "sample": sample},
+            "cpu_baseline": {"value": round(v, 2), "unit": "samples/s", "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": round(v, 2), "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def run_op_gpu_arm(args, wl):
+    import torch.distributed as dist
+    rank, world, local = dist_env()
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    import vaekit
+    from vaekit import _lib as L
+    vaekit.lib()
+    model = wl.model().to(dev)
+    t = wl.make(dev, rank, world)
+    torch.manual_seed(1265)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def timed(fn, steps, log_events):
+        barrier()
+        if log_events:
+            L.EVENT_LOG = []
+        n0 = L.LAUNCHES
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            r = fn()
+        e1.record()
+        barrier()
+        log, L.EVENT_LOG = L.EVENT_LOG, None
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            tms = torch.tensor([ms], device=dev)
+            dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+            ms = tms.item()
+        return ms, log, L.LAUNCHES - n0, r
+
+    for _ in range(max(args.warmup, 3)):
+        wl.step(model, t, world)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ms, log, launches, d = timed(lambda: wl.step(model, t, world), args.steps, True)
+    clocks = sampler.stop() if rank == 0 else None
+    value = wl.units(world) * args.steps / (ms / 1e3)
+    # roofline of the dominant library call, from CUDA events around each call on the launching stream
+    work, unit = wl.work(world)
+    acc = {}
+    for name, a, b in log:
+        acc.setdefault(name, []).append(a.elapsed_time(b))
+    kern = {k: {"ms": round(sum(v) / len(v), 4), "calls": len(v)} for k, v in acc.items()}
+    tot = sum(k["ms"] * k["calls"] for k in kern.values()) or 1.0
+    for k in kern:
+        kern[k]["share_of_library_time"] = round(kern[k]["ms"] * kern[k]["calls"] / tot, 4)
+    dom = wl.dominant
+    dms = kern[dom]["ms"]
+    if wl.bound == "tensor":
+        peak, src = bf16_peak()
+        ach = work[dom] / dms / 1e9
+    elif wl.bound == "hbm":
+        peak, src = peaks()
+        ach = work[dom] / dms / 1e6
+    else:
+        peak, src = 148 * 16 * 1.965, "16 MUFU ops/clk/SM x 148 SMs x 1.965 GHz (nominal)"
+        ach = work[dom] / dms / 1e6
+    roof = {"bound": "tensor" if wl.bound == "tensor" else "hbm" if wl.bound == "hbm" else "mufu", "kernel": dom,
+            "achieved": round(ach, 2), "peak": round(peak, 1), "unit": unit, "frac": round(ach / peak, 4), "traffic": None,
+            "peak_source": src, "algorithmic_work_per_launch": work[dom], "ms_per_launch": dms, "calls": kern}
+    # end to end: host (pinned) inputs copied in and the loss read back every step
+    e2e = None
+    if not args.no_e2e:
+        host = {k: v.cpu().pin_memory() for k, v in t.items()}
+        h2d = sum(v.numel() * v.element_size() for v in host.values())
+
+        def e2e_step():
+            td = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
+            dd = wl.step(model, td, world)
+            return [v.item() for v in dd.values()]
+
+        for _ in range(2):
+            e2e_step()
+        ems, _, _, vals = timed(e2e_step, args.steps, False)
+        e2e = {"value": round(wl.units(world) * args.steps / (ems / 1e3), 1), "unit": "samples/s",
+               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4 * len(vals), "ms_per_step": round(ems / args.steps, 3)}
+    if rank == 0:
+        cpu = None
+        if world == 1 and not args.no_cpu:
+            v, cores, ts = op_cpu_baseline(wl, 2)
+            cpu = {"value": round(v, 2), "unit": "samples/s", "cores": cores, "kind": "port",
+                   "sample": "batch %d of the %d-sample workload (the reference's formulation at that size), 2 iterations "
+                             "after 1 warm-up, torch CPU %d threads" % (wl.cpu_sample, wl.N, cores)}
+        line = {"metric": "latent+loss samples/s fwd+bwd", "value": round(value, 1), "unit": "samples/s", "n_gpus": world,
+                "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": round(ms / args.steps, 4),
+                "higher_is_better": True, "scaling": wl.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": wl.desc, "global_batch": wl.units(world),
+                           "l2_policy": "synthetic inputs regenerated never; working set (operand images / sort buffers) larger than L2 or tensor-bound",
+                           "parallelism": ("%s over %d ranks" % ("row-sharded after all-gather" if isinstance(wl, WaeMmd) else
+                                                                  "projection-sharded after all-gather" if isinstance(wl, SwaeWorkload)
+                                                                  else "batch-sharded", world)) if world > 1 else "single GPU",
+                           "step": "forward + backward through the drop-in model API"},
+                "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+                "loss": {k: v.item() for k, v in d.items()}}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--workload", default="iwae", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="iwae", choices=sorted(WORKLOADS) + sorted(OP_WORKLOADS))
     ap.add_argument("--impl", default="vaekit", choices=["vaekit", "reference"])
     ap.add_argument("--cpu-sample", type=int, default=0, help="batch of the bounded CPU-baseline sample")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
+    if args.workload in OP_WORKLOADS:
+        wl = OP_WORKLOADS[args.workload]()
+        (run_op_reference_arm if args.impl == "reference" else run_op_gpu_arm)(args, wl)
+        return
     wl = WORKLOADS[args.workload]
     if args.impl == "reference":
         run_reference_arm(args, wl)

@@ -1,0 +1,177 @@
+"""Multi-GPU decompositions of the two global-batch statistics (one process per GPU, torch.distributed).
+
+The reference never calls a collective itself: under Lightning DDP (run.py:86) every rank evaluates MMD / SWD on
+its *local* batch.  The sharded modes below are new capability: the statistic of the GLOBAL batch,
+with the quadratic / sort work split across ranks.
+
+* MMD (wae_mmd.py:193-204): all-gather z -> every rank holds [N, D]; rank r owns a 128-aligned row block and sweeps
+  its rows against all N columns (vk_mmd_fwd row range).  prior_z is regenerated locally from the shared Philox
+  (seed, offset) -- no traffic.  Each rank has complete rows, so the gradient of its own z rows is local: no
+  reduce-scatter in backward.  One all-reduce of three float64 sums.
+* SWD (swae.py:151-179): all-gather z; rank r owns a slice of the projections, projects all N rows on them, sorts,
+  and produces a partial [N, D] gradient; reduce-scatter (sum) gives each rank the gradient of its own rows, one
+  all-reduce of the float64 loss sum.
+
+The batch-local ops (K1-K3, K7) need no collective at all: shard the batch, which is what DDP already does.
+The plumbing helpers are backend-agnostic (NCCL on GPUs; gloo in the CPU tests).
+"""
+from typing import List, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+ROW_ALIGN = 128      # row-block granularity of the Gram kernel (vk_mmd_fwd)
+
+
+# ---------------------------------------------------------------------------
+# partition plans (pure host logic)
+# ---------------------------------------------------------------------------
+def plan_rows(n_local: int, world: int, rank: int, align: int = ROW_ALIGN) -> Tuple[int, int, int]:
+    """(N, row_begin, row_end) of the rows rank `rank` owns when every rank contributes `n_local` rows.
+    The Gram kernel needs 128-aligned row blocks, so n_local must be a multiple of `align` unless world == 1."""
+    if world < 1 or not (0 <= rank < world) or n_local < 1:
+        raise ValueError("bad partition request: n_local=%d world=%d rank=%d" % (n_local, world, rank))
+    if world > 1 and n_local % align != 0:
+        raise ValueError("row-sharded MMD needs a per-rank batch that is a multiple of %d (got %d)" % (align, n_local))
+    return n_local * world, rank * n_local, (rank + 1) * n_local
+
+
+def plan_projections(num_projections: int, world: int, rank: int) -> Tuple[int, int]:
+    """[s0, s1) of the projections rank `rank` owns: contiguous, sizes differ by at most one, empty slices allowed."""
+    if world < 1 or not (0 <= rank < world) or num_projections < 0:
+        raise ValueError("bad partition request: S=%d world=%d rank=%d" % (num_projections, world, rank))
+    base, extra = divmod(num_projections, world)
+    s0 = rank * base + min(rank, extra)
+    return s0, s0 + base + (1 if rank < extra else 0)
+
+
+# ---------------------------------------------------------------------------
+# collectives (thin wrappers; identity when no process group is active)
+# ---------------------------------------------------------------------------
+def _active(group) -> bool:
+    return dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
+
+
+def world_rank(group=None) -> Tuple[int, int]:
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_world_size(group), dist.get_rank(group)
+    return 1, 0
+
+
+def gather_rows(x_local: torch.Tensor, group=None) -> torch.Tensor:
+    """[n_local, D] on every rank -> [world * n_local, D] on every rank (rank-major)."""
+    if not _active(group):
+        return x_local.contiguous()
+    world = dist.get_world_size(group)
+    out = torch.empty((world * x_local.shape[0],) + tuple(x_local.shape[1:]), dtype=x_local.dtype, device=x_local.device)
+    dist.all_gather_into_tensor(out, x_local.contiguous(), group=group)
+    return out
+
+
+def reduce_sum_(t: torch.Tensor, group=None) -> torch.Tensor:
+    if _active(group):
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+    return t
+
+
+def scatter_rows_sum(x_all: torch.Tensor, group=None) -> torch.Tensor:
+    """Sum of every rank's [world * n_local, D] tensor, each rank keeping its own row block."""
+    if not _active(group):
+        return x_all
+    world = dist.get_world_size(group)
+    out = torch.empty((x_all.shape[0] // world,) + tuple(x_all.shape[1:]), dtype=x_all.dtype, device=x_all.device)
+    dist.reduce_scatter_tensor(out, x_all.contiguous(), op=dist.ReduceOp.SUM, group=group)
+    return out
+
+
+def shared_rng(device, numel: int, group=None) -> Tuple[int, int]:
+    """Philox (seed, offset) for `numel` normals, identical on every rank (rank 0's generator state wins)."""
+    from . import functional as F
+    seed, offset = F.next_philox(device, numel)
+    if _active(group):
+        t = torch.tensor([seed - (1 << 63), offset], dtype=torch.int64, device=device)     # seed as a signed payload
+        dist.broadcast(t, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+        seed, offset = int(t[0].item()) + (1 << 63), int(t[1].item())
+    return seed, offset
+
+
+def shared_tensor_(t: torch.Tensor, group=None) -> torch.Tensor:
+    if _active(group):
+        dist.broadcast(t, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+    return t
+
+
+# ---------------------------------------------------------------------------
+# sharded ops (CUDA)
+# ---------------------------------------------------------------------------
+class _ShardedMmd(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, z_local, kernel_type, z_var, reg_weight, passes, group):
+        from . import functional as F
+        world, rank = world_rank(group)
+        N, r0, r1 = plan_rows(z_local.shape[0], world, rank)
+        z_all = gather_rows(z_local, group)
+        rng = shared_rng(z_local.device, z_all.numel(), group)
+        prior_all = F.philox_normal(z_all.shape, z_all.device, rng=rng)
+        sums, grad = F.mmd_sweep(z_all, prior_all, kernel_type, z_var, r0, r1, passes)
+        reduce_sum_(sums, group)
+        out = F.mmd_combine(sums, N, kernel_type, reg_weight)
+        ctx.save_for_backward(grad)
+        ctx.factor = 4.0 * reg_weight * (1.0 / (float(N) * float(N)) if kernel_type == 0 else 1.0)
+        ctx.set_materialize_grads(False)
+        terms = out[1:].detach()
+        ctx.mark_non_differentiable(terms)
+        return out[0], terms
+
+    @staticmethod
+    def backward(ctx, g, _g_terms):
+        from . import functional as F
+        if g is None:
+            return (None,) * 6
+        return F.scale_by_scalar(ctx.saved_tensors[0], g.contiguous(), ctx.factor), None, None, None, None, None
+
+
+def sharded_mmd(z_local, reg_weight, kernel_type, z_var, passes=3, group=None):
+    """MMD of the GLOBAL batch (all ranks' z rows) against a shared prior sample; returns (mmd, terms[3]) identical
+    on every rank; backward gives d mmd / d z_local."""
+    from . import functional as F
+    if kernel_type not in F.KERNEL_TYPES:
+        raise ValueError('Undefined kernel type.')
+    return _ShardedMmd.apply(z_local, F.KERNEL_TYPES[kernel_type], float(z_var), float(reg_weight), int(passes), group)
+
+
+class _ShardedSwd(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, z_local, proj, p, reg_weight, group):
+        from . import functional as F
+        world, rank = world_rank(group)
+        z_all = gather_rows(z_local, group)
+        N, S = z_all.shape[0], proj.shape[0]
+        rng = shared_rng(z_local.device, z_all.numel(), group)
+        prior_all = F.philox_normal(z_all.shape, z_all.device, rng=rng)
+        s0, s1 = plan_projections(S, world, rank)
+        if s1 > s0:
+            total, grad_all = F.swd_sweep(z_all, prior_all, proj[s0:s1], p, want_grad=True)
+        else:
+            total = torch.zeros(1, dtype=torch.float64, device=z_all.device)
+            grad_all = torch.zeros_like(z_all)
+        reduce_sum_(total, group)
+        grad_local = scatter_rows_sum(grad_all, group)
+        ctx.save_for_backward(grad_local)
+        count = float(N) * float(S)
+        ctx.factor = reg_weight / count
+        ctx.set_materialize_grads(False)
+        return F.mean_scale(total, count, reg_weight)
+
+    @staticmethod
+    def backward(ctx, g):
+        from . import functional as F
+        if g is None:
+            return (None,) * 5
+        return F.scale_by_scalar(ctx.saved_tensors[0], g.contiguous(), ctx.factor), None, None, None, None
+
+
+def sharded_swd(z_local, proj, p, reg_weight, group=None):
+    """Sliced-Wasserstein distance of the GLOBAL batch; `proj` [S, D] must be identical on every rank
+    (use shared_tensor_ on the reference's CPU-generated directions)."""
+    return _ShardedSwd.apply(z_local, proj, float(p), float(reg_weight), group)
