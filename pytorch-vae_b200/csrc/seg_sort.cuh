@@ -22,6 +22,20 @@ constexpr int kBins = 256;
 __device__ __forceinline__ uint32_t f2ord(uint32_t u) { return u ^ ((u >> 31) ? 0xFFFFFFFFu : 0x80000000u); }
 __device__ __forceinline__ uint32_t ord2f(uint32_t u) { return u ^ ((u >> 31) ? 0x80000000u : 0xFFFFFFFFu); }
 
+// Lanes of the warp that hold the same 8-bit digit (among lanes with ok == true): eight ballots, fixed cost.
+// (match.any costs one pass per distinct value in the warp -- ~30 for uniform digits -- and made ranking the
+// bottleneck of the whole sort.)
+__device__ __forceinline__ uint32_t digit_peers(uint32_t d, bool ok) {
+  uint32_t peers = __ballot_sync(0xFFFFFFFFu, ok);
+#pragma unroll
+  for (int b = 0; b < 8; ++b) {
+    const bool bit = (d >> b) & 1u;
+    const uint32_t m = __ballot_sync(0xFFFFFFFFu, bit);
+    peers &= bit ? m : ~m;
+  }
+  return peers;
+}
+
 inline int chunks_for(int64_t n) { return (int)((n + kChunk - 1) / kChunk); }
 // bytes of scratch for the per-chunk digit counts of `segments` segments of length n
 inline size_t counts_bytes(int64_t segments, int64_t n) { return (size_t)segments * chunks_for(n) * kBins * sizeof(uint32_t); }
@@ -30,25 +44,34 @@ inline size_t counts_bytes(int64_t segments, int64_t n) { return (size_t)segment
 template <bool FIRST>
 __global__ void __launch_bounds__(kThreads)
 hist_kernel(const uint32_t* __restrict__ keys, int64_t n, int shift, uint32_t* __restrict__ counts) {
-  __shared__ uint32_t h[kBins];
+  __shared__ uint32_t h[kWarps][kBins];          // warp-private counters: leaders update them with plain ld/st
   const int seg = blockIdx.y, chunk = blockIdx.x;
-  h[threadIdx.x] = 0;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int i = threadIdx.x; i < kWarps * kBins; i += kThreads) (&h[0][0])[i] = 0;
   __syncthreads();
   const uint32_t* k = keys + (size_t)seg * n;
-  const int64_t base = (int64_t)chunk * kChunk;
-#pragma unroll 4
+  const int64_t base = (int64_t)chunk * kChunk + (int64_t)warp * (32 * kItems);
+  uint32_t key[kItems];
+#pragma unroll
   for (int i = 0; i < kItems; ++i) {
-    const int64_t e = base + (int64_t)i * kThreads + threadIdx.x;
-    const bool ok = e < n;
-    uint32_t u = ok ? k[e] : 0xFFFFFFFFu;
-    if (FIRST) u = f2ord(u);
-    const uint32_t d = (u >> shift) & 0xFFu;
-    // warp-aggregated shared-memory atomic (the top digit of Gaussian keys is concentrated in a few bins)
-    const uint32_t peers = __match_any_sync(0xFFFFFFFFu, ok ? d : 0x100u);
-    if (ok && (__ffs(peers) - 1) == (int)(threadIdx.x & 31)) atomicAdd(&h[d], __popc(peers));
+    const int64_t e = base + i * 32 + lane;
+    uint32_t u = e < n ? k[e] : 0xFFFFFFFFu;
+    if (FIRST && e < n) u = f2ord(u);
+    key[i] = u;
+  }
+#pragma unroll
+  for (int i = 0; i < kItems; ++i) {
+    const bool ok = base + i * 32 + lane < n;
+    const uint32_t d = (key[i] >> shift) & 0xFFu;
+    const uint32_t peers = digit_peers(d, ok);
+    if (ok && (__ffs(peers) - 1) == lane) h[warp][d] += __popc(peers);
+    __syncwarp();
   }
   __syncthreads();
-  counts[((size_t)seg * gridDim.x + chunk) * kBins + threadIdx.x] = h[threadIdx.x];
+  uint32_t t = 0;
+#pragma unroll
+  for (int w = 0; w < kWarps; ++w) t += h[w][threadIdx.x];
+  counts[((size_t)seg * gridDim.x + chunk) * kBins + threadIdx.x] = t;
 }
 
 // ---- scan: counts -> exclusive global offsets, in place ----------------------------------------------------------
@@ -115,8 +138,8 @@ scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict_
     const int64_t e = base + i * 32 + lane;
     const bool ok = e < n;
     const uint32_t d = (key[i] >> shift) & 0xFFu;
-    const uint32_t peers = __match_any_sync(0xFFFFFFFFu, ok ? d : 0x100u);
-    const int leader = __ffs(peers) - 1;
+    const uint32_t peers = digit_peers(d, ok);
+    const int leader = ok ? __ffs(peers) - 1 : lane;
     uint32_t prev = 0;
     if (ok && lane == leader) { prev = wcount[warp][d]; wcount[warp][d] = prev + __popc(peers); }
     prev = __shfl_sync(0xFFFFFFFFu, prev, leader);

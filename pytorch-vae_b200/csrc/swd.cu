@@ -100,7 +100,7 @@ sgemm_kernel(GemmArgs g) {
 }
 
 // ---- loss + gradient through the permutation ---------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(1024)
 swd_loss_kernel(const float* __restrict__ zs, const uint32_t* __restrict__ perm, const float* __restrict__ ps,
                 int64_t n, float p, float* __restrict__ g_lat, double* __restrict__ partials, unsigned int* ticket,
                 double* __restrict__ sum_out) {
@@ -116,7 +116,7 @@ swd_loss_kernel(const float* __restrict__ zs, const uint32_t* __restrict__ perm,
     acc += (double)v;
     if (g_lat) g_lat[base + perm[base + i]] = dv;
   }
-  __shared__ double red[8];
+  __shared__ double red[32];
   double v[1] = {acc};
   block_sum<1>(v, red);
   const unsigned int nblocks = gridDim.x * gridDim.y;
@@ -198,11 +198,13 @@ extern "C" int vk_swd_fwd(const float* z, const float* prior, const float* proj,
   if (rc != VK_OK) return rc;
   // 3. loss and d/dlat (scattered to sample order into the spare key buffer)
   float* g_lat = grad_unscaled ? (float*)(ws + w.keyZ1) : nullptr;
-  int bx = (int)((N + 256 * 8 - 1) / (256 * 8));
-  const int max_bx = (int)(kMaxReduceBlocks / S) > 0 ? (int)(kMaxReduceBlocks / S) : 1;
+  // 1024-thread CTAs of 64 K elements each, launched segment-major: with two resident CTAs per SM about 18 segments
+  // (~75 MB of scatter targets) are in flight at a time, so the random 4-byte writes merge in the 126 MB L2
+  int bx = (int)((N + 65535) / 65536);
+  const int max_bx = (int)(kMaxReduceBlocks * 8 / S) > 0 ? (int)(kMaxReduceBlocks * 8 / S) : 1;
   if (bx > max_bx) bx = max_bx;
   VK_REQUIRE((int64_t)bx * S <= (int64_t)kMaxReduceBlocks * 8, VK_ERR_UNSUPPORTED, "swd_fwd: too many projections");
-  swd_loss_kernel<<<dim3(bx, (unsigned)S), 256, 0, st>>>(latT, (const uint32_t*)(ws + w.idx0), priT, N, p, g_lat,
+  swd_loss_kernel<<<dim3(bx, (unsigned)S), 1024, 0, st>>>(latT, (const uint32_t*)(ws + w.idx0), priT, N, p, g_lat,
                                                         (double*)(ws + w.partials), (unsigned int*)ws, sum_out);
   rc = check_launch("swd loss");
   if (rc != VK_OK) return rc;

@@ -26,8 +26,8 @@ using namespace tc;
 namespace {
 
 constexpr int kTileRows = 128;
-constexpr int kProducerWarps = 4, kEpilogueWarps = 4;
-constexpr int kVqThreads = 32 * (kProducerWarps + kEpilogueWarps + 1);   // warps 0-3 producer, 4-7 epilogue, 8 MMA
+constexpr int kProducerWarps = 8, kEpilogueWarps = 8, kOutputWarps = 8, kMmaWarp = 24, kParts = kEpilogueWarps / 4;
+constexpr int kVqThreads = 32 * (kMmaWarp + 1);   // warps 0-7 producers, 8-15 argmin, 16-23 output, 24 MMA
 
 struct VqShape {
   int64_t B, D, HW, K, R;
@@ -55,7 +55,7 @@ inline VqWs vq_ws(const VqShape& s) {
 
 // smem layout of the forward kernel
 struct VqSmem {
-  uint32_t cb, x[2], ee, xx, bars, tmem, total;
+  uint32_t cb, x[2], ee, xx, cand, bars, tmem, total;
 };
 __host__ __device__ inline VqSmem vq_smem(int Dp, int Kp) {
   VqSmem m;
@@ -64,7 +64,8 @@ __host__ __device__ inline VqSmem vq_smem(int Dp, int Kp) {
   m.x[0] = o;          o += 2u * kTileRows * Dp * 2;
   m.x[1] = o;          o += 2u * kTileRows * Dp * 2;
   m.ee = o;            o += Kp * 4u;
-  m.xx = o;            o += 4u * kTileRows * 4;          // |x|^2, 4 slots (producer runs <= 3 tiles ahead of the epilogue)
+  m.xx = o;            o += 4u * 2u * kTileRows * 4;     // |x|^2 halves, 4 slots (producers run <= 3 tiles ahead of the epilogue)
+  m.cand = o;          o += 2u * 4u * kTileRows * 8 + 2u * kTileRows * 4;   // per-part argmin candidates (dist, index), double-buffered; idx hand-over
   m.bars = o;          o += 16 * 8;
   m.tmem = o;          o += 16;
   m.total = o;
@@ -92,6 +93,9 @@ __global__ void vq_pack_codebook_kernel(const float* __restrict__ E, int K, int 
 }
 
 // ---- forward -------------------------------------------------------------------------------------------------
+// warps 0-7 producers (4 row quadrants x 2 halves of D), warps 8-15 argmin (4 TMEM lane quadrants x 2 column parts),
+// warps 16-23 output (gather / straight-through store / loss, decoupled so its global-memory latency is off the
+// argmin -> MMA critical path), warp 24 MMA issuer.
 __global__ void __launch_bounds__(kVqThreads, 1)
 vq_fwd_kernel(const float* __restrict__ X, const float* __restrict__ E, const uint8_t* __restrict__ cb_image,
               const float* __restrict__ ee_g, VqShape s, float beta, float* __restrict__ q_out,
@@ -100,10 +104,13 @@ vq_fwd_kernel(const float* __restrict__ X, const float* __restrict__ E, const ui
   const VqSmem L = vq_smem(s.Dp, s.Kp);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t sbase = smem_u32(smem);
-  // barriers: 0 cb_full | 1,2 x_full | 3,4 x_empty | 5,6 tmem_full | 7,8 tmem_empty
+  // barriers: 0 cb_full | 1,2 x_full | 3,4 x_empty | 5,6 tmem_full | 7,8 tmem_empty | 9,10 idx_full | 11,12 idx_empty
   auto bar = [&](int i) { return sbase + L.bars + 8u * i; };
   float* ee_s = reinterpret_cast<float*>(smem + L.ee);
-  float* xx_s = reinterpret_cast<float*>(smem + L.xx);
+  float* xx_s = reinterpret_cast<float*>(smem + L.xx);          // [4 slots][2 halves][128]
+  float* cand_d = reinterpret_cast<float*>(smem + L.cand);      // [2][4 parts][128]
+  int* cand_i = reinterpret_cast<int*>(smem + L.cand) + 2 * 4 * kTileRows;
+  int* idx_s = cand_i + 2 * 4 * kTileRows;                      // [2][128] winning code per row
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + L.tmem);
 
   if (threadIdx.x == 0) {
@@ -112,9 +119,11 @@ vq_fwd_kernel(const float* __restrict__ X, const float* __restrict__ E, const ui
     mbar_init(bar(3), 1); mbar_init(bar(4), 1);
     mbar_init(bar(5), 1); mbar_init(bar(6), 1);
     mbar_init(bar(7), 32 * kEpilogueWarps); mbar_init(bar(8), 32 * kEpilogueWarps);
+    mbar_init(bar(9), kTileRows); mbar_init(bar(10), kTileRows);
+    mbar_init(bar(11), 32 * kOutputWarps); mbar_init(bar(12), 32 * kOutputWarps);
     mbar_fence_init();
   }
-  if (warp == 8) tmem_alloc(smem_u32(tmem_slot), 512);
+  if (warp == kMmaWarp) tmem_alloc(smem_u32(tmem_slot), 512);
   for (int k = threadIdx.x; k < s.Kp; k += blockDim.x) ee_s[k] = ee_g[k];
   fence_before_sync();
   __syncthreads();
@@ -124,8 +133,10 @@ vq_fwd_kernel(const float* __restrict__ X, const float* __restrict__ E, const ui
   const uint32_t cb_img_bytes = 2u * s.Kp * s.Dp;          // one codebook image (hi or lo)
 
   if (warp < kProducerWarps) {
-    // ===== producers: NCHW fp32 -> bf16 hi/lo operand image, |x|^2 =====
-    const int t = threadIdx.x;                               // row within the tile
+    // ===== producers: NCHW fp32 -> bf16 hi/lo operand image, |x|^2 (each warp: 32 rows x half of the latent dims) =====
+    const int t = (warp & 3) * 32 + lane;                    // row within the tile
+    const int half = warp >> 2;
+    const int dbeg = half * (s.Dp / 2), dend = dbeg + s.Dp / 2;
     int it = 0;
     for (int64_t tile = blockIdx.x; tile < s.tiles; tile += gridDim.x, ++it) {
       const int st = it & 1;
@@ -137,30 +148,35 @@ vq_fwd_kernel(const float* __restrict__ X, const float* __restrict__ E, const ui
       uint8_t* hi = smem + L.x[st];
       uint8_t* lo = hi + img_bytes;
       float xx = 0.f;
-      for (int d0 = 0; d0 < s.Dp; d0 += 8) {
-        float v[8];
+      for (int d0 = dbeg; d0 < dend; d0 += 16) {
+        float v[16];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) v[e] = (live && d0 + e < s.D) ? __ldg(xp + (int64_t)(d0 + e) * s.HW) : 0.f;
-        uint32_t ph[4], pl[4];
+        for (int e = 0; e < 16; ++e)
+          v[e] = (live && d0 + e < s.D && d0 + e < dend) ? __ldg(xp + (int64_t)(d0 + e) * s.HW) : 0.f;
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          __nv_bfloat16 h0, l0, h1, l1;
-          split_bf16(v[2 * e], h0, l0);
-          split_bf16(v[2 * e + 1], h1, l1);
-          ph[e] = pack2(h0, h1);
-          pl[e] = pack2(l0, l1);
-          xx += v[2 * e] * v[2 * e];
-          xx += v[2 * e + 1] * v[2 * e + 1];
+        for (int c = 0; c < 2; ++c) {
+          if (d0 + 8 * c >= dend) break;
+          uint32_t ph[4], pl[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            __nv_bfloat16 h0, l0, h1, l1;
+            split_bf16(v[8 * c + 2 * e], h0, l0);
+            split_bf16(v[8 * c + 2 * e + 1], h1, l1);
+            ph[e] = pack2(h0, h1);
+            pl[e] = pack2(l0, l1);
+            xx = fmaf(v[8 * c + 2 * e], v[8 * c + 2 * e], xx);
+            xx = fmaf(v[8 * c + 2 * e + 1], v[8 * c + 2 * e + 1], xx);
+          }
+          const uint32_t off = ((uint32_t)((d0 >> 3) + c) * kTileRows + t) * 16;
+          *reinterpret_cast<uint4*>(hi + off) = make_uint4(ph[0], ph[1], ph[2], ph[3]);
+          *reinterpret_cast<uint4*>(lo + off) = make_uint4(pl[0], pl[1], pl[2], pl[3]);
         }
-        const uint32_t off = ((uint32_t)(d0 >> 3) * kTileRows + t) * 16;
-        *reinterpret_cast<uint4*>(hi + off) = make_uint4(ph[0], ph[1], ph[2], ph[3]);
-        *reinterpret_cast<uint4*>(lo + off) = make_uint4(pl[0], pl[1], pl[2], pl[3]);
       }
-      xx_s[(it & 3) * kTileRows + t] = xx;
+      xx_s[((it & 3) * 2 + half) * kTileRows + t] = xx;
       fence_proxy_async();
       mbar_arrive(bar(1 + st));
     }
-  } else if (warp == 8) {
+  } else if (warp == kMmaWarp) {
     // ===== MMA issuer =====
     if (lane == 0) {
       mbar_expect_tx(bar(0), 2 * cb_img_bytes);
@@ -194,24 +210,25 @@ vq_fwd_kernel(const float* __restrict__ X, const float* __restrict__ E, const ui
         mma_commit(bar(3 + st));                            // x stage free once every MMA of this tile has run
       }
     }
-  } else {
-    // ===== epilogue: distances, argmin, gather, straight-through output, loss partial =====
-    const int ew = warp - kProducerWarps;                    // == warp % 4 -> TMEM lanes 32*ew .. 32*ew+31
+  } else if (warp < kProducerWarps + kEpilogueWarps) {
+    // ===== argmin warps: distances in the reference's association, first-index argmin over half of the codes, merge =====
+    const int ew = warp & 3;                                 // TMEM lanes 32*ew .. 32*ew+31 (hardware: warp id % 4)
+    const int part = (warp - kProducerWarps) >> 2;           // 0..1: which 32-column blocks of a chunk
     const int t = ew * 32 + lane;
-    double sq = 0.0;
+    const int nblk = s.NC / 32;
     int it = 0;
     uint32_t c = 0;
     for (int64_t tile = blockIdx.x; tile < s.tiles; tile += gridDim.x, ++it) {
-      const int st = it & 1;
       float best = INFINITY;
-      int bi = 0;
+      int bi = 0x7FFFFFFF;
       float xx = 0.f;
       for (int ch = 0; ch < s.nch; ++ch, ++c) {
         const uint32_t buf = c & 1;
         mbar_wait(bar(5 + buf), (c >> 1) & 1);
         fence_after_sync();
-        if (ch == 0) xx = xx_s[(it & 3) * kTileRows + t];    // written before x_full, which precedes tmem_full
-        for (int c0 = 0; c0 < s.NC; c0 += 32) {
+        if (ch == 0) xx = xx_s[((it & 3) * 2 + 0) * kTileRows + t] + xx_s[((it & 3) * 2 + 1) * kTileRows + t];
+        for (int blk = part; blk < nblk; blk += kParts) {
+          const int c0 = blk * 32;
           uint32_t r[32];
           tmem_ld32(tmem + ((uint32_t)(ew * 32) << 16) + buf * 256 + c0, r);
           tmem_ld_wait();
@@ -230,28 +247,61 @@ vq_fwd_kernel(const float* __restrict__ X, const float* __restrict__ E, const ui
         fence_before_sync();
         mbar_arrive(bar(7 + buf));
       }
+      // merge the column parts of this row (first index wins ties, like torch.argmin) and hand the index over
+      const int cbuf = (it & 1) * kParts * kTileRows;
+      cand_d[cbuf + part * kTileRows + t] = best;
+      cand_i[cbuf + part * kTileRows + t] = bi;
+      asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpilogueWarps) : "memory");
+      if (part == 0) {
+#pragma unroll
+        for (int q = 1; q < kParts; ++q) {
+          const float dq = cand_d[cbuf + q * kTileRows + t];
+          const int iq = cand_i[cbuf + q * kTileRows + t];
+          if (dq < best || (dq == best && iq < bi)) { best = dq; bi = iq; }
+        }
+        const int sl = it & 1;
+        if (it >= 2) mbar_wait(bar(11 + sl), ((it >> 1) - 1) & 1);
+        idx_s[sl * kTileRows + t] = bi;
+        mbar_arrive(bar(9 + sl));
+      }
+    }
+  } else {
+    // ===== output warps: gather the fp32 code, straight-through value back to NCHW, indices, squared error =====
+    const int ot = threadIdx.x - 32 * (kProducerWarps + kEpilogueWarps);   // 0..255
+    const int t = ot & 127, dh = ot >> 7;
+    double sq = 0.0;
+    int it = 0;
+    for (int64_t tile = blockIdx.x; tile < s.tiles; tile += gridDim.x, ++it) {
+      const int sl = it & 1;
+      mbar_wait(bar(9 + sl), (it >> 1) & 1);
+      const int bi = idx_s[sl * kTileRows + t];
+      mbar_arrive(bar(11 + sl));
       const int64_t r = tile * kTileRows + t;
       if (r < s.R) {
-        idx_out[r] = bi;
+        if (dh == 0) idx_out[r] = bi;
         const int64_t b = r / s.HW, hw = r % s.HW;
         const float* xp = X + (b * s.D) * s.HW + hw;
         float* qp = q_out + (b * s.D) * s.HW + hw;
         const float* ep = E + (size_t)bi * s.D;
         float acc = 0.f;
-        if ((s.D & 3) == 0) {
-          for (int d = 0; d < s.D; d += 4) {
-            const float4 e4 = __ldg(reinterpret_cast<const float4*>(ep + d));
-            const float ev[4] = {e4.x, e4.y, e4.z, e4.w};
+        if ((s.D & 15) == 0) {
+          const int dq = (int)s.D / 2;
+          for (int d = dh * dq; d < (dh + 1) * dq; d += 8) {
+            const float4 e0 = __ldg(reinterpret_cast<const float4*>(ep + d));
+            const float4 e1 = __ldg(reinterpret_cast<const float4*>(ep + d + 4));
+            const float ev[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w};
+            float xv[8];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const float x = __ldg(xp + (int64_t)(d + j) * s.HW);
-              const float df = ev[j] - x;
-              qp[(int64_t)(d + j) * s.HW] = x + df;          // latents + (quantized - latents).detach()
+            for (int j = 0; j < 8; ++j) xv[j] = __ldg(xp + (int64_t)(d + j) * s.HW);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float df = ev[j] - xv[j];
+              qp[(int64_t)(d + j) * s.HW] = xv[j] + df;      // latents + (quantized - latents).detach()
               acc = fmaf(df, df, acc);
             }
           }
         } else {
-          for (int d = 0; d < s.D; ++d) {
+          for (int d = dh; d < s.D; d += 2) {
             const float x = __ldg(xp + (int64_t)d * s.HW);
             const float df = __ldg(ep + d) - x;
             qp[(int64_t)d * s.HW] = x + df;
@@ -261,15 +311,14 @@ vq_fwd_kernel(const float* __restrict__ X, const float* __restrict__ E, const ui
         sq += (double)acc;
       }
     }
-    // block partial of sum (q-x)^2 over the epilogue warps, then the last-block combine
-    double v[1] = {sq};
-    __shared__ double red[kEpilogueWarps];
-    v[0] = warp_sum(v[0]);
-    if (lane == 0) red[ew] = v[0];
-    asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpilogueWarps));
-    if (ew == 0 && lane == 0) {
+    // block partial of sum (q-x)^2 over the output warps, then the last-block combine
+    __shared__ double red[kOutputWarps];
+    sq = warp_sum(sq);
+    if (lane == 0) red[ot >> 5] = sq;
+    asm volatile("bar.sync 2, %0;" ::"n"(32 * kOutputWarps) : "memory");
+    if (ot == 0) {
       double tot = 0;
-      for (int i = 0; i < kEpilogueWarps; ++i) tot += red[i];
+      for (int i = 0; i < kOutputWarps; ++i) tot += red[i];
       partials[blockIdx.x] = tot;
       __threadfence();
       const unsigned int tk = atomicAdd(ticket, 1u);
@@ -286,12 +335,12 @@ vq_fwd_kernel(const float* __restrict__ X, const float* __restrict__ E, const ui
   }
   fence_before_sync();
   __syncthreads();
-  if (warp == 8) tmem_dealloc(tmem, 512);
+  if (warp == kMmaWarp) tmem_dealloc(tmem, 512);
 }
 
 // ---- backward ------------------------------------------------------------------------------------------------
 // g_x = g_q + g_loss * (2 beta / numel) (x - q);   g_E[idx] += g_loss * (2 / numel) (q - x)   (vq_vae.py:47-51)
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(1024, 1)
 vq_bwd_kernel(const float* __restrict__ g_q, const float* __restrict__ g_loss, const float* __restrict__ X,
               const float* __restrict__ E, const int32_t* __restrict__ idx, VqShape s, float beta,
               float* __restrict__ g_x, float* __restrict__ g_E) {
@@ -303,19 +352,43 @@ vq_bwd_kernel(const float* __restrict__ g_q, const float* __restrict__ g_loss, c
   const float gl = g_loss ? *g_loss : 0.f;
   const float cx = gl * 2.f * beta / (float)((double)s.R * (double)s.D);
   const float ce = gl * 2.f / (float)((double)s.R * (double)s.D);
-  for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < s.R; r += (int64_t)gridDim.x * blockDim.x) {
+  // 128 rows x 8 slices of the latent dims per pass: loads stay coalesced along h*w, 8x more of them in flight
+  const int rl = threadIdx.x & 127, dc = threadIdx.x >> 7;
+  const bool vec = (s.D & 31) == 0;
+  const int dper = (int)s.D / 8;
+  for (int64_t tile = blockIdx.x; tile < s.tiles; tile += gridDim.x) {
+    const int64_t r = tile * kTileRows + rl;
+    if (r >= s.R) continue;
     const int64_t b = r / s.HW, hw = r % s.HW;
     const int k = idx[r];
     const float* xp = X + (b * s.D) * s.HW + hw;
     const float* gp = g_q ? g_q + (b * s.D) * s.HW + hw : nullptr;
     float* op = g_x ? g_x + (b * s.D) * s.HW + hw : nullptr;
     const float* ep = E + (size_t)k * s.D;
-#pragma unroll 8
-    for (int d = 0; d < s.D; ++d) {
-      const float x = __ldg(xp + (int64_t)d * s.HW);
-      const float df = __ldg(ep + d) - x;                    // q - x
-      if (op) op[(int64_t)d * s.HW] = (gp ? __ldg(gp + (int64_t)d * s.HW) : 0.f) - cx * df;
-      if (want_e) atomicAdd(&acc_s[k * ld + d], ce * df);
+    if (vec) {
+      for (int d0 = dc * dper; d0 < (dc + 1) * dper; d0 += 4) {
+        const float4 e4 = __ldg(reinterpret_cast<const float4*>(ep + d0));
+        const float ev[4] = {e4.x, e4.y, e4.z, e4.w};
+        float xv[4], gv[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          xv[j] = __ldg(xp + (int64_t)(d0 + j) * s.HW);
+          gv[j] = gp ? __ldg(gp + (int64_t)(d0 + j) * s.HW) : 0.f;
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float df = ev[j] - xv[j];                    // q - x
+          if (op) op[(int64_t)(d0 + j) * s.HW] = gv[j] - cx * df;
+          if (want_e) atomicAdd(&acc_s[k * ld + d0 + j], ce * df);
+        }
+      }
+    } else {
+      for (int d = dc; d < s.D; d += 8) {
+        const float x = __ldg(xp + (int64_t)d * s.HW);
+        const float df = __ldg(ep + d) - x;
+        if (op) op[(int64_t)d * s.HW] = (gp ? __ldg(gp + (int64_t)d * s.HW) : 0.f) - cx * df;
+        if (want_e) atomicAdd(&acc_s[k * ld + d], ce * df);
+      }
     }
   }
   if (want_e) {
@@ -395,8 +468,8 @@ extern "C" int vk_vq_bwd(const float* g_q, const float* g_loss, const float* lat
   if (sm > 48 * 1024 && cudaFuncSetAttribute(vq_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm) != cudaSuccess)
     return check_launch("vq_bwd (shared memory attribute)");
   if (g_codebook) zero_kernel<<<64, 256, 0, st>>>(g_codebook, K * D);
-  int64_t blocks = (s.R + 255) / 256;
+  int64_t blocks = s.tiles;
   if (blocks > sm_count()) blocks = sm_count();
-  vq_bwd_kernel<<<(int)blocks, 256, sm, st>>>(g_q, g_loss, latents, codebook, idx, s, beta, g_latents, g_codebook);
+  vq_bwd_kernel<<<(int)blocks, 1024, sm, st>>>(g_q, g_loss, latents, codebook, idx, s, beta, g_latents, g_codebook);
   return check_launch("vq_bwd");
 }
