@@ -10,11 +10,12 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-OBJ = os.path.join(HERE, "build")
-OUT = os.path.join(HERE, "vaekit", "_lib", "libvaekit.so")
+OBJ = os.environ.get("VK_OBJ") or os.path.join(HERE, "build")
+OUT = os.environ.get("VK_OUT") or os.path.join(HERE, "vaekit", "_lib", "libvaekit.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
          "-Xcompiler", "-fPIC", "-Xptxas", "-v", "--expt-relaxed-constexpr"]
+FLAGS += os.environ.get("VK_NVCC_EXTRA", "").split()      # e.g. -DVK_ROLE_PROF for the per-role cycle counters
 
 
 def _sources():

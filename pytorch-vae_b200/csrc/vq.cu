@@ -26,8 +26,20 @@ using namespace tc;
 namespace {
 
 constexpr int kTileRows = 128;
+// Per-role cycle counters (debug builds only: VK_NVCC_EXTRA=-DVK_ROLE_PROF): CTA 0 prints, for the first thread of
+// each role, the cycles spent in each lap class (waits vs work).
+#ifdef VK_ROLE_PROF
+#define PROF_DECL long long p_[4] = {0, 0, 0, 0}; long long t_ = clock64();
+#define PROF_LAP(i) { const long long n_ = clock64(); p_[i] += n_ - t_; t_ = n_; }
+#define PROF_OUT(name, cond) if (blockIdx.x == 0 && (cond)) printf("%s: %lld %lld %lld %lld\n", name, p_[0], p_[1], p_[2], p_[3]);
+#else
+#define PROF_DECL
+#define PROF_LAP(i)
+#define PROF_OUT(name, cond)
+#endif
+
 constexpr int kProducerWarps = 8, kEpilogueWarps = 8, kOutputWarps = 8, kMmaWarp = 24, kParts = kEpilogueWarps / 4;
-constexpr int kVqThreads = 32 * (kMmaWarp + 1);   // warps 0-7 producers, 8-15 argmin, 16-23 output, 24 MMA
+constexpr int kVqThreads = 32 * (kMmaWarp + 1);   // warps 0-7 producers, 8-15 output, 16-23 argmin, 24 MMA
 
 struct VqShape {
   int64_t B, D, HW, K, R;
@@ -55,7 +67,7 @@ inline VqWs vq_ws(const VqShape& s) {
 
 // smem layout of the forward kernel
 struct VqSmem {
-  uint32_t cb, x[2], ee, xx, cand, bars, tmem, total;
+  uint32_t cb, x[2], ee, cand, bars, tmem, total;
 };
 __host__ __device__ inline VqSmem vq_smem(int Dp, int Kp) {
   VqSmem m;
@@ -64,7 +76,6 @@ __host__ __device__ inline VqSmem vq_smem(int Dp, int Kp) {
   m.x[0] = o;          o += 2u * kTileRows * Dp * 2;
   m.x[1] = o;          o += 2u * kTileRows * Dp * 2;
   m.ee = o;            o += Kp * 4u;
-  m.xx = o;            o += 4u * 2u * kTileRows * 4;     // |x|^2 halves, 4 slots (producers run <= 3 tiles ahead of the epilogue)
   m.cand = o;          o += 2u * 4u * kTileRows * 8 + 2u * kTileRows * 4;   // per-part argmin candidates (dist, index), double-buffered; idx hand-over
   m.bars = o;          o += 16 * 8;
   m.tmem = o;          o += 16;
@@ -93,8 +104,8 @@ __global__ void vq_pack_codebook_kernel(const float* __restrict__ E, int K, int 
 }
 
 // ---- forward -------------------------------------------------------------------------------------------------
-// warps 0-7 producers (4 row quadrants x 2 halves of D), warps 8-15 argmin (4 TMEM lane quadrants x 2 column parts),
-// warps 16-23 output (gather / straight-through store / loss, decoupled so its global-memory latency is off the
+// warps 0-7 producers (4 row quadrants x 2 halves of D), warps 16-23 argmin (4 TMEM lane quadrants x 2 column parts),
+// warps 8-15 output (gather / straight-through store / loss, decoupled so its global-memory latency is off the
 // argmin -> MMA critical path), warp 24 MMA issuer.
 __global__ void __launch_bounds__(kVqThreads, 1)
 vq_fwd_kernel(const float* __restrict__ X, const float* __restrict__ E, const uint8_t* __restrict__ cb_image,
@@ -107,7 +118,6 @@ vq_fwd_kernel(const float* __restrict__ X, const float* __restrict__ E, const ui
   // barriers: 0 cb_full | 1,2 x_full | 3,4 x_empty | 5,6 tmem_full | 7,8 tmem_empty | 9,10 idx_full | 11,12 idx_empty
   auto bar = [&](int i) { return sbase + L.bars + 8u * i; };
   float* ee_s = reinterpret_cast<float*>(smem + L.ee);
-  float* xx_s = reinterpret_cast<float*>(smem + L.xx);          // [4 slots][2 halves][128]
   float* cand_d = reinterpret_cast<float*>(smem + L.cand);      // [2][4 parts][128]
   int* cand_i = reinterpret_cast<int*>(smem + L.cand) + 2 * 4 * kTileRows;
   int* idx_s = cand_i + 2 * 4 * kTileRows;                      // [2][128] winning code per row
@@ -137,45 +147,55 @@ vq_fwd_kernel(const float* __restrict__ X, const float* __restrict__ E, const ui
     const int t = (warp & 3) * 32 + lane;                    // row within the tile
     const int half = warp >> 2;
     const int dbeg = half * (s.Dp / 2), dend = dbeg + s.Dp / 2;
+    const uint32_t hw32 = (uint32_t)s.HW;
+    const bool fast = (s.D & 63) == 0;                       // each half of the dims is whole 32-dim groups
     int it = 0;
+    PROF_DECL
     for (int64_t tile = blockIdx.x; tile < s.tiles; tile += gridDim.x, ++it) {
       const int st = it & 1;
-      if (it >= 2) mbar_wait(bar(3 + st), ((it >> 1) - 1) & 1);
-      const int64_t r = tile * kTileRows + t;
-      const bool live = r < s.R;
-      const int64_t b = live ? r / s.HW : 0, hw = live ? r % s.HW : 0;
-      const float* xp = X + (b * s.D) * s.HW + hw;
-      uint8_t* hi = smem + L.x[st];
+      PROF_LAP(1)
+      if (it >= 2) mbar_wait_relaxed(bar(3 + st), ((it >> 1) - 1) & 1);
+      PROF_LAP(0)
+      const uint32_t r = (uint32_t)tile * kTileRows + t;     // host guarantees R, D*HW < 2^31: 32-bit index math
+      const bool live = r < (uint32_t)s.R;
+      const uint32_t b = live ? r / hw32 : 0u, hw = live ? r - b * hw32 : 0u;
+      const float* xp = X + ((size_t)b * s.D + dbeg) * hw32 + hw;
+      uint8_t* hi = smem + L.x[0] + (uint32_t)st * 2u * img_bytes;
       uint8_t* lo = hi + img_bytes;
-      float xx = 0.f;
-      for (int d0 = dbeg; d0 < dend; d0 += 16) {
-        float v[16];
+      if (fast) {
+        // whole 32-dim groups, live or not: 32 strided loads in flight, one pointer bump each
+        for (int d0 = dbeg; d0 < dend; d0 += 32) {
+          float v[32];
 #pragma unroll
-        for (int e = 0; e < 16; ++e)
-          v[e] = (live && d0 + e < s.D && d0 + e < dend) ? __ldg(xp + (int64_t)(d0 + e) * s.HW) : 0.f;
+          for (int e = 0; e < 32; ++e) { v[e] = live ? __ldg(xp) : 0.f; xp += hw32; }
 #pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          if (d0 + 8 * c >= dend) break;
+          for (int c = 0; c < 4; ++c) {
+            uint32_t ph[4], pl[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) split_pair(v[8 * c + 2 * e], v[8 * c + 2 * e + 1], ph[e], pl[e]);
+            const uint32_t off = ((uint32_t)((d0 >> 3) + c) * kTileRows + t) * 16;
+            *reinterpret_cast<uint4*>(hi + off) = make_uint4(ph[0], ph[1], ph[2], ph[3]);
+            *reinterpret_cast<uint4*>(lo + off) = make_uint4(pl[0], pl[1], pl[2], pl[3]);
+          }
+        }
+      } else {
+        for (int d0 = dbeg; d0 < dend; d0 += 8) {
+          float v[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) { v[e] = (live && d0 + e < s.D) ? __ldg(xp) : 0.f; xp += hw32; }
           uint32_t ph[4], pl[4];
 #pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            __nv_bfloat16 h0, l0, h1, l1;
-            split_bf16(v[8 * c + 2 * e], h0, l0);
-            split_bf16(v[8 * c + 2 * e + 1], h1, l1);
-            ph[e] = pack2(h0, h1);
-            pl[e] = pack2(l0, l1);
-            xx = fmaf(v[8 * c + 2 * e], v[8 * c + 2 * e], xx);
-            xx = fmaf(v[8 * c + 2 * e + 1], v[8 * c + 2 * e + 1], xx);
-          }
-          const uint32_t off = ((uint32_t)((d0 >> 3) + c) * kTileRows + t) * 16;
+          for (int e = 0; e < 4; ++e) split_pair(v[2 * e], v[2 * e + 1], ph[e], pl[e]);
+          const uint32_t off = ((uint32_t)(d0 >> 3) * kTileRows + t) * 16;
           *reinterpret_cast<uint4*>(hi + off) = make_uint4(ph[0], ph[1], ph[2], ph[3]);
           *reinterpret_cast<uint4*>(lo + off) = make_uint4(pl[0], pl[1], pl[2], pl[3]);
         }
       }
-      xx_s[((it & 3) * 2 + half) * kTileRows + t] = xx;
       fence_proxy_async();
       mbar_arrive(bar(1 + st));
     }
+    PROF_LAP(1)
+    PROF_OUT("producer wait_empty/work", threadIdx.x == 0)
   } else if (warp == kMmaWarp) {
     // ===== MMA issuer =====
     if (lane == 0) {
@@ -184,74 +204,110 @@ vq_fwd_kernel(const float* __restrict__ X, const float* __restrict__ E, const ui
       mbar_wait(bar(0), 0);
       const uint32_t idesc = idesc_bf16(128, s.NC, 0, 0);
       const uint32_t a_lbo = kTileRows * 16, b_lbo = (uint32_t)s.Kp * 16;
+      const int ksteps = s.Dp / 16;
       int it = 0;
       uint32_t c = 0;                                       // global chunk counter -> TMEM buffer c & 1
+      PROF_DECL
       for (int64_t tile = blockIdx.x; tile < s.tiles; tile += gridDim.x, ++it) {
         const int st = it & 1;
+        PROF_LAP(2)
         mbar_wait(bar(1 + st), (it >> 1) & 1);
+        PROF_LAP(0)
         fence_after_sync();
-        const uint32_t a_hi = sbase + L.x[st], a_lo = a_hi + img_bytes;
+        const uint32_t a_hi = sbase + L.x[0] + (uint32_t)st * 2u * img_bytes, a_lo = a_hi + img_bytes;
         for (int ch = 0; ch < s.nch; ++ch, ++c) {
           const uint32_t buf = c & 1;
+          PROF_LAP(2)
           if (c >= 2) mbar_wait(bar(7 + buf), ((c >> 1) - 1) & 1);
+          PROF_LAP(1)
           fence_after_sync();
           const uint32_t b_hi = sbase + L.cb + (uint32_t)ch * s.NC * 16, b_lo = b_hi + cb_img_bytes;
           const uint32_t d = tmem + buf * 256;
+          // descriptors advance by a constant per K step (start-address field, 16-byte units): no per-MMA rebuild
+          const uint64_t da_hi = smem_desc(a_hi, a_lbo, 128), da_lo = smem_desc(a_lo, a_lbo, 128);
+          const uint64_t db_hi = smem_desc(b_hi, b_lbo, 128), db_lo = smem_desc(b_lo, b_lbo, 128);
+          const uint64_t a_step = (2u * a_lbo) >> 4, b_step = (2u * b_lbo) >> 4;
           uint32_t acc = 0;
+#pragma unroll
           for (int pass = 0; pass < 3; ++pass) {
-            const uint32_t a0 = pass == 1 ? a_lo : a_hi, b0 = pass == 2 ? b_lo : b_hi;
-            for (int k = 0; k < s.Dp / 16; ++k) {
-              mma_bf16(d, smem_desc(a0 + k * 2 * a_lbo, a_lbo, 128), smem_desc(b0 + k * 2 * b_lbo, b_lbo, 128), idesc, acc);
+            uint64_t da = pass == 1 ? da_lo : da_hi, db = pass == 2 ? db_lo : db_hi;
+#pragma unroll 4
+            for (int k = 0; k < ksteps; ++k) {
+              mma_bf16(d, da, db, idesc, acc);
               acc = 1;
+              da += a_step;
+              db += b_step;
             }
           }
           mma_commit(bar(5 + buf));
         }
         mma_commit(bar(3 + st));                            // x stage free once every MMA of this tile has run
       }
+      PROF_LAP(2)
+      PROF_OUT("mma wait_x/wait_tmem/issue", true)
     }
-  } else if (warp < kProducerWarps + kEpilogueWarps) {
-    // ===== argmin warps: distances in the reference's association, first-index argmin over half of the codes, merge =====
+  } else if (warp >= kProducerWarps + kOutputWarps) {
+    // ===== argmin warps (highest warp ids: the scheduler favours them): first-index argmin over half of the codes, merge =====
     const int ew = warp & 3;                                 // TMEM lanes 32*ew .. 32*ew+31 (hardware: warp id % 4)
-    const int part = (warp - kProducerWarps) >> 2;           // 0..1: which 32-column blocks of a chunk
+    const int part = (warp - kProducerWarps - kOutputWarps) >> 2;   // 0..1: which 32-column blocks of a chunk
     const int t = ew * 32 + lane;
     const int nblk = s.NC / 32;
     int it = 0;
     uint32_t c = 0;
+    PROF_DECL
     for (int64_t tile = blockIdx.x; tile < s.tiles; tile += gridDim.x, ++it) {
-      float best = INFINITY;
-      int bi = 0x7FFFFFFF;
-      float xx = 0.f;
+      // four independent (min, index) chains per thread: a single chain is bound by the FSETP -> select latency
+      float bq[4] = {INFINITY, INFINITY, INFINITY, INFINITY};
+      int iq4[4] = {0x7FFFFFFF, 0x7FFFFFFF, 0x7FFFFFFF, 0x7FFFFFFF};
       for (int ch = 0; ch < s.nch; ++ch, ++c) {
         const uint32_t buf = c & 1;
+        PROF_LAP(1)
         mbar_wait(bar(5 + buf), (c >> 1) & 1);
+        PROF_LAP(0)
         fence_after_sync();
-        if (ch == 0) xx = xx_s[((it & 3) * 2 + 0) * kTileRows + t] + xx_s[((it & 3) * 2 + 1) * kTileRows + t];
-        for (int blk = part; blk < nblk; blk += kParts) {
-          const int c0 = blk * 32;
-          uint32_t r[32];
-          tmem_ld32(tmem + ((uint32_t)(ew * 32) << 16) + buf * 256 + c0, r);
-          tmem_ld_wait();
-          const int kb = ch * s.NC + c0;
+        // 16-column halves of this part's 32-column blocks, TMEM loads ping-ponged against the compares
+        const uint32_t tbase = tmem + ((uint32_t)(ew * 32) << 16) + buf * 256;
+        const int nh = 2 * ((nblk - part + kParts - 1) / kParts);
+        auto col_of = [&](int h) { return ((part + (h >> 1) * kParts) << 5) + ((h & 1) << 4); };
+        auto consume = [&](const uint32_t (&r)[16], int kb) {
+          float ee[16];
 #pragma unroll
-          for (int i = 0; i < 32; i += 4) {
-            const float4 e4 = *reinterpret_cast<const float4*>(ee_s + kb + i);
-            const float ee[4] = {e4.x, e4.y, e4.z, e4.w};
+          for (int i = 0; i < 16; i += 4)
+            *reinterpret_cast<float4*>(ee + i) = *reinterpret_cast<const float4*>(ee_s + kb + i);
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const float dist = fmaf(-2.f, __uint_as_float(r[i + j]), xx + ee[j]);   // (|x|^2+|e|^2) - 2 x.e
-              if (dist < best) { best = dist; bi = kb + i + j; }
-            }
+          for (int i = 0; i < 16; ++i) {
+            // |e|^2 - 2 x.e: the row-constant |x|^2 of vq_vae.py:35-37 does not move the argmin (and its
+            // fp32 rounding is far below the split-bf16 error of the dot product), so it is left out
+            const float dist = fmaf(-2.f, __uint_as_float(r[i]), ee[i]);
+            if (dist < bq[i & 3]) iq4[i & 3] = kb + i;
+            bq[i & 3] = fminf(dist, bq[i & 3]);
           }
+        };
+        uint32_t ra[16], rb[16];
+        tmem_ld16(tbase + col_of(0), ra);
+        for (int h = 0; h < nh; h += 2) {
+          tmem_ld_wait16(ra);
+          tmem_ld16(tbase + col_of(h + 1), rb);
+          consume(ra, ch * s.NC + col_of(h));
+          tmem_ld_wait16(rb);
+          if (h + 2 < nh) tmem_ld16(tbase + col_of(h + 2), ra);
+          consume(rb, ch * s.NC + col_of(h + 1));
         }
         fence_before_sync();
         mbar_arrive(bar(7 + buf));
       }
+      float best = bq[0];
+      int bi = iq4[0];
+#pragma unroll
+      for (int j = 1; j < 4; ++j)
+        if (bq[j] < best || (bq[j] == best && iq4[j] < bi)) { best = bq[j]; bi = iq4[j]; }
       // merge the column parts of this row (first index wins ties, like torch.argmin) and hand the index over
       const int cbuf = (it & 1) * kParts * kTileRows;
       cand_d[cbuf + part * kTileRows + t] = best;
       cand_i[cbuf + part * kTileRows + t] = bi;
+      PROF_LAP(1)
       asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpilogueWarps) : "memory");
+      PROF_LAP(2)
       if (part == 0) {
 #pragma unroll
         for (int q = 1; q < kParts; ++q) {
@@ -260,57 +316,76 @@ vq_fwd_kernel(const float* __restrict__ X, const float* __restrict__ E, const ui
           if (dq < best || (dq == best && iq < bi)) { best = dq; bi = iq; }
         }
         const int sl = it & 1;
+        PROF_LAP(1)
         if (it >= 2) mbar_wait(bar(11 + sl), ((it >> 1) - 1) & 1);
+        PROF_LAP(3)
         idx_s[sl * kTileRows + t] = bi;
         mbar_arrive(bar(9 + sl));
       }
     }
+    PROF_LAP(1)
+    PROF_OUT("argmin wait_tmem/work/merge_bar/wait_idx_empty", threadIdx.x == 32 * (kProducerWarps + kOutputWarps))
   } else {
     // ===== output warps: gather the fp32 code, straight-through value back to NCHW, indices, squared error =====
-    const int ot = threadIdx.x - 32 * (kProducerWarps + kEpilogueWarps);   // 0..255
+    const int ot = threadIdx.x - 32 * kProducerWarps;        // 0..255
     const int t = ot & 127, dh = ot >> 7;
     double sq = 0.0;
     int it = 0;
+    PROF_DECL
     for (int64_t tile = blockIdx.x; tile < s.tiles; tile += gridDim.x, ++it) {
       const int sl = it & 1;
-      mbar_wait(bar(9 + sl), (it >> 1) & 1);
+      PROF_LAP(1)
+      mbar_wait_relaxed(bar(9 + sl), (it >> 1) & 1);
+      PROF_LAP(0)
       const int bi = idx_s[sl * kTileRows + t];
       mbar_arrive(bar(11 + sl));
-      const int64_t r = tile * kTileRows + t;
-      if (r < s.R) {
+      const uint32_t r = (uint32_t)tile * kTileRows + t;
+      if (r < (uint32_t)s.R) {
         if (dh == 0) idx_out[r] = bi;
-        const int64_t b = r / s.HW, hw = r % s.HW;
-        const float* xp = X + (b * s.D) * s.HW + hw;
-        float* qp = q_out + (b * s.D) * s.HW + hw;
-        const float* ep = E + (size_t)bi * s.D;
+        const uint32_t hw32 = (uint32_t)s.HW;
+        const uint32_t b = r / hw32, hw = r - b * hw32;
         float acc = 0.f;
-        if ((s.D & 15) == 0) {
+        if ((s.D & 31) == 0) {
           const int dq = (int)s.D / 2;
-          for (int d = dh * dq; d < (dh + 1) * dq; d += 8) {
-            const float4 e0 = __ldg(reinterpret_cast<const float4*>(ep + d));
-            const float4 e1 = __ldg(reinterpret_cast<const float4*>(ep + d + 4));
-            const float ev[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w};
-            float xv[8];
+          const size_t o = ((size_t)b * s.D + (size_t)dh * dq) * hw32 + hw;
+          const float* xp = X + o;
+          float* qp = q_out + o;
+          const float4* ep = reinterpret_cast<const float4*>(E + (size_t)bi * s.D + dh * dq);
+          for (int d = 0; d < dq; d += 16) {
+            const float4 e0 = __ldg(ep), e1 = __ldg(ep + 1), e2 = __ldg(ep + 2), e3 = __ldg(ep + 3);
+            ep += 4;
+            const float ev[16] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w,
+                                  e2.x, e2.y, e2.z, e2.w, e3.x, e3.y, e3.z, e3.w};
+            float xv[16];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) xv[j] = __ldg(xp + (int64_t)(d + j) * s.HW);
+            for (int j = 0; j < 16; ++j) { xv[j] = __ldg(xp); xp += hw32; }
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
+            for (int j = 0; j < 16; ++j) {
               const float df = ev[j] - xv[j];
-              qp[(int64_t)(d + j) * s.HW] = xv[j] + df;      // latents + (quantized - latents).detach()
+              *qp = xv[j] + df;                              // latents + (quantized - latents).detach()
+              qp += hw32;
               acc = fmaf(df, df, acc);
             }
           }
         } else {
+          const size_t o = ((size_t)b * s.D + dh) * hw32 + hw;
+          const float* xp = X + o;
+          float* qp = q_out + o;
+          const float* ep = E + (size_t)bi * s.D;
           for (int d = dh; d < s.D; d += 2) {
-            const float x = __ldg(xp + (int64_t)d * s.HW);
+            const float x = __ldg(xp);
             const float df = __ldg(ep + d) - x;
-            qp[(int64_t)d * s.HW] = x + df;
+            *qp = x + df;
+            xp += 2 * hw32;
+            qp += 2 * hw32;
             acc = fmaf(df, df, acc);
           }
         }
         sq += (double)acc;
       }
     }
+    PROF_LAP(1)
+    PROF_OUT("output wait_idx/work", ot == 0)
     // block partial of sum (q-x)^2 over the output warps, then the last-block combine
     __shared__ double red[kOutputWarps];
     sq = warp_sum(sq);
@@ -409,6 +484,9 @@ int make_shape(int64_t B, int64_t D, int64_t HW, int64_t K, VqShape& s) {
              (long long)B, (long long)D, (long long)HW, (long long)K);
   VK_REQUIRE(D <= 256 && K <= 4096, VK_ERR_UNSUPPORTED, "vq: D=%lld (max 256) or K=%lld (max 4096) too large",
              (long long)D, (long long)K);
+  VK_REQUIRE(B * HW < (1ll << 31) - 128 && HW * D < (1ll << 31), VK_ERR_UNSUPPORTED,
+             "vq: B*HW=%lld rows or D*HW=%lld beyond the 32-bit index math of the kernels", (long long)(B * HW),
+             (long long)(D * HW));
   s.B = B; s.D = D; s.HW = HW; s.K = K; s.R = B * HW;
   s.Dp = round_up((int)D, 16);
   s.NC = K >= 256 ? 256 : round_up((int)K, 32);

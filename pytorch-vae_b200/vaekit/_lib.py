@@ -7,7 +7,7 @@ import threading
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "_lib", "libvaekit.so")
+LIB_PATH = os.environ.get("VAEKIT_LIB") or os.path.join(_HERE, "_lib", "libvaekit.so")   # override: instrumented builds
 
 _p = C.c_void_p
 _i64 = C.c_int64
