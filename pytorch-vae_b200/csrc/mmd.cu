@@ -33,9 +33,9 @@ constexpr int kRows = 128;       // row block (MMA M)
 constexpr int kCols = 64;        // column tile (GEMM1 N, GEMM2 K)
 constexpr int kBStages = 3;
 constexpr int kNormRing = 8;
-constexpr int kEpiWarps = 8, kTmaWarp = 8, kMmaWarp = 9;
+constexpr int kEpiWarps = 16, kColGroups = kEpiWarps / 4, kTmaWarp = 16, kMmaWarp = 17;
 constexpr int kEpiThreads = 32 * kEpiWarps;
-constexpr int kMmdThreads = 32 * 10;  // warps 0-7 epilogue, warp 8 TMA, warp 9 MMA
+constexpr int kMmdThreads = 32 * 18;  // warps 0-15 epilogue, warp 16 TMA, warp 17 MMA
 constexpr int kMaxQ = 8;
 
 struct MmdShape {
@@ -47,7 +47,7 @@ struct MmdShape {
   int kernel_type;      // 0 rbf, 1 imq
   int passes;           // 3 (hi/lo split, fp32-grade) or 1 (plain bf16)
   float a_exp;          // rbf: -log2(e) / (2 D^2 z_var)
-  float dk_scale;       // rbf: -1 / (2 D^2 z_var) ; imq: -1 / C
+  float dk_scale;       // dk/dd^2 = dk_scale * coefficient: rbf -1 / (2 D^2 z_var) (coef k) ; imq -C (coef (k/C)^2)
   float C, Ceps;        // imq: C, fl32(1e-7 + C)
 };
 
@@ -71,7 +71,7 @@ inline MmdWs mmd_ws(int64_t N, int D, int rows_local_blocks, int Q) {
   w.normZ = o; o += (size_t)T * kRows * 4;
   w.normP = o; o += (size_t)T * kRows * 4;
   w.Opart = o; o += (size_t)Q * rows_local_blocks * kRows * Dp * 4;
-  w.rspart = o; o += (size_t)2 * Q * rows_local_blocks * kRows * 4;   // two column halves per chunk
+  w.rspart = o; o += (size_t)kColGroups * Q * rows_local_blocks * kRows * 4;   // one partial per column group and chunk
   w.total = o;
   return w;
 }
@@ -138,14 +138,14 @@ __global__ void mmd_pack_kernel(const float* __restrict__ X, int64_t N, int D, i
   }
 }
 // one warp per row, fixed summation order
-__global__ void mmd_norm_kernel(const float* __restrict__ X, int64_t N, int D, float* __restrict__ norms, int T) {
+__global__ void mmd_norm_kernel(const float* __restrict__ X, int64_t N, int D, float scale, float* __restrict__ norms, int T) {
   const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (row >= (int64_t)T * kRows) return;
   float s = 0.f;
   if (row < N) for (int d = lane; d < D; d += 32) { const float v = X[row * D + d]; s = fmaf(v, v, s); }
   s = warp_sum(s);
-  if (lane == 0) norms[row] = s;
+  if (lane == 0) norms[row] = s * scale;                 // RBF: |x|^2 * a_exp (the epilogue's ex2 argument), IMQ: |x|^2
 }
 
 // ---- work items ---------------------------------------------------------------------------------------------
@@ -206,6 +206,11 @@ __device__ __forceinline__ float ex2_approx(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+__device__ __forceinline__ float rcp_approx(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 __device__ __forceinline__ bool tile_live(const MmdShape& s, const TileD& t) { return (int64_t)t.jt * kCols < s.N; }
 
 // ---- main kernel ----------------------------------------------------------------------------------------------
@@ -262,38 +267,45 @@ mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ im
           const uint8_t* bimg = (t.bm ? imgPb : imgZb) + (size_t)t.jt * (2 * b_half);
           const float* nrm = (t.bm ? normP : normZ) + (size_t)t.jt * kCols;
           mbar_expect_tx(bar(2 + slot), 2 * b_half + kCols * 4);
-          bulk_g2s(sbase + L.B[slot], bimg, 2 * b_half, bar(2 + slot));      // hi + lo images of 64 rows, one copy
+          bulk_g2s(sbase + L.B[0] + slot * (2u * b_half), bimg, 2 * b_half, bar(2 + slot));      // hi + lo images of 64 rows, one copy
           bulk_g2s(sbase + L.norms + (nb % kNormRing) * kCols * 4, nrm, kCols * 4, bar(2 + slot));
           ++nb;
         }
       }
     }
   } else if (warp == kMmaWarp) {
-    // ===== MMA issuer =====
-    if (lane == 0) {
+    // ===== MMA issuer: the whole warp runs the loop converged (operands stay in uniform registers), one elected
+    // lane issues =====
+    {
+      const uint32_t leader = elect_one();
       const uint32_t idesc1 = idesc_bf16(kRows, kCols, 0, 0);       // S = A(K-major) . B(K-major)^T
       const uint32_t idesc2 = idesc_bf16(kRows, s.Dp, 0, 1);        // O += Kmat(K-major) . B(MN-major)
       const uint32_t a_lbo = kRows * 16, b_lbo = kCols * 16;
+      const uint64_t a_step = (2u * a_lbo) >> 4, b_step = (2u * b_lbo) >> 4, b2_step = 256u >> 4;
+      const int ksteps1 = s.Dp / 16;
       uint32_t nb = 0, ns = 0, nk = 0, n_grad_items = 0;
       int iter = 0;
+      const uint64_t da_hi = smem_desc(sbase + L.A, a_lbo, 128), da_lo = smem_desc(sbase + L.A + a_half, a_lbo, 128);
       auto gemm1 = [&](uint32_t slot) {
         mbar_wait(bar(2 + slot), (nb / kBStages) & 1);
         const uint32_t sb = ns & 1;
         if (ns >= 2) mbar_wait(bar(10 + sb), ((ns >> 1) - 1) & 1);
         fence_after_sync();
-        const uint32_t a_hi = sbase + L.A, a_lo = a_hi + a_half;
-        const uint32_t b_hi = sbase + L.B[slot], b_lo = b_hi + b_half;
+        const uint32_t b_hi = sbase + L.B[0] + slot * (2u * b_half);
+        const uint64_t db_hi = smem_desc(b_hi, b_lbo, 128), db_lo = smem_desc(b_hi + b_half, b_lbo, 128);
         uint32_t acc = 0;
 #pragma unroll
         for (int pass = 0; pass < PASSES; ++pass) {
-          const uint32_t a0 = pass == 1 ? a_lo : a_hi, b0 = pass == 2 ? b_lo : b_hi;
-          for (int k = 0; k < s.Dp / 16; ++k) {
-            mma_bf16(tmem_S + sb * kCols, smem_desc(a0 + k * 2 * a_lbo, a_lbo, 128),
-                     smem_desc(b0 + k * 2 * b_lbo, b_lbo, 128), idesc1, acc);
+          uint64_t da = pass == 1 ? da_lo : da_hi, db = pass == 2 ? db_lo : db_hi;
+#pragma unroll 4
+          for (int k = 0; k < ksteps1; ++k) {
+            mma_bf16_if(leader, tmem_S + sb * kCols, da, db, idesc1, acc);
             acc = 1;
+            da += a_step;
+            db += b_step;
           }
         }
-        mma_commit(bar(8 + sb));
+        mma_commit_if(leader, bar(8 + sb));
         ++ns;
       };
       for (int idx = blockIdx.x; idx < n_items; idx += gridDim.x, ++iter) {
@@ -307,55 +319,67 @@ mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ im
         int issued1 = 0;
         for (; issued1 < 2 && issued1 < live; ++issued1) {
           gemm1((nb0 + issued1) % kBStages);
-          if (!it.grad) mma_commit(bar(5 + (nb0 + issued1) % kBStages));
+          if (!it.grad) mma_commit_if(leader, bar(5 + (nb0 + issued1) % kBStages));
           ++nb;
         }
         uint32_t oacc = 0;
+        int ug = it.u0;                                      // cursor over the tile sequence: kind of the j-th live tile
         for (int j = 0; j < live; ++j) {
           if (it.grad) {
             const uint32_t slot = (nb0 + j) % kBStages, kb = nk & 1;
+            TileD tg = get_tile(s, it, ug);
+            while (!tile_live(s, tg)) tg = get_tile(s, it, ++ug);
+            ++ug;
+            const uint32_t neg_a = tg.kind == 1 ? (1u << 13) : 0u;           // k(z, prior) enters with a minus sign
             mbar_wait(bar(12 + kb), (nk >> 1) & 1);
             if (j == 0 && n_grad_items > 0) mbar_wait(bar(17), (n_grad_items - 1) & 1);
             fence_after_sync();
-            const uint32_t k_hi = sbase + L.Kmat[kb], k_lo = k_hi + kRows * kCols * 2;
-            const uint32_t b_hi = sbase + L.B[slot], b_lo = b_hi + b_half;
+            const uint32_t k_hi = sbase + L.Kmat[0] + kb * (2u * kRows * kCols * 2u);
+            const uint32_t b_hi = sbase + L.B[0] + slot * (2u * b_half);
+            // A: K-major (K = column index), 128 rows ; B: MN-major (N = latent dim chunks, K = rows of the stage)
+            const uint64_t dk_hi = smem_desc(k_hi, a_lbo, 128), dk_lo = smem_desc(k_hi + kRows * kCols * 2, a_lbo, 128);
+            const uint64_t db_hi = smem_desc(b_hi, 128, b_lbo), db_lo = smem_desc(b_hi + b_half, 128, b_lbo);
 #pragma unroll
             for (int pass = 0; pass < PASSES; ++pass) {
-              const uint32_t a0 = pass == 1 ? k_lo : k_hi, b0 = pass == 2 ? b_lo : b_hi;
+              uint64_t da = pass == 1 ? dk_lo : dk_hi, db = pass == 2 ? db_lo : db_hi;
+#pragma unroll
               for (int k = 0; k < kCols / 16; ++k) {
-                // A: K-major (K = column index), 128 rows ; B: MN-major (N = latent dim chunks, K = rows of the stage)
-                mma_bf16(tmem_O, smem_desc(a0 + k * 2 * a_lbo, a_lbo, 128),
-                         smem_desc(b0 + k * 16 * 16, 128, b_lbo), idesc2, oacc);
+                mma_bf16_if(leader, tmem_O, da, db, idesc2 | neg_a, oacc);
                 oacc = 1;
+                da += a_step;
+                db += b2_step;
               }
             }
-            mma_commit(bar(5 + slot));
-            mma_commit(bar(14 + kb));
+            mma_commit_if(leader, bar(5 + slot));
+            mma_commit_if(leader, bar(14 + kb));
             ++nk;
           }
           if (issued1 < live) {
             gemm1((nb0 + issued1) % kBStages);
-            if (!it.grad) mma_commit(bar(5 + (nb0 + issued1) % kBStages));
+            if (!it.grad) mma_commit_if(leader, bar(5 + (nb0 + issued1) % kBStages));
             ++nb;
             ++issued1;
           }
         }
-        if (it.grad && live > 0) { mma_commit(bar(16)); ++n_grad_items; }
-        mma_commit(bar(1));
+        if (it.grad && live > 0) { mma_commit_if(leader, bar(16)); ++n_grad_items; }
+        mma_commit_if(leader, bar(1));
       }
     }
   } else {
-    // ===== epilogue: 8 warps = 4 TMEM lane quadrants x 2 column halves (32 of the 64 tile columns each) =====
+    // ===== epilogue: 16 warps = 4 TMEM lane quadrants x 4 column groups (16 of the 64 tile columns each); four warps
+    // per scheduler hide the TMEM / MUFU / shared-memory latencies that two could not =====
     const int ew = warp & 3;                                  // TMEM lane quadrant (must equal warp id % 4)
-    const int h = warp >> 2;                                  // column half
+    const int cg = warp >> 2;                                 // column group
     const int t = ew * 32 + lane;                             // row within the block
     double acc_zz = 0.0, acc_pz = 0.0, acc_pp = 0.0;
     uint32_t ns = 0, nk = 0, nb = 0, n_grad_items = 0;
+    // RBF: norms arrive pre-scaled by a_exp, so ex2's argument is one FADD + one FFMA; IMQ: t = C + eps + d^2
+    const float s_coef = KT == 0 ? -2.f * s.a_exp : -2.f;
     for (int idx = blockIdx.x; idx < n_items; idx += gridDim.x) {
       const Item it = get_item(s, idx);
       const int64_t grow = (int64_t)it.i * kRows + t;
       const bool rvalid = grow < s.N;
-      const float nx = (it.grad ? normZ : normP)[grow];
+      const float nx = (it.grad ? normZ : normP)[grow] + (KT == 1 ? s.Ceps : 0.f);
       float rs = 0.f;
       int live = 0;
       for (int u = it.u0; u < it.u1; ++u) {
@@ -364,62 +388,59 @@ mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ im
         const uint32_t sb = ns & 1;
         mbar_wait(bar(8 + sb), (ns >> 1) & 1);
         fence_after_sync();
-        uint32_t rr[32];
-        tmem_ld32(tmem_S + ((uint32_t)(ew * 32) << 16) + sb * kCols + h * 32, rr);
-        tmem_ld_wait();
+        uint32_t rr[16];
+        tmem_ld16(tmem_S + ((uint32_t)(ew * 32) << 16) + sb * kCols + cg * 16, rr);
+        tmem_ld_wait16(rr);
         fence_before_sync();
         mbar_arrive(bar(10 + sb));                            // S buffer free: the next GEMM1 may start
         ++ns;
         ++live;
-        const float* ny = reinterpret_cast<const float*>(smem + L.norms + (nb % kNormRing) * kCols * 4) + h * 32;
-        const int64_t gcol0 = (int64_t)td.jt * kCols + h * 32;
-        const bool slow = td.diag || gcol0 + 32 > s.N || !rvalid;
-        const float sign = td.kind == 1 ? -1.f : 1.f;
-        float ksum = 0.f;
-        uint8_t* kh = smem + L.Kmat[nk & 1];
+        const float* ny = reinterpret_cast<const float*>(smem + L.norms + (nb % kNormRing) * kCols * 4) + cg * 16;
+        const int64_t gcol0 = (int64_t)td.jt * kCols + cg * 16;
+        const bool slow = td.diag || gcol0 + 16 > s.N || !rvalid;
+        float ksum = 0.f, csum = 0.f;                         // sum of k (value) and of the coefficient (gradient)
+        uint8_t* kh = smem + L.Kmat[0] + (nk & 1) * (2u * kRows * kCols * 2u);
         uint8_t* kl = kh + kRows * kCols * 2;
         if (it.grad && nk >= 2) mbar_wait(bar(14 + (nk & 1)), ((nk >> 1) - 1) & 1);
         const bool diag_excl = KT == 1 && td.diag;
 #pragma unroll
-        for (int c8 = 0; c8 < 32; c8 += 8) {
+        for (int c8 = 0; c8 < 16; c8 += 8) {
           float cv[8];
+          const float4 n0 = *reinterpret_cast<const float4*>(ny + c8), n1 = *reinterpret_cast<const float4*>(ny + c8 + 4);
+          const float nyv[8] = {n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, n1.z, n1.w};
 #pragma unroll
           for (int e = 0; e < 8; ++e) {
             const int c = c8 + e;
-            const float d2 = fmaxf(fmaf(-2.f, __uint_as_float(rr[c]), nx + ny[c]), 0.f);
-            float k, dk;
+            // no clamp of d^2 at 0: a rounding-level negative distance moves k by < 1e-9 relative
+            const float arg = fmaf(__uint_as_float(rr[c]), s_coef, nx + nyv[e]);
+            float k;
             if (KT == 0) {
-              k = ex2_approx(d2 * s.a_exp);
-              dk = k * s.dk_scale;
+              k = ex2_approx(arg);                            // exp(-d^2 / (2 D^2 z_var))
+              cv[e] = k;                                      // dk/dd^2 = k * dk_scale: the constant is applied in finalize
             } else {
-              k = __fdividef(s.C, s.Ceps + d2);
-              dk = k * k * s.dk_scale;
+              k = rcp_approx(arg);                            // k / C = 1 / (C + eps + d^2)
+              cv[e] = k * k;                                  // dk/dd^2 = -C * (k/C)^2
             }
-            cv[e] = dk * sign;
             if (slow) {                                       // warp-uniform except for rvalid (tail rows)
               const bool ok = rvalid && (gcol0 + c < s.N) && !(diag_excl && gcol0 + c == grow);
               k = ok ? k : 0.f;
               cv[e] = ok ? cv[e] : 0.f;
             }
             ksum += k;
-            rs += cv[e];
+            if (KT == 1) csum += cv[e];
           }
           if (it.grad) {
             uint32_t ph[4], pl[4];
 #pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              __nv_bfloat16 h0, l0, h1, l1;
-              split_bf16(cv[2 * e], h0, l0);
-              split_bf16(cv[2 * e + 1], h1, l1);
-              ph[e] = pack2(h0, h1);
-              pl[e] = pack2(l0, l1);
-            }
-            const uint32_t off = ((uint32_t)((h * 32 + c8) >> 3) * kRows + t) * 16;
+            for (int e = 0; e < 4; ++e) split_pair(cv[2 * e], cv[2 * e + 1], ph[e], pl[e]);
+            const uint32_t off = ((uint32_t)((cg * 16 + c8) >> 3) * kRows + t) * 16;
             *reinterpret_cast<uint4*>(kh + off) = make_uint4(ph[0], ph[1], ph[2], ph[3]);
             *reinterpret_cast<uint4*>(kl + off) = make_uint4(pl[0], pl[1], pl[2], pl[3]);
           }
         }
-        const double kw = (double)(ksum * td.weight);
+        if (KT == 0) csum = ksum;
+        rs += td.kind == 1 ? -csum : csum;                    // GEMM2 applies the same sign with the negate-A bit
+        const double kw = (double)(ksum * td.weight) * (KT == 1 ? (double)s.C : 1.0);
         if (td.kind == 0) acc_zz += kw; else if (td.kind == 1) acc_pz += kw; else acc_pp += kw;
         if (it.grad) {
           fence_proxy_async();
@@ -433,15 +454,16 @@ mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ im
         const size_t lrow = (size_t)(it.i - s.rb0) * kRows + t;
         const size_t nloc = (size_t)(s.rb1 - s.rb0) * kRows;
         float* op = Opart + ((size_t)q * nloc + lrow) * s.Dp;
-        rspart[((size_t)q * 2 + h) * nloc + lrow] = rs;
+        rspart[((size_t)q * kColGroups + cg) * nloc + lrow] = rs;
+        const int c0 = cg * 32;                               // this warp's 32-column chunk of O (Dp <= 128)
         if (live == 0) {                                      // chunk made only of column tiles beyond N
-          for (int e = h; e < s.Dp; e += 2) op[e] = 0.f;
+          for (int e = c0; e < c0 + 32 && e < s.Dp; ++e) op[e] = 0.f;
           continue;
         }
-        // O complete -> partial gradient rows to the workspace (32-column chunks alternate between the halves)
+        // O complete -> partial gradient rows to the workspace
         mbar_wait(bar(16), n_grad_items & 1);
         fence_after_sync();
-        for (int c0 = h * 32; c0 < s.Dp; c0 += 64) {
+        if (c0 < s.Dp) {
           uint32_t o[32];
           tmem_ld32(tmem_O + ((uint32_t)(ew * 32) << 16) + c0, o);
           tmem_ld_wait();
@@ -464,7 +486,7 @@ mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ im
     double* red = reinterpret_cast<double*>(smem + L.red);
     acc_zz = warp_sum(acc_zz); acc_pz = warp_sum(acc_pz); acc_pp = warp_sum(acc_pp);
     if (lane == 0) { red[warp * 3 + 0] = acc_zz; red[warp * 3 + 1] = acc_pz; red[warp * 3 + 2] = acc_pp; }
-    asm volatile("bar.sync 1, 256;" ::: "memory");
+    asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");
     if (threadIdx.x < 3) {
       double tot = 0.0;
       for (int w = 0; w < kEpiWarps; ++w) tot += red[w * 3 + threadIdx.x];
@@ -490,11 +512,10 @@ __global__ void mmd_finalize_kernel(const float* __restrict__ Z, MmdShape s, con
     const int d = (int)(g % s.D);
     float rs = 0.f, o = 0.f;
     for (int q = 0; q < s.Q; ++q) {
-      rs += rspart[(size_t)(2 * q) * nloc_pad + r];
-      rs += rspart[(size_t)(2 * q + 1) * nloc_pad + r];
+      for (int c = 0; c < kColGroups; ++c) rs += rspart[(size_t)(q * kColGroups + c) * nloc_pad + r];
       o += Opart[((size_t)q * nloc_pad + r) * s.Dp + d];
     }
-    grad[g] = fmaf(Z[(row0 + r) * s.D + d], rs, -o);
+    grad[g] = s.dk_scale * fmaf(Z[(row0 + r) * s.D + d], rs, -o);     // dk/dd^2 constant: -1/(2 D^2 z_var) | -C
   }
   if (blockIdx.x == 0 && threadIdx.x < 3) {
     double t = 0.0;
@@ -540,7 +561,7 @@ int make_shape(int64_t N, int64_t D, int kernel_type, float z_var, int passes, i
   s.a_exp = (float)(-1.4426950408889634 / sp);
   s.C = (float)(2.0 * (double)D * (double)z_var);
   s.Ceps = (float)(1e-7 + (double)s.C);
-  s.dk_scale = kernel_type == 0 ? (float)(-1.0 / sp) : -1.f / s.C;
+  s.dk_scale = kernel_type == 0 ? (float)(-1.0 / sp) : -s.C;      // applied once, in finalize
   return VK_OK;
 }
 
@@ -572,8 +593,9 @@ extern "C" int vk_mmd_fwd(const float* z, const float* prior, int64_t N, int64_t
   const int norm_blocks = (int)(((int64_t)s.T * kRows * 32 + 255) / 256);
   mmd_pack_kernel<<<pack_blocks, 256, 0, st>>>(z, N, (int)D, s.Dp, ws + w.imgZ, ws + w.imgZb, s.T);
   mmd_pack_kernel<<<pack_blocks, 256, 0, st>>>(prior, N, (int)D, s.Dp, ws + w.imgP, ws + w.imgPb, s.T);
-  mmd_norm_kernel<<<norm_blocks, 256, 0, st>>>(z, N, (int)D, (float*)(ws + w.normZ), s.T);
-  mmd_norm_kernel<<<norm_blocks, 256, 0, st>>>(prior, N, (int)D, (float*)(ws + w.normP), s.T);
+  const float nscale = kernel_type == 0 ? s.a_exp : 1.f;
+  mmd_norm_kernel<<<norm_blocks, 256, 0, st>>>(z, N, (int)D, nscale, (float*)(ws + w.normZ), s.T);
+  mmd_norm_kernel<<<norm_blocks, 256, 0, st>>>(prior, N, (int)D, nscale, (float*)(ws + w.normP), s.T);
   const MmdSmem L = mmd_smem(s.Dp);
   const int n_items = (s.rb1 - s.rb0) * (s.Q + 1);
   const int grid = n_items < sm_count() ? n_items : sm_count();

@@ -197,10 +197,14 @@ vq_fwd_kernel(const float* __restrict__ X, const float* __restrict__ E, const ui
     PROF_LAP(1)
     PROF_OUT("producer wait_empty/work", threadIdx.x == 0)
   } else if (warp == kMmaWarp) {
-    // ===== MMA issuer =====
-    if (lane == 0) {
-      mbar_expect_tx(bar(0), 2 * cb_img_bytes);
-      bulk_g2s(sbase + L.cb, cb_image, 2 * cb_img_bytes, bar(0));
+    // ===== MMA issuer: the warp stays converged (uniform-register operands), one elected lane issues =====
+    {
+      const uint32_t leader = elect_one();
+      if (leader) {
+        mbar_expect_tx(bar(0), 2 * cb_img_bytes);
+        bulk_g2s(sbase + L.cb, cb_image, 2 * cb_img_bytes, bar(0));
+      }
+      __syncwarp();
       mbar_wait(bar(0), 0);
       const uint32_t idesc = idesc_bf16(128, s.NC, 0, 0);
       const uint32_t a_lbo = kTileRows * 16, b_lbo = (uint32_t)s.Kp * 16;
@@ -233,18 +237,18 @@ vq_fwd_kernel(const float* __restrict__ X, const float* __restrict__ E, const ui
             uint64_t da = pass == 1 ? da_lo : da_hi, db = pass == 2 ? db_lo : db_hi;
 #pragma unroll 4
             for (int k = 0; k < ksteps; ++k) {
-              mma_bf16(d, da, db, idesc, acc);
+              mma_bf16_if(leader, d, da, db, idesc, acc);
               acc = 1;
               da += a_step;
               db += b_step;
             }
           }
-          mma_commit(bar(5 + buf));
+          mma_commit_if(leader, bar(5 + buf));
         }
-        mma_commit(bar(3 + st));                            // x stage free once every MMA of this tile has run
+        mma_commit_if(leader, bar(3 + st));                            // x stage free once every MMA of this tile has run
       }
       PROF_LAP(2)
-      PROF_OUT("mma wait_x/wait_tmem/issue", true)
+      PROF_OUT("mma wait_x/wait_tmem/issue", leader)
     }
   } else if (warp >= kProducerWarps + kOutputWarps) {
     // ===== argmin warps (highest warp ids: the scheduler favours them): first-index argmin over half of the codes, merge =====
