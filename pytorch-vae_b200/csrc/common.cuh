@@ -92,3 +92,15 @@ __device__ __forceinline__ bool last_block_ticket(unsigned int* counter, unsigne
 }
 
 }  // namespace vk
+
+// Per-role cycle counters (debug builds only: VK_NVCC_EXTRA=-DVK_ROLE_PROF): CTA 0 prints, for the first thread of
+// each role, the cycles spent in each lap class (waits vs work).
+#ifdef VK_ROLE_PROF
+#define PROF_DECL long long p_[4] = {0, 0, 0, 0}; long long t_ = clock64();
+#define PROF_LAP(i) { const long long n_ = clock64(); p_[i] += n_ - t_; t_ = n_; }
+#define PROF_OUT(name, cond) if (blockIdx.x == 0 && (cond)) printf("%s: %lld %lld %lld %lld\n", name, p_[0], p_[1], p_[2], p_[3]);
+#else
+#define PROF_DECL
+#define PROF_LAP(i)
+#define PROF_OUT(name, cond)
+#endif

@@ -232,8 +232,8 @@ mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ im
     mbar_init(bar(0), 1); mbar_init(bar(1), 1);
     for (int i = 0; i < kBStages; ++i) { mbar_init(bar(2 + i), 1); mbar_init(bar(5 + i), 1); }
     for (int i = 0; i < 2; ++i) {
-      mbar_init(bar(8 + i), 1); mbar_init(bar(10 + i), kEpiThreads);
-      mbar_init(bar(12 + i), kEpiThreads); mbar_init(bar(14 + i), 1);
+      mbar_init(bar(8 + i), 1); mbar_init(bar(10 + i), kEpiThreads / 2);      // one tile group per S / Kmat buffer use
+      mbar_init(bar(12 + i), kEpiThreads / 2); mbar_init(bar(14 + i), 1);
     }
     mbar_init(bar(16), 1); mbar_init(bar(17), kEpiThreads);
     mbar_fence_init();
@@ -286,10 +286,14 @@ mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ im
       uint32_t nb = 0, ns = 0, nk = 0, n_grad_items = 0;
       int iter = 0;
       const uint64_t da_hi = smem_desc(sbase + L.A, a_lbo, 128), da_lo = smem_desc(sbase + L.A + a_half, a_lbo, 128);
+      PROF_DECL
       auto gemm1 = [&](uint32_t slot) {
+        PROF_LAP(3)
         mbar_wait(bar(2 + slot), (nb / kBStages) & 1);
+        PROF_LAP(0)
         const uint32_t sb = ns & 1;
         if (ns >= 2) mbar_wait(bar(10 + sb), ((ns >> 1) - 1) & 1);
+        PROF_LAP(1)
         fence_after_sync();
         const uint32_t b_hi = sbase + L.B[0] + slot * (2u * b_half);
         const uint64_t db_hi = smem_desc(b_hi, b_lbo, 128), db_lo = smem_desc(b_hi + b_half, b_lbo, 128);
@@ -331,8 +335,10 @@ mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ im
             while (!tile_live(s, tg)) tg = get_tile(s, it, ++ug);
             ++ug;
             const uint32_t neg_a = tg.kind == 1 ? (1u << 13) : 0u;           // k(z, prior) enters with a minus sign
+            PROF_LAP(3)
             mbar_wait(bar(12 + kb), (nk >> 1) & 1);
             if (j == 0 && n_grad_items > 0) mbar_wait(bar(17), (n_grad_items - 1) & 1);
+            PROF_LAP(2)
             fence_after_sync();
             const uint32_t k_hi = sbase + L.Kmat[0] + kb * (2u * kRows * kCols * 2u);
             const uint32_t b_hi = sbase + L.B[0] + slot * (2u * b_half);
@@ -364,17 +370,23 @@ mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ im
         if (it.grad && live > 0) { mma_commit_if(leader, bar(16)); ++n_grad_items; }
         mma_commit_if(leader, bar(1));
       }
+      PROF_LAP(3)
+      PROF_OUT("mma wait_b/wait_s_empty/wait_k_full/issue", leader)
     }
   } else {
-    // ===== epilogue: 16 warps = 4 TMEM lane quadrants x 4 column groups (16 of the 64 tile columns each); four warps
-    // per scheduler hide the TMEM / MUFU / shared-memory latencies that two could not =====
+    // ===== epilogue: 16 warps = 2 tile groups x 4 TMEM lane quadrants x 2 column halves.  Group g takes the tiles
+    // that land in S buffer g, so two tiles are in the epilogue at once (four warps per scheduler to hide the TMEM /
+    // MUFU / shared-memory latencies) while every warp still amortises its per-tile bookkeeping over 32 columns =====
     const int ew = warp & 3;                                  // TMEM lane quadrant (must equal warp id % 4)
-    const int cg = warp >> 2;                                 // column group
+    const int h = (warp >> 2) & 1;                            // column half of the tile
+    const uint32_t grp = warp >> 3;                           // tile group == S buffer
+    const int cg = warp >> 2;                                 // slot of this warp's partial row sums / O chunk
     const int t = ew * 32 + lane;                             // row within the block
     double acc_zz = 0.0, acc_pz = 0.0, acc_pp = 0.0;
     uint32_t ns = 0, nk = 0, nb = 0, n_grad_items = 0;
     // RBF: norms arrive pre-scaled by a_exp, so ex2's argument is one FADD + one FFMA; IMQ: t = C + eps + d^2
     const float s_coef = KT == 0 ? -2.f * s.a_exp : -2.f;
+    PROF_DECL
     for (int idx = blockIdx.x; idx < n_items; idx += gridDim.x) {
       const Item it = get_item(s, idx);
       const int64_t grow = (int64_t)it.i * kRows + t;
@@ -385,70 +397,79 @@ mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ im
       for (int u = it.u0; u < it.u1; ++u) {
         const TileD td = get_tile(s, it, u);
         if (!tile_live(s, td)) continue;
-        const uint32_t sb = ns & 1;
-        mbar_wait(bar(8 + sb), (ns >> 1) & 1);
-        fence_after_sync();
-        uint32_t rr[16];
-        tmem_ld16(tmem_S + ((uint32_t)(ew * 32) << 16) + sb * kCols + cg * 16, rr);
-        tmem_ld_wait16(rr);
-        fence_before_sync();
-        mbar_arrive(bar(10 + sb));                            // S buffer free: the next GEMM1 may start
+        if ((ns & 1) == grp) {
+          PROF_LAP(1)
+          mbar_wait(bar(8 + grp), (ns >> 1) & 1);
+          PROF_LAP(0)
+          fence_after_sync();
+          uint32_t rr[2][16];
+          const uint32_t taddr = tmem_S + ((uint32_t)(ew * 32) << 16) + grp * kCols + h * 32;
+          tmem_ld16(taddr, rr[0]);
+          tmem_ld16(taddr + 16, rr[1]);
+          tmem_ld_wait16(rr[0]);
+          tmem_ld_wait16(rr[1]);
+          fence_before_sync();
+          mbar_arrive(bar(10 + grp));                         // S buffer free: the next GEMM1 into it may start
+          const float* ny = reinterpret_cast<const float*>(smem + L.norms + (nb % kNormRing) * kCols * 4) + h * 32;
+          const int64_t gcol0 = (int64_t)td.jt * kCols + h * 32;
+          const bool slow = td.diag || gcol0 + 32 > s.N || !rvalid;
+          float ksum = 0.f, csum = 0.f;                       // sum of k (value) and of the coefficient (gradient)
+          uint8_t* kh = smem + L.Kmat[0] + (nk & 1) * (2u * kRows * kCols * 2u);
+          uint8_t* kl = kh + kRows * kCols * 2;
+          PROF_LAP(1)
+          if (it.grad && nk >= 2) mbar_wait(bar(14 + (nk & 1)), ((nk >> 1) - 1) & 1);
+          PROF_LAP(2)
+          const bool diag_excl = KT == 1 && td.diag;
+#pragma unroll
+          for (int c8 = 0; c8 < 32; c8 += 8) {
+            float cv[8];
+            const float4 n0 = *reinterpret_cast<const float4*>(ny + c8), n1 = *reinterpret_cast<const float4*>(ny + c8 + 4);
+            const float nyv[8] = {n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, n1.z, n1.w};
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              const int c = c8 + e;
+              // no clamp of d^2 at 0: a rounding-level negative distance moves k by < 1e-9 relative
+              const float arg = fmaf(__uint_as_float(rr[c >> 4][c & 15]), s_coef, nx + nyv[e]);
+              float k;
+              if (KT == 0) {
+                k = ex2_approx(arg);                          // exp(-d^2 / (2 D^2 z_var))
+                cv[e] = k;                                    // dk/dd^2 = k * dk_scale: the constant is applied in finalize
+              } else {
+                k = rcp_approx(arg);                          // k / C = 1 / (C + eps + d^2)
+                cv[e] = k * k;                                // dk/dd^2 = -C * (k/C)^2
+              }
+              if (slow) {                                     // warp-uniform except for rvalid (tail rows)
+                const bool ok = rvalid && (gcol0 + c < s.N) && !(diag_excl && gcol0 + c == grow);
+                k = ok ? k : 0.f;
+                cv[e] = ok ? cv[e] : 0.f;
+              }
+              ksum += k;
+              if (KT == 1) csum += cv[e];
+            }
+            if (it.grad) {
+              uint32_t ph[4], pl[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e) split_pair(cv[2 * e], cv[2 * e + 1], ph[e], pl[e]);
+              const uint32_t off = ((uint32_t)((h * 32 + c8) >> 3) * kRows + t) * 16;
+              *reinterpret_cast<uint4*>(kh + off) = make_uint4(ph[0], ph[1], ph[2], ph[3]);
+              *reinterpret_cast<uint4*>(kl + off) = make_uint4(pl[0], pl[1], pl[2], pl[3]);
+            }
+          }
+          if (KT == 0) csum = ksum;
+          rs += td.kind == 1 ? -csum : csum;                  // GEMM2 applies the same sign with the negate-A bit
+          const double kw = (double)(ksum * td.weight) * (KT == 1 ? (double)s.C : 1.0);
+          if (td.kind == 0) acc_zz += kw; else if (td.kind == 1) acc_pz += kw; else acc_pp += kw;
+          if (it.grad) {
+            fence_proxy_async();
+            mbar_arrive(bar(12 + (nk & 1)));
+          }
+        }
         ++ns;
         ++live;
-        const float* ny = reinterpret_cast<const float*>(smem + L.norms + (nb % kNormRing) * kCols * 4) + cg * 16;
-        const int64_t gcol0 = (int64_t)td.jt * kCols + cg * 16;
-        const bool slow = td.diag || gcol0 + 16 > s.N || !rvalid;
-        float ksum = 0.f, csum = 0.f;                         // sum of k (value) and of the coefficient (gradient)
-        uint8_t* kh = smem + L.Kmat[0] + (nk & 1) * (2u * kRows * kCols * 2u);
-        uint8_t* kl = kh + kRows * kCols * 2;
-        if (it.grad && nk >= 2) mbar_wait(bar(14 + (nk & 1)), ((nk >> 1) - 1) & 1);
-        const bool diag_excl = KT == 1 && td.diag;
-#pragma unroll
-        for (int c8 = 0; c8 < 16; c8 += 8) {
-          float cv[8];
-          const float4 n0 = *reinterpret_cast<const float4*>(ny + c8), n1 = *reinterpret_cast<const float4*>(ny + c8 + 4);
-          const float nyv[8] = {n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, n1.z, n1.w};
-#pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            const int c = c8 + e;
-            // no clamp of d^2 at 0: a rounding-level negative distance moves k by < 1e-9 relative
-            const float arg = fmaf(__uint_as_float(rr[c]), s_coef, nx + nyv[e]);
-            float k;
-            if (KT == 0) {
-              k = ex2_approx(arg);                            // exp(-d^2 / (2 D^2 z_var))
-              cv[e] = k;                                      // dk/dd^2 = k * dk_scale: the constant is applied in finalize
-            } else {
-              k = rcp_approx(arg);                            // k / C = 1 / (C + eps + d^2)
-              cv[e] = k * k;                                  // dk/dd^2 = -C * (k/C)^2
-            }
-            if (slow) {                                       // warp-uniform except for rvalid (tail rows)
-              const bool ok = rvalid && (gcol0 + c < s.N) && !(diag_excl && gcol0 + c == grow);
-              k = ok ? k : 0.f;
-              cv[e] = ok ? cv[e] : 0.f;
-            }
-            ksum += k;
-            if (KT == 1) csum += cv[e];
-          }
-          if (it.grad) {
-            uint32_t ph[4], pl[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e) split_pair(cv[2 * e], cv[2 * e + 1], ph[e], pl[e]);
-            const uint32_t off = ((uint32_t)((cg * 16 + c8) >> 3) * kRows + t) * 16;
-            *reinterpret_cast<uint4*>(kh + off) = make_uint4(ph[0], ph[1], ph[2], ph[3]);
-            *reinterpret_cast<uint4*>(kl + off) = make_uint4(pl[0], pl[1], pl[2], pl[3]);
-          }
-        }
-        if (KT == 0) csum = ksum;
-        rs += td.kind == 1 ? -csum : csum;                    // GEMM2 applies the same sign with the negate-A bit
-        const double kw = (double)(ksum * td.weight) * (KT == 1 ? (double)s.C : 1.0);
-        if (td.kind == 0) acc_zz += kw; else if (td.kind == 1) acc_pz += kw; else acc_pp += kw;
-        if (it.grad) {
-          fence_proxy_async();
-          mbar_arrive(bar(12 + (nk & 1)));
-          ++nk;
-        }
+        if (it.grad) ++nk;
         ++nb;
       }
+      PROF_LAP(1)
       if (it.grad) {
         const int q = (idx % (s.Q + 1));
         const size_t lrow = (size_t)(it.i - s.rb0) * kRows + t;
@@ -481,7 +502,9 @@ mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ im
         mbar_arrive(bar(17));
         ++n_grad_items;
       }
+      PROF_LAP(3)
     }
+    PROF_OUT("epilogue wait_s_full/work/wait_k_empty/item_end", threadIdx.x == 0)
     // per-CTA sums (fixed order) -> workspace
     double* red = reinterpret_cast<double*>(smem + L.red);
     acc_zz = warp_sum(acc_zz); acc_pz = warp_sum(acc_pz); acc_pp = warp_sum(acc_pp);

@@ -26,18 +26,6 @@ using namespace tc;
 namespace {
 
 constexpr int kTileRows = 128;
-// Per-role cycle counters (debug builds only: VK_NVCC_EXTRA=-DVK_ROLE_PROF): CTA 0 prints, for the first thread of
-// each role, the cycles spent in each lap class (waits vs work).
-#ifdef VK_ROLE_PROF
-#define PROF_DECL long long p_[4] = {0, 0, 0, 0}; long long t_ = clock64();
-#define PROF_LAP(i) { const long long n_ = clock64(); p_[i] += n_ - t_; t_ = n_; }
-#define PROF_OUT(name, cond) if (blockIdx.x == 0 && (cond)) printf("%s: %lld %lld %lld %lld\n", name, p_[0], p_[1], p_[2], p_[3]);
-#else
-#define PROF_DECL
-#define PROF_LAP(i)
-#define PROF_OUT(name, cond)
-#endif
-
 constexpr int kProducerWarps = 8, kEpilogueWarps = 8, kOutputWarps = 8, kMmaWarp = 24, kParts = kEpilogueWarps / 4;
 constexpr int kVqThreads = 32 * (kMmaWarp + 1);   // warps 0-7 producers, 8-15 output, 16-23 argmin, 24 MMA
 
