@@ -31,8 +31,15 @@ namespace {
 
 constexpr int kRows = 128;       // row block (MMA M)
 constexpr int kCols = 64;        // column tile (GEMM1 N, GEMM2 K)
-constexpr int kBStages = 3;
+constexpr int kBStages = 4;
 constexpr int kNormRing = 8;
+// mbarriers
+constexpr int kBarAFull = 0, kBarAEmpty = 1, kBarBFull = 2, kBarBEmpty = kBarBFull + kBStages, kBarSFull = kBarBEmpty + kBStages,
+              kBarSEmpty = kBarSFull + 2, kBarKFull = kBarSEmpty + 2, kBarKEmpty = kBarKFull + 2, kBarOFull = kBarKEmpty + 2,
+              kBarOEmpty = kBarOFull + 1, kNumBars = kBarOEmpty + 1;
+// tensor memory map (512 columns): S 2 x 64 | O <= 128 | row-block operand hi, lo (Dp/2 columns each, two bf16 per
+// column) | coefficient tile hi, lo (32 columns each), double-buffered
+constexpr uint32_t kTmS = 0, kTmO = 128, kTmAhi = 256, kTmAlo = 320, kTmK = 384;
 constexpr int kEpiWarps = 16, kColGroups = kEpiWarps / 4, kTmaWarp = 16, kMmaWarp = 17;
 constexpr int kEpiThreads = 32 * kEpiWarps;
 constexpr int kMmdThreads = 32 * 18;  // warps 0-15 epilogue, warp 16 TMA, warp 17 MMA
@@ -55,7 +62,7 @@ __host__ __device__ inline int rup(int x, int m) { return (x + m - 1) / m * m; }
 __host__ __device__ inline uint32_t tile_img_bytes(int Dp) { return 2u * kRows * Dp * 2u; }   // hi + lo of 128 rows
 
 struct MmdWs {
-  size_t cta_sums, imgZ, imgP, imgZb, imgPb, normZ, normP, Opart, rspart, total;
+  size_t cta_sums, imgZb, imgPb, normZ, normP, Opart, rspart, total;
 };
 inline MmdWs mmd_ws(int64_t N, int D, int rows_local_blocks, int Q) {
   const int Dp = rup(D, 16);
@@ -64,9 +71,7 @@ inline MmdWs mmd_ws(int64_t N, int D, int rows_local_blocks, int Q) {
   size_t o = kWsHeader;
   w.cta_sums = o; o += (size_t)256 * 3 * sizeof(double);
   o = (o + 255) & ~(size_t)255;
-  w.imgZ = o; o += (size_t)T * tile_img_bytes(Dp);
-  w.imgP = o; o += (size_t)T * tile_img_bytes(Dp);
-  w.imgZb = o; o += (size_t)T * tile_img_bytes(Dp);      // same data as 64-row granules (B stages: one bulk copy each)
+  w.imgZb = o; o += (size_t)T * tile_img_bytes(Dp);      // bf16 hi/lo images in 64-row granules (column stages: one bulk copy each)
   w.imgPb = o; o += (size_t)T * tile_img_bytes(Dp);
   w.normZ = o; o += (size_t)T * kRows * 4;
   w.normP = o; o += (size_t)T * kRows * 4;
@@ -86,16 +91,14 @@ inline int pick_Q(int T, int row_blocks) {
 }
 
 struct MmdSmem {
-  uint32_t A, B[kBStages], Kmat[2], norms, bars, tmem, red, total;
+  uint32_t B, norms, bars, tmem, red, total;
 };
 __host__ __device__ inline MmdSmem mmd_smem(int Dp) {
   MmdSmem m;
   uint32_t o = 0;
-  m.A = o; o += tile_img_bytes(Dp);
-  for (int i = 0; i < kBStages; ++i) { m.B[i] = o; o += 2u * kCols * Dp * 2u; }
-  for (int i = 0; i < 2; ++i) { m.Kmat[i] = o; o += 2u * kRows * kCols * 2u; }
+  m.B = o; o += kBStages * 2u * kCols * Dp * 2u;             // column stages: hi + lo image of 64 rows each
   m.norms = o; o += kNormRing * kCols * 4u;   // deeper than the B ring: read by the epilogue after b_empty may have fired
-  m.bars = o; o += 24 * 8;
+  m.bars = o; o += kNumBars * 8;
   m.tmem = o; o += 16;
   m.red = o; o += kEpiWarps * 3 * 8;
   m.total = o;
@@ -103,8 +106,7 @@ __host__ __device__ inline MmdSmem mmd_smem(int Dp) {
 }
 
 // ---- pack: fp32 [N,D] -> image tiles [T][hi/lo][Dp/8][128][8] bf16 ; norms [T*128] fp32 ----------------------
-__global__ void mmd_pack_kernel(const float* __restrict__ X, int64_t N, int D, int Dp, uint8_t* __restrict__ img,
-                                uint8_t* __restrict__ imgB, int T) {
+__global__ void mmd_pack_kernel(const float* __restrict__ X, int64_t N, int D, int Dp, uint8_t* __restrict__ imgB, int T) {
   const int nkc = Dp / 8;
   const int64_t total = (int64_t)T * kRows * nkc;
   for (int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (int64_t)gridDim.x * blockDim.x) {
@@ -125,12 +127,7 @@ __global__ void mmd_pack_kernel(const float* __restrict__ X, int64_t N, int D, i
       ph[e] = pack2(h0, h1);
       pl[e] = pack2(l0, l1);
     }
-    const int64_t tile = row / kRows;
-    const int r = (int)(row % kRows);
-    uint8_t* base = img + tile * tile_img_bytes(Dp);
-    *reinterpret_cast<uint4*>(base + ((size_t)kc * kRows + r) * 16) = make_uint4(ph[0], ph[1], ph[2], ph[3]);
-    *reinterpret_cast<uint4*>(base + ((size_t)(nkc + kc) * kRows + r) * 16) = make_uint4(pl[0], pl[1], pl[2], pl[3]);
-    // 64-row granule copy of the same data: [granule][hi/lo][Dp/8][64][8]
+    // 64-row granules: [granule][hi/lo][Dp/8][64][8]
     uint8_t* gb = imgB + (row / kCols) * (tile_img_bytes(Dp) / 2);
     const int rb = (int)(row % kCols);
     *reinterpret_cast<uint4*>(gb + ((size_t)kc * kCols + rb) * 16) = make_uint4(ph[0], ph[1], ph[2], ph[3]);
@@ -214,11 +211,9 @@ __device__ __forceinline__ float rcp_approx(float x) {
 __device__ __forceinline__ bool tile_live(const MmdShape& s, const TileD& t) { return (int64_t)t.jt * kCols < s.N; }
 
 // ---- main kernel ----------------------------------------------------------------------------------------------
-// barriers: 0 a_full | 1 a_empty | 2..4 b_full | 5..7 b_empty | 8,9 s_full | 10,11 s_empty | 12,13 k_full |
-//           14,15 k_empty | 16 o_full | 17 o_empty
 template <int PASSES, int KT>
 __global__ void __launch_bounds__(kMmdThreads, 1)
-mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ imgP, const uint8_t* __restrict__ imgZb,
+mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, const uint8_t* __restrict__ imgZb,
                 const uint8_t* __restrict__ imgPb, const float* __restrict__ normZ,
                 const float* __restrict__ normP, MmdShape s, int n_items, float* __restrict__ Opart,
                 float* __restrict__ rspart, double* __restrict__ cta_sums) {
@@ -229,13 +224,13 @@ mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ im
   auto bar = [&](int i) { return sbase + L.bars + 8u * i; };
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + L.tmem);
   if (threadIdx.x == 0) {
-    mbar_init(bar(0), 1); mbar_init(bar(1), 1);
-    for (int i = 0; i < kBStages; ++i) { mbar_init(bar(2 + i), 1); mbar_init(bar(5 + i), 1); }
+    mbar_init(bar(kBarAFull), kEpiThreads); mbar_init(bar(kBarAEmpty), 1);
+    for (int i = 0; i < kBStages; ++i) { mbar_init(bar(kBarBFull + i), 1); mbar_init(bar(kBarBEmpty + i), 1); }
     for (int i = 0; i < 2; ++i) {
-      mbar_init(bar(8 + i), 1); mbar_init(bar(10 + i), kEpiThreads / 2);      // one tile group per S / Kmat buffer use
-      mbar_init(bar(12 + i), kEpiThreads / 2); mbar_init(bar(14 + i), 1);
+      mbar_init(bar(kBarSFull + i), 1); mbar_init(bar(kBarSEmpty + i), kEpiThreads / 2);      // one tile group per S / Kmat buffer use
+      mbar_init(bar(kBarKFull + i), kEpiThreads / 2); mbar_init(bar(kBarKEmpty + i), 1);
     }
-    mbar_init(bar(16), 1); mbar_init(bar(17), kEpiThreads);
+    mbar_init(bar(kBarOFull), 1); mbar_init(bar(kBarOEmpty), kEpiThreads);
     mbar_fence_init();
   }
   if (warp == kMmaWarp) tmem_alloc(smem_u32(tmem_slot), 512);
@@ -243,10 +238,8 @@ mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ im
   __syncthreads();
   fence_after_sync();
   const uint32_t tmem = *tmem_slot;
-  const uint32_t tmem_S = tmem, tmem_O = tmem + 128;        // S: 2 x 64 columns ; O: Dp (<=128) columns
-  const uint32_t a_bytes = tile_img_bytes(s.Dp);
+  const uint32_t tmem_S = tmem + kTmS, tmem_O = tmem + kTmO;
   const uint32_t b_half = (uint32_t)kCols * s.Dp * 2u;      // one hi (or lo) image of a 64-row stage
-  const uint32_t a_half = (uint32_t)kRows * s.Dp * 2u;
 
   if (warp == kTmaWarp) {
     // ===== TMA producer =====
@@ -255,20 +248,16 @@ mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ im
       int iter = 0;
       for (int idx = blockIdx.x; idx < n_items; idx += gridDim.x, ++iter) {
         const Item it = get_item(s, idx);
-        if (iter > 0) mbar_wait(bar(1), (iter - 1) & 1);
-        const uint8_t* aimg = (it.grad ? imgZ : imgP) + (size_t)it.i * a_bytes;
-        mbar_expect_tx(bar(0), a_bytes);
-        bulk_g2s(sbase + L.A, aimg, a_bytes, bar(0));
         for (int u = it.u0; u < it.u1; ++u) {
           const TileD t = get_tile(s, it, u);
           if (!tile_live(s, t)) continue;
           const uint32_t slot = nb % kBStages;
-          if (nb >= kBStages) mbar_wait(bar(5 + slot), ((nb / kBStages) - 1) & 1);
+          if (nb >= kBStages) mbar_wait(bar(kBarBEmpty + slot), ((nb / kBStages) - 1) & 1);
           const uint8_t* bimg = (t.bm ? imgPb : imgZb) + (size_t)t.jt * (2 * b_half);
           const float* nrm = (t.bm ? normP : normZ) + (size_t)t.jt * kCols;
-          mbar_expect_tx(bar(2 + slot), 2 * b_half + kCols * 4);
-          bulk_g2s(sbase + L.B[0] + slot * (2u * b_half), bimg, 2 * b_half, bar(2 + slot));      // hi + lo images of 64 rows, one copy
-          bulk_g2s(sbase + L.norms + (nb % kNormRing) * kCols * 4, nrm, kCols * 4, bar(2 + slot));
+          mbar_expect_tx(bar(kBarBFull + slot), 2 * b_half + kCols * 4);
+          bulk_g2s(sbase + L.B + slot * (2u * b_half), bimg, 2 * b_half, bar(kBarBFull + slot));      // hi + lo images of 64 rows, one copy
+          bulk_g2s(sbase + L.norms + (nb % kNormRing) * kCols * 4, nrm, kCols * 4, bar(kBarBFull + slot));
           ++nb;
         }
       }
@@ -280,41 +269,43 @@ mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ im
       const uint32_t leader = elect_one();
       const uint32_t idesc1 = idesc_bf16(kRows, kCols, 0, 0);       // S = A(K-major) . B(K-major)^T
       const uint32_t idesc2 = idesc_bf16(kRows, s.Dp, 0, 1);        // O += Kmat(K-major) . B(MN-major)
-      const uint32_t a_lbo = kRows * 16, b_lbo = kCols * 16;
-      const uint64_t a_step = (2u * a_lbo) >> 4, b_step = (2u * b_lbo) >> 4, b2_step = 256u >> 4;
+      const uint32_t b_lbo = kCols * 16;
+      const uint64_t b_step = (2u * b_lbo) >> 4, b2_step = 256u >> 4;
+      const uint32_t tmem_Ahi = tmem + kTmAhi, tmem_Alo = tmem + kTmAlo;
       const int ksteps1 = s.Dp / 16;
       uint32_t nb = 0, ns = 0, nk = 0, n_grad_items = 0;
       int iter = 0;
-      const uint64_t da_hi = smem_desc(sbase + L.A, a_lbo, 128), da_lo = smem_desc(sbase + L.A + a_half, a_lbo, 128);
       PROF_DECL
       auto gemm1 = [&](uint32_t slot) {
         PROF_LAP(3)
-        mbar_wait(bar(2 + slot), (nb / kBStages) & 1);
+        mbar_wait(bar(kBarBFull + slot), (nb / kBStages) & 1);
         PROF_LAP(0)
         const uint32_t sb = ns & 1;
-        if (ns >= 2) mbar_wait(bar(10 + sb), ((ns >> 1) - 1) & 1);
+        if (ns >= 2) mbar_wait(bar(kBarSEmpty + sb), ((ns >> 1) - 1) & 1);
         PROF_LAP(1)
         fence_after_sync();
-        const uint32_t b_hi = sbase + L.B[0] + slot * (2u * b_half);
+        const uint32_t b_hi = sbase + L.B + slot * (2u * b_half);
         const uint64_t db_hi = smem_desc(b_hi, b_lbo, 128), db_lo = smem_desc(b_hi + b_half, b_lbo, 128);
         uint32_t acc = 0;
 #pragma unroll
         for (int pass = 0; pass < PASSES; ++pass) {
-          uint64_t da = pass == 1 ? da_lo : da_hi, db = pass == 2 ? db_lo : db_hi;
+          uint32_t ta = pass == 1 ? tmem_Alo : tmem_Ahi;       // row-block operand from tensor memory: 8 columns per K=16
+          uint64_t db = pass == 2 ? db_lo : db_hi;
 #pragma unroll 4
           for (int k = 0; k < ksteps1; ++k) {
-            mma_bf16_if(leader, tmem_S + sb * kCols, da, db, idesc1, acc);
+            mma_bf16_ts_if(leader, tmem_S + sb * kCols, ta, db, idesc1, acc);
             acc = 1;
-            da += a_step;
+            ta += 8;
             db += b_step;
           }
         }
-        mma_commit_if(leader, bar(8 + sb));
+        mma_commit_if(leader, bar(kBarSFull + sb));
         ++ns;
       };
       for (int idx = blockIdx.x; idx < n_items; idx += gridDim.x, ++iter) {
         const Item it = get_item(s, idx);
-        mbar_wait(bar(0), iter & 1);
+        mbar_wait(bar(kBarAFull), iter & 1);
+        fence_after_sync();
         // live tiles of this item, in order
         int live = 0;
         for (int u = it.u0; u < it.u1; ++u) live += tile_live(s, get_tile(s, it, u)) ? 1 : 0;
@@ -323,7 +314,7 @@ mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ im
         int issued1 = 0;
         for (; issued1 < 2 && issued1 < live; ++issued1) {
           gemm1((nb0 + issued1) % kBStages);
-          if (!it.grad) mma_commit_if(leader, bar(5 + (nb0 + issued1) % kBStages));
+          if (!it.grad) mma_commit_if(leader, bar(kBarBEmpty + (nb0 + issued1) % kBStages));
           ++nb;
         }
         uint32_t oacc = 0;
@@ -336,39 +327,39 @@ mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ im
             ++ug;
             const uint32_t neg_a = tg.kind == 1 ? (1u << 13) : 0u;           // k(z, prior) enters with a minus sign
             PROF_LAP(3)
-            mbar_wait(bar(12 + kb), (nk >> 1) & 1);
-            if (j == 0 && n_grad_items > 0) mbar_wait(bar(17), (n_grad_items - 1) & 1);
+            mbar_wait(bar(kBarKFull + kb), (nk >> 1) & 1);
+            if (j == 0 && n_grad_items > 0) mbar_wait(bar(kBarOEmpty), (n_grad_items - 1) & 1);
             PROF_LAP(2)
             fence_after_sync();
-            const uint32_t k_hi = sbase + L.Kmat[0] + kb * (2u * kRows * kCols * 2u);
-            const uint32_t b_hi = sbase + L.B[0] + slot * (2u * b_half);
-            // A: K-major (K = column index), 128 rows ; B: MN-major (N = latent dim chunks, K = rows of the stage)
-            const uint64_t dk_hi = smem_desc(k_hi, a_lbo, 128), dk_lo = smem_desc(k_hi + kRows * kCols * 2, a_lbo, 128);
+            const uint32_t tk_hi = tmem + kTmK + kb * 64, tk_lo = tk_hi + 32;
+            const uint32_t b_hi = sbase + L.B + slot * (2u * b_half);
+            // A: coefficient tile in tensor memory (K = column index) ; B: MN-major (N = latent dims, K = rows of the stage)
             const uint64_t db_hi = smem_desc(b_hi, 128, b_lbo), db_lo = smem_desc(b_hi + b_half, 128, b_lbo);
 #pragma unroll
             for (int pass = 0; pass < PASSES; ++pass) {
-              uint64_t da = pass == 1 ? dk_lo : dk_hi, db = pass == 2 ? db_lo : db_hi;
+              uint32_t ta = pass == 1 ? tk_lo : tk_hi;
+              uint64_t db = pass == 2 ? db_lo : db_hi;
 #pragma unroll
               for (int k = 0; k < kCols / 16; ++k) {
-                mma_bf16_if(leader, tmem_O, da, db, idesc2 | neg_a, oacc);
+                mma_bf16_ts_if(leader, tmem_O, ta, db, idesc2 | neg_a, oacc);
                 oacc = 1;
-                da += a_step;
+                ta += 8;
                 db += b2_step;
               }
             }
-            mma_commit_if(leader, bar(5 + slot));
-            mma_commit_if(leader, bar(14 + kb));
+            mma_commit_if(leader, bar(kBarBEmpty + slot));
+            mma_commit_if(leader, bar(kBarKEmpty + kb));
             ++nk;
           }
           if (issued1 < live) {
             gemm1((nb0 + issued1) % kBStages);
-            if (!it.grad) mma_commit_if(leader, bar(5 + (nb0 + issued1) % kBStages));
+            if (!it.grad) mma_commit_if(leader, bar(kBarBEmpty + (nb0 + issued1) % kBStages));
             ++nb;
             ++issued1;
           }
         }
-        if (it.grad && live > 0) { mma_commit_if(leader, bar(16)); ++n_grad_items; }
-        mma_commit_if(leader, bar(1));
+        if (it.grad && live > 0) { mma_commit_if(leader, bar(kBarOFull)); ++n_grad_items; }
+        mma_commit_if(leader, bar(kBarAEmpty));
       }
       PROF_LAP(3)
       PROF_OUT("mma wait_b/wait_s_empty/wait_k_full/issue", leader)
@@ -383,7 +374,7 @@ mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ im
     const int cg = warp >> 2;                                 // slot of this warp's partial row sums / O chunk
     const int t = ew * 32 + lane;                             // row within the block
     double acc_zz = 0.0, acc_pz = 0.0, acc_pp = 0.0;
-    uint32_t ns = 0, nk = 0, nb = 0, n_grad_items = 0;
+    uint32_t ns = 0, nk = 0, nb = 0, n_grad_items = 0, item_iter = 0;
     // RBF: norms arrive pre-scaled by a_exp, so ex2's argument is one FADD + one FFMA; IMQ: t = C + eps + d^2
     const float s_coef = KT == 0 ? -2.f * s.a_exp : -2.f;
     PROF_DECL
@@ -394,65 +385,95 @@ mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ im
       const float nx = (it.grad ? normZ : normP)[grow] + (KT == 1 ? s.Ceps : 0.f);
       float rs = 0.f;
       int live = 0;
+      {
+        // this row block's operand -> tensor memory: fp32 row slice [cg*32, cg*32+32) split into bf16 hi / lo, two per
+        // column.  The previous item's MMAs must be finished with the old block first.
+        if (item_iter > 0) mbar_wait(bar(kBarAEmpty), (item_iter - 1) & 1);
+        fence_after_sync();
+        const float* xr = (it.grad ? Zf : Pf) + grow * s.D + cg * 32;
+        const uint32_t ta = tmem + ((uint32_t)(ew * 32) << 16) + cg * 16;
+#pragma unroll
+        for (int j8 = 0; j8 < 16; j8 += 8) {
+          uint32_t ah[8], al[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const int d = cg * 32 + 2 * (j8 + j);
+            const float a = (rvalid && d < s.D) ? __ldg(xr + 2 * (j8 + j)) : 0.f;
+            const float b = (rvalid && d + 1 < s.D) ? __ldg(xr + 2 * (j8 + j) + 1) : 0.f;
+            split_pair(a, b, ah[j], al[j]);
+          }
+          tmem_st8(ta + kTmAhi + j8, ah);
+          tmem_st8(ta + kTmAlo + j8, al);
+        }
+        tmem_st_wait();
+        fence_before_sync();
+        mbar_arrive(bar(kBarAFull));
+        ++item_iter;
+      }
       for (int u = it.u0; u < it.u1; ++u) {
         const TileD td = get_tile(s, it, u);
         if (!tile_live(s, td)) continue;
         if ((ns & 1) == grp) {
           PROF_LAP(1)
-          mbar_wait(bar(8 + grp), (ns >> 1) & 1);
+          mbar_wait(bar(kBarSFull + grp), (ns >> 1) & 1);
           PROF_LAP(0)
           fence_after_sync();
           uint32_t rr[2][16];
           const uint32_t taddr = tmem_S + ((uint32_t)(ew * 32) << 16) + grp * kCols + h * 32;
           tmem_ld16(taddr, rr[0]);
           tmem_ld16(taddr + 16, rr[1]);
-          tmem_ld_wait16(rr[0]);
-          tmem_ld_wait16(rr[1]);
-          fence_before_sync();
-          mbar_arrive(bar(10 + grp));                         // S buffer free: the next GEMM1 into it may start
           const float* ny = reinterpret_cast<const float*>(smem + L.norms + (nb % kNormRing) * kCols * 4) + h * 32;
           const int64_t gcol0 = (int64_t)td.jt * kCols + h * 32;
           const bool slow = td.diag || gcol0 + 32 > s.N || !rvalid;
           float ksum = 0.f, csum = 0.f;                       // sum of k (value) and of the coefficient (gradient)
-          uint8_t* kh = smem + L.Kmat[0] + (nk & 1) * (2u * kRows * kCols * 2u);
-          uint8_t* kl = kh + kRows * kCols * 2;
+          const uint32_t tk = tmem + ((uint32_t)(ew * 32) << 16) + kTmK + (nk & 1) * 64 + h * 16;
           PROF_LAP(1)
-          if (it.grad && nk >= 2) mbar_wait(bar(14 + (nk & 1)), ((nk >> 1) - 1) & 1);
+          if (it.grad && nk >= 2) mbar_wait(bar(kBarKEmpty + (nk & 1)), ((nk >> 1) - 1) & 1);
           PROF_LAP(2)
           const bool diag_excl = KT == 1 && td.diag;
 #pragma unroll
-          for (int c8 = 0; c8 < 32; c8 += 8) {
-            float cv[8];
-            const float4 n0 = *reinterpret_cast<const float4*>(ny + c8), n1 = *reinterpret_cast<const float4*>(ny + c8 + 4);
-            const float nyv[8] = {n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, n1.z, n1.w};
+          for (int hf = 0; hf < 2; ++hf) {
+            tmem_ld_wait16(rr[hf]);
+            if (hf == 1) {                                    // both halves are in registers: the next GEMM1 into this
+              fence_before_sync();                            // S buffer may start
+              mbar_arrive(bar(kBarSEmpty + grp));
+            }
+            uint32_t kh[8], kl[8];                            // 16 coefficients: 8 hi + 8 lo columns of the tile in TMEM
 #pragma unroll
-            for (int e = 0; e < 8; ++e) {
-              const int c = c8 + e;
-              // no clamp of d^2 at 0: a rounding-level negative distance moves k by < 1e-9 relative
-              const float arg = fmaf(__uint_as_float(rr[c >> 4][c & 15]), s_coef, nx + nyv[e]);
-              float k;
-              if (KT == 0) {
-                k = ex2_approx(arg);                          // exp(-d^2 / (2 D^2 z_var))
-                cv[e] = k;                                    // dk/dd^2 = k * dk_scale: the constant is applied in finalize
-              } else {
-                k = rcp_approx(arg);                          // k / C = 1 / (C + eps + d^2)
-                cv[e] = k * k;                                // dk/dd^2 = -C * (k/C)^2
+            for (int c8 = 0; c8 < 16; c8 += 8) {
+              float cv[8];
+              const float4 n0 = *reinterpret_cast<const float4*>(ny + hf * 16 + c8);
+              const float4 n1 = *reinterpret_cast<const float4*>(ny + hf * 16 + c8 + 4);
+              const float nyv[8] = {n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, n1.z, n1.w};
+#pragma unroll
+              for (int e = 0; e < 8; ++e) {
+                const int c = hf * 16 + c8 + e;
+                // no clamp of d^2 at 0: a rounding-level negative distance moves k by < 1e-9 relative
+                const float arg = fmaf(__uint_as_float(rr[hf][c8 + e]), s_coef, nx + nyv[e]);
+                float k;
+                if (KT == 0) {
+                  k = ex2_approx(arg);                        // exp(-d^2 / (2 D^2 z_var))
+                  cv[e] = k;                                  // dk/dd^2 = k * dk_scale: the constant is applied in finalize
+                } else {
+                  k = rcp_approx(arg);                        // k / C = 1 / (C + eps + d^2)
+                  cv[e] = k * k;                              // dk/dd^2 = -C * (k/C)^2
+                }
+                if (slow) {                                   // warp-uniform except for rvalid (tail rows)
+                  const bool ok = rvalid && (gcol0 + c < s.N) && !(diag_excl && gcol0 + c == grow);
+                  k = ok ? k : 0.f;
+                  cv[e] = ok ? cv[e] : 0.f;
+                }
+                ksum += k;
+                if (KT == 1) csum += cv[e];
               }
-              if (slow) {                                     // warp-uniform except for rvalid (tail rows)
-                const bool ok = rvalid && (gcol0 + c < s.N) && !(diag_excl && gcol0 + c == grow);
-                k = ok ? k : 0.f;
-                cv[e] = ok ? cv[e] : 0.f;
+              if (it.grad) {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) split_pair(cv[2 * e], cv[2 * e + 1], kh[(c8 >> 1) + e], kl[(c8 >> 1) + e]);
               }
-              ksum += k;
-              if (KT == 1) csum += cv[e];
             }
             if (it.grad) {
-              uint32_t ph[4], pl[4];
-#pragma unroll
-              for (int e = 0; e < 4; ++e) split_pair(cv[2 * e], cv[2 * e + 1], ph[e], pl[e]);
-              const uint32_t off = ((uint32_t)((h * 32 + c8) >> 3) * kRows + t) * 16;
-              *reinterpret_cast<uint4*>(kh + off) = make_uint4(ph[0], ph[1], ph[2], ph[3]);
-              *reinterpret_cast<uint4*>(kl + off) = make_uint4(pl[0], pl[1], pl[2], pl[3]);
+              tmem_st8(tk + hf * 8, kh);
+              tmem_st8(tk + 32 + hf * 8, kl);
             }
           }
           if (KT == 0) csum = ksum;
@@ -460,8 +481,9 @@ mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ im
           const double kw = (double)(ksum * td.weight) * (KT == 1 ? (double)s.C : 1.0);
           if (td.kind == 0) acc_zz += kw; else if (td.kind == 1) acc_pz += kw; else acc_pp += kw;
           if (it.grad) {
-            fence_proxy_async();
-            mbar_arrive(bar(12 + (nk & 1)));
+            tmem_st_wait();
+            fence_before_sync();
+            mbar_arrive(bar(kBarKFull + (nk & 1)));
           }
         }
         ++ns;
@@ -482,7 +504,7 @@ mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ im
           continue;
         }
         // O complete -> partial gradient rows to the workspace
-        mbar_wait(bar(16), n_grad_items & 1);
+        mbar_wait(bar(kBarOFull), n_grad_items & 1);
         fence_after_sync();
         if (c0 < s.Dp) {
           uint32_t o[32];
@@ -499,7 +521,7 @@ mmd_main_kernel(const uint8_t* __restrict__ imgZ, const uint8_t* __restrict__ im
           }
         }
         fence_before_sync();
-        mbar_arrive(bar(17));
+        mbar_arrive(bar(kBarOEmpty));
         ++n_grad_items;
       }
       PROF_LAP(3)
@@ -614,8 +636,8 @@ extern "C" int vk_mmd_fwd(const float* z, const float* prior, int64_t N, int64_t
   const int64_t pack_work = (int64_t)s.T * kRows * s.nkc;
   const int pack_blocks = (int)((pack_work + 255) / 256 < 148 * 16 ? (pack_work + 255) / 256 : 148 * 16);
   const int norm_blocks = (int)(((int64_t)s.T * kRows * 32 + 255) / 256);
-  mmd_pack_kernel<<<pack_blocks, 256, 0, st>>>(z, N, (int)D, s.Dp, ws + w.imgZ, ws + w.imgZb, s.T);
-  mmd_pack_kernel<<<pack_blocks, 256, 0, st>>>(prior, N, (int)D, s.Dp, ws + w.imgP, ws + w.imgPb, s.T);
+  mmd_pack_kernel<<<pack_blocks, 256, 0, st>>>(z, N, (int)D, s.Dp, ws + w.imgZb, s.T);
+  mmd_pack_kernel<<<pack_blocks, 256, 0, st>>>(prior, N, (int)D, s.Dp, ws + w.imgPb, s.T);
   const float nscale = kernel_type == 0 ? s.a_exp : 1.f;
   mmd_norm_kernel<<<norm_blocks, 256, 0, st>>>(z, N, (int)D, nscale, (float*)(ws + w.normZ), s.T);
   mmd_norm_kernel<<<norm_blocks, 256, 0, st>>>(prior, N, (int)D, nscale, (float*)(ws + w.normP), s.T);
@@ -626,7 +648,7 @@ extern "C" int vk_mmd_fwd(const float* z, const float* prior, int64_t N, int64_t
                           : (kernel_type == 0 ? mmd_main_kernel<1, 0> : mmd_main_kernel<1, 1>);
   if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total) != cudaSuccess)
     return check_launch("mmd_fwd (shared memory attribute)");
-  kern<<<grid, kMmdThreads, L.total, st>>>(ws + w.imgZ, ws + w.imgP, ws + w.imgZb, ws + w.imgPb, (const float*)(ws + w.normZ),
+  kern<<<grid, kMmdThreads, L.total, st>>>(z, prior, ws + w.imgZb, ws + w.imgPb, (const float*)(ws + w.normZ),
                                            (const float*)(ws + w.normP), s, n_items, (float*)(ws + w.Opart),
                                            (float*)(ws + w.rspart), (double*)(ws + w.cta_sums));
   rc = check_launch("mmd_main");
