@@ -21,6 +21,7 @@
 // Reference quirks kept: RBF = exp(-|x-y|^2 / (2 D^2 z_var)) averaged over the full N x N including the diagonal
 // (wae_mmd.py:164-167); IMQ = C / (1e-7 + C + |x-y|^2), C = 2 D z_var, summed with the diagonal removed from
 // all three terms, including k(prior_i, z_i) (wae_mmd.py:185-191).
+#include <type_traits>
 #include "common.cuh"
 #include "tc.cuh"
 
@@ -373,7 +374,8 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
     const uint32_t grp = warp >> 3;                           // tile group == S buffer
     const int cg = warp >> 2;                                 // slot of this warp's partial row sums / O chunk
     const int t = ew * 32 + lane;                             // row within the block
-    double acc_zz = 0.0, acc_pz = 0.0, acc_pp = 0.0;
+    double acc_zz = 0.0, acc_pz = 0.0, acc_pp = 0.0, acc_run = 0.0;   // acc_run: sums of the term run_kind, not yet flushed
+    int run_kind = -1;
     uint32_t ns = 0, nk = 0, nb = 0, n_grad_items = 0, item_iter = 0;
     // RBF: norms arrive pre-scaled by a_exp, so ex2's argument is one FADD + one FFMA; IMQ: t = C + eps + d^2
     const float s_coef = KT == 0 ? -2.f * s.a_exp : -2.f;
@@ -382,6 +384,7 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
       const Item it = get_item(s, idx);
       const int64_t grow = (int64_t)it.i * kRows + t;
       const bool rvalid = grow < s.N;
+      const bool row_tail = (int64_t)(it.i + 1) * kRows > s.N;     // this row block has rows beyond N
       const float nx = (it.grad ? normZ : normP)[grow] + (KT == 1 ? s.Ceps : 0.f);
       float rs = 0.f;
       int live = 0;
@@ -424,13 +427,17 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
           tmem_ld16(taddr + 16, rr[1]);
           const float* ny = reinterpret_cast<const float*>(smem + L.norms + (nb % kNormRing) * kCols * 4) + h * 32;
           const int64_t gcol0 = (int64_t)td.jt * kCols + h * 32;
-          const bool slow = td.diag || gcol0 + 32 > s.N || !rvalid;
+          // uniform across the warp (the two instances below contain .sync.aligned tcgen05 instructions)
+          const bool slow = td.diag || gcol0 + 32 > s.N || row_tail;
           float ksum = 0.f, csum = 0.f;                       // sum of k (value) and of the coefficient (gradient)
           const uint32_t tk = tmem + ((uint32_t)(ew * 32) << 16) + kTmK + (nk & 1) * 64 + h * 16;
           PROF_LAP(1)
           if (it.grad && nk >= 2) mbar_wait(bar(kBarKEmpty + (nk & 1)), ((nk >> 1) - 1) & 1);
           PROF_LAP(2)
           const bool diag_excl = KT == 1 && td.diag;
+          // interior tiles take the branch-free instance; diagonal / tail tiles the masked one
+          auto tile_math = [&](auto masked_c, auto grad_c) {
+            constexpr bool MASKED = decltype(masked_c)::value, GRAD = decltype(grad_c)::value;
 #pragma unroll
           for (int hf = 0; hf < 2; ++hf) {
             tmem_ld_wait16(rr[hf]);
@@ -458,7 +465,7 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
                   k = rcp_approx(arg);                        // k / C = 1 / (C + eps + d^2)
                   cv[e] = k * k;                              // dk/dd^2 = -C * (k/C)^2
                 }
-                if (slow) {                                   // warp-uniform except for rvalid (tail rows)
+                if (MASKED) {                                 // diagonal exclusion, tail rows / columns
                   const bool ok = rvalid && (gcol0 + c < s.N) && !(diag_excl && gcol0 + c == grow);
                   k = ok ? k : 0.f;
                   cv[e] = ok ? cv[e] : 0.f;
@@ -466,20 +473,30 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
                 ksum += k;
                 if (KT == 1) csum += cv[e];
               }
-              if (it.grad) {
+              if (GRAD) {
 #pragma unroll
                 for (int e = 0; e < 4; ++e) split_pair(cv[2 * e], cv[2 * e + 1], kh[(c8 >> 1) + e], kl[(c8 >> 1) + e]);
               }
             }
-            if (it.grad) {
+            if (GRAD) {
               tmem_st8(tk + hf * 8, kh);
               tmem_st8(tk + 32 + hf * 8, kl);
             }
           }
+          };
+          if (it.grad) {
+            if (slow) tile_math(std::true_type{}, std::true_type{}); else tile_math(std::false_type{}, std::true_type{});
+          } else {
+            if (slow) tile_math(std::true_type{}, std::false_type{}); else tile_math(std::false_type{}, std::false_type{});
+          }
           if (KT == 0) csum = ksum;
           rs += td.kind == 1 ? -csum : csum;                  // GEMM2 applies the same sign with the negate-A bit
-          const double kw = (double)(ksum * td.weight) * (KT == 1 ? (double)s.C : 1.0);
-          if (td.kind == 0) acc_zz += kw; else if (td.kind == 1) acc_pz += kw; else acc_pp += kw;
+          if (td.kind != run_kind) {                          // (warp-uniform, once or twice per item)
+            if (run_kind == 0) acc_zz += acc_run; else if (run_kind == 1) acc_pz += acc_run; else if (run_kind == 2) acc_pp += acc_run;
+            acc_run = 0.0;
+            run_kind = td.kind;
+          }
+          acc_run += (double)(ksum * td.weight);
           if (it.grad) {
             tmem_st_wait();
             fence_before_sync();
@@ -527,6 +544,8 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
       PROF_LAP(3)
     }
     PROF_OUT("epilogue wait_s_full/work/wait_k_empty/item_end", threadIdx.x == 0)
+    if (run_kind == 0) acc_zz += acc_run; else if (run_kind == 1) acc_pz += acc_run; else if (run_kind == 2) acc_pp += acc_run;
+    if (KT == 1) { acc_zz *= (double)s.C; acc_pz *= (double)s.C; acc_pp *= (double)s.C; }   // IMQ sums were of k / C
     // per-CTA sums (fixed order) -> workspace
     double* red = reinterpret_cast<double*>(smem + L.red);
     acc_zz = warp_sum(acc_zz); acc_pz = warp_sum(acc_pz); acc_pp = warp_sum(acc_pp);
