@@ -99,8 +99,17 @@ __device__ __forceinline__ bool last_block_ticket(unsigned int* counter, unsigne
 #define PROF_DECL long long p_[4] = {0, 0, 0, 0}; long long t_ = clock64();
 #define PROF_LAP(i) { const long long n_ = clock64(); p_[i] += n_ - t_; t_ = n_; }
 #define PROF_OUT(name, cond) if (blockIdx.x == 0 && (cond)) printf("%s: %lld %lld %lld %lld\n", name, p_[0], p_[1], p_[2], p_[3]);
+// event trace: clock of event `ev` of pipeline step `j` for steps [kTraceLo, kTraceLo + 8), printed by CTA 0
+#define TRACE_DECL(nev) long long tr_[nev][8]; for (int a_ = 0; a_ < nev; ++a_) for (int b_ = 0; b_ < 8; ++b_) tr_[a_][b_] = 0;
+#define TRACE(ev, j) { const int j_ = (int)(j) - 40; if (j_ >= 0 && j_ < 8) tr_[ev][j_] = clock64(); }
+#define TRACE_OUT(name, nev, cond) if (blockIdx.x == 0 && (cond)) for (int a_ = 0; a_ < nev; ++a_) \
+  printf("trace %s ev%d: %lld %lld %lld %lld %lld %lld %lld %lld\n", name, a_, tr_[a_][0], tr_[a_][1], tr_[a_][2], tr_[a_][3], \
+         tr_[a_][4], tr_[a_][5], tr_[a_][6], tr_[a_][7]);
 #else
 #define PROF_DECL
 #define PROF_LAP(i)
 #define PROF_OUT(name, cond)
+#define TRACE_DECL(nev)
+#define TRACE(ev, j)
+#define TRACE_OUT(name, nev, cond)
 #endif

@@ -277,7 +277,9 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
       uint32_t nb = 0, ns = 0, nk = 0, n_grad_items = 0;
       int iter = 0;
       PROF_DECL
+      TRACE_DECL(4)
       auto gemm1 = [&](uint32_t slot) {
+        TRACE(0, ns)
         PROF_LAP(3)
         mbar_wait(bar(kBarBFull + slot), (nb / kBStages) & 1);
         PROF_LAP(0)
@@ -301,6 +303,7 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
           }
         }
         mma_commit_if(leader, bar(kBarSFull + sb));
+        TRACE(1, ns)
         ++ns;
       };
       for (int idx = blockIdx.x; idx < n_items; idx += gridDim.x, ++iter) {
@@ -311,7 +314,7 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
         int live = 0;
         for (int u = it.u0; u < it.u1; ++u) live += tile_live(s, get_tile(s, it, u)) ? 1 : 0;
         const uint32_t nb0 = nb;
-        // software pipeline: G1(0), G1(1), then for each j: G2(j), G1(j+2)
+        // software pipeline: G1(0), G1(1), then for each j: G1(j+2), G2(j)
         int issued1 = 0;
         for (; issued1 < 2 && issued1 < live; ++issued1) {
           gemm1((nb0 + issued1) % kBStages);
@@ -321,6 +324,14 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
         uint32_t oacc = 0;
         int ug = it.u0;                                      // cursor over the tile sequence: kind of the j-th live tile
         for (int j = 0; j < live; ++j) {
+          // G1(j+2) goes first: its S buffer was freed as soon as the epilogue had tile j in registers, so the distance
+          // GEMM of tile j+2 runs while the epilogue is still computing the coefficients G2(j) waits for
+          if (issued1 < live) {
+            gemm1((nb0 + issued1) % kBStages);
+            if (!it.grad) mma_commit_if(leader, bar(kBarBEmpty + (nb0 + issued1) % kBStages));
+            ++nb;
+            ++issued1;
+          }
           if (it.grad) {
             const uint32_t slot = (nb0 + j) % kBStages, kb = nk & 1;
             TileD tg = get_tile(s, it, ug);
@@ -331,6 +342,7 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
             mbar_wait(bar(kBarKFull + kb), (nk >> 1) & 1);
             if (j == 0 && n_grad_items > 0) mbar_wait(bar(kBarOEmpty), (n_grad_items - 1) & 1);
             PROF_LAP(2)
+            TRACE(2, nk)
             fence_after_sync();
             const uint32_t tk_hi = tmem + kTmK + kb * 64, tk_lo = tk_hi + 32;
             const uint32_t b_hi = sbase + L.B + slot * (2u * b_half);
@@ -350,13 +362,8 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
             }
             mma_commit_if(leader, bar(kBarBEmpty + slot));
             mma_commit_if(leader, bar(kBarKEmpty + kb));
+            TRACE(3, nk)
             ++nk;
-          }
-          if (issued1 < live) {
-            gemm1((nb0 + issued1) % kBStages);
-            if (!it.grad) mma_commit_if(leader, bar(kBarBEmpty + (nb0 + issued1) % kBStages));
-            ++nb;
-            ++issued1;
           }
         }
         if (it.grad && live > 0) { mma_commit_if(leader, bar(kBarOFull)); ++n_grad_items; }
@@ -364,6 +371,7 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
       }
       PROF_LAP(3)
       PROF_OUT("mma wait_b/wait_s_empty/wait_k_full/issue", leader)
+      TRACE_OUT("mma g1_start/g1_issued/g2_kfull/g2_issued", 4, leader)
     }
   } else {
     // ===== epilogue: 16 warps = 2 tile groups x 4 TMEM lane quadrants x 2 column halves.  Group g takes the tiles
@@ -380,6 +388,7 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
     // RBF: norms arrive pre-scaled by a_exp, so ex2's argument is one FADD + one FFMA; IMQ: t = C + eps + d^2
     const float s_coef = KT == 0 ? -2.f * s.a_exp : -2.f;
     PROF_DECL
+    TRACE_DECL(3)
     for (int idx = blockIdx.x; idx < n_items; idx += gridDim.x) {
       const Item it = get_item(s, idx);
       const int64_t grow = (int64_t)it.i * kRows + t;
@@ -420,6 +429,7 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
           PROF_LAP(1)
           mbar_wait(bar(kBarSFull + grp), (ns >> 1) & 1);
           PROF_LAP(0)
+          TRACE(0, ns)
           fence_after_sync();
           uint32_t rr[2][16];
           const uint32_t taddr = tmem_S + ((uint32_t)(ew * 32) << 16) + grp * kCols + h * 32;
@@ -431,9 +441,6 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
           const bool slow = td.diag || gcol0 + 32 > s.N || row_tail;
           float ksum = 0.f, csum = 0.f;                       // sum of k (value) and of the coefficient (gradient)
           const uint32_t tk = tmem + ((uint32_t)(ew * 32) << 16) + kTmK + (nk & 1) * 64 + h * 16;
-          PROF_LAP(1)
-          if (it.grad && nk >= 2) mbar_wait(bar(kBarKEmpty + (nk & 1)), ((nk >> 1) - 1) & 1);
-          PROF_LAP(2)
           const bool diag_excl = KT == 1 && td.diag;
           // interior tiles take the branch-free instance; diagonal / tail tiles the masked one
           auto tile_math = [&](auto masked_c, auto grad_c) {
@@ -479,6 +486,12 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
               }
             }
             if (GRAD) {
+              if (hf == 0) {                                  // the coefficient buffer is needed only now: G2 of the tile
+                PROF_LAP(1)                                   // two back has had the first half of this tile's math to finish
+                if (nk >= 2) mbar_wait(bar(kBarKEmpty + (nk & 1)), ((nk >> 1) - 1) & 1);
+                PROF_LAP(2)
+                TRACE(1, ns)
+              }
               tmem_st8(tk + hf * 8, kh);
               tmem_st8(tk + 32 + hf * 8, kl);
             }
@@ -502,6 +515,7 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
             fence_before_sync();
             mbar_arrive(bar(kBarKFull + (nk & 1)));
           }
+          TRACE(2, ns)
         }
         ++ns;
         ++live;
@@ -544,6 +558,7 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
       PROF_LAP(3)
     }
     PROF_OUT("epilogue wait_s_full/work/wait_k_empty/item_end", threadIdx.x == 0)
+    TRACE_OUT("epi s_full/k_empty/done", 3, threadIdx.x == 0 || threadIdx.x == 256)
     if (run_kind == 0) acc_zz += acc_run; else if (run_kind == 1) acc_pz += acc_run; else if (run_kind == 2) acc_pp += acc_run;
     if (KT == 1) { acc_zz *= (double)s.C; acc_pz *= (double)s.C; acc_pp *= (double)s.C; }   // IMQ sums were of k / C
     // per-CTA sums (fixed order) -> workspace
