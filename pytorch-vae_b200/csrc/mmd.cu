@@ -50,6 +50,7 @@ struct MmdShape {
   int64_t N;
   int D, Dp, nkc;       // latent dim, padded to 16, number of 8-element K chunks
   int T;                // 128-row tiles of the full matrix
+  int lz;               // live 64-column tiles per side: ceil(N / 64)
   int rb0, rb1;         // row-block range owned by this call
   int Q;                // column chunks per row block (gradient items)
   int kernel_type;      // 0 rbf, 1 imq
@@ -190,7 +191,8 @@ __device__ __forceinline__ TileD get_tile(const MmdShape& s, const Item& it, int
     t.diag = (t.jt >> 1) == it.i;
   } else {
     const int o = u >> 1;
-    const int j128 = (it.i + o) % s.T;
+    int j128 = it.i + o;                                  // o <= T/2 + 1: one conditional wrap instead of a modulo
+    if (j128 >= s.T) j128 -= s.T;
     t.bm = 1;
     t.jt = 2 * j128 + (u & 1);
     t.kind = 2;
@@ -209,7 +211,7 @@ __device__ __forceinline__ float rcp_approx(float x) {
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
-__device__ __forceinline__ bool tile_live(const MmdShape& s, const TileD& t) { return (int64_t)t.jt * kCols < s.N; }
+__device__ __forceinline__ bool tile_live(const MmdShape& s, const TileD& t) { return t.jt < s.lz; }
 
 // ---- main kernel ----------------------------------------------------------------------------------------------
 template <int PASSES, int KT>
@@ -322,7 +324,13 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
           ++nb;
         }
         uint32_t oacc = 0;
-        int ug = it.u0;                                      // cursor over the tile sequence: kind of the j-th live tile
+        // live z-side tiles of this chunk come first (tile sequence: [z tiles | prior tiles], dead tiles = columns >= N)
+        int nz_live = 0;
+        if (it.grad) {
+          const int zend = it.u1 < 2 * s.T ? it.u1 : 2 * s.T;
+          const int hi = zend < s.lz ? zend : s.lz;
+          nz_live = hi > it.u0 ? hi - it.u0 : 0;
+        }
         for (int j = 0; j < live; ++j) {
           // G1(j+2) goes first: its S buffer was freed as soon as the epilogue had tile j in registers, so the distance
           // GEMM of tile j+2 runs while the epilogue is still computing the coefficients G2(j) waits for
@@ -334,10 +342,7 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
           }
           if (it.grad) {
             const uint32_t slot = (nb0 + j) % kBStages, kb = nk & 1;
-            TileD tg = get_tile(s, it, ug);
-            while (!tile_live(s, tg)) tg = get_tile(s, it, ++ug);
-            ++ug;
-            const uint32_t neg_a = tg.kind == 1 ? (1u << 13) : 0u;           // k(z, prior) enters with a minus sign
+            const uint32_t neg_a = j >= nz_live ? (1u << 13) : 0u;           // k(z, prior) enters with a minus sign
             PROF_LAP(3)
             mbar_wait(bar(kBarKFull + kb), (nk >> 1) & 1);
             if (j == 0 && n_grad_items > 0) mbar_wait(bar(kBarOEmpty), (n_grad_items - 1) & 1);
@@ -391,9 +396,10 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
     TRACE_DECL(3)
     for (int idx = blockIdx.x; idx < n_items; idx += gridDim.x) {
       const Item it = get_item(s, idx);
-      const int64_t grow = (int64_t)it.i * kRows + t;
-      const bool rvalid = grow < s.N;
-      const bool row_tail = (int64_t)(it.i + 1) * kRows > s.N;     // this row block has rows beyond N
+      const int n32 = (int)s.N;                                // N <= 2^24: 32-bit index math in the tile loop
+      const int grow = it.i * kRows + t;
+      const bool rvalid = grow < n32;
+      const bool row_tail = (it.i + 1) * kRows > n32;     // this row block has rows beyond N
       const float nx = (it.grad ? normZ : normP)[grow] + (KT == 1 ? s.Ceps : 0.f);
       float rs = 0.f;
       int live = 0;
@@ -402,7 +408,7 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
         // column.  The previous item's MMAs must be finished with the old block first.
         if (item_iter > 0) mbar_wait(bar(kBarAEmpty), (item_iter - 1) & 1);
         fence_after_sync();
-        const float* xr = (it.grad ? Zf : Pf) + grow * s.D + cg * 32;
+        const float* xr = (it.grad ? Zf : Pf) + (int64_t)grow * s.D + cg * 32;
         const uint32_t ta = tmem + ((uint32_t)(ew * 32) << 16) + cg * 16;
 #pragma unroll
         for (int j8 = 0; j8 < 16; j8 += 8) {
@@ -436,9 +442,9 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
           tmem_ld16(taddr, rr[0]);
           tmem_ld16(taddr + 16, rr[1]);
           const float* ny = reinterpret_cast<const float*>(smem + L.norms + (nb % kNormRing) * kCols * 4) + h * 32;
-          const int64_t gcol0 = (int64_t)td.jt * kCols + h * 32;
+          const int gcol0 = td.jt * kCols + h * 32;
           // uniform across the warp (the two instances below contain .sync.aligned tcgen05 instructions)
-          const bool slow = td.diag || gcol0 + 32 > s.N || row_tail;
+          const bool slow = td.diag || gcol0 + 32 > n32 || row_tail;
           float ksum = 0.f, csum = 0.f;                       // sum of k (value) and of the coefficient (gradient)
           const uint32_t tk = tmem + ((uint32_t)(ew * 32) << 16) + kTmK + (nk & 1) * 64 + h * 16;
           const bool diag_excl = KT == 1 && td.diag;
@@ -473,7 +479,7 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
                   cv[e] = k * k;                              // dk/dd^2 = -C * (k/C)^2
                 }
                 if (MASKED) {                                 // diagonal exclusion, tail rows / columns
-                  const bool ok = rvalid && (gcol0 + c < s.N) && !(diag_excl && gcol0 + c == grow);
+                  const bool ok = rvalid && (gcol0 + c < n32) && !(diag_excl && gcol0 + c == grow);
                   k = ok ? k : 0.f;
                   cv[e] = ok ? cv[e] : 0.f;
                 }
@@ -632,6 +638,7 @@ int make_shape(int64_t N, int64_t D, int kernel_type, float z_var, int passes, i
              "mmd: row range [%lld,%lld) must be 128-aligned inside [0,%lld)", (long long)row_begin, (long long)row_end, (long long)N);
   s.N = N; s.D = (int)D; s.Dp = rup((int)D, 16); s.nkc = s.Dp / 8;
   s.T = (int)((N + kRows - 1) / kRows);
+  s.lz = (int)((N + kCols - 1) / kCols);
   s.rb0 = (int)(row_begin / kRows);
   s.rb1 = (int)((row_end + kRows - 1) / kRows);
   s.Q = pick_Q(s.T, s.rb1 - s.rb0);
