@@ -212,7 +212,9 @@ int vk_seg_sort(float* keys, uint32_t* perm_out, int64_t segments, int64_t n, vo
  * (columns 0 and 1 and entry [B-2,0] special, betatc_vae.py:179-182) are added to every latent dim before both
  * logsumexps (betatc_vae.py:185).  gamma_anneal = anneal_rate * gamma (host state, betatc_vae.py:196-200).
  *   out[4]   = { alpha*mi + (beta*tc + gamma_anneal*kld),  kld,  tc,  mi }       (means over the batch)
- *   lqz_out [B], lse_out [B, D]: log_q_z[i] and LSE_j(ld_ijd + lw_ij), saved for the backward
+ *   lqz_out [2B], lse_out [B, D]: log_q_z[i] (first B floats; the next B hold its fp32 rounding residual, so the
+ *   backward can rebuild the softmax weights exp(A_ij - log_q_z[i]) without ulp(|log_q_z|) noise) and
+ *   LSE_j(ld_ijd + lw_ij), saved for the backward
  * Backward: g_loss upstream of out[0] (NULL = 1); writes g_z, g_mu, g_lv [B, D] (overwritten).
  * The B^2 D densities each need their own exp (per-dimension LSE), so the kernels are MUFU/FP32 bound.
  * -------------------------------------------------------------------------*/

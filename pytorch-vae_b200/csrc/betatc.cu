@@ -151,7 +151,7 @@ tc_fwd_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const f
       lpz += -0.5f * kLog2Pi - 0.5f * z * z;
     }
     lpq = warp_sum(lpq); lqzx = warp_sum(lqzx); lpz = warp_sum(lpz);
-    if (lane == 0) lqz_out[i] = lqz;
+    if (lane == 0) { lqz_out[i] = lqz; lqz_out[p.B + i] = 0.f; }   // [B, 2B): fp32 residual (fast path only)
     t_qzx = lqzx; t_qz = lqz; t_pq = lpq; t_pz = lpz;
   }
   __shared__ double red[kW * 4];
@@ -312,6 +312,8 @@ int make_params(int64_t B, int64_t D, float M_N, float alpha, float beta, float 
   return VK_OK;
 }
 
+#include "betatc_tiled.cuh"
+
 }  // namespace
 }  // namespace vk
 
@@ -320,7 +322,7 @@ using namespace vk;
 extern "C" int64_t vk_tc_workspace_bytes(int64_t B, int64_t D) {
   if (B < 2 || D < 1) return -1;
   const int64_t blocks = (B + kW - 1) / kW;
-  return (int64_t)kWsHeader + blocks * 4 * 8 + 256 + 2 * B * D * 4;
+  return (int64_t)kWsHeader + blocks * 4 * 8 + 256 + 2 * B * D * 4 + 256 + B * 8;
 }
 
 extern "C" int vk_tc_fwd(const float* z, const float* mu, const float* log_var, int64_t B, int64_t D, float M_N,
@@ -337,7 +339,22 @@ extern "C" int vk_tc_fwd(const float* z, const float* mu, const float* log_var, 
   double* partials = (double*)(ws + kWsHeader);
   float* H = (float*)(ws + kWsHeader + (((size_t)blocks * 32 + 255) & ~(size_t)255));
   float* C0 = H + B * D;
-  tc_prep_kernel<<<(int)((B * D + 255) / 256 < 1184 ? (B * D + 255) / 256 : 1184), 256, 0, st>>>(log_var, B * D, H, C0);
+  const int prep_blocks = (int)((B * D + 255) / 256 < 1184 ? (B * D + 255) / 256 : 1184);
+  if (D <= 128) {
+    // lanes-own-dims path (betatc_tiled.cuh)
+    const int KD = D <= 32 ? 1 : (D <= 64 ? 2 : 4);
+    const int tb = (int)((B + tiled::kTW * tiled::kR - 1) / (tiled::kTW * tiled::kR));
+    const size_t tsm = tiled::smem_bytes(KD);
+    double* Cb = (double*)(((uintptr_t)(C0 + B * D) + 255) & ~(uintptr_t)255);
+    tiled::prep_kernel<<<prep_blocks, 256, 0, st>>>(log_var, p, H, C0);
+    tiled::cbar_kernel<<<(int)((B * 32 + 255) / 256), 256, 0, st>>>(C0, p, Cb);
+    auto kern = KD == 1 ? tiled::fwd_kernel<1> : (KD == 2 ? tiled::fwd_kernel<2> : tiled::fwd_kernel<4>);
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm) != cudaSuccess)
+      return check_launch("tc_fwd (shared memory attribute)");
+    kern<<<tb, tiled::kThreads, tsm, st>>>(z, mu, log_var, H, C0, Cb, p, lqz_out, lse_out, partials, (unsigned int*)ws, out);
+    return check_launch("tc_fwd");
+  }
+  tc_prep_kernel<<<prep_blocks, 256, 0, st>>>(log_var, B * D, H, C0);
   const size_t sm = tc_smem_fwd((int)D);
   if (cudaFuncSetAttribute(tc_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm) != cudaSuccess)
     return check_launch("tc_fwd (shared memory attribute)");
@@ -359,7 +376,24 @@ extern "C" int vk_tc_bwd(const float* z, const float* mu, const float* log_var, 
   const int blocks = (int)((B + kW - 1) / kW);
   float* H = (float*)(ws + kWsHeader + (((size_t)blocks * 32 + 255) & ~(size_t)255));
   float* C0 = H + B * D;
-  tc_prep_kernel<<<(int)((B * D + 255) / 256 < 1184 ? (B * D + 255) / 256 : 1184), 256, 0, st>>>(log_var, B * D, H, C0);
+  const int prep_blocks = (int)((B * D + 255) / 256 < 1184 ? (B * D + 255) / 256 : 1184);
+  if (D <= 128) {
+    const int KD = D <= 32 ? 1 : (D <= 64 ? 2 : 4);
+    const int tb = (int)((B + tiled::kTW * tiled::kR - 1) / (tiled::kTW * tiled::kR));
+    const size_t tsm = tiled::smem_bytes(KD);
+    double* Cb = (double*)(((uintptr_t)(C0 + B * D) + 255) & ~(uintptr_t)255);
+    tiled::prep_kernel<<<prep_blocks, 256, 0, st>>>(log_var, p, H, C0);
+    tiled::cbar_kernel<<<(int)((B * 32 + 255) / 256), 256, 0, st>>>(C0, p, Cb);
+    auto kr = KD == 1 ? tiled::bwd_rows_kernel<1> : (KD == 2 ? tiled::bwd_rows_kernel<2> : tiled::bwd_rows_kernel<4>);
+    auto kc = KD == 1 ? tiled::bwd_cols_kernel<1> : (KD == 2 ? tiled::bwd_cols_kernel<2> : tiled::bwd_cols_kernel<4>);
+    if (cudaFuncSetAttribute(kr, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm) != cudaSuccess ||
+        cudaFuncSetAttribute(kc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm) != cudaSuccess)
+      return check_launch("tc_bwd (shared memory attribute)");
+    kr<<<tb, tiled::kThreads, tsm, st>>>(z, mu, log_var, H, C0, Cb, lqz, lse, p, g_loss, g_z);
+    kc<<<tb, tiled::kThreads, tsm, st>>>(z, mu, log_var, H, C0, Cb, lqz, lse, p, g_loss, g_mu, g_lv);
+    return check_launch("tc_bwd");
+  }
+  tc_prep_kernel<<<prep_blocks, 256, 0, st>>>(log_var, B * D, H, C0);
   const size_t sm = tc_smem_bwd((int)D);
   if (cudaFuncSetAttribute(tc_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm) != cudaSuccess ||
       cudaFuncSetAttribute(tc_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm) != cudaSuccess)

@@ -1,0 +1,450 @@
+// K5 fast path (latent dim <= 128): lanes own latent dims, anchors are register-blocked.
+//
+// The first version of these sweeps gave one anchor row to a warp and spread the PARTNERS over the lanes, so every
+// (anchor, dim) sum needed a warp reduction per 128 partners and three shared-memory loads per density.  Here a warp
+// owns kR anchors and lane l owns dims l, l+32, ...: the per-(anchor, dim) sums (the per-dimension logsumexp of
+// betatc_vae.py:188, the gradient rows) never leave the lane, a staged partner value is used by kR anchors, and only
+// the per-pair sum over dims  A_ij = sum_d ld_ijd  crosses lanes -- sixteen pairs at a time through a transposing
+// butterfly (one shuffle per pair).  Everything is carried in log2 units (operands pre-scaled by log2 e) so each
+// exponential is one FADD + ex2.approx; the log importance weight of column j (betatc_vae.py:179-182) is folded into
+// the column's constant term, the single (B-2, 0) exception is a compile-time variant of the step taken only by the
+// warp and step that contain it.
+#pragma once
+#include <type_traits>
+
+namespace tiled {
+
+constexpr int kR = 4;          // anchors per warp
+constexpr int kP = 4;          // partners per step
+constexpr int kTW = 4;         // warps per CTA
+constexpr int kTR = 32;        // partner rows staged per tile
+constexpr int kThreads = 32 * kTW;
+constexpr float kLn2 = 0.6931471805599453f;
+
+// hs = 0.5 exp(-lv) log2e ; cs = (-0.5 (log 2pi + lv) + lw_j) log2e, lw_j = the generic-row log importance weight of column j
+__global__ void prep_kernel(const float* __restrict__ lv, TcParams p, float* __restrict__ hs, float* __restrict__ cs) {
+  const int64_t n = (int64_t)p.B * p.D;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float v = lv[i];
+    const int j = (int)(i / p.D);
+    const float lw = j == 0 ? p.lw_ds : (j == 1 ? p.lw_strat : p.lw_bm1);
+    hs[i] = 0.5f * expf(-v) * kLog2e;
+    cs[i] = (-0.5f * (kLog2Pi + v) + lw) * kLog2e;
+  }
+}
+
+// Cb_j = sum_d cs_jd in double: the part of  sum_d (ld_ijd + lw_j) log2e  that does not depend on the anchor.  Keeping it
+// out of the fp32 pair sums (which then hold only the positive quadratic part, a few tens) and combining per pair in
+// double keeps the softmax weights p_ij = exp(A_ij - log q(z_i)) at ~1e-6 instead of ulp(250).
+__global__ void cbar_kernel(const float* __restrict__ cs, TcParams p, double* __restrict__ cb) {
+  const int j = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
+  if (j >= p.B) return;
+  double t = 0.0;
+  for (int d = lane; d < p.D; d += 32) t += (double)cs[(size_t)j * p.D + d];
+  t = warp_sum(t);
+  if (lane == 0) cb[j] = t;
+}
+
+// 16 per-pair partial sums (index q = r * kP + pp) in every lane -> the complete sum of pair q = lane >> 1
+__device__ __forceinline__ float pair_reduce(const float (&a)[kR][kP], int lane) {
+  float v8[8], v4[4], v2[2];
+  const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4, b1 = lane & 2;
+#pragma unroll
+  for (int t = 0; t < 8; ++t) {
+    const float lo = a[t >> 2][t & 3], hi = a[(t + 8) >> 2][(t + 8) & 3];
+    v8[t] = (b4 ? hi : lo) + __shfl_xor_sync(0xFFFFFFFFu, b4 ? lo : hi, 16);
+  }
+#pragma unroll
+  for (int t = 0; t < 4; ++t) v4[t] = (b3 ? v8[t + 4] : v8[t]) + __shfl_xor_sync(0xFFFFFFFFu, b3 ? v8[t] : v8[t + 4], 8);
+#pragma unroll
+  for (int t = 0; t < 2; ++t) v2[t] = (b2 ? v4[t + 2] : v4[t]) + __shfl_xor_sync(0xFFFFFFFFu, b2 ? v4[t] : v4[t + 2], 4);
+  float v = (b1 ? v2[1] : v2[0]) + __shfl_xor_sync(0xFFFFFFFFu, b1 ? v2[0] : v2[1], 2);
+  v += __shfl_xor_sync(0xFFFFFFFFu, v, 1);
+  return v;
+}
+
+// stage kTR rows of a row-major [B, D] array into a [kTR][DP] tile: rows >= B get `dead`, padded dims of live rows 0
+template <int DP>
+__device__ __forceinline__ void stage(float* t, const float* __restrict__ src, int B, int D, int j0, float dead, float scale) {
+  for (int e = threadIdx.x; e < kTR * DP; e += kThreads) {
+    const int r = e / DP, c = e % DP;
+    const int j = j0 + r;
+    t[e] = j < B ? (c < D ? __ldg(src + (size_t)j * D + c) * scale : 0.f) : dead;
+  }
+}
+
+// ---- forward -----------------------------------------------------------------------------------------------------
+template <int KD>
+__global__ void __launch_bounds__(kThreads)
+fwd_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const float* __restrict__ LV,
+           const float* __restrict__ Hs, const float* __restrict__ Cs, const double* __restrict__ Cb, TcParams p,
+           float* __restrict__ lqz_out, float* __restrict__ lse_out, double* __restrict__ partials, unsigned int* ticket,
+           float* __restrict__ out) {
+  constexpr int DP = 32 * KD;
+  extern __shared__ __align__(16) float sm[];
+  double* Tb = reinterpret_cast<double*>(sm);        // [kTR] Cb of the staged partners (-inf for dead rows)
+  float* Tm = sm + 2 * kTR;
+  float* Th = Tm + kTR * DP;
+  float* Tc = Th + kTR * DP;
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int i0 = (blockIdx.x * kTW + w) * kR;
+  float z[kR][KD], m[kR][KD], s[kR][KD];
+#pragma unroll
+  for (int r = 0; r < kR; ++r)
+#pragma unroll
+    for (int k = 0; k < KD; ++k) {
+      const int d = lane + 32 * k;
+      z[r][k] = (i0 + r < p.B && d < p.D) ? Z[(size_t)(i0 + r) * p.D + d] : 0.f;
+      m[r][k] = -INFINITY;
+      s[r][k] = 0.f;
+    }
+  double rm = -INFINITY;                             // online row logsumexp of the pair slot q = lane >> 1
+  float rs = 0.f;
+  const float dcorr = (p.lw_strat - p.lw_ds) * kLog2e;  // pair (B-2, 0) uses lw_strat where column 0 folds lw_ds
+  const int r_special = p.B - 2 - i0;                // anchor slot of row B-2 in this warp (if in [0, kR))
+  const int pq = (lane >> 1) & 3;                    // partner slot of this lane's pair
+  for (int j0 = 0; j0 < p.B; j0 += kTR) {
+    __syncthreads();
+    stage<DP>(Tm, MU, p.B, p.D, j0, 0.f, 1.f);
+    stage<DP>(Th, Hs, p.B, p.D, j0, 0.f, 1.f);
+    stage<DP>(Tc, Cs, p.B, p.D, j0, -INFINITY, 1.f);   // dead partners: every density -inf
+    if (threadIdx.x < kTR) Tb[threadIdx.x] = j0 + threadIdx.x < p.B ? Cb[j0 + threadIdx.x] : -(double)INFINITY;
+    __syncthreads();
+    for (int jb = 0; jb < kTR && j0 + jb < p.B; jb += kP) {
+      auto step = [&](auto special_c) {
+        constexpr bool SPECIAL = decltype(special_c)::value;
+        float a[kR][kP];
+#pragma unroll
+        for (int r = 0; r < kR; ++r)
+#pragma unroll
+          for (int pp = 0; pp < kP; ++pp) a[r][pp] = 0.f;
+#pragma unroll
+        for (int k = 0; k < KD; ++k) {
+          float pm[kP], ph[kP], pc[kP];
+#pragma unroll
+          for (int pp = 0; pp < kP; ++pp) {
+            const int o = (jb + pp) * DP + lane + 32 * k;
+            pm[pp] = Tm[o]; ph[pp] = Th[o]; pc[pp] = Tc[o];
+          }
+#pragma unroll
+          for (int r = 0; r < kR; ++r) {
+            float e[kP];
+#pragma unroll
+            for (int pp = 0; pp < kP; ++pp) {
+              const float df = z[r][k] - pm[pp];
+              const float d2 = df * df;
+              e[pp] = fmaf(-d2, ph[pp], pc[pp]);                // (log N(z_id; mu_jd, var_jd) + lw_j) log2e
+              if (SPECIAL && pp == 0 && r == r_special && lane + 32 * k < p.D) e[pp] += dcorr;
+              a[r][pp] = fmaf(d2, ph[pp], a[r][pp]);            // quadratic part of the pair sum
+            }
+            const float bmax = fmaxf(fmaxf(e[0], e[1]), fmaxf(e[2], e[3]));
+            const float mn = fmaxf(fmaxf(m[r][k], bmax), -1e30f);
+            const float sum = (ex2f(e[0] - mn) + ex2f(e[1] - mn)) + (ex2f(e[2] - mn) + ex2f(e[3] - mn));
+            s[r][k] = fmaf(s[r][k], ex2f(m[r][k] - mn), sum);
+            m[r][k] = mn;
+          }
+        }
+        // A_ij + D lw_ij complete for the 16 pairs of this step: online logsumexp over j (betatc_vae.py:185-187)
+        double val = Tb[jb + pq] - (double)pair_reduce(a, lane);
+        if (SPECIAL && pq == 0 && (lane >> 3) == r_special) val += (double)p.D * (double)dcorr;
+        const double mn = fmax(fmax(rm, val), -1e300);
+        rs = fmaf(rs, ex2f((float)(rm - mn)), ex2f((float)(val - mn)));
+        rm = mn;
+      };
+      if (j0 + jb == 0 && r_special >= 0 && r_special < kR) step(std::true_type{}); else step(std::false_type{});
+    }
+  }
+  // merge the four partner slots of every anchor (lanes 8r .. 8r+7; the xor-1 neighbour is a duplicate)
+#pragma unroll
+  for (int o = 2; o <= 4; o <<= 1) {
+    const double om = __shfl_xor_sync(0xFFFFFFFFu, rm, o);
+    const float os = __shfl_xor_sync(0xFFFFFFFFu, rs, o);
+    const double mn = fmax(fmax(rm, om), -1e300);
+    rs = rs * ex2f((float)(rm - mn)) + os * ex2f((float)(om - mn));
+    rm = mn;
+  }
+  // log q(z_i), i = i0 + (lane >> 3), as an fp32 value plus its fp32 residual (the backward sweeps use both)
+  const double lqz_d = (rm + (double)log2f(rs)) * 0.6931471805599453;
+  const float lqz_mine = (float)lqz_d, lqz_res = (float)(lqz_d - (double)lqz_mine);
+  double t_qzx = 0.0, t_qz = 0.0, t_pq = 0.0, t_pz = 0.0;
+#pragma unroll
+  for (int r = 0; r < kR; ++r) {
+    const int i = i0 + r;
+    const float lqz = __shfl_sync(0xFFFFFFFFu, lqz_mine, 8 * r);
+    const float lqr = __shfl_sync(0xFFFFFFFFu, lqz_res, 8 * r);
+    float lpq = 0.f, lqzx = 0.f, lpz = 0.f;
+#pragma unroll
+    for (int k = 0; k < KD; ++k) {
+      const int d = lane + 32 * k;
+      if (i < p.B && d < p.D) {
+        const size_t o = (size_t)i * p.D + d;
+        const float l = (m[r][k] + log2f(s[r][k])) * kLn2;
+        lse_out[o] = l;
+        lpq += l;
+        const float v = LV[o], df = z[r][k] - MU[o];
+        lqzx += fmaf(-df * df, 0.5f * expf(-v), -0.5f * (kLog2Pi + v));
+        lpz += -0.5f * kLog2Pi - 0.5f * z[r][k] * z[r][k];
+      }
+    }
+    lpq = warp_sum(lpq); lqzx = warp_sum(lqzx); lpz = warp_sum(lpz);
+    if (i < p.B) {
+      if (lane == 0) { lqz_out[i] = lqz; lqz_out[p.B + i] = lqr; }
+      t_qzx += lqzx; t_qz += lqz; t_pq += lpq; t_pz += lpz;
+    }
+  }
+  __shared__ double red[kTW * 4];
+  if (lane == 0) { red[w * 4 + 0] = t_qzx; red[w * 4 + 1] = t_qz; red[w * 4 + 2] = t_pq; red[w * 4 + 3] = t_pz; }
+  __syncthreads();
+  if (threadIdx.x < 4) {
+    double t = 0.0;
+    for (int k = 0; k < kTW; ++k) t += red[k * 4 + threadIdx.x];
+    partials[(size_t)blockIdx.x * 4 + threadIdx.x] = t;
+  }
+  if (last_block_ticket(ticket, gridDim.x)) {
+    if (threadIdx.x < 4) {
+      double t = 0.0;
+      for (unsigned int b = 0; b < gridDim.x; ++b) t += ((volatile double*)partials)[(size_t)b * 4 + threadIdx.x];
+      red[threadIdx.x] = t / (double)p.B;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const float qzx = (float)red[0], qz = (float)red[1], pq = (float)red[2], pz = (float)red[3];
+      const float mi = qzx - qz, tc = qz - pq, kld = pq - pz;                 // betatc_vae.py:190-192 (means)
+      out[0] = p.alpha * mi + (p.beta * tc + p.gamma_anneal * kld);           // the latent part of betatc_vae.py:202-205
+      out[1] = kld;
+      out[2] = tc;
+      out[3] = mi;
+    }
+  }
+}
+
+// ---- backward, row sweep: d/dz_i -------------------------------------------------------------------------------------
+// L = (1/B) sum_i [ alpha lqzx_i + (beta - alpha) lqz_i + (ga - beta) lpq_i - ga lpz_i ],  ga = anneal * gamma
+//   d/d ld_ijd = [ (beta - alpha) p_ij + (ga - beta) r_ijd ] / B,   p = softmax_j(A), r = softmax_j(ld + lw) per d
+//   d ld_ijd / d z_id = -2 h_jd (z_id - mu_jd)
+template <int KD>
+__global__ void __launch_bounds__(kThreads)
+bwd_rows_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const float* __restrict__ LV,
+                const float* __restrict__ Hs, const float* __restrict__ Cs, const double* __restrict__ Cb,
+                const float* __restrict__ lqz, const float* __restrict__ lse, TcParams p, const float* __restrict__ g_loss,
+                float* __restrict__ g_z) {
+  constexpr int DP = 32 * KD;
+  extern __shared__ __align__(16) float sm[];
+  double* Tb = reinterpret_cast<double*>(sm);
+  float* Tm = sm + 2 * kTR;
+  float* Th = Tm + kTR * DP;
+  float* Tc = Th + kTR * DP;
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int i0 = (blockIdx.x * kTW + w) * kR;
+  const float g = g_loss ? *g_loss : 1.f;
+  const float invB = 1.f / (float)p.B;
+  const float cq = (p.beta - p.alpha) * invB * g, cp = (p.gamma_anneal - p.beta) * invB * g;
+  float z[kR][KD], l2[kR][KD], gz[kR][KD];
+#pragma unroll
+  for (int r = 0; r < kR; ++r)
+#pragma unroll
+    for (int k = 0; k < KD; ++k) {
+      const int d = lane + 32 * k;
+      const bool ok = i0 + r < p.B && d < p.D;
+      z[r][k] = ok ? Z[(size_t)(i0 + r) * p.D + d] : 0.f;
+      l2[r][k] = ok ? lse[(size_t)(i0 + r) * p.D + d] * kLog2e : 0.f;
+      gz[r][k] = 0.f;
+    }
+  // log q(z_i) (log2 units) of the anchor of this lane's pair slot q = lane >> 1
+  const int iq = i0 + (lane >> 3);
+  const int pq = (lane >> 1) & 3;
+  const double lqz2 = iq < p.B ? ((double)lqz[iq] + (double)lqz[p.B + iq]) * 1.4426950408889634 : (double)INFINITY;
+  const float dcorr = (p.lw_strat - p.lw_ds) * kLog2e;
+  const int r_special = p.B - 2 - i0;
+  for (int j0 = 0; j0 < p.B; j0 += kTR) {
+    __syncthreads();
+    stage<DP>(Tm, MU, p.B, p.D, j0, 0.f, 1.f);
+    stage<DP>(Th, Hs, p.B, p.D, j0, 0.f, 1.f);
+    stage<DP>(Tc, Cs, p.B, p.D, j0, -INFINITY, 1.f);
+    if (threadIdx.x < kTR) Tb[threadIdx.x] = j0 + threadIdx.x < p.B ? Cb[j0 + threadIdx.x] : -(double)INFINITY;
+    __syncthreads();
+    for (int jb = 0; jb < kTR && j0 + jb < p.B; jb += kP) {
+      auto step = [&](auto special_c) {
+        constexpr bool SPECIAL = decltype(special_c)::value;
+        float pm[KD][kP], ph[KD][kP], pc[KD][kP];
+        float a[kR][kP];
+#pragma unroll
+        for (int r = 0; r < kR; ++r)
+#pragma unroll
+          for (int pp = 0; pp < kP; ++pp) a[r][pp] = 0.f;
+#pragma unroll
+        for (int k = 0; k < KD; ++k) {
+#pragma unroll
+          for (int pp = 0; pp < kP; ++pp) {
+            const int o = (jb + pp) * DP + lane + 32 * k;
+            pm[k][pp] = Tm[o]; ph[k][pp] = Th[o]; pc[k][pp] = Tc[o];
+          }
+#pragma unroll
+          for (int r = 0; r < kR; ++r)
+#pragma unroll
+            for (int pp = 0; pp < kP; ++pp) {
+              const float df = z[r][k] - pm[k][pp];
+              a[r][pp] = fmaf(df * df, ph[k][pp], a[r][pp]);         // quadratic part of the pair sum
+            }
+        }
+        // softmax weight of (i, j) in log q(z_i), times its coefficient; dead partners / anchors give exactly 0
+        double x = (Tb[jb + pq] - (double)pair_reduce(a, lane)) - lqz2;
+        if (SPECIAL && pq == 0 && (lane >> 3) == r_special) x += (double)p.D * (double)dcorr;
+        const float wq = cq * ex2f((float)x);
+        float cqp[kR][kP];
+#pragma unroll
+        for (int r = 0; r < kR; ++r)
+#pragma unroll
+          for (int pp = 0; pp < kP; ++pp) cqp[r][pp] = __shfl_sync(0xFFFFFFFFu, wq, 2 * (r * kP + pp));
+#pragma unroll
+        for (int k = 0; k < KD; ++k)
+#pragma unroll
+          for (int r = 0; r < kR; ++r)
+#pragma unroll
+            for (int pp = 0; pp < kP; ++pp) {
+              const float df = z[r][k] - pm[k][pp];
+              const float t = ph[k][pp] * df;                        // h (z - mu) log2e
+              float e = fmaf(-df, t, pc[k][pp]);
+              if (SPECIAL && pp == 0 && r == r_special && lane + 32 * k < p.D) e += dcorr;
+              const float rr = ex2f(e - l2[r][k]);                   // softmax weight inside LSE_j[i, d]
+              const float cf = fmaf(cp, rr, cqp[r][pp]);             // dL / d ld_ijd
+              gz[r][k] = fmaf(-cf, t, gz[r][k]);
+            }
+      };
+      if (j0 + jb == 0 && r_special >= 0 && r_special < kR) step(std::true_type{}); else step(std::false_type{});
+    }
+  }
+  const float ca = p.alpha * invB * g, cz = p.gamma_anneal * invB * g;
+#pragma unroll
+  for (int r = 0; r < kR; ++r)
+#pragma unroll
+    for (int k = 0; k < KD; ++k) {
+      const int i = i0 + r, d = lane + 32 * k;
+      if (i < p.B && d < p.D) {
+        const size_t o = (size_t)i * p.D + d;
+        const float df = z[r][k] - MU[o];
+        const float t = expf(-LV[o]) * df;                           // 2 h (z - mu)
+        // off-diagonal sweep (t carried the factor log2e / 2) + diagonal terms: alpha/B d log q(z_i|x_i)/dz and
+        // -ga/B d log p(z_i)/dz = +ga/B z
+        g_z[o] = 2.f * kLn2 * gz[r][k] - ca * t + cz * z[r][k];
+      }
+    }
+}
+
+// ---- backward, column sweep: d/dmu_j, d/dlog_var_j -------------------------------------------------------------------
+//   d ld_ijd / d mu_jd = 2 h_jd (z_id - mu_jd) ;  d ld_ijd / d lv_jd = h_jd (z_id - mu_jd)^2 - 1/2
+template <int KD>
+__global__ void __launch_bounds__(kThreads)
+bwd_cols_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const float* __restrict__ LV,
+                const float* __restrict__ Hs, const float* __restrict__ Cs, const double* __restrict__ Cb,
+                const float* __restrict__ lqz, const float* __restrict__ lse, TcParams p, const float* __restrict__ g_loss,
+                float* __restrict__ g_mu, float* __restrict__ g_lv) {
+  constexpr int DP = 32 * KD;
+  extern __shared__ __align__(16) float sm[];
+  double* Tq = reinterpret_cast<double*>(sm);   // partner rows i: log q(z_i) (log2 units, double), z, LSE_j[i, d] (log2 units)
+  float* Tz = sm + 2 * kTR;
+  float* Tl = Tz + kTR * DP;
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int c0 = (blockIdx.x * kTW + w) * kR;        // first anchor column of this warp
+  const float g = g_loss ? *g_loss : 1.f;
+  const float invB = 1.f / (float)p.B;
+  const float cq = (p.beta - p.alpha) * invB * g, cp = (p.gamma_anneal - p.beta) * invB * g;
+  float mu[kR][KD], hs[kR][KD], cs[kR][KD], g0[kR][KD], g1[kR][KD];
+#pragma unroll
+  for (int r = 0; r < kR; ++r)
+#pragma unroll
+    for (int k = 0; k < KD; ++k) {
+      const int d = lane + 32 * k;
+      const bool ok = c0 + r < p.B && d < p.D;
+      const size_t o = (size_t)(c0 + r) * p.D + d;
+      mu[r][k] = ok ? MU[o] : 0.f;
+      hs[r][k] = ok ? Hs[o] : 0.f;
+      cs[r][k] = ok ? Cs[o] : 0.f;
+      g0[r][k] = 0.f; g1[r][k] = 0.f;
+    }
+  const float dcorr = (p.lw_strat - p.lw_ds) * kLog2e;
+  const int pq = (lane >> 1) & 3;                    // partner slot of this lane's pair
+  const bool anchor_dead = c0 + (lane >> 3) >= p.B;
+  const double cbq = anchor_dead ? 0.0 : Cb[c0 + (lane >> 3)];
+  for (int i0 = 0; i0 < p.B; i0 += kTR) {
+    __syncthreads();
+    stage<DP>(Tz, Z, p.B, p.D, i0, 0.f, 1.f);
+    stage<DP>(Tl, lse, p.B, p.D, i0, INFINITY, kLog2e);            // dead partners: softmax weight exactly 0
+    if (threadIdx.x < kTR) {
+      const int i = i0 + threadIdx.x;
+      Tq[threadIdx.x] = i < p.B ? ((double)lqz[i] + (double)lqz[p.B + i]) * 1.4426950408889634 : (double)INFINITY;
+    }
+    __syncthreads();
+    for (int ib = 0; ib < kTR && i0 + ib < p.B; ib += kP) {
+      const int pp_special = p.B - 2 - (i0 + ib);     // partner slot of row B-2 in this step (if in [0, kP))
+      auto step = [&](auto special_c) {
+        constexpr bool SPECIAL = decltype(special_c)::value;
+        float pz[KD][kP], pl[KD][kP];
+        float a[kR][kP];
+#pragma unroll
+        for (int r = 0; r < kR; ++r)
+#pragma unroll
+          for (int pp = 0; pp < kP; ++pp) a[r][pp] = 0.f;
+#pragma unroll
+        for (int k = 0; k < KD; ++k) {
+#pragma unroll
+          for (int pp = 0; pp < kP; ++pp) {
+            const int o = (ib + pp) * DP + lane + 32 * k;
+            pz[k][pp] = Tz[o]; pl[k][pp] = Tl[o];
+          }
+#pragma unroll
+          for (int r = 0; r < kR; ++r)
+#pragma unroll
+            for (int pp = 0; pp < kP; ++pp) {
+              const float df = pz[k][pp] - mu[r][k];
+              a[r][pp] = fmaf(df * df, hs[r][k], a[r][pp]);          // quadratic part of the pair sum
+            }
+        }
+        double x = (cbq - (double)pair_reduce(a, lane)) - Tq[ib + pq];
+        if (SPECIAL && (lane >> 3) == 0 && pq == pp_special) x += (double)p.D * (double)dcorr;
+        const float wq = anchor_dead ? 0.f : cq * ex2f((float)x);
+        float cqp[kR][kP];
+#pragma unroll
+        for (int r = 0; r < kR; ++r)
+#pragma unroll
+          for (int pp = 0; pp < kP; ++pp) cqp[r][pp] = __shfl_sync(0xFFFFFFFFu, wq, 2 * (r * kP + pp));
+#pragma unroll
+        for (int k = 0; k < KD; ++k)
+#pragma unroll
+          for (int r = 0; r < kR; ++r)
+#pragma unroll
+            for (int pp = 0; pp < kP; ++pp) {
+              const float df = pz[k][pp] - mu[r][k];
+              const float t = hs[r][k] * df;                         // h (z - mu) log2e
+              const float u = df * t;                                // h (z - mu)^2 log2e
+              float e = cs[r][k] - u;
+              if (SPECIAL && r == 0 && pp == pp_special && lane + 32 * k < p.D) e += dcorr;
+              const float rr = ex2f(e - pl[k][pp]);                  // softmax weight inside LSE_j[i, d]
+              const float cf = fmaf(cp, rr, cqp[r][pp]);             // dL / d ld_ijd
+              g0[r][k] = fmaf(cf, t, g0[r][k]);
+              g1[r][k] = fmaf(cf, fmaf(u, kLn2, -0.5f), g1[r][k]);   // h (z - mu)^2 - 1/2
+
+            }
+      };
+      if (c0 == 0 && pp_special >= 0 && pp_special < kP) step(std::true_type{}); else step(std::false_type{});
+    }
+  }
+  const float ca = p.alpha * invB * g;
+#pragma unroll
+  for (int r = 0; r < kR; ++r)
+#pragma unroll
+    for (int k = 0; k < KD; ++k) {
+      const int j = c0 + r, d = lane + 32 * k;
+      if (j < p.B && d < p.D) {
+        const size_t o = (size_t)j * p.D + d;
+        const float df = Z[o] - mu[r][k];
+        const float h2 = expf(-LV[o]);                               // 2 h
+        g_mu[o] = 2.f * kLn2 * g0[r][k] + ca * (h2 * df);
+        g_lv[o] = g1[r][k] + ca * (0.5f * h2 * df * df - 0.5f);
+      }
+    }
+}
+
+inline size_t smem_bytes(int KD) { return (size_t)(3 * kTR * 32 * KD + 2 * kTR) * sizeof(float); }
+
+}  // namespace tiled

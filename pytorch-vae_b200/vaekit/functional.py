@@ -422,7 +422,7 @@ class _BetaTc(torch.autograd.Function):
             raise RuntimeError("vaekit: the Beta-TC decomposition needs a batch of at least 2")
         zc, mc, lc = z.contiguous(), mu.contiguous(), log_var.contiguous()
         dev = z.device
-        lqz = torch.empty(B, dtype=torch.float32, device=dev)
+        lqz = torch.empty(2 * B, dtype=torch.float32, device=dev)     # value, then its fp32 residual
         lse = torch.empty((B, D), dtype=torch.float32, device=dev)
         out = torch.empty(4, dtype=torch.float32, device=dev)
         ws = L.workspace(dev, int(L.lib().vk_tc_workspace_bytes(B, D)))

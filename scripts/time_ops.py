@@ -36,6 +36,18 @@ if "vq" in which:
         torch.autograd.backward([q, l], [gq, None])
     ms = timeit(step, it=20)
     print("vq fwd+bwd B=1024: %.4f ms  %.2f M images/s, %.1f GB/s on 337.9 MB" % (ms, 1024 / ms / 1e3, 337.9e6 / ms / 1e6))
+if "tc" in which:
+    B, D = 4096, 128
+    mu = torch.randn(B, D, device=dev); lv = 0.3 * torch.randn(B, D, device=dev)
+    z = mu + torch.randn(B, D, device=dev) * torch.exp(0.5 * lv)
+    ms = timeit(lambda: F.betatc_terms(z, mu, lv, 0.00025, 1.0, 6.0, 0.37), warm=1, it=3)
+    print("betatc fwd B=%d D=%d: %.3f ms  (%.1f G densities/s)" % (B, D, ms, B * B * D / ms / 1e6), flush=True)
+    zg, mg, lg = (t.clone().requires_grad_(True) for t in (z, mu, lv))
+    def tc_step():
+        zg.grad = None; mg.grad = None; lg.grad = None
+        F.betatc_terms(zg, mg, lg, 0.00025, 1.0, 6.0, 0.37)[0].backward()
+    ms = timeit(tc_step, warm=1, it=3)
+    print("betatc fwd+bwd B=%d D=%d: %.3f ms" % (B, D, ms), flush=True)
 if "swd" in which:
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     from vaekit import _lib as L

@@ -55,7 +55,7 @@ def test_betatc_golden(vk, name):
     assert_close(z2.grad, g["grad_eval_z"], TOL)
 
 
-@pytest.mark.parametrize("B,D", [(2, 3), (64, 10), (130, 128), (257, 33), (1024, 128)])
+@pytest.mark.parametrize("B,D", [(2, 3), (64, 10), (130, 128), (257, 33), (1024, 128), (6, 64), (1030, 40), (40, 160)])
 def test_betatc_vs_oracle(vk, B, D):
     F, _ = vk
     gen = torch.Generator().manual_seed(B + D)
@@ -66,6 +66,12 @@ def test_betatc_vs_oracle(vk, B, D):
     zc, mc, lc = leaf(z), leaf(mu), leaf(lv)
     ref = O.betatc_loss(rz, rz, mc, lc, zc, 0.00025, alpha=1.0, beta=6.0, gamma=1.0, anneal_rate=0.37)
     ref["loss"].backward()
+    # float64 run of the same oracle: the reference's fp32 softmax weights exp(A_ij - log_q_z[i]) carry ulp(|log_q_z|)
+    # ~ 1e-5 noise at D = 128 (its gradients sit 2-4e-5 from float64, scripts/check_tc_precision.py); the kernels
+    # combine the pair sums in double and are held to 1e-5 against float64, 5e-5 against the fp32 oracle.
+    z64, m64, l64 = (leaf(t.double()) for t in (z, mu, lv))
+    ref64 = O.betatc_loss(rz.double(), rz.double(), m64, l64, z64, 0.00025, alpha=1.0, beta=6.0, gamma=1.0, anneal_rate=0.37)
+    ref64["loss"].backward()
     zg, mg, lg = leaf(z.to(DEV)), leaf(mu.to(DEV)), leaf(lv.to(DEV))
     latent, terms = F.betatc_terms(zg, mg, lg, 0.00025, 1.0, 6.0, 0.37 * 1.0)
     (latent * 2.0).backward()
@@ -73,9 +79,14 @@ def test_betatc_vs_oracle(vk, B, D):
     assert_close(terms[0], ref["KLD"], TOL, "kld")
     assert_close(terms[1], ref["TC_Loss"], TOL, "tc")
     assert_close(terms[2], ref["MI_Loss"], TOL, "mi")
-    for a, b, n in ((zg, zc, "z"), (mg, mc, "mu"), (lg, lc, "log_var")):
-        e = rel_err(a.grad / 2.0, b.grad)
-        assert e <= 2e-5, "grad %s rel err %.2e" % (n, e)
+    for a, b, b64, n in ((zg, zc, z64, "z"), (mg, mc, m64, "mu"), (lg, lc, l64, "log_var")):
+        e64 = rel_err((a.grad / 2.0).double(), b64.grad)
+        e32 = rel_err(a.grad / 2.0, b.grad)
+        print("B=%d D=%d grad %s: vs float64 %.2e, vs fp32 oracle %.2e (fp32 oracle vs float64 %.2e)" %
+              (B, D, n, e64, e32, rel_err(b.grad.double(), b64.grad)))
+        # latent dims > 128 take the general (fp32 pair sum) kernels: as accurate as the reference, not more
+        assert e64 <= (TOL if D <= 128 else 5e-5), "grad %s rel err vs float64 %.2e" % (n, e64)
+        assert e32 <= 5e-5, "grad %s rel err vs fp32 oracle %.2e" % (n, e32)
 
 
 def test_betatc_model_contract(vk):
