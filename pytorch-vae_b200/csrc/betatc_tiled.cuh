@@ -63,13 +63,26 @@ __device__ __forceinline__ float pair_reduce(const float (&a)[kR][kP], int lane)
   return v;
 }
 
-// stage kTR rows of a row-major [B, D] array into a [kTR][DP] tile: rows >= B get `dead`, padded dims of live rows 0
+// stage kTR rows of a row-major [B, D] array into a [kTR][DP] tile with cp.async (the copy of tile t+1 overlaps the
+// sweep of tile t): rows >= B get `dead`, padded dims of live rows 0
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void cp_async4(float* dst, const float* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async8(double* dst, const double* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
 template <int DP>
-__device__ __forceinline__ void stage(float* t, const float* __restrict__ src, int B, int D, int j0, float dead, float scale) {
+__device__ __forceinline__ void stage(float* t, const float* __restrict__ src, int B, int D, int j0, float dead) {
   for (int e = threadIdx.x; e < kTR * DP; e += kThreads) {
     const int r = e / DP, c = e % DP;
     const int j = j0 + r;
-    t[e] = j < B ? (c < D ? __ldg(src + (size_t)j * D + c) * scale : 0.f) : dead;
+    if (j < B && c < D) cp_async4(t + e, src + (size_t)j * D + c);
+    else t[e] = j < B ? 0.f : dead;
   }
 }
 
@@ -82,10 +95,7 @@ fwd_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const floa
            float* __restrict__ out) {
   constexpr int DP = 32 * KD;
   extern __shared__ __align__(16) float sm[];
-  double* Tb = reinterpret_cast<double*>(sm);        // [kTR] Cb of the staged partners (-inf for dead rows)
-  float* Tm = sm + 2 * kTR;
-  float* Th = Tm + kTR * DP;
-  float* Tc = Th + kTR * DP;
+  constexpr int kBuf = 2 * kTR + 3 * kTR * DP;       // floats per staging buffer: Cb (double) | mu | hs | cs
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int i0 = (blockIdx.x * kTW + w) * kR;
   float z[kR][KD], m[kR][KD], s[kR][KD];
@@ -103,13 +113,29 @@ fwd_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const floa
   const float dcorr = (p.lw_strat - p.lw_ds) * kLog2e;  // pair (B-2, 0) uses lw_strat where column 0 folds lw_ds
   const int r_special = p.B - 2 - i0;                // anchor slot of row B-2 in this warp (if in [0, kR))
   const int pq = (lane >> 1) & 3;                    // partner slot of this lane's pair
-  for (int j0 = 0; j0 < p.B; j0 += kTR) {
+  auto issue = [&](int t, int buf) {
+    float* base = sm + buf * kBuf;
+    const int j0 = t * kTR;
+    stage<DP>(base + 2 * kTR, MU, p.B, p.D, j0, 0.f);
+    stage<DP>(base + 2 * kTR + kTR * DP, Hs, p.B, p.D, j0, 0.f);
+    stage<DP>(base + 2 * kTR + 2 * kTR * DP, Cs, p.B, p.D, j0, -INFINITY);   // dead partners: every density -inf
+    if (threadIdx.x < kTR) {
+      double* tb = reinterpret_cast<double*>(base) + threadIdx.x;
+      if (j0 + threadIdx.x < p.B) cp_async8(tb, Cb + j0 + threadIdx.x); else *tb = -(double)INFINITY;
+    }
+    cp_async_commit();
+  };
+  const int ntiles = (p.B + kTR - 1) / kTR;
+  issue(0, 0);
+  for (int tile = 0; tile < ntiles; ++tile) {
+    const int j0 = tile * kTR;
+    if (tile + 1 < ntiles) { issue(tile + 1, (tile + 1) & 1); cp_async_wait<1>(); } else cp_async_wait<0>();
     __syncthreads();
-    stage<DP>(Tm, MU, p.B, p.D, j0, 0.f, 1.f);
-    stage<DP>(Th, Hs, p.B, p.D, j0, 0.f, 1.f);
-    stage<DP>(Tc, Cs, p.B, p.D, j0, -INFINITY, 1.f);   // dead partners: every density -inf
-    if (threadIdx.x < kTR) Tb[threadIdx.x] = j0 + threadIdx.x < p.B ? Cb[j0 + threadIdx.x] : -(double)INFINITY;
-    __syncthreads();
+    const float* base = sm + (tile & 1) * kBuf;
+    const double* Tb = reinterpret_cast<const double*>(base);   // [kTR] Cb of the staged partners (-inf for dead rows)
+    const float* Tm = base + 2 * kTR;
+    const float* Th = Tm + kTR * DP;
+    const float* Tc = Th + kTR * DP;
     for (int jb = 0; jb < kTR && j0 + jb < p.B; jb += kP) {
       auto step = [&](auto special_c) {
         constexpr bool SPECIAL = decltype(special_c)::value;
@@ -153,6 +179,7 @@ fwd_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const floa
       };
       if (j0 + jb == 0 && r_special >= 0 && r_special < kR) step(std::true_type{}); else step(std::false_type{});
     }
+    __syncthreads();                                  // everyone is done with this buffer before it is refilled
   }
   // merge the four partner slots of every anchor (lanes 8r .. 8r+7; the xor-1 neighbour is a duplicate)
 #pragma unroll
@@ -230,10 +257,7 @@ bwd_rows_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
                 float* __restrict__ g_z) {
   constexpr int DP = 32 * KD;
   extern __shared__ __align__(16) float sm[];
-  double* Tb = reinterpret_cast<double*>(sm);
-  float* Tm = sm + 2 * kTR;
-  float* Th = Tm + kTR * DP;
-  float* Tc = Th + kTR * DP;
+  constexpr int kBuf = 2 * kTR + 3 * kTR * DP;
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int i0 = (blockIdx.x * kTW + w) * kR;
   const float g = g_loss ? *g_loss : 1.f;
@@ -256,13 +280,29 @@ bwd_rows_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
   const double lqz2 = iq < p.B ? ((double)lqz[iq] + (double)lqz[p.B + iq]) * 1.4426950408889634 : (double)INFINITY;
   const float dcorr = (p.lw_strat - p.lw_ds) * kLog2e;
   const int r_special = p.B - 2 - i0;
-  for (int j0 = 0; j0 < p.B; j0 += kTR) {
+  auto issue = [&](int t, int buf) {
+    float* base = sm + buf * kBuf;
+    const int j0 = t * kTR;
+    stage<DP>(base + 2 * kTR, MU, p.B, p.D, j0, 0.f);
+    stage<DP>(base + 2 * kTR + kTR * DP, Hs, p.B, p.D, j0, 0.f);
+    stage<DP>(base + 2 * kTR + 2 * kTR * DP, Cs, p.B, p.D, j0, -INFINITY);
+    if (threadIdx.x < kTR) {
+      double* tb = reinterpret_cast<double*>(base) + threadIdx.x;
+      if (j0 + threadIdx.x < p.B) cp_async8(tb, Cb + j0 + threadIdx.x); else *tb = -(double)INFINITY;
+    }
+    cp_async_commit();
+  };
+  const int ntiles = (p.B + kTR - 1) / kTR;
+  issue(0, 0);
+  for (int tile = 0; tile < ntiles; ++tile) {
+    const int j0 = tile * kTR;
+    if (tile + 1 < ntiles) { issue(tile + 1, (tile + 1) & 1); cp_async_wait<1>(); } else cp_async_wait<0>();
     __syncthreads();
-    stage<DP>(Tm, MU, p.B, p.D, j0, 0.f, 1.f);
-    stage<DP>(Th, Hs, p.B, p.D, j0, 0.f, 1.f);
-    stage<DP>(Tc, Cs, p.B, p.D, j0, -INFINITY, 1.f);
-    if (threadIdx.x < kTR) Tb[threadIdx.x] = j0 + threadIdx.x < p.B ? Cb[j0 + threadIdx.x] : -(double)INFINITY;
-    __syncthreads();
+    const float* base = sm + (tile & 1) * kBuf;
+    const double* Tb = reinterpret_cast<const double*>(base);
+    const float* Tm = base + 2 * kTR;
+    const float* Th = Tm + kTR * DP;
+    const float* Tc = Th + kTR * DP;
     for (int jb = 0; jb < kTR && j0 + jb < p.B; jb += kP) {
       auto step = [&](auto special_c) {
         constexpr bool SPECIAL = decltype(special_c)::value;
@@ -313,6 +353,7 @@ bwd_rows_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
       };
       if (j0 + jb == 0 && r_special >= 0 && r_special < kR) step(std::true_type{}); else step(std::false_type{});
     }
+    __syncthreads();                                  // everyone is done with this buffer before it is refilled
   }
   const float ca = p.alpha * invB * g, cz = p.gamma_anneal * invB * g;
 #pragma unroll
@@ -341,9 +382,7 @@ bwd_cols_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
                 float* __restrict__ g_mu, float* __restrict__ g_lv) {
   constexpr int DP = 32 * KD;
   extern __shared__ __align__(16) float sm[];
-  double* Tq = reinterpret_cast<double*>(sm);   // partner rows i: log q(z_i) (log2 units, double), z, LSE_j[i, d] (log2 units)
-  float* Tz = sm + 2 * kTR;
-  float* Tl = Tz + kTR * DP;
+  constexpr int kBuf = 2 * kTR + 3 * kTR * DP;       // (same size as the other sweeps; the third tile is unused here)
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int c0 = (blockIdx.x * kTW + w) * kR;        // first anchor column of this warp
   const float g = g_loss ? *g_loss : 1.f;
@@ -366,15 +405,28 @@ bwd_cols_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
   const int pq = (lane >> 1) & 3;                    // partner slot of this lane's pair
   const bool anchor_dead = c0 + (lane >> 3) >= p.B;
   const double cbq = anchor_dead ? 0.0 : Cb[c0 + (lane >> 3)];
-  for (int i0 = 0; i0 < p.B; i0 += kTR) {
-    __syncthreads();
-    stage<DP>(Tz, Z, p.B, p.D, i0, 0.f, 1.f);
-    stage<DP>(Tl, lse, p.B, p.D, i0, INFINITY, kLog2e);            // dead partners: softmax weight exactly 0
-    if (threadIdx.x < kTR) {
+  auto issue = [&](int t, int buf) {
+    float* base = sm + buf * kBuf;
+    const int i0 = t * kTR;
+    stage<DP>(base + 2 * kTR, Z, p.B, p.D, i0, 0.f);
+    stage<DP>(base + 2 * kTR + kTR * DP, lse, p.B, p.D, i0, INFINITY);          // dead partners: softmax weight exactly 0
+    if (threadIdx.x < kTR) {                                                     // log q(z_i): value | residual
       const int i = i0 + threadIdx.x;
-      Tq[threadIdx.x] = i < p.B ? ((double)lqz[i] + (double)lqz[p.B + i]) * 1.4426950408889634 : (double)INFINITY;
+      if (i < p.B) { cp_async4(base + threadIdx.x, lqz + i); cp_async4(base + kTR + threadIdx.x, lqz + p.B + i); }
+      else { base[threadIdx.x] = INFINITY; base[kTR + threadIdx.x] = 0.f; }
     }
+    cp_async_commit();
+  };
+  const int ntiles = (p.B + kTR - 1) / kTR;
+  issue(0, 0);
+  for (int tile = 0; tile < ntiles; ++tile) {
+    const int i0 = tile * kTR;
+    if (tile + 1 < ntiles) { issue(tile + 1, (tile + 1) & 1); cp_async_wait<1>(); } else cp_async_wait<0>();
     __syncthreads();
+    const float* base = sm + (tile & 1) * kBuf;
+    const float* Tq = base;                          // partner rows i: log q(z_i) value [kTR] | residual [kTR]
+    const float* Tz = base + 2 * kTR;                // z
+    const float* Tl = Tz + kTR * DP;                 // LSE_j[i, d] (natural log units)
     for (int ib = 0; ib < kTR && i0 + ib < p.B; ib += kP) {
       const int pp_special = p.B - 2 - (i0 + ib);     // partner slot of row B-2 in this step (if in [0, kP))
       auto step = [&](auto special_c) {
@@ -400,7 +452,8 @@ bwd_cols_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
               a[r][pp] = fmaf(df * df, hs[r][k], a[r][pp]);          // quadratic part of the pair sum
             }
         }
-        double x = (cbq - (double)pair_reduce(a, lane)) - Tq[ib + pq];
+        double x = (cbq - (double)pair_reduce(a, lane)) -
+                   ((double)Tq[ib + pq] + (double)Tq[kTR + ib + pq]) * 1.4426950408889634;
         if (SPECIAL && (lane >> 3) == 0 && pq == pp_special) x += (double)p.D * (double)dcorr;
         const float wq = anchor_dead ? 0.f : cq * ex2f((float)x);
         float cqp[kR][kP];
@@ -419,7 +472,7 @@ bwd_cols_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
               const float u = df * t;                                // h (z - mu)^2 log2e
               float e = cs[r][k] - u;
               if (SPECIAL && r == 0 && pp == pp_special && lane + 32 * k < p.D) e += dcorr;
-              const float rr = ex2f(e - pl[k][pp]);                  // softmax weight inside LSE_j[i, d]
+              const float rr = ex2f(fmaf(-pl[k][pp], kLog2e, e));    // softmax weight inside LSE_j[i, d]
               const float cf = fmaf(cp, rr, cqp[r][pp]);             // dL / d ld_ijd
               g0[r][k] = fmaf(cf, t, g0[r][k]);
               g1[r][k] = fmaf(cf, fmaf(u, kLn2, -0.5f), g1[r][k]);   // h (z - mu)^2 - 1/2
@@ -428,6 +481,7 @@ bwd_cols_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
       };
       if (c0 == 0 && pp_special >= 0 && pp_special < kP) step(std::true_type{}); else step(std::false_type{});
     }
+    __syncthreads();
   }
   const float ca = p.alpha * invB * g;
 #pragma unroll
@@ -445,6 +499,6 @@ bwd_cols_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
     }
 }
 
-inline size_t smem_bytes(int KD) { return (size_t)(3 * kTR * 32 * KD + 2 * kTR) * sizeof(float); }
+inline size_t smem_bytes(int KD) { return (size_t)2 * (3 * kTR * 32 * KD + 2 * kTR) * sizeof(float); }   // two staging buffers
 
 }  // namespace tiled
