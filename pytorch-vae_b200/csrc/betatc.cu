@@ -342,13 +342,17 @@ extern "C" int vk_tc_fwd(const float* z, const float* mu, const float* log_var, 
   const int prep_blocks = (int)((B * D + 255) / 256 < 1184 ? (B * D + 255) / 256 : 1184);
   if (D <= 128) {
     // lanes-own-dims path (betatc_tiled.cuh)
-    const int KD = D <= 32 ? 1 : (D <= 64 ? 2 : 4);
-    const int tb = (int)((B + tiled::kTW * tiled::kR - 1) / (tiled::kTW * tiled::kR));
-    const size_t tsm = tiled::smem_bytes(KD);
+    // D <= 32: one dim per lane; <= 64: two; <= 128: four.  (Two warps per anchor group with two dims per lane each --
+    // NS = 2 -- doubles the warps but the per-step exchange barrier costs more than it hides: 5.1 -> 7.4 ms, measured.)
+    const int cfg = D <= 32 ? 0 : (D <= 64 ? 1 : 2);
+    const int DP = cfg == 0 ? 32 : (cfg == 1 ? 64 : 128), NS = 1;
+    const int per_cta = tiled::kTW / NS * tiled::kR;
+    const int tb = (int)((B + per_cta - 1) / per_cta);
+    const size_t tsm = tiled::smem_bytes(DP);
     double* Cb = (double*)(((uintptr_t)(C0 + B * D) + 255) & ~(uintptr_t)255);
     tiled::prep_kernel<<<prep_blocks, 256, 0, st>>>(log_var, p, H, C0);
     tiled::cbar_kernel<<<(int)((B * 32 + 255) / 256), 256, 0, st>>>(C0, p, Cb);
-    auto kern = KD == 1 ? tiled::fwd_kernel<1> : (KD == 2 ? tiled::fwd_kernel<2> : tiled::fwd_kernel<4>);
+    auto kern = cfg == 0 ? tiled::fwd_kernel<1, 1> : (cfg == 1 ? tiled::fwd_kernel<2, 1> : tiled::fwd_kernel<4, 1>);
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm) != cudaSuccess)
       return check_launch("tc_fwd (shared memory attribute)");
     kern<<<tb, tiled::kThreads, tsm, st>>>(z, mu, log_var, H, C0, Cb, p, lqz_out, lse_out, partials, (unsigned int*)ws, out);
@@ -378,14 +382,16 @@ extern "C" int vk_tc_bwd(const float* z, const float* mu, const float* log_var, 
   float* C0 = H + B * D;
   const int prep_blocks = (int)((B * D + 255) / 256 < 1184 ? (B * D + 255) / 256 : 1184);
   if (D <= 128) {
-    const int KD = D <= 32 ? 1 : (D <= 64 ? 2 : 4);
-    const int tb = (int)((B + tiled::kTW * tiled::kR - 1) / (tiled::kTW * tiled::kR));
-    const size_t tsm = tiled::smem_bytes(KD);
+    const int cfg = D <= 32 ? 0 : (D <= 64 ? 1 : 2);
+    const int DP = cfg == 0 ? 32 : (cfg == 1 ? 64 : 128), NS = 1;
+    const int per_cta = tiled::kTW / NS * tiled::kR;
+    const int tb = (int)((B + per_cta - 1) / per_cta);
+    const size_t tsm = tiled::smem_bytes(DP);
     double* Cb = (double*)(((uintptr_t)(C0 + B * D) + 255) & ~(uintptr_t)255);
     tiled::prep_kernel<<<prep_blocks, 256, 0, st>>>(log_var, p, H, C0);
     tiled::cbar_kernel<<<(int)((B * 32 + 255) / 256), 256, 0, st>>>(C0, p, Cb);
-    auto kr = KD == 1 ? tiled::bwd_rows_kernel<1> : (KD == 2 ? tiled::bwd_rows_kernel<2> : tiled::bwd_rows_kernel<4>);
-    auto kc = KD == 1 ? tiled::bwd_cols_kernel<1> : (KD == 2 ? tiled::bwd_cols_kernel<2> : tiled::bwd_cols_kernel<4>);
+    auto kr = cfg == 0 ? tiled::bwd_rows_kernel<1, 1> : (cfg == 1 ? tiled::bwd_rows_kernel<2, 1> : tiled::bwd_rows_kernel<4, 1>);
+    auto kc = cfg == 0 ? tiled::bwd_cols_kernel<1, 1> : (cfg == 1 ? tiled::bwd_cols_kernel<2, 1> : tiled::bwd_cols_kernel<4, 1>);
     if (cudaFuncSetAttribute(kr, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm) != cudaSuccess ||
         cudaFuncSetAttribute(kc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm) != cudaSuccess)
       return check_launch("tc_bwd (shared memory attribute)");

@@ -63,6 +63,20 @@ __device__ __forceinline__ float pair_reduce(const float (&a)[kR][kP], int lane)
   return v;
 }
 
+// Complete pair sums when NS = 2 warps split the latent dims of one anchor group: each warp reduces its half, the halves
+// meet in shared memory (slot alternates with the step parity so one 64-thread named barrier per step is enough).
+template <int NS>
+__device__ __forceinline__ float pair_sum(const float (&a)[kR][kP], int lane, int grp, int slice, float* xch, int step_no) {
+  float v = pair_reduce(a, lane);
+  if (NS == 2) {
+    float* slot = xch + (((step_no & 1) * (kTW / 2) + grp) * 2) * 16;
+    if ((lane & 1) == 0) slot[slice * 16 + (lane >> 1)] = v;
+    asm volatile("bar.sync %0, 64;" ::"r"(1 + grp) : "memory");
+    v += slot[(slice ^ 1) * 16 + (lane >> 1)];
+  }
+  return v;
+}
+
 // stage kTR rows of a row-major [B, D] array into a [kTR][DP] tile with cp.async (the copy of tile t+1 overlaps the
 // sweep of tile t): rows >= B get `dead`, padded dims of live rows 0
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -87,23 +101,27 @@ __device__ __forceinline__ void stage(float* t, const float* __restrict__ src, i
 }
 
 // ---- forward -----------------------------------------------------------------------------------------------------
-template <int KD>
+template <int KD, int NS>
 __global__ void __launch_bounds__(kThreads)
 fwd_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const float* __restrict__ LV,
            const float* __restrict__ Hs, const float* __restrict__ Cs, const double* __restrict__ Cb, TcParams p,
            float* __restrict__ lqz_out, float* __restrict__ lse_out, double* __restrict__ partials, unsigned int* ticket,
            float* __restrict__ out) {
-  constexpr int DP = 32 * KD;
+  constexpr int DP = 32 * KD * NS;                   // staged tile width: NS warps share an anchor group, KD dims per lane each
   extern __shared__ __align__(16) float sm[];
+  __shared__ float xch_s[2 * (kTW / 2) * 2 * 16];
+  float* xch = xch_s;
+  int step_no = 0;
   constexpr int kBuf = 2 * kTR + 3 * kTR * DP;       // floats per staging buffer: Cb (double) | mu | hs | cs
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int i0 = (blockIdx.x * kTW + w) * kR;
+  const int grp = w / NS, dbase = (w % NS) * 32 * KD;
+  const int i0 = (blockIdx.x * (kTW / NS) + grp) * kR;
   float z[kR][KD], m[kR][KD], s[kR][KD];
 #pragma unroll
   for (int r = 0; r < kR; ++r)
 #pragma unroll
     for (int k = 0; k < KD; ++k) {
-      const int d = lane + 32 * k;
+      const int d = dbase + lane + 32 * k;
       z[r][k] = (i0 + r < p.B && d < p.D) ? Z[(size_t)(i0 + r) * p.D + d] : 0.f;
       m[r][k] = -INFINITY;
       s[r][k] = 0.f;
@@ -149,7 +167,7 @@ fwd_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const floa
           float pm[kP], ph[kP], pc[kP];
 #pragma unroll
           for (int pp = 0; pp < kP; ++pp) {
-            const int o = (jb + pp) * DP + lane + 32 * k;
+            const int o = (jb + pp) * DP + dbase + lane + 32 * k;
             pm[pp] = Tm[o]; ph[pp] = Th[o]; pc[pp] = Tc[o];
           }
 #pragma unroll
@@ -160,7 +178,7 @@ fwd_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const floa
               const float df = z[r][k] - pm[pp];
               const float d2 = df * df;
               e[pp] = fmaf(-d2, ph[pp], pc[pp]);                // (log N(z_id; mu_jd, var_jd) + lw_j) log2e
-              if (SPECIAL && pp == 0 && r == r_special && lane + 32 * k < p.D) e[pp] += dcorr;
+              if (SPECIAL && pp == 0 && r == r_special && dbase + lane + 32 * k < p.D) e[pp] += dcorr;
               a[r][pp] = fmaf(d2, ph[pp], a[r][pp]);            // quadratic part of the pair sum
             }
             const float bmax = fmaxf(fmaxf(e[0], e[1]), fmaxf(e[2], e[3]));
@@ -171,13 +189,14 @@ fwd_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const floa
           }
         }
         // A_ij + D lw_ij complete for the 16 pairs of this step: online logsumexp over j (betatc_vae.py:185-187)
-        double val = Tb[jb + pq] - (double)pair_reduce(a, lane);
+        double val = Tb[jb + pq] - (double)pair_sum<NS>(a, lane, grp, w % NS, xch, step_no);
         if (SPECIAL && pq == 0 && (lane >> 3) == r_special) val += (double)p.D * (double)dcorr;
         const double mn = fmax(fmax(rm, val), -1e300);
         rs = fmaf(rs, ex2f((float)(rm - mn)), ex2f((float)(val - mn)));
         rm = mn;
       };
       if (j0 + jb == 0 && r_special >= 0 && r_special < kR) step(std::true_type{}); else step(std::false_type{});
+      ++step_no;
     }
     __syncthreads();                                  // everyone is done with this buffer before it is refilled
   }
@@ -202,7 +221,7 @@ fwd_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const floa
     float lpq = 0.f, lqzx = 0.f, lpz = 0.f;
 #pragma unroll
     for (int k = 0; k < KD; ++k) {
-      const int d = lane + 32 * k;
+      const int d = dbase + lane + 32 * k;
       if (i < p.B && d < p.D) {
         const size_t o = (size_t)i * p.D + d;
         const float l = (m[r][k] + log2f(s[r][k])) * kLn2;
@@ -215,8 +234,11 @@ fwd_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const floa
     }
     lpq = warp_sum(lpq); lqzx = warp_sum(lqzx); lpz = warp_sum(lpz);
     if (i < p.B) {
-      if (lane == 0) { lqz_out[i] = lqz; lqz_out[p.B + i] = lqr; }
-      t_qzx += lqzx; t_qz += lqz; t_pq += lpq; t_pz += lpz;
+      if (dbase == 0) {                              // one of the NS warps of the group owns the row value
+        if (lane == 0) { lqz_out[i] = lqz; lqz_out[p.B + i] = lqr; }
+        t_qz += lqz;
+      }
+      t_qzx += lqzx; t_pq += lpq; t_pz += lpz;
     }
   }
   __shared__ double red[kTW * 4];
@@ -249,17 +271,21 @@ fwd_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const floa
 // L = (1/B) sum_i [ alpha lqzx_i + (beta - alpha) lqz_i + (ga - beta) lpq_i - ga lpz_i ],  ga = anneal * gamma
 //   d/d ld_ijd = [ (beta - alpha) p_ij + (ga - beta) r_ijd ] / B,   p = softmax_j(A), r = softmax_j(ld + lw) per d
 //   d ld_ijd / d z_id = -2 h_jd (z_id - mu_jd)
-template <int KD>
+template <int KD, int NS>
 __global__ void __launch_bounds__(kThreads)
 bwd_rows_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const float* __restrict__ LV,
                 const float* __restrict__ Hs, const float* __restrict__ Cs, const double* __restrict__ Cb,
                 const float* __restrict__ lqz, const float* __restrict__ lse, TcParams p, const float* __restrict__ g_loss,
                 float* __restrict__ g_z) {
-  constexpr int DP = 32 * KD;
+  constexpr int DP = 32 * KD * NS;                   // staged tile width: NS warps share an anchor group, KD dims per lane each
   extern __shared__ __align__(16) float sm[];
+  __shared__ float xch_s[2 * (kTW / 2) * 2 * 16];
+  float* xch = xch_s;
+  int step_no = 0;
   constexpr int kBuf = 2 * kTR + 3 * kTR * DP;
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int i0 = (blockIdx.x * kTW + w) * kR;
+  const int grp = w / NS, dbase = (w % NS) * 32 * KD;
+  const int i0 = (blockIdx.x * (kTW / NS) + grp) * kR;
   const float g = g_loss ? *g_loss : 1.f;
   const float invB = 1.f / (float)p.B;
   const float cq = (p.beta - p.alpha) * invB * g, cp = (p.gamma_anneal - p.beta) * invB * g;
@@ -268,7 +294,7 @@ bwd_rows_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
   for (int r = 0; r < kR; ++r)
 #pragma unroll
     for (int k = 0; k < KD; ++k) {
-      const int d = lane + 32 * k;
+      const int d = dbase + lane + 32 * k;
       const bool ok = i0 + r < p.B && d < p.D;
       z[r][k] = ok ? Z[(size_t)(i0 + r) * p.D + d] : 0.f;
       l2[r][k] = ok ? lse[(size_t)(i0 + r) * p.D + d] * kLog2e : 0.f;
@@ -316,7 +342,7 @@ bwd_rows_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
         for (int k = 0; k < KD; ++k) {
 #pragma unroll
           for (int pp = 0; pp < kP; ++pp) {
-            const int o = (jb + pp) * DP + lane + 32 * k;
+            const int o = (jb + pp) * DP + dbase + lane + 32 * k;
             pm[k][pp] = Tm[o]; ph[k][pp] = Th[o]; pc[k][pp] = Tc[o];
           }
 #pragma unroll
@@ -328,7 +354,7 @@ bwd_rows_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
             }
         }
         // softmax weight of (i, j) in log q(z_i), times its coefficient; dead partners / anchors give exactly 0
-        double x = (Tb[jb + pq] - (double)pair_reduce(a, lane)) - lqz2;
+        double x = (Tb[jb + pq] - (double)pair_sum<NS>(a, lane, grp, w % NS, xch, step_no)) - lqz2;
         if (SPECIAL && pq == 0 && (lane >> 3) == r_special) x += (double)p.D * (double)dcorr;
         const float wq = cq * ex2f((float)x);
         float cqp[kR][kP];
@@ -345,13 +371,14 @@ bwd_rows_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
               const float df = z[r][k] - pm[k][pp];
               const float t = ph[k][pp] * df;                        // h (z - mu) log2e
               float e = fmaf(-df, t, pc[k][pp]);
-              if (SPECIAL && pp == 0 && r == r_special && lane + 32 * k < p.D) e += dcorr;
+              if (SPECIAL && pp == 0 && r == r_special && dbase + lane + 32 * k < p.D) e += dcorr;
               const float rr = ex2f(e - l2[r][k]);                   // softmax weight inside LSE_j[i, d]
               const float cf = fmaf(cp, rr, cqp[r][pp]);             // dL / d ld_ijd
               gz[r][k] = fmaf(-cf, t, gz[r][k]);
             }
       };
       if (j0 + jb == 0 && r_special >= 0 && r_special < kR) step(std::true_type{}); else step(std::false_type{});
+      ++step_no;
     }
     __syncthreads();                                  // everyone is done with this buffer before it is refilled
   }
@@ -360,7 +387,7 @@ bwd_rows_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
   for (int r = 0; r < kR; ++r)
 #pragma unroll
     for (int k = 0; k < KD; ++k) {
-      const int i = i0 + r, d = lane + 32 * k;
+      const int i = i0 + r, d = dbase + lane + 32 * k;
       if (i < p.B && d < p.D) {
         const size_t o = (size_t)i * p.D + d;
         const float df = z[r][k] - MU[o];
@@ -374,17 +401,21 @@ bwd_rows_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
 
 // ---- backward, column sweep: d/dmu_j, d/dlog_var_j -------------------------------------------------------------------
 //   d ld_ijd / d mu_jd = 2 h_jd (z_id - mu_jd) ;  d ld_ijd / d lv_jd = h_jd (z_id - mu_jd)^2 - 1/2
-template <int KD>
+template <int KD, int NS>
 __global__ void __launch_bounds__(kThreads)
 bwd_cols_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const float* __restrict__ LV,
                 const float* __restrict__ Hs, const float* __restrict__ Cs, const double* __restrict__ Cb,
                 const float* __restrict__ lqz, const float* __restrict__ lse, TcParams p, const float* __restrict__ g_loss,
                 float* __restrict__ g_mu, float* __restrict__ g_lv) {
-  constexpr int DP = 32 * KD;
+  constexpr int DP = 32 * KD * NS;                   // staged tile width: NS warps share an anchor group, KD dims per lane each
   extern __shared__ __align__(16) float sm[];
+  __shared__ float xch_s[2 * (kTW / 2) * 2 * 16];
+  float* xch = xch_s;
+  int step_no = 0;
   constexpr int kBuf = 2 * kTR + 3 * kTR * DP;       // (same size as the other sweeps; the third tile is unused here)
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int c0 = (blockIdx.x * kTW + w) * kR;        // first anchor column of this warp
+  const int grp = w / NS, dbase = (w % NS) * 32 * KD;
+  const int c0 = (blockIdx.x * (kTW / NS) + grp) * kR;   // first anchor column of this warp
   const float g = g_loss ? *g_loss : 1.f;
   const float invB = 1.f / (float)p.B;
   const float cq = (p.beta - p.alpha) * invB * g, cp = (p.gamma_anneal - p.beta) * invB * g;
@@ -393,7 +424,7 @@ bwd_cols_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
   for (int r = 0; r < kR; ++r)
 #pragma unroll
     for (int k = 0; k < KD; ++k) {
-      const int d = lane + 32 * k;
+      const int d = dbase + lane + 32 * k;
       const bool ok = c0 + r < p.B && d < p.D;
       const size_t o = (size_t)(c0 + r) * p.D + d;
       mu[r][k] = ok ? MU[o] : 0.f;
@@ -441,7 +472,7 @@ bwd_cols_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
         for (int k = 0; k < KD; ++k) {
 #pragma unroll
           for (int pp = 0; pp < kP; ++pp) {
-            const int o = (ib + pp) * DP + lane + 32 * k;
+            const int o = (ib + pp) * DP + dbase + lane + 32 * k;
             pz[k][pp] = Tz[o]; pl[k][pp] = Tl[o];
           }
 #pragma unroll
@@ -452,7 +483,7 @@ bwd_cols_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
               a[r][pp] = fmaf(df * df, hs[r][k], a[r][pp]);          // quadratic part of the pair sum
             }
         }
-        double x = (cbq - (double)pair_reduce(a, lane)) -
+        double x = (cbq - (double)pair_sum<NS>(a, lane, grp, w % NS, xch, step_no)) -
                    ((double)Tq[ib + pq] + (double)Tq[kTR + ib + pq]) * 1.4426950408889634;
         if (SPECIAL && (lane >> 3) == 0 && pq == pp_special) x += (double)p.D * (double)dcorr;
         const float wq = anchor_dead ? 0.f : cq * ex2f((float)x);
@@ -471,7 +502,7 @@ bwd_cols_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
               const float t = hs[r][k] * df;                         // h (z - mu) log2e
               const float u = df * t;                                // h (z - mu)^2 log2e
               float e = cs[r][k] - u;
-              if (SPECIAL && r == 0 && pp == pp_special && lane + 32 * k < p.D) e += dcorr;
+              if (SPECIAL && r == 0 && pp == pp_special && dbase + lane + 32 * k < p.D) e += dcorr;
               const float rr = ex2f(fmaf(-pl[k][pp], kLog2e, e));    // softmax weight inside LSE_j[i, d]
               const float cf = fmaf(cp, rr, cqp[r][pp]);             // dL / d ld_ijd
               g0[r][k] = fmaf(cf, t, g0[r][k]);
@@ -480,6 +511,7 @@ bwd_cols_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
             }
       };
       if (c0 == 0 && pp_special >= 0 && pp_special < kP) step(std::true_type{}); else step(std::false_type{});
+      ++step_no;
     }
     __syncthreads();
   }
@@ -488,7 +520,7 @@ bwd_cols_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
   for (int r = 0; r < kR; ++r)
 #pragma unroll
     for (int k = 0; k < KD; ++k) {
-      const int j = c0 + r, d = lane + 32 * k;
+      const int j = c0 + r, d = dbase + lane + 32 * k;
       if (j < p.B && d < p.D) {
         const size_t o = (size_t)j * p.D + d;
         const float df = Z[o] - mu[r][k];
@@ -499,6 +531,6 @@ bwd_cols_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
     }
 }
 
-inline size_t smem_bytes(int KD) { return (size_t)2 * (3 * kTR * 32 * KD + 2 * kTR) * sizeof(float); }   // two staging buffers
+inline size_t smem_bytes(int DP) { return (size_t)2 * (3 * kTR * DP + 2 * kTR) * sizeof(float); }   // two staging buffers of width DP
 
 }  // namespace tiled
