@@ -205,6 +205,17 @@ int64_t vk_seg_sort_workspace_bytes(int64_t segments, int64_t n);
 int vk_seg_sort(float* keys, uint32_t* perm_out, int64_t segments, int64_t n, void* workspace,
                 int64_t workspace_bytes, void* stream);
 
+/* vk_gemm_nt: the fp32-grade tensor-core product used by the two SWAE GEMMs, on its own:
+ *   C(n, j) = sum_k A(n, k) * B(j, k)     A(n, k) = A[n*a_sn + k*a_sk], B(j, k) = B[j*b_sj + k*b_sk], C likewise
+ * J and K small (J, K <= 256 after padding to 16, 3*K/2 + J <= 512 tensor-memory columns), N arbitrary.  Operands are
+ * split three ways into bf16 and accumulated from six tcgen05 passes in fp32 (error ~ 2^-23 |A||B|).
+ * Returns VK_ERR_UNSUPPORTED when the shape does not fit (vk_swd_fwd then uses its fp32 FFMA GEMM).
+ * workspace: vk_gemm_nt_workspace_bytes() bytes. */
+int64_t vk_gemm_nt_workspace_bytes(void);
+int vk_gemm_nt(const float* A, int64_t a_sn, int64_t a_sk, const float* B, int64_t b_sj, int64_t b_sk, float* C,
+               int64_t c_sn, int64_t c_sj, int64_t N, int64_t J, int64_t K, void* workspace, int64_t workspace_bytes,
+               void* stream);
+
 /* ---------------------------------------------------------------------------
  * K5  Beta-TC-VAE latent terms             (reference: models/betatc_vae.py:132-142, 165-211)
  *

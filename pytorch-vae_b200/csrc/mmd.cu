@@ -294,8 +294,10 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
         uint32_t acc = 0;
 #pragma unroll
         for (int pass = 0; pass < PASSES; ++pass) {
-          uint32_t ta = pass == 1 ? tmem_Alo : tmem_Ahi;       // row-block operand from tensor memory: 8 columns per K=16
-          uint64_t db = pass == 2 ? db_lo : db_hi;
+          // passes: lo*hi, hi*lo, then hi*hi LAST -- the tensor core's fp32 accumulation truncates (~2^-23 |acc| per
+          // MMA), so the correction terms are summed while the accumulator is still small (gemm3x.cuh, measured 8x)
+          uint32_t ta = (PASSES == 3 && pass == 0) ? tmem_Alo : tmem_Ahi;   // operand from tensor memory: 8 columns per K=16
+          uint64_t db = (PASSES == 3 && pass == 1) ? db_lo : db_hi;
 #pragma unroll 4
           for (int k = 0; k < ksteps1; ++k) {
             mma_bf16_ts_if(leader, tmem_S + sb * kCols, ta, db, idesc1, acc);
@@ -355,8 +357,8 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
             const uint64_t db_hi = smem_desc(b_hi, 128, b_lbo), db_lo = smem_desc(b_hi + b_half, 128, b_lbo);
 #pragma unroll
             for (int pass = 0; pass < PASSES; ++pass) {
-              uint32_t ta = pass == 1 ? tk_lo : tk_hi;
-              uint64_t db = pass == 2 ? db_lo : db_hi;
+              uint32_t ta = (PASSES == 3 && pass == 0) ? tk_lo : tk_hi;
+              uint64_t db = (PASSES == 3 && pass == 1) ? db_lo : db_hi;
 #pragma unroll
               for (int k = 0; k < kCols / 16; ++k) {
                 mma_bf16_ts_if(leader, tmem_O, ta, db, idesc2 | neg_a, oacc);

@@ -12,6 +12,7 @@
 // and the [N,D] gradients of the shards add up).
 #include "common.cuh"
 #include "seg_sort.cuh"
+#include "gemm3x.cuh"
 
 namespace vk {
 namespace {
@@ -138,8 +139,9 @@ __global__ void mean_scale_kernel(const double* sum, double count, float reg, fl
 }
 
 struct SwdWs {
-  size_t partials, keyZ0, keyZ1, idx0, idx1, keyP0, keyP1, counts, total;
+  size_t partials, keyZ0, keyZ1, idx0, idx1, keyP0, keyP1, counts, bimg, total;
 };
+constexpr size_t kBimgBytes = 3u * 256u * 256u * 2u;      // packed theta images of the tcgen05 GEMMs (upper bound)
 inline SwdWs swd_ws(int64_t N, int64_t S) {
   SwdWs w;
   const size_t seg = ((size_t)S * N * 4 + 255) & ~(size_t)255;
@@ -153,6 +155,8 @@ inline SwdWs swd_ws(int64_t N, int64_t S) {
   w.keyP0 = o; o += seg;
   w.keyP1 = o; o += seg;
   w.counts = o; o += segsort::counts_bytes(S, N);
+  o = (o + 255) & ~(size_t)255;
+  w.bimg = o; o += kBimgBytes;
   w.total = o;
   return w;
 }
@@ -183,11 +187,19 @@ extern "C" int vk_swd_fwd(const float* z, const float* prior, const float* proj,
   float* priT = (float*)(ws + w.keyP0);
   // 1. projections, stored [S][N]
   const dim3 pg((unsigned)((N + BM - 1) / BM), (unsigned)((S + BN - 1) / BN));
-  GemmArgs ga{z, proj, latT, N, S, D, D, 1, 1, D, 1, N};
-  sgemm_kernel<true, true, true><<<pg, GT, 0, st>>>(ga);
-  GemmArgs gp{prior, proj, priT, N, S, D, D, 1, 1, D, 1, N};
-  sgemm_kernel<true, true, true><<<pg, GT, 0, st>>>(gp);
-  int rc = check_launch("swd project");
+  int rc;
+  if (g3::fits((int)S, (int)D)) {
+    // tcgen05 path: latT(n, s) = sum_d z(n, d) theta(s, d), six bf16 passes of a three-way split (fp32-grade keys)
+    rc = g3::launch(z, D, 1, proj, D, 1, latT, 1, N, N, (int)S, (int)D, ws + w.bimg, st, "swd project (tcgen05)");
+    if (rc != VK_OK) return rc;
+    rc = g3::launch(prior, D, 1, proj, D, 1, priT, 1, N, N, (int)S, (int)D, ws + w.bimg, st, "swd project (tcgen05)");
+  } else {
+    GemmArgs ga{z, proj, latT, N, S, D, D, 1, 1, D, 1, N};
+    sgemm_kernel<true, true, true><<<pg, GT, 0, st>>>(ga);
+    GemmArgs gp{prior, proj, priT, N, S, D, D, 1, 1, D, 1, N};
+    sgemm_kernel<true, true, true><<<pg, GT, 0, st>>>(gp);
+    rc = check_launch("swd project");
+  }
   if (rc != VK_OK) return rc;
   // 2. sorts
   rc = segsort::sort<true>((uint32_t*)(ws + w.keyZ0), (uint32_t*)(ws + w.keyZ1), (uint32_t*)(ws + w.idx0),
@@ -210,12 +222,34 @@ extern "C" int vk_swd_fwd(const float* z, const float* prior, const float* proj,
   if (rc != VK_OK) return rc;
   // 4. dz = g_lat^T theta
   if (grad_unscaled) {
-    const dim3 gg((unsigned)((N + BM - 1) / BM), (unsigned)((D + BN - 1) / BN));
-    GemmArgs gb{g_lat, proj, grad_unscaled, N, D, S, 1, N, D, 1, D, 1};
-    sgemm_kernel<false, false, false><<<gg, GT, 0, st>>>(gb);
-    rc = check_launch("swd grad gemm");
+    if (g3::fits((int)D, (int)S)) {
+      // dz(n, d) = sum_s g(s, n) theta(s, d):  A(n, k = s) = g_lat[s * N + n],  B(j = d, k = s) = theta[s * D + d]
+      rc = g3::launch(g_lat, 1, N, proj, 1, D, grad_unscaled, D, 1, N, (int)D, (int)S, ws + w.bimg, st,
+                      "swd grad gemm (tcgen05)");
+    } else {
+      const dim3 gg((unsigned)((N + BM - 1) / BM), (unsigned)((D + BN - 1) / BN));
+      GemmArgs gb{g_lat, proj, grad_unscaled, N, D, S, 1, N, D, 1, D, 1};
+      sgemm_kernel<false, false, false><<<gg, GT, 0, st>>>(gb);
+      rc = check_launch("swd grad gemm");
+    }
   }
   return rc;
+}
+
+extern "C" int64_t vk_gemm_nt_workspace_bytes(void) { return (int64_t)(kWsHeader + kBimgBytes); }
+
+extern "C" int vk_gemm_nt(const float* A, int64_t a_sn, int64_t a_sk, const float* B, int64_t b_sj, int64_t b_sk, float* C,
+                          int64_t c_sn, int64_t c_sj, int64_t N, int64_t J, int64_t K, void* workspace,
+                          int64_t workspace_bytes, void* stream) {
+  VK_REQUIRE(A && B && C && workspace, VK_ERR_BAD_ARG, "gemm_nt: null pointer");
+  VK_REQUIRE(N >= 1 && J >= 1 && K >= 1, VK_ERR_BAD_ARG, "gemm_nt: empty shape N=%lld J=%lld K=%lld", (long long)N,
+             (long long)J, (long long)K);
+  VK_REQUIRE(J <= 256 && K <= 256 && g3::fits((int)J, (int)K), VK_ERR_UNSUPPORTED,
+             "gemm_nt: J=%lld, K=%lld do not fit the tensor-memory / shared-memory budget of the tcgen05 GEMM", (long long)J,
+             (long long)K);
+  VK_REQUIRE(workspace_bytes >= vk_gemm_nt_workspace_bytes(), VK_ERR_WORKSPACE, "gemm_nt: workspace too small");
+  return g3::launch(A, a_sn, a_sk, B, b_sj, b_sk, C, c_sn, c_sj, N, (int)J, (int)K, (uint8_t*)workspace + kWsHeader,
+                    (cudaStream_t)stream, "gemm_nt");
 }
 
 extern "C" int vk_mean_scale(const double* sum, double count, float scale, float* out, void* stream) {

@@ -222,7 +222,8 @@ vq_fwd_kernel(const float* __restrict__ X, const float* __restrict__ E, const ui
           uint32_t acc = 0;
 #pragma unroll
           for (int pass = 0; pass < 3; ++pass) {
-            uint64_t da = pass == 1 ? da_lo : da_hi, db = pass == 2 ? db_lo : db_hi;
+            // lo*hi, hi*lo, then hi*hi last: the truncating fp32 accumulation sees the small terms first
+            uint64_t da = pass == 0 ? da_lo : da_hi, db = pass == 1 ? db_lo : db_hi;
 #pragma unroll 4
             for (int k = 0; k < ksteps; ++k) {
               mma_bf16_if(leader, d, da, db, idesc, acc);

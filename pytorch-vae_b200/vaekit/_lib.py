@@ -38,6 +38,8 @@ _SIGNATURES = {
     "vk_mean_scale": ([_p, C.c_double, _f, _p, _p], _i),
     "vk_seg_sort_workspace_bytes": ([_i64, _i64], _i64),
     "vk_seg_sort": ([_p, _p, _i64, _i64, _p, _i64, _p], _i),
+    "vk_gemm_nt_workspace_bytes": ([], _i64),
+    "vk_gemm_nt": ([_p, _i64, _i64, _p, _i64, _i64, _p, _i64, _i64, _i64, _i64, _i64, _p, _i64, _p], _i),
     "vk_tc_workspace_bytes": ([_i64, _i64], _i64),
     "vk_tc_fwd": ([_p, _p, _p, _i64, _i64, _f, _f, _f, _f, _p, _p, _p, _p, _i64, _p], _i),
     "vk_tc_bwd": ([_p, _p, _p, _p, _p, _i64, _i64, _f, _f, _f, _f, _p, _p, _p, _p, _p, _i64, _p], _i),

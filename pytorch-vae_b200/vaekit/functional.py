@@ -406,6 +406,24 @@ def seg_sort(keys, want_perm=False):
     return out, (perm.long() if want_perm else None)
 
 
+def gemm_nt(a, b):
+    """a [N, K] @ b[J, K]^T -> [N, J] with the library's fp32-grade tcgen05 GEMM (any strides; J, K small)."""
+    L.require(a, "a", dims=(2,))
+    L.require(b, "b", dims=(2,))
+    if a.shape[1] != b.shape[1]:
+        raise ValueError("gemm_nt: inner dimensions differ: %s vs %s" % (tuple(a.shape), tuple(b.shape)))
+    N, K = a.shape
+    J = b.shape[0]
+    out = torch.empty((N, J), dtype=torch.float32, device=a.device)
+    if N * J == 0:
+        return out
+    ws = L.workspace(a.device, int(L.lib().vk_gemm_nt_workspace_bytes()))
+    with torch.cuda.device(a.device):
+        L.call("gemm_nt", L.ptr(a), a.stride(0), a.stride(1), L.ptr(b), b.stride(0), b.stride(1), L.ptr(out), J, 1,
+               N, J, K, L.ptr(ws), ws.numel(), L.stream_ptr())
+    return out
+
+
 # ---------------------------------------------------------------------------
 # K5
 # ---------------------------------------------------------------------------

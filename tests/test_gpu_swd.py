@@ -48,6 +48,22 @@ def test_seg_sort_matches_torch_sort(vk, segs, n):
     assert none is None and torch.equal(out2, out)
 
 
+def rank_clear_rows(z, proj, rel_gap=2e-6):
+    """Rows none of whose projections has a float64 neighbour gap below rel_gap: two correct fp32 GEMMs (different
+    summation order) may rank such near-tied samples differently, which moves their gradient by the neighbouring
+    prior gap (SURVEY 7.3#5).  Parity of the gradient is asserted on the other rows; the rest is reported."""
+    z, proj = z.detach().double().cpu(), proj.detach().double().cpu()
+    n, S = z.shape[0], proj.shape[0]
+    srt, order = torch.sort(z @ proj.t(), dim=0)
+    gaps = srt[1:] - srt[:-1]
+    big = torch.full((1, S), float("inf"), dtype=torch.float64)
+    near = torch.minimum(torch.cat([gaps, big]), torch.cat([big, gaps])) < rel_gap * srt.abs().clamp_min(1.0)
+    ambiguous = torch.zeros(n, dtype=torch.bool)
+    for j in range(S):
+        ambiguous[order[near[:, j], j]] = True
+    return ~ambiguous
+
+
 @pytest.mark.parametrize("name", ["swae_n64_d16", "swae_n256_d128"])
 def test_swae_golden(vk, name):
     F, _ = vk
@@ -62,7 +78,15 @@ def test_swae_golden(vk, name):
     assert_close(s, g["out_SWD"], TOL, "SWD")
     assert_close(recons_loss + s, g["out_loss"], TOL)
     assert_close(r.grad, g["grad_recons"], TOL)
-    assert_close(z.grad, g["grad_z"], TOL, "grad z")
+    clear = rank_clear_rows(g["in_z"], g["in_proj"])
+    g_ours, g_ref = z.grad.cpu(), g["grad_z"].cpu()
+    den = g_ref.abs().max().item()
+    e_clear = (g_ours[clear] - g_ref[clear]).abs().max().item() / den
+    e_all = (g_ours - g_ref).abs().max().item() / den
+    print("%s: grad rel err %.2e on %d clear rows, %.2e overall (%d rank-ambiguous rows)" %
+          (name, e_clear, int(clear.sum()), e_all, int((~clear).sum())))
+    assert e_clear <= TOL, "grad z on rank-unambiguous rows: %.2e" % e_clear
+    assert int((~clear).sum()) <= max(2, n // 20) and e_all <= 5e-3
 
 
 @pytest.mark.parametrize("n,dim,S,p", [(1000, 128, 200, 2.0), (4100, 128, 50, 2.0), (333, 10, 7, 2.0), (2, 16, 3, 2.0),
@@ -82,19 +106,9 @@ def test_swd_vs_oracle(vk, n, dim, S, p):
     s = F.swd(zg, prior.to(DEV), proj.to(DEV), p, reg)
     (s * 0.7).backward()
     assert_close(s, ref, TOL, "swd")
-    # The gradient goes through the sort permutation: two samples whose fp32 projections are within rounding of
-    # each other may swap ranks between two correct fp32 GEMMs (different summation order), which changes their
-    # gradient by the neighbouring prior gap.  Parity is asserted on the rows none of whose S
-    # projections has a float64 neighbour gap below 2e-6 relative; the rest is reported.
-    lat64 = z.double() @ proj.double().t()
-    srt, order = torch.sort(lat64, dim=0)
-    gaps = (srt[1:] - srt[:-1])
-    big = torch.full((1, S), float("inf"), dtype=torch.float64)
-    near = torch.minimum(torch.cat([gaps, big]), torch.cat([big, gaps])) < 2e-6 * srt.abs().clamp_min(1.0)
-    ambiguous = torch.zeros(n, dtype=torch.bool)
-    for j in range(S):
-        ambiguous[order[near[:, j], j]] = True
-    clear = ~ambiguous
+    # the gradient goes through the sort permutation: see rank_clear_rows
+    clear = rank_clear_rows(z, proj)
+    ambiguous = ~clear
     g_ours, g_ref = (zg.grad / 0.7).cpu(), zc.grad
     den = g_ref.abs().max().item()
     e_all = (g_ours - g_ref).abs().max().item() / den
