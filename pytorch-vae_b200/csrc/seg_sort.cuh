@@ -44,7 +44,7 @@ inline size_t counts_bytes(int64_t segments, int64_t n) { return (size_t)segment
 template <bool FIRST>
 __global__ void __launch_bounds__(kThreads)
 hist_kernel(const uint32_t* __restrict__ keys, int64_t n, int shift, uint32_t* __restrict__ counts) {
-  __shared__ uint32_t h[kWarps][kBins];          // warp-private counters: leaders update them with plain ld/st
+  __shared__ uint32_t h[kWarps][kBins];          // warp-private counters
   const int seg = blockIdx.y, chunk = blockIdx.x;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   for (int i = threadIdx.x; i < kWarps * kBins; i += kThreads) (&h[0][0])[i] = 0;
@@ -59,13 +59,11 @@ hist_kernel(const uint32_t* __restrict__ keys, int64_t n, int shift, uint32_t* _
     if (FIRST && e < n) u = f2ord(u);
     key[i] = u;
   }
+  // counting needs no order: plain shared-memory atomics on the warp-private counters (a few bank-conflict replays
+  // per warp instruction) are ~4x cheaper than building peer masks with nine ballots per key
 #pragma unroll
   for (int i = 0; i < kItems; ++i) {
-    const bool ok = base + i * 32 + lane < n;
-    const uint32_t d = (key[i] >> shift) & 0xFFu;
-    const uint32_t peers = digit_peers(d, ok);
-    if (ok && (__ffs(peers) - 1) == lane) h[warp][d] += __popc(peers);
-    __syncwarp();
+    if (base + i * 32 + lane < n) atomicAdd(&h[warp][(key[i] >> shift) & 0xFFu], 1u);
   }
   __syncthreads();
   uint32_t t = 0;
