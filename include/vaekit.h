@@ -87,7 +87,7 @@ int vk_philox_raw(uint32_t* out, int64_t n_quads, uint64_t seed, uint64_t offset
 /* ---------------------------------------------------------------------------
  * K2  reconstruction term + KL combine       (reference: vanilla_vae.py:134-146,
  *     beta_vae.py:129-152, logcosh_vae.py:125-155, betatc_vae.py:163,
- *     swae.py:121-122, wae_mmd.py:118, vq_vae.py:205)
+ *     swae.py:121-122, wae_mmd.py:118, vq_vae.py:205, info_vae.py:127-133)
  *
  * recon_mode: what out[1] is
  *   VK_RECON_MSE_MEAN     mean((r-x)^2)
@@ -98,10 +98,11 @@ int vk_philox_raw(uint32_t* out, int64_t n_quads, uint64_t seed, uint64_t offset
  *   VK_COMBINE_NONE       out[0] = out[1]
  *   VK_COMBINE_LINEAR     out[0] = out[1] + w * kld
  *   VK_COMBINE_ABS        out[0] = out[1] + w * |kld - C|
+ *   VK_COMBINE_SCALED     out[0] = C * out[1] + w * kld        (info_vae.py:131-132; applies without kl_rows too)
  * out[4] = { loss, recon_loss, kld, -kld }.
  * -------------------------------------------------------------------------*/
 enum { VK_RECON_MSE_MEAN = 0, VK_RECON_MSE_SUM = 1, VK_RECON_LOGCOSH = 2, VK_RECON_MSE_L1_MEAN = 3 };
-enum { VK_COMBINE_NONE = 0, VK_COMBINE_LINEAR = 1, VK_COMBINE_ABS = 2 };
+enum { VK_COMBINE_NONE = 0, VK_COMBINE_LINEAR = 1, VK_COMBINE_ABS = 2, VK_COMBINE_SCALED = 3 };
 
 int vk_elbo_fwd(const float* recons, const float* input, int64_t numel,
                 const float* kl_rows, int64_t rows,

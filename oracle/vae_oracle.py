@@ -251,6 +251,19 @@ def wae_loss(recons: Tensor, input: Tensor, z: Tensor, prior_z: Tensor, *, reg_w
     return {"loss": recons_loss + mmd_loss, "Reconstruction_Loss": recons_loss, "MMD": mmd_loss}
 
 
+
+def infovae_loss(recons: Tensor, input: Tensor, z: Tensor, mu: Tensor, log_var: Tensor, prior_z: Tensor, M_N: float,
+                 *, alpha: float, beta: float, reg_weight: float, kernel_type: str, z_var: float) -> Dict[str, Tensor]:
+    """info_vae.py:117-134 (compute_mmd :203-215 is wae's with weight 1; the scaling sits outside)."""
+    b = input.size(0)
+    bias_corr = b * (b - 1)
+    recons_loss = F.mse_loss(recons, input)
+    mmd_loss = mmd(z, prior_z, 1.0, kernel_type, z_var)
+    kld_loss = torch.mean(kld_rows(mu, log_var), dim=0)
+    loss = beta * recons_loss + (1. - alpha) * M_N * kld_loss + (alpha + reg_weight - 1.) / bias_corr * mmd_loss
+    return {"loss": loss, "Reconstruction_Loss": recons_loss, "MMD": mmd_loss, "KLD": -kld_loss}
+
+
 # --------------------------------------------------------------------------
 # K5: Beta-TC-VAE
 # --------------------------------------------------------------------------

@@ -43,6 +43,7 @@ __device__ __forceinline__ void elbo_finalize(const ElboParams& p, double s0, do
   float loss = recon;
   if (has_kl && p.combine_mode == VK_COMBINE_LINEAR) loss = recon + p.w * kld;
   if (has_kl && p.combine_mode == VK_COMBINE_ABS) loss = recon + p.w * fabsf(kld - p.C);
+  if (p.combine_mode == VK_COMBINE_SCALED) loss = p.C * recon + p.w * kld;      // kld = 0 without kl_rows
   out[0] = loss;
   out[1] = recon;
   out[2] = kld;
@@ -138,13 +139,13 @@ elbo_bwd_kernel(const float* __restrict__ recons, const float* __restrict__ inpu
   const int64_t nthreads = (int64_t)gridDim.x * blockDim.x;
   if (g_kl_rows) {
     float dk = (g_kld ? *g_kld : 0.0f) - (g_negkld ? *g_negkld : 0.0f);
-    if (p.combine_mode == VK_COMBINE_LINEAR) dk += gl * p.w;
+    if (p.combine_mode == VK_COMBINE_LINEAR || p.combine_mode == VK_COMBINE_SCALED) dk += gl * p.w;
     if (p.combine_mode == VK_COMBINE_ABS) dk += gl * p.w * sgnf(out[2] - p.C);
     dk /= (float)p.rows;
     for (int64_t j = tid; j < p.rows; j += nthreads) g_kl_rows[j] = dk;
   }
   if (!g_recons) return;
-  float c = gl + (g_recon ? *g_recon : 0.0f);
+  float c = (p.combine_mode == VK_COMBINE_SCALED ? gl * p.C : gl) + (g_recon ? *g_recon : 0.0f);
   if (MODE == VK_RECON_LOGCOSH) c = c / (p.alpha * (float)p.numel);
   else if (MODE != VK_RECON_MSE_SUM) c = c / (float)p.numel;
   const bool vec = ((reinterpret_cast<uintptr_t>(recons) | reinterpret_cast<uintptr_t>(input) |
@@ -199,7 +200,7 @@ extern "C" int vk_elbo_fwd(const float* recons, const float* input, int64_t nume
                            float* out, void* workspace, int64_t workspace_bytes, void* stream) {
   VK_REQUIRE(recons && input && out && workspace, VK_ERR_BAD_ARG, "elbo_fwd: null pointer");
   VK_REQUIRE(numel > 0 && rows >= 0, VK_ERR_BAD_ARG, "elbo_fwd: bad sizes");
-  VK_REQUIRE(recon_mode >= 0 && recon_mode <= 3 && combine_mode >= 0 && combine_mode <= 2, VK_ERR_BAD_ARG,
+  VK_REQUIRE(recon_mode >= 0 && recon_mode <= 3 && combine_mode >= 0 && combine_mode <= 3, VK_ERR_BAD_ARG,
              "elbo_fwd: unknown mode");
   VK_REQUIRE(workspace_bytes >= kWsBytes, VK_ERR_WORKSPACE, "elbo_fwd: workspace needs %lld bytes", (long long)kWsBytes);
   VK_REQUIRE(!kl_rows || rows > 0, VK_ERR_BAD_ARG, "elbo_fwd: kl_rows given but rows == 0");
@@ -226,7 +227,7 @@ extern "C" int vk_elbo_bwd(const float* recons, const float* input, int64_t nume
                            float* g_kl_rows, void* stream) {
   VK_REQUIRE(recons && input && out, VK_ERR_BAD_ARG, "elbo_bwd: null pointer");
   VK_REQUIRE(numel > 0 && rows >= 0, VK_ERR_BAD_ARG, "elbo_bwd: bad sizes");
-  VK_REQUIRE(recon_mode >= 0 && recon_mode <= 3 && combine_mode >= 0 && combine_mode <= 2, VK_ERR_BAD_ARG,
+  VK_REQUIRE(recon_mode >= 0 && recon_mode <= 3 && combine_mode >= 0 && combine_mode <= 3, VK_ERR_BAD_ARG,
              "elbo_bwd: unknown mode");
   if (!g_recons && !g_kl_rows) return VK_OK;
   ElboParams p{recon_mode, combine_mode, alpha, w, C, numel, rows};

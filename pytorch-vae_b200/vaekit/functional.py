@@ -5,7 +5,7 @@ import torch
 from . import _lib as L
 
 RECON_MSE_MEAN, RECON_MSE_SUM, RECON_LOGCOSH, RECON_MSE_L1_MEAN = 0, 1, 2, 3
-COMBINE_NONE, COMBINE_LINEAR, COMBINE_ABS = 0, 1, 2
+COMBINE_NONE, COMBINE_LINEAR, COMBINE_ABS, COMBINE_SCALED = 0, 1, 2, 3
 
 
 # ---------------------------------------------------------------------------

@@ -1,5 +1,5 @@
 """Model registry with the reference's keys (models/__init__.py:65-91) for the classes on the
-hot path; the remaining reference variants are out of scope."""
+hot path (plus InfoVAE); the remaining reference variants are out of scope."""
 from .base import BaseVAE
 from .vanilla_vae import VanillaVAE
 from .beta_vae import BetaVAE
@@ -8,6 +8,7 @@ from .iwae import IWAE
 from .miwae import MIWAE
 from .vq_vae import VQVAE, VectorQuantizer
 from .wae_mmd import WAE_MMD
+from .info_vae import InfoVAE
 from .swae import SWAE
 from .betatc_vae import BetaTCVAE
 
@@ -22,6 +23,7 @@ vae_models = {
     'VanillaVAE': VanillaVAE,
     'VQVAE': VQVAE,
     'WAE_MMD': WAE_MMD,
+    'InfoVAE': InfoVAE,
     'SWAE': SWAE,
     'BetaTCVAE': BetaTCVAE,
 }

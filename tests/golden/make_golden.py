@@ -238,6 +238,35 @@ def gen_vq():
              grad_latents=ll.grad, grad_codebook=q.embedding.weight.grad)
 
 
+def gen_info():
+    """info_vae.py:117-134 with z chained to (mu, log_var) through reparameterize, as forward() does."""
+    g = torch.Generator().manual_seed(1272)
+    for kt, n, dim, kw in (("imq", 40, 16, dict(alpha=-9.0, beta=10.5, reg_weight=110)),
+                           ("rbf", 96, 128, dict(alpha=-0.5, beta=5.0, reg_weight=100))):
+        m = ref.InfoVAE(3, dim, kernel_type=kt, **kw)
+        r, x = images(g, n, hw=8)
+        mu, lv = gaussians(g, n, dim)
+        eps = torch.randn(n, dim, generator=g)
+        pz = torch.randn(n, dim, generator=g)
+        rl, mul, lvl = leaf(r), leaf(mu), leaf(lv)
+        with injected_noise(eps, pz):
+            z = m.reparameterize(mul, lvl)
+            d = m.loss_function(rl, x, z, mul, lvl, M_N=0.005)
+        d["loss"].backward()
+        with torch.no_grad():
+            pp = m.compute_kernel(pz, pz).mean()
+            zz = m.compute_kernel(z, z).mean()
+            pzt = m.compute_kernel(pz, z).mean()
+        save(f"info_{kt}_d{dim}", in_recons=r, in_input=x, in_mu=mu, in_log_var=lv, noise_eps=eps, noise_prior=pz,
+             hp_M_N=0.005, hp_alpha=kw["alpha"], hp_beta=kw["beta"], hp_reg_weight=kw["reg_weight"], hp_z_var=2.0,
+             out_z=z, out_loss=d["loss"], out_Reconstruction_Loss=d["Reconstruction_Loss"], out_MMD=d["MMD"],
+             out_KLD=d["KLD"], out_term_pp=pp, out_term_zz=zz, out_term_pz=pzt,
+             grad_recons=rl.grad, grad_mu=mul.grad, grad_log_var=lvl.grad)
+
+
 if __name__ == "__main__":
     torch.set_num_threads(4)
-    gen_vanilla(); gen_beta(); gen_logcosh(); gen_iw(); gen_wae(); gen_betatc(); gen_swae(); gen_vq()
+    only = sys.argv[1:]
+    for fn in (gen_vanilla, gen_beta, gen_logcosh, gen_iw, gen_wae, gen_betatc, gen_swae, gen_vq, gen_info):
+        if not only or fn.__name__[4:] in only:
+            fn()

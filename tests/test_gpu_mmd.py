@@ -161,3 +161,58 @@ def test_wae_model_contract(vk):
     with pytest.raises(ZeroDivisionError):
         models["WAE_MMD"](3, 16).loss_function(torch.rand(1, 3, 8, 8, device=DEV), torch.rand(1, 3, 8, 8, device=DEV),
                                                torch.randn(1, 16, device=DEV))
+
+
+@pytest.mark.parametrize("name,kt", [("info_imq_d16", "imq"), ("info_rbf_d128", "rbf")])
+def test_infovae_golden(vk, name, kt, monkeypatch):
+    """SURVEY 8(f) rank 1 (info_vae.py:117-134): the drop-in loss_function on the fixture made from the unmodified
+    reference; the prior draw of compute_mmd is replaced by the fixture's (noise injection) and z is chained to
+    (mu, log_var) with the fixture's eps, so the gradients include the path through the MMD term."""
+    F, models = vk
+    g = load(name, DEV)
+    n, dim = g["in_mu"].shape
+    m = models["InfoVAE"](3, dim, alpha=g["hp_alpha"], beta=g["hp_beta"], reg_weight=g["hp_reg_weight"],
+                          kernel_type=kt, latent_var=g["hp_z_var"])
+    r, mu, lv = leaf(g["in_recons"]), leaf(g["in_mu"]), leaf(g["in_log_var"])
+    z = g["noise_eps"] * torch.exp(0.5 * lv) + mu
+    monkeypatch.setattr(F, "philox_normal", lambda shape, device, rng=None: g["noise_prior"])
+    d = m.loss_function(r, g["in_input"], z, mu, lv, M_N=g["hp_M_N"])
+    assert set(d) == {"loss", "Reconstruction_Loss", "MMD", "KLD"}
+    d["loss"].backward()
+    check_terms(m.last_terms, (g["out_term_pp"], g["out_term_zz"], g["out_term_pz"]), name)
+    scale = max(abs(g["out_term_" + t].item()) for t in ("pp", "zz", "pz"))
+    assert abs(d["MMD"].item() - g["out_MMD"].item()) <= TOL * scale
+    coef = abs(g["hp_alpha"] + g["hp_reg_weight"] - 1.0) / (n * (n - 1))
+    assert abs(d["loss"].item() - g["out_loss"].item()) <= TOL * (abs(g["out_loss"].item()) + coef * scale)
+    assert_close(d["Reconstruction_Loss"], g["out_Reconstruction_Loss"], TOL)
+    assert_close(d["KLD"], g["out_KLD"], TOL)
+    assert_close(r.grad, g["grad_recons"], TOL)
+    assert_close(mu.grad, g["grad_mu"], 2e-5, "grad mu")
+    assert_close(lv.grad, g["grad_log_var"], 2e-5, "grad log_var")
+
+
+def test_infovae_model_contract(vk):
+    _, models = vk
+    torch.manual_seed(1265)
+    kw = dict(alpha=-9.0, beta=10.5, reg_weight=110)                # configs/vae/infovae.yaml
+    m = models["InfoVAE"](3, 128, kernel_type="imq", **kw).to(DEV)
+    x = torch.rand(8, 3, 64, 64, device=DEV)
+    out = m(x, labels=None)
+    assert len(out) == 5 and out[2].shape == (8, 128) and out[1] is x
+    d = m.loss_function(*out, M_N=0.005)
+    d["loss"].backward()
+    assert m.fc_mu.weight.grad is not None and m.fc_var.weight.grad is not None
+    for v in d.values():
+        v.item()
+    ref = O.infovae_loss(out[0].detach().cpu(), x.cpu(), out[2].detach().cpu(), out[3].detach().cpu(),
+                         out[4].detach().cpu(), m.last_prior_z.cpu(), 0.005, kernel_type="imq", z_var=2.0, **kw)
+    assert_close(d["Reconstruction_Loss"], ref["Reconstruction_Loss"], TOL)
+    assert_close(d["KLD"], ref["KLD"], TOL)
+    terms = O.mmd_terms(out[2].detach().cpu(), m.last_prior_z.cpu(), "imq", 2.0)
+    scale = max(abs(t.item()) for t in terms)
+    assert abs(d["MMD"].item() - ref["MMD"].item()) <= TOL * scale
+    assert abs(d["loss"].item() - ref["loss"].item()) <= TOL * (abs(ref["loss"].item()) + 100 / 56 * scale)
+    m.kernel_type = "poly"
+    with pytest.raises(ValueError, match="Undefined kernel type"):
+        m.compute_mmd(out[2].detach())
+    assert m.sample(3, DEV).shape == (3, 3, 64, 64) and m.generate(x).shape == x.shape

@@ -70,3 +70,7 @@ def test_registry_and_constructor_contracts(built):
     hd = [16, 32]
     vae_models["VanillaVAE"](3, 4, hidden_dims=hd)
     assert hd == [32, 16]          # the reference reverses the caller's list in place (vanilla_vae.py:45)
+    m = vae_models["InfoVAE"](3, 16, alpha=-9.0, beta=10.5, reg_weight=110)
+    assert (m.alpha, m.beta, m.reg_weight, m.kernel_type, m.z_var) == (-9.0, 10.5, 110, "imq", 2.0)
+    with pytest.raises(AssertionError, match="alpha must be negative or zero"):
+        vae_models["InfoVAE"](3, 16, alpha=0.5)          # info_vae.py:27

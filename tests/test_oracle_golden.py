@@ -187,3 +187,22 @@ def test_vq(name):
     assert_close(vq_loss, g["out_vq_loss"], TOL)
     assert_close(lat.grad, g["grad_latents"], TOL)
     assert_close(cb.grad, g["grad_codebook"], TOL)
+
+
+@pytest.mark.parametrize("name,kt", [("info_imq_d16", "imq"), ("info_rbf_d128", "rbf")])
+def test_infovae(name, kt):
+    """info_vae.py:117-134 with z chained to (mu, log_var) through reparameterize."""
+    g = load(name)
+    r, mu, lv = leaf(g["in_recons"]), leaf(g["in_mu"]), leaf(g["in_log_var"])
+    z = O.reparameterize(mu, lv, g["noise_eps"])
+    assert_close(z, g["out_z"], TOL)
+    d = O.infovae_loss(r, g["in_input"], z, mu, lv, g["noise_prior"], g["hp_M_N"], alpha=g["hp_alpha"],
+                       beta=g["hp_beta"], reg_weight=g["hp_reg_weight"], kernel_type=kt, z_var=g["hp_z_var"])
+    d["loss"].backward()
+    for k in ("loss", "Reconstruction_Loss", "KLD"):
+        assert_close(d[k], g["out_" + k], TOL, k)
+    scale = max(abs(g["out_term_" + t].item()) for t in ("pp", "zz", "pz"))
+    assert abs(d["MMD"].item() - g["out_MMD"].item()) <= 1e-5 * scale
+    assert_close(r.grad, g["grad_recons"], TOL)
+    assert_close(mu.grad, g["grad_mu"], 2e-5)
+    assert_close(lv.grad, g["grad_log_var"], 2e-5)
