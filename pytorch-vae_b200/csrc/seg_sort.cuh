@@ -126,11 +126,25 @@ scan_kernel(uint32_t* __restrict__ counts, int chunks) {
 // (every peer reads the warp's counter, the highest peer lane bumps it: no leader election, no shuffle), and
 // precombined tables for the two passes over the chunk (counter := position of the warp's run, gdelta := global
 // run start minus chunk-sorted run start).
-template <int PASS, bool PAYLOAD, bool FULL>
+//
+// FUSE (last pass of a key + index sort only): instead of storing the sorted keys and the permutation, the pass
+// consumes them on the spot for the sliced-Wasserstein loss (swae.py:176-179): with `other` = the already sorted
+// keys of the second operand, element r of the sorted order contributes |key_r - other_r|^p to the CTA's partial
+// sum and its derivative goes straight to the source position of the key (g_out[perm_r]).  That removes one write
+// and one read of the sorted keys and of the permutation (3.4 GB at config 5) and a kernel.
+struct LossFuse {
+  const float* other;      // [segments, n] sorted ascending
+  float* g_out;            // [segments, n] in source order, may be NULL
+  double* partials;        // [segments * chunks]
+  float p;
+};
+
+template <int PASS, bool PAYLOAD, bool FULL, bool FUSE>
 __global__ void __launch_bounds__(kThreads)
 scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in, int64_t n,
                const uint32_t* __restrict__ offsets, uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
-               int chunk0, int chunks) {
+               int chunk0, int chunks, LossFuse fuse) {
+  static_assert(!FUSE || (PASS == 3 && PAYLOAD), "the fused loss replaces the stores of the last key+index pass");
   constexpr int shift = 8 * PASS;
   constexpr bool FIRST = PASS == 0, LAST = PASS == 3;
   __shared__ uint32_t wcount[kWarps][kBins];     // per-warp digit counters -> position of the warp's run of the digit
@@ -209,36 +223,67 @@ scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict_
   __syncthreads();
   uint32_t* kout = keys_out + sbase;
   uint32_t* vout = PAYLOAD ? vals_out + sbase : nullptr;
+  float acc = 0.f;
+  const bool p2 = fuse.p == 2.0f;
 #pragma unroll
   for (int i = 0; i < kItems; ++i) {
     const int pos = i * kThreads + threadIdx.x;
     if (FULL || pos < live) {
       const uint32_t u = skey[pos];
       const uint32_t g = gdelta[(u >> shift) & 0xFFu] + (uint32_t)pos;
-      kout[g] = LAST ? ord2f(u) : u;
-      if (PAYLOAD) vout[g] = sval[pos];
+      if (FUSE) {
+        const float w = __uint_as_float(ord2f(u)) - fuse.other[sbase + g];
+        float v, dv;
+        if (p2) { v = w * w; dv = 2.f * w; }
+        else { v = powf(w, fuse.p); dv = fuse.p * powf(w, fuse.p - 1.f); }
+        acc += v;
+        if (fuse.g_out) fuse.g_out[sbase + sval[pos]] = dv;
+      } else {
+        kout[g] = LAST ? ord2f(u) : u;
+        if (PAYLOAD) vout[g] = sval[pos];
+      }
     }
+  }
+  if (FUSE) {
+    __syncthreads();
+    double* red = reinterpret_cast<double*>(skey);      // the sorted chunk is consumed
+    double v[1] = {(double)acc};
+    block_sum<1>(v, red);
+    if (threadIdx.x == 0) fuse.partials[(size_t)seg * chunks + chunk] = v[0];
   }
 }
 
-template <int PASS, bool PAYLOAD>
+// deterministic sum of the per-chunk partials of the fused loss
+__global__ void __launch_bounds__(1024)
+sum_partials_kernel(const double* __restrict__ partials, int64_t count, double* __restrict__ out) {
+  __shared__ double red[32];
+  double t = 0.0;
+  for (int64_t i = threadIdx.x; i < count; i += blockDim.x) t += partials[i];
+  double v[1] = {t};
+  block_sum<1>(v, red);
+  if (threadIdx.x == 0) *out = v[0];
+}
+
+template <int PASS, bool PAYLOAD, bool FUSE = false>
 inline void scatter_pass(dim3 grid, int64_t n, const uint32_t* ki, const uint32_t* vi, const uint32_t* counts,
-                         uint32_t* ko, uint32_t* vo, cudaStream_t st) {
+                         uint32_t* ko, uint32_t* vo, cudaStream_t st, LossFuse fuse = LossFuse{nullptr, nullptr, nullptr, 0.f}) {
   // all chunks but the last are full; when n is a multiple of kChunk the whole grid takes the predicate-free path
   const unsigned full = (unsigned)(n / kChunk);
   if (full > 0)
-    scatter_kernel<PASS, PAYLOAD, true><<<dim3(full, grid.y), kThreads, 0, st>>>(ki, vi, n, counts, ko, vo, 0,
-                                                                                (int)grid.x);
+    scatter_kernel<PASS, PAYLOAD, true, FUSE><<<dim3(full, grid.y), kThreads, 0, st>>>(ki, vi, n, counts, ko, vo, 0,
+                                                                                      (int)grid.x, fuse);
   if (full < grid.x)      // the ragged last chunk of every segment: the bounds-checked instance
-    scatter_kernel<PASS, PAYLOAD, false><<<dim3(1, grid.y), kThreads, 0, st>>>(ki, vi, n, counts, ko, vo, (int)full,
-                                                                               (int)grid.x);
+    scatter_kernel<PASS, PAYLOAD, false, FUSE><<<dim3(1, grid.y), kThreads, 0, st>>>(ki, vi, n, counts, ko, vo,
+                                                                                     (int)full, (int)grid.x, fuse);
 }
 
 // Sorts `segments` rows of length n.  keys: input floats in buf0; result (floats) lands in buf0 again after 4
 // passes (buf0 -> buf1 -> buf0 -> buf1 -> buf0).  vals (PAYLOAD): element indices, result in val0.
+// With `fuse` (PAYLOAD only) the last pass stores nothing: buf0 / val0 are left untouched by it and the loss partials
+// / gradient are produced instead (fuse->g_out may alias buf0 / val0, not buf1 / val1 which the pass reads).
 template <bool PAYLOAD>
 inline int sort(uint32_t* key0, uint32_t* key1, uint32_t* val0, uint32_t* val1, int64_t segments, int64_t n,
-                uint32_t* counts, cudaStream_t st) {
+                uint32_t* counts, cudaStream_t st, const LossFuse* fuse = nullptr) {
   const int chunks = chunks_for(n);
   const dim3 grid(chunks, (unsigned)segments);
   uint32_t *ki = key0, *ko = key1, *vi = val0, *vo = val1;
@@ -250,6 +295,7 @@ inline int sort(uint32_t* key0, uint32_t* key1, uint32_t* val0, uint32_t* val1, 
     if (pass == 0) scatter_pass<0, PAYLOAD>(grid, n, ki, vi, counts, ko, vo, st);
     else if (pass == 1) scatter_pass<1, PAYLOAD>(grid, n, ki, vi, counts, ko, vo, st);
     else if (pass == 2) scatter_pass<2, PAYLOAD>(grid, n, ki, vi, counts, ko, vo, st);
+    else if (PAYLOAD && fuse) scatter_pass<3, true, true>(grid, n, ki, vi, counts, ko, vo, st, *fuse);
     else scatter_pass<3, PAYLOAD>(grid, n, ki, vi, counts, ko, vo, st);
     uint32_t* t = ki; ki = ko; ko = t;
     t = vi; vi = vo; vo = t;

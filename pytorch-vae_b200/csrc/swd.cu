@@ -100,38 +100,7 @@ sgemm_kernel(GemmArgs g) {
   }
 }
 
-// ---- loss + gradient through the permutation ---------------------------------------------------------------------
-__global__ void __launch_bounds__(1024)
-swd_loss_kernel(const float* __restrict__ zs, const uint32_t* __restrict__ perm, const float* __restrict__ ps,
-                int64_t n, float p, float* __restrict__ g_lat, double* __restrict__ partials, unsigned int* ticket,
-                double* __restrict__ sum_out) {
-  const int seg = blockIdx.y;
-  const size_t base = (size_t)seg * n;
-  double acc = 0.0;
-  const bool p2 = p == 2.0f;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-    const float w = zs[base + i] - ps[base + i];
-    float v, dv;
-    if (p2) { v = w * w; dv = 2.f * w; }
-    else { v = powf(w, p); dv = p * powf(w, p - 1.f); }
-    acc += (double)v;
-    if (g_lat) g_lat[base + perm[base + i]] = dv;
-  }
-  __shared__ double red[32];
-  double v[1] = {acc};
-  block_sum<1>(v, red);
-  const unsigned int nblocks = gridDim.x * gridDim.y;
-  const unsigned int bid = blockIdx.y * gridDim.x + blockIdx.x;
-  if (threadIdx.x == 0) partials[bid] = v[0];
-  if (last_block_ticket(ticket, nblocks)) {
-    double t = 0.0;
-    for (unsigned int i = threadIdx.x; i < nblocks; i += blockDim.x) t += ((volatile double*)partials)[i];
-    double tv[1] = {t};
-    __syncthreads();
-    block_sum<1>(tv, red);
-    if (threadIdx.x == 0) *sum_out = tv[0];
-  }
-}
+// (the loss and its gradient through the permutation are fused into the last sort pass: segsort::LossFuse)
 
 // out[0] = reg * (float)(sum / count)   (reg_weight * w_dist.mean(), swae.py:179)
 __global__ void mean_scale_kernel(const double* sum, double count, float reg, float* out) {
@@ -139,7 +108,7 @@ __global__ void mean_scale_kernel(const double* sum, double count, float reg, fl
 }
 
 struct SwdWs {
-  size_t partials, keyZ0, keyZ1, idx0, idx1, keyP0, keyP1, counts, bimg, total;
+  size_t partials, keyZ0, keyZ1, idx0, idx1, keyP0, keyP1, counts, bimg, lossp, total;
 };
 constexpr size_t kBimgBytes = 3u * 256u * 256u * 2u;      // packed theta images of the tcgen05 GEMMs (upper bound)
 inline SwdWs swd_ws(int64_t N, int64_t S) {
@@ -157,6 +126,7 @@ inline SwdWs swd_ws(int64_t N, int64_t S) {
   w.counts = o; o += segsort::counts_bytes(S, N);
   o = (o + 255) & ~(size_t)255;
   w.bimg = o; o += kBimgBytes;
+  w.lossp = o; o += (size_t)S * segsort::chunks_for(N) * sizeof(double);     // per-chunk partials of the fused loss
   w.total = o;
   return w;
 }
@@ -201,24 +171,20 @@ extern "C" int vk_swd_fwd(const float* z, const float* prior, const float* proj,
     rc = check_launch("swd project");
   }
   if (rc != VK_OK) return rc;
-  // 2. sorts
-  rc = segsort::sort<true>((uint32_t*)(ws + w.keyZ0), (uint32_t*)(ws + w.keyZ1), (uint32_t*)(ws + w.idx0),
-                           (uint32_t*)(ws + w.idx1), S, N, (uint32_t*)(ws + w.counts), st);
-  if (rc != VK_OK) return rc;
+  // 2. sorts.  The prior goes first; the last pass of the latent sort (key + source index) then consumes the sorted
+  // prior and produces the loss partials and d/dlat in sample order (segsort::LossFuse) instead of storing its result.
   rc = segsort::sort<false>((uint32_t*)(ws + w.keyP0), (uint32_t*)(ws + w.keyP1), nullptr, nullptr, S, N,
                             (uint32_t*)(ws + w.counts), st);
   if (rc != VK_OK) return rc;
-  // 3. loss and d/dlat (scattered to sample order into the spare key buffer)
-  float* g_lat = grad_unscaled ? (float*)(ws + w.keyZ1) : nullptr;
-  // 1024-thread CTAs of 64 K elements each, launched segment-major: with two resident CTAs per SM about 18 segments
-  // (~75 MB of scatter targets) are in flight at a time, so the random 4-byte writes merge in the 126 MB L2
-  int bx = (int)((N + 65535) / 65536);
-  const int max_bx = (int)(kMaxReduceBlocks * 8 / S) > 0 ? (int)(kMaxReduceBlocks * 8 / S) : 1;
-  if (bx > max_bx) bx = max_bx;
-  VK_REQUIRE((int64_t)bx * S <= (int64_t)kMaxReduceBlocks * 8, VK_ERR_UNSUPPORTED, "swd_fwd: too many projections");
-  swd_loss_kernel<<<dim3(bx, (unsigned)S), 1024, 0, st>>>(latT, (const uint32_t*)(ws + w.idx0), priT, N, p, g_lat,
-                                                        (double*)(ws + w.partials), (unsigned int*)ws, sum_out);
-  rc = check_launch("swd loss");
+  // 3. d/dlat lands in keyZ0: the fused pass reads keyZ1 / idx1 and would have written keyZ0 / idx0
+  float* g_lat = grad_unscaled ? (float*)(ws + w.keyZ0) : nullptr;
+  const segsort::LossFuse fuse{priT, g_lat, (double*)(ws + w.lossp), p};
+  rc = segsort::sort<true>((uint32_t*)(ws + w.keyZ0), (uint32_t*)(ws + w.keyZ1), (uint32_t*)(ws + w.idx0),
+                           (uint32_t*)(ws + w.idx1), S, N, (uint32_t*)(ws + w.counts), st, &fuse);
+  if (rc != VK_OK) return rc;
+  segsort::sum_partials_kernel<<<1, 1024, 0, st>>>((const double*)(ws + w.lossp), S * (int64_t)segsort::chunks_for(N),
+                                                   sum_out);
+  rc = check_launch("swd loss sum");
   if (rc != VK_OK) return rc;
   // 4. dz = g_lat^T theta
   if (grad_unscaled) {
