@@ -8,8 +8,8 @@
 //
 //   B (the small matrix: theta) is packed once per call into three UMMA K-major images [Kp/8][Jp][8] that stay resident
 //   in shared memory for the whole persistent CTA.
-//   A (the tall matrix) never touches shared memory: four producer warps read 128-row tiles with their natural strides,
-//   split in registers and tcgen05.st the three images straight into tensor memory (lane = row, 32-bit column = two
+//   A (the tall matrix) never touches shared memory: four producer warps read 128-row tiles with their natural strides
+//   (software-pipelined one 64-k group ahead), split in registers and tcgen05.st the three images straight into tensor memory (lane = row, 32-bit column = two
 //   consecutive k), from where the MMAs take their A operand.
 //   The accumulator is two column halves in tensor memory, so the epilogue of one half (tcgen05.ld -> strided global
 //   stores, coalesced along whichever of n / j is contiguous in C) overlaps the MMAs of the other.
@@ -104,37 +104,98 @@ gemm3x_kernel(Args g, const uint8_t* __restrict__ bimg) {
 
   if (warp < kProducerWarps) {
     // ===== producers: A rows -> three bf16 images in tensor memory =====
+    // Work unit = one group of kGroup K-steps (64 k) of one tile.  The loads of unit u+1 (which may belong to the
+    // next tile) are issued before unit u is split and stored, so every lane keeps 2 x 256 B of A in flight --
+    // across the wait for the MMAs of the previous tile too; without this the loop exposed one DRAM round trip per
+    // 64 bytes and the whole GEMM ran at 1.2 TB/s.
+    constexpr int kGroup = 4;
     const bool vec = g.a_sk == 1 && (g.K & 3) == 0 && (g.a_sn & 3) == 0 && ((uintptr_t)g.A & 15) == 0;
-    int it = 0;
-    for (int64_t tile = blockIdx.x; tile < g.tiles; tile += gridDim.x, ++it) {
+    const int groups = (kch + kGroup - 1) / kGroup;
+    auto load_unit = [&](float (&v)[16 * kGroup], int64_t tile, int grp) {
       const int64_t n = tile * kRows + warp * 32 + lane;
-      const bool live = n < g.N;
+      const bool live = tile < g.tiles && n < g.N;
       const float* ap = g.A + (live ? n : 0) * g.a_sn;
-      if (it > 0) mbar_wait(bar(2), (it - 1) & 1);           // the MMAs of the previous tile have consumed A
-      fence_after_sync();
-      const uint32_t ta = tA + ((uint32_t)(warp * 32) << 16);
-      for (int kc = 0; kc < kch; ++kc) {
-        float v[16];
+      const int k0 = grp * (16 * kGroup);
+      if (live && k0 + 16 * kGroup <= g.K) {          // whole group in range: no predicates, pointer bumps only
         if (vec) {
+          const float4* q = reinterpret_cast<const float4*>(ap + k0);
 #pragma unroll
-          for (int e = 0; e < 16; e += 4) {
-            const int k = kc * 16 + e;
-            const float4 f = (live && k < g.K) ? __ldg(reinterpret_cast<const float4*>(ap + k)) : make_float4(0.f, 0.f, 0.f, 0.f);
-            v[e] = f.x; v[e + 1] = f.y; v[e + 2] = f.z; v[e + 3] = f.w;
+          for (int e = 0; e < 4 * kGroup; ++e) {
+            const float4 f = __ldg(q + e);
+            v[4 * e] = f.x; v[4 * e + 1] = f.y; v[4 * e + 2] = f.z; v[4 * e + 3] = f.w;
           }
         } else {
+          const float* q = ap + (int64_t)k0 * g.a_sk;
 #pragma unroll
-          for (int e = 0; e < 16; ++e) {
-            const int k = kc * 16 + e;
-            v[e] = (live && k < g.K) ? __ldg(ap + (int64_t)k * g.a_sk) : 0.f;
+          for (int e = 0; e < 16 * kGroup; ++e) { v[e] = __ldg(q); q += g.a_sk; }
+        }
+        return;
+      }
+      // ragged group (tail of K, or rows past N): per 16-k step, skipping steps that lie wholly in the padding
+#pragma unroll
+      for (int kk = 0; kk < kGroup; ++kk) {
+        const int k1 = k0 + 16 * kk;
+        if (!live || k1 >= g.K) {
+#pragma unroll
+          for (int e = 0; e < 16; ++e) v[16 * kk + e] = 0.f;
+        } else if (vec) {
+#pragma unroll
+          for (int e = 0; e < 16; e += 4) {
+            const float4 f = k1 + e < g.K ? __ldg(reinterpret_cast<const float4*>(ap + k1 + e)) : make_float4(0.f, 0.f, 0.f, 0.f);
+            v[16 * kk + e] = f.x; v[16 * kk + e + 1] = f.y; v[16 * kk + e + 2] = f.z; v[16 * kk + e + 3] = f.w;
+          }
+        } else {
+          const float* q = ap + (int64_t)k1 * g.a_sk;
+#pragma unroll
+          for (int e = 0; e < 16; ++e) { v[16 * kk + e] = k1 + e < g.K ? __ldg(q) : 0.f; q += g.a_sk; }
+        }
+      }
+    };
+    // The tile two rounds ahead is pulled into L2 by bulk prefetches (one row or one k-slice per thread), so the
+    // register prefetch one group ahead only has to cover an L2 hit, not a DRAM round trip.
+    const bool pf_rows = vec;                                                       // row-major A: K * 4 bytes per row
+    const bool pf_cols = !vec && g.a_sn == 1 && (g.a_sk & 3) == 0 && ((uintptr_t)g.A & 15) == 0;   // k-major A
+    auto prefetch_tile = [&](int64_t tile) {
+      if (tile >= g.tiles) return;
+      const int64_t n0 = tile * kRows;
+      if (pf_rows) {
+        const int64_t n = n0 + warp * 32 + lane;
+        if (n < g.N) l2_prefetch_bulk(g.A + n * g.a_sn, (uint32_t)g.K * 4u);
+      } else if (pf_cols) {
+        const int64_t rows = g.N - n0 < kRows ? g.N - n0 : kRows;
+        const uint32_t bytes = (uint32_t)(rows * 4) & ~15u;
+        if (bytes)
+          for (int k = warp * 32 + lane; k < g.K; k += 32 * kProducerWarps) l2_prefetch_bulk(g.A + k * g.a_sk + n0, bytes);
+      }
+    };
+    float cur[16 * kGroup], nxt[16 * kGroup];
+    int it = 0;
+    if ((int64_t)blockIdx.x < g.tiles) load_unit(cur, blockIdx.x, 0);
+    prefetch_tile((int64_t)blockIdx.x + gridDim.x);
+    for (int64_t tile = blockIdx.x; tile < g.tiles; tile += gridDim.x, ++it) {
+      const uint32_t ta = tA + ((uint32_t)(warp * 32) << 16);
+      prefetch_tile(tile + 2 * (int64_t)gridDim.x);
+      for (int grp = 0; grp < groups; ++grp) {
+        const bool last = grp + 1 == groups;
+        load_unit(nxt, last ? tile + gridDim.x : tile, last ? 0 : grp + 1);
+        if (grp == 0) {
+          if (it > 0) mbar_wait(bar(2), (it - 1) & 1);         // the MMAs of the previous tile have consumed A
+          fence_after_sync();
+        }
+#pragma unroll
+        for (int kk = 0; kk < kGroup; ++kk) {
+          const int kc = grp * kGroup + kk;
+          if (kc < kch) {
+            uint32_t h[8], m[8], l[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) split3_pair(cur[16 * kk + 2 * e], cur[16 * kk + 2 * e + 1], h[e], m[e], l[e]);
+            tmem_st8(ta + kc * 8, h);
+            tmem_st8(ta + acol + kc * 8, m);
+            tmem_st8(ta + 2 * acol + kc * 8, l);
           }
         }
-        uint32_t h[8], m[8], l[8];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) split3_pair(v[2 * e], v[2 * e + 1], h[e], m[e], l[e]);
-        tmem_st8(ta + kc * 8, h);
-        tmem_st8(ta + acol + kc * 8, m);
-        tmem_st8(ta + 2 * acol + kc * 8, l);
+        for (int e = 0; e < 16 * kGroup; ++e) cur[e] = nxt[e];
       }
       tmem_st_wait();
       fence_before_sync();
@@ -205,7 +266,19 @@ gemm3x_kernel(Args g, const uint8_t* __restrict__ bimg) {
           tmem_ld16(tAcc + ((uint32_t)(q * 32) << 16) + hoff + c0, r);
           tmem_ld_wait16(r);
           const int j0 = hoff + c0;
-          if (n < g.N) {
+          if (n < g.N && j0 + 16 <= g.J) {            // whole block in range: no predicates, pointer bumps only
+            if (vec) {
+              float4* q = reinterpret_cast<float4*>(cp + j0);
+#pragma unroll
+              for (int e = 0; e < 4; ++e)
+                q[e] = make_float4(__uint_as_float(r[4 * e]), __uint_as_float(r[4 * e + 1]), __uint_as_float(r[4 * e + 2]),
+                                   __uint_as_float(r[4 * e + 3]));
+            } else {
+              float* q = cp + (int64_t)j0 * g.c_sj;
+#pragma unroll
+              for (int e = 0; e < 16; ++e) { *q = __uint_as_float(r[e]); q += g.c_sj; }
+            }
+          } else if (n < g.N) {
             if (vec) {
 #pragma unroll
               for (int e = 0; e < 16; e += 4)

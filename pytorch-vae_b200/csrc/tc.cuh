@@ -178,5 +178,10 @@ __device__ __forceinline__ void split_pair(float a, float b, uint32_t& hi2, uint
   asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(lo2) : "f"(b - hb), "f"(a - ha));
 }
 
+// Asynchronous prefetch of [p, p + bytes) into L2 (p 16-byte aligned, bytes a multiple of 16); no completion to wait for.
+__device__ __forceinline__ void l2_prefetch_bulk(const void* p, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
+
 }  // namespace tc
 }  // namespace vk
