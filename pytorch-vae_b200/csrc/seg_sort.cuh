@@ -87,34 +87,53 @@ hist_kernel(const uint32_t* __restrict__ keys, int64_t n, int shift, uint32_t* _
 }
 
 // ---- scan: counts -> exclusive global offsets, in place ----------------------------------------------------------
-__global__ void __launch_bounds__(kBins)
+// One CTA per segment, 4 chunk ranges x 256 digits: every thread totals its range (batches of independent loads),
+// the digit totals are scanned across digits, then the range is rewritten with its running prefix.
+constexpr int kScanQ = 4;
+constexpr int kScanBatch = 8;
+__global__ void __launch_bounds__(kScanQ * kBins)
 scan_kernel(uint32_t* __restrict__ counts, int chunks) {
-  __shared__ uint32_t tot[kBins];
-  const int seg = blockIdx.x, d = threadIdx.x;
-  uint32_t* c = counts + (size_t)seg * chunks * kBins;
-  uint32_t run = 0;
-  for (int b = 0; b < chunks; ++b) {          // coalesced across digits
-    const uint32_t v = c[(size_t)b * kBins + d];
-    c[(size_t)b * kBins + d] = run;
-    run += v;
+  __shared__ uint32_t qtot[kScanQ][kBins];
+  __shared__ uint32_t part[kScanQ][8];
+  const int seg = blockIdx.x, d = threadIdx.x & (kBins - 1), q = threadIdx.x >> 8;
+  uint32_t* c = counts + (size_t)seg * chunks * kBins + d;
+  const int per = (chunks + kScanQ - 1) / kScanQ;
+  const int b0 = q * per, b1 = b0 + per < chunks ? b0 + per : chunks;
+  uint32_t sum = 0;
+  for (int b = b0; b < b1; b += kScanBatch) {          // coalesced across digits
+    uint32_t v[kScanBatch];
+#pragma unroll
+    for (int u = 0; u < kScanBatch; ++u) v[u] = b + u < b1 ? c[(size_t)(b + u) * kBins] : 0u;
+#pragma unroll
+    for (int u = 0; u < kScanBatch; ++u) sum += v[u];
   }
-  tot[d] = run;
+  qtot[q][d] = sum;
   __syncthreads();
-  // exclusive scan of the 256 digit totals (one warp-shuffle scan per 32, then 8 partials)
-  __shared__ uint32_t part[8];
+  uint32_t total = 0, below = 0;
+#pragma unroll
+  for (int i = 0; i < kScanQ; ++i) { const uint32_t t = qtot[i][d]; total += t; if (i < q) below += t; }
+  // exclusive scan of the 256 digit totals (one warp-shuffle scan per 32, then 8 partials), once per chunk range
   const int lane = d & 31, w = d >> 5;
-  uint32_t v = tot[d], incl = v;
+  uint32_t incl = total;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
     const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
     if (lane >= o) incl += t;
   }
-  if (lane == 31) part[w] = incl;
+  if (lane == 31) part[q][w] = incl;
   __syncthreads();
-  uint32_t pre = 0;
-  for (int i = 0; i < w; ++i) pre += part[i];
-  const uint32_t start = pre + incl - v;
-  for (int b = 0; b < chunks; ++b) c[(size_t)b * kBins + d] += start;
+  uint32_t run = incl - total + below;
+  for (int i = 0; i < w; ++i) run += part[q][i];
+  for (int b = b0; b < b1; b += kScanBatch) {
+    uint32_t v[kScanBatch];
+#pragma unroll
+    for (int u = 0; u < kScanBatch; ++u) v[u] = b + u < b1 ? c[(size_t)(b + u) * kBins] : 0u;
+#pragma unroll
+    for (int u = 0; u < kScanBatch; ++u) {
+      if (b + u < b1) c[(size_t)(b + u) * kBins] = run;
+      run += v[u];
+    }
+  }
 }
 
 // ---- scatter -----------------------------------------------------------------------------------------------------
@@ -291,7 +310,7 @@ inline int sort(uint32_t* key0, uint32_t* key1, uint32_t* val0, uint32_t* val1, 
     const int shift = 8 * pass;
     if (pass == 0) hist_kernel<true><<<grid, kThreads, 0, st>>>(ki, n, shift, counts);
     else hist_kernel<false><<<grid, kThreads, 0, st>>>(ki, n, shift, counts);
-    scan_kernel<<<(unsigned)segments, kBins, 0, st>>>(counts, chunks);
+    scan_kernel<<<(unsigned)segments, kScanQ * kBins, 0, st>>>(counts, chunks);
     if (pass == 0) scatter_pass<0, PAYLOAD>(grid, n, ki, vi, counts, ko, vo, st);
     else if (pass == 1) scatter_pass<1, PAYLOAD>(grid, n, ki, vi, counts, ko, vo, st);
     else if (pass == 2) scatter_pass<2, PAYLOAD>(grid, n, ki, vi, counts, ko, vo, st);
