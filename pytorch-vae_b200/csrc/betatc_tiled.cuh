@@ -14,10 +14,22 @@
 
 namespace tiled {
 
-constexpr int kR = 4;          // anchors per warp
-constexpr int kP = 4;          // partners per step
-constexpr int kTW = 4;         // warps per CTA
-constexpr int kTR = 32;        // partner rows staged per tile
+// kR * kP = 16 pairs per step (the transposing butterfly leaves pair q = r * kP + pp in lanes 2q, 2q+1).  Two anchors
+// x eight partners instead of 4 x 4 doubles the number of warps a batch provides (B / kR: 2048 at B = 4096, where
+// the sweeps are bound by how many warps an SM has in flight), and 16-row tiles let four CTAs share an SM.
+#ifndef VK_TC_R
+#define VK_TC_R 4
+#define VK_TC_PSH 2
+#define VK_TC_TR 32
+#define VK_TC_TW 4
+#define VK_TC_MINB 2
+#endif
+constexpr int kR = VK_TC_R;    // anchors per warp
+constexpr int kPSh = VK_TC_PSH;   // log2 kP
+constexpr int kP = 1 << kPSh;  // partners per step
+constexpr int kTW = VK_TC_TW;  // warps per CTA
+constexpr int kTR = VK_TC_TR;  // partner rows staged per tile
+static_assert(kR * kP == 16 && (1 << kPSh) == kP && kTR % kP == 0, "pair layout");
 constexpr int kThreads = 32 * kTW;
 constexpr float kLn2 = 0.6931471805599453f;
 
@@ -51,7 +63,7 @@ __device__ __forceinline__ float pair_reduce(const float (&a)[kR][kP], int lane)
   const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4, b1 = lane & 2;
 #pragma unroll
   for (int t = 0; t < 8; ++t) {
-    const float lo = a[t >> 2][t & 3], hi = a[(t + 8) >> 2][(t + 8) & 3];
+    const float lo = a[t >> kPSh][t & (kP - 1)], hi = a[(t + 8) >> kPSh][(t + 8) & (kP - 1)];
     v8[t] = (b4 ? hi : lo) + __shfl_xor_sync(0xFFFFFFFFu, b4 ? lo : hi, 16);
   }
 #pragma unroll
@@ -90,8 +102,18 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
+__device__ __forceinline__ void cp_async16(float* dst, const float* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+
 template <int DP>
 __device__ __forceinline__ void stage(float* t, const float* __restrict__ src, int B, int D, int j0, float dead) {
+  if (D == DP && j0 + kTR <= B && ((uintptr_t)src & 15) == 0) {
+    // full tile of unpadded rows: one contiguous block, 16-byte copies, no index arithmetic
+    const float* s0 = src + (size_t)j0 * D;
+    for (int e = threadIdx.x * 4; e < kTR * DP; e += kThreads * 4) cp_async16(t + e, s0 + e);
+    return;
+  }
   for (int e = threadIdx.x; e < kTR * DP; e += kThreads) {
     const int r = e / DP, c = e % DP;
     const int j = j0 + r;
@@ -102,7 +124,7 @@ __device__ __forceinline__ void stage(float* t, const float* __restrict__ src, i
 
 // ---- forward -----------------------------------------------------------------------------------------------------
 template <int KD, int NS>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, VK_TC_MINB)
 fwd_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const float* __restrict__ LV,
            const float* __restrict__ Hs, const float* __restrict__ Cs, const double* __restrict__ Cb, TcParams p,
            float* __restrict__ lqz_out, float* __restrict__ lse_out, double* __restrict__ partials, unsigned int* ticket,
@@ -130,7 +152,7 @@ fwd_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const floa
   float rs = 0.f;
   const float dcorr = (p.lw_strat - p.lw_ds) * kLog2e;  // pair (B-2, 0) uses lw_strat where column 0 folds lw_ds
   const int r_special = p.B - 2 - i0;                // anchor slot of row B-2 in this warp (if in [0, kR))
-  const int pq = (lane >> 1) & 3;                    // partner slot of this lane's pair
+  const int pq = (lane >> 1) & (kP - 1);                    // partner slot of this lane's pair
   auto issue = [&](int t, int buf) {
     float* base = sm + buf * kBuf;
     const int j0 = t * kTR;
@@ -181,16 +203,29 @@ fwd_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const floa
               if (SPECIAL && pp == 0 && r == r_special && dbase + lane + 32 * k < p.D) e[pp] += dcorr;
               a[r][pp] = fmaf(d2, ph[pp], a[r][pp]);            // quadratic part of the pair sum
             }
-            const float bmax = fmaxf(fmaxf(e[0], e[1]), fmaxf(e[2], e[3]));
-            const float mn = fmaxf(fmaxf(m[r][k], bmax), -1e30f);
-            const float sum = (ex2f(e[0] - mn) + ex2f(e[1] - mn)) + (ex2f(e[2] - mn) + ex2f(e[3] - mn));
+            float bm[kP / 2];
+#pragma unroll
+            for (int pp = 0; pp < kP / 2; ++pp) bm[pp] = fmaxf(e[2 * pp], e[2 * pp + 1]);
+#pragma unroll
+            for (int h = kP / 4; h >= 1; h >>= 1)
+#pragma unroll
+              for (int pp = 0; pp < h; ++pp) bm[pp] = fmaxf(bm[pp], bm[pp + h]);
+            const float mn = fmaxf(fmaxf(m[r][k], bm[0]), -1e30f);
+            float sm2[kP / 2];
+#pragma unroll
+            for (int pp = 0; pp < kP / 2; ++pp) sm2[pp] = ex2f(e[2 * pp] - mn) + ex2f(e[2 * pp + 1] - mn);
+#pragma unroll
+            for (int h = kP / 4; h >= 1; h >>= 1)
+#pragma unroll
+              for (int pp = 0; pp < h; ++pp) sm2[pp] += sm2[pp + h];
+            const float sum = sm2[0];
             s[r][k] = fmaf(s[r][k], ex2f(m[r][k] - mn), sum);
             m[r][k] = mn;
           }
         }
         // A_ij + D lw_ij complete for the 16 pairs of this step: online logsumexp over j (betatc_vae.py:185-187)
         double val = Tb[jb + pq] - (double)pair_sum<NS>(a, lane, grp, w % NS, xch, step_no);
-        if (SPECIAL && pq == 0 && (lane >> 3) == r_special) val += (double)p.D * (double)dcorr;
+        if (SPECIAL && pq == 0 && (lane >> (kPSh + 1)) == r_special) val += (double)p.D * (double)dcorr;
         const double mn = fmax(fmax(rm, val), -1e300);
         rs = fmaf(rs, ex2f((float)(rm - mn)), ex2f((float)(val - mn)));
         rm = mn;
@@ -200,24 +235,24 @@ fwd_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const floa
     }
     __syncthreads();                                  // everyone is done with this buffer before it is refilled
   }
-  // merge the four partner slots of every anchor (lanes 8r .. 8r+7; the xor-1 neighbour is a duplicate)
+  // merge the kP partner slots of every anchor (lanes 2 kP r .. 2 kP (r+1) - 1; the xor-1 neighbour is a duplicate)
 #pragma unroll
-  for (int o = 2; o <= 4; o <<= 1) {
+  for (int o = 2; o <= kP; o <<= 1) {
     const double om = __shfl_xor_sync(0xFFFFFFFFu, rm, o);
     const float os = __shfl_xor_sync(0xFFFFFFFFu, rs, o);
     const double mn = fmax(fmax(rm, om), -1e300);
     rs = rs * ex2f((float)(rm - mn)) + os * ex2f((float)(om - mn));
     rm = mn;
   }
-  // log q(z_i), i = i0 + (lane >> 3), as an fp32 value plus its fp32 residual (the backward sweeps use both)
+  // log q(z_i), i = i0 + (lane >> (kPSh + 1)), as an fp32 value plus its fp32 residual (the backward sweeps use both)
   const double lqz_d = (rm + (double)log2f(rs)) * 0.6931471805599453;
   const float lqz_mine = (float)lqz_d, lqz_res = (float)(lqz_d - (double)lqz_mine);
   double t_qzx = 0.0, t_qz = 0.0, t_pq = 0.0, t_pz = 0.0;
 #pragma unroll
   for (int r = 0; r < kR; ++r) {
     const int i = i0 + r;
-    const float lqz = __shfl_sync(0xFFFFFFFFu, lqz_mine, 8 * r);
-    const float lqr = __shfl_sync(0xFFFFFFFFu, lqz_res, 8 * r);
+    const float lqz = __shfl_sync(0xFFFFFFFFu, lqz_mine, 2 * kP * r);
+    const float lqr = __shfl_sync(0xFFFFFFFFu, lqz_res, 2 * kP * r);
     float lpq = 0.f, lqzx = 0.f, lpz = 0.f;
 #pragma unroll
     for (int k = 0; k < KD; ++k) {
@@ -272,7 +307,7 @@ fwd_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const floa
 //   d/d ld_ijd = [ (beta - alpha) p_ij + (ga - beta) r_ijd ] / B,   p = softmax_j(A), r = softmax_j(ld + lw) per d
 //   d ld_ijd / d z_id = -2 h_jd (z_id - mu_jd)
 template <int KD, int NS>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, VK_TC_MINB)
 bwd_rows_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const float* __restrict__ LV,
                 const float* __restrict__ Hs, const float* __restrict__ Cs, const double* __restrict__ Cb,
                 const float* __restrict__ lqz, const float* __restrict__ lse, TcParams p, const float* __restrict__ g_loss,
@@ -301,8 +336,8 @@ bwd_rows_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
       gz[r][k] = 0.f;
     }
   // log q(z_i) (log2 units) of the anchor of this lane's pair slot q = lane >> 1
-  const int iq = i0 + (lane >> 3);
-  const int pq = (lane >> 1) & 3;
+  const int iq = i0 + (lane >> (kPSh + 1));
+  const int pq = (lane >> 1) & (kP - 1);
   const double lqz2 = iq < p.B ? ((double)lqz[iq] + (double)lqz[p.B + iq]) * 1.4426950408889634 : (double)INFINITY;
   const float dcorr = (p.lw_strat - p.lw_ds) * kLog2e;
   const int r_special = p.B - 2 - i0;
@@ -332,7 +367,8 @@ bwd_rows_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
     for (int jb = 0; jb < kTR && j0 + jb < p.B; jb += kP) {
       auto step = [&](auto special_c) {
         constexpr bool SPECIAL = decltype(special_c)::value;
-        float pm[KD][kP], ph[KD][kP], pc[KD][kP];
+        // the staged partner values are read from shared memory in both phases rather than held across the pair
+        // reduction: 3 KD kP registers would cost a resident CTA per SM
         float a[kR][kP];
 #pragma unroll
         for (int r = 0; r < kR; ++r)
@@ -343,19 +379,17 @@ bwd_rows_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
 #pragma unroll
           for (int pp = 0; pp < kP; ++pp) {
             const int o = (jb + pp) * DP + dbase + lane + 32 * k;
-            pm[k][pp] = Tm[o]; ph[k][pp] = Th[o]; pc[k][pp] = Tc[o];
-          }
+            const float pm = Tm[o], ph = Th[o];
 #pragma unroll
-          for (int r = 0; r < kR; ++r)
-#pragma unroll
-            for (int pp = 0; pp < kP; ++pp) {
-              const float df = z[r][k] - pm[k][pp];
-              a[r][pp] = fmaf(df * df, ph[k][pp], a[r][pp]);         // quadratic part of the pair sum
+            for (int r = 0; r < kR; ++r) {
+              const float df = z[r][k] - pm;
+              a[r][pp] = fmaf(df * df, ph, a[r][pp]);                // quadratic part of the pair sum
             }
+          }
         }
         // softmax weight of (i, j) in log q(z_i), times its coefficient; dead partners / anchors give exactly 0
         double x = (Tb[jb + pq] - (double)pair_sum<NS>(a, lane, grp, w % NS, xch, step_no)) - lqz2;
-        if (SPECIAL && pq == 0 && (lane >> 3) == r_special) x += (double)p.D * (double)dcorr;
+        if (SPECIAL && pq == 0 && (lane >> (kPSh + 1)) == r_special) x += (double)p.D * (double)dcorr;
         const float wq = cq * ex2f((float)x);
         float cqp[kR][kP];
 #pragma unroll
@@ -365,17 +399,20 @@ bwd_rows_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
 #pragma unroll
         for (int k = 0; k < KD; ++k)
 #pragma unroll
-          for (int r = 0; r < kR; ++r)
+          for (int pp = 0; pp < kP; ++pp) {
+            const int o = (jb + pp) * DP + dbase + lane + 32 * k;
+            const float pm = Tm[o], ph = Th[o], pc = Tc[o];
 #pragma unroll
-            for (int pp = 0; pp < kP; ++pp) {
-              const float df = z[r][k] - pm[k][pp];
-              const float t = ph[k][pp] * df;                        // h (z - mu) log2e
-              float e = fmaf(-df, t, pc[k][pp]);
+            for (int r = 0; r < kR; ++r) {
+              const float df = z[r][k] - pm;
+              const float t = ph * df;                               // h (z - mu) log2e
+              float e = fmaf(-df, t, pc);
               if (SPECIAL && pp == 0 && r == r_special && dbase + lane + 32 * k < p.D) e += dcorr;
               const float rr = ex2f(e - l2[r][k]);                   // softmax weight inside LSE_j[i, d]
               const float cf = fmaf(cp, rr, cqp[r][pp]);             // dL / d ld_ijd
               gz[r][k] = fmaf(-cf, t, gz[r][k]);
             }
+          }
       };
       if (j0 + jb == 0 && r_special >= 0 && r_special < kR) step(std::true_type{}); else step(std::false_type{});
       ++step_no;
@@ -402,7 +439,7 @@ bwd_rows_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
 // ---- backward, column sweep: d/dmu_j, d/dlog_var_j -------------------------------------------------------------------
 //   d ld_ijd / d mu_jd = 2 h_jd (z_id - mu_jd) ;  d ld_ijd / d lv_jd = h_jd (z_id - mu_jd)^2 - 1/2
 template <int KD, int NS>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, VK_TC_MINB)
 bwd_cols_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const float* __restrict__ LV,
                 const float* __restrict__ Hs, const float* __restrict__ Cs, const double* __restrict__ Cb,
                 const float* __restrict__ lqz, const float* __restrict__ lse, TcParams p, const float* __restrict__ g_loss,
@@ -433,9 +470,9 @@ bwd_cols_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
       g0[r][k] = 0.f; g1[r][k] = 0.f;
     }
   const float dcorr = (p.lw_strat - p.lw_ds) * kLog2e;
-  const int pq = (lane >> 1) & 3;                    // partner slot of this lane's pair
-  const bool anchor_dead = c0 + (lane >> 3) >= p.B;
-  const double cbq = anchor_dead ? 0.0 : Cb[c0 + (lane >> 3)];
+  const int pq = (lane >> 1) & (kP - 1);                    // partner slot of this lane's pair
+  const bool anchor_dead = c0 + (lane >> (kPSh + 1)) >= p.B;
+  const double cbq = anchor_dead ? 0.0 : Cb[c0 + (lane >> (kPSh + 1))];
   auto issue = [&](int t, int buf) {
     float* base = sm + buf * kBuf;
     const int i0 = t * kTR;
@@ -462,7 +499,6 @@ bwd_cols_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
       const int pp_special = p.B - 2 - (i0 + ib);     // partner slot of row B-2 in this step (if in [0, kP))
       auto step = [&](auto special_c) {
         constexpr bool SPECIAL = decltype(special_c)::value;
-        float pz[KD][kP], pl[KD][kP];
         float a[kR][kP];
 #pragma unroll
         for (int r = 0; r < kR; ++r)
@@ -472,20 +508,17 @@ bwd_cols_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
         for (int k = 0; k < KD; ++k) {
 #pragma unroll
           for (int pp = 0; pp < kP; ++pp) {
-            const int o = (ib + pp) * DP + dbase + lane + 32 * k;
-            pz[k][pp] = Tz[o]; pl[k][pp] = Tl[o];
-          }
+            const float pz = Tz[(ib + pp) * DP + dbase + lane + 32 * k];
 #pragma unroll
-          for (int r = 0; r < kR; ++r)
-#pragma unroll
-            for (int pp = 0; pp < kP; ++pp) {
-              const float df = pz[k][pp] - mu[r][k];
+            for (int r = 0; r < kR; ++r) {
+              const float df = pz - mu[r][k];
               a[r][pp] = fmaf(df * df, hs[r][k], a[r][pp]);          // quadratic part of the pair sum
             }
+          }
         }
         double x = (cbq - (double)pair_sum<NS>(a, lane, grp, w % NS, xch, step_no)) -
                    ((double)Tq[ib + pq] + (double)Tq[kTR + ib + pq]) * 1.4426950408889634;
-        if (SPECIAL && (lane >> 3) == 0 && pq == pp_special) x += (double)p.D * (double)dcorr;
+        if (SPECIAL && (lane >> (kPSh + 1)) == 0 && pq == pp_special) x += (double)p.D * (double)dcorr;
         const float wq = anchor_dead ? 0.f : cq * ex2f((float)x);
         float cqp[kR][kP];
 #pragma unroll
@@ -495,20 +528,22 @@ bwd_cols_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
 #pragma unroll
         for (int k = 0; k < KD; ++k)
 #pragma unroll
-          for (int r = 0; r < kR; ++r)
+          for (int pp = 0; pp < kP; ++pp) {
+            const int o = (ib + pp) * DP + dbase + lane + 32 * k;
+            const float pz = Tz[o], pl = Tl[o];
 #pragma unroll
-            for (int pp = 0; pp < kP; ++pp) {
-              const float df = pz[k][pp] - mu[r][k];
+            for (int r = 0; r < kR; ++r) {
+              const float df = pz - mu[r][k];
               const float t = hs[r][k] * df;                         // h (z - mu) log2e
               const float u = df * t;                                // h (z - mu)^2 log2e
               float e = cs[r][k] - u;
               if (SPECIAL && r == 0 && pp == pp_special && dbase + lane + 32 * k < p.D) e += dcorr;
-              const float rr = ex2f(fmaf(-pl[k][pp], kLog2e, e));    // softmax weight inside LSE_j[i, d]
+              const float rr = ex2f(fmaf(-pl, kLog2e, e));           // softmax weight inside LSE_j[i, d]
               const float cf = fmaf(cp, rr, cqp[r][pp]);             // dL / d ld_ijd
               g0[r][k] = fmaf(cf, t, g0[r][k]);
               g1[r][k] = fmaf(cf, fmaf(u, kLn2, -0.5f), g1[r][k]);   // h (z - mu)^2 - 1/2
-
             }
+          }
       };
       if (c0 == 0 && pp_special >= 0 && pp_special < kP) step(std::true_type{}); else step(std::false_type{});
       ++step_no;

@@ -1,3 +1,5 @@
-timeout 600 python -m pytest tests/test_gpu_swd.py tests/test_gpu_gemm.py -x -q > gpurun_out/pytest_swd.log 2>&1; tail -3 gpurun_out/pytest_swd.log
-timeout 300 python scripts/time_ops.py swd 2>&1 | grep -v torch.sort | tail -3
-timeout 300 python bench.py --workload swae --steps 5 --warmup 3 --no-cpu > gpurun_out/b_swae.json 2>gpurun_out/b_swae.err && ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/launches_swae_r01j.csv python bench.py --workload swae --steps 1 --warmup 1 --no-cpu > /dev/null 2>&1; python scripts/summarize_launches.py gpurun_out/launches_swae_r01j.csv 2>&1 | head -4;  grep -n "gemm3x" gpurun_out/launches_swae_r01j.csv | awk -F'","' '{print $NF}' | tr -d '"' | tr '\n' ' '
+for lib in libvaekit.so libvaekit_tcB.so libvaekit_tcC.so; do
+  echo "== $lib"
+  VAEKIT_LIB=$PWD/pytorch-vae_b200/vaekit/_lib/$lib timeout 300 python scripts/time_ops.py tc 2>&1 | tail -2
+  VAEKIT_LIB=$PWD/pytorch-vae_b200/vaekit/_lib/$lib timeout 300 python -m pytest tests/test_gpu_betatc.py -x -q 2>&1 | tail -1
+done
