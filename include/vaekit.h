@@ -195,12 +195,19 @@ int vk_scale_by_scalar(const float* in, const float* g, float factor, int64_t n,
  * Steps: fp32 projection GEMM stored projection-major, segmented LSD radix sort (8-bit digits; key + sample index
  * for z, key-only for the prior), loss + scatter of d/dlat, fp32 GEMM back to [N, D].
  * vk_mean_scale: out[0] = scale * (float)(sum / count)     (reg_weight * w_dist.mean(), swae.py:179)
+ * vk_swd_segments_fwd: the middle of vk_swd_fwd on its own, for the multi-GPU decomposition in which ranks project
+ * their own rows and exchange projected values (all-to-all): lat, pri [S, N] projection-major segments (swae.py:176-177
+ * sorts exactly these rows).  On return *sum_out = sum (sort(lat) - sort(pri))^p, `lat` holds d sum / d lat in SAMPLE
+ * order when want_grad (else garbage) and `pri` holds the sorted prior projections.
  * vk_seg_sort: the sort on its own -- keys [segments, n] fp32 ascending in place, perm_out (uint32 source index
  * of every sorted element) or NULL.
  * -------------------------------------------------------------------------*/
 int64_t vk_swd_workspace_bytes(int64_t N, int64_t S);
 int vk_swd_fwd(const float* z, const float* prior, const float* proj, int64_t N, int64_t D, int64_t S, float p,
                double* sum_out, float* grad_unscaled, void* workspace, int64_t workspace_bytes, void* stream);
+int64_t vk_swd_segments_workspace_bytes(int64_t N, int64_t S);
+int vk_swd_segments_fwd(float* lat, float* pri, int64_t N, int64_t S, float p, double* sum_out, int want_grad,
+                        void* workspace, int64_t workspace_bytes, void* stream);
 int vk_mean_scale(const double* sum, double count, float scale, float* out, void* stream);
 int64_t vk_seg_sort_workspace_bytes(int64_t segments, int64_t n);
 int vk_seg_sort(float* keys, uint32_t* perm_out, int64_t segments, int64_t n, void* workspace,

@@ -131,6 +131,41 @@ inline SwdWs swd_ws(int64_t N, int64_t S) {
   return w;
 }
 
+
+// Sorts + loss + d/dlat for S projection-major segments of N keys each.  The prior goes first; the last pass of the
+// latent sort (key + source index) then consumes the sorted prior and produces the loss partials and d/dlat in sample
+// order (segsort::LossFuse) instead of storing its result: d/dlat lands in `lat` (the fused pass reads keyZ1 / idx1
+// and would have written lat / idx0).  `pri` holds the sorted prior projections afterwards.
+inline int swd_segments(float* lat, float* pri, uint32_t* keyZ1, uint32_t* idx0, uint32_t* idx1, uint32_t* keyP1,
+                        uint32_t* counts, double* lossp, int64_t N, int64_t S, float p, double* sum_out, bool want_grad,
+                        cudaStream_t st) {
+  int rc = segsort::sort<false>((uint32_t*)pri, keyP1, nullptr, nullptr, S, N, counts, st);
+  if (rc != VK_OK) return rc;
+  const segsort::LossFuse fuse{pri, want_grad ? lat : nullptr, lossp, p};
+  rc = segsort::sort<true>((uint32_t*)lat, keyZ1, idx0, idx1, S, N, counts, st, &fuse);
+  if (rc != VK_OK) return rc;
+  segsort::sum_partials_kernel<<<1, 1024, 0, st>>>(lossp, S * (int64_t)segsort::chunks_for(N), sum_out);
+  return check_launch("swd loss sum");
+}
+
+struct SegWs {
+  size_t keyZ1, idx0, idx1, keyP1, counts, lossp, total;
+};
+inline SegWs seg_ws(int64_t N, int64_t S) {
+  SegWs w;
+  const size_t seg = ((size_t)S * N * 4 + 255) & ~(size_t)255;
+  size_t o = kWsHeader;
+  w.keyZ1 = o; o += seg;
+  w.idx0 = o; o += seg;
+  w.idx1 = o; o += seg;
+  w.keyP1 = o; o += seg;
+  w.counts = o; o += segsort::counts_bytes(S, N);
+  o = (o + 255) & ~(size_t)255;
+  w.lossp = o; o += (size_t)S * segsort::chunks_for(N) * sizeof(double);
+  w.total = o;
+  return w;
+}
+
 }  // namespace
 }  // namespace vk
 
@@ -171,21 +206,12 @@ extern "C" int vk_swd_fwd(const float* z, const float* prior, const float* proj,
     rc = check_launch("swd project");
   }
   if (rc != VK_OK) return rc;
-  // 2. sorts.  The prior goes first; the last pass of the latent sort (key + source index) then consumes the sorted
-  // prior and produces the loss partials and d/dlat in sample order (segsort::LossFuse) instead of storing its result.
-  rc = segsort::sort<false>((uint32_t*)(ws + w.keyP0), (uint32_t*)(ws + w.keyP1), nullptr, nullptr, S, N,
-                            (uint32_t*)(ws + w.counts), st);
+  // 2.+3. sorts, loss and d/dlat (lands in keyZ0, sample order)
+  rc = swd_segments(latT, priT, (uint32_t*)(ws + w.keyZ1), (uint32_t*)(ws + w.idx0), (uint32_t*)(ws + w.idx1),
+                    (uint32_t*)(ws + w.keyP1), (uint32_t*)(ws + w.counts), (double*)(ws + w.lossp), N, S, p, sum_out,
+                    grad_unscaled != nullptr, st);
   if (rc != VK_OK) return rc;
-  // 3. d/dlat lands in keyZ0: the fused pass reads keyZ1 / idx1 and would have written keyZ0 / idx0
-  float* g_lat = grad_unscaled ? (float*)(ws + w.keyZ0) : nullptr;
-  const segsort::LossFuse fuse{priT, g_lat, (double*)(ws + w.lossp), p};
-  rc = segsort::sort<true>((uint32_t*)(ws + w.keyZ0), (uint32_t*)(ws + w.keyZ1), (uint32_t*)(ws + w.idx0),
-                           (uint32_t*)(ws + w.idx1), S, N, (uint32_t*)(ws + w.counts), st, &fuse);
-  if (rc != VK_OK) return rc;
-  segsort::sum_partials_kernel<<<1, 1024, 0, st>>>((const double*)(ws + w.lossp), S * (int64_t)segsort::chunks_for(N),
-                                                   sum_out);
-  rc = check_launch("swd loss sum");
-  if (rc != VK_OK) return rc;
+  float* g_lat = grad_unscaled ? latT : nullptr;
   // 4. dz = g_lat^T theta
   if (grad_unscaled) {
     if (g3::fits((int)D, (int)S)) {
@@ -200,6 +226,26 @@ extern "C" int vk_swd_fwd(const float* z, const float* prior, const float* proj,
     }
   }
   return rc;
+}
+
+extern "C" int64_t vk_swd_segments_workspace_bytes(int64_t N, int64_t S) {
+  if (N < 1 || S < 1) return -1;
+  return (int64_t)seg_ws(N, S).total;
+}
+
+extern "C" int vk_swd_segments_fwd(float* lat, float* pri, int64_t N, int64_t S, float p, double* sum_out, int want_grad,
+                                   void* workspace, int64_t workspace_bytes, void* stream) {
+  VK_REQUIRE(lat && pri && sum_out && workspace, VK_ERR_BAD_ARG, "swd_segments_fwd: null pointer");
+  VK_REQUIRE(N >= 1 && S >= 1, VK_ERR_BAD_ARG, "swd_segments_fwd: empty shape N=%lld S=%lld", (long long)N, (long long)S);
+  VK_REQUIRE(N < ((int64_t)1 << 32) && S <= 65535, VK_ERR_UNSUPPORTED, "swd_segments_fwd: N=%lld or S=%lld too large",
+             (long long)N, (long long)S);
+  const SegWs w = seg_ws(N, S);
+  VK_REQUIRE(workspace_bytes >= (int64_t)w.total, VK_ERR_WORKSPACE, "swd_segments_fwd: workspace %lld < %lld",
+             (long long)workspace_bytes, (long long)w.total);
+  uint8_t* ws = (uint8_t*)workspace;
+  return swd_segments(lat, pri, (uint32_t*)(ws + w.keyZ1), (uint32_t*)(ws + w.idx0), (uint32_t*)(ws + w.idx1),
+                      (uint32_t*)(ws + w.keyP1), (uint32_t*)(ws + w.counts), (double*)(ws + w.lossp), N, S, p, sum_out,
+                      want_grad != 0, (cudaStream_t)stream);
 }
 
 extern "C" int64_t vk_gemm_nt_workspace_bytes(void) { return (int64_t)(kWsHeader + kBimgBytes); }

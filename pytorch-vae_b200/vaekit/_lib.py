@@ -36,6 +36,8 @@ _SIGNATURES = {
     "vk_swd_workspace_bytes": ([_i64, _i64], _i64),
     "vk_swd_fwd": ([_p, _p, _p, _i64, _i64, _i64, _f, _p, _p, _p, _i64, _p], _i),
     "vk_mean_scale": ([_p, C.c_double, _f, _p, _p], _i),
+    "vk_swd_segments_workspace_bytes": ([_i64, _i64], _i64),
+    "vk_swd_segments_fwd": ([_p, _p, _i64, _i64, _f, _p, _i, _p, _i64, _p], _i),
     "vk_seg_sort_workspace_bytes": ([_i64, _i64], _i64),
     "vk_seg_sort": ([_p, _p, _i64, _i64, _p, _i64, _p], _i),
     "vk_gemm_nt_workspace_bytes": ([], _i64),

@@ -8,9 +8,11 @@ with the quadratic / sort work split across ranks.
   its rows against all N columns (vk_mmd_fwd row range).  prior_z is regenerated locally from the shared Philox
   (seed, offset) -- no traffic.  Each rank has complete rows, so the gradient of its own z rows is local: no
   reduce-scatter in backward.  One all-reduce of three float64 sums.
-* SWD (swae.py:151-179): all-gather z; rank r owns a slice of the projections, projects all N rows on them, sorts,
-  and produces a partial [N, D] gradient; reduce-scatter (sum) gives each rank the gradient of its own rows, one
-  all-reduce of the float64 loss sum.
+* SWD (swae.py:151-179): every rank projects its own rows (z and its slice of the shared prior stream) on all S
+  projections; ONE all-to-all of the projected values gives rank r all N values of its S / world projections, which it
+  sorts; d/dlat goes back through a second all-to-all and the gradient GEMM runs on the rank's own rows; one
+  all-reduce of the float64 loss sum.  (The older all-gather-z / reduce-scatter-gradient form is kept as
+  exchange="all_gather".)
 
 The batch-local ops (K1-K3, K7) need no collective at all: shard the batch, which is what DDP already does.
 The plumbing helpers are backend-agnostic (NCCL on GPUs; gloo in the CPU tests).
@@ -171,7 +173,93 @@ class _ShardedSwd(torch.autograd.Function):
         return F.scale_by_scalar(ctx.saved_tensors[0], g.contiguous(), ctx.factor), None, None, None, None
 
 
-def sharded_swd(z_local, proj, p, reg_weight, group=None):
+# ---- exchange of projected values (all-to-all): every stage of the SWD shrinks with the world size ----------------
+def exchange_segments(local: torch.Tensor, group=None) -> torch.Tensor:
+    """[S, C, n] on every rank (all S projections of the rank's own n rows, C channels) -> [S_r, C, world * n]: all rows
+    of the projections [s0, s1) this rank owns (plan_projections), rows in rank-major (= global) order."""
+    if not _active(group):
+        return local.contiguous()
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    S, C, n = local.shape
+    splits = [b - a for a, b in (plan_projections(S, world, r) for r in range(world))]
+    mine = splits[rank]
+    recv = torch.empty((world * mine, C, n), dtype=local.dtype, device=local.device)
+    dist.all_to_all_single(recv, local.contiguous(), output_split_sizes=[mine] * world, input_split_sizes=splits,
+                           group=group)
+    return recv.view(world, mine, C, n).permute(1, 2, 0, 3).reshape(mine, C, world * n)
+
+
+def return_segments(seg: torch.Tensor, num_projections: int, group=None) -> torch.Tensor:
+    """Inverse of exchange_segments for one channel: [S_r, world * n] (this rank's projections, all rows) -> [S, n]
+    (all projections, this rank's rows)."""
+    if not _active(group):
+        return seg.contiguous()
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    mine, N = seg.shape
+    n = N // world
+    splits = [b - a for a, b in (plan_projections(num_projections, world, r) for r in range(world))]
+    send = seg.view(mine, world, n).permute(1, 0, 2).contiguous().view(world * mine, n)
+    recv = torch.empty((num_projections, n), dtype=seg.dtype, device=seg.device)
+    dist.all_to_all_single(recv, send, output_split_sizes=splits, input_split_sizes=[mine] * world, group=group)
+    return recv
+
+
+def local_prior_rows(n_local: int, D: int, device, rng, rank: int) -> torch.Tensor:
+    """Rows [rank * n_local, (rank + 1) * n_local) of the [N, D] prior sample of Philox stream `rng`: noise is a pure
+    function of (seed, offset, element index) with one counter per four elements, so a rank's row block is the same
+    stream started rank * n_local * D / 4 counters later -- nothing is communicated."""
+    from . import functional as F
+    first = rank * n_local * D
+    if first % 4 != 0:
+        raise ValueError("sharded prior needs n_local * D to be a multiple of 4 (got %d x %d)" % (n_local, D))
+    return F.philox_normal((n_local, D), device, rng=(rng[0], rng[1] + first // 4))
+
+
+class _ShardedSwdA2A(torch.autograd.Function):
+    """swae.py:151-179 on the global batch with every stage sharded: rank r projects ITS rows (z and the locally
+    regenerated prior rows) on all S projections, one all-to-all hands rank r all N values of its S / world projections,
+    it sorts them and forms the loss partial and d/dlat, one all-to-all returns d/dlat to the row owners, and the
+    gradient GEMM runs on the rank's own rows.  No [N, D] tensor is gathered or reduced."""
+
+    @staticmethod
+    def forward(ctx, z_local, proj, p, reg_weight, group):
+        from . import functional as F
+        world, rank = world_rank(group)
+        n, D = z_local.shape
+        S = proj.shape[0]
+        N = n * world
+        rng = shared_rng(z_local.device, N * D, group)
+        prior_local = local_prior_rows(n, D, z_local.device, rng, rank)
+        both = torch.empty((S, 2, n), dtype=torch.float32, device=z_local.device)
+        F.swd_project(z_local, proj, out=both[:, 0, :])
+        F.swd_project(prior_local, proj, out=both[:, 1, :])
+        seg = exchange_segments(both, group)                       # [S_r, 2, N]
+        lat, pri = seg[:, 0, :].contiguous(), seg[:, 1, :].contiguous()
+        total = F.swd_segments(lat, pri, p, want_grad=True)        # lat <- d sum / d lat (sample order)
+        reduce_sum_(total, group)
+        g_local = return_segments(lat, S, group)                   # [S, n]
+        grad_local = F.swd_project_back(g_local, proj)
+        ctx.save_for_backward(grad_local)
+        count = float(N) * float(S)
+        ctx.factor = reg_weight / count
+        ctx.set_materialize_grads(False)
+        return F.mean_scale(total, count, reg_weight)
+
+    @staticmethod
+    def backward(ctx, g):
+        from . import functional as F
+        if g is None:
+            return (None,) * 5
+        return F.scale_by_scalar(ctx.saved_tensors[0], g.contiguous(), ctx.factor), None, None, None, None
+
+
+def sharded_swd(z_local, proj, p, reg_weight, group=None, exchange="all_to_all"):
     """Sliced-Wasserstein distance of the GLOBAL batch; `proj` [S, D] must be identical on every rank
-    (use shared_tensor_ on the reference's CPU-generated directions)."""
-    return _ShardedSwd.apply(z_local, proj, float(p), float(reg_weight), group)
+    (use shared_tensor_ on the reference's CPU-generated directions).  exchange = "all_to_all" (projected values travel;
+    every stage shrinks with the world size) or "all_gather" (z travels; each rank projects all rows on its slice of
+    the projections and the [N, D] gradient is reduce-scattered -- kept for shapes the tcgen05 GEMM does not take)."""
+    if exchange == "all_to_all":
+        return _ShardedSwdA2A.apply(z_local, proj, float(p), float(reg_weight), group)
+    if exchange == "all_gather":
+        return _ShardedSwd.apply(z_local, proj, float(p), float(reg_weight), group)
+    raise ValueError("Unknown exchange %r" % (exchange,))

@@ -390,6 +390,63 @@ def swd(z, prior_z, proj, p, reg_weight):
     return _Swd.apply(z, prior_z, proj, float(p), float(reg_weight))
 
 
+def swd_project(x, proj, out=None):
+    """Projection-major projections out[s, n] = x[n, :] . proj[s, :] (the transposed z.matmul(proj) of swae.py:171-176)
+    with the fp32-grade tcgen05 GEMM (vk_gemm_nt, transposed store).  `out` may be a [S, n] view with stride(1) == 1
+    (e.g. one channel of an exchange buffer)."""
+    L.require(x, "x", dims=(2,)); L.require(proj, "projections", dims=(2,))
+    if x.shape[1] != proj.shape[1]:
+        raise RuntimeError("vaekit: rows %s and projections %s do not fit together" % (tuple(x.shape), tuple(proj.shape)))
+    n, D = x.shape
+    S = proj.shape[0]
+    if out is None:
+        out = torch.empty((S, n), dtype=torch.float32, device=x.device)
+    if tuple(out.shape) != (S, n) or (n > 1 and out.stride(1) != 1) or out.dtype != torch.float32:
+        raise RuntimeError("vaekit: swd_project output must be a [S, n] fp32 view contiguous along n")
+    if n * S == 0:
+        return out
+    ws = L.workspace(x.device, int(L.lib().vk_gemm_nt_workspace_bytes()))
+    with torch.cuda.device(x.device):
+        L.call("gemm_nt", L.ptr(x), x.stride(0), x.stride(1), L.ptr(proj), proj.stride(0), proj.stride(1), L.ptr(out), 1,
+               out.stride(0), n, S, D, L.ptr(ws), ws.numel(), L.stream_ptr())
+    return out
+
+
+def swd_segments(lat, pri, p, want_grad=True):
+    """Sorts + loss (+ d/dlat through the permutation) of [S, N] projection-major segments (vk_swd_segments_fwd).
+    Both inputs are consumed: on return `lat` holds d sum / d lat in sample order (when want_grad).
+    Returns sum[1] float64 device tensor."""
+    L.require(lat, "lat", dims=(2,)); L.require(pri, "pri", dims=(2,))
+    if lat.shape != pri.shape or not lat.is_contiguous() or not pri.is_contiguous():
+        raise RuntimeError("vaekit: swd_segments needs two contiguous [S, N] tensors of the same shape")
+    S, N = lat.shape
+    total = torch.zeros(1, dtype=torch.float64, device=lat.device)
+    if S * N == 0:
+        return total
+    ws = L.workspace(lat.device, int(L.lib().vk_swd_segments_workspace_bytes(N, S)))
+    with torch.cuda.device(lat.device):
+        L.call("swd_segments_fwd", L.ptr(lat), L.ptr(pri), N, S, p, L.ptr(total), 1 if want_grad else 0, L.ptr(ws),
+               ws.numel(), L.stream_ptr())
+    return total
+
+
+def swd_project_back(g_lat, proj):
+    """dz[n, :] = sum_s g_lat[s, n] * proj[s, :]  (the gradient GEMM of swae.py:171 through vk_gemm_nt)."""
+    L.require(g_lat, "g_lat", dims=(2,)); L.require(proj, "projections", dims=(2,))
+    S, n = g_lat.shape
+    D = proj.shape[1]
+    out = torch.empty((n, D), dtype=torch.float32, device=g_lat.device)
+    if n == 0:
+        return out
+    if S == 0:
+        return out.zero_()
+    ws = L.workspace(g_lat.device, int(L.lib().vk_gemm_nt_workspace_bytes()))
+    with torch.cuda.device(g_lat.device):
+        L.call("gemm_nt", L.ptr(g_lat), g_lat.stride(1), g_lat.stride(0), L.ptr(proj), proj.stride(1), proj.stride(0),
+               L.ptr(out), D, 1, n, D, S, L.ptr(ws), ws.numel(), L.stream_ptr())
+    return out
+
+
 def seg_sort(keys, want_perm=False):
     """Ascending sort of every row of a [segments, n] fp32 CUDA tensor with the library's radix sort.
     Returns (sorted, perm or None); perm[s, i] (int64) is the source column of sorted[s, i]."""
