@@ -496,7 +496,7 @@ class SwaeWorkload(OpWorkload):
         self.N, self.D, self.S = 1 << 20, 128, 200
         self.desc = "SWAE sliced-Wasserstein, 200 projections, batch 1048576x128, projection GEMM + radix sort (BASELINE configs[4])"
         self.cpu_sample, self.bound = 1 << 16, "hbm"
-        self.dominant = "swd_fwd"
+        self.dominant, self.dominant_sharded = "swd_fwd", "swd_segments_fwd"
 
     def model(self):
         from vaekit.models import vae_models
@@ -522,7 +522,11 @@ class SwaeWorkload(OpWorkload):
         return {"SWD": swd}
 
     def work(self, world):
-        return {"swd_fwd": 27424.0 * self.N / world}, "GB/s"       # radix-sort traffic model of SURVEY 8(d)
+        # radix-sort traffic model of SURVEY 8(d); sharded (all-to-all) runs time the sort + loss stage on its own:
+        # 120 of the model's 132 bytes per (sample, projection) belong to it (key+index sort 68, key-only sort 36,
+        # loss read 8, gradient scatter 8)
+        return {"swd_fwd": 27424.0 * self.N / world,
+                "swd_segments_fwd": 120.0 * self.N * self.S / world}, "GB/s"
 
     def cpu_step(self, t):
         import vae_oracle as O
@@ -662,7 +666,7 @@ def run_op_gpu_arm(args, wl):
     tot = sum(k["ms"] * k["calls"] for k in kern.values()) or 1.0
     for k in kern:
         kern[k]["share_of_library_time"] = round(kern[k]["ms"] * kern[k]["calls"] / tot, 4)
-    dom = wl.dominant
+    dom = wl.dominant if wl.dominant in kern else wl.dominant_sharded
     dms = kern[dom]["ms"]
     if wl.bound == "tensor":
         peak, src = bf16_peak()

@@ -81,6 +81,10 @@ int vk_reparam_kl_bwd(const float* g_z, const float* g_kl, const float* mu, cons
 
 /* Standard-normal fill with the contract stream (prior_z of wae_mmd.py:195 / swae.py:165). */
 int vk_philox_normal(float* out, int64_t numel, uint64_t seed, uint64_t offset, void* stream);
+/* The same stream with (seed, offset) read from DEVICE memory (seed_offset[0], [1] as int64 bit patterns) and started
+ * quad_shift counters later: a process group shares one rank's generator state by broadcast without a host sync, and a
+ * rank generates only its row block of a global [N, D] sample (quad_shift = first_row * D / 4). */
+int vk_philox_normal_dev(float* out, int64_t numel, const int64_t* seed_offset, int64_t quad_shift, void* stream);
 /* Raw Philox words, [n_quads,4] uint32 -- for the bit-exact stream test. */
 int vk_philox_raw(uint32_t* out, int64_t n_quads, uint64_t seed, uint64_t offset, void* stream);
 
@@ -183,6 +187,33 @@ int vk_mmd_fwd(const float* z, const float* prior, int64_t N, int64_t D, int ker
 int vk_mmd_combine(const double* sums /*[3]*/, int64_t N, int kernel_type, float reg_weight, float* out /*[4]*/, void* stream);
 /* out[i] = in[i] * (*g) * factor  (g may be NULL = 1): backward of an op whose gradient was produced in the forward sweep */
 int vk_scale_by_scalar(const float* in, const float* g, float factor, int64_t n, float* out, void* stream);
+
+/* ---------------------------------------------------------------------------
+ * K4b  the kernel matrix on its own   (reference: models/wae_mmd.py:125-191, models/info_vae.py:150-201 --
+ *      compute_kernel / compute_rbf / compute_inv_mult_quad called directly; compute_mmd uses vk_mmd_fwd instead)
+ *
+ * x1, x2: the reference's [N1, N2, D] operands as base pointer + element strides s[3] = {i, j, d}; the expand() views
+ * of wae_mmd.py:140-141 have stride 0 on the broadcast axis and are read in place.
+ *   rbf: kmat[i, j] = exp(-(mean_d (x1 - x2)^2) / (2 D z_var))                                (wae_mmd.py:164-167)
+ *   imq: kmat[i, j] = C / (eps + C + sum_d (x1 - x2)^2), C = 2 D z_var, and
+ *        imq_out[0] = sum kmat - sum diag kmat   (the scalar the reference returns, wae_mmd.py:185-189);
+ *        imq_out must be NULL for rbf and non-NULL for imq.
+ * Backward, g = upstream gradient read as g[i * g_sr + j * g_sc] (rbf: the [N1, N2] gradient of kmat; imq: the scalar
+ * gradient with both strides 0, the diagonal is excluded):
+ *   vk_pair_kernel_bwd_rows : x1 [N1, D], x2 [N2, D] (the compute_kernel case) -> g_x1 [N1, D], g_x2 [N2, D] (either
+ *                             may be NULL), i.e. the expanded gradients already summed over the broadcast axis;
+ *   vk_pair_kernel_bwd_dense: general [N1, N2, D] operands -> g_x1, g_x2 [N1, N2, D] contiguous (either may be NULL).
+ * workspace: vk_workspace_bytes().
+ * -------------------------------------------------------------------------*/
+int vk_pair_kernel_fwd(const float* x1, const int64_t* s1, const float* x2, const int64_t* s2, int64_t N1, int64_t N2,
+                       int64_t D, int kernel_type, float z_var, float eps, float* kmat, float* imq_out, void* workspace,
+                       int64_t workspace_bytes, void* stream);
+int vk_pair_kernel_bwd_rows(const float* x1, int64_t x1_sr, int64_t x1_sd, const float* x2, int64_t x2_sr, int64_t x2_sd,
+                            int64_t N1, int64_t N2, int64_t D, int kernel_type, float z_var, float eps, const float* kmat,
+                            const float* g, int64_t g_sr, int64_t g_sc, float* g_x1, float* g_x2, void* stream);
+int vk_pair_kernel_bwd_dense(const float* x1, const int64_t* s1, const float* x2, const int64_t* s2, int64_t N1, int64_t N2,
+                             int64_t D, int kernel_type, float z_var, float eps, const float* kmat, const float* g,
+                             int64_t g_sr, int64_t g_sc, float* g_x1, float* g_x2, void* stream);
 
 /* ---------------------------------------------------------------------------
  * K6  SWAE sliced-Wasserstein distance       (reference: models/swae.py:151-179)

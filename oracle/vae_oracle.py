@@ -196,6 +196,19 @@ def imq_kernel_offdiag_sum(x1: Tensor, x2: Tensor, z_var: float, eps: float = 1e
     return k.sum() - k.diag().sum()
 
 
+def compute_rbf(x1: Tensor, x2: Tensor, z_var: float) -> Tensor:
+    """wae_mmd.py:153-168 on the [N1, N2, D] operands themselves (the public method, any broadcastable pair)."""
+    sigma = 2.0 * x2.size(-1) * z_var
+    return torch.exp(-((x1 - x2).pow(2).mean(-1) / sigma))
+
+
+def compute_inv_mult_quad(x1: Tensor, x2: Tensor, z_var: float, eps: float = 1e-7) -> Tensor:
+    """wae_mmd.py:170-191 on the [N1, N2, D] operands themselves."""
+    C = 2 * x2.size(-1) * z_var
+    k = C / (eps + C + (x1 - x2).pow(2).sum(dim=-1))
+    return k.sum() - k.diag().sum()
+
+
 def mmd_terms(z: Tensor, prior_z: Tensor, kernel_type: str, z_var: float) -> Tuple[Tensor, Tensor, Tensor]:
     """The three ``.mean()`` operands of wae_mmd.py:197-203 (pp, zz, pz)."""
     if kernel_type == "rbf":

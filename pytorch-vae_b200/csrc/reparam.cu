@@ -162,6 +162,25 @@ philox_normal_kernel(float* __restrict__ out, int64_t numel, uint64_t seed, uint
   }
 }
 
+// Same stream, with (seed, offset) read from device memory: lets a process group share one rank's generator state with a
+// broadcast and no host synchronisation (vaekit/dist.py).  key[0] = seed, key[1] = offset (both as int64 bit patterns).
+__global__ void __launch_bounds__(256)
+philox_normal_dev_kernel(float* __restrict__ out, int64_t numel, const int64_t* __restrict__ key, int64_t quad_shift) {
+  const uint64_t seed = (uint64_t)key[0], offset = (uint64_t)key[1] + (uint64_t)quad_shift;
+  const int64_t nq = (numel + 3) >> 2;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < nq; q += stride) {
+    const float4 n = philox_normal4(seed, offset, (uint64_t)q);
+    if (4 * q + 3 < numel && ((reinterpret_cast<uintptr_t>(out) & 15) == 0)) {
+      *reinterpret_cast<float4*>(out + 4 * q) = n;
+    } else {
+      const float v[4] = {n.x, n.y, n.z, n.w};
+      for (int c = 0; c < 4; ++c)
+        if (4 * q + c < numel) out[4 * q + c] = v[c];
+    }
+  }
+}
+
 __global__ void philox_raw_kernel(uint32_t* __restrict__ out, int64_t nq, uint64_t seed, uint64_t offset) {
   const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (q < nq) {
@@ -253,6 +272,18 @@ extern "C" int vk_philox_normal(float* out, int64_t numel, uint64_t seed, uint64
   if (blocks > cap) blocks = cap;
   philox_normal_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(out, numel, seed, offset);
   return check_launch("philox_normal");
+}
+
+extern "C" int vk_philox_normal_dev(float* out, int64_t numel, const int64_t* seed_offset, int64_t quad_shift,
+                                    void* stream) {
+  VK_REQUIRE(out && seed_offset && numel >= 0 && quad_shift >= 0, VK_ERR_BAD_ARG, "philox_normal_dev: bad argument");
+  if (numel == 0) return VK_OK;
+  const int64_t nq = (numel + 3) / 4;
+  int64_t blocks = (nq + 255) / 256;
+  const int64_t cap = (int64_t)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  philox_normal_dev_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(out, numel, seed_offset, quad_shift);
+  return check_launch("philox_normal_dev");
 }
 
 extern "C" int vk_philox_raw(uint32_t* out, int64_t n_quads, uint64_t seed, uint64_t offset, void* stream) {

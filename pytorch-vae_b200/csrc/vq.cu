@@ -408,62 +408,173 @@ vq_fwd_kernel(const float* __restrict__ X, const float* __restrict__ E, const ui
 
 // ---- backward ------------------------------------------------------------------------------------------------
 // g_x = g_q + g_loss * (2 beta / numel) (x - q);   g_E[idx] += g_loss * (2 / numel) (q - x)   (vq_vae.py:47-51)
-__global__ void __launch_bounds__(1024, 1)
+//
+// One CTA (1024 threads) per SM walks 128-row tiles.  Loads / stores run with lanes over rows (coalesced along h*w in
+// NCHW; thread = row x slice of the latent dims) and the NEXT tile's x, g_q and indices are fetched into registers while
+// the current tile's codebook-gradient phase runs.  The codebook gradient is accumulated in a per-CTA [K][D] shared
+// tile WITHOUT atomics (a shared fp32 atomicAdd is an ATOMS.CAST.SPIN loop at >= 2 cycles per lane, which bounded the
+// previous version at > 100 us): the tile's x is transposed through shared memory, rows with equal codes are grouped
+// with match.any inside each 32-row group and a per-code table of the four groups' member masks; the first row of the
+// tile with a given code (its warp has lanes over latent dims, bank-conflict free) adds its members' (e - x) and does
+// one plain read-modify-write per (code, dim), so a code has exactly one writer per tile and the phase needs no global
+// loads and a single barrier.  The accumulator is flushed with 128-bit global reductions.
+__device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+constexpr int kBwdThreads = 1024;
+struct VqBwdSmem { uint32_t acc, xs, idx, tab, total; int ldx; };
+inline VqBwdSmem vq_bwd_smem(int64_t D, int64_t K, bool want_e) {
+  VqBwdSmem m;
+  m.ldx = (int)D | 1;
+  uint32_t o = 0;
+  m.acc = o;  o += want_e ? (uint32_t)(K * D * 4) : 0u;
+  m.xs = o;   o += want_e ? (uint32_t)(kTileRows * m.ldx * 4) : 0u;
+  m.idx = o;  o += kTileRows * 4;
+  m.tab = o;  o += want_e ? (uint32_t)(K * 16) : 0u;          // per code: member masks of the tile's four 32-row groups
+  m.total = o;
+  return m;
+}
+
+// DPER > 0: D == 8 * DPER, thread (row, slice) owns DPER consecutive dims, register prefetch of the next tile.
+// DPER == 0: any D, dims strided by 8, no prefetch.
+template <int DPER>
+__global__ void __launch_bounds__(kBwdThreads, 1)
 vq_bwd_kernel(const float* __restrict__ g_q, const float* __restrict__ g_loss, const float* __restrict__ X,
-              const float* __restrict__ E, const int32_t* __restrict__ idx, VqShape s, float beta,
+              const float* __restrict__ E, const int32_t* __restrict__ idx, VqShape s, float beta, VqBwdSmem L,
               float* __restrict__ g_x, float* __restrict__ g_E) {
-  extern __shared__ float acc_s[];                           // [K][D+1] per-CTA codebook-gradient accumulator
-  const int ld = (int)s.D + 1;
+  extern __shared__ __align__(16) uint8_t bsm[];
+  float* acc_s = reinterpret_cast<float*>(bsm + L.acc);      // [K][D] sum over this CTA's rows of (e - x)
+  float* x_s = reinterpret_cast<float*>(bsm + L.xs);         // [128][ldx] the tile's (e - x), row-major
+  int* idx_s = reinterpret_cast<int*>(bsm + L.idx);
+  uint32_t* tab_s = reinterpret_cast<uint32_t*>(bsm + L.tab);
   const bool want_e = g_E != nullptr;
-  if (want_e) for (int i = threadIdx.x; i < s.K * ld; i += blockDim.x) acc_s[i] = 0.f;
-  __syncthreads();
+  const int D = (int)s.D, ldx = L.ldx;
+  if (want_e) {
+    for (int i = threadIdx.x; i < s.K * D; i += kBwdThreads) acc_s[i] = 0.f;
+    for (int i = threadIdx.x; i < s.K * 4; i += kBwdThreads) tab_s[i] = 0u;
+  }
   const float gl = g_loss ? *g_loss : 0.f;
   const float cx = gl * 2.f * beta / (float)((double)s.R * (double)s.D);
   const float ce = gl * 2.f / (float)((double)s.R * (double)s.D);
-  // 128 rows x 8 slices of the latent dims per pass: loads stay coalesced along h*w, 8x more of them in flight
   const int rl = threadIdx.x & 127, dc = threadIdx.x >> 7;
-  const bool vec = (s.D & 31) == 0;
-  const int dper = (int)s.D / 8;
-  for (int64_t tile = blockIdx.x; tile < s.tiles; tile += gridDim.x) {
-    const int64_t r = tile * kTileRows + rl;
-    if (r >= s.R) continue;
-    const int64_t b = r / s.HW, hw = r % s.HW;
-    const int k = idx[r];
-    const float* xp = X + (b * s.D) * s.HW + hw;
-    const float* gp = g_q ? g_q + (b * s.D) * s.HW + hw : nullptr;
-    float* op = g_x ? g_x + (b * s.D) * s.HW + hw : nullptr;
-    const float* ep = E + (size_t)k * s.D;
-    if (vec) {
-      for (int d0 = dc * dper; d0 < (dc + 1) * dper; d0 += 4) {
-        const float4 e4 = __ldg(reinterpret_cast<const float4*>(ep + d0));
-        const float ev[4] = {e4.x, e4.y, e4.z, e4.w};
-        float xv[4], gv[4];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t hw32 = (uint32_t)s.HW;
+  constexpr int NP = DPER > 0 ? DPER : 1;
+  float xr[NP], gr[NP];
+  int kr = -1;
+  size_t base = 0;                                            // element offset of (row, first dim of the slice)
+
+  auto fetch = [&](int64_t tile) {
+    const uint32_t r = (uint32_t)tile * kTileRows + rl;
+    kr = -1;
+    if (tile < s.tiles && r < (uint32_t)s.R) {
+      const uint32_t b = r / hw32, hw = r - b * hw32;
+      kr = __ldg(idx + r);
+      if (DPER > 0) {
+        base = ((size_t)b * D + (size_t)(dc * DPER)) * hw32 + hw;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          xv[j] = __ldg(xp + (int64_t)(d0 + j) * s.HW);
-          gv[j] = gp ? __ldg(gp + (int64_t)(d0 + j) * s.HW) : 0.f;
-        }
+        for (int j = 0; j < NP; ++j) xr[j] = __ldg(X + base + (uint32_t)j * hw32);
+        if (g_q) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const float df = ev[j] - xv[j];                    // q - x
-          if (op) op[(int64_t)(d0 + j) * s.HW] = gv[j] - cx * df;
-          if (want_e) atomicAdd(&acc_s[k * ld + d0 + j], ce * df);
+          for (int j = 0; j < NP; ++j) gr[j] = __ldg(g_q + base + (uint32_t)j * hw32);
+        } else {
+#pragma unroll
+          for (int j = 0; j < NP; ++j) gr[j] = 0.f;
         }
-      }
-    } else {
-      for (int d = dc; d < s.D; d += 8) {
-        const float x = __ldg(xp + (int64_t)d * s.HW);
-        const float df = __ldg(ep + d) - x;
-        if (op) op[(int64_t)d * s.HW] = (gp ? __ldg(gp + (int64_t)d * s.HW) : 0.f) - cx * df;
-        if (want_e) atomicAdd(&acc_s[k * ld + d], ce * df);
+      } else {
+        base = (size_t)b * D * hw32 + hw;
       }
     }
+  };
+
+  fetch(blockIdx.x);
+  __syncthreads();
+  for (int64_t tile = blockIdx.x; tile < s.tiles; tile += gridDim.x) {
+    // ---- consume the registers: straight-through + commitment gradient, x into the transposed tile
+    const int k = kr;
+    if (dc == 0) idx_s[rl] = k;
+    if (k >= 0) {
+      const float* ep = E + (size_t)k * D;
+      if (DPER > 0) {
+        float ev[NP];
+        if (DPER % 4 == 0) {
+#pragma unroll
+          for (int j = 0; j < NP; j += 4) {
+            const float4 e4 = __ldg(reinterpret_cast<const float4*>(ep + dc * DPER + j));
+            ev[j] = e4.x; ev[j + 1 < NP ? j + 1 : 0] = e4.y; ev[j + 2 < NP ? j + 2 : 0] = e4.z; ev[j + 3 < NP ? j + 3 : 0] = e4.w;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < NP; ++j) ev[j] = __ldg(ep + dc * DPER + j);
+        }
+#pragma unroll
+        for (int j = 0; j < NP; ++j) {
+          const float df = ev[j] - xr[j];                     // q - x
+          if (g_x) g_x[base + (uint32_t)j * hw32] = gr[j] - cx * df;
+          if (want_e) x_s[rl * ldx + dc * DPER + j] = df;
+        }
+      } else {
+        for (int d = dc; d < D; d += 8) {
+          const float df = __ldg(ep + d) - __ldg(X + base + (uint32_t)d * hw32);
+          if (g_x) g_x[base + (uint32_t)d * hw32] = (g_q ? __ldg(g_q + base + (uint32_t)d * hw32) : 0.f) - cx * df;
+          if (want_e) x_s[rl * ldx + d] = df;
+        }
+      }
+    }
+    fetch(tile + gridDim.x);                                  // in flight during the codebook-gradient phase
+    if (!want_e) continue;
+    __syncthreads();
+    // rows with equal codes: match.any inside each 32-row group, the group's first such row publishes the member mask
+    uint32_t my_mask = 0u;
+    int my_code = -1;
+    if (warp < kTileRows / 32) {
+      const int kk = idx_s[warp * 32 + lane];
+      const uint32_t m = __match_any_sync(0xffffffffu, kk);
+      if (kk >= 0 && (__ffs(m) - 1) == lane) { my_mask = m; my_code = kk; tab_s[kk * 4 + warp] = m; }
+    }
+    __syncthreads();
+    // warp w looks at rows w, w + 32, w + 64, w + 96; the FIRST row of the tile with a given code sums all its members
+    // (lanes over latent dims) and is the only writer of that code's accumulator row in this tile
+#pragma unroll 1
+    for (int g = 0; g < kTileRows / 32; ++g) {
+      const int kk = idx_s[g * 32 + warp];
+      if (kk < 0) continue;
+      const uint4 t4 = *reinterpret_cast<const uint4*>(tab_s + kk * 4);
+      const uint32_t m[4] = {t4.x, t4.y, t4.z, t4.w};
+      bool lead = (__ffs(m[g]) - 1) == warp;
+      for (int h = 0; h < g; ++h) lead = lead && m[h] == 0u;
+      if (!lead) continue;
+      for (int d = lane; d < D; d += 32) {
+        float sum = 0.f;
+#pragma unroll
+        for (int h = 0; h < 4; ++h) {
+          uint32_t mm = m[h];
+          while (mm) {
+            const int j = __ffs(mm) - 1;
+            mm &= mm - 1;
+            sum += x_s[(h * 32 + j) * ldx + d];
+          }
+        }
+        acc_s[kk * D + d] += sum;
+      }
+    }
+    __syncthreads();
+    if (my_code >= 0) tab_s[my_code * 4 + warp] = 0u;         // (next written after the next tile's first barrier)
+    (void)my_mask;
   }
   if (want_e) {
     __syncthreads();
-    for (int i = threadIdx.x; i < s.K * s.D; i += blockDim.x) {
-      const float v = acc_s[(i / s.D) * ld + (i % s.D)];
-      if (v != 0.f) atomicAdd(&g_E[i], v);
+    if ((D & 3) == 0 && ((reinterpret_cast<uintptr_t>(g_E) & 15) == 0)) {
+      for (int i = threadIdx.x; i < s.K * D / 4; i += kBwdThreads) {
+        const float4 v = *reinterpret_cast<const float4*>(acc_s + 4 * i);
+        if (v.x != 0.f || v.y != 0.f || v.z != 0.f || v.w != 0.f) red_add_v4(g_E + 4 * i, ce * v.x, ce * v.y, ce * v.z, ce * v.w);
+      }
+    } else {
+      for (int i = threadIdx.x; i < s.K * D; i += kBwdThreads) {
+        const float v = acc_s[i];
+        if (v != 0.f) atomicAdd(&g_E[i], ce * v);
+      }
     }
   }
 }
@@ -534,13 +645,15 @@ extern "C" int vk_vq_bwd(const float* g_q, const float* g_loss, const float* lat
   int rc = make_shape(B, D, HW, K, s);
   if (rc != VK_OK) return rc;
   cudaStream_t st = (cudaStream_t)stream;
-  const size_t sm = g_codebook ? (size_t)K * (D + 1) * 4 : 0;
-  VK_REQUIRE(sm <= 226 * 1024, VK_ERR_UNSUPPORTED, "vq_bwd: codebook gradient tile needs %zu bytes of shared memory", sm);
-  if (sm > 48 * 1024 && cudaFuncSetAttribute(vq_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm) != cudaSuccess)
+  const VqBwdSmem L = vq_bwd_smem(D, K, g_codebook != nullptr);
+  VK_REQUIRE(L.total <= 226 * 1024, VK_ERR_UNSUPPORTED, "vq_bwd: codebook gradient tile needs %u bytes of shared memory",
+             L.total);
+  auto kern = D == 32 ? vq_bwd_kernel<4> : D == 64 ? vq_bwd_kernel<8> : D == 128 ? vq_bwd_kernel<16> : vq_bwd_kernel<0>;
+  if (L.total > 48 * 1024 && cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total) != cudaSuccess)
     return check_launch("vq_bwd (shared memory attribute)");
   if (g_codebook) zero_kernel<<<64, 256, 0, st>>>(g_codebook, K * D);
   int64_t blocks = s.tiles;
   if (blocks > sm_count()) blocks = sm_count();
-  vq_bwd_kernel<<<(int)blocks, 1024, sm, st>>>(g_q, g_loss, latents, codebook, idx, s, beta, g_latents, g_codebook);
+  kern<<<(int)blocks, kBwdThreads, L.total, st>>>(g_q, g_loss, latents, codebook, idx, s, beta, L, g_latents, g_codebook);
   return check_launch("vq_bwd");
 }

@@ -22,6 +22,7 @@ _SIGNATURES = {
     "vk_reparam_kl_fwd": ([_p, _p, _p, _p, _p, _i64, _u64, _u64, _p, _p, _p, _p], _i),
     "vk_reparam_kl_bwd": ([_p, _p, _p, _p, _p, _p, _p, _i64, _u64, _u64, _p, _p, _p], _i),
     "vk_philox_normal": ([_p, _i64, _u64, _u64, _p], _i),
+    "vk_philox_normal_dev": ([_p, _i64, _p, _i64, _p], _i),
     "vk_philox_raw": ([_p, _i64, _u64, _u64, _p], _i),
     "vk_elbo_fwd": ([_p, _p, _i64, _p, _i64, _i, _f, _i, _f, _f, _p, _p, _i64, _p], _i),
     "vk_elbo_bwd": ([_p, _p, _i64, _i64, _i, _f, _i, _f, _f, _p, _p, _p, _p, _p, _p, _p, _p], _i),
@@ -33,6 +34,10 @@ _SIGNATURES = {
     "vk_mmd_fwd": ([_p, _p, _i64, _i64, _i, _f, _i, _i64, _i64, _p, _p, _p, _i64, _p], _i),
     "vk_mmd_combine": ([_p, _i64, _i, _f, _p, _p], _i),
     "vk_scale_by_scalar": ([_p, _p, _f, _i64, _p, _p], _i),
+    "vk_pair_kernel_fwd": ([_p, _p, _p, _p, _i64, _i64, _i64, _i, _f, _f, _p, _p, _p, _i64, _p], _i),
+    "vk_pair_kernel_bwd_rows": ([_p, _i64, _i64, _p, _i64, _i64, _i64, _i64, _i64, _i, _f, _f, _p, _p, _i64, _i64, _p, _p,
+                                _p], _i),
+    "vk_pair_kernel_bwd_dense": ([_p, _p, _p, _p, _i64, _i64, _i64, _i, _f, _f, _p, _p, _i64, _i64, _p, _p, _p], _i),
     "vk_swd_workspace_bytes": ([_i64, _i64], _i64),
     "vk_swd_fwd": ([_p, _p, _p, _i64, _i64, _i64, _f, _p, _p, _p, _i64, _p], _i),
     "vk_mean_scale": ([_p, C.c_double, _f, _p, _p], _i),

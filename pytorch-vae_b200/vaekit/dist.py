@@ -97,6 +97,19 @@ def shared_rng(device, numel: int, group=None) -> Tuple[int, int]:
     return seed, offset
 
 
+def shared_rng_key(device, numel: int, group=None) -> torch.Tensor:
+    """The same reservation as shared_rng, as an int64 CUDA tensor [seed, offset] (bit patterns) that is identical on
+    every rank after an asynchronous broadcast of rank 0's values: no host synchronisation in the step
+    (vk_philox_normal_dev reads the key on the device)."""
+    from . import functional as F
+    seed, offset = F.next_philox(device, numel)
+    signed = seed - (1 << 64) if seed >= (1 << 63) else seed
+    key = torch.tensor([signed, offset], dtype=torch.int64, device=device)
+    if _active(group):
+        dist.broadcast(key, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+    return key
+
+
 def shared_tensor_(t: torch.Tensor, group=None) -> torch.Tensor:
     if _active(group):
         dist.broadcast(t, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
@@ -113,8 +126,7 @@ class _ShardedMmd(torch.autograd.Function):
         world, rank = world_rank(group)
         N, r0, r1 = plan_rows(z_local.shape[0], world, rank)
         z_all = gather_rows(z_local, group)
-        rng = shared_rng(z_local.device, z_all.numel(), group)
-        prior_all = F.philox_normal(z_all.shape, z_all.device, rng=rng)
+        prior_all = F.philox_normal_dev(z_all.shape, shared_rng_key(z_local.device, z_all.numel(), group))
         sums, grad = F.mmd_sweep(z_all, prior_all, kernel_type, z_var, r0, r1, passes)
         reduce_sum_(sums, group)
         out = F.mmd_combine(sums, N, kernel_type, reg_weight)
@@ -149,8 +161,7 @@ class _ShardedSwd(torch.autograd.Function):
         world, rank = world_rank(group)
         z_all = gather_rows(z_local, group)
         N, S = z_all.shape[0], proj.shape[0]
-        rng = shared_rng(z_local.device, z_all.numel(), group)
-        prior_all = F.philox_normal(z_all.shape, z_all.device, rng=rng)
+        prior_all = F.philox_normal_dev(z_all.shape, shared_rng_key(z_local.device, z_all.numel(), group))
         s0, s1 = plan_projections(S, world, rank)
         if s1 > s0:
             total, grad_all = F.swd_sweep(z_all, prior_all, proj[s0:s1], p, want_grad=True)
@@ -204,41 +215,94 @@ def return_segments(seg: torch.Tensor, num_projections: int, group=None) -> torc
     return recv
 
 
-def local_prior_rows(n_local: int, D: int, device, rng, rank: int) -> torch.Tensor:
-    """Rows [rank * n_local, (rank + 1) * n_local) of the [N, D] prior sample of Philox stream `rng`: noise is a pure
-    function of (seed, offset, element index) with one counter per four elements, so a rank's row block is the same
-    stream started rank * n_local * D / 4 counters later -- nothing is communicated."""
+def local_prior_rows(n_local: int, D: int, key: torch.Tensor, rank: int) -> torch.Tensor:
+    """Rows [rank * n_local, (rank + 1) * n_local) of the [N, D] prior sample of the shared Philox stream `key`
+    (shared_rng_key): noise is a pure function of (seed, offset, element index) with one counter per four elements, so
+    a rank's row block is the same stream started rank * n_local * D / 4 counters later -- nothing is communicated."""
     from . import functional as F
     first = rank * n_local * D
     if first % 4 != 0:
         raise ValueError("sharded prior needs n_local * D to be a multiple of 4 (got %d x %d)" % (n_local, D))
-    return F.philox_normal((n_local, D), device, rng=(rng[0], rng[1] + first // 4))
+    return F.philox_normal_dev((n_local, D), key, quad_shift=first // 4)
+
+
+def plan_waves(num_projections: int, world: int, waves: int) -> List[List[Tuple[int, int]]]:
+    """Pipelining plan of the all-to-all SWD: wave q holds, for every rank r, the q-th piece [a, b) of the projections
+    rank r owns (plan_projections split again into `waves` pieces).  Returns waves x world ranges."""
+    out = []
+    for q in range(waves):
+        per_rank = []
+        for r in range(world):
+            s0, s1 = plan_projections(num_projections, world, r)
+            c0, c1 = plan_projections(s1 - s0, waves, q)
+            per_rank.append((s0 + c0, s0 + c1))
+        out.append(per_rank)
+    return out
+
+
+def _all_to_all(out, inp, out_splits, in_splits, group, async_op):
+    if not _active(group):
+        out.copy_(inp)
+        return None
+    return dist.all_to_all_single(out, inp, output_split_sizes=out_splits, input_split_sizes=in_splits, group=group,
+                                  async_op=async_op)
 
 
 class _ShardedSwdA2A(torch.autograd.Function):
     """swae.py:151-179 on the global batch with every stage sharded: rank r projects ITS rows (z and the locally
-    regenerated prior rows) on all S projections, one all-to-all hands rank r all N values of its S / world projections,
-    it sorts them and forms the loss partial and d/dlat, one all-to-all returns d/dlat to the row owners, and the
-    gradient GEMM runs on the rank's own rows.  No [N, D] tensor is gathered or reduced."""
+    regenerated prior rows) on all S projections, an all-to-all hands rank r all N values of its S / world projections,
+    it sorts them and forms the loss partial and d/dlat, a second all-to-all returns d/dlat to the row owners, and the
+    gradient GEMM runs on the rank's own rows.  No [N, D] tensor is gathered or reduced.  The projections travel in
+    `waves` pieces so the exchange of wave q + 1 (and the return of wave q - 1) overlaps the sort of wave q."""
 
     @staticmethod
-    def forward(ctx, z_local, proj, p, reg_weight, group):
+    def forward(ctx, z_local, proj, p, reg_weight, group, waves):
         from . import functional as F
         world, rank = world_rank(group)
         n, D = z_local.shape
         S = proj.shape[0]
         N = n * world
-        rng = shared_rng(z_local.device, N * D, group)
-        prior_local = local_prior_rows(n, D, z_local.device, rng, rank)
-        both = torch.empty((S, 2, n), dtype=torch.float32, device=z_local.device)
-        F.swd_project(z_local, proj, out=both[:, 0, :])
-        F.swd_project(prior_local, proj, out=both[:, 1, :])
-        seg = exchange_segments(both, group)                       # [S_r, 2, N]
-        lat, pri = seg[:, 0, :].contiguous(), seg[:, 1, :].contiguous()
-        total = F.swd_segments(lat, pri, p, want_grad=True)        # lat <- d sum / d lat (sample order)
+        dev = z_local.device
+        key = shared_rng_key(dev, N * D, group)
+        prior_local = local_prior_rows(n, D, key, rank)
+        plan = plan_waves(S, world, waves)
+        order = [i for per_rank in plan for a, b in per_rank for i in range(a, b)]      # projections, wave-major
+        proj_w = proj[torch.tensor(order, dtype=torch.long, device=dev)] if waves > 1 else proj
+        # ---- stage 1: project the rank's rows wave by wave and start every exchange
+        pending, row0 = [], 0
+        for per_rank in plan:
+            splits = [b - a for a, b in per_rank]
+            Sq, mine = sum(splits), splits[rank]
+            both = torch.empty((Sq, 2, n), dtype=torch.float32, device=dev)
+            F.swd_project(z_local, proj_w[row0:row0 + Sq], out=both[:, 0, :])
+            F.swd_project(prior_local, proj_w[row0:row0 + Sq], out=both[:, 1, :])
+            recv = torch.empty((world * mine, 2, n), dtype=torch.float32, device=dev)
+            work = _all_to_all(recv, both, [mine] * world, splits, group, True)
+            pending.append((work, recv, both, splits, mine, row0))
+            row0 += Sq
+        # ---- stage 2: per wave, sort + loss + d/dlat on the rank's projections, and send d/dlat back
+        g_all = torch.empty((S, n), dtype=torch.float32, device=dev)
+        total = torch.zeros(1, dtype=torch.float64, device=dev)
+        returning = []
+        for work, recv, both, splits, mine, r0 in pending:
+            if work is not None:
+                work.wait()
+            Sq = sum(splits)
+            if mine > 0:
+                v = recv.view(world, mine, 2, n)
+                lat = v[:, :, 0, :].permute(1, 0, 2).reshape(mine, N)              # rows in rank-major = global order
+                pri = v[:, :, 1, :].permute(1, 0, 2).reshape(mine, N)
+                total += F.swd_segments(lat, pri, p, want_grad=True)                # lat <- d sum / d lat, sample order
+                send = lat.view(mine, world, n).permute(1, 0, 2).contiguous().view(world * mine, n)
+            else:
+                send = torch.empty((0, n), dtype=torch.float32, device=dev)
+            back = _all_to_all(g_all[r0:r0 + Sq], send, splits, [mine] * world, group, True)
+            returning.append((back, send))
         reduce_sum_(total, group)
-        g_local = return_segments(lat, S, group)                   # [S, n]
-        grad_local = F.swd_project_back(g_local, proj)
+        for back, _ in returning:
+            if back is not None:
+                back.wait()
+        grad_local = F.swd_project_back(g_all, proj_w)
         ctx.save_for_backward(grad_local)
         count = float(N) * float(S)
         ctx.factor = reg_weight / count
@@ -249,17 +313,20 @@ class _ShardedSwdA2A(torch.autograd.Function):
     def backward(ctx, g):
         from . import functional as F
         if g is None:
-            return (None,) * 5
-        return F.scale_by_scalar(ctx.saved_tensors[0], g.contiguous(), ctx.factor), None, None, None, None
+            return (None,) * 6
+        return F.scale_by_scalar(ctx.saved_tensors[0], g.contiguous(), ctx.factor), None, None, None, None, None
 
 
-def sharded_swd(z_local, proj, p, reg_weight, group=None, exchange="all_to_all"):
+def sharded_swd(z_local, proj, p, reg_weight, group=None, exchange="all_to_all", waves=None):
     """Sliced-Wasserstein distance of the GLOBAL batch; `proj` [S, D] must be identical on every rank
     (use shared_tensor_ on the reference's CPU-generated directions).  exchange = "all_to_all" (projected values travel;
-    every stage shrinks with the world size) or "all_gather" (z travels; each rank projects all rows on its slice of
+    every stage shrinks with the world size; `waves` pieces pipeline the exchange under the sorts) or "all_gather" (z travels; each rank projects all rows on its slice of
     the projections and the [N, D] gradient is reduce-scattered -- kept for shapes the tcgen05 GEMM does not take)."""
     if exchange == "all_to_all":
-        return _ShardedSwdA2A.apply(z_local, proj, float(p), float(reg_weight), group)
+        if waves is None:                       # pipeline depth: pieces of the rank's projection slice
+            world, _ = world_rank(group)
+            waves = 1 if world == 1 else max(1, min(4, proj.shape[0] // world))
+        return _ShardedSwdA2A.apply(z_local, proj, float(p), float(reg_weight), group, int(waves))
     if exchange == "all_gather":
         return _ShardedSwd.apply(z_local, proj, float(p), float(reg_weight), group)
     raise ValueError("Unknown exchange %r" % (exchange,))

@@ -103,6 +103,17 @@ def philox_normal(shape, device, rng=None):
     return out
 
 
+def philox_normal_dev(shape, key, quad_shift=0):
+    """Standard normals from the contract stream whose (seed, offset) live in the int64 CUDA tensor `key` [2], started
+    `quad_shift` counters (4 elements each) later.  No host synchronisation."""
+    if key.dtype != torch.int64 or not key.is_cuda or key.numel() != 2:
+        raise RuntimeError("vaekit: philox key must be an int64 CUDA tensor with two elements")
+    out = torch.empty(shape, dtype=torch.float32, device=key.device)
+    with torch.cuda.device(out.device):
+        L.call("philox_normal_dev", L.ptr(out), out.numel(), L.ptr(key), int(quad_shift), L.stream_ptr())
+    return out
+
+
 def philox_raw(n_quads, device, seed, offset):
     out = torch.empty((n_quads, 4), dtype=torch.int32, device=device)
     with torch.cuda.device(out.device):
@@ -333,6 +344,97 @@ def mmd(z, prior_z, reg_weight, kernel_type, z_var, passes=3):
     if kernel_type not in KERNEL_TYPES:
         raise ValueError('Undefined kernel type.')
     return _Mmd.apply(z, prior_z, KERNEL_TYPES[kernel_type], float(z_var), float(reg_weight), int(passes))
+
+
+# ---------------------------------------------------------------------------
+# K4b: the kernel matrix on its own (compute_kernel / compute_rbf / compute_inv_mult_quad called directly)
+# ---------------------------------------------------------------------------
+def _pair_fwd(x1, s1, x2, s2, N1, N2, D, kt, z_var, eps):
+    dev = x1.device
+    kmat = torch.empty((N1, N2), dtype=torch.float32, device=dev)
+    imq = torch.empty(1, dtype=torch.float32, device=dev) if kt == 1 else None
+    ws = L.workspace(dev)
+    with torch.cuda.device(dev):
+        L.call("pair_kernel_fwd", L.ptr(x1), L.i64x3(s1), L.ptr(x2), L.i64x3(s2), N1, N2, D, kt, z_var, eps, L.ptr(kmat),
+               L.ptr(imq), L.ptr(ws), ws.numel(), L.stream_ptr())
+    return kmat, imq
+
+
+def _upstream(g, kt):
+    """(tensor, row stride, column stride) of the upstream gradient: [N1, N2] for rbf, a scalar for imq."""
+    g = g.contiguous()
+    return (g, 0, 0) if kt == 1 else (g, g.stride(0), g.stride(1))
+
+
+class _PairKernelRows(torch.autograd.Function):
+    """k(x1_i, x2_j) for x1 [N1, D], x2 [N2, D]: what compute_kernel computes after its unsqueeze/expand."""
+
+    @staticmethod
+    def forward(ctx, x1, x2, kt, z_var, eps):
+        N1, D = x1.shape
+        N2 = x2.shape[0]
+        kmat, imq = _pair_fwd(x1, (x1.stride(0), 0, x1.stride(1)), x2, (0, x2.stride(0), x2.stride(1)), N1, N2, D, kt,
+                              z_var, eps)
+        ctx.save_for_backward(x1, x2, kmat)
+        ctx.cfg = (kt, z_var, eps)
+        return kmat if kt == 0 else imq[0]
+
+    @staticmethod
+    def backward(ctx, g):
+        x1, x2, kmat = ctx.saved_tensors
+        kt, z_var, eps = ctx.cfg
+        N1, D = x1.shape
+        N2 = x2.shape[0]
+        g, g_sr, g_sc = _upstream(g, kt)
+        g1 = torch.empty((N1, D), dtype=torch.float32, device=x1.device) if ctx.needs_input_grad[0] else None
+        g2 = torch.empty((N2, D), dtype=torch.float32, device=x1.device) if ctx.needs_input_grad[1] else None
+        with torch.cuda.device(x1.device):
+            L.call("pair_kernel_bwd_rows", L.ptr(x1), x1.stride(0), x1.stride(1), L.ptr(x2), x2.stride(0), x2.stride(1), N1,
+                   N2, D, kt, z_var, eps, L.ptr(kmat), L.ptr(g), g_sr, g_sc, L.ptr(g1), L.ptr(g2), L.stream_ptr())
+        return g1, g2, None, None, None
+
+
+class _PairKernelDense(torch.autograd.Function):
+    """The same kernels on general [N1, N2, D] operands (any strides)."""
+
+    @staticmethod
+    def forward(ctx, x1, x2, kt, z_var, eps):
+        N1, N2, D = x1.shape
+        kmat, imq = _pair_fwd(x1, x1.stride(), x2, x2.stride(), N1, N2, D, kt, z_var, eps)
+        ctx.save_for_backward(x1, x2, kmat)
+        ctx.cfg = (kt, z_var, eps)
+        return kmat if kt == 0 else imq[0]
+
+    @staticmethod
+    def backward(ctx, g):
+        x1, x2, kmat = ctx.saved_tensors
+        kt, z_var, eps = ctx.cfg
+        N1, N2, D = x1.shape
+        g, g_sr, g_sc = _upstream(g, kt)
+        g1 = torch.empty((N1, N2, D), dtype=torch.float32, device=x1.device) if ctx.needs_input_grad[0] else None
+        g2 = torch.empty((N1, N2, D), dtype=torch.float32, device=x1.device) if ctx.needs_input_grad[1] else None
+        with torch.cuda.device(x1.device):
+            L.call("pair_kernel_bwd_dense", L.ptr(x1), L.i64x3(x1.stride()), L.ptr(x2), L.i64x3(x2.stride()), N1, N2, D,
+                   kt, z_var, eps, L.ptr(kmat), L.ptr(g), g_sr, g_sc, L.ptr(g1), L.ptr(g2), L.stream_ptr())
+        return g1, g2, None, None, None
+
+
+def pair_kernel(x1, x2, kernel_type, z_var, eps=1e-7):
+    """compute_rbf / compute_inv_mult_quad (wae_mmd.py:153-191) on the reference's [N1, N2, D] operands.  When they are
+    the expand() views compute_kernel builds (x1 constant along axis 1, x2 along axis 0) the work is done on the
+    [N, D] bases and the gradient comes back already summed over the broadcast axis; otherwise the dense form runs.
+    Returns [N1, N2] for 'rbf' and the 0-dim `sum - diag sum` for 'imq', like the reference."""
+    if kernel_type not in KERNEL_TYPES:
+        raise ValueError('Undefined kernel type.')
+    kt = KERNEL_TYPES[kernel_type]
+    L.require(x1, "x1", dims=(3,)); L.require(x2, "x2", dims=(3,))
+    if x1.shape != x2.shape:
+        x1, x2 = torch.broadcast_tensors(x1, x2)
+    if 0 in x1.shape:
+        raise RuntimeError("vaekit: empty operand for the kernel matrix")
+    if x1.shape[1] > 1 and x1.shape[0] > 1 and x1.stride(1) == 0 and x2.stride(0) == 0:
+        return _PairKernelRows.apply(x1[:, 0, :], x2[0, :, :], kt, float(z_var), float(eps))
+    return _PairKernelDense.apply(x1, x2, kt, float(z_var), float(eps))
 
 
 # ---------------------------------------------------------------------------

@@ -7,9 +7,10 @@ from torch import Tensor
 
 from .. import functional as F
 from .base import GaussianConvVAE
+from .wae_mmd import KernelMatrixMixin
 
 
-class InfoVAE(GaussianConvVAE):
+class InfoVAE(KernelMatrixMixin, GaussianConvVAE):
     def __init__(self, in_channels: int, latent_dim: int, hidden_dims: List = None, alpha: float = -0.5,
                  beta: float = 5.0, reg_weight: int = 100, kernel_type: str = 'imq', latent_var: float = 2.,
                  **kwargs) -> None:

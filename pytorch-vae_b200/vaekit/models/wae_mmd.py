@@ -7,7 +7,30 @@ from .. import functional as F
 from .base import DeterministicConvAE
 
 
-class WAE_MMD(DeterministicConvAE):
+class KernelMatrixMixin:
+    """compute_kernel / compute_rbf / compute_inv_mult_quad with the reference's signatures and results
+    (wae_mmd.py:125-191, info_vae.py:150-201) on vk_pair_kernel_*.  compute_mmd does not go through them: it never
+    needs the [N, N] matrices (vk_mmd_fwd)."""
+
+    def compute_kernel(self, x1: Tensor, x2: Tensor) -> Tensor:
+        D = x1.size(1)
+        N = x1.size(0)
+        x1 = x1.unsqueeze(-2).expand(N, N, D)      # column tensor, wae_mmd.py:132,140
+        x2 = x2.unsqueeze(-3).expand(N, N, D)      # row tensor, wae_mmd.py:133,141
+        if self.kernel_type == 'rbf':
+            return self.compute_rbf(x1, x2)
+        elif self.kernel_type == 'imq':
+            return self.compute_inv_mult_quad(x1, x2)
+        raise ValueError('Undefined kernel type.')
+
+    def compute_rbf(self, x1: Tensor, x2: Tensor, eps: float = 1e-7) -> Tensor:
+        return F.pair_kernel(x1, x2, 'rbf', self.z_var, eps)
+
+    def compute_inv_mult_quad(self, x1: Tensor, x2: Tensor, eps: float = 1e-7) -> Tensor:
+        return F.pair_kernel(x1, x2, 'imq', self.z_var, eps)
+
+
+class WAE_MMD(KernelMatrixMixin, DeterministicConvAE):
     def __init__(self, in_channels: int, latent_dim: int, hidden_dims: List = None, reg_weight: int = 100,
                  kernel_type: str = 'imq', latent_var: float = 2., **kwargs) -> None:
         super().__init__(in_channels, latent_dim, hidden_dims)

@@ -1,1 +1,4 @@
-timeout 900 ncu --set full --clock-control none --import-source on -k "regex:^gemm3x_kernel" -s 3 -c 3 -f -o gpurun_out/gemm3x_r01k python bench.py --workload swae --steps 1 --warmup 1 --no-cpu > gpurun_out/ncu_gemm3x.log 2>&1; tail -2 gpurun_out/ncu_gemm3x.log
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29513 scripts/probe/symm_probe.py 2>&1 | grep -v "^\*\|OMP_NUM\|^$" | tail -30 | tee gpurun_out/symm_probe.log
+nvidia-smi topo -m | head -12

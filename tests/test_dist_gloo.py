@@ -31,6 +31,16 @@ def test_partition_plans():
         assert all(a[1] == b[0] for a, b in zip(parts, parts[1:]))
         sizes = [b - a for a, b in parts]
         assert max(sizes) - min(sizes) <= 1
+    # wave plan of the pipelined all-to-all SWD: every projection exactly once, each piece inside its owner's slice
+    for S, w, q in ((200, 8, 4), (7, 3, 2), (5, 4, 3), (10, 2, 1)):
+        plan = vd.plan_waves(S, w, q)
+        assert len(plan) == q and all(len(per_rank) == w for per_rank in plan)
+        seen = sorted(i for per_rank in plan for a, b in per_rank for i in range(a, b))
+        assert seen == list(range(S))
+        for r in range(w):
+            s0, s1 = vd.plan_projections(S, w, r)
+            pieces = [plan[k][r] for k in range(q)]
+            assert pieces[0][0] == s0 and pieces[-1][1] == s1 and all(a[1] == b[0] for a, b in zip(pieces, pieces[1:]))
     # without a process group the collectives are identities
     x = torch.arange(6.0).view(3, 2)
     assert torch.equal(vd.gather_rows(x), x) and torch.equal(vd.scatter_rows_sum(x), x)
@@ -108,6 +118,31 @@ def _worker(rank, world, port, out):
         total = tot.detach().double().view(1)
         vd.reduce_sum_(total)
         grad_local = vd.scatter_rows_sum(za.grad)
+
+        # ---- all-to-all exchange of projected values: [S, C, n] per rank -> [S_r, C, N], and back
+        Sx = 7                                                       # uneven split: 4 + 3
+        full = torch.arange(Sx * 2 * N, dtype=torch.float32).view(Sx, 2, N)        # the global [S, C, N] table
+        mine = full[:, :, rank * n_local:(rank + 1) * n_local].contiguous()
+        seg = vd.exchange_segments(mine)
+        a0, a1 = vd.plan_projections(Sx, world, rank)
+        assert torch.equal(seg, full[a0:a1])
+        back = vd.return_segments(seg[:, 1, :].contiguous(), Sx)
+        assert torch.equal(back, mine[:, 1, :])
+        # the SWD through the exchange: local projections -> segments -> sorted loss / d/dlat -> back -> local gradient
+        zl = z_local.clone().requires_grad_(True)
+        pl = prior_all[rank * n_local:(rank + 1) * n_local]
+        both = torch.stack([zl @ proj.t(), pl @ proj.t()], dim=0).permute(2, 0, 1).contiguous()   # [S, 2, n]
+        segs = vd.exchange_segments(both.detach())
+        lat = segs[:, 0, :].clone().requires_grad_(True)
+        w2 = torch.sort(lat, dim=1)[0] - torch.sort(segs[:, 1, :], dim=1)[0]
+        t2 = w2.pow(2).sum()
+        t2.backward()
+        tot2 = t2.detach().double().view(1)
+        vd.reduce_sum_(tot2)
+        g_back = vd.return_segments(lat.grad, S)                     # [S, n]
+        grad_a2a = g_back.t() @ proj
+        assert abs(tot2.item() - total.item()) <= 1e-5 * abs(total.item())
+        assert ((grad_a2a - grad_local).abs().max() / grad_local.abs().max()).item() < 1e-5
 
         if rank == 0:
             torch.save({"z_all": z_all, "prior": prior_all, "proj": proj, "res": res, "swd_total": total,

@@ -50,11 +50,13 @@ def _worker(rank, world, port, out):
             res[kt] = (mmd.detach().cpu(), terms.cpu(), z.grad.cpu())
         proj = O.random_projections(D, S).to(dev) if rank == 0 else torch.zeros(S, D, device=dev)
         vd.shared_tensor_(proj)
-        torch.manual_seed(SEED)
-        z = _local_z(rank, dev).requires_grad_(True)
-        swd = vd.sharded_swd(z, proj, 2.0, 7.0)
-        swd.backward()
-        res["swd"] = (swd.detach().cpu(), z.grad.cpu())
+        for key, exchange, waves in (("swd", "all_to_all", None), ("swd_w1", "all_to_all", 1), ("swd_w3", "all_to_all", 3),
+                                     ("swd_ag", "all_gather", None)):
+            torch.manual_seed(SEED)
+            z = _local_z(rank, dev).requires_grad_(True)
+            swd = vd.sharded_swd(z, proj, 2.0, 7.0, exchange=exchange, waves=waves)
+            swd.backward()
+            res[key] = (swd.detach().cpu(), z.grad.cpu())
         res["proj"] = proj.cpu()
         torch.save(res, out + ".r%d" % rank)
     finally:
@@ -108,10 +110,11 @@ def test_sharded_ops_match_single_gpu_and_oracle(tmp_path):
     zs = z_all.clone().requires_grad_(True)
     one = F.swd(zs, prior, proj, 2.0, 7.0)
     one.backward()
-    for r in range(world):
-        assert abs(parts[r]["swd"][0].item() - one.item()) <= 1e-6 * abs(one.item()), r
-    g = torch.cat([parts[r]["swd"][1] for r in range(world)])
-    assert ((g - zs.grad.cpu()).abs().max() / zs.grad.abs().max().cpu()).item() < 1e-5
+    for key in ("swd", "swd_w1", "swd_w3", "swd_ag"):                                 # all-to-all of projected values / all-gather of z
+        for r in range(world):
+            assert abs(parts[r][key][0].item() - one.item()) <= 1e-6 * abs(one.item()), (key, r)
+        g = torch.cat([parts[r][key][1] for r in range(world)])
+        assert ((g - zs.grad.cpu()).abs().max() / zs.grad.abs().max().cpu()).item() < 1e-5, key
     zo = z_all.cpu().requires_grad_(True)
     ref = O.swd(zo, prior.cpu(), proj.cpu(), 2.0, 7.0)
     ref.backward()

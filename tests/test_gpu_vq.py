@@ -58,7 +58,8 @@ def test_vq_golden(vk, name):
 
 @pytest.mark.parametrize("B,D,H,K,init", [(4, 64, 16, 512, "normal"), (4, 64, 16, 512, "default"),
                                            (3, 16, 5, 40, "normal"), (2, 8, 3, 300, "normal"),
-                                           (1, 128, 8, 128, "normal")])
+                                           (1, 128, 8, 128, "normal"), (2, 32, 8, 5, "normal"),
+                                           (3, 64, 16, 3, "normal"), (2, 12, 7, 2, "normal")])
 def test_vq_vs_oracle(vk, B, D, H, K, init):
     F, _ = vk
     gen = torch.Generator().manual_seed(11 + K)
@@ -105,6 +106,18 @@ def test_vq_full_size_properties(vk):
     d = O.vq_distances(flat[sel].double(), cb.double())
     chosen = d.gather(1, idx[sel].long().view(-1, 1)).squeeze(1)
     assert ((chosen - d.min(1).values) <= 1e-5 * d.min(1).values.abs()).all()
+    # backward at full size against the closed form of vq_vae.py:47-51 evaluated in float64 on the kernel's indices
+    lat_g, cb_g = leaf(lat), leaf(cb)
+    gq = 1e-3 * torch.randn(lat.shape, device=DEV, generator=gen)
+    q3, l3, idx3 = F.vector_quantize(lat_g, cb_g, 0.25)
+    (l3 * 1.7 + (q3 * gq).sum()).backward()
+    numel = float(flat.numel())
+    diff = (e - flat).double()                                                     # q - x
+    gx_ref = gq.double() - (1.7 * 2 * 0.25 / numel) * diff.view(1024, 16, 16, 64).permute(0, 3, 1, 2)
+    ge_ref = torch.zeros(512, 64, dtype=torch.float64, device=DEV).index_add_(0, idx.long(), diff * (1.7 * 2 / numel))
+    assert torch.equal(idx3, idx)
+    assert_close(lat_g.grad, gx_ref, TOL, "full-size grad latents")
+    assert_close(cb_g.grad, ge_ref, TOL, "full-size grad codebook")
     # idempotence on exact codes: latents made of codebook rows quantise to themselves with zero loss
     pick = torch.randint(0, 512, (4 * 256,), device=DEV, generator=gen)
     lat2 = cb[pick].view(4, 16, 16, 64).permute(0, 3, 1, 2).contiguous()

@@ -63,6 +63,27 @@ def test_mmd_random(ref, kt):
     assert_close(gb, ga, 1e-5)
 
 
+@pytest.mark.parametrize("kt", ["rbf", "imq"])
+def test_kernel_matrix_methods(ref, kt):
+    """compute_kernel / compute_rbf / compute_inv_mult_quad called directly (wae_mmd.py:125-191, info_vae.py:150-201)."""
+    g = torch.Generator().manual_seed(8)
+    for cls in (ref.WAE_MMD, ref.InfoVAE):
+        m = cls(3, 12, reg_weight=100, kernel_type=kt, latent_var=1.5)
+        x1 = leaf(torch.randn(9, 12, generator=g)); x2 = leaf(torch.randn(9, 12, generator=g))
+        a = m.compute_kernel(x1, x2)
+        ga = torch.autograd.grad(a.sum(), (x1, x2))
+        y1, y2 = leaf(x1.detach()), leaf(x2.detach())
+        b = O.rbf_kernel_matrix(y1, y2, 1.5) if kt == "rbf" else O.imq_kernel_offdiag_sum(y1, y2, 1.5)
+        gb = torch.autograd.grad(b.sum(), (y1, y2))
+        assert a.shape == b.shape and torch.equal(a, b)
+        assert_close(gb[0], ga[0], 1e-6); assert_close(gb[1], ga[1], 1e-6)
+        # dense [N1, N2, D] operands straight into the two kernel methods
+        d1 = leaf(torch.randn(5, 7, 12, generator=g)); d2 = leaf(torch.randn(5, 7, 12, generator=g))
+        a = m.compute_rbf(d1, d2) if kt == "rbf" else m.compute_inv_mult_quad(d1, d2)
+        b = O.compute_rbf(d1, d2, 1.5) if kt == "rbf" else O.compute_inv_mult_quad(d1, d2, 1.5)
+        assert a.shape == b.shape and torch.equal(a, b)
+
+
 def test_zero_division_at_batch_one(ref):
     """wae_mmd.py:114-116 / swae.py:117-119: B=1 raises ZeroDivisionError."""
     m = ref.WAE_MMD(3, 8)
