@@ -191,6 +191,14 @@ KERNEL_BYTES = {
 }
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from `ncu --set full` captures of the SAME workload size
+# (profiles/): (kernel, B, G*K) -> bytes.  Anything not captured reports traffic = null.
+NCU_TRAFFIC = {
+    ("iw_bound_bwd", 4096, 5): (1.208158e9 + 952.969216e6, "profiles/ncu_iw_bound_r01a_summary.csv"),
+    ("iw_bound_fwd", 4096, 5): (1.208144e9 + 4.415744e6, "profiles/ncu_iw_bound_r01a_summary.csv"),
+}
+
+
 def roofline_from_events(wl, B, log):
     """Per-kernel average duration from the CUDA events recorded around every libvaekit launch
     inside the timed region (same stream), turned into achieved GB/s on algorithmic bytes."""
@@ -209,8 +217,10 @@ def roofline_from_events(wl, B, log):
     for k in res:
         res[k]["share_of_kernel_time"] = round(res[k]["ms"] / total, 4)
     d = res[dom]
+    traffic = NCU_TRAFFIC.get((dom, B, GK))
     return {"bound": "hbm", "kernel": dom + "_kernel", "achieved": d["GBps"], "peak": peak, "unit": "GB/s",
-            "frac": round(d["GBps"] / peak, 4), "traffic": None, "peak_source": peak_src,
+            "frac": round(d["GBps"] / peak, 4), "traffic": traffic[0] if traffic else None,
+            "traffic_source": traffic[1] if traffic else None, "peak_source": peak_src,
             "algorithmic_bytes_per_launch": d["bytes"], "ms_per_launch": d["ms"], "kernels": res}
 
 
@@ -514,8 +524,8 @@ class SwaeWorkload(OpWorkload):
         reg = m.reg_weight / (n_glob * (n_glob - 1))
         if world > 1:
             from vaekit import dist as vd
-            proj = vd.shared_tensor_(m.get_random_projections(self.D, self.S).to(z.device))
-            swd = vd.sharded_swd(z, proj, m.p, reg)
+            proj = vd.shared_projections(m, self.D, self.S, z.device)
+            swd = vd.sharded_swd(z, proj, m.p, reg, exchange=os.environ.get("VAEKIT_SWD_EXCHANGE", "peer"))
         else:
             swd = m.compute_swd(z, m.p, reg)
         swd.backward()

@@ -255,6 +255,16 @@ int vk_gemm_nt(const float* A, int64_t a_sn, int64_t a_sk, const float* B, int64
                int64_t c_sn, int64_t c_sj, int64_t N, int64_t J, int64_t K, void* workspace, int64_t workspace_bytes,
                void* stream);
 
+/* vk_gemm_nt_tab: the same GEMM with optional per-column base addresses (device arrays of device pointers):
+ *   a_cols[k] = address of A(0, k) (then A(n, k) = a_cols[k][n * a_sn]; A and a_sk are ignored),
+ *   c_cols[j] = address of C(0, j) (then C(n, j) = c_cols[j][n * c_sn]; C and c_sj are ignored).
+ * A column may live in another GPU's peer-mapped memory: the multi-GPU SWD (vaekit/dist.py, exchange="peer") stores
+ * every projection straight into the segment buffer of the rank that sorts it and reads d/dlat columns straight from
+ * their owners over NVLink, so the exchange that follows / precedes the GEMM is fused into it. */
+int vk_gemm_nt_tab(const float* const* a_cols, const float* A, int64_t a_sn, int64_t a_sk, const float* B, int64_t b_sj,
+                   int64_t b_sk, float* const* c_cols, float* C, int64_t c_sn, int64_t c_sj, int64_t N, int64_t J,
+                   int64_t K, void* workspace, int64_t workspace_bytes, void* stream);
+
 /* ---------------------------------------------------------------------------
  * K5  Beta-TC-VAE latent terms             (reference: models/betatc_vae.py:132-142, 165-211)
  *

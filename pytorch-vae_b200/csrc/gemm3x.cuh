@@ -33,6 +33,11 @@ struct Args {
   int64_t c_sn, c_sj;        // element strides of C(n, j)
   int JH0;                   // columns of the first accumulator half (multiple of 16); the second has Jp - JH0
   int64_t tiles;
+  // Optional column tables (device arrays): a_tab[k] = address of A(0, k), c_tab[j] = address of C(0, j).  A column may
+  // live in ANOTHER GPU's memory (peer-mapped): the multi-GPU SWD stores each projection straight into the segment buffer
+  // of the rank that sorts it and reads d/dlat columns straight from their owners -- the exchange is fused into the GEMM.
+  const float* const* a_tab;
+  float* const* c_tab;
 };
 
 __host__ __device__ inline int rup16(int x) { return (x + 15) / 16 * 16; }
@@ -81,6 +86,10 @@ gemm3x_kernel(Args g, const uint8_t* __restrict__ bimg) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ __align__(8) uint64_t bars[8];
   __shared__ uint32_t tmem_slot;
+  __shared__ const float* a_tab_s[256];                // column tables (K, J <= 256), staged once per CTA
+  __shared__ float* c_tab_s[256];
+  if (g.a_tab) for (int i = threadIdx.x; i < g.K; i += kThreads) a_tab_s[i] = g.a_tab[i];
+  if (g.c_tab) for (int i = threadIdx.x; i < g.J; i += kThreads) c_tab_s[i] = g.c_tab[i];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t sbase = smem_u32(smem);
   auto bar = [&](int i) { return smem_u32(&bars[i]); };
@@ -109,13 +118,19 @@ gemm3x_kernel(Args g, const uint8_t* __restrict__ bimg) {
     // across the wait for the MMAs of the previous tile too; without this the loop exposed one DRAM round trip per
     // 64 bytes and the whole GEMM ran at 1.2 TB/s.
     constexpr int kGroup = 4;
-    const bool vec = g.a_sk == 1 && (g.K & 3) == 0 && (g.a_sn & 3) == 0 && ((uintptr_t)g.A & 15) == 0;
+    const bool vec = !g.a_tab && g.a_sk == 1 && (g.K & 3) == 0 && (g.a_sn & 3) == 0 && ((uintptr_t)g.A & 15) == 0;
     const int groups = (kch + kGroup - 1) / kGroup;
     auto load_unit = [&](float (&v)[16 * kGroup], int64_t tile, int grp) {
       const int64_t n = tile * kRows + warp * 32 + lane;
       const bool live = tile < g.tiles && n < g.N;
       const float* ap = g.A + (live ? n : 0) * g.a_sn;
       const int k0 = grp * (16 * kGroup);
+      if (g.a_tab) {                                  // per-column bases (possibly peer memory): plain loads
+        const int64_t no = (live ? n : 0) * g.a_sn;
+#pragma unroll
+        for (int e = 0; e < 16 * kGroup; ++e) v[e] = (live && k0 + e < g.K) ? a_tab_s[k0 + e][no] : 0.f;
+        return;
+      }
       if (live && k0 + 16 * kGroup <= g.K) {          // whole group in range: no predicates, pointer bumps only
         if (vec) {
           const float4* q = reinterpret_cast<const float4*>(ap + k0);
@@ -153,8 +168,8 @@ gemm3x_kernel(Args g, const uint8_t* __restrict__ bimg) {
     };
     // The tile two rounds ahead is pulled into L2 by bulk prefetches (one row or one k-slice per thread), so the
     // register prefetch one group ahead only has to cover an L2 hit, not a DRAM round trip.
-    const bool pf_rows = vec;                                                       // row-major A: K * 4 bytes per row
-    const bool pf_cols = !vec && g.a_sn == 1 && (g.a_sk & 3) == 0 && ((uintptr_t)g.A & 15) == 0;   // k-major A
+    const bool pf_rows = vec && !g.a_tab;                                                       // row-major A: K * 4 bytes per row
+    const bool pf_cols = !vec && !g.a_tab && g.a_sn == 1 && (g.a_sk & 3) == 0 && ((uintptr_t)g.A & 15) == 0;   // k-major A
     auto prefetch_tile = [&](int64_t tile) {
       if (tile >= g.tiles) return;
       const int64_t n0 = tile * kRows;
@@ -249,7 +264,7 @@ gemm3x_kernel(Args g, const uint8_t* __restrict__ bimg) {
   } else {
     // ===== epilogue: accumulator half -> C with its strides =====
     const int q = warp & 3;
-    const bool vec = g.c_sj == 1 && (g.J & 3) == 0 && (g.c_sn & 3) == 0 && ((uintptr_t)g.C & 15) == 0;
+    const bool vec = !g.c_tab && g.c_sj == 1 && (g.J & 3) == 0 && (g.c_sn & 3) == 0 && ((uintptr_t)g.C & 15) == 0;
     int it = 0;
     for (int64_t tile = blockIdx.x; tile < g.tiles; tile += gridDim.x, ++it) {
       const int64_t n = tile * kRows + q * 32 + lane;
@@ -266,7 +281,14 @@ gemm3x_kernel(Args g, const uint8_t* __restrict__ bimg) {
           tmem_ld16(tAcc + ((uint32_t)(q * 32) << 16) + hoff + c0, r);
           tmem_ld_wait16(r);
           const int j0 = hoff + c0;
-          if (n < g.N && j0 + 16 <= g.J) {            // whole block in range: no predicates, pointer bumps only
+          if (g.c_tab) {                              // per-column bases (possibly peer memory)
+            if (n < g.N) {
+              const int64_t no = n * g.c_sn;
+#pragma unroll
+              for (int e = 0; e < 16; ++e)
+                if (j0 + e < g.J) c_tab_s[j0 + e][no] = __uint_as_float(r[e]);
+            }
+          } else if (n < g.N && j0 + 16 <= g.J) {            // whole block in range: no predicates, pointer bumps only
             if (vec) {
               float4* q = reinterpret_cast<float4*>(cp + j0);
 #pragma unroll
@@ -304,8 +326,10 @@ gemm3x_kernel(Args g, const uint8_t* __restrict__ bimg) {
 
 // C(n, j) = sum_k A(n, k) B(j, k); `bimg` is scratch for the packed B images (3 * Jp * Kp * 2 bytes)
 inline int launch(const float* A, int64_t a_sn, int64_t a_sk, const float* B, int64_t b_sj, int64_t b_sk, float* C,
-                  int64_t c_sn, int64_t c_sj, int64_t N, int J, int K, uint8_t* bimg, cudaStream_t st, const char* what) {
+                  int64_t c_sn, int64_t c_sj, int64_t N, int J, int K, uint8_t* bimg, cudaStream_t st, const char* what,
+                  const float* const* a_tab = nullptr, float* const* c_tab = nullptr) {
   Args g;
+  g.a_tab = a_tab; g.c_tab = c_tab;
   g.A = A; g.C = C; g.N = N; g.J = J; g.K = K; g.Jp = rup16(J); g.Kp = rup16(K);
   g.a_sn = a_sn; g.a_sk = a_sk; g.c_sn = c_sn; g.c_sj = c_sj;
   g.JH0 = rup16(g.Jp / 2);

@@ -264,6 +264,20 @@ extern "C" int vk_gemm_nt(const float* A, int64_t a_sn, int64_t a_sk, const floa
                     (cudaStream_t)stream, "gemm_nt");
 }
 
+extern "C" int vk_gemm_nt_tab(const float* const* a_cols, const float* A, int64_t a_sn, int64_t a_sk, const float* B,
+                              int64_t b_sj, int64_t b_sk, float* const* c_cols, float* C, int64_t c_sn, int64_t c_sj,
+                              int64_t N, int64_t J, int64_t K, void* workspace, int64_t workspace_bytes, void* stream) {
+  VK_REQUIRE((A || a_cols) && B && (C || c_cols) && workspace, VK_ERR_BAD_ARG, "gemm_nt_tab: null pointer");
+  VK_REQUIRE(N >= 1 && J >= 1 && K >= 1, VK_ERR_BAD_ARG, "gemm_nt_tab: empty shape N=%lld J=%lld K=%lld", (long long)N,
+             (long long)J, (long long)K);
+  VK_REQUIRE(J <= 256 && K <= 256 && g3::fits((int)J, (int)K), VK_ERR_UNSUPPORTED,
+             "gemm_nt_tab: J=%lld, K=%lld do not fit the tensor-memory / shared-memory budget of the tcgen05 GEMM",
+             (long long)J, (long long)K);
+  VK_REQUIRE(workspace_bytes >= vk_gemm_nt_workspace_bytes(), VK_ERR_WORKSPACE, "gemm_nt_tab: workspace too small");
+  return g3::launch(A, a_sn, a_sk, B, b_sj, b_sk, C, c_sn, c_sj, N, (int)J, (int)K, (uint8_t*)workspace + kWsHeader,
+                    (cudaStream_t)stream, "gemm_nt_tab", a_cols, c_cols);
+}
+
 extern "C" int vk_mean_scale(const double* sum, double count, float scale, float* out, void* stream) {
   VK_REQUIRE(sum && out && count > 0, VK_ERR_BAD_ARG, "mean_scale: bad argument");
   mean_scale_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(sum, count, scale, out);

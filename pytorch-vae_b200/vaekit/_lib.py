@@ -47,6 +47,7 @@ _SIGNATURES = {
     "vk_seg_sort": ([_p, _p, _i64, _i64, _p, _i64, _p], _i),
     "vk_gemm_nt_workspace_bytes": ([], _i64),
     "vk_gemm_nt": ([_p, _i64, _i64, _p, _i64, _i64, _p, _i64, _i64, _i64, _i64, _i64, _p, _i64, _p], _i),
+    "vk_gemm_nt_tab": ([_p, _p, _i64, _i64, _p, _i64, _i64, _p, _p, _i64, _i64, _i64, _i64, _i64, _p, _i64, _p], _i),
     "vk_tc_workspace_bytes": ([_i64, _i64], _i64),
     "vk_tc_fwd": ([_p, _p, _p, _i64, _i64, _f, _f, _f, _f, _p, _p, _p, _p, _i64, _p], _i),
     "vk_tc_bwd": ([_p, _p, _p, _p, _p, _i64, _i64, _f, _f, _f, _f, _p, _p, _p, _p, _p, _i64, _p], _i),

@@ -104,10 +104,22 @@ def shared_rng_key(device, numel: int, group=None) -> torch.Tensor:
     from . import functional as F
     seed, offset = F.next_philox(device, numel)
     signed = seed - (1 << 64) if seed >= (1 << 63) else seed
-    key = torch.tensor([signed, offset], dtype=torch.int64, device=device)
+    # pinned staging + non-blocking copy: a pageable host->device copy would synchronise the stream every step
+    host = torch.tensor([signed, offset], dtype=torch.int64).pin_memory() if device.type == "cuda" else \
+        torch.tensor([signed, offset], dtype=torch.int64)
+    key = host.to(device, non_blocking=True)
     if _active(group):
         dist.broadcast(key, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
     return key
+
+
+def shared_projections(model, latent_dim: int, num_projections: int, device, group=None) -> torch.Tensor:
+    """The reference's CPU-generated projection directions (swae.py:129-148 via model.get_random_projections), moved to
+    `device` through pinned memory without a host synchronisation and made identical on every rank (rank 0's draw)."""
+    proj = model.get_random_projections(latent_dim, num_samples=num_projections)
+    if torch.device(device).type == "cuda":
+        proj = proj.contiguous().pin_memory().to(device, non_blocking=True)
+    return shared_tensor_(proj, group)
 
 
 def shared_tensor_(t: torch.Tensor, group=None) -> torch.Tensor:
@@ -269,13 +281,14 @@ class _ShardedSwdA2A(torch.autograd.Function):
         order = [i for per_rank in plan for a, b in per_rank for i in range(a, b)]      # projections, wave-major
         proj_w = proj[torch.tensor(order, dtype=torch.long, device=dev)] if waves > 1 else proj
         # ---- stage 1: project the rank's rows wave by wave and start every exchange
+        both_all = torch.empty((S, 2, n), dtype=torch.float32, device=dev)       # wave-major projection order
+        F.swd_project(z_local, proj_w, out=both_all[:, 0, :])
+        F.swd_project(prior_local, proj_w, out=both_all[:, 1, :])
         pending, row0 = [], 0
         for per_rank in plan:
             splits = [b - a for a, b in per_rank]
             Sq, mine = sum(splits), splits[rank]
-            both = torch.empty((Sq, 2, n), dtype=torch.float32, device=dev)
-            F.swd_project(z_local, proj_w[row0:row0 + Sq], out=both[:, 0, :])
-            F.swd_project(prior_local, proj_w[row0:row0 + Sq], out=both[:, 1, :])
+            both = both_all[row0:row0 + Sq]
             recv = torch.empty((world * mine, 2, n), dtype=torch.float32, device=dev)
             work = _all_to_all(recv, both, [mine] * world, splits, group, True)
             pending.append((work, recv, both, splits, mine, row0))
@@ -317,15 +330,106 @@ class _ShardedSwdA2A(torch.autograd.Function):
         return F.scale_by_scalar(ctx.saved_tensors[0], g.contiguous(), ctx.factor), None, None, None, None, None
 
 
+# ---- exchange fused into the GEMMs over peer-mapped memory (NVLink / NVSwitch) ---------------------------------------
+class _PeerSegments:
+    """Symmetric (peer-mapped) segment buffers of one (group, n_local, S) shape: on every rank a [2 parities][2 channels
+    (z, prior)][S_max][N] fp32 block, plus the column tables that tell the GEMMs where each projection lives:
+      store[parity][channel][s] = address, in the memory of the rank that OWNS projection s, of that rank's
+                                  segment row for s at column rank * n (where this rank's n values go);
+      load[parity][s]           = address of the same spot in the z channel (after the sort it holds d/dlat)."""
+
+    def __init__(self, group, device, n, S):
+        import torch.distributed._symmetric_memory as symm
+        world, rank = world_rank(group)
+        self.world, self.rank, self.n, self.S, self.N = world, rank, n, S, n * world
+        self.parts = [plan_projections(S, world, r) for r in range(world)]
+        self.s_max = max(b - a for a, b in self.parts)
+        self.mine = self.parts[rank][1] - self.parts[rank][0]
+        shape = (2, 2, self.s_max, self.N)
+        self.buf = symm.empty(shape, dtype=torch.float32, device=device)
+        self.hdl = symm.rendezvous(self.buf, group if group is not None else dist.group.WORLD)
+        ptrs = self.hdl.buffer_ptrs
+        self.store, self.load = [], []
+        for parity in range(2):
+            per_chan = []
+            for chan in range(2):
+                addr = []
+                for r, (a, b) in enumerate(self.parts):
+                    for j in range(b - a):
+                        off = ((parity * 2 + chan) * self.s_max + j) * self.N + rank * n
+                        addr.append(ptrs[r] + 4 * off)
+                per_chan.append(torch.tensor(addr, dtype=torch.int64, device=device))
+            self.store.append(per_chan)
+            self.load.append(per_chan[0])
+        self.parity = 0
+
+    def segments(self, parity):
+        """This rank's (lat, pri) [S_r, N] views of the local block."""
+        return self.buf[parity, 0, :self.mine], self.buf[parity, 1, :self.mine]
+
+
+_peer_cache = {}
+
+
+def _peer_segments(group, device, n, S) -> "_PeerSegments":
+    key = (id(group) if group is not None else 0, device.index, n, S)
+    if key not in _peer_cache:
+        _peer_cache[key] = _PeerSegments(group, device, n, S)
+    return _peer_cache[key]
+
+
+class _ShardedSwdPeer(torch.autograd.Function):
+    """swae.py:151-179 on the global batch with both exchanges FUSED into the tcgen05 GEMMs over peer memory: the
+    projection GEMM's epilogue stores each projected value straight into the segment buffer of the rank that sorts that
+    projection (vk_gemm_nt_tab column table), and the gradient GEMM's producer warps read d/dlat columns straight from
+    their owners.  No NCCL transfer, no staging copy, no permute; two device-side barriers per step, buffers
+    double-buffered by step parity so a rank never writes a block a slower peer is still reading."""
+
+    @staticmethod
+    def forward(ctx, z_local, proj, p, reg_weight, group):
+        from . import functional as F
+        world, rank = world_rank(group)
+        n, D = z_local.shape
+        S = proj.shape[0]
+        N = n * world
+        ps = _peer_segments(group, z_local.device, n, S)
+        parity, ps.parity = ps.parity, ps.parity ^ 1
+        key = shared_rng_key(z_local.device, N * D, group)
+        prior_local = local_prior_rows(n, D, key, rank)
+        F.swd_project_cols(z_local.contiguous(), proj, ps.store[parity][0])
+        F.swd_project_cols(prior_local, proj, ps.store[parity][1])
+        ps.hdl.barrier(channel=0)                                  # every rank's projections have landed
+        lat, pri = ps.segments(parity)
+        total = F.swd_segments(lat, pri, p, want_grad=True)        # lat <- d sum / d lat (sample order)
+        ps.hdl.barrier(channel=1)                                  # every rank's d/dlat is final
+        reduce_sum_(total, group)
+        grad_local = F.swd_project_back_cols(ps.load[parity], n, proj)
+        ctx.save_for_backward(grad_local)
+        count = float(N) * float(S)
+        ctx.factor = reg_weight / count
+        ctx.set_materialize_grads(False)
+        return F.mean_scale(total, count, reg_weight)
+
+    @staticmethod
+    def backward(ctx, g):
+        from . import functional as F
+        if g is None:
+            return (None,) * 5
+        return F.scale_by_scalar(ctx.saved_tensors[0], g.contiguous(), ctx.factor), None, None, None, None
+
+
 def sharded_swd(z_local, proj, p, reg_weight, group=None, exchange="all_to_all", waves=None):
     """Sliced-Wasserstein distance of the GLOBAL batch; `proj` [S, D] must be identical on every rank
     (use shared_tensor_ on the reference's CPU-generated directions).  exchange = "all_to_all" (projected values travel;
-    every stage shrinks with the world size; `waves` pieces pipeline the exchange under the sorts) or "all_gather" (z travels; each rank projects all rows on its slice of
+    every stage shrinks with the world size; `waves` pieces pipeline the exchange under the sorts), "peer" (the same
+    decomposition with both exchanges fused into the GEMMs over peer-mapped memory, CUDA + NVLink only) or "all_gather" (z travels; each rank projects all rows on its slice of
     the projections and the [N, D] gradient is reduce-scattered -- kept for shapes the tcgen05 GEMM does not take)."""
-    if exchange == "all_to_all":
+    if exchange == "peer" and world_rank(group)[0] > 1:
+        return _ShardedSwdPeer.apply(z_local, proj.contiguous(), float(p), float(reg_weight), group)
+    if exchange in ("all_to_all", "peer"):
         if waves is None:                       # pipeline depth: pieces of the rank's projection slice
             world, _ = world_rank(group)
-            waves = 1 if world == 1 else max(1, min(4, proj.shape[0] // world))
+            waves = 1 if world == 1 else max(1, min(2, proj.shape[0] // world))
         return _ShardedSwdA2A.apply(z_local, proj, float(p), float(reg_weight), group, int(waves))
     if exchange == "all_gather":
         return _ShardedSwd.apply(z_local, proj, float(p), float(reg_weight), group)

@@ -549,6 +549,40 @@ def swd_project_back(g_lat, proj):
     return out
 
 
+def swd_project_cols(x, proj, c_cols):
+    """swd_project with every output column stored at its own base address: c_cols is an int64 CUDA tensor [S] of
+    device pointers, c_cols[s] = address of out(s, 0) (contiguous along the rows of x).  The addresses may be
+    peer-mapped memory of other GPUs (vk_gemm_nt_tab)."""
+    L.require(x, "x", dims=(2,)); L.require(proj, "projections", dims=(2,))
+    n, D = x.shape
+    S = proj.shape[0]
+    if c_cols.dtype != torch.int64 or not c_cols.is_cuda or c_cols.numel() != S:
+        raise RuntimeError("vaekit: column table must be an int64 CUDA tensor with one address per projection")
+    if n * S == 0:
+        return
+    ws = L.workspace(x.device, int(L.lib().vk_gemm_nt_workspace_bytes()))
+    with torch.cuda.device(x.device):
+        L.call("gemm_nt_tab", None, L.ptr(x), x.stride(0), x.stride(1), L.ptr(proj), proj.stride(0), proj.stride(1),
+               L.ptr(c_cols), None, 1, 0, n, S, D, L.ptr(ws), ws.numel(), L.stream_ptr())
+
+
+def swd_project_back_cols(a_cols, n, proj):
+    """swd_project_back with every d/dlat column read from its own base address (a_cols[s] = address of g_lat(s, 0),
+    n contiguous floats, possibly in a peer GPU's memory)."""
+    L.require(proj, "projections", dims=(2,))
+    S, D = proj.shape
+    if a_cols.dtype != torch.int64 or not a_cols.is_cuda or a_cols.numel() != S:
+        raise RuntimeError("vaekit: column table must be an int64 CUDA tensor with one address per projection")
+    out = torch.empty((n, D), dtype=torch.float32, device=proj.device)
+    if n == 0:
+        return out
+    ws = L.workspace(proj.device, int(L.lib().vk_gemm_nt_workspace_bytes()))
+    with torch.cuda.device(proj.device):
+        L.call("gemm_nt_tab", L.ptr(a_cols), None, 1, 0, L.ptr(proj), proj.stride(1), proj.stride(0), None, L.ptr(out), D, 1,
+               n, D, S, L.ptr(ws), ws.numel(), L.stream_ptr())
+    return out
+
+
 def seg_sort(keys, want_perm=False):
     """Ascending sort of every row of a [segments, n] fp32 CUDA tensor with the library's radix sort.
     Returns (sorted, perm or None); perm[s, i] (int64) is the source column of sorted[s, i]."""

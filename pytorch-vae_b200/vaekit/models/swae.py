@@ -45,6 +45,8 @@ class SWAE(DeterministicConvAE):
         """swae.py:151-179: prior_z from the contract Philox stream; projection GEMM, per-projection radix sort,
         loss and d/dz in one library call (vk_swd_fwd)."""
         prior_z = F.philox_normal(z.shape, z.device)
-        proj = self.get_random_projections(self.latent_dim, num_samples=self.num_projections).to(z.device)
+        proj = self.get_random_projections(self.latent_dim, num_samples=self.num_projections)
+        # through pinned memory, non-blocking: a pageable .to(device) would synchronise the stream on every call
+        proj = proj.contiguous().pin_memory().to(z.device, non_blocking=True) if z.is_cuda else proj.to(z.device)
         self.last_prior_z, self.last_proj = prior_z, proj
         return F.swd(z, prior_z, proj, p, reg_weight)

@@ -1,0 +1,20 @@
+#!/bin/bash
+TAG=${1:-r01n}
+mkdir -p gpurun_out
+run() { # workload n
+  timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $2 --master-addr 127.0.0.1 --master-port $((29500 + $2)) \
+    bench.py --workload $1 --gpus $2 --steps 10 --warmup 3 --no-cpu --no-e2e > gpurun_out/scale_$1_${TAG}_n$2.json 2> gpurun_out/scale_$1_${TAG}_n$2.err
+  python - <<PY
+import json
+try:
+    d=json.loads(open("gpurun_out/scale_$1_${TAG}_n$2.json").read().strip().splitlines()[-1])
+    print("$1 n=$2", d["ms_per_step"], d["value"], d["roofline"]["frac"], {k:round(v["ms"],4) for k,v in d["roofline"]["calls"].items()})
+except Exception as e:
+    print("$1 n=$2 failed", e); print(open("gpurun_out/scale_$1_${TAG}_n$2.err").read()[-1500:])
+PY
+}
+run swae 8
+run swae 4
+run wae_mmd_rbf 8
+timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29520 scripts/prof_swd_dist.py 1 peer 2>&1 | grep -v "^\*\|OMP_NUM\|^$\|warn\|Warn" | head -24 | tee gpurun_out/prof_swd_dist_n8_peer.log
+VAEKIT_SWD_EXCHANGE=all_to_all run swae 8 2>&1 | sed 's/^/a2a: /'

@@ -51,7 +51,7 @@ def _worker(rank, world, port, out):
         proj = O.random_projections(D, S).to(dev) if rank == 0 else torch.zeros(S, D, device=dev)
         vd.shared_tensor_(proj)
         for key, exchange, waves in (("swd", "all_to_all", None), ("swd_w1", "all_to_all", 1), ("swd_w3", "all_to_all", 3),
-                                     ("swd_ag", "all_gather", None)):
+                                     ("swd_ag", "all_gather", None), ("swd_peer", "peer", None), ("swd_peer2", "peer", None)):
             torch.manual_seed(SEED)
             z = _local_z(rank, dev).requires_grad_(True)
             swd = vd.sharded_swd(z, proj, 2.0, 7.0, exchange=exchange, waves=waves)
@@ -110,7 +110,7 @@ def test_sharded_ops_match_single_gpu_and_oracle(tmp_path):
     zs = z_all.clone().requires_grad_(True)
     one = F.swd(zs, prior, proj, 2.0, 7.0)
     one.backward()
-    for key in ("swd", "swd_w1", "swd_w3", "swd_ag"):                                 # all-to-all of projected values / all-gather of z
+    for key in ("swd", "swd_w1", "swd_w3", "swd_ag", "swd_peer", "swd_peer2"):     # peer twice: both buffer parities                               # all-to-all of projected values / all-gather of z
         for r in range(world):
             assert abs(parts[r][key][0].item() - one.item()) <= 1e-6 * abs(one.item()), (key, r)
         g = torch.cat([parts[r][key][1] for r in range(world)])
