@@ -546,18 +546,20 @@ class SwaeWorkload(OpWorkload):
 
 
 class BetaTcWorkload(OpWorkload):
+    scaling = "strong"          # fixed global batch, anchor rows sharded after an all-gather of z, mu, log_var
+
     def __init__(self):
         self.N, self.D = 4096, 128
         self.desc = "BetaTC-VAE latent terms (log_q_z, per-dim LSE, MI/TC/KLD), batch 4096, latent 128 (SURVEY 8(d) extra)"
         self.cpu_sample, self.bound = 1024, "mufu"
-        self.dominant = "tc_bwd"
+        self.dominant, self.dominant_sharded = "tc_bwd", "tc_bwd_rows"
 
     def model(self):
         from vaekit.models import vae_models
         return vae_models["BetaTCVAE"](3, self.D).eval()
 
     def make(self, dev, rank, world, n=None):
-        n = n or self.N
+        n = n or self.N // world
         g = torch.Generator(device=dev).manual_seed(1265 + rank)
         mu = torch.randn(n, self.D, device=dev, generator=g)
         lv = 0.3 * torch.randn(n, self.D, device=dev, generator=g)
@@ -568,12 +570,17 @@ class BetaTcWorkload(OpWorkload):
         mu, lv = t["mu"].requires_grad_(True), t["lv"].requires_grad_(True)
         mu.grad = lv.grad = None
         z = m.reparameterize(mu, lv)
-        latent, terms = F.betatc_terms(z, mu, lv, 0.00025, m.alpha, m.beta, m.gamma)
+        if world > 1:
+            from vaekit import dist as vd
+            latent, terms = vd.sharded_betatc_terms(z, mu, lv, 0.00025, m.alpha, m.beta, m.gamma)
+        else:
+            latent, terms = F.betatc_terms(z, mu, lv, 0.00025, m.alpha, m.beta, m.gamma)
         latent.backward()
         return {"latent": latent}
 
     def work(self, world):
-        return {"tc_fwd": float(self.N) * self.N * self.D, "tc_bwd": 2.0 * self.N * self.N * self.D}, "Gexp/s"
+        e = float(self.N) * self.N * self.D
+        return {"tc_fwd": e, "tc_bwd": 2.0 * e, "tc_fwd_rows": e / world, "tc_bwd_rows": 2.0 * e / world}, "Gexp/s"
 
     def cpu_step(self, t):
         import vae_oracle as O
@@ -718,8 +725,9 @@ def run_op_gpu_arm(args, wl):
                 "higher_is_better": True, "scaling": wl.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": wl.desc, "global_batch": wl.units(world),
                            "l2_policy": "synthetic inputs regenerated never; working set (operand images / sort buffers) larger than L2 or tensor-bound",
-                           "parallelism": ("%s over %d ranks" % ("row-sharded after all-gather" if isinstance(wl, WaeMmd) else
-                                                                  "projection-sharded after all-gather" if isinstance(wl, SwaeWorkload)
+                           "parallelism": ("%s over %d ranks" % ("row-sharded after all-gather" if isinstance(wl, (WaeMmd, BetaTcWorkload)) else
+                                                                  "projection-sharded, exchange fused into the GEMMs over peer memory (%s)"
+                                                                  % os.environ.get("VAEKIT_SWD_EXCHANGE", "peer") if isinstance(wl, SwaeWorkload)
                                                                   else "batch-sharded", world)) if world > 1 else "single GPU",
                            "step": "forward + backward through the drop-in model API"},
                 "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,

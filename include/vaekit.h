@@ -285,6 +285,18 @@ int vk_tc_fwd(const float* z, const float* mu, const float* log_var, int64_t B, 
 int vk_tc_bwd(const float* z, const float* mu, const float* log_var, const float* lqz, const float* lse,
               int64_t B, int64_t D, float M_N, float alpha, float beta, float gamma_anneal, const float* g_loss,
               float* g_z, float* g_mu, float* g_lv, void* workspace, int64_t workspace_bytes, void* stream);
+/* Row-block forms for the multi-GPU decomposition (all-gather z, mu, log_var; rank r owns anchor rows
+ * [row_begin, row_end) against all B partner columns).  All pointers address the FULL [B, ...] arrays; only the rows of
+ * the range are written (lqz_out, lse_out, g_z, g_mu, g_lv), and out[4] holds the range's share of the batch means, so
+ * the shares of disjoint ranges add up to vk_tc_fwd's out.  The backward needs lqz / lse of ALL rows (all-gathered):
+ * g_mu / g_lv of a partner column sum over every anchor row.  Latent dim <= 128. */
+int vk_tc_fwd_rows(const float* z, const float* mu, const float* log_var, int64_t B, int64_t D, int64_t row_begin,
+                   int64_t row_end, float M_N, float alpha, float beta, float gamma_anneal, float* lqz_out, float* lse_out,
+                   float* out /*[4]*/, void* workspace, int64_t workspace_bytes, void* stream);
+int vk_tc_bwd_rows(const float* z, const float* mu, const float* log_var, const float* lqz, const float* lse, int64_t B,
+                   int64_t D, int64_t row_begin, int64_t row_end, float M_N, float alpha, float beta, float gamma_anneal,
+                   const float* g_loss, float* g_z, float* g_mu, float* g_lv, void* workspace, int64_t workspace_bytes,
+                   void* stream);
 
 #ifdef __cplusplus
 }

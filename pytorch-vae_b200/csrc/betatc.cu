@@ -28,6 +28,7 @@ constexpr float kLog2e = 1.4426950408889634f;
 
 struct TcParams {
   int B, D;
+  int r0, r1;                      // anchor rows / columns this call covers (a rank's row block; [0, B) on one GPU)
   float lw_ds, lw_strat, lw_bm1;   // log importance weights: column 0, column 1 (and [B-2,0]), everything else
   float alpha, beta, gamma_anneal; // loss = alpha*mi + (beta*tc + anneal*gamma*kld)
 };
@@ -302,6 +303,7 @@ int make_params(int64_t B, int64_t D, float M_N, float alpha, float beta, float 
   VK_REQUIRE(B >= 2 && D >= 1, VK_ERR_BAD_ARG, "betatc: needs batch >= 2 and latent dim >= 1 (got %lld, %lld)", (long long)B, (long long)D);
   VK_REQUIRE(B <= (1 << 20) && D <= 1024, VK_ERR_UNSUPPORTED, "betatc: B=%lld or D=%lld too large", (long long)B, (long long)D);
   p.B = (int)B; p.D = (int)D;
+  p.r0 = 0; p.r1 = (int)B;
   // betatc_vae.py:177-183: the table is fp32; its log is taken in fp32
   const double ds = (1.0 / (double)M_N) * (double)B;
   const double strat = (ds - (double)B + 1.0) / (ds * (double)(B - 1));
@@ -325,13 +327,18 @@ extern "C" int64_t vk_tc_workspace_bytes(int64_t B, int64_t D) {
   return (int64_t)kWsHeader + blocks * 4 * 8 + 256 + 2 * B * D * 4 + 256 + B * 8;
 }
 
-extern "C" int vk_tc_fwd(const float* z, const float* mu, const float* log_var, int64_t B, int64_t D, float M_N,
-                         float alpha, float beta, float gamma_anneal, float* lqz_out, float* lse_out, float* out,
-                         void* workspace, int64_t workspace_bytes, void* stream) {
+static int tc_fwd_impl(const float* z, const float* mu, const float* log_var, int64_t B, int64_t D, int64_t row_begin,
+                       int64_t row_end, float M_N, float alpha, float beta, float gamma_anneal, float* lqz_out,
+                       float* lse_out, float* out, void* workspace, int64_t workspace_bytes, void* stream) {
   VK_REQUIRE(z && mu && log_var && lqz_out && lse_out && out && workspace, VK_ERR_BAD_ARG, "tc_fwd: null pointer");
   TcParams p;
   int rc = make_params(B, D, M_N, alpha, beta, gamma_anneal, p);
   if (rc != VK_OK) return rc;
+  VK_REQUIRE(0 <= row_begin && row_begin < row_end && row_end <= B, VK_ERR_BAD_ARG, "tc_fwd: bad row range [%lld, %lld) of %lld",
+             (long long)row_begin, (long long)row_end, (long long)B);
+  VK_REQUIRE(D <= 128 || (row_begin == 0 && row_end == B), VK_ERR_UNSUPPORTED,
+             "tc_fwd: row ranges need latent dim <= 128 (got %lld)", (long long)D);
+  p.r0 = (int)row_begin; p.r1 = (int)row_end;
   VK_REQUIRE(workspace_bytes >= vk_tc_workspace_bytes(B, D), VK_ERR_WORKSPACE, "tc_fwd: workspace too small");
   cudaStream_t st = (cudaStream_t)stream;
   uint8_t* ws = (uint8_t*)workspace;
@@ -347,7 +354,7 @@ extern "C" int vk_tc_fwd(const float* z, const float* mu, const float* log_var, 
     const int cfg = D <= 32 ? 0 : (D <= 64 ? 1 : 2);
     const int DP = cfg == 0 ? 32 : (cfg == 1 ? 64 : 128), NS = 1;
     const int per_cta = tiled::kTW / NS * tiled::kR;
-    const int tb = (int)((B + per_cta - 1) / per_cta);
+    const int tb = (int)((p.r1 - p.r0 + per_cta - 1) / per_cta);
     const size_t tsm = tiled::smem_bytes(DP);
     double* Cb = (double*)(((uintptr_t)(C0 + B * D) + 255) & ~(uintptr_t)255);
     tiled::prep_kernel<<<prep_blocks, 256, 0, st>>>(log_var, p, H, C0);
@@ -366,14 +373,33 @@ extern "C" int vk_tc_fwd(const float* z, const float* mu, const float* log_var, 
   return check_launch("tc_fwd");
 }
 
-extern "C" int vk_tc_bwd(const float* z, const float* mu, const float* log_var, const float* lqz, const float* lse,
-                         int64_t B, int64_t D, float M_N, float alpha, float beta, float gamma_anneal,
-                         const float* g_loss, float* g_z, float* g_mu, float* g_lv, void* workspace,
-                         int64_t workspace_bytes, void* stream) {
+extern "C" int vk_tc_fwd(const float* z, const float* mu, const float* log_var, int64_t B, int64_t D, float M_N,
+                         float alpha, float beta, float gamma_anneal, float* lqz_out, float* lse_out, float* out,
+                         void* workspace, int64_t workspace_bytes, void* stream) {
+  return tc_fwd_impl(z, mu, log_var, B, D, 0, B, M_N, alpha, beta, gamma_anneal, lqz_out, lse_out, out, workspace,
+                     workspace_bytes, stream);
+}
+
+extern "C" int vk_tc_fwd_rows(const float* z, const float* mu, const float* log_var, int64_t B, int64_t D, int64_t row_begin,
+                              int64_t row_end, float M_N, float alpha, float beta, float gamma_anneal, float* lqz_out,
+                              float* lse_out, float* out, void* workspace, int64_t workspace_bytes, void* stream) {
+  return tc_fwd_impl(z, mu, log_var, B, D, row_begin, row_end, M_N, alpha, beta, gamma_anneal, lqz_out, lse_out, out,
+                     workspace, workspace_bytes, stream);
+}
+
+static int tc_bwd_impl(const float* z, const float* mu, const float* log_var, const float* lqz, const float* lse, int64_t B,
+                       int64_t D, int64_t row_begin, int64_t row_end, float M_N, float alpha, float beta, float gamma_anneal,
+                       const float* g_loss, float* g_z, float* g_mu, float* g_lv, void* workspace, int64_t workspace_bytes,
+                       void* stream) {
   VK_REQUIRE(z && mu && log_var && lqz && lse && g_z && g_mu && g_lv && workspace, VK_ERR_BAD_ARG, "tc_bwd: null pointer");
   TcParams p;
   int rc = make_params(B, D, M_N, alpha, beta, gamma_anneal, p);
   if (rc != VK_OK) return rc;
+  VK_REQUIRE(0 <= row_begin && row_begin < row_end && row_end <= B, VK_ERR_BAD_ARG, "tc_bwd: bad row range [%lld, %lld) of %lld",
+             (long long)row_begin, (long long)row_end, (long long)B);
+  VK_REQUIRE(D <= 128 || (row_begin == 0 && row_end == B), VK_ERR_UNSUPPORTED,
+             "tc_bwd: row ranges need latent dim <= 128 (got %lld)", (long long)D);
+  p.r0 = (int)row_begin; p.r1 = (int)row_end;
   VK_REQUIRE(workspace_bytes >= vk_tc_workspace_bytes(B, D), VK_ERR_WORKSPACE, "tc_bwd: workspace too small");
   cudaStream_t st = (cudaStream_t)stream;
   uint8_t* ws = (uint8_t*)workspace;
@@ -385,7 +411,7 @@ extern "C" int vk_tc_bwd(const float* z, const float* mu, const float* log_var, 
     const int cfg = D <= 32 ? 0 : (D <= 64 ? 1 : 2);
     const int DP = cfg == 0 ? 32 : (cfg == 1 ? 64 : 128), NS = 1;
     const int per_cta = tiled::kTW / NS * tiled::kR;
-    const int tb = (int)((B + per_cta - 1) / per_cta);
+    const int tb = (int)((p.r1 - p.r0 + per_cta - 1) / per_cta);
     const size_t tsm = tiled::smem_bytes(DP);
     double* Cb = (double*)(((uintptr_t)(C0 + B * D) + 255) & ~(uintptr_t)255);
     tiled::prep_kernel<<<prep_blocks, 256, 0, st>>>(log_var, p, H, C0);
@@ -407,4 +433,20 @@ extern "C" int vk_tc_bwd(const float* z, const float* mu, const float* log_var, 
   tc_bwd_kernel<true><<<blocks, 32 * kW, sm, st>>>(z, mu, H, C0, lqz, lse, p, g_loss, g_z, g_mu, g_lv);
   tc_bwd_kernel<false><<<blocks, 32 * kW, sm, st>>>(z, mu, H, C0, lqz, lse, p, g_loss, g_z, g_mu, g_lv);
   return check_launch("tc_bwd");
+}
+
+extern "C" int vk_tc_bwd(const float* z, const float* mu, const float* log_var, const float* lqz, const float* lse,
+                         int64_t B, int64_t D, float M_N, float alpha, float beta, float gamma_anneal,
+                         const float* g_loss, float* g_z, float* g_mu, float* g_lv, void* workspace,
+                         int64_t workspace_bytes, void* stream) {
+  return tc_bwd_impl(z, mu, log_var, lqz, lse, B, D, 0, B, M_N, alpha, beta, gamma_anneal, g_loss, g_z, g_mu, g_lv, workspace,
+                     workspace_bytes, stream);
+}
+
+extern "C" int vk_tc_bwd_rows(const float* z, const float* mu, const float* log_var, const float* lqz, const float* lse,
+                              int64_t B, int64_t D, int64_t row_begin, int64_t row_end, float M_N, float alpha, float beta,
+                              float gamma_anneal, const float* g_loss, float* g_z, float* g_mu, float* g_lv,
+                              void* workspace, int64_t workspace_bytes, void* stream) {
+  return tc_bwd_impl(z, mu, log_var, lqz, lse, B, D, row_begin, row_end, M_N, alpha, beta, gamma_anneal, g_loss, g_z, g_mu,
+                     g_lv, workspace, workspace_bytes, stream);
 }

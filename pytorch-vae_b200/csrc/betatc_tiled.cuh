@@ -137,14 +137,14 @@ fwd_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const floa
   constexpr int kBuf = 2 * kTR + 3 * kTR * DP;       // floats per staging buffer: Cb (double) | mu | hs | cs
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int grp = w / NS, dbase = (w % NS) * 32 * KD;
-  const int i0 = (blockIdx.x * (kTW / NS) + grp) * kR;
+  const int i0 = p.r0 + (blockIdx.x * (kTW / NS) + grp) * kR;   // anchors [p.r0, p.r1): a rank's row block
   float z[kR][KD], m[kR][KD], s[kR][KD];
 #pragma unroll
   for (int r = 0; r < kR; ++r)
 #pragma unroll
     for (int k = 0; k < KD; ++k) {
       const int d = dbase + lane + 32 * k;
-      z[r][k] = (i0 + r < p.B && d < p.D) ? Z[(size_t)(i0 + r) * p.D + d] : 0.f;
+      z[r][k] = (i0 + r < p.r1 && d < p.D) ? Z[(size_t)(i0 + r) * p.D + d] : 0.f;
       m[r][k] = -INFINITY;
       s[r][k] = 0.f;
     }
@@ -257,7 +257,7 @@ fwd_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const floa
 #pragma unroll
     for (int k = 0; k < KD; ++k) {
       const int d = dbase + lane + 32 * k;
-      if (i < p.B && d < p.D) {
+      if (i < p.r1 && d < p.D) {
         const size_t o = (size_t)i * p.D + d;
         const float l = (m[r][k] + log2f(s[r][k])) * kLn2;
         lse_out[o] = l;
@@ -268,7 +268,7 @@ fwd_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const floa
       }
     }
     lpq = warp_sum(lpq); lqzx = warp_sum(lqzx); lpz = warp_sum(lpz);
-    if (i < p.B) {
+    if (i < p.r1) {
       if (dbase == 0) {                              // one of the NS warps of the group owns the row value
         if (lane == 0) { lqz_out[i] = lqz; lqz_out[p.B + i] = lqr; }
         t_qz += lqz;
@@ -320,7 +320,7 @@ bwd_rows_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
   constexpr int kBuf = 2 * kTR + 3 * kTR * DP;
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int grp = w / NS, dbase = (w % NS) * 32 * KD;
-  const int i0 = (blockIdx.x * (kTW / NS) + grp) * kR;
+  const int i0 = p.r0 + (blockIdx.x * (kTW / NS) + grp) * kR;   // anchors [p.r0, p.r1): a rank's row block
   const float g = g_loss ? *g_loss : 1.f;
   const float invB = 1.f / (float)p.B;
   const float cq = (p.beta - p.alpha) * invB * g, cp = (p.gamma_anneal - p.beta) * invB * g;
@@ -330,7 +330,7 @@ bwd_rows_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
 #pragma unroll
     for (int k = 0; k < KD; ++k) {
       const int d = dbase + lane + 32 * k;
-      const bool ok = i0 + r < p.B && d < p.D;
+      const bool ok = i0 + r < p.r1 && d < p.D;
       z[r][k] = ok ? Z[(size_t)(i0 + r) * p.D + d] : 0.f;
       l2[r][k] = ok ? lse[(size_t)(i0 + r) * p.D + d] * kLog2e : 0.f;
       gz[r][k] = 0.f;
@@ -338,7 +338,7 @@ bwd_rows_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
   // log q(z_i) (log2 units) of the anchor of this lane's pair slot q = lane >> 1
   const int iq = i0 + (lane >> (kPSh + 1));
   const int pq = (lane >> 1) & (kP - 1);
-  const double lqz2 = iq < p.B ? ((double)lqz[iq] + (double)lqz[p.B + iq]) * 1.4426950408889634 : (double)INFINITY;
+  const double lqz2 = iq < p.r1 ? ((double)lqz[iq] + (double)lqz[p.B + iq]) * 1.4426950408889634 : (double)INFINITY;
   const float dcorr = (p.lw_strat - p.lw_ds) * kLog2e;
   const int r_special = p.B - 2 - i0;
   auto issue = [&](int t, int buf) {
@@ -425,7 +425,7 @@ bwd_rows_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
 #pragma unroll
     for (int k = 0; k < KD; ++k) {
       const int i = i0 + r, d = dbase + lane + 32 * k;
-      if (i < p.B && d < p.D) {
+      if (i < p.r1 && d < p.D) {
         const size_t o = (size_t)i * p.D + d;
         const float df = z[r][k] - MU[o];
         const float t = expf(-LV[o]) * df;                           // 2 h (z - mu)
@@ -452,7 +452,7 @@ bwd_cols_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
   constexpr int kBuf = 2 * kTR + 3 * kTR * DP;       // (same size as the other sweeps; the third tile is unused here)
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int grp = w / NS, dbase = (w % NS) * 32 * KD;
-  const int c0 = (blockIdx.x * (kTW / NS) + grp) * kR;   // first anchor column of this warp
+  const int c0 = p.r0 + (blockIdx.x * (kTW / NS) + grp) * kR;   // first anchor column of this warp, in [p.r0, p.r1)
   const float g = g_loss ? *g_loss : 1.f;
   const float invB = 1.f / (float)p.B;
   const float cq = (p.beta - p.alpha) * invB * g, cp = (p.gamma_anneal - p.beta) * invB * g;
@@ -462,7 +462,7 @@ bwd_cols_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
 #pragma unroll
     for (int k = 0; k < KD; ++k) {
       const int d = dbase + lane + 32 * k;
-      const bool ok = c0 + r < p.B && d < p.D;
+      const bool ok = c0 + r < p.r1 && d < p.D;
       const size_t o = (size_t)(c0 + r) * p.D + d;
       mu[r][k] = ok ? MU[o] : 0.f;
       hs[r][k] = ok ? Hs[o] : 0.f;
@@ -471,7 +471,7 @@ bwd_cols_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
     }
   const float dcorr = (p.lw_strat - p.lw_ds) * kLog2e;
   const int pq = (lane >> 1) & (kP - 1);                    // partner slot of this lane's pair
-  const bool anchor_dead = c0 + (lane >> (kPSh + 1)) >= p.B;
+  const bool anchor_dead = c0 + (lane >> (kPSh + 1)) >= p.r1;
   const double cbq = anchor_dead ? 0.0 : Cb[c0 + (lane >> (kPSh + 1))];
   auto issue = [&](int t, int buf) {
     float* base = sm + buf * kBuf;
@@ -556,7 +556,7 @@ bwd_cols_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
 #pragma unroll
     for (int k = 0; k < KD; ++k) {
       const int j = c0 + r, d = dbase + lane + 32 * k;
-      if (j < p.B && d < p.D) {
+      if (j < p.r1 && d < p.D) {
         const size_t o = (size_t)j * p.D + d;
         const float df = Z[o] - mu[r][k];
         const float h2 = expf(-LV[o]);                               // 2 h

@@ -51,6 +51,8 @@ _SIGNATURES = {
     "vk_tc_workspace_bytes": ([_i64, _i64], _i64),
     "vk_tc_fwd": ([_p, _p, _p, _i64, _i64, _f, _f, _f, _f, _p, _p, _p, _p, _i64, _p], _i),
     "vk_tc_bwd": ([_p, _p, _p, _p, _p, _i64, _i64, _f, _f, _f, _f, _p, _p, _p, _p, _p, _i64, _p], _i),
+    "vk_tc_fwd_rows": ([_p, _p, _p, _i64, _i64, _i64, _i64, _f, _f, _f, _f, _p, _p, _p, _p, _i64, _p], _i),
+    "vk_tc_bwd_rows": ([_p, _p, _p, _p, _p, _i64, _i64, _i64, _i64, _f, _f, _f, _f, _p, _p, _p, _p, _p, _i64, _p], _i),
     "vk_iw_bound_bwd": ([_p, _p, _p, _p, _i64, _i64, _i64, _i64, _f, _p, _p, _p, _p, _p, _p, _p], _i),
 }
 

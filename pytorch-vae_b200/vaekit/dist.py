@@ -14,6 +14,10 @@ with the quadratic / sort work split across ranks.
   all-reduce of the float64 loss sum.  (The older all-gather-z / reduce-scatter-gradient form is kept as
   exchange="all_gather".)
 
+* BetaTC (betatc_vae.py:165-205): all-gather z, mu, log_var; rank r sweeps its anchor rows against all columns; the four
+  batch means are all-reduced, log_q_z and the per-dimension LSE rows all-gathered for the backward's column sweep; the
+  gradient of the rank's own rows is complete locally.
+
 The batch-local ops (K1-K3, K7) need no collective at all: shard the batch, which is what DDP already does.
 The plumbing helpers are backend-agnostic (NCCL on GPUs; gloo in the CPU tests).
 """
@@ -164,6 +168,50 @@ def sharded_mmd(z_local, reg_weight, kernel_type, z_var, passes=3, group=None):
     if kernel_type not in F.KERNEL_TYPES:
         raise ValueError('Undefined kernel type.')
     return _ShardedMmd.apply(z_local, F.KERNEL_TYPES[kernel_type], float(z_var), float(reg_weight), int(passes), group)
+
+
+class _ShardedBetaTc(torch.autograd.Function):
+    """betatc_vae.py:165-205 (latent terms) on the GLOBAL batch: all-gather z, mu, log_var; rank r sweeps its anchor rows
+    against all B columns (vk_tc_fwd_rows); the four batch means are all-reduced; log_q_z / the per-dimension LSE rows are
+    all-gathered because the column sweep of the backward (g_mu, g_lv of the rank's own rows as PARTNERS) sums over every
+    anchor.  Every rank ends with the complete gradient of its own rows: no reduce-scatter."""
+
+    @staticmethod
+    def forward(ctx, z_local, mu_local, lv_local, M_N, alpha, beta, gamma_anneal, group):
+        from . import functional as F
+        world, rank = world_rank(group)
+        n = z_local.shape[0]
+        r0, r1 = rank * n, (rank + 1) * n
+        z_all, mu_all, lv_all = (gather_rows(t, group) for t in (z_local, mu_local, lv_local))
+        B = z_all.shape[0]
+        out, lqz, lse = F.betatc_rows_fwd(z_all, mu_all, lv_all, r0, r1, M_N, alpha, beta, gamma_anneal)
+        reduce_sum_(out, group)
+        lqz_all = gather_rows(lqz.view(2, B)[:, r0:r1].t().contiguous(), group).t().contiguous().view(2 * B)
+        lse_all = gather_rows(lse[r0:r1], group)
+        ctx.save_for_backward(z_all, mu_all, lv_all, lqz_all, lse_all)
+        ctx.cfg = (r0, r1, M_N, alpha, beta, gamma_anneal)
+        ctx.set_materialize_grads(False)
+        terms = out[1:].detach()
+        ctx.mark_non_differentiable(terms)
+        return out[0], terms
+
+    @staticmethod
+    def backward(ctx, g, _g_terms):
+        from . import functional as F
+        if g is None:
+            return (None,) * 8
+        z_all, mu_all, lv_all, lqz_all, lse_all = ctx.saved_tensors
+        r0, r1, M_N, alpha, beta, gamma_anneal = ctx.cfg
+        g_z, g_mu, g_lv = F.betatc_rows_bwd(z_all, mu_all, lv_all, lqz_all, lse_all, r0, r1, M_N, alpha, beta, gamma_anneal, g)
+        return g_z, g_mu, g_lv, None, None, None, None, None
+
+
+def sharded_betatc_terms(z_local, mu_local, log_var_local, M_N, alpha, beta, gamma_anneal, group=None):
+    """(alpha*mi + beta*tc + gamma_anneal*kld, terms[3] = {kld, tc, mi}) of the GLOBAL batch, identical on every rank;
+    backward gives the gradient w.r.t. the rank's own rows.  M_N refers to the global batch (dataset_size = B_global / M_N,
+    betatc_vae.py:176).  Every rank must contribute the same number of rows; latent dim <= 128."""
+    return _ShardedBetaTc.apply(z_local, mu_local, log_var_local, float(M_N), float(alpha), float(beta),
+                                float(gamma_anneal), group)
 
 
 class _ShardedSwd(torch.autograd.Function):

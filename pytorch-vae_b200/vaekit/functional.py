@@ -662,6 +662,38 @@ class _BetaTc(torch.autograd.Function):
         return g_z, g_mu, g_lv, None, None, None, None
 
 
+def betatc_rows_fwd(z_all, mu_all, lv_all, row_begin, row_end, M_N, alpha, beta, gamma_anneal):
+    """Forward row sweep of anchor rows [row_begin, row_end) against all B columns (vk_tc_fwd_rows).  Returns
+    (out[4] = the range's share of {latent loss, kld, tc, mi}, lqz [2B], lse [B, D]) with only the range's rows valid."""
+    for t, n in ((z_all, "z"), (mu_all, "mu"), (lv_all, "log_var")):
+        L.require(t, n, dims=(2,))
+    B, D = z_all.shape
+    dev = z_all.device
+    zc, mc, lc = z_all.contiguous(), mu_all.contiguous(), lv_all.contiguous()
+    lqz = torch.zeros(2 * B, dtype=torch.float32, device=dev)
+    lse = torch.zeros((B, D), dtype=torch.float32, device=dev)
+    out = torch.empty(4, dtype=torch.float32, device=dev)
+    ws = L.workspace(dev, int(L.lib().vk_tc_workspace_bytes(B, D)))
+    with torch.cuda.device(dev):
+        L.call("tc_fwd_rows", L.ptr(zc), L.ptr(mc), L.ptr(lc), B, D, int(row_begin), int(row_end), M_N, alpha, beta,
+               gamma_anneal, L.ptr(lqz), L.ptr(lse), L.ptr(out), L.ptr(ws), ws.numel(), L.stream_ptr())
+    return out, lqz, lse
+
+
+def betatc_rows_bwd(z_all, mu_all, lv_all, lqz_all, lse_all, row_begin, row_end, M_N, alpha, beta, gamma_anneal, g):
+    """Backward of the rows [row_begin, row_end): (g_z, g_mu, g_lv) [rows, D] (vk_tc_bwd_rows); lqz_all / lse_all must
+    hold every row's forward values."""
+    B, D = z_all.shape
+    dev = z_all.device
+    g_z, g_mu, g_lv = (torch.empty((B, D), dtype=torch.float32, device=dev) for _ in range(3))
+    ws = L.workspace(dev, int(L.lib().vk_tc_workspace_bytes(B, D)))
+    with torch.cuda.device(dev):
+        L.call("tc_bwd_rows", L.ptr(z_all), L.ptr(mu_all), L.ptr(lv_all), L.ptr(lqz_all), L.ptr(lse_all), B, D,
+               int(row_begin), int(row_end), M_N, alpha, beta, gamma_anneal, L.ptr(g.contiguous()), L.ptr(g_z), L.ptr(g_mu),
+               L.ptr(g_lv), L.ptr(ws), ws.numel(), L.stream_ptr())
+    return g_z[row_begin:row_end], g_mu[row_begin:row_end], g_lv[row_begin:row_end]
+
+
 def betatc_terms(z, mu, log_var, M_N, alpha, beta, gamma_anneal):
     """betatc_vae.py:165-205 without the reconstruction term: returns (alpha*mi + beta*tc + gamma_anneal*kld,
     terms[3] = {kld, tc, mi})."""

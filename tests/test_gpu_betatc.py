@@ -104,3 +104,33 @@ def test_betatc_model_contract(vk):
         m.loss_function(*out)                                   # M_N is required (betatc_vae.py:177)
     ld = m.log_density_gaussian(out[4], out[2], out[3])
     assert_close(ld, O.log_density_gaussian(out[4].cpu(), out[2].cpu(), out[3].cpu()), TOL)
+
+
+@pytest.mark.parametrize("B,D,cuts", [(256, 128, (0, 100, 256)), (130, 10, (0, 1, 64, 129, 130)), (96, 40, (0, 95, 96))])
+def test_betatc_row_shards_add_up(vk, B, D, cuts):
+    """Multi-GPU decomposition emulated on one GPU: anchor-row blocks swept separately (vk_tc_fwd_rows /
+    vk_tc_bwd_rows) give per-row outputs identical to the full sweep, shares of the batch means that add up, and row
+    blocks of the gradients equal to the full backward."""
+    F, _ = vk
+    gen = torch.Generator().manual_seed(B + D)
+    mu = torch.randn(B, D, generator=gen).to(DEV); lv = (0.3 * torch.randn(B, D, generator=gen)).to(DEV)
+    z = (mu + torch.exp(0.5 * lv) * torch.randn(B, D, generator=gen).to(DEV)).contiguous()
+    hp = (0.005, 1.0, 6.0, 0.7)
+    zf, mf, lf = leaf(z), leaf(mu), leaf(lv)
+    full, terms = F.betatc_terms(zf, mf, lf, *hp)
+    (full * 1.3).backward()
+    g = torch.tensor(1.3, device=DEV)
+    outs, lqz_all, lse_all = [], torch.zeros(2 * B, device=DEV), torch.zeros(B, D, device=DEV)
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        out, lqz, lse = F.betatc_rows_fwd(z, mu, lv, a, b, *hp)
+        outs.append(out)
+        lqz_all.view(2, B)[:, a:b] = lqz.view(2, B)[:, a:b]
+        lse_all[a:b] = lse[a:b]
+    tot = torch.stack(outs).double().sum(0)
+    assert_close(tot[0], full.detach().double(), 2e-6, "latent loss")
+    assert_close(tot[1:], terms.double(), 2e-6, "terms")
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        gz, gm, gl = F.betatc_rows_bwd(z, mu, lv, lqz_all, lse_all, a, b, *hp, g)
+        assert_close(gz, zf.grad[a:b], 1e-6, "g_z rows %d:%d" % (a, b))
+        assert_close(gm, mf.grad[a:b], 1e-6, "g_mu rows %d:%d" % (a, b))
+        assert_close(gl, lf.grad[a:b], 1e-6, "g_lv rows %d:%d" % (a, b))

@@ -48,6 +48,16 @@ def _worker(rank, world, port, out):
             mmd, terms = vd.sharded_mmd(z, 3.0, kt, 2.0)
             mmd.backward()
             res[kt] = (mmd.detach().cpu(), terms.cpu(), z.grad.cpu())
+        # Beta-TC latent terms, row-sharded
+        gtc = torch.Generator(device="cpu").manual_seed(700 + rank)
+        mu = torch.randn(N_LOCAL, D, generator=gtc).to(dev).requires_grad_(True)
+        lv = (0.3 * torch.randn(N_LOCAL, D, generator=gtc)).to(dev).requires_grad_(True)
+        eps = torch.randn(N_LOCAL, D, generator=gtc).to(dev)
+        ztc = mu + torch.exp(0.5 * lv) * eps
+        tc_loss, tc_terms = vd.sharded_betatc_terms(ztc, mu, lv, 0.005, 1.0, 6.0, 0.7)
+        (tc_loss * 1.3).backward()
+        res["tc"] = (tc_loss.detach().cpu(), tc_terms.cpu(), mu.grad.cpu(), lv.grad.cpu(),
+                     mu.detach().cpu(), lv.detach().cpu(), eps.cpu())
         proj = O.random_projections(D, S).to(dev) if rank == 0 else torch.zeros(S, D, device=dev)
         vd.shared_tensor_(proj)
         for key, exchange, waves in (("swd", "all_to_all", None), ("swd_w1", "all_to_all", 1), ("swd_w3", "all_to_all", 3),
@@ -103,6 +113,24 @@ def test_sharded_ops_match_single_gpu_and_oracle(tmp_path):
         scale = 3.0 * max(abs(t.item()) for t in ref_terms)       # the statistic is a difference of these sums
         assert abs(one.item() - ref.item()) <= 1e-5 * scale, kt
         assert ((g.double() - zo.grad).abs().max() / zo.grad.abs().max()).item() < 2e-5, kt
+
+    # Beta-TC: sharded == single-GPU kernels on the gathered batch (gradients flow into mu / log_var through z too)
+    mu = torch.cat([parts[r]["tc"][4] for r in range(world)]).to(dev).requires_grad_(True)
+    lv = torch.cat([parts[r]["tc"][5] for r in range(world)]).to(dev).requires_grad_(True)
+    eps = torch.cat([parts[r]["tc"][6] for r in range(world)]).to(dev)
+    one, terms = F.betatc_terms(mu + torch.exp(0.5 * lv) * eps, mu, lv, 0.005, 1.0, 6.0, 0.7)
+    (one * 1.3).backward()
+    for r in range(world):
+        assert abs(parts[r]["tc"][0].item() - one.item()) <= 2e-6 * abs(one.item()), r
+        assert torch.allclose(parts[r]["tc"][1], terms.cpu(), rtol=2e-6, atol=1e-7)
+    for k, ref in ((2, mu.grad), (3, lv.grad)):
+        g = torch.cat([parts[r]["tc"][k] for r in range(world)])
+        assert ((g - ref.cpu()).abs().max() / ref.abs().max().cpu()).item() < 2e-6, k
+    mo, lo = mu.detach().cpu().double().requires_grad_(True), lv.detach().cpu().double().requires_grad_(True)
+    zo = mo + torch.exp(0.5 * lo) * eps.cpu().double()
+    ref = O.betatc_loss(torch.zeros(N, 1, dtype=torch.float64), torch.zeros(N, 1, dtype=torch.float64), mo, lo, zo, 0.005,
+                        alpha=1.0, beta=6.0, gamma=1.0, anneal_rate=0.7)
+    assert abs(one.item() - ref["loss"].item()) <= 1e-5 * abs(ref["loss"].item())
 
     prior = shared_prior()
     proj = parts[0]["proj"].to(dev)
