@@ -525,7 +525,7 @@ class SwaeWorkload(OpWorkload):
         if world > 1:
             from vaekit import dist as vd
             proj = vd.shared_projections(m, self.D, self.S, z.device)
-            swd = vd.sharded_swd(z, proj, m.p, reg, exchange=os.environ.get("VAEKIT_SWD_EXCHANGE", "peer"))
+            swd = vd.sharded_swd(z, proj, m.p, reg, exchange=os.environ.get("VAEKIT_SWD_EXCHANGE", "auto"))
         else:
             swd = m.compute_swd(z, m.p, reg)
         swd.backward()
@@ -727,7 +727,7 @@ def run_op_gpu_arm(args, wl):
                            "l2_policy": "synthetic inputs regenerated never; working set (operand images / sort buffers) larger than L2 or tensor-bound",
                            "parallelism": ("%s over %d ranks" % ("row-sharded after all-gather" if isinstance(wl, (WaeMmd, BetaTcWorkload)) else
                                                                   "projection-sharded, exchange fused into the GEMMs over peer memory (%s)"
-                                                                  % os.environ.get("VAEKIT_SWD_EXCHANGE", "peer") if isinstance(wl, SwaeWorkload)
+                                                                  % os.environ.get("VAEKIT_SWD_EXCHANGE", "auto") if isinstance(wl, SwaeWorkload)
                                                                   else "batch-sharded", world)) if world > 1 else "single GPU",
                            "step": "forward + backward through the drop-in model API"},
                 "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,

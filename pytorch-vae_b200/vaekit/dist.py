@@ -466,12 +466,35 @@ class _ShardedSwdPeer(torch.autograd.Function):
         return F.scale_by_scalar(ctx.saved_tensors[0], g.contiguous(), ctx.factor), None, None, None, None
 
 
-def sharded_swd(z_local, proj, p, reg_weight, group=None, exchange="all_to_all", waves=None):
+_peer_ok = {}
+
+
+def _peer_available(group, z_local, S) -> bool:
+    """Can this process group map peer memory (torch symmetric memory over NVLink)?  Decided once per group by trying the
+    rendezvous; all ranks take the same branch because the rendezvous itself is collective."""
+    key = id(group) if group is not None else 0
+    if key not in _peer_ok:
+        ok = z_local.is_cuda and dist.get_backend(group) == "nccl"
+        if ok:
+            try:
+                _peer_segments(group, z_local.device, z_local.shape[0], S)
+            except Exception as e:                                   # no P2P mapping on this box: NCCL all-to-all instead
+                import warnings
+                warnings.warn("vaekit: peer-mapped memory unavailable (%s); the sharded SWD uses NCCL all-to-all" % (e,))
+                ok = False
+        _peer_ok[key] = ok
+    return _peer_ok[key]
+
+
+def sharded_swd(z_local, proj, p, reg_weight, group=None, exchange="auto", waves=None):
     """Sliced-Wasserstein distance of the GLOBAL batch; `proj` [S, D] must be identical on every rank
-    (use shared_tensor_ on the reference's CPU-generated directions).  exchange = "all_to_all" (projected values travel;
+    (use shared_projections / shared_tensor_ on the reference's CPU-generated directions).  exchange = "auto" (default:
+    "peer" where the group can map peer memory, else "all_to_all"), "all_to_all" (projected values travel through NCCL;
     every stage shrinks with the world size; `waves` pieces pipeline the exchange under the sorts), "peer" (the same
     decomposition with both exchanges fused into the GEMMs over peer-mapped memory, CUDA + NVLink only) or "all_gather" (z travels; each rank projects all rows on its slice of
     the projections and the [N, D] gradient is reduce-scattered -- kept for shapes the tcgen05 GEMM does not take)."""
+    if exchange == "auto":
+        exchange = "peer" if world_rank(group)[0] > 1 and _peer_available(group, z_local, proj.shape[0]) else "all_to_all"
     if exchange == "peer" and world_rank(group)[0] > 1:
         return _ShardedSwdPeer.apply(z_local, proj.contiguous(), float(p), float(reg_weight), group)
     if exchange in ("all_to_all", "peer"):
