@@ -320,7 +320,6 @@ def run_gpu_arm(args, wl):
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    L.EVENT_LOG = []
     launches0 = L.LAUNCHES
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
@@ -328,9 +327,15 @@ def run_gpu_arm(args, wl):
         d = hot_path_step(model, wl, t)
     e1.record()
     barrier()
-    log, L.EVENT_LOG = L.EVENT_LOG, None
     launches = L.LAUNCHES - launches0
     ms = e0.elapsed_time(e1)
+    # the same K steps again with CUDA events around every library call (launching stream): per-kernel durations for the
+    # roofline.  Kept out of the pass that gives `value`: two event records per call cost the host 20-60 us per call.
+    L.EVENT_LOG = []
+    for _ in range(args.steps):
+        hot_path_step(model, wl, t)
+    barrier()
+    log, L.EVENT_LOG = L.EVENT_LOG, None
     clocks = sampler.stop() if rank == 0 else None
     if world > 1:
         tms = torch.tensor([ms], device=dev)
@@ -385,7 +390,9 @@ def run_gpu_arm(args, wl):
             "config": {"workload": wl["desc"], "per_gpu_batch": B, "global_batch": B * world,
                        "l2_policy": "inputs (%.2f GB/step) larger than L2, no flush" % (alg / 1e9),
                        "parallelism": "batch-sharded, no data-path collective" if world > 1 else "single GPU",
-                       "step": "reparameterize + loss_function + backward through the drop-in model API"},
+                       "step": "reparameterize + loss_function + backward through the drop-in model API",
+                       "timing": "value: K steps between two CUDA events; roofline: the same K steps repeated with CUDA "
+                                 "events around every library call"},
             "step_GBps_algorithmic": round(alg / (ms / args.steps) / 1e6, 1),
             "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
             "loss": loss_val,
@@ -671,7 +678,10 @@ def run_op_gpu_arm(args, wl):
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    ms, log, launches, d = timed(lambda: wl.step(model, t, world), args.steps, True)
+    ms, _, launches, d = timed(lambda: wl.step(model, t, world), args.steps, False)
+    # the same K steps again with CUDA events around every library call (launching stream): per-call durations for the
+    # roofline.  Kept out of the pass that gives `value`: two event records per call cost the host 20-60 us per call.
+    _, log, _, _ = timed(lambda: wl.step(model, t, world), args.steps, True)
     clocks = sampler.stop() if rank == 0 else None
     value = wl.units(world) * args.steps / (ms / 1e3)
     # roofline of the dominant library call, from CUDA events around each call on the launching stream
@@ -729,7 +739,9 @@ def run_op_gpu_arm(args, wl):
                                                                   "projection-sharded, exchange fused into the GEMMs over peer memory (%s)"
                                                                   % os.environ.get("VAEKIT_SWD_EXCHANGE", "auto") if isinstance(wl, SwaeWorkload)
                                                                   else "batch-sharded", world)) if world > 1 else "single GPU",
-                           "step": "forward + backward through the drop-in model API"},
+                           "step": "forward + backward through the drop-in model API",
+                           "timing": "value: K steps between two CUDA events; roofline: the same K steps repeated with CUDA "
+                                     "events around every library call"},
                 "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
                 "loss": {k: v.item() for k, v in d.items()}}
         print(json.dumps(line), flush=True)

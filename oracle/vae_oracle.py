@@ -121,6 +121,37 @@ def vanilla_loss(recons: Tensor, input: Tensor, mu: Tensor, log_var: Tensor, M_N
     return {"loss": loss, "Reconstruction_Loss": recons_loss.detach(), "KLD": -kld_loss.detach()}
 
 
+def cvae_loss(recons: Tensor, input: Tensor, mu: Tensor, log_var: Tensor, M_N: float) -> Dict[str, Tensor]:
+    """cvae.py:131-146: the vanilla terms with neither side output detached."""
+    recons_loss = F.mse_loss(recons, input)
+    kld_loss = torch.mean(kld_rows(mu, log_var), dim=0)
+    return {"loss": recons_loss + M_N * kld_loss, "Reconstruction_Loss": recons_loss, "KLD": -kld_loss}
+
+
+def dip_loss(recons: Tensor, input: Tensor, mu: Tensor, log_var: Tensor, M_N: float, *, lambda_diag: float,
+             lambda_offdiag: float) -> Dict[str, Tensor]:
+    """dip_vae.py:124-164 (DIP-VAE II): summed reconstruction and KL terms plus the covariance regulariser."""
+    recons_loss = F.mse_loss(recons, input, reduction="sum")
+    kld_loss = torch.sum(kld_rows(mu, log_var), dim=0)
+    centered_mu = mu - mu.mean(dim=1, keepdim=True)
+    cov_mu = centered_mu.t().matmul(centered_mu).squeeze()
+    cov_z = cov_mu + torch.mean(torch.diagonal((2. * log_var).exp(), dim1=0), dim=0)
+    cov_diag = torch.diag(cov_z)
+    cov_offdiag = cov_z - torch.diag(cov_diag)
+    dip = lambda_offdiag * torch.sum(cov_offdiag ** 2) + lambda_diag * torch.sum((cov_diag - 1) ** 2)
+    return {"loss": recons_loss + M_N * kld_loss + dip, "Reconstruction_Loss": recons_loss, "KLD": -kld_loss, "DIP_Loss": dip}
+
+
+def factor_vae_loss(recons: Tensor, input: Tensor, mu: Tensor, log_var: Tensor, d_z: Tensor, M_N: float, *,
+                    gamma: float) -> Dict[str, Tensor]:
+    """fvae.py:165-181 (optimizer_idx == 0) with the discriminator's logits d_z [B, 2] given."""
+    recons_loss = F.mse_loss(recons, input)
+    kld_loss = torch.mean(kld_rows(mu, log_var), dim=0)
+    vae_tc_loss = (d_z[:, 0] - d_z[:, 1]).mean()
+    return {"loss": recons_loss + M_N * kld_loss + gamma * vae_tc_loss, "Reconstruction_Loss": recons_loss,
+            "KLD": -kld_loss, "VAE_TC_Loss": vae_tc_loss}
+
+
 def beta_loss(recons: Tensor, input: Tensor, mu: Tensor, log_var: Tensor, M_N: float, *,
               loss_type: str, beta: float, gamma: float, C_max: float, C_stop_iter: float,
               num_iter: int) -> Dict[str, Tensor]:

@@ -1,5 +1,6 @@
 """Model registry with the reference's keys (models/__init__.py:65-91) for the classes on the
-hot path (plus InfoVAE); the remaining reference variants are out of scope."""
+hot path, plus the SURVEY 8(f) "next" rows built so far: InfoVAE (rank 1) and the Gaussian-KL models ConditionalVAE, DIPVAE
+and FactorVAE (rank 2); the remaining reference variants are out of scope."""
 from .base import BaseVAE
 from .vanilla_vae import VanillaVAE
 from .beta_vae import BetaVAE
@@ -11,9 +12,13 @@ from .wae_mmd import WAE_MMD
 from .info_vae import InfoVAE
 from .swae import SWAE
 from .betatc_vae import BetaTCVAE
+from .cvae import ConditionalVAE
+from .dip_vae import DIPVAE
+from .fvae import FactorVAE
 
 VAE = VanillaVAE
 GaussianVAE = VanillaVAE
+CVAE = ConditionalVAE
 
 vae_models = {
     'IWAE': IWAE,
@@ -26,4 +31,7 @@ vae_models = {
     'InfoVAE': InfoVAE,
     'SWAE': SWAE,
     'BetaTCVAE': BetaTCVAE,
+    'ConditionalVAE': ConditionalVAE,
+    'DIPVAE': DIPVAE,
+    'FactorVAE': FactorVAE,
 }

@@ -1,16 +1,18 @@
 #!/bin/bash
-# r01o: ncu --set full captures of the dominant kernel of every op workload (one launch each), + the new VQ backward
-TAG=r01o
+# r01q: full GPU parity suite, smoke, bench lines of every workload (value pass uninstrumented), reference arm
+TAG=r01q
 mkdir -p gpurun_out
-cap() { # workload kernel-regex name skip
-  timeout 600 ncu --set full --clock-control none --import-source on -k "regex:$2" -s $4 -c 1 -f -o gpurun_out/ncu_$3_${TAG} \
-    python bench.py --workload $1 --steps 1 --warmup 3 --no-cpu --no-e2e > gpurun_out/ncu_$3.log 2>&1; tail -1 gpurun_out/ncu_$3.log
-}
-cap vq vq_fwd_kernel vq_fwd 2
-cap vq vq_bwd_kernel vq_bwd 2
-cap swae "scatter_kernel<1, true" swae_scatter_kv 1
-cap swae "scatter_kernel<1, false" swae_scatter_k 1
-cap swae "scatter_kernel<3, true" swae_scatter_fused 1
-cap wae_mmd_rbf mmd_main_kernel mmd_main 1
-cap betatc bwd_rows_kernel tc_bwd_rows 1
-ls -la gpurun_out/*.ncu-rep
+timeout 1200 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu_${TAG}.log 2>&1; tail -3 gpurun_out/pytest_gpu_${TAG}.log
+timeout 600 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -2
+python bench.py > gpurun_out/bench_iwae_${TAG}.json 2> gpurun_out/bench_iwae_${TAG}.err; cut -c1-300 gpurun_out/bench_iwae_${TAG}.json
+python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref_${TAG}.json 2>&1; cut -c1-200 gpurun_out/bench_ref_${TAG}.json
+for w in miwae vanilla; do python bench.py --workload $w --steps 20 > gpurun_out/bench_${w}_${TAG}.json 2> gpurun_out/bench_${w}_${TAG}.err; cut -c1-200 gpurun_out/bench_${w}_${TAG}.json; done
+for w in wae_mmd_rbf wae_mmd_imq vq swae betatc; do
+  python bench.py --workload $w --steps 20 --warmup 3 > gpurun_out/bench_${w}_${TAG}.json 2> gpurun_out/bench_${w}_${TAG}.err
+  tail -c 300 gpurun_out/bench_${w}_${TAG}.err
+  python - <<PY
+import json
+d=json.loads(open("gpurun_out/bench_${w}_${TAG}.json").read().strip().splitlines()[-1])
+print("${w}", d["ms_per_step"], d["value"], d["roofline"]["frac"], {k:round(v["ms"],4) for k,v in d["roofline"]["calls"].items()}, "e2e", d["e2e"]["value"], "cpu", d["cpu_baseline"]["value"])
+PY
+done

@@ -264,9 +264,46 @@ def gen_info():
              grad_recons=rl.grad, grad_mu=mul.grad, grad_log_var=lvl.grad)
 
 
+def gen_next_models():
+    """ConditionalVAE, DIPVAE, FactorVAE (VAE branch) loss functions of the unmodified reference."""
+    g = torch.Generator().manual_seed(77)
+    r, x = images(g, 6)
+    mu, lv = gaussians(g, 6, 16)
+    # ConditionalVAE
+    m = ref.ConditionalVAE(3, 10, 16)
+    rl, mul, lvl = leaf(r), leaf(mu), leaf(lv)
+    d = m.loss_function(rl, x, mul, lvl, M_N=0.005)
+    d["loss"].backward()
+    save("cvae", in_recons=r, in_input=x, in_mu=mu, in_log_var=lv, hp_M_N=0.005, out_loss=d["loss"],
+         out_Reconstruction_Loss=d["Reconstruction_Loss"], out_KLD=d["KLD"], grad_recons=rl.grad, grad_mu=mul.grad,
+         grad_log_var=lvl.grad)
+    # DIPVAE
+    m = ref.DIPVAE(3, 16, lambda_diag=10., lambda_offdiag=5.)
+    rl, mul, lvl = leaf(r), leaf(mu), leaf(lv)
+    d = m.loss_function(rl, x, mul, lvl, M_N=0.005)
+    d["loss"].backward()
+    save("dipvae", in_recons=r, in_input=x, in_mu=mu, in_log_var=lv, hp_M_N=0.005, out_loss=d["loss"],
+         out_Reconstruction_Loss=d["Reconstruction_Loss"], out_KLD=d["KLD"], out_DIP_Loss=d["DIP_Loss"],
+         grad_recons=rl.grad, grad_mu=mul.grad, grad_log_var=lvl.grad)
+    # FactorVAE, optimizer_idx = 0; the discriminator is replaced by a fixed linear map so the fixture stays small
+    m = ref.FactorVAE(3, 16, gamma=40.)
+    W = 0.3 * torch.randn(16, 2, generator=g)
+    lin = torch.nn.Linear(16, 2, bias=False)
+    with torch.no_grad():
+        lin.weight.copy_(W.t())
+    m.discriminator = lin
+    z = torch.randn(6, 16, generator=g)
+    rl, mul, lvl, zl = leaf(r), leaf(mu), leaf(lv), leaf(z)
+    d = m.loss_function(rl, x, mul, lvl, zl, M_N=0.005, optimizer_idx=0)
+    d["loss"].backward()
+    save("factorvae", in_recons=r, in_input=x, in_mu=mu, in_log_var=lv, in_z=z, in_W=W, hp_M_N=0.005, out_loss=d["loss"],
+         out_Reconstruction_Loss=d["Reconstruction_Loss"], out_KLD=d["KLD"], out_VAE_TC_Loss=d["VAE_TC_Loss"],
+         grad_recons=rl.grad, grad_mu=mul.grad, grad_log_var=lvl.grad, grad_z=zl.grad)
+
+
 if __name__ == "__main__":
     torch.set_num_threads(4)
     only = sys.argv[1:]
-    for fn in (gen_vanilla, gen_beta, gen_logcosh, gen_iw, gen_wae, gen_betatc, gen_swae, gen_vq, gen_info):
+    for fn in (gen_vanilla, gen_beta, gen_logcosh, gen_iw, gen_wae, gen_betatc, gen_swae, gen_vq, gen_info, gen_next_models):
         if not only or fn.__name__[4:] in only:
             fn()

@@ -206,3 +206,29 @@ def test_infovae(name, kt):
     assert_close(r.grad, g["grad_recons"], TOL)
     assert_close(mu.grad, g["grad_mu"], 2e-5)
     assert_close(lv.grad, g["grad_log_var"], 2e-5)
+
+
+def test_next_models():
+    """ConditionalVAE, DIPVAE, FactorVAE (VAE branch)."""
+    g = load("cvae")
+    r, mu, lv = leaf(g["in_recons"]), leaf(g["in_mu"]), leaf(g["in_log_var"])
+    d = O.cvae_loss(r, g["in_input"], mu, lv, g["hp_M_N"])
+    d["loss"].backward()
+    for k in ("loss", "Reconstruction_Loss", "KLD"):
+        assert_close(d[k], g["out_" + k], TOL, k)
+    assert d["KLD"].requires_grad and d["Reconstruction_Loss"].requires_grad
+    assert_close(r.grad, g["grad_recons"], TOL); assert_close(mu.grad, g["grad_mu"], TOL); assert_close(lv.grad, g["grad_log_var"], TOL)
+    g = load("dipvae")
+    r, mu, lv = leaf(g["in_recons"]), leaf(g["in_mu"]), leaf(g["in_log_var"])
+    d = O.dip_loss(r, g["in_input"], mu, lv, g["hp_M_N"], lambda_diag=10., lambda_offdiag=5.)
+    d["loss"].backward()
+    for k in ("loss", "Reconstruction_Loss", "KLD", "DIP_Loss"):
+        assert_close(d[k], g["out_" + k], TOL, k)
+    assert_close(r.grad, g["grad_recons"], TOL); assert_close(mu.grad, g["grad_mu"], TOL); assert_close(lv.grad, g["grad_log_var"], TOL)
+    g = load("factorvae")
+    r, mu, lv, z = leaf(g["in_recons"]), leaf(g["in_mu"]), leaf(g["in_log_var"]), leaf(g["in_z"])
+    d = O.factor_vae_loss(r, g["in_input"], mu, lv, z @ g["in_W"], g["hp_M_N"], gamma=40.)
+    d["loss"].backward()
+    for k in ("loss", "Reconstruction_Loss", "KLD", "VAE_TC_Loss"):
+        assert_close(d[k], g["out_" + k], TOL, k)
+    assert_close(z.grad, g["grad_z"], TOL); assert_close(mu.grad, g["grad_mu"], TOL)
