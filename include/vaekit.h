@@ -122,6 +122,11 @@ int vk_elbo_bwd(const float* recons, const float* input, int64_t numel, int64_t 
                 const float* g_kld, const float* g_negkld,
                 float* g_recons, float* g_kl_rows, void* stream);
 
+/* Per-image reconstruction error for the trainer (reference: experiment.py:58-62 recomputes
+ * F.mse_loss(recons, input, reduction='none').mean(dim=[1,2,3]) and reads it back image by image):
+ * out[b] = mean over the P = C*H*W elements of image b of (recons - input)^2, one streaming pass. */
+int vk_per_image_mse(const float* recons, const float* input, int64_t B, int64_t P, float* out, void* stream);
+
 /* ---------------------------------------------------------------------------
  * K3  IWAE / MIWAE importance-weighted bound   (reference: iwae.py:129-160,
  *     miwae.py:132-164; closed-form backward: SURVEY.md A.2)

@@ -245,3 +245,46 @@ extern "C" int vk_elbo_bwd(const float* recons, const float* input, int64_t nume
   }
   return check_launch("elbo_bwd");
 }
+
+// ---- per-image MSE (the trainer's difficulty-sampling side output) ------------------------------------------------
+// experiment.py:58-62 recomputes F.mse_loss(recons, input, reduction='none').mean(dim=[1,2,3]) after the loss: a
+// [B,C,H,W] temporary, a reduction and one .item() per image.  Here: one streaming pass, one CTA per image (grid-stride
+// over images), fp32 sums per thread combined in double, out[b] = mean over the image's P pixels.
+namespace vk {
+namespace {
+__global__ void __launch_bounds__(256)
+per_image_mse_kernel(const float* __restrict__ recons, const float* __restrict__ input, int64_t B, int64_t P,
+                     float* __restrict__ out) {
+  __shared__ double red[8];
+  for (int64_t b = blockIdx.x; b < B; b += gridDim.x) {
+    const float* r = recons + b * P;
+    const float* x = input + b * P;
+    float s = 0.f;
+    const bool vec = (P & 3) == 0 && ((reinterpret_cast<uintptr_t>(r) | reinterpret_cast<uintptr_t>(x)) & 15) == 0;
+    if (vec) {
+      const float4* r4 = reinterpret_cast<const float4*>(r);
+      const float4* x4 = reinterpret_cast<const float4*>(x);
+      for (int64_t i = threadIdx.x; i < P / 4; i += blockDim.x) {
+        const float4 a = ldg_stream(r4 + i), c = ldg_stream(x4 + i);
+        const float d0 = a.x - c.x, d1 = a.y - c.y, d2 = a.z - c.z, d3 = a.w - c.w;
+        s += d0 * d0 + d1 * d1 + d2 * d2 + d3 * d3;
+      }
+    } else {
+      for (int64_t i = threadIdx.x; i < P; i += blockDim.x) { const float d = r[i] - x[i]; s += d * d; }
+    }
+    double v[1] = {(double)s};
+    block_sum<1>(v, red);
+    if (threadIdx.x == 0) out[b] = (float)(v[0] / (double)P);
+    __syncthreads();
+  }
+}
+}  // namespace
+}  // namespace vk
+
+extern "C" int vk_per_image_mse(const float* recons, const float* input, int64_t B, int64_t P, float* out, void* stream) {
+  VK_REQUIRE(recons && input && out, VK_ERR_BAD_ARG, "per_image_mse: null pointer");
+  VK_REQUIRE(B >= 1 && P >= 1, VK_ERR_BAD_ARG, "per_image_mse: empty shape B=%lld P=%lld", (long long)B, (long long)P);
+  const int64_t cap = (int64_t)sm_count() * 8;
+  per_image_mse_kernel<<<(unsigned)(B < cap ? B : cap), 256, 0, (cudaStream_t)stream>>>(recons, input, B, P, out);
+  return check_launch("per_image_mse");
+}

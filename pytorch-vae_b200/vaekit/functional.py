@@ -170,6 +170,34 @@ def elbo(recons, input, kl=None, *, recon_mode=RECON_MSE_MEAN, alpha=1.0, combin
     return _Elbo.apply(recons, input, kl, int(recon_mode), float(alpha), int(combine_mode), float(w), float(C))
 
 
+def per_image_mse(recons, input):
+    """[B] mean squared error of every image (experiment.py:58-62: mse_loss(reduction='none').mean(dim=[1,2,3])), one
+    streaming pass (vk_per_image_mse).  Not differentiable: it is the trainer's bookkeeping value."""
+    L.require(recons, "recons"); L.require(input, "input")
+    if recons.shape != input.shape or recons.dim() < 2:
+        raise RuntimeError("vaekit: recons %s and input %s must be equal-shaped batches" % (tuple(recons.shape), tuple(input.shape)))
+    r, x = recons.detach().contiguous(), input.detach().contiguous()
+    B = r.shape[0]
+    out = torch.empty(B, dtype=torch.float32, device=r.device)
+    if r.numel() == 0:
+        return out
+    with torch.cuda.device(r.device):
+        L.call("per_image_mse", L.ptr(r), L.ptr(x), B, r.numel() // B, L.ptr(out), L.stream_ptr())
+    return out
+
+
+def step_report(loss_dict, per_image=None):
+    """Everything the trainer reads back after a step in ONE device-to-host copy: the reference's
+    training_step does len(dict) + B separate .item() synchronisations (experiment.py:55, 64-66).  Returns
+    ({key: float}, per-image list or None)."""
+    keys = list(loss_dict)
+    parts = [loss_dict[k].detach().reshape(-1)[:1].float() for k in keys]
+    if per_image is not None:
+        parts.append(per_image.detach().reshape(-1).float())
+    flat = torch.cat(parts).tolist()                         # the step's single synchronisation
+    return dict(zip(keys, flat[:len(keys)])), (flat[len(keys):] if per_image is not None else None)
+
+
 # ---------------------------------------------------------------------------
 # K3
 # ---------------------------------------------------------------------------

@@ -1,9 +1,10 @@
 #!/bin/bash
-TAG=${1:-r01n}
+TAG=${1:-r01r}
 mkdir -p gpurun_out
+timeout 300 python -m pytest tests/test_gpu_next_models.py -x -q 2>&1 | tail -3
 run() { # workload n
   timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $2 --master-addr 127.0.0.1 --master-port $((29500 + $2)) \
-    bench.py --workload $1 --gpus $2 --steps 10 --warmup 3 --no-cpu --no-e2e > gpurun_out/scale_$1_${TAG}_n$2.json 2> gpurun_out/scale_$1_${TAG}_n$2.err
+    bench.py --workload $1 --gpus $2 --steps 20 --warmup 3 --no-cpu --no-e2e > gpurun_out/scale_$1_${TAG}_n$2.json 2> gpurun_out/scale_$1_${TAG}_n$2.err
   python - <<PY
 import json
 try:
@@ -15,6 +16,9 @@ PY
 }
 run swae 8
 run swae 4
+run swae 2
+run betatc 8
+run betatc 2
 run wae_mmd_rbf 8
-timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29520 scripts/prof_swd_dist.py 1 peer 2>&1 | grep -v "^\*\|OMP_NUM\|^$\|warn\|Warn" | head -24 | tee gpurun_out/prof_swd_dist_n8_peer.log
-VAEKIT_SWD_EXCHANGE=all_to_all run swae 8 2>&1 | sed 's/^/a2a: /'
+run wae_mmd_rbf 4
+run wae_mmd_imq 8

@@ -84,3 +84,22 @@ def test_factorvae(models):
     d1 = m2.loss_function(*out, M_N=0.005, optimizer_idx=1)
     assert set(d1) == {"loss", "D_TC_Loss"}
     d1["loss"].backward()
+
+
+@pytest.mark.parametrize("shape", [(6, 3, 16, 16), (5, 3, 7, 9), (300, 3, 64, 64), (1, 1, 1, 1)])
+def test_per_image_mse_and_step_report(models, shape):
+    """the trainer's per-image MSE (experiment.py:58-62) as one streaming kernel and the whole step
+    read-back (loss dict + per-image values) as one device-to-host copy."""
+    from vaekit import functional as F
+    gen = torch.Generator().manual_seed(sum(shape))
+    r = torch.tanh(torch.randn(*shape, generator=gen)).to(DEV); x = torch.rand(*shape, generator=gen).to(DEV)
+    got = F.per_image_mse(r, x)
+    ref = torch.nn.functional.mse_loss(r.double(), x.double(), reduction="none").mean(dim=[1, 2, 3])
+    assert got.shape == (shape[0],)
+    assert_close(got, ref, 2e-6, "per-image mse")
+    d = {"loss": torch.tensor([1.5], device=DEV), "KLD": torch.tensor(-2.25, device=DEV)}       # Beta-B style [1] loss
+    vals, per = F.step_report(d, got)
+    assert vals == {"loss": 1.5, "KLD": -2.25} and len(per) == shape[0]
+    assert abs(per[0] - ref[0].item()) <= 2e-6 * abs(ref[0].item()) + 1e-12
+    vals, per = F.step_report(d)
+    assert per is None and vals["KLD"] == -2.25

@@ -74,3 +74,13 @@ def test_registry_and_constructor_contracts(built):
     assert (m.alpha, m.beta, m.reg_weight, m.kernel_type, m.z_var) == (-9.0, 10.5, 110, "imq", 2.0)
     with pytest.raises(AssertionError, match="alpha must be negative or zero"):
         vae_models["InfoVAE"](3, 16, alpha=0.5)          # info_vae.py:27
+
+
+def test_step_report_packs_one_copy(built):
+    """SURVEY 8(f) rank 3 host logic: loss dict (+ per-image values) -> Python floats through one concatenated tensor."""
+    from vaekit import functional as F
+    d = {"loss": torch.tensor([0.5]), "Reconstruction_Loss": torch.tensor(0.25), "KLD": torch.tensor(-1.0)}
+    vals, per = F.step_report(d, torch.tensor([1.0, 2.0, 3.0]))
+    assert vals == {"loss": 0.5, "Reconstruction_Loss": 0.25, "KLD": -1.0} and per == [1.0, 2.0, 3.0]
+    with pytest.raises(RuntimeError, match="CUDA"):
+        F.per_image_mse(torch.zeros(2, 3, 4, 4), torch.zeros(2, 3, 4, 4))
