@@ -13,6 +13,7 @@
 //                  row terms log q(z|x), log p(z); deterministic two-stage reduction -> {mi, tc, kld, weighted sum}
 //   tc_bwd<ROWS>   anchor row i  -> d/dz_i ;  tc_bwd<COLS> anchor column j -> d/dmu_j, d/dlog_var_j
 //                  (softmax weights p_ij, r_ijd recomputed from the saved log_q_z[i] and LSE_j[i,d])
+#include <stdlib.h>
 #include "common.cuh"
 
 namespace vk {
@@ -324,7 +325,8 @@ using namespace vk;
 extern "C" int64_t vk_tc_workspace_bytes(int64_t B, int64_t D) {
   if (B < 2 || D < 1) return -1;
   const int64_t blocks = (B + kW - 1) / kW;
-  return (int64_t)kWsHeader + blocks * 4 * 8 + 256 + 2 * B * D * 4 + 256 + B * 8;
+  // header | per-CTA partials | H, C0 [B, D] | Cb [B] doubles | partner-split partial sums of the backward (3 x [B, D])
+  return (int64_t)kWsHeader + blocks * 4 * 8 + 256 + 2 * B * D * 4 + 256 + B * 8 + 256 + 3 * B * D * 4 + 256 + 16 * B;
 }
 
 static int tc_fwd_impl(const float* z, const float* mu, const float* log_var, int64_t B, int64_t D, int64_t row_begin,
@@ -362,7 +364,19 @@ static int tc_fwd_impl(const float* z, const float* mu, const float* log_var, in
     auto kern = cfg == 0 ? tiled::fwd_kernel<1, 1> : (cfg == 1 ? tiled::fwd_kernel<2, 1> : tiled::fwd_kernel<4, 1>);
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm) != cudaSuccess)
       return check_launch("tc_fwd (shared memory attribute)");
-    kern<<<tb, tiled::kThreads, tsm, st>>>(z, mu, log_var, H, C0, Cb, p, lqz_out, lse_out, partials, (unsigned int*)ws, out);
+    // row block of a multi-GPU shard: split the partner range over gridDim.y (see tc_bwd_impl) and merge the LSE states
+    const int64_t rows = p.r1 - p.r0;
+    int nsplit = rows == B ? 1 : (int)(B / rows < 8 ? B / rows : 8);
+    if (nsplit < 1 || getenv("VAEKIT_TC_NO_FWD_SPLIT")) nsplit = 1;
+    double2* part_r = (double2*)(((uintptr_t)(Cb + B) + 255) & ~(uintptr_t)255);
+    float2* part_ms = (float2*)(((uintptr_t)(part_r + (size_t)nsplit * rows) + 255) & ~(uintptr_t)255);
+    kern<<<dim3(tb, nsplit), tiled::kThreads, tsm, st>>>(z, mu, log_var, H, C0, Cb, p, lqz_out, lse_out, partials,
+                                                          (unsigned int*)ws, out, part_ms, part_r);
+    if (nsplit > 1) {
+      const unsigned mb = (unsigned)((rows + 7) / 8 < blocks ? (rows + 7) / 8 : blocks);      // <= blocks: partials fit
+      tiled::fwd_merge_kernel<<<mb, 256, 0, st>>>(z, mu, log_var, p, nsplit, part_ms, part_r, lqz_out, lse_out, partials,
+                                                  (unsigned int*)ws, out);
+    }
     return check_launch("tc_fwd");
   }
   tc_prep_kernel<<<prep_blocks, 256, 0, st>>>(log_var, B * D, H, C0);
@@ -421,8 +435,21 @@ static int tc_bwd_impl(const float* z, const float* mu, const float* log_var, co
     if (cudaFuncSetAttribute(kr, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm) != cudaSuccess ||
         cudaFuncSetAttribute(kc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm) != cudaSuccess)
       return check_launch("tc_bwd (shared memory attribute)");
-    kr<<<tb, tiled::kThreads, tsm, st>>>(z, mu, log_var, H, C0, Cb, lqz, lse, p, g_loss, g_z);
-    kc<<<tb, tiled::kThreads, tsm, st>>>(z, mu, log_var, H, C0, Cb, lqz, lse, p, g_loss, g_mu, g_lv);
+    // A row block of a multi-GPU shard has too few anchor groups to fill the GPU (every CTA sweeps all B partners, so
+    // fewer CTAs are not faster): split the partner range over gridDim.y and merge in a fixed order.
+    const int64_t rows = p.r1 - p.r0;
+    int nsplit = rows == B ? 1 : (int)(B / rows < 8 ? B / rows : 8);
+    if (nsplit < 1) nsplit = 1;
+    float* part = (float*)(((uintptr_t)(Cb + B) + 255) & ~(uintptr_t)255);
+    float* part_mu = part + (size_t)nsplit * rows * D;
+    float* part_lv = part_mu + (size_t)nsplit * rows * D;
+    kr<<<dim3(tb, nsplit), tiled::kThreads, tsm, st>>>(z, mu, log_var, H, C0, Cb, lqz, lse, p, g_loss, g_z, part);
+    kc<<<dim3(tb, nsplit), tiled::kThreads, tsm, st>>>(z, mu, log_var, H, C0, Cb, lqz, lse, p, g_loss, g_mu, g_lv, part_mu, part_lv);
+    if (nsplit > 1) {
+      const int64_t n = rows * D;
+      tiled::bwd_merge_kernel<<<(unsigned)((n + 255) / 256 < 1184 ? (n + 255) / 256 : 1184), 256, 0, st>>>(
+          z, mu, log_var, p, g_loss, nsplit, part, part_mu, part_lv, g_z, g_mu, g_lv);
+    }
     return check_launch("tc_bwd");
   }
   tc_prep_kernel<<<prep_blocks, 256, 0, st>>>(log_var, B * D, H, C0);

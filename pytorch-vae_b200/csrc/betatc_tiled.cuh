@@ -128,7 +128,9 @@ __global__ void __launch_bounds__(kThreads, VK_TC_MINB)
 fwd_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const float* __restrict__ LV,
            const float* __restrict__ Hs, const float* __restrict__ Cs, const double* __restrict__ Cb, TcParams p,
            float* __restrict__ lqz_out, float* __restrict__ lse_out, double* __restrict__ partials, unsigned int* ticket,
-           float* __restrict__ out) {
+           float* __restrict__ out, float2* __restrict__ part_ms, double2* __restrict__ part_r) {
+  // gridDim.y > 1 (row block of a multi-GPU shard): partner tiles split over blockIdx.y; every split leaves its online
+  // logsumexp states (max, sum) in part_ms[y][row - r0][d] / part_r[y][row - r0] and fwd_merge_kernel finishes.
   constexpr int DP = 32 * KD * NS;                   // staged tile width: NS warps share an anchor group, KD dims per lane each
   extern __shared__ __align__(16) float sm[];
   __shared__ float xch_s[2 * (kTW / 2) * 2 * 16];
@@ -165,13 +167,14 @@ fwd_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const floa
     }
     cp_async_commit();
   };
-  const int ntiles = (p.B + kTR - 1) / kTR;
-  issue(0, 0);
-  for (int tile = 0; tile < ntiles; ++tile) {
+  const int ntiles_all = (p.B + kTR - 1) / kTR;
+  const int tile0 = (int)((long long)ntiles_all * blockIdx.y / gridDim.y), ntiles = (int)((long long)ntiles_all * (blockIdx.y + 1) / gridDim.y);
+  if (tile0 < ntiles) issue(tile0, 0);
+  for (int tile = tile0; tile < ntiles; ++tile) {
     const int j0 = tile * kTR;
-    if (tile + 1 < ntiles) { issue(tile + 1, (tile + 1) & 1); cp_async_wait<1>(); } else cp_async_wait<0>();
+    if (tile + 1 < ntiles) { issue(tile + 1, (tile + 1 - tile0) & 1); cp_async_wait<1>(); } else cp_async_wait<0>();
     __syncthreads();
-    const float* base = sm + (tile & 1) * kBuf;
+    const float* base = sm + ((tile - tile0) & 1) * kBuf;
     const double* Tb = reinterpret_cast<const double*>(base);   // [kTR] Cb of the staged partners (-inf for dead rows)
     const float* Tm = base + 2 * kTR;
     const float* Th = Tm + kTR * DP;
@@ -244,6 +247,24 @@ fwd_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const floa
     rs = rs * ex2f((float)(rm - mn)) + os * ex2f((float)(om - mn));
     rm = mn;
   }
+  if (gridDim.y > 1) {
+    const size_t rows = (size_t)(p.r1 - p.r0);
+#pragma unroll
+    for (int r = 0; r < kR; ++r) {
+      const int i = i0 + r;
+      const double rmr = __shfl_sync(0xFFFFFFFFu, rm, 2 * kP * r);
+      const float rsr = __shfl_sync(0xFFFFFFFFu, rs, 2 * kP * r);
+      if (i >= p.r1) continue;
+      const size_t ro = (size_t)blockIdx.y * rows + (size_t)(i - p.r0);
+      if (dbase == 0 && lane == 0) part_r[ro] = make_double2(rmr, (double)rsr);
+#pragma unroll
+      for (int k = 0; k < KD; ++k) {
+        const int d = dbase + lane + 32 * k;
+        if (d < p.D) part_ms[ro * p.D + d] = make_float2(m[r][k], s[r][k]);
+      }
+    }
+    return;
+  }
   // log q(z_i), i = i0 + (lane >> (kPSh + 1)), as an fp32 value plus its fp32 residual (the backward sweeps use both)
   const double lqz_d = (rm + (double)log2f(rs)) * 0.6931471805599453;
   const float lqz_mine = (float)lqz_d, lqz_res = (float)(lqz_d - (double)lqz_mine);
@@ -311,7 +332,9 @@ __global__ void __launch_bounds__(kThreads, VK_TC_MINB)
 bwd_rows_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const float* __restrict__ LV,
                 const float* __restrict__ Hs, const float* __restrict__ Cs, const double* __restrict__ Cb,
                 const float* __restrict__ lqz, const float* __restrict__ lse, TcParams p, const float* __restrict__ g_loss,
-                float* __restrict__ g_z) {
+                float* __restrict__ g_z, float* __restrict__ part) {
+  // gridDim.y > 1: partner tiles are split over blockIdx.y (a row block of a multi-GPU shard has too few anchor groups
+  // to fill the GPU); each split writes its raw sweep sums to part[y][row - r0][d] and bwd_merge_kernel finishes.
   constexpr int DP = 32 * KD * NS;                   // staged tile width: NS warps share an anchor group, KD dims per lane each
   extern __shared__ __align__(16) float sm[];
   __shared__ float xch_s[2 * (kTW / 2) * 2 * 16];
@@ -353,13 +376,14 @@ bwd_rows_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
     }
     cp_async_commit();
   };
-  const int ntiles = (p.B + kTR - 1) / kTR;
-  issue(0, 0);
-  for (int tile = 0; tile < ntiles; ++tile) {
+  const int ntiles_all = (p.B + kTR - 1) / kTR;
+  const int tile0 = (int)((long long)ntiles_all * blockIdx.y / gridDim.y), ntiles = (int)((long long)ntiles_all * (blockIdx.y + 1) / gridDim.y);
+  if (tile0 < ntiles) issue(tile0, 0);
+  for (int tile = tile0; tile < ntiles; ++tile) {
     const int j0 = tile * kTR;
-    if (tile + 1 < ntiles) { issue(tile + 1, (tile + 1) & 1); cp_async_wait<1>(); } else cp_async_wait<0>();
+    if (tile + 1 < ntiles) { issue(tile + 1, (tile + 1 - tile0) & 1); cp_async_wait<1>(); } else cp_async_wait<0>();
     __syncthreads();
-    const float* base = sm + (tile & 1) * kBuf;
+    const float* base = sm + ((tile - tile0) & 1) * kBuf;
     const double* Tb = reinterpret_cast<const double*>(base);
     const float* Tm = base + 2 * kTR;
     const float* Th = Tm + kTR * DP;
@@ -425,6 +449,10 @@ bwd_rows_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
 #pragma unroll
     for (int k = 0; k < KD; ++k) {
       const int i = i0 + r, d = dbase + lane + 32 * k;
+      if (gridDim.y > 1) {
+        if (i < p.r1 && d < p.D) part[((size_t)blockIdx.y * (p.r1 - p.r0) + (i - p.r0)) * p.D + d] = gz[r][k];
+        continue;
+      }
       if (i < p.r1 && d < p.D) {
         const size_t o = (size_t)i * p.D + d;
         const float df = z[r][k] - MU[o];
@@ -443,7 +471,7 @@ __global__ void __launch_bounds__(kThreads, VK_TC_MINB)
 bwd_cols_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const float* __restrict__ LV,
                 const float* __restrict__ Hs, const float* __restrict__ Cs, const double* __restrict__ Cb,
                 const float* __restrict__ lqz, const float* __restrict__ lse, TcParams p, const float* __restrict__ g_loss,
-                float* __restrict__ g_mu, float* __restrict__ g_lv) {
+                float* __restrict__ g_mu, float* __restrict__ g_lv, float* __restrict__ part_mu, float* __restrict__ part_lv) {
   constexpr int DP = 32 * KD * NS;                   // staged tile width: NS warps share an anchor group, KD dims per lane each
   extern __shared__ __align__(16) float sm[];
   __shared__ float xch_s[2 * (kTW / 2) * 2 * 16];
@@ -485,13 +513,14 @@ bwd_cols_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
     }
     cp_async_commit();
   };
-  const int ntiles = (p.B + kTR - 1) / kTR;
-  issue(0, 0);
-  for (int tile = 0; tile < ntiles; ++tile) {
+  const int ntiles_all = (p.B + kTR - 1) / kTR;
+  const int tile0 = (int)((long long)ntiles_all * blockIdx.y / gridDim.y), ntiles = (int)((long long)ntiles_all * (blockIdx.y + 1) / gridDim.y);
+  if (tile0 < ntiles) issue(tile0, 0);
+  for (int tile = tile0; tile < ntiles; ++tile) {
     const int i0 = tile * kTR;
-    if (tile + 1 < ntiles) { issue(tile + 1, (tile + 1) & 1); cp_async_wait<1>(); } else cp_async_wait<0>();
+    if (tile + 1 < ntiles) { issue(tile + 1, (tile + 1 - tile0) & 1); cp_async_wait<1>(); } else cp_async_wait<0>();
     __syncthreads();
-    const float* base = sm + (tile & 1) * kBuf;
+    const float* base = sm + ((tile - tile0) & 1) * kBuf;
     const float* Tq = base;                          // partner rows i: log q(z_i) value [kTR] | residual [kTR]
     const float* Tz = base + 2 * kTR;                // z
     const float* Tl = Tz + kTR * DP;                 // LSE_j[i, d] (natural log units)
@@ -556,6 +585,14 @@ bwd_cols_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
 #pragma unroll
     for (int k = 0; k < KD; ++k) {
       const int j = c0 + r, d = dbase + lane + 32 * k;
+      if (gridDim.y > 1) {
+        if (j < p.r1 && d < p.D) {
+          const size_t po = ((size_t)blockIdx.y * (p.r1 - p.r0) + (j - p.r0)) * p.D + d;
+          part_mu[po] = g0[r][k];
+          part_lv[po] = g1[r][k];
+        }
+        continue;
+      }
       if (j < p.r1 && d < p.D) {
         const size_t o = (size_t)j * p.D + d;
         const float df = Z[o] - mu[r][k];
@@ -564,6 +601,97 @@ bwd_cols_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
         g_lv[o] = g1[r][k] + ca * (0.5f * h2 * df * df - 0.5f);
       }
     }
+}
+
+// Finishes a partner-split forward: merges the splits' online-logsumexp states in a fixed order, then does what the
+// epilogue of fwd_kernel does (per-dimension LSE rows, log q(z_i) with its residual, the four batch sums).  One warp per
+// anchor row, lanes over latent dims.
+__global__ void __launch_bounds__(256)
+fwd_merge_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const float* __restrict__ LV, TcParams p,
+                 int nsplit, const float2* __restrict__ part_ms, const double2* __restrict__ part_r,
+                 float* __restrict__ lqz_out, float* __restrict__ lse_out, double* __restrict__ partials,
+                 unsigned int* ticket, float* __restrict__ out) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const size_t rows = (size_t)(p.r1 - p.r0);
+  double t_qzx = 0.0, t_qz = 0.0, t_pq = 0.0, t_pz = 0.0;
+  for (size_t row = (size_t)blockIdx.x * 8 + w; row < rows; row += (size_t)gridDim.x * 8) {
+    const size_t i = (size_t)p.r0 + row;
+    float lpq = 0.f, lqzx = 0.f, lpz = 0.f;
+    for (int d = lane; d < p.D; d += 32) {
+      float mn = -1e30f;
+      for (int y = 0; y < nsplit; ++y) mn = fmaxf(mn, part_ms[((size_t)y * rows + row) * p.D + d].x);
+      float sum = 0.f;
+      for (int y = 0; y < nsplit; ++y) {
+        const float2 ms = part_ms[((size_t)y * rows + row) * p.D + d];
+        sum = fmaf(ms.y, ex2f(ms.x - mn), sum);
+      }
+      const size_t o = i * p.D + d;
+      const float l = (mn + log2f(sum)) * kLn2;
+      lse_out[o] = l;
+      lpq += l;
+      const float v = LV[o], zz = Z[o], df = zz - MU[o];
+      lqzx += fmaf(-df * df, 0.5f * expf(-v), -0.5f * (kLog2Pi + v));
+      lpz += -0.5f * kLog2Pi - 0.5f * zz * zz;
+    }
+    lpq = warp_sum(lpq); lqzx = warp_sum(lqzx); lpz = warp_sum(lpz);
+    double rm = -1e300;
+    for (int y = 0; y < nsplit; ++y) rm = fmax(rm, part_r[(size_t)y * rows + row].x);
+    float rs = 0.f;
+    for (int y = 0; y < nsplit; ++y) {
+      const double2 r2 = part_r[(size_t)y * rows + row];
+      rs = fmaf((float)r2.y, ex2f((float)(r2.x - rm)), rs);
+    }
+    const double lqz_d = (rm + (double)log2f(rs)) * 0.6931471805599453;
+    const float lqz = (float)lqz_d, lqr = (float)(lqz_d - (double)lqz);
+    if (lane == 0) { lqz_out[i] = lqz; lqz_out[p.B + i] = lqr; }
+    t_qz += lqz; t_qzx += lqzx; t_pq += lpq; t_pz += lpz;
+  }
+  __shared__ double red[8 * 4];
+  if (lane == 0) { red[w * 4 + 0] = t_qzx; red[w * 4 + 1] = t_qz; red[w * 4 + 2] = t_pq; red[w * 4 + 3] = t_pz; }
+  __syncthreads();
+  if (threadIdx.x < 4) {
+    double t = 0.0;
+    for (int k = 0; k < 8; ++k) t += red[k * 4 + threadIdx.x];
+    partials[(size_t)blockIdx.x * 4 + threadIdx.x] = t;
+  }
+  if (last_block_ticket(ticket, gridDim.x)) {
+    if (threadIdx.x < 4) {
+      double t = 0.0;
+      for (unsigned int b = 0; b < gridDim.x; ++b) t += ((volatile double*)partials)[(size_t)b * 4 + threadIdx.x];
+      red[threadIdx.x] = t / (double)p.B;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const float qzx = (float)red[0], qz = (float)red[1], pq = (float)red[2], pz = (float)red[3];
+      const float mi = qzx - qz, tc = qz - pq, kld = pq - pz;                 // betatc_vae.py:190-192 (means)
+      out[0] = p.alpha * mi + (p.beta * tc + p.gamma_anneal * kld);
+      out[1] = kld;
+      out[2] = tc;
+      out[3] = mi;
+    }
+  }
+}
+
+// Finishes a partner-split backward: sums the splits' raw sweep sums in a fixed order and adds the diagonal terms (the
+// epilogues of bwd_rows_kernel / bwd_cols_kernel).
+__global__ void __launch_bounds__(256)
+bwd_merge_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const float* __restrict__ LV, TcParams p,
+                 const float* __restrict__ g_loss, int nsplit, const float* __restrict__ part_z,
+                 const float* __restrict__ part_mu, const float* __restrict__ part_lv, float* __restrict__ g_z,
+                 float* __restrict__ g_mu, float* __restrict__ g_lv) {
+  const float g = g_loss ? *g_loss : 1.f;
+  const float invB = 1.f / (float)p.B;
+  const float ca = p.alpha * invB * g, cz = p.gamma_anneal * invB * g;
+  const size_t rows = (size_t)(p.r1 - p.r0), n = rows * p.D;
+  for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (size_t)gridDim.x * blockDim.x) {
+    float sz = 0.f, s0 = 0.f, s1 = 0.f;
+    for (int y = 0; y < nsplit; ++y) { sz += part_z[y * n + e]; s0 += part_mu[y * n + e]; s1 += part_lv[y * n + e]; }
+    const size_t o = (size_t)p.r0 * p.D + e;
+    const float zv = Z[o], df = zv - MU[o], h2 = expf(-LV[o]);     // 2 h
+    g_z[o] = 2.f * kLn2 * sz - ca * (h2 * df) + cz * zv;
+    g_mu[o] = 2.f * kLn2 * s0 + ca * (h2 * df);
+    g_lv[o] = s1 + ca * (0.5f * h2 * df * df - 0.5f);
+  }
 }
 
 inline size_t smem_bytes(int DP) { return (size_t)2 * (3 * kTR * DP + 2 * kTR) * sizeof(float); }   // two staging buffers of width DP

@@ -469,6 +469,12 @@ class _ShardedSwdPeer(torch.autograd.Function):
 _peer_ok = {}
 
 
+def _gemm_fits(J: int, K: int) -> bool:
+    """Shape limits of vk_gemm_nt (csrc/gemm3x.cuh g3::fits): tensor-memory columns and the shared-memory B images."""
+    Jp, Kp = (J + 15) // 16 * 16, (K + 15) // 16 * 16
+    return Jp <= 256 and Kp <= 256 and 3 * (Kp // 2) + Jp <= 512 and 3 * Jp * Kp * 2 + 256 <= 200 * 1024
+
+
 def _peer_available(group, z_local, S) -> bool:
     """Can this process group map peer memory (torch symmetric memory over NVLink)?  Decided once per group by trying the
     rendezvous; all ranks take the same branch because the rendezvous itself is collective."""
@@ -494,7 +500,11 @@ def sharded_swd(z_local, proj, p, reg_weight, group=None, exchange="auto", waves
     decomposition with both exchanges fused into the GEMMs over peer-mapped memory, CUDA + NVLink only) or "all_gather" (z travels; each rank projects all rows on its slice of
     the projections and the [N, D] gradient is reduce-scattered -- kept for shapes the tcgen05 GEMM does not take)."""
     if exchange == "auto":
-        exchange = "peer" if world_rank(group)[0] > 1 and _peer_available(group, z_local, proj.shape[0]) else "all_to_all"
+        S, D = proj.shape
+        if not (_gemm_fits(S, D) and _gemm_fits(D, S)):
+            exchange = "all_gather"             # shapes the tcgen05 GEMM does not take: vk_swd_fwd has an FFMA GEMM
+        else:
+            exchange = "peer" if world_rank(group)[0] > 1 and _peer_available(group, z_local, S) else "all_to_all"
     if exchange == "peer" and world_rank(group)[0] > 1:
         return _ShardedSwdPeer.apply(z_local, proj.contiguous(), float(p), float(reg_weight), group)
     if exchange in ("all_to_all", "peer"):

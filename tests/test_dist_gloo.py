@@ -41,6 +41,7 @@ def test_partition_plans():
             s0, s1 = vd.plan_projections(S, w, r)
             pieces = [plan[k][r] for k in range(q)]
             assert pieces[0][0] == s0 and pieces[-1][1] == s1 and all(a[1] == b[0] for a, b in zip(pieces, pieces[1:]))
+    assert vd._gemm_fits(200, 128) and vd._gemm_fits(128, 200) and not vd._gemm_fits(300, 128) and not vd._gemm_fits(256, 256)
     # without a process group the collectives are identities
     x = torch.arange(6.0).view(3, 2)
     assert torch.equal(vd.gather_rows(x), x) and torch.equal(vd.scatter_rows_sum(x), x)
