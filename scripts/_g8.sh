@@ -1,9 +1,8 @@
 #!/bin/bash
-TAG=${1:-r01r}
+TAG=${1:-r01t}
 mkdir -p gpurun_out
-timeout 300 python -m pytest tests/test_gpu_next_models.py -x -q 2>&1 | tail -3
 run() { # workload n
-  timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $2 --master-addr 127.0.0.1 --master-port $((29500 + $2)) \
+  timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $2 --master-addr 127.0.0.1 --master-port $((29500 + $2)) \
     bench.py --workload $1 --gpus $2 --steps 20 --warmup 3 --no-cpu --no-e2e > gpurun_out/scale_$1_${TAG}_n$2.json 2> gpurun_out/scale_$1_${TAG}_n$2.err
   python - <<PY
 import json
@@ -14,11 +13,5 @@ except Exception as e:
     print("$1 n=$2 failed", e); print(open("gpurun_out/scale_$1_${TAG}_n$2.err").read()[-1500:])
 PY
 }
-run swae 8
-run swae 4
-run swae 2
 run betatc 8
-run betatc 2
-run wae_mmd_rbf 8
-run wae_mmd_rbf 4
-run wae_mmd_imq 8
+run betatc 4
