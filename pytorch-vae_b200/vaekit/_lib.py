@@ -115,7 +115,38 @@ def ptr(t):
 
 
 def stream_ptr():
-    return torch.cuda.current_stream().cuda_stream
+    return _raw_stream(torch.cuda.current_device())
+
+
+# Host fast paths: the public torch.cuda.current_stream() / torch.cuda.device() helpers spend 5-10 us each in Python
+# argument handling, which is visible on the short steps (VQ: ~180 us of host time per step).  The underlying C entry
+# points are used directly when this torch has them.
+if hasattr(torch._C, "_cuda_getCurrentRawStream"):
+    def _raw_stream(index):
+        return torch._C._cuda_getCurrentRawStream(index)
+else:                                                    # pragma: no cover
+    def _raw_stream(index):
+        return torch.cuda.current_stream(index).cuda_stream
+
+
+class on:
+    """`with on(device):` == `with torch.cuda.device(device):` without the argument parsing."""
+    __slots__ = ("idx", "prev")
+
+    def __init__(self, device):
+        self.idx = device.index if device.index is not None else -1
+        self.prev = -1
+
+    def __enter__(self):
+        self.prev = torch.cuda._exchange_device(self.idx)
+
+    def __exit__(self, *exc):
+        self.idx = torch.cuda._maybe_exchange_device(self.prev)
+        return False
+
+
+if not (hasattr(torch.cuda, "_exchange_device") and hasattr(torch.cuda, "_maybe_exchange_device")):   # pragma: no cover
+    on = torch.cuda.device
 
 
 def require(t, name, dims=None):
@@ -132,13 +163,29 @@ def require(t, name, dims=None):
 
 
 _workspaces = {}
+_ws_min = None
+_ws_sizes = {}
+
+
+def ws_bytes(op, *shape):
+    """vk_<op>_workspace_bytes(*shape), cached per shape (a ctypes round trip per call otherwise)."""
+    key = (op,) + shape
+    v = _ws_sizes.get(key)
+    if v is None:
+        v = int(getattr(lib(), "vk_%s_workspace_bytes" % op)(*shape))
+        _ws_sizes[key] = v
+    return v
 
 
 def workspace(device, min_bytes=0):
     """Zero-initialised scratch buffer, one per (device, stream); kernels leave the
     ticket header zeroed, so it is reused across calls without a memset."""
-    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
-    need = max(int(lib().vk_workspace_bytes()), int(min_bytes))
+    global _ws_min
+    index = device.index if device.index is not None else torch.cuda.current_device()
+    key = (index, _raw_stream(index))
+    if _ws_min is None:
+        _ws_min = int(lib().vk_workspace_bytes())
+    need = max(_ws_min, int(min_bytes))
     ws = _workspaces.get(key)
     if ws is None or ws.numel() < need:
         ws = torch.zeros(need, dtype=torch.uint8, device=device)

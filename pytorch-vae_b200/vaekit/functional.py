@@ -49,7 +49,7 @@ class _ReparamKL(torch.autograd.Function):
         kl = torch.empty(mu.shape[:-1], dtype=torch.float32, device=dev) if want_kl else None
         eps = torch.empty(mu.shape, dtype=torch.float32, device=dev) if want_eps else None
         if rows * D > 0:
-            with torch.cuda.device(dev):
+            with L.on(dev):
                 L.call("reparam_kl_fwd", L.ptr(mu_v), L.ptr(lv_v), L.i64x3(outer), L.i64x3(ms), L.i64x3(ls), D,
                                                seed, offset, L.ptr(z), L.ptr(kl), L.ptr(eps), L.stream_ptr())
         ctx.save_for_backward(mu, log_var)
@@ -73,7 +73,7 @@ class _ReparamKL(torch.autograd.Function):
         if g_kl is not None:
             g_kl = g_kl.contiguous()
         if g_mu.numel() > 0:
-            with torch.cuda.device(dev):
+            with L.on(dev):
                 L.call("reparam_kl_bwd", L.ptr(g_z), L.ptr(g_kl), L.ptr(mu_v), L.ptr(lv_v), L.i64x3(outer),
                                                L.i64x3(ms), L.i64x3(ls), D, ctx.rng[0], ctx.rng[1], L.ptr(g_mu),
                                                L.ptr(g_lv), L.stream_ptr())
@@ -98,7 +98,7 @@ def philox_normal(shape, device, rng=None):
     out = torch.empty(shape, dtype=torch.float32, device=device)
     if rng is None:
         rng = next_philox(out.device, out.numel())
-    with torch.cuda.device(out.device):
+    with L.on(out.device):
         L.call("philox_normal", L.ptr(out), out.numel(), rng[0], rng[1], L.stream_ptr())
     return out
 
@@ -109,14 +109,14 @@ def philox_normal_dev(shape, key, quad_shift=0):
     if key.dtype != torch.int64 or not key.is_cuda or key.numel() != 2:
         raise RuntimeError("vaekit: philox key must be an int64 CUDA tensor with two elements")
     out = torch.empty(shape, dtype=torch.float32, device=key.device)
-    with torch.cuda.device(out.device):
+    with L.on(out.device):
         L.call("philox_normal_dev", L.ptr(out), out.numel(), L.ptr(key), int(quad_shift), L.stream_ptr())
     return out
 
 
 def philox_raw(n_quads, device, seed, offset):
     out = torch.empty((n_quads, 4), dtype=torch.int32, device=device)
-    with torch.cuda.device(out.device):
+    with L.on(out.device):
         L.call("philox_raw", L.ptr(out), n_quads, seed, offset, L.stream_ptr())
     return out
 
@@ -139,7 +139,7 @@ class _Elbo(torch.autograd.Function):
         dev = recons.device
         out = torch.empty(4, dtype=torch.float32, device=dev)
         ws = L.workspace(dev)
-        with torch.cuda.device(dev):
+        with L.on(dev):
             L.call("elbo_fwd", L.ptr(r), L.ptr(x), r.numel(), L.ptr(klc), 0 if klc is None else klc.numel(),
                                      recon_mode, alpha, combine_mode, w, C, L.ptr(out), L.ptr(ws), ws.numel(),
                                      L.stream_ptr())
@@ -158,7 +158,7 @@ class _Elbo(torch.autograd.Function):
         g_kl = torch.empty(kl_shape, dtype=torch.float32, device=dev) if (need_kl and kl_shape is not None) else None
         gs = [None if g is None else g.contiguous() for g in (g0, g1, g2, g3)]
         rows = 0 if kl_shape is None else max(1, int(torch.Size(kl_shape).numel()))
-        with torch.cuda.device(dev):
+        with L.on(dev):
             L.call("elbo_bwd", L.ptr(r), L.ptr(x), r.numel(), rows, recon_mode, alpha, combine_mode, w, C,
                                      L.ptr(out), L.ptr(gs[0]), L.ptr(gs[1]), L.ptr(gs[2]), L.ptr(gs[3]),
                                      L.ptr(g_rec), L.ptr(g_kl), L.stream_ptr())
@@ -181,7 +181,7 @@ def per_image_mse(recons, input):
     out = torch.empty(B, dtype=torch.float32, device=r.device)
     if r.numel() == 0:
         return out
-    with torch.cuda.device(r.device):
+    with L.on(r.device):
         L.call("per_image_mse", L.ptr(r), L.ptr(x), B, r.numel() // B, L.ptr(out), L.stream_ptr())
     return out
 
@@ -223,7 +223,7 @@ class _IwBound(torch.autograd.Function):
         lp = torch.empty(kl.shape, dtype=torch.float32, device=dev)
         out = torch.empty(4, dtype=torch.float32, device=dev)
         ws = L.workspace(dev, 256 + 24 * B)
-        with torch.cuda.device(dev):
+        with L.on(dev):
             L.call("iw_bound_fwd", L.ptr(r), L.ptr(x), L.ptr(klc), B, G, K, P, M_N, L.ptr(lp), L.ptr(out),
                                          L.ptr(ws), ws.numel(), L.stream_ptr())
         ctx.save_for_backward(r, x, klc, lp)
@@ -240,7 +240,7 @@ class _IwBound(torch.autograd.Function):
         g_rec = torch.empty_like(r) if ctx.needs_input_grad[0] else None
         g_kl = torch.empty_like(klc) if ctx.needs_input_grad[2] else None
         gs = [None if g is None else g.contiguous() for g in (g0, g1, g2, g3)]
-        with torch.cuda.device(r.device):
+        with L.on(r.device):
             L.call("iw_bound_bwd", L.ptr(r), L.ptr(x), L.ptr(lp), L.ptr(klc), B, G, K, P, M_N, L.ptr(gs[0]),
                                          L.ptr(gs[1]), L.ptr(gs[2]), L.ptr(gs[3]), L.ptr(g_rec), L.ptr(g_kl),
                                          L.stream_ptr())
@@ -272,11 +272,11 @@ class _VectorQuantize(torch.autograd.Function):
         q = torch.empty_like(x)
         idx = torch.empty(B * HW, dtype=torch.int32, device=dev)
         out = torch.empty(2, dtype=torch.float32, device=dev)
-        need = int(L.lib().vk_vq_workspace_bytes(D, K))
+        need = L.ws_bytes("vq", D, K)
         if need < 0:
             raise RuntimeError("vaekit: VectorQuantizer shape D=%d K=%d is not supported" % (D, K))
         ws = L.workspace(dev, need)
-        with torch.cuda.device(dev):
+        with L.on(dev):
             L.call("vq_fwd", L.ptr(x), L.ptr(e), B, D, HW, K, beta, L.ptr(q), L.ptr(idx), L.ptr(out), L.ptr(ws),
                    ws.numel(), L.stream_ptr())
         ctx.save_for_backward(x, e, idx)
@@ -293,7 +293,7 @@ class _VectorQuantize(torch.autograd.Function):
         g_e = torch.empty_like(e) if ctx.needs_input_grad[1] else None
         g_q = None if g_q is None else g_q.contiguous()
         g_loss = None if g_loss is None else g_loss.contiguous()
-        with torch.cuda.device(x.device):
+        with L.on(x.device):
             L.call("vq_bwd", L.ptr(g_q), L.ptr(g_loss), L.ptr(x), L.ptr(e), L.ptr(idx), B, D, HW, K, beta,
                    L.ptr(g_x), L.ptr(g_e), L.stream_ptr())
         return g_x, g_e, None
@@ -319,13 +319,13 @@ def mmd_sweep(z_all, prior_all, kernel_type, z_var, row_begin, row_end, passes=3
     z, p = z_all.contiguous(), prior_all.contiguous()
     N, D = z.shape
     dev = z.device
-    need = int(L.lib().vk_mmd_workspace_bytes(N, D))
+    need = L.ws_bytes("mmd", N, D)
     if need < 0:
         raise RuntimeError("vaekit: MMD shape N=%d D=%d is not supported (latent dim must be <= 128)" % (N, D))
     ws = L.workspace(dev, need)
     sums = torch.empty(3, dtype=torch.float64, device=dev)
     grad = torch.empty((row_end - row_begin, D), dtype=torch.float32, device=dev)
-    with torch.cuda.device(dev):
+    with L.on(dev):
         L.call("mmd_fwd", L.ptr(z), L.ptr(p), N, D, kernel_type, z_var, passes, row_begin, row_end, L.ptr(sums),
                L.ptr(grad), L.ptr(ws), ws.numel(), L.stream_ptr())
     return sums, grad
@@ -333,14 +333,14 @@ def mmd_sweep(z_all, prior_all, kernel_type, z_var, row_begin, row_end, passes=3
 
 def mmd_combine(sums, N, kernel_type, reg_weight):
     out = torch.empty(4, dtype=torch.float32, device=sums.device)
-    with torch.cuda.device(sums.device):
+    with L.on(sums.device):
         L.call("mmd_combine", L.ptr(sums), N, kernel_type, reg_weight, L.ptr(out), L.stream_ptr())
     return out
 
 
 def scale_by_scalar(t, g, factor):
     out = torch.empty_like(t)
-    with torch.cuda.device(t.device):
+    with L.on(t.device):
         L.call("scale_by_scalar", L.ptr(t), L.ptr(g), factor, t.numel(), L.ptr(out), L.stream_ptr())
     return out
 
@@ -382,7 +382,7 @@ def _pair_fwd(x1, s1, x2, s2, N1, N2, D, kt, z_var, eps):
     kmat = torch.empty((N1, N2), dtype=torch.float32, device=dev)
     imq = torch.empty(1, dtype=torch.float32, device=dev) if kt == 1 else None
     ws = L.workspace(dev)
-    with torch.cuda.device(dev):
+    with L.on(dev):
         L.call("pair_kernel_fwd", L.ptr(x1), L.i64x3(s1), L.ptr(x2), L.i64x3(s2), N1, N2, D, kt, z_var, eps, L.ptr(kmat),
                L.ptr(imq), L.ptr(ws), ws.numel(), L.stream_ptr())
     return kmat, imq
@@ -416,7 +416,7 @@ class _PairKernelRows(torch.autograd.Function):
         g, g_sr, g_sc = _upstream(g, kt)
         g1 = torch.empty((N1, D), dtype=torch.float32, device=x1.device) if ctx.needs_input_grad[0] else None
         g2 = torch.empty((N2, D), dtype=torch.float32, device=x1.device) if ctx.needs_input_grad[1] else None
-        with torch.cuda.device(x1.device):
+        with L.on(x1.device):
             L.call("pair_kernel_bwd_rows", L.ptr(x1), x1.stride(0), x1.stride(1), L.ptr(x2), x2.stride(0), x2.stride(1), N1,
                    N2, D, kt, z_var, eps, L.ptr(kmat), L.ptr(g), g_sr, g_sc, L.ptr(g1), L.ptr(g2), L.stream_ptr())
         return g1, g2, None, None, None
@@ -441,7 +441,7 @@ class _PairKernelDense(torch.autograd.Function):
         g, g_sr, g_sc = _upstream(g, kt)
         g1 = torch.empty((N1, N2, D), dtype=torch.float32, device=x1.device) if ctx.needs_input_grad[0] else None
         g2 = torch.empty((N1, N2, D), dtype=torch.float32, device=x1.device) if ctx.needs_input_grad[1] else None
-        with torch.cuda.device(x1.device):
+        with L.on(x1.device):
             L.call("pair_kernel_bwd_dense", L.ptr(x1), L.i64x3(x1.stride()), L.ptr(x2), L.i64x3(x2.stride()), N1, N2, D,
                    kt, z_var, eps, L.ptr(kmat), L.ptr(g), g_sr, g_sc, L.ptr(g1), L.ptr(g2), L.stream_ptr())
         return g1, g2, None, None, None
@@ -481,10 +481,10 @@ def swd_sweep(z, prior, proj, p, want_grad=True):
     if N * S == 0:
         raise RuntimeError("vaekit: empty input to the sliced-Wasserstein distance")
     dev = zc.device
-    ws = L.workspace(dev, int(L.lib().vk_swd_workspace_bytes(N, S)))
+    ws = L.workspace(dev, L.ws_bytes("swd", N, S))
     total = torch.empty(1, dtype=torch.float64, device=dev)
     grad = torch.empty((N, D), dtype=torch.float32, device=dev) if want_grad else None
-    with torch.cuda.device(dev):
+    with L.on(dev):
         L.call("swd_fwd", L.ptr(zc), L.ptr(pc), L.ptr(th), N, D, S, p, L.ptr(total), L.ptr(grad), L.ptr(ws), ws.numel(),
                L.stream_ptr())
     return total, grad
@@ -492,7 +492,7 @@ def swd_sweep(z, prior, proj, p, want_grad=True):
 
 def mean_scale(total, count, scale):
     out = torch.empty(1, dtype=torch.float32, device=total.device)
-    with torch.cuda.device(total.device):
+    with L.on(total.device):
         L.call("mean_scale", L.ptr(total), float(count), scale, L.ptr(out), L.stream_ptr())
     return out[0]
 
@@ -535,8 +535,8 @@ def swd_project(x, proj, out=None):
         raise RuntimeError("vaekit: swd_project output must be a [S, n] fp32 view contiguous along n")
     if n * S == 0:
         return out
-    ws = L.workspace(x.device, int(L.lib().vk_gemm_nt_workspace_bytes()))
-    with torch.cuda.device(x.device):
+    ws = L.workspace(x.device, L.ws_bytes("gemm_nt"))
+    with L.on(x.device):
         L.call("gemm_nt", L.ptr(x), x.stride(0), x.stride(1), L.ptr(proj), proj.stride(0), proj.stride(1), L.ptr(out), 1,
                out.stride(0), n, S, D, L.ptr(ws), ws.numel(), L.stream_ptr())
     return out
@@ -553,8 +553,8 @@ def swd_segments(lat, pri, p, want_grad=True):
     total = torch.zeros(1, dtype=torch.float64, device=lat.device)
     if S * N == 0:
         return total
-    ws = L.workspace(lat.device, int(L.lib().vk_swd_segments_workspace_bytes(N, S)))
-    with torch.cuda.device(lat.device):
+    ws = L.workspace(lat.device, L.ws_bytes("swd_segments", N, S))
+    with L.on(lat.device):
         L.call("swd_segments_fwd", L.ptr(lat), L.ptr(pri), N, S, p, L.ptr(total), 1 if want_grad else 0, L.ptr(ws),
                ws.numel(), L.stream_ptr())
     return total
@@ -570,8 +570,8 @@ def swd_project_back(g_lat, proj):
         return out
     if S == 0:
         return out.zero_()
-    ws = L.workspace(g_lat.device, int(L.lib().vk_gemm_nt_workspace_bytes()))
-    with torch.cuda.device(g_lat.device):
+    ws = L.workspace(g_lat.device, L.ws_bytes("gemm_nt"))
+    with L.on(g_lat.device):
         L.call("gemm_nt", L.ptr(g_lat), g_lat.stride(1), g_lat.stride(0), L.ptr(proj), proj.stride(1), proj.stride(0),
                L.ptr(out), D, 1, n, D, S, L.ptr(ws), ws.numel(), L.stream_ptr())
     return out
@@ -588,8 +588,8 @@ def swd_project_cols(x, proj, c_cols):
         raise RuntimeError("vaekit: column table must be an int64 CUDA tensor with one address per projection")
     if n * S == 0:
         return
-    ws = L.workspace(x.device, int(L.lib().vk_gemm_nt_workspace_bytes()))
-    with torch.cuda.device(x.device):
+    ws = L.workspace(x.device, L.ws_bytes("gemm_nt"))
+    with L.on(x.device):
         L.call("gemm_nt_tab", None, L.ptr(x), x.stride(0), x.stride(1), L.ptr(proj), proj.stride(0), proj.stride(1),
                L.ptr(c_cols), None, 1, 0, n, S, D, L.ptr(ws), ws.numel(), L.stream_ptr())
 
@@ -604,8 +604,8 @@ def swd_project_back_cols(a_cols, n, proj):
     out = torch.empty((n, D), dtype=torch.float32, device=proj.device)
     if n == 0:
         return out
-    ws = L.workspace(proj.device, int(L.lib().vk_gemm_nt_workspace_bytes()))
-    with torch.cuda.device(proj.device):
+    ws = L.workspace(proj.device, L.ws_bytes("gemm_nt"))
+    with L.on(proj.device):
         L.call("gemm_nt_tab", L.ptr(a_cols), None, 1, 0, L.ptr(proj), proj.stride(1), proj.stride(0), None, L.ptr(out), D, 1,
                n, D, S, L.ptr(ws), ws.numel(), L.stream_ptr())
     return out
@@ -621,8 +621,8 @@ def seg_sort(keys, want_perm=False):
         return out, (torch.empty((S, n), dtype=torch.int64, device=out.device) if want_perm else None)
     dev = out.device
     perm = torch.empty((S, n), dtype=torch.int32, device=dev) if want_perm else None
-    ws = L.workspace(dev, int(L.lib().vk_seg_sort_workspace_bytes(S, n)))
-    with torch.cuda.device(dev):
+    ws = L.workspace(dev, L.ws_bytes("seg_sort", S, n))
+    with L.on(dev):
         L.call("seg_sort", L.ptr(out), L.ptr(perm), S, n, L.ptr(ws), ws.numel(), L.stream_ptr())
     return out, (perm.long() if want_perm else None)
 
@@ -638,8 +638,8 @@ def gemm_nt(a, b):
     out = torch.empty((N, J), dtype=torch.float32, device=a.device)
     if N * J == 0:
         return out
-    ws = L.workspace(a.device, int(L.lib().vk_gemm_nt_workspace_bytes()))
-    with torch.cuda.device(a.device):
+    ws = L.workspace(a.device, L.ws_bytes("gemm_nt"))
+    with L.on(a.device):
         L.call("gemm_nt", L.ptr(a), a.stride(0), a.stride(1), L.ptr(b), b.stride(0), b.stride(1), L.ptr(out), J, 1,
                N, J, K, L.ptr(ws), ws.numel(), L.stream_ptr())
     return out
@@ -664,8 +664,8 @@ class _BetaTc(torch.autograd.Function):
         lqz = torch.empty(2 * B, dtype=torch.float32, device=dev)     # value, then its fp32 residual
         lse = torch.empty((B, D), dtype=torch.float32, device=dev)
         out = torch.empty(4, dtype=torch.float32, device=dev)
-        ws = L.workspace(dev, int(L.lib().vk_tc_workspace_bytes(B, D)))
-        with torch.cuda.device(dev):
+        ws = L.workspace(dev, L.ws_bytes("tc", B, D))
+        with L.on(dev):
             L.call("tc_fwd", L.ptr(zc), L.ptr(mc), L.ptr(lc), B, D, M_N, alpha, beta, gamma_anneal, L.ptr(lqz), L.ptr(lse),
                    L.ptr(out), L.ptr(ws), ws.numel(), L.stream_ptr())
         ctx.save_for_backward(zc, mc, lc, lqz, lse)
@@ -683,8 +683,8 @@ class _BetaTc(torch.autograd.Function):
         B, D, M_N, alpha, beta, gamma_anneal = ctx.cfg
         dev = zc.device
         g_z, g_mu, g_lv = torch.empty_like(zc), torch.empty_like(mc), torch.empty_like(lc)
-        ws = L.workspace(dev, int(L.lib().vk_tc_workspace_bytes(B, D)))
-        with torch.cuda.device(dev):
+        ws = L.workspace(dev, L.ws_bytes("tc", B, D))
+        with L.on(dev):
             L.call("tc_bwd", L.ptr(zc), L.ptr(mc), L.ptr(lc), L.ptr(lqz), L.ptr(lse), B, D, M_N, alpha, beta, gamma_anneal,
                    L.ptr(g.contiguous()), L.ptr(g_z), L.ptr(g_mu), L.ptr(g_lv), L.ptr(ws), ws.numel(), L.stream_ptr())
         return g_z, g_mu, g_lv, None, None, None, None
@@ -701,8 +701,8 @@ def betatc_rows_fwd(z_all, mu_all, lv_all, row_begin, row_end, M_N, alpha, beta,
     lqz = torch.zeros(2 * B, dtype=torch.float32, device=dev)
     lse = torch.zeros((B, D), dtype=torch.float32, device=dev)
     out = torch.empty(4, dtype=torch.float32, device=dev)
-    ws = L.workspace(dev, int(L.lib().vk_tc_workspace_bytes(B, D)))
-    with torch.cuda.device(dev):
+    ws = L.workspace(dev, L.ws_bytes("tc", B, D))
+    with L.on(dev):
         L.call("tc_fwd_rows", L.ptr(zc), L.ptr(mc), L.ptr(lc), B, D, int(row_begin), int(row_end), M_N, alpha, beta,
                gamma_anneal, L.ptr(lqz), L.ptr(lse), L.ptr(out), L.ptr(ws), ws.numel(), L.stream_ptr())
     return out, lqz, lse
@@ -714,8 +714,8 @@ def betatc_rows_bwd(z_all, mu_all, lv_all, lqz_all, lse_all, row_begin, row_end,
     B, D = z_all.shape
     dev = z_all.device
     g_z, g_mu, g_lv = (torch.empty((B, D), dtype=torch.float32, device=dev) for _ in range(3))
-    ws = L.workspace(dev, int(L.lib().vk_tc_workspace_bytes(B, D)))
-    with torch.cuda.device(dev):
+    ws = L.workspace(dev, L.ws_bytes("tc", B, D))
+    with L.on(dev):
         L.call("tc_bwd_rows", L.ptr(z_all), L.ptr(mu_all), L.ptr(lv_all), L.ptr(lqz_all), L.ptr(lse_all), B, D,
                int(row_begin), int(row_end), M_N, alpha, beta, gamma_anneal, L.ptr(g.contiguous()), L.ptr(g_z), L.ptr(g_mu),
                L.ptr(g_lv), L.ptr(ws), ws.numel(), L.stream_ptr())

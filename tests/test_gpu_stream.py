@@ -47,6 +47,36 @@ def test_philox_bits_and_normals(vk):
     assert abs((x ** 4).mean().item() - 3) < 3e-2
 
 
+def test_philox_distribution_and_partition_invariance(vk):
+    """SURVEY 8(c) RNG contract: moments and a Kolmogorov-Smirnov distance on 2^26 normals, and bit-reproducibility of a
+    fixed (seed, offset) stream however the [N, D] sample is partitioned over 1/2/4/8 ranks (each rank starts the stream
+    at its first row: vk_philox_normal_dev with a counter shift, key held on the device)."""
+    F, _ = vk
+    dev = torch.device(DEV)
+    n = 1 << 26
+    x = F.philox_normal((n,), dev, rng=(1265, 0))
+    xd = x.double()
+    m, sd = xd.mean().item(), xd.std().item()
+    z = (xd - m) / sd
+    assert abs(m) < 5e-4 and abs(sd - 1) < 5e-4
+    assert abs((z ** 3).mean().item()) < 2e-3 and abs((z ** 4).mean().item() - 3) < 5e-3
+    srt = torch.sort(x[: 1 << 24]).values.double()
+    cdf = 0.5 * (1 + torch.erf(srt / 2 ** 0.5))
+    emp = (torch.arange(1, srt.numel() + 1, device=dev, dtype=torch.float64)) / srt.numel()
+    ks = (cdf - emp).abs().max().item()
+    assert ks < 1.63 / (srt.numel() ** 0.5) * 1.5, ks                  # 1 % critical value of the KS statistic, with slack
+    # partition invariance
+    N, D = 1024, 128
+    seed, offset = (1 << 63) + 99, 12345
+    full = F.philox_normal((N, D), dev, rng=(seed, offset))
+    key = torch.tensor([seed - (1 << 64), offset], dtype=torch.int64, device=dev)
+    assert torch.equal(F.philox_normal_dev((N, D), key), full)
+    for world in (2, 4, 8):
+        rows = N // world
+        parts = [F.philox_normal_dev((rows, D), key, quad_shift=r * rows * D // 4) for r in range(world)]
+        assert torch.equal(torch.cat(parts), full), world
+
+
 def test_reparam_matches_golden_with_injected_noise(vk):
     F, _ = vk
     g = load("vanilla", DEV)
