@@ -303,6 +303,26 @@ int vk_tc_bwd_rows(const float* z, const float* mu, const float* log_var, const 
                    const float* g_loss, float* g_z, float* g_mu, float* g_lv, void* workspace, int64_t workspace_bytes,
                    void* stream);
 
+/* ---------------------------------------------------------------------------
+ * K8  Gumbel-softmax reparameterisation and categorical KL   (reference: models/cat_vae.py:118-131, 133-173; the same
+ *     trick in joint_vae.py:142-167) -- SURVEY 8(f) rank 4
+ *
+ * q [R, C] logits, one categorical row per (sample, latent dim).
+ *   vk_gumbel_softmax_fwd: u ~ U(0,1) from the contract Philox stream (one 23-bit uniform per element, keyed by the
+ *     element index) or read from u_in when non-NULL; g = -log(-log(u + eps) + eps); s_out = softmax((q + g) / temp, -1).
+ *     u_out (optional) receives the uniforms so the oracle can be evaluated on the same noise.
+ *   vk_gumbel_softmax_bwd: g_q = s (g_s - sum_c g_s s) / temp.
+ *   vk_cat_kl_rows_fwd: rows_out[b] = sum_{l, c} p (log(p + eps) - log(1/C + eps)), p = softmax(q[b, l, :]); the batch
+ *     mean and the loss combine happen in vk_elbo_fwd (rows_out goes in as its kl_rows).
+ *   vk_cat_kl_rows_bwd: g_q from the per-sample upstream gradients g_rows [B].
+ * -------------------------------------------------------------------------*/
+int vk_gumbel_softmax_fwd(const float* q, int64_t R, int64_t C, float temp, float eps, uint64_t seed, uint64_t offset,
+                          const float* u_in, float* s_out, float* u_out, void* stream);
+int vk_gumbel_softmax_bwd(const float* s, const float* g_s, int64_t R, int64_t C, float temp, float* g_q, void* stream);
+int vk_cat_kl_rows_fwd(const float* q, int64_t B, int64_t L, int64_t C, float eps, float* rows_out, void* stream);
+int vk_cat_kl_rows_bwd(const float* q, const float* g_rows, int64_t B, int64_t L, int64_t C, float eps, float* g_q,
+                       void* stream);
+
 #ifdef __cplusplus
 }
 #endif

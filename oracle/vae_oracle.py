@@ -152,6 +152,24 @@ def factor_vae_loss(recons: Tensor, input: Tensor, mu: Tensor, log_var: Tensor, 
             "KLD": -kld_loss, "VAE_TC_Loss": vae_tc_loss}
 
 
+def gumbel_softmax(q: Tensor, u: Tensor, temp: float, eps: float = 1e-7) -> Tensor:
+    """cat_vae.py:118-131 with the uniforms u (torch.rand_like in the reference) injected; returns [B, D * Q]."""
+    g = -torch.log(-torch.log(u + eps) + eps)
+    s = F.softmax((q + g) / temp, dim=-1)
+    return s.view(-1, q.shape[-2] * q.shape[-1])
+
+
+def cat_vae_loss(recons: Tensor, input: Tensor, q: Tensor, M_N: float, *, alpha: float) -> Dict[str, Tensor]:
+    """cat_vae.py:133-173 (the temperature annealing is host state, tested separately)."""
+    q_p = F.softmax(q, dim=-1)
+    recons_loss = F.mse_loss(recons, input, reduction="mean")
+    eps = 1e-7
+    h1 = q_p * torch.log(q_p + eps)
+    h2 = q_p * math.log(1. / q.shape[-1] + eps)
+    kld_loss = torch.mean(torch.sum(h1 - h2, dim=(1, 2)), dim=0)
+    return {"loss": alpha * recons_loss + M_N * kld_loss, "Reconstruction_Loss": recons_loss, "KLD": -kld_loss}
+
+
 def beta_loss(recons: Tensor, input: Tensor, mu: Tensor, log_var: Tensor, M_N: float, *,
               loss_type: str, beta: float, gamma: float, C_max: float, C_stop_iter: float,
               num_iter: int) -> Dict[str, Tensor]:

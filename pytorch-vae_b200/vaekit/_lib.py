@@ -54,6 +54,10 @@ _SIGNATURES = {
     "vk_tc_bwd": ([_p, _p, _p, _p, _p, _i64, _i64, _f, _f, _f, _f, _p, _p, _p, _p, _p, _i64, _p], _i),
     "vk_tc_fwd_rows": ([_p, _p, _p, _i64, _i64, _i64, _i64, _f, _f, _f, _f, _p, _p, _p, _p, _i64, _p], _i),
     "vk_tc_bwd_rows": ([_p, _p, _p, _p, _p, _i64, _i64, _i64, _i64, _f, _f, _f, _f, _p, _p, _p, _p, _p, _i64, _p], _i),
+    "vk_gumbel_softmax_fwd": ([_p, _i64, _i64, _f, _f, _u64, _u64, _p, _p, _p, _p], _i),
+    "vk_gumbel_softmax_bwd": ([_p, _p, _i64, _i64, _f, _p, _p], _i),
+    "vk_cat_kl_rows_fwd": ([_p, _i64, _i64, _i64, _f, _p, _p], _i),
+    "vk_cat_kl_rows_bwd": ([_p, _p, _i64, _i64, _i64, _f, _p, _p], _i),
     "vk_iw_bound_bwd": ([_p, _p, _p, _p, _i64, _i64, _i64, _i64, _f, _p, _p, _p, _p, _p, _p, _p], _i),
 }
 

@@ -726,3 +726,78 @@ def betatc_terms(z, mu, log_var, M_N, alpha, beta, gamma_anneal):
     """betatc_vae.py:165-205 without the reconstruction term: returns (alpha*mi + beta*tc + gamma_anneal*kld,
     terms[3] = {kld, tc, mi})."""
     return _BetaTc.apply(z, mu, log_var, float(M_N), float(alpha), float(beta), float(gamma_anneal))
+
+
+# ---------------------------------------------------------------------------
+# K8: Gumbel-softmax + categorical KL (SURVEY 8(f) rank 4)
+# ---------------------------------------------------------------------------
+class _GumbelSoftmax(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, q, temp, eps, seed, offset, u_in, want_u):
+        L.require(q, "logits")
+        if q.dim() < 1 or q.numel() == 0:
+            raise RuntimeError("vaekit: empty logits")
+        qc = q.contiguous()
+        C = qc.shape[-1]
+        R = qc.numel() // C
+        s = torch.empty_like(qc)
+        u_out = torch.empty_like(qc) if want_u else None
+        uc = None if u_in is None else L.require(u_in, "uniforms").contiguous()
+        with L.on(qc.device):
+            L.call("gumbel_softmax_fwd", L.ptr(qc), R, C, temp, eps, seed, offset, L.ptr(uc), L.ptr(s), L.ptr(u_out),
+                   L.stream_ptr())
+        ctx.save_for_backward(s)
+        ctx.cfg = (R, C, temp)
+        if u_out is not None:
+            ctx.mark_non_differentiable(u_out)
+        return s, u_out
+
+    @staticmethod
+    def backward(ctx, g_s, _g_u):
+        if g_s is None:
+            return (None,) * 7
+        s, = ctx.saved_tensors
+        R, C, temp = ctx.cfg
+        g_q = torch.empty_like(s)
+        with L.on(s.device):
+            L.call("gumbel_softmax_bwd", L.ptr(s), L.ptr(g_s.contiguous()), R, C, temp, L.ptr(g_q), L.stream_ptr())
+        return g_q, None, None, None, None, None, None
+
+
+def gumbel_softmax(q, temp, eps=1e-7, *, rng=None, uniforms=None, want_uniforms=False):
+    """cat_vae.py:118-131 on logits [..., C]: softmax((q + gumbel) / temp, -1), same shape as q.  The uniforms come from the
+    contract Philox stream (torch.manual_seed governs them) unless `uniforms` is given.  Returns (s, uniforms or None)."""
+    if rng is None:
+        rng = next_philox(q.device, q.numel()) if q.is_cuda and uniforms is None else (0, 0)
+    return _GumbelSoftmax.apply(q, float(temp), float(eps), rng[0], rng[1], uniforms, bool(want_uniforms))
+
+
+class _CatKlRows(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, q, eps):
+        L.require(q, "logits", dims=(3,))
+        if q.numel() == 0:
+            raise RuntimeError("vaekit: empty logits")
+        qc = q.contiguous()
+        B, Ld, C = qc.shape
+        rows = torch.empty(B, dtype=torch.float32, device=qc.device)
+        with L.on(qc.device):
+            L.call("cat_kl_rows_fwd", L.ptr(qc), B, Ld, C, eps, L.ptr(rows), L.stream_ptr())
+        ctx.save_for_backward(qc)
+        ctx.eps = eps
+        return rows
+
+    @staticmethod
+    def backward(ctx, g_rows):
+        qc, = ctx.saved_tensors
+        B, Ld, C = qc.shape
+        g_q = torch.empty_like(qc)
+        with L.on(qc.device):
+            L.call("cat_kl_rows_bwd", L.ptr(qc), L.ptr(g_rows.contiguous()), B, Ld, C, ctx.eps, L.ptr(g_q), L.stream_ptr())
+        return g_q, None
+
+
+def cat_kl_rows(q, eps=1e-7):
+    """Per-sample KL(softmax(q) || uniform) of cat_vae.py:156-169 for logits [B, latent_dim, C]: [B] rows whose batch mean
+    is the reference's kld_loss."""
+    return _CatKlRows.apply(q, float(eps))

@@ -1,6 +1,6 @@
 """Model registry with the reference's keys (models/__init__.py:65-91) for the classes on the
 hot path, plus the SURVEY 8(f) "next" rows built so far: InfoVAE (rank 1) and the Gaussian-KL models ConditionalVAE, DIPVAE
-and FactorVAE (rank 2); the remaining reference variants are out of scope."""
+and FactorVAE (rank 2), CategoricalVAE (rank 4, Gumbel-softmax kernels); the remaining reference variants are out of scope."""
 from .base import BaseVAE
 from .vanilla_vae import VanillaVAE
 from .beta_vae import BetaVAE
@@ -15,10 +15,12 @@ from .betatc_vae import BetaTCVAE
 from .cvae import ConditionalVAE
 from .dip_vae import DIPVAE
 from .fvae import FactorVAE
+from .cat_vae import CategoricalVAE
 
 VAE = VanillaVAE
 GaussianVAE = VanillaVAE
 CVAE = ConditionalVAE
+GumbelVAE = CategoricalVAE
 
 vae_models = {
     'IWAE': IWAE,
@@ -34,4 +36,5 @@ vae_models = {
     'ConditionalVAE': ConditionalVAE,
     'DIPVAE': DIPVAE,
     'FactorVAE': FactorVAE,
+    'CategoricalVAE': CategoricalVAE,
 }

@@ -301,9 +301,35 @@ def gen_next_models():
          grad_recons=rl.grad, grad_mu=mul.grad, grad_log_var=lvl.grad, grad_z=zl.grad)
 
 
+def gen_cat():
+    """CategoricalVAE reparameterize (Gumbel-softmax, torch.rand_like patched to return the fixture's
+    uniforms) and loss_function of the unmodified reference."""
+    g = torch.Generator().manual_seed(404)
+    m = ref.CategoricalVAE(3, 6, categorical_dim=40, temperature=0.5, alpha=30.)
+    r, x = images(g, 5)
+    q = 1.5 * torch.randn(5, 6, 40, generator=g)
+    u = torch.rand(5, 6, 40, generator=g)
+    gs = torch.randn(5, 240, generator=g)
+    ql = leaf(q)
+    orig = torch.rand_like
+    torch.rand_like = lambda t, **kw: u.to(t.dtype)
+    try:
+        s = m.reparameterize(ql)
+    finally:
+        torch.rand_like = orig
+    s.backward(gs)
+    rl, q2 = leaf(r), leaf(q)
+    m.eval()                                           # no annealing: the temperature stays at its constructor value
+    d = m.loss_function(rl, x, q2, M_N=0.005, batch_idx=3)
+    d["loss"].backward()
+    save("catvae", in_recons=r, in_input=x, in_q=q, noise_u=u, in_gs=gs, hp_M_N=0.005, hp_temp=0.5, hp_alpha=30.,
+         out_s=s, grad_s_q=ql.grad, out_loss=d["loss"], out_Reconstruction_Loss=d["Reconstruction_Loss"],
+         out_KLD=d["KLD"], grad_recons=rl.grad, grad_q=q2.grad)
+
+
 if __name__ == "__main__":
     torch.set_num_threads(4)
     only = sys.argv[1:]
-    for fn in (gen_vanilla, gen_beta, gen_logcosh, gen_iw, gen_wae, gen_betatc, gen_swae, gen_vq, gen_info, gen_next_models):
+    for fn in (gen_vanilla, gen_beta, gen_logcosh, gen_iw, gen_wae, gen_betatc, gen_swae, gen_vq, gen_info, gen_next_models, gen_cat):
         if not only or fn.__name__[4:] in only:
             fn()

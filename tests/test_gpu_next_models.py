@@ -103,3 +103,68 @@ def test_per_image_mse_and_step_report(models, shape):
     assert abs(per[0] - ref[0].item()) <= 2e-6 * abs(ref[0].item()) + 1e-12
     vals, per = F.step_report(d)
     assert per is None and vals["KLD"] == -2.25
+
+
+def test_categorical_vae_golden(models):
+    """CategoricalVAE on vk_gumbel_softmax_* / vk_cat_kl_rows_* against the reference's fixture
+    (uniforms injected), forward and backward."""
+    from vaekit import functional as F
+    g = load("catvae", DEV)
+    q = leaf(g["in_q"])
+    s, _ = F.gumbel_softmax(q, g["hp_temp"], 1e-7, uniforms=g["noise_u"])
+    s.view(5, 240).backward(g["in_gs"])
+    assert_close(s.view(5, 240), g["out_s"], TOL, "gumbel-softmax sample")
+    assert_close(q.grad, g["grad_s_q"], TOL, "d sample / d logits")
+    m = models["CategoricalVAE"](3, 6, categorical_dim=40, temperature=0.5, alpha=30.).to(DEV).eval()
+    r, q = leaf(g["in_recons"]), leaf(g["in_q"])
+    d = m.loss_function(r, g["in_input"], q, M_N=g["hp_M_N"], batch_idx=3)
+    d["loss"].backward()
+    for k in ("loss", "Reconstruction_Loss", "KLD"):
+        assert_close(d[k], g["out_" + k], TOL, k)
+    assert_close(r.grad, g["grad_recons"], TOL); assert_close(q.grad, g["grad_q"], TOL, "d loss / d logits")
+
+
+@pytest.mark.parametrize("shape", [(3, 7, 40), (2, 5, 33), (4, 3, 1), (2, 2, 130), (64, 128, 40)])
+def test_gumbel_softmax_own_noise_vs_oracle(models, shape):
+    """The kernel's own Philox uniforms (emitted on request) fed to the oracle: same sample, same gradient; the draw is
+    a pure function of (seed, offset) and lies strictly inside (0, 1)."""
+    import vae_oracle as O
+    from vaekit import functional as F
+    gen = torch.Generator().manual_seed(sum(shape))
+    q0 = 2.0 * torch.randn(*shape, generator=gen)
+    gs = torch.randn(shape[0], shape[1] * shape[2], generator=gen)
+    q = leaf(q0.to(DEV))
+    s, u = F.gumbel_softmax(q, 0.7, 1e-7, rng=(1265, 40), want_uniforms=True)
+    s2, u2 = F.gumbel_softmax(q0.to(DEV), 0.7, 1e-7, rng=(1265, 40), want_uniforms=True)
+    assert torch.equal(u, u2) and torch.equal(s, s2)
+    assert 0.0 < u.min().item() and u.max().item() < 1.0
+    s.view(shape[0], -1).backward(gs.to(DEV))
+    qc = leaf(q0)
+    ref = O.gumbel_softmax(qc, u.cpu(), 0.7)
+    ref.backward(gs)
+    assert_close(s.view(shape[0], -1), ref, TOL, "sample")
+    assert_close(q.grad, qc.grad, TOL, "gradient")
+    rows = F.cat_kl_rows(leaf(q0.to(DEV)))
+    p = torch.softmax(q0.double(), -1)
+    import math
+    want = (p * torch.log(p + 1e-7) - p * math.log(1. / shape[2] + 1e-7)).sum(dim=(1, 2))
+    assert torch.allclose(rows.double().cpu(), want, rtol=1e-5, atol=1e-6 * shape[1])
+
+
+def test_categorical_vae_contract(models):
+    """forward list, annealing of the temperature every anneal_interval batches in training mode only, sample()."""
+    m = models["CategoricalVAE"](3, 8, categorical_dim=10, anneal_interval=2, anneal_rate=0.5, temperature=0.5).to(DEV)
+    x = torch.rand(4, 3, 64, 64, device=DEV)
+    out = m(x)
+    assert len(out) == 3 and out[0].shape == x.shape and out[2].shape == (4, 8, 10)
+    m.temp = 2.0
+    m.train()
+    m.loss_function(*out, M_N=0.005, batch_idx=2)["loss"].backward()
+    assert abs(float(m.temp) - max(2.0 * 2.718281828459045 ** (-1.0), 0.5)) < 1e-6      # annealed: batch_idx % 2 == 0
+    t = float(m.temp)
+    m.loss_function(*m(x), M_N=0.005, batch_idx=3)
+    assert float(m.temp) == t                                                           # not on odd batches
+    m.eval()
+    m.loss_function(*m(x), M_N=0.005, batch_idx=4)
+    assert float(m.temp) == t                                                           # not in eval mode
+    assert m.sample(3, 0).shape == (3, 3, 64, 64)

@@ -232,3 +232,18 @@ def test_next_models():
     for k in ("loss", "Reconstruction_Loss", "KLD", "VAE_TC_Loss"):
         assert_close(d[k], g["out_" + k], TOL, k)
     assert_close(z.grad, g["grad_z"], TOL); assert_close(mu.grad, g["grad_mu"], TOL)
+
+
+def test_cat_vae():
+    """Gumbel-softmax reparameterisation and categorical KL of cat_vae.py."""
+    g = load("catvae")
+    q = leaf(g["in_q"])
+    s = O.gumbel_softmax(q, g["noise_u"], g["hp_temp"])
+    s.backward(g["in_gs"])
+    assert_close(s, g["out_s"], TOL, "s"); assert_close(q.grad, g["grad_s_q"], TOL, "ds/dq")
+    r, q = leaf(g["in_recons"]), leaf(g["in_q"])
+    d = O.cat_vae_loss(r, g["in_input"], q, g["hp_M_N"], alpha=g["hp_alpha"])
+    d["loss"].backward()
+    for k in ("loss", "Reconstruction_Loss", "KLD"):
+        assert_close(d[k], g["out_" + k], TOL, k)
+    assert_close(r.grad, g["grad_recons"], TOL); assert_close(q.grad, g["grad_q"], TOL)
