@@ -170,6 +170,23 @@ def cat_vae_loss(recons: Tensor, input: Tensor, q: Tensor, M_N: float, *, alpha:
     return {"loss": alpha * recons_loss + M_N * kld_loss, "Reconstruction_Loss": recons_loss, "KLD": -kld_loss}
 
 
+def joint_vae_loss(recons: Tensor, input: Tensor, q: Tensor, mu: Tensor, log_var: Tensor, M_N: float, *, alpha: float,
+                   num_iter: int, disc_min: float, disc_max: float, disc_iter: int, disc_gamma: float, cont_min: float,
+                   cont_max: float, cont_iter: int, cont_gamma: float) -> Dict[str, Tensor]:
+    """joint_vae.py:174-222 with the host counter num_iter given (q is [B, C])."""
+    q_p = F.softmax(q, dim=-1)
+    recons_loss = F.mse_loss(recons, input, reduction="mean")
+    disc_curr = min((disc_max - disc_min) * num_iter / float(disc_iter) + disc_min, math.log(q.shape[-1]))
+    eps = 1e-7
+    h1 = q_p * torch.log(q_p + eps)
+    h2 = q_p * math.log(1. / q.shape[-1] + eps)
+    kld_disc = torch.mean(torch.sum(h1 - h2, dim=1), dim=0)
+    cont_curr = min((cont_max - cont_min) * num_iter / float(cont_iter) + cont_min, cont_max)
+    kld_cont = torch.mean(kld_rows(mu, log_var), dim=0)
+    cap = disc_gamma * torch.abs(disc_curr - kld_disc) + cont_gamma * torch.abs(cont_curr - kld_cont)
+    return {"loss": alpha * recons_loss + M_N * cap, "Reconstruction_Loss": recons_loss, "Capacity_Loss": cap}
+
+
 def beta_loss(recons: Tensor, input: Tensor, mu: Tensor, log_var: Tensor, M_N: float, *,
               loss_type: str, beta: float, gamma: float, C_max: float, C_stop_iter: float,
               num_iter: int) -> Dict[str, Tensor]:

@@ -327,9 +327,43 @@ def gen_cat():
          out_KLD=d["KLD"], grad_recons=rl.grad, grad_q=q2.grad)
 
 
+def gen_joint():
+    """JointVAE reparameterize (randn_like / rand_like patched) and two training-mode loss calls
+    (num_iter 1 then 2) of the unmodified reference."""
+    g = torch.Generator().manual_seed(505)
+    kw = dict(latent_num_iter=50, categorical_num_iter=20, latent_max_capacity=25., categorical_max_capacity=25.)
+    m = ref.JointVAE(3, 12, 10, **kw)
+    r, x = images(g, 6)
+    mu, lv = gaussians(g, 6, 12)
+    q = 1.5 * torch.randn(6, 10, generator=g)
+    e, u = torch.randn(6, 12, generator=g), torch.rand(6, 10, generator=g)
+    gz = torch.randn(6, 22, generator=g)
+    mul, lvl, ql = leaf(mu), leaf(lv), leaf(q)
+    orig = torch.rand_like
+    torch.rand_like = lambda t, **k2: u.to(t.dtype)
+    try:
+        with injected_noise(e):
+            z = m.reparameterize(mul, lvl, ql)
+    finally:
+        torch.rand_like = orig
+    z.backward(gz)
+    out = dict(in_recons=r, in_input=x, in_mu=mu, in_log_var=lv, in_q=q, noise_eps=e, noise_u=u, in_gz=gz, hp_M_N=0.005,
+               out_z=z, grad_z_mu=mul.grad, grad_z_log_var=lvl.grad, grad_z_q=ql.grad)
+    m.train()
+    for call in (1, 2):
+        rl, mul, lvl, ql = leaf(r), leaf(mu), leaf(lv), leaf(q)
+        d = m.loss_function(rl, x, ql, mul, lvl, M_N=0.005, batch_idx=7)
+        d["loss"].backward()
+        out.update({"out_loss_%d" % call: d["loss"], "out_Capacity_Loss_%d" % call: d["Capacity_Loss"],
+                    "out_Reconstruction_Loss_%d" % call: d["Reconstruction_Loss"], "grad_recons_%d" % call: rl.grad,
+                    "grad_mu_%d" % call: mul.grad, "grad_log_var_%d" % call: lvl.grad, "grad_q_%d" % call: ql.grad})
+    assert m.num_iter == 3
+    save("jointvae", **out)
+
+
 if __name__ == "__main__":
     torch.set_num_threads(4)
     only = sys.argv[1:]
-    for fn in (gen_vanilla, gen_beta, gen_logcosh, gen_iw, gen_wae, gen_betatc, gen_swae, gen_vq, gen_info, gen_next_models, gen_cat):
+    for fn in (gen_vanilla, gen_beta, gen_logcosh, gen_iw, gen_wae, gen_betatc, gen_swae, gen_vq, gen_info, gen_next_models, gen_cat, gen_joint):
         if not only or fn.__name__[4:] in only:
             fn()

@@ -168,3 +168,36 @@ def test_categorical_vae_contract(models):
     m.loss_function(*m(x), M_N=0.005, batch_idx=4)
     assert float(m.temp) == t                                                           # not in eval mode
     assert m.sample(3, 0).shape == (3, 3, 64, 64)
+
+
+def test_joint_vae_golden(models):
+    """JointVAE on K1 + K8 against the reference's fixture: the Gumbel half of reparameterize with the
+    fixture's uniforms, the Gaussian half through the noise the kernel itself reports, and two training-mode loss calls
+    (the capacity targets move with num_iter)."""
+    from vaekit import functional as F
+    import vae_oracle as O
+    g = load("jointvae", DEV)
+    q = leaf(g["in_q"])
+    s, _ = F.gumbel_softmax(q, 0.5, 1e-7, uniforms=g["noise_u"])
+    s.backward(g["in_gz"][:, 12:])
+    assert_close(s, g["out_z"][:, 12:], TOL, "categorical half of z")
+    assert_close(q.grad, g["grad_z_q"], TOL, "d z / d q")
+    m = models["JointVAE"](3, 12, 10, latent_num_iter=50, categorical_num_iter=20).to(DEV).train()
+    z = m.reparameterize(leaf(g["in_mu"]), leaf(g["in_log_var"]), leaf(g["in_q"]))
+    assert z.shape == (6, 22) and torch.allclose(z[:, 12:].sum(1), torch.ones(6, device=DEV), atol=1e-5)
+    for call in (1, 2):
+        r, mu, lv, q = leaf(g["in_recons"]), leaf(g["in_mu"]), leaf(g["in_log_var"]), leaf(g["in_q"])
+        assert m.num_iter == call
+        d = m.loss_function(r, g["in_input"], q, mu, lv, M_N=g["hp_M_N"], batch_idx=7)
+        d["loss"].backward()
+        for k in ("loss", "Capacity_Loss", "Reconstruction_Loss"):
+            assert_close(d[k], g["out_%s_%d" % (k, call)], TOL, "%s call %d" % (k, call))
+        assert_close(q.grad, g["grad_q_%d" % call], TOL); assert_close(mu.grad, g["grad_mu_%d" % call], TOL)
+        assert_close(lv.grad, g["grad_log_var_%d" % call], TOL); assert_close(r.grad, g["grad_recons_%d" % call], TOL)
+    m.eval()
+    m.loss_function(leaf(g["in_recons"]), g["in_input"], leaf(g["in_q"]), leaf(g["in_mu"]), leaf(g["in_log_var"]),
+                    M_N=0.005, batch_idx=7)
+    assert m.num_iter == 3                                      # eval mode leaves the counter alone
+    out = m(torch.rand(4, 3, 64, 64, device=DEV))
+    assert len(out) == 5 and out[2].shape == (4, 10)
+    assert m.sample(3, 0).shape == (3, 3, 64, 64)

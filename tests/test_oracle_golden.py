@@ -247,3 +247,22 @@ def test_cat_vae():
     for k in ("loss", "Reconstruction_Loss", "KLD"):
         assert_close(d[k], g["out_" + k], TOL, k)
     assert_close(r.grad, g["grad_recons"], TOL); assert_close(q.grad, g["grad_q"], TOL)
+
+
+def test_joint_vae():
+    """JointVAE reparameterize (Gaussian | Gumbel-softmax) and capacity loss, two training calls."""
+    g = load("jointvae")
+    mu, lv, q = leaf(g["in_mu"]), leaf(g["in_log_var"]), leaf(g["in_q"])
+    z = torch.cat([O.reparameterize(mu, lv, g["noise_eps"]), O.gumbel_softmax(q.view(6, 1, 10), g["noise_u"].view(6, 1, 10), 0.5)], dim=1)
+    z.backward(g["in_gz"])
+    assert_close(z, g["out_z"], TOL); assert_close(mu.grad, g["grad_z_mu"], TOL); assert_close(q.grad, g["grad_z_q"], TOL)
+    kw = dict(alpha=30., disc_min=0., disc_max=25., disc_iter=20, disc_gamma=30., cont_min=0., cont_max=25., cont_iter=50,
+              cont_gamma=30.)
+    for call in (1, 2):
+        r, mu, lv, q = leaf(g["in_recons"]), leaf(g["in_mu"]), leaf(g["in_log_var"]), leaf(g["in_q"])
+        d = O.joint_vae_loss(r, g["in_input"], q, mu, lv, g["hp_M_N"], num_iter=call, **kw)
+        d["loss"].backward()
+        for k in ("loss", "Capacity_Loss", "Reconstruction_Loss"):
+            assert_close(d[k], g["out_%s_%d" % (k, call)], TOL, k)
+        assert_close(q.grad, g["grad_q_%d" % call], TOL); assert_close(mu.grad, g["grad_mu_%d" % call], TOL)
+        assert_close(lv.grad, g["grad_log_var_%d" % call], TOL); assert_close(r.grad, g["grad_recons_%d" % call], TOL)
