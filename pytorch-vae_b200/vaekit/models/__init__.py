@@ -1,6 +1,6 @@
 """Model registry with the reference's keys (models/__init__.py:65-91) for the classes on the
-hot path, plus the SURVEY 8(f) "next" rows built so far: InfoVAE (rank 1) and the Gaussian-KL models ConditionalVAE, DIPVAE
-and FactorVAE (rank 2), CategoricalVAE and JointVAE (rank 4, Gumbel-softmax kernels); the remaining reference variants are out of scope."""
+hot path, plus the SURVEY 8(f) "next" rows built so far: InfoVAE (rank 1) and the Gaussian-KL models ConditionalVAE, DIPVAE,
+FactorVAE and TwoStageVAE (rank 2), CategoricalVAE and JointVAE (rank 4, Gumbel-softmax kernels); the remaining reference variants are out of scope."""
 from .base import BaseVAE
 from .vanilla_vae import VanillaVAE
 from .beta_vae import BetaVAE
@@ -17,6 +17,7 @@ from .dip_vae import DIPVAE
 from .fvae import FactorVAE
 from .cat_vae import CategoricalVAE
 from .joint_vae import JointVAE
+from .twostage_vae import TwoStageVAE
 
 VAE = VanillaVAE
 GaussianVAE = VanillaVAE
@@ -39,4 +40,5 @@ vae_models = {
     'FactorVAE': FactorVAE,
     'CategoricalVAE': CategoricalVAE,
     'JointVAE': JointVAE,
+    'TwoStageVAE': TwoStageVAE,
 }

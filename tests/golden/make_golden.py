@@ -285,6 +285,14 @@ def gen_next_models():
     save("dipvae", in_recons=r, in_input=x, in_mu=mu, in_log_var=lv, hp_M_N=0.005, out_loss=d["loss"],
          out_Reconstruction_Loss=d["Reconstruction_Loss"], out_KLD=d["KLD"], out_DIP_Loss=d["DIP_Loss"],
          grad_recons=rl.grad, grad_mu=mul.grad, grad_log_var=lvl.grad)
+    # TwoStageVAE (first-stage loss)
+    m = ref.TwoStageVAE(3, 16)
+    rl, mul, lvl = leaf(r), leaf(mu), leaf(lv)
+    d = m.loss_function(rl, x, mul, lvl, M_N=0.005)
+    d["loss"].backward()
+    save("twostage", in_recons=r, in_input=x, in_mu=mu, in_log_var=lv, hp_M_N=0.005, out_loss=d["loss"],
+         out_Reconstruction_Loss=d["Reconstruction_Loss"], out_KLD=d["KLD"], grad_recons=rl.grad, grad_mu=mul.grad,
+         grad_log_var=lvl.grad)
     # FactorVAE, optimizer_idx = 0; the discriminator is replaced by a fixed linear map so the fixture stays small
     m = ref.FactorVAE(3, 16, gamma=40.)
     W = 0.3 * torch.randn(16, 2, generator=g)

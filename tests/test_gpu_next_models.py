@@ -201,3 +201,19 @@ def test_joint_vae_golden(models):
     out = m(torch.rand(4, 3, 64, 64, device=DEV))
     assert len(out) == 5 and out[2].shape == (4, 10)
     assert m.sample(3, 0).shape == (3, 3, 64, 64)
+
+
+def test_twostage_vae(models):
+    g = load("twostage", DEV)
+    m = models["TwoStageVAE"](3, 16).to(DEV)
+    r, mu, lv = leaf(g["in_recons"]), leaf(g["in_mu"]), leaf(g["in_log_var"])
+    d = m.loss_function(r, g["in_input"], mu, lv, M_N=g["hp_M_N"])
+    d["loss"].backward()
+    for k in ("loss", "Reconstruction_Loss", "KLD"):
+        assert_close(d[k], g["out_" + k], TOL, k)
+    assert d["KLD"].requires_grad
+    assert_close(r.grad, g["grad_recons"], TOL); assert_close(mu.grad, g["grad_mu"], TOL)
+    assert_close(lv.grad, g["grad_log_var"], TOL)
+    out = m(torch.rand(4, 3, 64, 64, device=DEV))
+    m.loss_function(*out, M_N=0.005)["loss"].backward()
+    assert m.encoder2[0][0].weight.grad is None                 # the second stage is never called, as in the reference

@@ -266,3 +266,13 @@ def test_joint_vae():
             assert_close(d[k], g["out_%s_%d" % (k, call)], TOL, k)
         assert_close(q.grad, g["grad_q_%d" % call], TOL); assert_close(mu.grad, g["grad_mu_%d" % call], TOL)
         assert_close(lv.grad, g["grad_log_var_%d" % call], TOL); assert_close(r.grad, g["grad_recons_%d" % call], TOL)
+
+
+def test_twostage_vae():
+    g = load("twostage")
+    r, mu, lv = leaf(g["in_recons"]), leaf(g["in_mu"]), leaf(g["in_log_var"])
+    d = O.cvae_loss(r, g["in_input"], mu, lv, g["hp_M_N"])          # twostage_vae.py:141-167 is the same undetached ELBO
+    d["loss"].backward()
+    for k in ("loss", "Reconstruction_Loss", "KLD"):
+        assert_close(d[k], g["out_" + k], TOL, k)
+    assert_close(r.grad, g["grad_recons"], TOL); assert_close(mu.grad, g["grad_mu"], TOL); assert_close(lv.grad, g["grad_log_var"], TOL)
