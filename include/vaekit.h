@@ -323,6 +323,29 @@ int vk_cat_kl_rows_fwd(const float* q, int64_t B, int64_t L, int64_t C, float ep
 int vk_cat_kl_rows_bwd(const float* q, const float* g_rows, int64_t B, int64_t L, int64_t C, float eps, float* g_q,
                        void* stream);
 
+/* ---------------------------------------------------------------------------
+ * K9  VampPrior term   (reference: models/vampvae.py:124-160) -- SURVEY 8(f) rank 4
+ *
+ * z [B, D] samples; (pmu, plv) [K, D] the encodings of the K pseudo-inputs; (mu, log_var) [B, D] the posterior.
+ *   vk_gauss_logq_rows_fwd: rows_out[i] = sum_d -0.5 (lv_id + (z_id - mu_id)^2) / exp(lv_id)   (vampvae.py:136-138; the
+ *     batch mean is E_log_q_z).  _bwd: (g_z, g_mu, g_lv) from the per-row upstream gradients g_rows [B].
+ *   vk_vamp_prior_fwd: t_out[i, k] = sum_d -0.5 (plv_kd + (z_id - pmu_kd)^2) / exp(plv_kd) - log K, lse_out[i] =
+ *     logsumexp_k t[i, k]   (vampvae.py:153-158; the batch mean is E_log_p_z).  The [B, K, D] broadcast of the reference
+ *     is never materialised.
+ *   vk_vamp_prior_bwd: g_z [B, D], g_pmu [K, D], g_plv [K, D] from g_rows [B] (gradient w.r.t. lse_out), with the
+ *     mixture weights recomputed from (t, lse).  Fixed summation order, no atomics.
+ * K, D <= 8192.
+ * -------------------------------------------------------------------------*/
+int vk_gauss_logq_rows_fwd(const float* z, const float* mu, const float* log_var, int64_t B, int64_t D, float* rows_out,
+                           void* stream);
+int vk_gauss_logq_rows_bwd(const float* z, const float* mu, const float* log_var, const float* g_rows, int64_t B, int64_t D,
+                           float* g_z, float* g_mu, float* g_lv, void* stream);
+int vk_vamp_prior_fwd(const float* z, const float* pmu, const float* plv, int64_t B, int64_t K, int64_t D, float* t_out,
+                      float* lse_out, void* stream);
+int vk_vamp_prior_bwd(const float* z, const float* pmu, const float* plv, const float* t, const float* lse,
+                      const float* g_rows, int64_t B, int64_t K, int64_t D, float* g_z, float* g_pmu, float* g_plv,
+                      void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -187,6 +187,72 @@ def joint_vae_loss(recons: Tensor, input: Tensor, q: Tensor, mu: Tensor, log_var
     return {"loss": alpha * recons_loss + M_N * cap, "Reconstruction_Loss": recons_loss, "Capacity_Loss": cap}
 
 
+def vamp_logq_rows(z: Tensor, mu: Tensor, log_var: Tensor) -> Tensor:
+    """vampvae.py:136-138 before the batch mean: [B]."""
+    return torch.sum(-0.5 * (log_var + (z - mu) ** 2) / log_var.exp(), dim=1)
+
+
+def vamp_prior_rows(z: Tensor, prior_mu: Tensor, prior_log_var: Tensor) -> Tensor:
+    """vampvae.py:149-158 before the batch mean: logsumexp over the K components of the [B, K, D] broadcast, [B]."""
+    K = prior_mu.shape[0]
+    t = torch.sum(-0.5 * (prior_log_var.unsqueeze(0) + (z.unsqueeze(1) - prior_mu.unsqueeze(0)) ** 2)
+                  / prior_log_var.unsqueeze(0).exp(), dim=2) - torch.log(torch.tensor(K).float()).to(z.dtype)
+    return torch.logsumexp(t, dim=1)
+
+
+def vamp_loss(recons: Tensor, input: Tensor, mu: Tensor, log_var: Tensor, z: Tensor, prior_mu: Tensor,
+              prior_log_var: Tensor, M_N: float) -> Dict[str, Tensor]:
+    """vampvae.py:124-166 with the pseudo-input encodings (prior_mu, prior_log_var) [K, D] given."""
+    recons_loss = F.mse_loss(recons, input)
+    kld_loss = -(torch.mean(vamp_prior_rows(z, prior_mu, prior_log_var), dim=0)
+                 - torch.mean(vamp_logq_rows(z, mu, log_var), dim=0))
+    return {"loss": recons_loss + M_N * kld_loss, "Reconstruction_Loss": recons_loss, "KLD": -kld_loss}
+
+
+def dfc_loss(recons: Tensor, input: Tensor, recons_features, input_features, mu: Tensor, log_var: Tensor, M_N: float, *,
+             alpha: float, beta: float) -> Dict[str, Tensor]:
+    """dfcvae.py:164-190 with the extracted feature maps given."""
+    recons_loss = F.mse_loss(recons, input)
+    feature_loss = 0.0
+    for r, i in zip(recons_features, input_features):
+        feature_loss = feature_loss + F.mse_loss(r, i)
+    kld_loss = torch.mean(kld_rows(mu, log_var), dim=0)
+    return {"loss": beta * (recons_loss + feature_loss) + alpha * M_N * kld_loss, "Reconstruction_Loss": beta * recons_loss,
+            "KLD": -kld_loss, "feature_loss": beta * feature_loss}
+
+
+def mssim(img1: Tensor, img2: Tensor, *, in_channels: int = 3, window_size: int = 11, normalize: bool = True) -> Tensor:
+    """mssim_vae.py:182-283 (size_average = True): 1 - MS-SSIM over five dyadic levels, with the reference's window
+    (exp of a POSITIVE exponent, mssim_vae.py:206-209) and final product (mssim_vae.py:282)."""
+    half = window_size // 2
+    taps = torch.tensor([math.exp((x - half) ** 2 / (2 * 1.5 ** 2)) for x in range(window_size)])
+    taps = (taps / taps.sum()).unsqueeze(1)
+    window = taps.mm(taps.t()).float()[None, None].expand(in_channels, 1, window_size, window_size).contiguous()
+    window = window.to(img1.device, img1.dtype)
+    weights = torch.tensor([0.0448, 0.2856, 0.3001, 0.2363, 0.1333], dtype=img1.dtype, device=img1.device)
+    sims, css = [], []
+    for _ in range(5):
+        conv = lambda t: F.conv2d(t, window, padding=half, groups=in_channels)
+        m1, m2 = conv(img1), conv(img2)
+        s1, s2, s12 = conv(img1 * img1) - m1 * m1, conv(img2 * img2) - m2 * m2, conv(img1 * img2) - m1 * m2
+        C1, C2 = 0.01 ** 2, 0.03 ** 2
+        v1, v2 = 2.0 * s12 + C2, s1 + s2 + C2
+        css.append(torch.mean(v1 / v2))
+        sims.append((((2 * m1 * m2 + C1) * v1) / ((m1 * m1 + m2 * m2 + C1) * v2)).mean())
+        img1, img2 = F.avg_pool2d(img1, (2, 2)), F.avg_pool2d(img2, (2, 2))
+    sims, css = torch.stack(sims), torch.stack(css)
+    if normalize:
+        sims, css = (sims + 1) / 2, (css + 1) / 2
+    return 1 - torch.prod((css ** weights)[:-1] * (sims ** weights)[-1])
+
+
+def mssim_vae_loss(recons: Tensor, input: Tensor, mu: Tensor, log_var: Tensor, M_N: float) -> Dict[str, Tensor]:
+    """mssim_vae.py:131-153."""
+    recons_loss = mssim(recons, input, in_channels=recons.shape[1])
+    kld_loss = torch.mean(kld_rows(mu, log_var), dim=0)
+    return {"loss": recons_loss + M_N * kld_loss, "Reconstruction_Loss": recons_loss, "KLD": -kld_loss}
+
+
 def beta_loss(recons: Tensor, input: Tensor, mu: Tensor, log_var: Tensor, M_N: float, *,
               loss_type: str, beta: float, gamma: float, C_max: float, C_stop_iter: float,
               num_iter: int) -> Dict[str, Tensor]:

@@ -158,8 +158,16 @@ struct LossFuse {
   float p;
 };
 
+// kScatterMinBlocks CTAs per SM: ncu (profiles/ncu_swae_r01v_summary.txt) shows the pass latency-bound (issue slots 57 %
+// busy, long-scoreboard stalls) at 3 resident CTAs -- the 70 registers per thread were the occupancy limit.
+#ifndef VK_SCATTER_MINB
+#define VK_SCATTER_MINB 4
+#endif
+#ifndef VK_SCATTER_MINB_KV
+#define VK_SCATTER_MINB_KV 4
+#endif
 template <int PASS, bool PAYLOAD, bool FULL, bool FUSE>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, (PAYLOAD || FUSE) ? VK_SCATTER_MINB_KV : VK_SCATTER_MINB)
 scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in, int64_t n,
                const uint32_t* __restrict__ offsets, uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
                int chunk0, int chunks, LossFuse fuse) {

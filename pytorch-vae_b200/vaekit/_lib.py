@@ -58,6 +58,10 @@ _SIGNATURES = {
     "vk_gumbel_softmax_bwd": ([_p, _p, _i64, _i64, _f, _p, _p], _i),
     "vk_cat_kl_rows_fwd": ([_p, _i64, _i64, _i64, _f, _p, _p], _i),
     "vk_cat_kl_rows_bwd": ([_p, _p, _i64, _i64, _i64, _f, _p, _p], _i),
+    "vk_gauss_logq_rows_fwd": ([_p, _p, _p, _i64, _i64, _p, _p], _i),
+    "vk_gauss_logq_rows_bwd": ([_p, _p, _p, _p, _i64, _i64, _p, _p, _p, _p], _i),
+    "vk_vamp_prior_fwd": ([_p, _p, _p, _i64, _i64, _i64, _p, _p, _p], _i),
+    "vk_vamp_prior_bwd": ([_p, _p, _p, _p, _p, _p, _i64, _i64, _i64, _p, _p, _p, _p], _i),
     "vk_iw_bound_bwd": ([_p, _p, _p, _p, _i64, _i64, _i64, _i64, _f, _p, _p, _p, _p, _p, _p, _p], _i),
 }
 

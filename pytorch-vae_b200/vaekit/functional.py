@@ -801,3 +801,73 @@ def cat_kl_rows(q, eps=1e-7):
     """Per-sample KL(softmax(q) || uniform) of cat_vae.py:156-169 for logits [B, latent_dim, C]: [B] rows whose batch mean
     is the reference's kld_loss."""
     return _CatKlRows.apply(q, float(eps))
+
+
+# ---------------------------------------------------------------------------
+# K9: VampPrior term (SURVEY 8(f) rank 4)
+# ---------------------------------------------------------------------------
+class _GaussLogqRows(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, z, mu, log_var):
+        for t, n in ((z, "z"), (mu, "mu"), (log_var, "log_var")):
+            L.require(t, n, dims=(2,))
+        if z.shape != mu.shape or z.shape != log_var.shape or z.numel() == 0:
+            raise RuntimeError("vaekit: z / mu / log_var must share a non-empty [B, D] shape")
+        zc, mc, vc = z.contiguous(), mu.contiguous(), log_var.contiguous()
+        B, D = zc.shape
+        rows = torch.empty(B, dtype=torch.float32, device=zc.device)
+        with L.on(zc.device):
+            L.call("gauss_logq_rows_fwd", L.ptr(zc), L.ptr(mc), L.ptr(vc), B, D, L.ptr(rows), L.stream_ptr())
+        ctx.save_for_backward(zc, mc, vc)
+        return rows
+
+    @staticmethod
+    def backward(ctx, g_rows):
+        zc, mc, vc = ctx.saved_tensors
+        B, D = zc.shape
+        g_z, g_mu, g_lv = torch.empty_like(zc), torch.empty_like(zc), torch.empty_like(zc)
+        with L.on(zc.device):
+            L.call("gauss_logq_rows_bwd", L.ptr(zc), L.ptr(mc), L.ptr(vc), L.ptr(g_rows.contiguous()), B, D, L.ptr(g_z),
+                   L.ptr(g_mu), L.ptr(g_lv), L.stream_ptr())
+        return g_z, g_mu, g_lv
+
+
+def gauss_logq_rows(z, mu, log_var):
+    """vampvae.py:136-138 per sample: sum_d -0.5 (log_var + (z - mu)^2) / exp(log_var), [B]; its batch mean is E_log_q_z."""
+    return _GaussLogqRows.apply(z, mu, log_var)
+
+
+class _VampPrior(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, z, prior_mu, prior_log_var):
+        L.require(z, "z", dims=(2,))
+        L.require(prior_mu, "prior_mu", dims=(2,))
+        L.require(prior_log_var, "prior_log_var", dims=(2,))
+        if prior_mu.shape != prior_log_var.shape or prior_mu.shape[1] != z.shape[1] or z.numel() == 0 or prior_mu.numel() == 0:
+            raise RuntimeError("vaekit: vamp prior needs z [B, D] and prior_mu / prior_log_var [K, D]")
+        zc, mc, vc = z.contiguous(), prior_mu.contiguous(), prior_log_var.contiguous()
+        B, D = zc.shape
+        K = mc.shape[0]
+        t = torch.empty(B, K, dtype=torch.float32, device=zc.device)
+        lse = torch.empty(B, dtype=torch.float32, device=zc.device)
+        with L.on(zc.device):
+            L.call("vamp_prior_fwd", L.ptr(zc), L.ptr(mc), L.ptr(vc), B, K, D, L.ptr(t), L.ptr(lse), L.stream_ptr())
+        ctx.save_for_backward(zc, mc, vc, t, lse)
+        return lse
+
+    @staticmethod
+    def backward(ctx, g_rows):
+        zc, mc, vc, t, lse = ctx.saved_tensors
+        B, D = zc.shape
+        K = mc.shape[0]
+        g_z, g_m, g_v = torch.empty_like(zc), torch.empty_like(mc), torch.empty_like(vc)
+        with L.on(zc.device):
+            L.call("vamp_prior_bwd", L.ptr(zc), L.ptr(mc), L.ptr(vc), L.ptr(t), L.ptr(lse), L.ptr(g_rows.contiguous()), B, K, D,
+                   L.ptr(g_z), L.ptr(g_m), L.ptr(g_v), L.stream_ptr())
+        return g_z, g_m, g_v
+
+
+def vamp_prior_rows(z, prior_mu, prior_log_var):
+    """vampvae.py:149-158 per sample: logsumexp over the K pseudo-input components of the (reference's un-normalised)
+    Gaussian log density minus log K, [B]; its batch mean is E_log_p_z.  The [B, K, D] broadcast is not materialised."""
+    return _VampPrior.apply(z, prior_mu, prior_log_var)

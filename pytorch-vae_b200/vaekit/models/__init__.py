@@ -1,6 +1,7 @@
 """Model registry with the reference's keys (models/__init__.py:65-91) for the classes on the
 hot path, plus the SURVEY 8(f) "next" rows built so far: InfoVAE (rank 1) and the Gaussian-KL models ConditionalVAE, DIPVAE,
-FactorVAE and TwoStageVAE (rank 2), CategoricalVAE and JointVAE (rank 4, Gumbel-softmax kernels); the remaining reference variants are out of scope."""
+FactorVAE, TwoStageVAE, MSSIMVAE and DFCVAE (rank 2), CategoricalVAE and JointVAE (rank 4, Gumbel-softmax kernels) and
+VampVAE (rank 4, VampPrior kernels); the remaining reference variants (GammaVAE, HVAE, LVAE) are out of scope."""
 from .base import BaseVAE
 from .vanilla_vae import VanillaVAE
 from .beta_vae import BetaVAE
@@ -18,6 +19,9 @@ from .fvae import FactorVAE
 from .cat_vae import CategoricalVAE
 from .joint_vae import JointVAE
 from .twostage_vae import TwoStageVAE
+from .mssim_vae import MSSIMVAE
+from .dfcvae import DFCVAE
+from .vampvae import VampVAE
 
 VAE = VanillaVAE
 GaussianVAE = VanillaVAE
@@ -41,4 +45,7 @@ vae_models = {
     'CategoricalVAE': CategoricalVAE,
     'JointVAE': JointVAE,
     'TwoStageVAE': TwoStageVAE,
+    'MSSIMVAE': MSSIMVAE,
+    'DFCVAE': DFCVAE,
+    'VampVAE': VampVAE,
 }

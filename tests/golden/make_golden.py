@@ -369,9 +369,64 @@ def gen_joint():
     save("jointvae", **out)
 
 
+def gen_last_models():
+    """SURVEY 8(f) rank 2 / rank 4, last three: MSSIMVAE, DFCVAE and VampVAE loss functions of the unmodified reference."""
+    g = torch.Generator().manual_seed(909)
+    # MSSIMVAE: 32x32 so that the five dyadic levels (32 .. 2) and the trailing pool exist
+    r, x = images(g, 4, hw=32)
+    mu, lv = gaussians(g, 4, 16)
+    m = ref.MSSIMVAE(3, 16)
+    rl, mul, lvl = leaf(r), leaf(mu), leaf(lv)
+    d = m.loss_function(rl, x, mul, lvl, M_N=0.005)
+    d["loss"].backward()
+    save("mssimvae", in_recons=r, in_input=x, in_mu=mu, in_log_var=lv, hp_M_N=0.005, out_loss=d["loss"],
+         out_Reconstruction_Loss=d["Reconstruction_Loss"], out_KLD=d["KLD"], grad_recons=rl.grad, grad_mu=mul.grad,
+         grad_log_var=lvl.grad)
+    # DFCVAE: the constructor downloads VGG weights, and loss_function only reads alpha / beta -> bare instance
+    m = ref.DFCVAE.__new__(ref.DFCVAE)
+    torch.nn.Module.__init__(m)
+    m.alpha, m.beta = 1.0, 0.5
+    r, x = images(g, 5)
+    mu, lv = gaussians(g, 5, 16)
+    shapes = [(5, 8, 8, 8), (5, 12, 4, 4), (5, 16, 2, 2), (5, 16, 1, 1)]
+    fr = [torch.relu(torch.randn(*sh, generator=g)) for sh in shapes]
+    fi = [torch.relu(torch.randn(*sh, generator=g)) for sh in shapes]
+    rl, mul, lvl, frl = leaf(r), leaf(mu), leaf(lv), [leaf(t) for t in fr]
+    d = m.loss_function(rl, x, frl, fi, mul, lvl, M_N=0.005)
+    d["loss"].backward()
+    feats = {}
+    for n, (a, b, al) in enumerate(zip(fr, fi, frl)):
+        feats["in_fr%d" % n], feats["in_fi%d" % n], feats["grad_fr%d" % n] = a, b, al.grad
+    save("dfcvae", in_recons=r, in_input=x, in_mu=mu, in_log_var=lv, hp_M_N=0.005, hp_alpha=1.0, hp_beta=0.5,
+         out_loss=d["loss"], out_Reconstruction_Loss=d["Reconstruction_Loss"], out_KLD=d["KLD"],
+         out_feature_loss=d["feature_loss"], grad_recons=rl.grad, grad_mu=mul.grad, grad_log_var=lvl.grad, **feats)
+    # VampVAE: the pseudo-input encodings are injected (encode patched on the instance) so the fixture carries the
+    # [K, D] prior and its gradients; Tensor.cuda is mapped to Tensor.to for this CPU run (vampvae.py:145).
+    K, D, B = 10, 16, 7
+    m = ref.VampVAE(3, D, num_components=K)
+    r, x = images(g, B)
+    mu, lv = gaussians(g, B, D)
+    pmu, plv = gaussians(g, K, D)
+    z = mu + torch.exp(0.5 * lv) * torch.randn(B, D, generator=g)
+    rl, mul, lvl, zl, pml, pvl = leaf(r), leaf(mu), leaf(lv), leaf(z), leaf(pmu), leaf(plv)
+    m.encode = lambda t: [pml, pvl]
+    orig = torch.Tensor.cuda
+    torch.Tensor.cuda = lambda self, device=None, **kw: self.to(device)
+    try:
+        d = m.loss_function(rl, x, mul, lvl, zl, M_N=0.005)
+    finally:
+        torch.Tensor.cuda = orig
+    d["loss"].backward()
+    save("vampvae", in_recons=r, in_input=x, in_mu=mu, in_log_var=lv, in_z=z, in_prior_mu=pmu, in_prior_log_var=plv,
+         hp_M_N=0.005, out_loss=d["loss"], out_Reconstruction_Loss=d["Reconstruction_Loss"], out_KLD=d["KLD"],
+         grad_recons=rl.grad, grad_mu=mul.grad, grad_log_var=lvl.grad, grad_z=zl.grad, grad_prior_mu=pml.grad,
+         grad_prior_log_var=pvl.grad)
+
+
 if __name__ == "__main__":
     torch.set_num_threads(4)
     only = sys.argv[1:]
-    for fn in (gen_vanilla, gen_beta, gen_logcosh, gen_iw, gen_wae, gen_betatc, gen_swae, gen_vq, gen_info, gen_next_models, gen_cat, gen_joint):
+    for fn in (gen_vanilla, gen_beta, gen_logcosh, gen_iw, gen_wae, gen_betatc, gen_swae, gen_vq, gen_info, gen_next_models, gen_cat, gen_joint,
+               gen_last_models):
         if not only or fn.__name__[4:] in only:
             fn()

@@ -217,3 +217,113 @@ def test_twostage_vae(models):
     out = m(torch.rand(4, 3, 64, 64, device=DEV))
     m.loss_function(*out, M_N=0.005)["loss"].backward()
     assert m.encoder2[0][0].weight.grad is None                 # the second stage is never called, as in the reference
+
+
+def test_mssim_vae(models):
+    """MSSIMVAE.loss_function (K1 rows + the torch MS-SSIM pyramid) against the reference fixture."""
+    g = load("mssimvae", DEV)
+    m = models["MSSIMVAE"](3, 16).to(DEV)
+    r, mu, lv = leaf(g["in_recons"]), leaf(g["in_mu"]), leaf(g["in_log_var"])
+    tf32 = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False                          # the fixture is an fp32 CPU run of the reference
+    try:
+        d = m.loss_function(r, g["in_input"], mu, lv, M_N=g["hp_M_N"])
+        d["loss"].backward()
+    finally:
+        torch.backends.cudnn.allow_tf32 = tf32
+    assert_close(d["KLD"], g["out_KLD"], TOL, "KLD")
+    for k in ("loss", "Reconstruction_Loss"):                        # torch / cuDNN depthwise convs, not a vaekit kernel
+        assert_close(d[k], g["out_" + k], 5e-5, k)
+    assert d["KLD"].requires_grad
+    assert_close(r.grad, g["grad_recons"], 5e-5, "recons")
+    assert_close(mu.grad, g["grad_mu"], TOL); assert_close(lv.grad, g["grad_log_var"], TOL)
+    out = m(torch.rand(4, 3, 64, 64, device=DEV))
+    assert len(out) == 4
+    m.loss_function(*out, M_N=0.005)["loss"].backward()
+    assert m.fc_mu.weight.grad is not None and m.sample(3, 0).shape == (3, 3, 64, 64)
+
+
+def test_dfc_vae(models):
+    """DFCVAE.loss_function (pixel + four feature-map K2 reductions, K1 rows) against the reference
+    fixture, and the forward contract with a stand-in extractor (the VGG weights are a download in the reference)."""
+    g = load("dfcvae", DEV)
+    feats = torch.nn.Sequential(*[torch.nn.Conv2d(3, 3, 3, padding=1) if i % 3 == 0 else torch.nn.ReLU() for i in range(44)])
+    net = torch.nn.Module()
+    net.features = feats
+    m = models["DFCVAE"](3, 16, alpha=g["hp_alpha"], beta=g["hp_beta"], feature_network=net).to(DEV)
+    r, mu, lv = leaf(g["in_recons"]), leaf(g["in_mu"]), leaf(g["in_log_var"])
+    fr = [leaf(g["in_fr%d" % n]) for n in range(4)]
+    fi = [g["in_fi%d" % n] for n in range(4)]
+    d = m.loss_function(r, g["in_input"], fr, fi, mu, lv, M_N=g["hp_M_N"])
+    d["loss"].backward()
+    for k in ("loss", "Reconstruction_Loss", "KLD", "feature_loss"):
+        assert_close(d[k], g["out_" + k], TOL, k)
+    assert_close(r.grad, g["grad_recons"], TOL); assert_close(mu.grad, g["grad_mu"], TOL)
+    assert_close(lv.grad, g["grad_log_var"], TOL)
+    for n in range(4):
+        assert_close(fr[n].grad, g["grad_fr%d" % n], TOL, "feature %d" % n)
+    out = m(torch.rand(4, 3, 64, 64, device=DEV))
+    assert len(out) == 6 and len(out[2]) == 4 and len(out[3]) == 4
+    m.loss_function(*out, M_N=0.005)["loss"].backward()
+    assert m.fc_mu.weight.grad is not None and all(p.grad is None for p in m.feature_network.parameters())
+
+
+def test_vamp_vae_golden(models):
+    """VampVAE.loss_function on vk_gauss_logq_rows_* / vk_vamp_prior_* / K2 against the reference
+    fixture (pseudo-input encodings injected), forward and backward into all six inputs."""
+    g = load("vampvae", DEV)
+    m = models["VampVAE"](3, 16, num_components=10).to(DEV)
+    r, mu, lv, z = leaf(g["in_recons"]), leaf(g["in_mu"]), leaf(g["in_log_var"]), leaf(g["in_z"])
+    pm, pv = leaf(g["in_prior_mu"]), leaf(g["in_prior_log_var"])
+    m.prior_components = lambda inp: [pm, pv]
+    d = m.loss_function(r, g["in_input"], mu, lv, z, M_N=g["hp_M_N"])
+    d["loss"].backward()
+    for k in ("loss", "Reconstruction_Loss", "KLD"):
+        assert_close(d[k], g["out_" + k], TOL, k)
+    for t, n in ((r, "recons"), (mu, "mu"), (lv, "log_var"), (z, "z"), (pm, "prior_mu"), (pv, "prior_log_var")):
+        assert_close(t.grad, g["grad_" + n], TOL, n)
+    # full model: gradients reach the pseudo-input embedding through the encoder
+    m2 = models["VampVAE"](3, 16, num_components=10).to(DEV)
+    out = m2(torch.rand(4, 3, 64, 64, device=DEV))
+    assert len(out) == 5 and out[4].shape == (4, 16)
+    d = m2.loss_function(*out, M_N=0.005)
+    assert set(d) == {"loss", "Reconstruction_Loss", "KLD"}
+    d["loss"].backward()
+    assert m2.embed_pseudo[0].weight.grad is not None and torch.isfinite(m2.embed_pseudo[0].weight.grad).all()
+
+
+@pytest.mark.parametrize("B,K,D", [(7, 10, 16), (144, 50, 128), (64, 500, 128), (5, 1, 3), (33, 37, 70), (300, 3, 300)])
+def test_vamp_prior_kernels_vs_oracle(models, B, K, D):
+    """K9 kernels against the float64 oracle (vampvae.py:136-158) on shapes around the shipped config (B 64 / 144, K 50 /
+    500, D 128) and ragged ones; values and all gradients, plus run-to-run bit reproducibility (no atomics)."""
+    import vae_oracle as O
+    from vaekit import functional as F
+    gen = torch.Generator().manual_seed(B * 1000 + K * 10 + D)
+    z, mu = torch.randn(B, D, generator=gen), torch.randn(B, D, generator=gen)
+    lv = 0.5 * torch.randn(B, D, generator=gen) - 1.0
+    pm, pv = torch.randn(K, D, generator=gen), 0.5 * torch.randn(K, D, generator=gen) - 0.5
+    gq, gp = torch.randn(B, generator=gen), torch.randn(B, generator=gen)
+    dev = [leaf(t.to(DEV)) for t in (z, mu, lv, pm, pv)]
+    ref = [leaf(t.double()) for t in (z, mu, lv, pm, pv)]
+    lq = F.gauss_logq_rows(dev[0], dev[1], dev[2])
+    lp = F.vamp_prior_rows(dev[0], dev[3], dev[4])
+    (lq * gq.to(DEV)).sum().backward(retain_graph=True)
+    gz_q = dev[0].grad.clone(); dev[0].grad = None
+    (lp * gp.to(DEV)).sum().backward(retain_graph=True)
+    lq_o = O.vamp_logq_rows(ref[0], ref[1], ref[2])
+    lp_o = O.vamp_prior_rows(ref[0], ref[3], ref[4])
+    (lq_o * gq.double()).sum().backward()
+    gz_q_o = ref[0].grad.clone(); ref[0].grad = None
+    (lp_o * gp.double()).sum().backward()
+    tol = 2e-5
+    assert_close(lq, lq_o, tol, "log q rows"); assert_close(lp, lp_o, tol, "vamp prior rows")
+    assert_close(gz_q, gz_q_o, tol, "d logq / d z")
+    for a, b, n in zip(dev, ref, ("z", "mu", "log_var", "prior_mu", "prior_log_var")):
+        assert_close(a.grad, b.grad, tol, "grad " + n)
+    first = [t.grad.clone() for t in dev]
+    for t in dev:
+        t.grad = None
+    (lp * gp.to(DEV)).sum().backward()
+    assert torch.equal(dev[0].grad, first[0]) and torch.equal(dev[3].grad, first[3]) and torch.equal(dev[4].grad, first[4])
+    with pytest.raises(RuntimeError):
+        F.vamp_prior_rows(dev[0], dev[3][:, :-1], dev[4][:, :-1])

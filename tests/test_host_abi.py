@@ -84,3 +84,38 @@ def test_step_report_packs_one_copy(built):
     assert vals == {"loss": 0.5, "Reconstruction_Loss": 0.25, "KLD": -1.0} and per == [1.0, 2.0, 3.0]
     with pytest.raises(RuntimeError, match="CUDA"):
         F.per_image_mse(torch.zeros(2, 3, 4, 4), torch.zeros(2, 3, 4, 4))
+
+
+def test_last_model_host_parts(built):
+    """Torch-side pieces of the MSSIMVAE / DFCVAE / VampVAE drop-ins that need no GPU: the MS-SSIM module against the
+    reference fixture (quirks of mssim_vae.py:80-82, 206-209, 282 included), the DFCVAE extractor hook and constructor
+    contracts.  Their loss_function kernels are covered by tests/test_gpu_next_models.py."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from goldens import assert_close, leaf, load
+    from vaekit.models import vae_models
+    from vaekit.models.mssim_vae import MSSIM
+    g = load("mssimvae")
+    m = vae_models["MSSIMVAE"](3, 16)
+    assert m.mssim_loss.normalize is True and m.mssim_loss.size_average is True and m.mssim_loss.window_size == 11
+    assert vae_models["MSSIMVAE"](3, 16, size_average=False).mssim_loss.normalize is False      # lands in `normalize`
+    r = leaf(g["in_recons"])
+    out = m.mssim_loss(r, g["in_input"])
+    assert_close(out, g["out_Reconstruction_Loss"], 1e-6, "1 - MS-SSIM")
+    out.backward()
+    w = MSSIM().gaussian_window(11, 1.5)
+    assert abs(float(w.sum()) - 1.0) < 1e-6 and w[0] > w[5]            # exp(+d^2): heaviest at the edges
+
+    feats = torch.nn.Sequential(*[torch.nn.Conv2d(3, 3, 1) if i % 3 == 0 else torch.nn.ReLU() for i in range(44)])
+    net = torch.nn.Module()
+    net.features = feats
+    d = vae_models["DFCVAE"](3, 16, feature_network=net)
+    assert (d.alpha, d.beta) == (1, 0.5) and not d.feature_network.training
+    assert all(not p.requires_grad for p in d.feature_network.parameters())
+    f = d.extract_features(torch.rand(2, 3, 8, 8))
+    assert len(f) == 4 and len(d.extract_features(torch.rand(2, 3, 8, 8), ['0', '1'])) == 2
+
+    v = vae_models["VampVAE"](3, 16, num_components=12)
+    assert v.pseudo_input.shape == (12, 12) and not v.pseudo_input.requires_grad
+    assert "pseudo_input" not in v.state_dict() and v.embed_pseudo[0].out_features == 12288
+    pm, pv = v.prior_components(torch.rand(2, 3, 64, 64))
+    assert pm.shape == (12, 16) and pv.shape == (12, 16)

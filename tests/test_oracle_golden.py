@@ -3,6 +3,7 @@
 tests/golden/make_golden.py).  CPU-only; runs on any box."""
 import sys, os
 
+import numpy as np
 import pytest
 import torch
 
@@ -276,3 +277,66 @@ def test_twostage_vae():
     for k in ("loss", "Reconstruction_Loss", "KLD"):
         assert_close(d[k], g["out_" + k], TOL, k)
     assert_close(r.grad, g["grad_recons"], TOL); assert_close(mu.grad, g["grad_mu"], TOL); assert_close(lv.grad, g["grad_log_var"], TOL)
+
+
+def test_mssim_vae():
+    g = load("mssimvae")
+    r, mu, lv = leaf(g["in_recons"]), leaf(g["in_mu"]), leaf(g["in_log_var"])
+    d = O.mssim_vae_loss(r, g["in_input"], mu, lv, g["hp_M_N"])
+    d["loss"].backward()
+    for k in ("loss", "Reconstruction_Loss", "KLD"):
+        assert_close(d[k], g["out_" + k], TOL, k)
+    assert_close(r.grad, g["grad_recons"], TOL); assert_close(mu.grad, g["grad_mu"], TOL); assert_close(lv.grad, g["grad_log_var"], TOL)
+
+
+def test_dfc_vae():
+    g = load("dfcvae")
+    r, mu, lv = leaf(g["in_recons"]), leaf(g["in_mu"]), leaf(g["in_log_var"])
+    fr = [leaf(g["in_fr%d" % n]) for n in range(4)]
+    fi = [g["in_fi%d" % n] for n in range(4)]
+    d = O.dfc_loss(r, g["in_input"], fr, fi, mu, lv, g["hp_M_N"], alpha=g["hp_alpha"], beta=g["hp_beta"])
+    d["loss"].backward()
+    for k in ("loss", "Reconstruction_Loss", "KLD", "feature_loss"):
+        assert_close(d[k], g["out_" + k], TOL, k)
+    assert_close(r.grad, g["grad_recons"], TOL); assert_close(mu.grad, g["grad_mu"], TOL); assert_close(lv.grad, g["grad_log_var"], TOL)
+    for n in range(4):
+        assert_close(fr[n].grad, g["grad_fr%d" % n], TOL, "feature %d" % n)
+
+
+def test_vamp_vae():
+    g = load("vampvae")
+    r, mu, lv, z = leaf(g["in_recons"]), leaf(g["in_mu"]), leaf(g["in_log_var"]), leaf(g["in_z"])
+    pm, pv = leaf(g["in_prior_mu"]), leaf(g["in_prior_log_var"])
+    d = O.vamp_loss(r, g["in_input"], mu, lv, z, pm, pv, g["hp_M_N"])
+    d["loss"].backward()
+    for k in ("loss", "Reconstruction_Loss", "KLD"):
+        assert_close(d[k], g["out_" + k], TOL, k)
+    for t, n in ((r, "recons"), (mu, "mu"), (lv, "log_var"), (z, "z"), (pm, "prior_mu"), (pv, "prior_log_var")):
+        assert_close(t.grad, g["grad_" + n], TOL, n)
+
+
+def test_vamp_closed_form_backward():
+    """The hand-derived gradients the K9 kernels implement (csrc/vamp.cu), restated in float64 numpy and checked against
+    the reference's autograd gradients in the fixture: softmax weights from (t, lse), fixed-order sums."""
+    g = load("vampvae", dtype=torch.float64)
+    z, mu, lv = (g[k].double().numpy() for k in ("in_z", "in_mu", "in_log_var"))
+    pm, pv = g["in_prior_mu"].double().numpy(), g["in_prior_log_var"].double().numpy()
+    B, K, M_N = z.shape[0], pm.shape[0], g["hp_M_N"]
+    diff = z[:, None, :] - pm[None]                                     # [B, K, D]
+    e = np.exp(-pv)[None]
+    t = np.sum(-0.5 * (pv[None] + diff ** 2) * e, axis=2) - np.log(K)
+    lse = np.log(np.sum(np.exp(t - t.max(1, keepdims=True)), axis=1)) + t.max(1)
+    w = np.exp(t - lse[:, None])
+    g_lse = -M_N / B                                                    # d loss / d lse_i: kld = mean(logq) - mean(lse)
+    g_lq = +M_N / B
+    gz_prior = g_lse * np.einsum("bk,bkd->bd", w, -diff * e)
+    g_pm = g_lse * np.einsum("bk,bkd->kd", w, diff * e)
+    g_pv = g_lse * np.einsum("bk,bkd->kd", w, 0.5 * e * (pv[None] + diff ** 2 - 1.0))
+    dq, eq = z - mu, np.exp(-lv)
+    gz_q = g_lq * (-dq * eq)
+    g_mu = g_lq * (dq * eq)
+    g_lv = g_lq * 0.5 * eq * (lv + dq ** 2 - 1.0)
+    assert_close(gz_prior + gz_q, g["grad_z"], TOL, "z")
+    assert_close(g_pm, g["grad_prior_mu"], TOL, "prior_mu")
+    assert_close(g_pv, g["grad_prior_log_var"], TOL, "prior_log_var")
+    assert_close(g_mu, g["grad_mu"], TOL, "mu"); assert_close(g_lv, g["grad_log_var"], TOL, "log_var")
