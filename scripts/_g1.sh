@@ -1,8 +1,8 @@
 #!/bin/bash
-# r01v: ncu --set full of the SWD sort kernels (one key-only scatter, one key+index scatter, the fused last pass, one histogram) and the tcgen05 GEMM
+# scratch: r01w regression -- full GPU suite, smoke, SWAE bench line, launch list
 mkdir -p gpurun_out
-CMD="python bench.py --workload swae --steps 1 --warmup 3 --no-cpu --no-e2e"
-$CMD > gpurun_out/plain_swae.log 2>&1
-# launch order per step: gemm x2, then prior sort (hist,scan,scatter)x4, then z sort x4 (last fused), gemm
-timeout 900 ncu --set full --clock-control none --import-source on -k "regex:scatter_kernel|hist_kernel|gemm3x_kernel" -s 57 -c 19 -f -o gpurun_out/ncu_swae_r01v $CMD > gpurun_out/ncu_swae.log 2>&1; tail -2 gpurun_out/ncu_swae.log
-ls -la gpurun_out/ncu_swae_r01v.ncu-rep
+timeout 150 python -m pytest tests -m gpu -q > gpurun_out/pytest_gpu_r01w.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu_r01w.log
+tail -3 gpurun_out/pytest_gpu_r01w.log
+timeout 60 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > gpurun_out/smoke_r01w.log 2>&1; tail -1 gpurun_out/smoke_r01w.log
+timeout 90 python bench.py --workload swae > gpurun_out/bench_swae_r01w.json 2> gpurun_out/bench_swae_r01w.err; grep -o '"ms_per_step": [0-9.]*' gpurun_out/bench_swae_r01w.json
+timeout 70 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/ncu_list_swae_r01w.csv python bench.py --workload swae --steps 2 --warmup 3 --no-cpu --no-e2e > gpurun_out/ncu_list_swae_r01w.log 2>&1; echo "ncu rc=$?"
