@@ -514,6 +514,9 @@ class SwaeWorkload(OpWorkload):
         self.desc = "SWAE sliced-Wasserstein, 200 projections, batch 1048576x128, projection GEMM + radix sort (BASELINE configs[4])"
         self.cpu_sample, self.bound = 1 << 16, "hbm"
         self.dominant, self.dominant_sharded = "swd_fwd", "swd_segments_fwd"
+        # dram__bytes_read.sum + dram__bytes_write.sum over the 19 kernels of one vk_swd_fwd call at this size
+        # (`ncu --set full`, r01v): 30.82 GB against the 28.76 GB of the traffic model
+        self.ncu_traffic = {"swd_fwd": (30.822819e9, "profiles/ncu_swae_r01v_summary.txt")}
 
     def model(self):
         from vaekit.models import vae_models
@@ -704,13 +707,18 @@ def run_op_gpu_arm(args, wl):
     else:
         peak, src = 148 * 16 * 1.965, "16 MUFU ops/clk/SM x 148 SMs x 1.965 GHz (nominal)"
         ach = work[dom] / dms / 1e6
+    ncu_t = getattr(wl, "ncu_traffic", {}).get(dom) if world == 1 else None
     roof = {"bound": "tensor" if wl.bound == "tensor" else "hbm" if wl.bound == "hbm" else "mufu", "kernel": dom,
-            "achieved": round(ach, 2), "peak": round(peak, 1), "unit": unit, "frac": round(ach / peak, 4), "traffic": None,
+            "achieved": round(ach, 2), "peak": round(peak, 1), "unit": unit, "frac": round(ach / peak, 4),
+            "traffic": ncu_t[0] if ncu_t else None, "traffic_source": ncu_t[1] if ncu_t else None,
             "peak_source": src, "algorithmic_work_per_launch": work[dom], "ms_per_launch": dms, "calls": kern}
     # end to end: host (pinned) inputs copied in and the loss read back every step
     e2e = None
     if not args.no_e2e:
-        host = {k: v.cpu().pin_memory() for k, v in t.items()}
+        # detached: the workload marks its inputs requires_grad in place, and a host copy that stayed in the autograd
+        # graph would make every backward() end with a pageable device-to-host copy of the gradient (r01w and earlier
+        # ops-workload e2e numbers carry that artefact: 1.7-3.4 GB/s effective instead of the 54 GB/s of pinned copies)
+        host = {k: v.detach().cpu().pin_memory() for k, v in t.items()}
         h2d = sum(v.numel() * v.element_size() for v in host.values())
 
         def e2e_step():

@@ -1,8 +1,12 @@
 #!/bin/bash
-# scratch: r01w regression -- full GPU suite, smoke, SWAE bench line, launch list
+# scratch: r01x -- e2e of the ops workloads after the host-copy fix (no CPU baseline leg, 10 steps)
 mkdir -p gpurun_out
-timeout 150 python -m pytest tests -m gpu -q > gpurun_out/pytest_gpu_r01w.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu_r01w.log
-tail -3 gpurun_out/pytest_gpu_r01w.log
-timeout 60 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > gpurun_out/smoke_r01w.log 2>&1; tail -1 gpurun_out/smoke_r01w.log
-timeout 90 python bench.py --workload swae > gpurun_out/bench_swae_r01w.json 2> gpurun_out/bench_swae_r01w.err; grep -o '"ms_per_step": [0-9.]*' gpurun_out/bench_swae_r01w.json
-timeout 70 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/ncu_list_swae_r01w.csv python bench.py --workload swae --steps 2 --warmup 3 --no-cpu --no-e2e > gpurun_out/ncu_list_swae_r01w.log 2>&1; echo "ncu rc=$?"
+for w in swae vq betatc wae_mmd_rbf; do
+  timeout 60 python bench.py --workload $w --steps 10 --warmup 3 --no-cpu > gpurun_out/bench_${w}_r01x.json 2>> gpurun_out/r01x_err.log
+  python - gpurun_out/bench_${w}_r01x.json <<'PY'
+import json,sys
+for l in open(sys.argv[1]):
+    if l.startswith('{'):
+        d=json.loads(l); print(sys.argv[1], d['ms_per_step'], d['e2e'], d['roofline'].get('traffic'))
+PY
+done
