@@ -44,7 +44,14 @@ constexpr uint32_t kTmS = 0, kTmO = 128, kTmAhi = 256, kTmAlo = 320, kTmK = 384;
 constexpr int kEpiWarps = 16, kColGroups = kEpiWarps / 4, kTmaWarp = 16, kMmaWarp = 17;
 constexpr int kEpiThreads = 32 * kEpiWarps;
 constexpr int kMmdThreads = 32 * 18;  // warps 0-15 epilogue, warp 16 TMA, warp 17 MMA
-constexpr int kMaxQ = 8;
+// Column chunks per row block.  Two rules pick Q: enough gradient items for the static schedule to balance (up to
+// kBalanceQ), and a bound on how many 64-column tiles are accumulated into one gradient tile in tensor memory: the
+// tcgen05 fp32 accumulator truncates, a bias that grows with the length of the chain (measured at N = 65 536 with 683
+// tiles per chain: 2.3e-4 of the gradient's maximum against float64; 16-tile chains at N = 4096 stay below 2e-5).
+// Chains are therefore cut at kChainTiles and the partial tiles are summed in fp32 round-to-nearest by the finalize
+// kernel; kMaxGradItems bounds the workspace that costs (4 GiB of partial tiles at D = 128).
+constexpr int kMaxQ = 64, kBalanceQ = 8, kChainTiles = 32;
+constexpr int64_t kMaxGradItems = 65536;
 
 struct MmdShape {
   int64_t N;
@@ -82,14 +89,30 @@ inline MmdWs mmd_ws(int64_t N, int D, int rows_local_blocks, int Q) {
   w.total = o;
   return w;
 }
+inline int q_cap(int row_blocks) {
+  int64_t c = kMaxGradItems / (row_blocks > 0 ? row_blocks : 1);
+  if (c > kMaxQ) c = kMaxQ;
+  if (c < kBalanceQ) c = kBalanceQ;
+  return (int)c;
+}
 inline int pick_Q(int T, int row_blocks) {
   // aim for >= 8 gradient items per SM so the static round-robin schedule balances
   int q = (148 * 8 + row_blocks - 1) / row_blocks;
-  if (q > kMaxQ) q = kMaxQ;
+  if (q > kBalanceQ) q = kBalanceQ;
+  const int chain = (4 * T + kChainTiles - 1) / kChainTiles;      // accumulation chains of at most kChainTiles tiles
+  if (chain > q) q = chain;
+  if (q > q_cap(row_blocks)) q = q_cap(row_blocks);
   if (q > 4 * T) q = 4 * T;
   if (q < 1) q = 1;
   const int n = 4 * T, len = (n + q - 1) / q;
   return (n + len - 1) / len;                 // no empty chunk
+}
+// upper bound of Q * row_blocks over every row range of an N-row problem (what the workspace query must cover)
+inline int64_t max_grad_items(int T) {
+  int64_t a = (int64_t)kMaxQ * T;
+  if (a > kMaxGradItems) a = kMaxGradItems;
+  const int64_t b = (int64_t)kBalanceQ * T;
+  return a > b ? a : b;
 }
 
 struct MmdSmem {
@@ -661,7 +684,9 @@ using namespace vk;
 extern "C" int64_t vk_mmd_workspace_bytes(int64_t N, int64_t D) {
   if (N < 1 || D < 1 || D > 128) return -1;
   const int T = (int)((N + kRows - 1) / kRows);
-  return (int64_t)mmd_ws(N, (int)D, T, kMaxQ).total;
+  const int64_t items = max_grad_items(T);
+  VK_REQUIRE(items < (int64_t)1 << 31, -1, "mmd_workspace_bytes: N too large");
+  return (int64_t)mmd_ws(N, (int)D, (int)items, 1).total;
 }
 
 extern "C" int vk_mmd_fwd(const float* z, const float* prior, int64_t N, int64_t D, int kernel_type, float z_var,

@@ -261,8 +261,4 @@ def test_mmd_full_size_vs_fp64_blocks(vk, kt):
           % (kt, e, terms.cpu().tolist(), tot, mmd.item(), ref_mmd))
     check_terms(terms, ref_terms, kt + " full size")
     assert abs(mmd.item() - ref_mmd) <= TOL * reg * max(abs(t) for t in tot)
-    # KNOWN GAP: the terms and the scalar meet 1e-5 at this size, the gradient does not.
-    # Measured r01y: 2.3e-4 (rbf) / 1.2e-4 (imq) of max|grad| against float64, 2e-5 at N = 4096.  The gradient tile is
-    # accumulated in tensor memory over 683 column tiles per chain here (16 at N = 4096) and the tcgen05 fp32 accumulator
-    # truncates; the bound below only pins today's behaviour until the chains are cut.
-    assert e <= 5e-4
+    assert e <= 2e-5

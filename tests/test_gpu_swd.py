@@ -198,6 +198,12 @@ def test_swd_full_size_stages(vk):
     assert torch.equal(s_lat, t_lat), "sorted keys differ from torch.sort"
     assert torch.equal(perm, t_perm), "permutation differs from torch's stable sort"
     del s_lat, perm
+    eq = t_lat[:, 1:] == t_lat[:, :-1]                           # exact key ties, needed by step 5
+    tie_sorted = torch.zeros_like(t_lat, dtype=torch.bool)
+    tie_sorted[:, 1:] |= eq
+    tie_sorted[:, :-1] |= eq
+    tied = torch.zeros_like(tie_sorted).scatter_(1, t_perm, tie_sorted)      # sample order
+    del eq, tie_sorted
     s_pri, _ = F.seg_sort(pri)
     t_pri = torch.sort(pri, dim=1)[0]
     assert torch.equal(s_pri, t_pri)
@@ -227,7 +233,17 @@ def test_swd_full_size_stages(vk):
     tot0, g0 = F.swd_sweep(z, z.clone(), proj, p)
     assert tot0.item() == 0.0 and not g0.any()
     rp = torch.randperm(n, device=DEV)
-    del glat, lat, pri
+    lat_p = F.swd_project(z[rp], proj)
+    assert torch.equal(lat_p, lat[:, rp]), "a row's projections depend on its position in the batch"
+    tot_p = F.swd_segments(lat_p, pri.clone(), p)                # lat_p now holds d sum / d lat of the permuted batch
+    assert abs(tot_p.item() - total.item()) <= 1e-9 * total_ref    # same sorted values, other grouping of the fp32 partials
+    # only samples whose key is bit-identical to another sample's may trade ranks (the sort is stable in batch order)
+    tied_p, want = tied[:, rp], glat[:, rp]
+    frac = tied.float().mean().item()
+    print("full-size swd: %.2f %% of the (projection, sample) keys are exact ties" % (100 * frac))
+    assert frac < 0.2
+    assert torch.equal(lat_p[~tied_p], want[~tied_p]), "an untied sample's d/dlat changed under a batch permutation"
+    del lat_p, want, tied, tied_p, glat, lat, pri
     tot_q, grad_p = F.swd_sweep(z[rp], prior, proj, p)
     assert abs(tot_q.item() - tot_f.item()) <= 1e-9 * total_ref
     e = dev_rel(grad_p, grad_f[rp])
