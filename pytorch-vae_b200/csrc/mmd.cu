@@ -52,6 +52,13 @@ constexpr int kMmdThreads = 32 * 18;  // warps 0-15 epilogue, warp 16 TMA, warp 
 // kernel; kMaxGradItems bounds the workspace that costs (4 GiB of partial tiles at D = 128).
 constexpr int kMaxQ = 64, kBalanceQ = 8, kChainTiles = 32;
 constexpr int64_t kMaxGradItems = 65536;
+// -DVK_MMD_INNER_DRAIN=1 (NOT validated on a GPU yet): cut the chains INSIDE a scheduler item instead --
+// the MMA warp commits o_full every s.chain live tiles, the epilogue drains O into sub-slot (q * subs + sub) while the
+// distance GEMMs of the next tiles run, and the row block's A operand stays in tensor memory.  Q follows the balance
+// rule only.  With the switch off the preprocessed source is the validated r01z kernel, token for token.
+#ifndef VK_MMD_INNER_DRAIN
+#define VK_MMD_INNER_DRAIN 0
+#endif
 
 struct MmdShape {
   int64_t N;
@@ -60,6 +67,9 @@ struct MmdShape {
   int lz;               // live 64-column tiles per side: ceil(N / 64)
   int rb0, rb1;         // row-block range owned by this call
   int Q;                // column chunks per row block (gradient items)
+#if VK_MMD_INNER_DRAIN
+  int subs, chain;      // partial-gradient sub-slots per item, live tiles per accumulation chain
+#endif
   int kernel_type;      // 0 rbf, 1 imq
   int passes;           // 3 (hi/lo split, fp32-grade) or 1 (plain bf16)
   float a_exp;          // rbf: -log2(e) / (2 D^2 z_var)
@@ -107,6 +117,37 @@ inline int pick_Q(int T, int row_blocks) {
   const int n = 4 * T, len = (n + q - 1) / q;
   return (n + len - 1) / len;                 // no empty chunk
 }
+#if VK_MMD_INNER_DRAIN
+inline int pick_Q_balance(int T, int row_blocks) {
+  int q = (148 * 8 + row_blocks - 1) / row_blocks;
+  if (q > kBalanceQ) q = kBalanceQ;
+  if (q > 4 * T) q = 4 * T;
+  if (q < 1) q = 1;
+  const int n = 4 * T, len = (n + q - 1) / q;
+  return (n + len - 1) / len;
+}
+// sub-slots per item and live tiles per chain: kChainTiles unless that needs more than kMaxGradItems partial tiles
+inline void pick_chain(int T, int row_blocks, int Q, int& subs, int& chain) {
+  const int n = 4 * T, len = (n + Q - 1) / Q;
+  int64_t per_rb = kMaxGradItems / (row_blocks > 0 ? row_blocks : 1);
+  if (per_rb < Q) per_rb = Q;
+  const int subs_cap = (int)(per_rb / Q);                        // >= 1
+  chain = kChainTiles;
+  subs = (len + chain - 1) / chain;
+  if (subs > subs_cap) {
+    chain = (len + subs_cap - 1) / subs_cap;
+    subs = (len + chain - 1) / chain;
+  }
+  if (subs < 1) subs = 1;
+}
+// bound of Q * subs * row_blocks over every row range: Q * subs <= T / 8 + 9, and never more than the cap allows
+inline int64_t max_grad_slots(int T) {
+  const int64_t a = (int64_t)T * (T / 8 + 9);
+  int64_t b = kMaxGradItems;
+  if (b < (int64_t)kBalanceQ * T) b = (int64_t)kBalanceQ * T;
+  return a < b ? a : b;
+}
+#endif
 // upper bound of Q * row_blocks over every row range of an N-row problem (what the workspace query must cover)
 inline int64_t max_grad_items(int T) {
   int64_t a = (int64_t)kMaxQ * T;
@@ -349,6 +390,9 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
           ++nb;
         }
         uint32_t oacc = 0;
+#if VK_MMD_INNER_DRAIN
+        bool o_wait = true;                                  // the next G2 is the first one into a fresh accumulator
+#endif
         // live z-side tiles of this chunk come first (tile sequence: [z tiles | prior tiles], dead tiles = columns >= N)
         int nz_live = 0;
         if (it.grad) {
@@ -370,7 +414,12 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
             const uint32_t neg_a = j >= nz_live ? (1u << 13) : 0u;           // k(z, prior) enters with a minus sign
             PROF_LAP(3)
             mbar_wait(bar(kBarKFull + kb), (nk >> 1) & 1);
+#if VK_MMD_INNER_DRAIN
+            if (o_wait && n_grad_items > 0) mbar_wait(bar(kBarOEmpty), (n_grad_items - 1) & 1);
+            o_wait = false;
+#else
             if (j == 0 && n_grad_items > 0) mbar_wait(bar(kBarOEmpty), (n_grad_items - 1) & 1);
+#endif
             PROF_LAP(2)
             TRACE(2, nk)
             fence_after_sync();
@@ -394,6 +443,14 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
             mma_commit_if(leader, bar(kBarKEmpty + kb));
             TRACE(3, nk)
             ++nk;
+#if VK_MMD_INNER_DRAIN
+            if ((j + 1) % s.chain == 0 && j + 1 < live) {      // chain complete: hand O to the epilogue, start a new one
+              mma_commit_if(leader, bar(kBarOFull));
+              ++n_grad_items;
+              oacc = 0;
+              o_wait = true;
+            }
+#endif
           }
         }
         if (it.grad && live > 0) { mma_commit_if(leader, bar(kBarOFull)); ++n_grad_items; }
@@ -428,6 +485,46 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
       const float nx = (it.grad ? normZ : normP)[grow] + (KT == 1 ? s.Ceps : 0.f);
       float rs = 0.f;
       int live = 0;
+#if VK_MMD_INNER_DRAIN
+      const int q_item = idx % (s.Q + 1);
+      const size_t lrow_i = (size_t)(it.i - s.rb0) * kRows + t;
+      const size_t nloc_i = (size_t)(s.rb1 - s.rb0) * kRows;
+      int nlive = 0;
+      if (it.grad)
+        for (int u = it.u0; u < it.u1; ++u) nlive += tile_live(s, get_tile(s, it, u)) ? 1 : 0;
+      // partial slot (q * subs + sub) <- this warp's row sums of the chain and its 32 x 32 chunk of O (zeros when there
+      // is no accumulator to read); every epilogue warp calls it at the same live-tile count (.sync.aligned inside)
+      auto drain_o = [&](int sub, bool have_o) {
+        const size_t slot = (size_t)q_item * s.subs + sub;
+        float* op = Opart + (slot * nloc_i + lrow_i) * s.Dp;
+        rspart[(slot * kColGroups + cg) * nloc_i + lrow_i] = rs;
+        rs = 0.f;
+        const int c0 = cg * 32;
+        if (!have_o) {
+          for (int e = c0; e < c0 + 32 && e < s.Dp; ++e) op[e] = 0.f;
+          return;
+        }
+        mbar_wait(bar(kBarOFull), n_grad_items & 1);
+        fence_after_sync();
+        if (c0 < s.Dp) {
+          uint32_t o[32];
+          tmem_ld32(tmem_O + ((uint32_t)(ew * 32) << 16) + c0, o);
+          tmem_ld_wait();
+          if (c0 + 32 <= s.Dp) {
+#pragma unroll
+            for (int e = 0; e < 32; e += 4)
+              *reinterpret_cast<float4*>(op + c0 + e) = make_float4(__uint_as_float(o[e]), __uint_as_float(o[e + 1]),
+                                                                     __uint_as_float(o[e + 2]), __uint_as_float(o[e + 3]));
+          } else {
+#pragma unroll
+            for (int e = 0; e < 32; ++e) if (c0 + e < s.Dp) op[c0 + e] = __uint_as_float(o[e]);
+          }
+        }
+        fence_before_sync();
+        mbar_arrive(bar(kBarOEmpty));
+        ++n_grad_items;
+      };
+#endif
       {
         // this row block's operand -> tensor memory: fp32 row slice [cg*32, cg*32+32) split into bf16 hi / lo, two per
         // column.  The previous item's MMAs must be finished with the old block first.
@@ -552,8 +649,18 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
         ++live;
         if (it.grad) ++nk;
         ++nb;
+#if VK_MMD_INNER_DRAIN
+        if (it.grad && live % s.chain == 0 && live < nlive) drain_o(live / s.chain - 1, true);
+#endif
       }
       PROF_LAP(1)
+#if VK_MMD_INNER_DRAIN
+      if (it.grad) {
+        const int last = live == 0 ? 0 : (live - 1) / s.chain;
+        drain_o(last, live > 0);
+        for (int sub = last + 1; sub < s.subs; ++sub) drain_o(sub, false);     // unused sub-slots of a short item
+      }
+#else
       if (it.grad) {
         const int q = (idx % (s.Q + 1));
         const size_t lrow = (size_t)(it.i - s.rb0) * kRows + t;
@@ -586,6 +693,7 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
         mbar_arrive(bar(kBarOEmpty));
         ++n_grad_items;
       }
+#endif
       PROF_LAP(3)
     }
     PROF_OUT("epilogue wait_s_full/work/wait_k_empty/item_end", threadIdx.x == 0)
@@ -621,7 +729,12 @@ __global__ void mmd_finalize_kernel(const float* __restrict__ Z, MmdShape s, con
     const int64_t r = g / s.D;
     const int d = (int)(g % s.D);
     float rs = 0.f, o = 0.f;
-    for (int q = 0; q < s.Q; ++q) {
+#if VK_MMD_INNER_DRAIN
+    const int n_slots = s.Q * s.subs;
+#else
+    const int n_slots = s.Q;
+#endif
+    for (int q = 0; q < n_slots; ++q) {
       for (int c = 0; c < kColGroups; ++c) rs += rspart[(size_t)(q * kColGroups + c) * nloc_pad + r];
       o += Opart[((size_t)q * nloc_pad + r) * s.Dp + d];
     }
@@ -666,7 +779,12 @@ int make_shape(int64_t N, int64_t D, int kernel_type, float z_var, int passes, i
   s.lz = (int)((N + kCols - 1) / kCols);
   s.rb0 = (int)(row_begin / kRows);
   s.rb1 = (int)((row_end + kRows - 1) / kRows);
+#if VK_MMD_INNER_DRAIN
+  s.Q = pick_Q_balance(s.T, s.rb1 - s.rb0);
+  pick_chain(s.T, s.rb1 - s.rb0, s.Q, s.subs, s.chain);
+#else
   s.Q = pick_Q(s.T, s.rb1 - s.rb0);
+#endif
   s.kernel_type = kernel_type; s.passes = passes;
   const double sp = 2.0 * (double)D * (double)D * (double)z_var;
   s.a_exp = (float)(-1.4426950408889634 / sp);
@@ -684,7 +802,11 @@ using namespace vk;
 extern "C" int64_t vk_mmd_workspace_bytes(int64_t N, int64_t D) {
   if (N < 1 || D < 1 || D > 128) return -1;
   const int T = (int)((N + kRows - 1) / kRows);
+#if VK_MMD_INNER_DRAIN
+  const int64_t items = max_grad_slots(T);
+#else
   const int64_t items = max_grad_items(T);
+#endif
   VK_REQUIRE(items < (int64_t)1 << 31, -1, "mmd_workspace_bytes: N too large");
   return (int64_t)mmd_ws(N, (int)D, (int)items, 1).total;
 }
@@ -696,7 +818,11 @@ extern "C" int vk_mmd_fwd(const float* z, const float* prior, int64_t N, int64_t
   MmdShape s;
   int rc = make_shape(N, D, kernel_type, z_var, passes, row_begin, row_end, s);
   if (rc != VK_OK) return rc;
+#if VK_MMD_INNER_DRAIN
+  const MmdWs w = mmd_ws(N, (int)D, s.rb1 - s.rb0, s.Q * s.subs);
+#else
   const MmdWs w = mmd_ws(N, (int)D, s.rb1 - s.rb0, s.Q);
+#endif
   VK_REQUIRE(workspace_bytes >= (int64_t)w.total, VK_ERR_WORKSPACE, "mmd_fwd: workspace %lld < %lld",
              (long long)workspace_bytes, (long long)w.total);
   cudaStream_t st = (cudaStream_t)stream;
