@@ -27,8 +27,10 @@ def _row_layout(t):
         t = t.reshape(1, 1)
     if t.dim() == 1:
         t = t.unsqueeze(0)
-    if t.dim() > 4 or (t.shape[-1] > 1 and t.stride(-1) != 1):
+    if t.shape[-1] > 1 and t.stride(-1) != 1:
         t = t.contiguous()
+    if t.dim() > 4:                       # more than three outer dims: a dense copy addressed as [rows, D]
+        t = t.contiguous().view(-1, t.shape[-1])
     outer = list(t.shape[:-1])
     strides = list(t.stride()[:-1])
     pad = 3 - len(outer)

@@ -25,6 +25,12 @@ class BaseVAE(nn.Module):
     def generate(self, x: Tensor, **kwargs) -> Tensor:
         raise NotImplementedError
 
+    def _module_order(self, *names: str) -> None:
+        """Registration order of the sub-modules = the reference's: `state_dict()` and `parameters()` then enumerate in
+        the reference's order, which is what an optimizer state saved by run.py:80-99 is indexed by."""
+        mods = self._modules
+        self._modules = type(mods)([(n, mods[n]) for n in names] + [(n, m) for n, m in mods.items() if n not in names])
+
     @abstractmethod
     def forward(self, *inputs: Tensor) -> Tensor:
         pass

@@ -21,6 +21,8 @@ class ConditionalVAE(GaussianConvVAE):
         self.embed_data = nn.Conv2d(in_channels, in_channels, kernel_size=1)      # cvae.py:24
         self.encoder = down_stack(in_channels + 1, widths)                        # extra label channel, cvae.py:30
         self.decoder_input = nn.Linear(latent_dim + num_classes, widths[-1] * 4)  # cvae.py:51
+        self._module_order('embed_class', 'embed_data', 'encoder', 'fc_mu', 'fc_var', 'decoder_input', 'decoder',
+                           'final_layer')
 
     def decode(self, z: Tensor) -> Tensor:
         h = self.decoder_input(z).view(-1, 512, 2, 2)          # hard-wired like cvae.py:102

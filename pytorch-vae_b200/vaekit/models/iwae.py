@@ -1,6 +1,7 @@
 """Drop-in for models/iwae.py."""
 from typing import List
 
+import torch
 from torch import Tensor
 
 from .. import functional as F
@@ -36,6 +37,11 @@ class IWAE(GaussianConvVAE):
         kld_weight = kwargs['M_N']
         loss, recon, _, neg_kld = F.iw_bound(recons, input, self._kl_rows(mu, log_var), kld_weight)
         return {'loss': loss, 'Reconstruction_Loss': recon, 'KLD': neg_kld}
+
+    def sample(self, num_samples: int, current_device: int, **kwargs) -> Tensor:
+        """iwae.py:162-180: one sample dim of size 1 through the [B,S,D] decode, squeezed away again."""
+        z = torch.randn(num_samples, 1, self.latent_dim)      # CPU generator, as the reference
+        return self.decode(z.to(current_device)).squeeze()
 
     def generate(self, x: Tensor, **kwargs) -> Tensor:
         return self.forward(x)[0][:, 0, :]

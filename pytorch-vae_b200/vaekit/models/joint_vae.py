@@ -35,6 +35,7 @@ class JointVAE(GaussianConvVAE):
         self.cont_iter, self.disc_iter = latent_num_iter, categorical_num_iter
         self.fc_z = nn.Linear(width * 4, categorical_dim)                              # joint_vae.py:67
         self.decoder_input = nn.Linear(latent_dim + categorical_dim, width * 4)        # joint_vae.py:71
+        self._module_order('encoder', 'fc_mu', 'fc_var', 'fc_z', 'decoder_input', 'decoder', 'final_layer')
         self.sampling_dist = torch.distributions.OneHotCategorical(1. / categorical_dim * torch.ones((categorical_dim, 1)))
 
     def encode(self, input: Tensor) -> List[Tensor]:

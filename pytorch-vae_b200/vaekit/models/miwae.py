@@ -1,6 +1,7 @@
 """Drop-in for models/miwae.py."""
 from typing import List
 
+import torch
 from torch import Tensor
 
 from .. import functional as F
@@ -35,6 +36,11 @@ class MIWAE(GaussianConvVAE):
         kld_weight = kwargs['M_N']
         loss, recon, _, neg_kld = F.iw_bound(recons, input, self._kl_rows(mu, log_var), kld_weight)
         return {'loss': loss, 'Reconstruction_Loss': recon, 'KLD': neg_kld}
+
+    def sample(self, num_samples: int, current_device: int, **kwargs) -> Tensor:
+        """miwae.py:166-183: [N,1,1,D] through the [B,M,S,D] decode, squeezed."""
+        z = torch.randn(num_samples, 1, 1, self.latent_dim)   # CPU generator, as the reference
+        return self.decode(z.to(current_device)).squeeze()
 
     def generate(self, x: Tensor, **kwargs) -> Tensor:
         return self.forward(x)[0][:, 0, 0, :]

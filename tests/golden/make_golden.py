@@ -423,10 +423,47 @@ def gen_last_models():
          grad_prior_log_var=pvl.grad)
 
 
+def gen_iw_forward():
+    """IWAE.forward / MIWAE.forward / generate (iwae.py:121-127,188, miwae.py:124-130,192) of the reference classes in
+    eval mode on a narrow conv stack; the module weights travel in the fixture (w_<state_dict key>).  IWAE.forward
+    itself raises on current torch (iwae.py:103 view() of the permuted z), so its body is replayed line by
+    line with the reference's own methods and a .contiguous() z handed to decode -- the same values."""
+    g = torch.Generator().manual_seed(1290)
+    B, D, K, M = 3, 8, 4, 2
+    hd = [2, 4, 4, 8, 512]                                   # decode() hard-wires 512 channels (iwae.py:104)
+    x = torch.rand(B, 3, 64, 64, generator=g)
+    torch.manual_seed(1290)
+    m = ref.IWAE(3, D, hidden_dims=list(hd), num_samples=K).eval()
+    eps = torch.randn(B, K, D, generator=g)
+    with torch.no_grad():
+        mu, lv = m.encode(x)
+        mu = mu.repeat(K, 1, 1).permute(1, 0, 2)
+        lv = lv.repeat(K, 1, 1).permute(1, 0, 2)
+        with injected_noise(eps):
+            z = m.reparameterize(mu, lv)
+        e = (z - mu) / lv
+        rec = m.decode(z.contiguous())
+    save("iwae_forward", in_input=x, noise_eps=eps, hp_K=K, hp_D=D, out_recons=rec, out_mu=mu.contiguous(),
+         out_log_var=lv.contiguous(), out_z=z.contiguous(), out_eps=e.contiguous(), out_generate=rec[:, 0, :],
+         **{"w_" + k: v for k, v in m.state_dict().items()})
+    torch.manual_seed(1291)
+    m = ref.MIWAE(3, D, hidden_dims=list(hd), num_samples=K, num_estimates=M).eval()
+    eps = torch.randn(B, M, K, D, generator=g)
+    with torch.no_grad():
+        with injected_noise(eps):
+            rec, xin, mu, lv, z, e = m(x)
+        with injected_noise(eps):
+            gen = m.generate(x)
+    assert xin is x
+    save("miwae_forward", in_input=x, noise_eps=eps, hp_K=K, hp_M=M, hp_D=D, out_recons=rec, out_mu=mu.contiguous(),
+         out_log_var=lv.contiguous(), out_z=z.contiguous(), out_eps=e.contiguous(), out_generate=gen,
+         **{"w_" + k: v for k, v in m.state_dict().items()})
+
+
 if __name__ == "__main__":
     torch.set_num_threads(4)
     only = sys.argv[1:]
     for fn in (gen_vanilla, gen_beta, gen_logcosh, gen_iw, gen_wae, gen_betatc, gen_swae, gen_vq, gen_info, gen_next_models, gen_cat, gen_joint,
-               gen_last_models):
+               gen_last_models, gen_iw_forward):
         if not only or fn.__name__[4:] in only:
             fn()

@@ -334,28 +334,113 @@ def test_rejects_cpu_and_wrong_dtype(vk):
         F.elbo(torch.zeros(4, device=DEV), torch.zeros(5, device=DEV), None)
 
 
-def test_full_size_properties(vk):
-    """BASELINE config 2a size (B=4096,K=5,P=12288) is too big for the CPU oracle in seconds: check
-    size-independent properties instead -- batch-replication invariance of the mean bound, linearity of
-    the backward in the upstream gradient, and a checksum of g_recons against the closed form."""
-    F, _ = vk
-    gen = torch.Generator(device=DEV).manual_seed(1)
-    B, K, P, D = 512, 5, 12288, 128
-    r = torch.tanh(torch.randn(B, K, P, device=DEV, generator=gen)); x = torch.rand(B, P, device=DEV, generator=gen)
-    mu = torch.randn(B, K, D, device=DEV, generator=gen); lv = 0.5 * torch.randn(B, K, D, device=DEV, generator=gen) - 1
-    kl = F.kl_rows(mu, lv)
-    rg = leaf(r)
-    a = F.iw_bound(rg, x, kl, 0.00025)
-    a[0].backward()
-    b = F.iw_bound(r.repeat(2, 1, 1), x.repeat(2, 1), kl.repeat(2, 1), 0.00025)
-    assert_close(b[0], a[0], 2e-6); assert_close(b[1], a[1], 2e-6)
-    rg2 = leaf(r)
-    (3.0 * F.iw_bound(rg2, x, kl, 0.00025)[0]).backward()
-    assert_close(rg2.grad, 3.0 * rg.grad, 2e-6)
-    # closed form on a slice through torch ops on the GPU (torch is only the checker here)
-    sl = slice(0, 8)
-    lp = ((r[sl] - x[sl, None]) ** 2).mean(-1); lw = lp + 0.00025 * kl[sl]
-    w = torch.softmax(lw, -1); S = (w * lw).sum(-1, keepdim=True)
-    c = w * (1 + lw - S) / B
-    expect = c[..., None] * 2 * (r[sl] - x[sl, None]) / P
-    assert_close(rg.grad[sl], expect, TOL)
+def _iw_fp64(recons, x, mu0, lv0, M_N, G, K):
+    """iwae.py:145-158 / miwae.py:148-162 evaluated in float64 with torch ON THE GPU (torch is only the checker): the
+    input is broadcast instead of repeated, everything else is the reference's sequence of ops."""
+    r = recons.double().requires_grad_(True)
+    m = mu0.double().requires_grad_(True); v = lv0.double().requires_grad_(True)
+    shp = (r.shape[0],) + (1,) * (r.dim() - 4) + tuple(x.shape[1:])
+    lp = ((r - x.double().view(shp)) ** 2).flatten(r.dim() - 3).mean(-1)            # [B,(M,)K]
+    ms = (mu0.shape[0],) + (1,) * (r.dim() - 4) + (mu0.shape[1],)
+    kld = -0.5 * torch.sum(1 + v.view(ms) - m.view(ms) ** 2 - v.view(ms).exp(), dim=-1).expand_as(lp)
+    lw = lp + M_N * kld
+    w = torch.softmax(lw, dim=-1)
+    loss = torch.sum(w * lw, dim=-1).mean()
+    loss.backward()
+    return loss, lp.mean(), -kld.mean(), r.grad, m.grad, v.grad
+
+
+@pytest.mark.parametrize("G", [1, 3])
+def test_iw_bound_at_benchmark_size_vs_fp64(vk, G):
+    """BASELINE configs[1] at the size bench.py times: IWAE K=5 (and MIWAE M=3) at B=4096, D=128, 3x64x64.  The loss, its
+    two side outputs and all three gradients (recons, mu, log_var through the stride-0 expand) against the float64
+    restatement of iwae.py:145-158 / miwae.py:148-162 on the same tensors, 1e-5 relative."""
+    F, vae_models = vk
+    B, K, D, M_N = 4096, 5, 128, 0.00025
+    gen = torch.Generator(device=DEV).manual_seed(1265)
+    ss = (B, G, K) if G > 1 else (B, K)
+    r = torch.tanh(torch.randn(*ss, 3, 64, 64, device=DEV, generator=gen))
+    x = torch.rand(B, 3, 64, 64, device=DEV, generator=gen)
+    mu0 = torch.randn(B, D, device=DEV, generator=gen); lv0 = 0.5 * torch.randn(B, D, device=DEV, generator=gen) - 1
+    m = (vae_models["MIWAE"](3, D, num_samples=K, num_estimates=G) if G > 1 else vae_models["IWAE"](3, D, num_samples=K))
+    rg, mg, vg = leaf(r), leaf(mu0), leaf(lv0)
+    es = (-1, G, K, -1) if G > 1 else (-1, K, -1)
+    mu = mg.view(B, *([1] * (len(ss) - 1)), D).expand(*es); lv = vg.view(B, *([1] * (len(ss) - 1)), D).expand(*es)
+    d = m.loss_function(rg, x, mu, lv, None, None, M_N=M_N)
+    d["loss"].backward()
+    # float64 reference in row chunks of the batch (3 GB of recons in double does not fit twice): the loss is a mean over
+    # rows, so chunk gradients are scaled by chunk/B and the chunk losses averaged
+    loss = rl = kl = 0.0
+    g_r = torch.empty_like(r); g_m = torch.empty_like(mu0); g_v = torch.empty_like(lv0)
+    CH = 512
+    for b0 in range(0, B, CH):
+        sl = slice(b0, b0 + CH)
+        l, a, k, gr, gm, gv = _iw_fp64(r[sl], x[sl], mu0[sl], lv0[sl], M_N, G, K)
+        loss += l.item() * CH / B; rl += a.item() * CH / B; kl += k.item() * CH / B
+        g_r[sl] = (gr * (CH / B)).float(); g_m[sl] = (gm * (CH / B)).float(); g_v[sl] = (gv * (CH / B)).float()
+    assert abs(d["loss"].item() - loss) <= TOL * abs(loss)
+    assert abs(d["Reconstruction_Loss"].item() - rl) <= TOL * abs(rl)
+    assert abs(d["KLD"].item() - kl) <= TOL * abs(kl)
+    assert_close(rg.grad, g_r, TOL, "g_recons"); assert_close(mg.grad, g_m, TOL, "g_mu"); assert_close(vg.grad, g_v, TOL, "g_log_var")
+    # and per row: the recons gradient of every sample row, relative to that row's own maximum (the global max-norm above
+    # would hide a wrong low-weight sample)
+    num = (rg.grad - g_r).flatten(len(ss)).abs().amax(-1); den = g_r.flatten(len(ss)).abs().amax(-1).clamp_min(1e-30)
+    assert (num / den).max().item() <= 2e-5
+
+
+def _load_forward_fixture(name, cls, dev):
+    fx = load(name)
+    D, K = int(fx["hp_D"]), int(fx["hp_K"])
+    kw = dict(num_samples=K)
+    if "hp_M" in fx:
+        kw["num_estimates"] = int(fx["hp_M"])
+    m = cls(3, D, hidden_dims=[2, 4, 4, 8, 512], **kw).eval()
+    m.load_state_dict({k[2:]: v for k, v in fx.items() if k.startswith("w_")}, strict=True)
+    return fx, m.to(dev)
+
+
+@pytest.mark.parametrize("name", ["iwae_forward", "miwae_forward"])
+def test_iw_forward_contract_and_fixture(vk, name):
+    """IWAE.forward / MIWAE.forward / generate (iwae.py:121-127,188, miwae.py:124-130,192) against the fixture made from
+    the reference classes with their own weights: the 6-element list, shapes, a dense [B,(M,)S,D] z,
+    eps = (z - mu) / log_var, and -- with the fixture's noise handed in -- every returned tensor."""
+    F, vae_models = vk
+    tf32 = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+    torch.backends.cudnn.allow_tf32 = False; torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        fx, m = _load_forward_fixture(name, vae_models["MIWAE" if "hp_M" in load(name) else "IWAE"], DEV)
+        x = fx["in_input"].to(DEV)
+        B, D, K = x.shape[0], int(fx["hp_D"]), int(fx["hp_K"])
+        ss = (B, int(fx["hp_M"]), K) if "hp_M" in fx else (B, K)
+        with torch.no_grad():
+            torch.manual_seed(5)
+            out = m(x, labels=None)                              # forward must swallow labels= (experiment.py:36)
+        assert isinstance(out, list) and len(out) == 6 and out[1] is x
+        rec, _, mu, lv, z, eps = out
+        assert tuple(rec.shape) == ss + (3, 64, 64) and all(tuple(t.shape) == ss + (D,) for t in (mu, lv, z, eps))
+        assert z.is_contiguous() and rec.is_contiguous()
+        assert torch.equal(eps, (z - mu) / lv)
+        assert_close(mu, fx["out_mu"].to(DEV), 1e-4, "mu"); assert_close(lv, fx["out_log_var"].to(DEV), 1e-4, "log_var")
+        # the kernel's own noise: independent per sample (not one draw broadcast over the sample dims), and the same
+        # stream F.reparam_kl draws for the same generator state
+        n = (z - mu) * torch.exp(-0.5 * lv)
+        assert (n.flatten(1)[:, :D] - n.flatten(1)[:, D:2 * D]).abs().min().item() > 0
+        torch.manual_seed(5)
+        z2, _, n2 = F.reparam_kl(mu, lv, want_eps=True)
+        assert torch.equal(z2, z) and (n2 - n).abs().max().item() < 1e-5
+        # the fixture's noise handed in: every tensor of the reference's forward
+        inj = fx["noise_eps"].to(DEV)
+        m.reparameterize = lambda a, b: inj * torch.exp(0.5 * b) + a
+        with torch.no_grad():
+            out = m(x)
+            gen = m.generate(x)
+        for got, key in zip((out[0], out[2], out[3], out[4], out[5]), ("recons", "mu", "log_var", "z", "eps")):
+            assert_close(got, fx["out_" + key].to(DEV), 1e-4, key)
+        assert tuple(gen.shape) == (B, 3, 64, 64)
+        assert_close(gen, fx["out_generate"].to(DEV), 1e-4, "generate")
+        del m.reparameterize
+        with torch.no_grad():
+            s = m.sample(5, torch.device(DEV))
+        assert tuple(s.shape) == (5, 3, 64, 64)
+    finally:
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = tf32

@@ -250,3 +250,29 @@ def test_swd_full_size_stages(vk):
     print("full-size swd: gradient under a batch permutation differs by %.2e of its maximum (tied keys in the tails, "
           "where neighbouring prior order statistics are far apart)" % e)
     assert e <= 1e-3
+
+
+@pytest.mark.parametrize("p", [1.0, 3.0, 2.5])
+def test_swd_other_wasserstein_degrees(vk, p):
+    """swae.py:178 `w.pow(p)` for degrees other than the shipped p = 2: odd degrees keep the sign of the sorted difference
+    (the 'distance' can be negative, as in the reference), p = 1 has the constant gradient 1, and a fractional degree
+    turns negative differences into NaN exactly as torch.pow does."""
+    F, _ = vk
+    gen = torch.Generator().manual_seed(31 + int(10 * p))
+    n, D, S = 777, 24, 13
+    z = 1.5 * torch.randn(n, D, generator=gen) + 0.1
+    pz = torch.randn(n, D, generator=gen)
+    th = O.random_projections(D, S)
+    zc = leaf(z)
+    ref = O.swd(zc.double(), pz.double(), th.double(), p, 0.01)
+    zg = leaf(z.to(DEV))
+    s = F.swd(zg, pz.to(DEV), th.to(DEV), p, 0.01)
+    if p == 2.5:
+        assert torch.isnan(ref) and torch.isnan(s)
+        return
+    ref.backward()
+    s.backward()
+    assert_close(s, ref, TOL, "swd p=%g" % p)
+    clear = rank_clear_rows(z, th)
+    assert clear.float().mean() > 0.9
+    assert_close(zg.grad.cpu()[clear], zc.grad[clear], TOL, "d swd / dz p=%g" % p)
