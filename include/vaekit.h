@@ -79,6 +79,19 @@ int vk_reparam_kl_bwd(const float* g_z, const float* g_kl, const float* mu, cons
                       uint64_t seed, uint64_t offset,
                       float* g_mu, float* g_lv, void* stream);
 
+/* The same two entry points with (seed, offset) read from DEVICE memory (seed_offset[0], [1] as int64 bit patterns,
+ * like vk_philox_normal_dev): the pair is no launch argument, so a CUDA graph that captured these launches draws fresh
+ * noise on every replay once the caller advances seed_offset[1] on the device between replays (config 1 at
+ * batch 64 is launch-latency-bound and wants the whole step in one graph). */
+int vk_reparam_kl_fwd_dev(const float* mu, const float* log_var,
+                          const int64_t* outer_host, const int64_t* mu_strides_host,
+                          const int64_t* lv_strides_host, int64_t D, const int64_t* seed_offset,
+                          float* z, float* kl_rows, float* eps_out, void* stream);
+int vk_reparam_kl_bwd_dev(const float* g_z, const float* g_kl, const float* mu, const float* log_var,
+                          const int64_t* outer_host, const int64_t* mu_strides_host,
+                          const int64_t* lv_strides_host, int64_t D, const int64_t* seed_offset,
+                          float* g_mu, float* g_lv, void* stream);
+
 /* Standard-normal fill with the contract stream (prior_z of wae_mmd.py:195 / swae.py:165). */
 int vk_philox_normal(float* out, int64_t numel, uint64_t seed, uint64_t offset, void* stream);
 /* The same stream with (seed, offset) read from DEVICE memory (seed_offset[0], [1] as int64 bit patterns) and started
@@ -98,6 +111,10 @@ int vk_philox_raw(uint32_t* out, int64_t n_quads, uint64_t seed, uint64_t offset
  *   VK_RECON_MSE_SUM      sum((r-x)^2)
  *   VK_RECON_LOGCOSH      (1/alpha) * mean(alpha*t + log(1+exp(-2 alpha t)) - log 2), t = r-x
  *   VK_RECON_MSE_L1_MEAN  mean((r-x)^2) + mean(|r-x|)
+ *   VK_RECON_BCE_MEAN / VK_RECON_BCE_SUM   the "MSE/BCE" of the north star: the reference itself has no BCE term
+ *                         (SURVEY 0.5), so the contract is torch's F.binary_cross_entropy(recons, input, reduction=
+ *                         'mean' | 'sum'): -(x * max(log r, -100) + (1 - x) * max(log1p(-r), -100)); backward
+ *                         (r - x) / max((1 - r) r, 1e-12).  recons outside [0, 1] give NaN (torch raises).
  * combine_mode: what out[0] is (kld = mean(kl_rows); ignored when kl_rows is NULL)
  *   VK_COMBINE_NONE       out[0] = out[1]
  *   VK_COMBINE_LINEAR     out[0] = out[1] + w * kld
@@ -105,7 +122,8 @@ int vk_philox_raw(uint32_t* out, int64_t n_quads, uint64_t seed, uint64_t offset
  *   VK_COMBINE_SCALED     out[0] = C * out[1] + w * kld        (info_vae.py:131-132; applies without kl_rows too)
  * out[4] = { loss, recon_loss, kld, -kld }.
  * -------------------------------------------------------------------------*/
-enum { VK_RECON_MSE_MEAN = 0, VK_RECON_MSE_SUM = 1, VK_RECON_LOGCOSH = 2, VK_RECON_MSE_L1_MEAN = 3 };
+enum { VK_RECON_MSE_MEAN = 0, VK_RECON_MSE_SUM = 1, VK_RECON_LOGCOSH = 2, VK_RECON_MSE_L1_MEAN = 3, VK_RECON_BCE_MEAN = 4,
+       VK_RECON_BCE_SUM = 5 };
 enum { VK_COMBINE_NONE = 0, VK_COMBINE_LINEAR = 1, VK_COMBINE_ABS = 2, VK_COMBINE_SCALED = 3 };
 
 int vk_elbo_fwd(const float* recons, const float* input, int64_t numel,

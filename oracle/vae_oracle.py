@@ -121,6 +121,17 @@ def vanilla_loss(recons: Tensor, input: Tensor, mu: Tensor, log_var: Tensor, M_N
     return {"loss": loss, "Reconstruction_Loss": recons_loss.detach(), "KLD": -kld_loss.detach()}
 
 
+def bce_vanilla_loss(recons: Tensor, input: Tensor, mu: Tensor, log_var: Tensor, M_N: float,
+                     reduction: str = "mean") -> Dict[str, Tensor]:
+    """The north star's "MSE/BCE" variant of vanilla_vae.py:134-146.  The reference has no BCE term (its only
+    cross-entropy is FactorVAE's discriminator, fvae.py:197), so the contract is torch's own F.binary_cross_entropy in
+    place of the mse_loss of vanilla_vae.py:140 -- parity for this mode is pinned to torch, not to a reference line."""
+    recons_loss = F.binary_cross_entropy(recons, input, reduction=reduction)
+    kld_loss = torch.mean(kld_rows(mu, log_var), dim=0)
+    loss = recons_loss + M_N * kld_loss
+    return {"loss": loss, "Reconstruction_Loss": recons_loss.detach(), "KLD": -kld_loss.detach()}
+
+
 def cvae_loss(recons: Tensor, input: Tensor, mu: Tensor, log_var: Tensor, M_N: float) -> Dict[str, Tensor]:
     """cvae.py:131-146: the vanilla terms with neither side output detached."""
     recons_loss = F.mse_loss(recons, input)

@@ -14,7 +14,10 @@ constexpr float kLog2f = 0.69314718055994530942f;  // torch.log(torch.tensor(2.0
 template <int MODE>
 __device__ __forceinline__ void recon_accum(float r, float x, float alpha, float neg2alpha, float& s0, float& s1) {
   const float t = r - x;
-  if (MODE == VK_RECON_LOGCOSH) {
+  if (MODE == VK_RECON_BCE_MEAN) {
+    // F.binary_cross_entropy (ATen binary_cross_entropy kernel): both logs clamped at -100, log(1 - r) as log1p(-r)
+    s0 += (x - 1.0f) * fmaxf(log1pf(-r), -100.0f) - x * fmaxf(logf(r), -100.0f);
+  } else if (MODE == VK_RECON_LOGCOSH) {
     // literal (unstabilised) form of logcosh_vae.py:146-148 so overflow behaviour matches
     s0 += (alpha * t + logf(1.0f + expf(neg2alpha * t))) - kLog2f;
   } else {
@@ -36,6 +39,8 @@ __device__ __forceinline__ void elbo_finalize(const ElboParams& p, double s0, do
   switch (p.recon_mode) {
     case VK_RECON_MSE_MEAN: recon = (float)(s0 / n); break;
     case VK_RECON_MSE_SUM: recon = (float)s0; break;
+    case VK_RECON_BCE_MEAN: recon = (float)(s0 / n); break;
+    case VK_RECON_BCE_SUM: recon = (float)s0; break;
     case VK_RECON_LOGCOSH: recon = (1.0f / p.alpha) * (float)(s0 / n); break;
     default: recon = (float)(s0 / n) + (float)(s1 / n); break;
   }
@@ -117,7 +122,9 @@ __device__ __forceinline__ float sgnf(float v) { return (float)((v > 0.0f) - (v 
 template <int MODE>
 __device__ __forceinline__ float recon_grad(float r, float x, float c, float alpha, float neg2alpha) {
   const float t = r - x;
-  if (MODE == VK_RECON_LOGCOSH) {
+  if (MODE == VK_RECON_BCE_MEAN || MODE == VK_RECON_BCE_SUM) {
+    return c * (t / fmaxf((1.0f - r) * r, 1e-12f));      // binary_cross_entropy_backward: (r - x) / max((1 - r) r, 1e-12)
+  } else if (MODE == VK_RECON_LOGCOSH) {
     const float e = expf(neg2alpha * t);
     return c * (alpha + neg2alpha * (e / (1.0f + e)));   // c = g / (alpha * numel)
   } else if (MODE == VK_RECON_MSE_L1_MEAN) {
@@ -147,7 +154,7 @@ elbo_bwd_kernel(const float* __restrict__ recons, const float* __restrict__ inpu
   if (!g_recons) return;
   float c = (p.combine_mode == VK_COMBINE_SCALED ? gl * p.C : gl) + (g_recon ? *g_recon : 0.0f);
   if (MODE == VK_RECON_LOGCOSH) c = c / (p.alpha * (float)p.numel);
-  else if (MODE != VK_RECON_MSE_SUM) c = c / (float)p.numel;
+  else if (MODE != VK_RECON_MSE_SUM && MODE != VK_RECON_BCE_SUM) c = c / (float)p.numel;
   const bool vec = ((reinterpret_cast<uintptr_t>(recons) | reinterpret_cast<uintptr_t>(input) |
                      reinterpret_cast<uintptr_t>(g_recons)) & 15) == 0;
   const int64_t nvec = vec ? (p.numel >> 2) : 0;
@@ -200,7 +207,7 @@ extern "C" int vk_elbo_fwd(const float* recons, const float* input, int64_t nume
                            float* out, void* workspace, int64_t workspace_bytes, void* stream) {
   VK_REQUIRE(recons && input && out && workspace, VK_ERR_BAD_ARG, "elbo_fwd: null pointer");
   VK_REQUIRE(numel > 0 && rows >= 0, VK_ERR_BAD_ARG, "elbo_fwd: bad sizes");
-  VK_REQUIRE(recon_mode >= 0 && recon_mode <= 3 && combine_mode >= 0 && combine_mode <= 3, VK_ERR_BAD_ARG,
+  VK_REQUIRE(recon_mode >= 0 && recon_mode <= 5 && combine_mode >= 0 && combine_mode <= 3, VK_ERR_BAD_ARG,
              "elbo_fwd: unknown mode");
   VK_REQUIRE(workspace_bytes >= kWsBytes, VK_ERR_WORKSPACE, "elbo_fwd: workspace needs %lld bytes", (long long)kWsBytes);
   VK_REQUIRE(!kl_rows || rows > 0, VK_ERR_BAD_ARG, "elbo_fwd: kl_rows given but rows == 0");
@@ -215,6 +222,9 @@ extern "C" int vk_elbo_fwd(const float* recons, const float* input, int64_t nume
       elbo_fwd_kernel<VK_RECON_MSE_MEAN><<<grid, 256, 0, s>>>(recons, input, kl_rows, p, out, ticket, partials); break;
     case VK_RECON_LOGCOSH:
       elbo_fwd_kernel<VK_RECON_LOGCOSH><<<grid, 256, 0, s>>>(recons, input, kl_rows, p, out, ticket, partials); break;
+    case VK_RECON_BCE_MEAN:
+    case VK_RECON_BCE_SUM:
+      elbo_fwd_kernel<VK_RECON_BCE_MEAN><<<grid, 256, 0, s>>>(recons, input, kl_rows, p, out, ticket, partials); break;
     default:
       elbo_fwd_kernel<VK_RECON_MSE_L1_MEAN><<<grid, 256, 0, s>>>(recons, input, kl_rows, p, out, ticket, partials); break;
   }
@@ -227,7 +237,7 @@ extern "C" int vk_elbo_bwd(const float* recons, const float* input, int64_t nume
                            float* g_kl_rows, void* stream) {
   VK_REQUIRE(recons && input && out, VK_ERR_BAD_ARG, "elbo_bwd: null pointer");
   VK_REQUIRE(numel > 0 && rows >= 0, VK_ERR_BAD_ARG, "elbo_bwd: bad sizes");
-  VK_REQUIRE(recon_mode >= 0 && recon_mode <= 3 && combine_mode >= 0 && combine_mode <= 3, VK_ERR_BAD_ARG,
+  VK_REQUIRE(recon_mode >= 0 && recon_mode <= 5 && combine_mode >= 0 && combine_mode <= 3, VK_ERR_BAD_ARG,
              "elbo_bwd: unknown mode");
   if (!g_recons && !g_kl_rows) return VK_OK;
   ElboParams p{recon_mode, combine_mode, alpha, w, C, numel, rows};
@@ -240,6 +250,10 @@ extern "C" int vk_elbo_bwd(const float* recons, const float* input, int64_t nume
       elbo_bwd_kernel<VK_RECON_MSE_SUM><<<grid, 256, 0, s>>>(recons, input, p, out, g_loss, g_recon, g_kld, g_negkld, g_recons, g_kl_rows); break;
     case VK_RECON_LOGCOSH:
       elbo_bwd_kernel<VK_RECON_LOGCOSH><<<grid, 256, 0, s>>>(recons, input, p, out, g_loss, g_recon, g_kld, g_negkld, g_recons, g_kl_rows); break;
+    case VK_RECON_BCE_MEAN:
+      elbo_bwd_kernel<VK_RECON_BCE_MEAN><<<grid, 256, 0, s>>>(recons, input, p, out, g_loss, g_recon, g_kld, g_negkld, g_recons, g_kl_rows); break;
+    case VK_RECON_BCE_SUM:
+      elbo_bwd_kernel<VK_RECON_BCE_SUM><<<grid, 256, 0, s>>>(recons, input, p, out, g_loss, g_recon, g_kld, g_negkld, g_recons, g_kl_rows); break;
     default:
       elbo_bwd_kernel<VK_RECON_MSE_L1_MEAN><<<grid, 256, 0, s>>>(recons, input, p, out, g_loss, g_recon, g_kld, g_negkld, g_recons, g_kl_rows); break;
   }

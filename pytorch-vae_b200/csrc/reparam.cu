@@ -39,8 +39,9 @@ __device__ __forceinline__ float kl_term(float mu, float lv, float elv) {
 template <bool VEC>
 __global__ void __launch_bounds__(256)
 reparam_kl_fwd_kernel(const float* __restrict__ mu, const float* __restrict__ lv, RowMap m, int gs,
-                      uint64_t seed, uint64_t offset, float* __restrict__ z, float* __restrict__ kl_rows,
-                      float* __restrict__ eps_out) {
+                      uint64_t seed, uint64_t offset, const int64_t* __restrict__ key, float* __restrict__ z,
+                      float* __restrict__ kl_rows, float* __restrict__ eps_out) {
+  if (key) { seed = (uint64_t)key[0]; offset = (uint64_t)key[1]; }      // (seed, offset) held on the device: graph-replayable
   const int lane = threadIdx.x & 31;
   const int rpw = 32 / gs;                      // rows per warp
   const int sub = lane % gs;
@@ -98,7 +99,9 @@ template <bool VEC>
 __global__ void __launch_bounds__(256)
 reparam_kl_bwd_kernel(const float* __restrict__ g_z, const float* __restrict__ g_kl,
                       const float* __restrict__ mu, const float* __restrict__ lv, RowMap m, int gs,
-                      uint64_t seed, uint64_t offset, float* __restrict__ g_mu, float* __restrict__ g_lv) {
+                      uint64_t seed, uint64_t offset, const int64_t* __restrict__ key, float* __restrict__ g_mu,
+                      float* __restrict__ g_lv) {
+  if (key) { seed = (uint64_t)key[0]; offset = (uint64_t)key[1]; }
   const int lane = threadIdx.x & 31;
   const int rpw = 32 / gs;
   const int sub = lane % gs;
@@ -218,10 +221,10 @@ static int group_size(int64_t work_items) {  // smallest power of two >= work_it
 
 using namespace vk;
 
-extern "C" int vk_reparam_kl_fwd(const float* mu, const float* log_var, const int64_t* outer_host,
-                                 const int64_t* mu_strides_host, const int64_t* lv_strides_host, int64_t D,
-                                 uint64_t seed, uint64_t offset, float* z, float* kl_rows, float* eps_out,
-                                 void* stream) {
+static int reparam_fwd(const float* mu, const float* log_var, const int64_t* outer_host,
+                       const int64_t* mu_strides_host, const int64_t* lv_strides_host, int64_t D,
+                       uint64_t seed, uint64_t offset, const int64_t* key, float* z, float* kl_rows, float* eps_out,
+                       void* stream) {
   VK_REQUIRE(mu && log_var, VK_ERR_BAD_ARG, "reparam_kl_fwd: null mu/log_var");
   VK_REQUIRE(z || kl_rows || eps_out, VK_ERR_BAD_ARG, "reparam_kl_fwd: no output requested");
   RowMap m;
@@ -235,16 +238,33 @@ extern "C" int vk_reparam_kl_fwd(const float* mu, const float* log_var, const in
   VK_REQUIRE(blocks < (1ll << 31), VK_ERR_UNSUPPORTED, "reparam_kl_fwd: too many rows");
   cudaStream_t s = (cudaStream_t)stream;
   if (vec)
-    reparam_kl_fwd_kernel<true><<<(unsigned)blocks, 256, 0, s>>>(mu, log_var, m, gs, seed, offset, z, kl_rows, eps_out);
+    reparam_kl_fwd_kernel<true><<<(unsigned)blocks, 256, 0, s>>>(mu, log_var, m, gs, seed, offset, key, z, kl_rows, eps_out);
   else
-    reparam_kl_fwd_kernel<false><<<(unsigned)blocks, 256, 0, s>>>(mu, log_var, m, gs, seed, offset, z, kl_rows, eps_out);
+    reparam_kl_fwd_kernel<false><<<(unsigned)blocks, 256, 0, s>>>(mu, log_var, m, gs, seed, offset, key, z, kl_rows, eps_out);
   return check_launch("reparam_kl_fwd");
 }
 
-extern "C" int vk_reparam_kl_bwd(const float* g_z, const float* g_kl, const float* mu, const float* log_var,
-                                 const int64_t* outer_host, const int64_t* mu_strides_host,
-                                 const int64_t* lv_strides_host, int64_t D, uint64_t seed, uint64_t offset,
-                                 float* g_mu, float* g_lv, void* stream) {
+extern "C" int vk_reparam_kl_fwd(const float* mu, const float* log_var, const int64_t* outer_host,
+                                 const int64_t* mu_strides_host, const int64_t* lv_strides_host, int64_t D,
+                                 uint64_t seed, uint64_t offset, float* z, float* kl_rows, float* eps_out,
+                                 void* stream) {
+  return reparam_fwd(mu, log_var, outer_host, mu_strides_host, lv_strides_host, D, seed, offset, nullptr, z, kl_rows,
+                     eps_out, stream);
+}
+
+extern "C" int vk_reparam_kl_fwd_dev(const float* mu, const float* log_var, const int64_t* outer_host,
+                                     const int64_t* mu_strides_host, const int64_t* lv_strides_host, int64_t D,
+                                     const int64_t* seed_offset, float* z, float* kl_rows, float* eps_out,
+                                     void* stream) {
+  VK_REQUIRE(seed_offset, VK_ERR_BAD_ARG, "reparam_kl_fwd_dev: null (seed, offset) pointer");
+  return reparam_fwd(mu, log_var, outer_host, mu_strides_host, lv_strides_host, D, 0, 0, seed_offset, z, kl_rows,
+                     eps_out, stream);
+}
+
+static int reparam_bwd(const float* g_z, const float* g_kl, const float* mu, const float* log_var,
+                       const int64_t* outer_host, const int64_t* mu_strides_host,
+                       const int64_t* lv_strides_host, int64_t D, uint64_t seed, uint64_t offset, const int64_t* key,
+                       float* g_mu, float* g_lv, void* stream) {
   VK_REQUIRE(mu && log_var && g_mu && g_lv, VK_ERR_BAD_ARG, "reparam_kl_bwd: null pointer");
   RowMap m;
   int rc = make_rowmap(outer_host, mu_strides_host, lv_strides_host, D, m);
@@ -257,10 +277,27 @@ extern "C" int vk_reparam_kl_bwd(const float* g_z, const float* g_kl, const floa
   VK_REQUIRE(blocks < (1ll << 31), VK_ERR_UNSUPPORTED, "reparam_kl_bwd: too many rows");
   cudaStream_t s = (cudaStream_t)stream;
   if (vec)
-    reparam_kl_bwd_kernel<true><<<(unsigned)blocks, 256, 0, s>>>(g_z, g_kl, mu, log_var, m, gs, seed, offset, g_mu, g_lv);
+    reparam_kl_bwd_kernel<true><<<(unsigned)blocks, 256, 0, s>>>(g_z, g_kl, mu, log_var, m, gs, seed, offset, key, g_mu, g_lv);
   else
-    reparam_kl_bwd_kernel<false><<<(unsigned)blocks, 256, 0, s>>>(g_z, g_kl, mu, log_var, m, gs, seed, offset, g_mu, g_lv);
+    reparam_kl_bwd_kernel<false><<<(unsigned)blocks, 256, 0, s>>>(g_z, g_kl, mu, log_var, m, gs, seed, offset, key, g_mu, g_lv);
   return check_launch("reparam_kl_bwd");
+}
+
+extern "C" int vk_reparam_kl_bwd(const float* g_z, const float* g_kl, const float* mu, const float* log_var,
+                                 const int64_t* outer_host, const int64_t* mu_strides_host,
+                                 const int64_t* lv_strides_host, int64_t D, uint64_t seed, uint64_t offset,
+                                 float* g_mu, float* g_lv, void* stream) {
+  return reparam_bwd(g_z, g_kl, mu, log_var, outer_host, mu_strides_host, lv_strides_host, D, seed, offset, nullptr, g_mu,
+                     g_lv, stream);
+}
+
+extern "C" int vk_reparam_kl_bwd_dev(const float* g_z, const float* g_kl, const float* mu, const float* log_var,
+                                     const int64_t* outer_host, const int64_t* mu_strides_host,
+                                     const int64_t* lv_strides_host, int64_t D, const int64_t* seed_offset,
+                                     float* g_mu, float* g_lv, void* stream) {
+  VK_REQUIRE(seed_offset, VK_ERR_BAD_ARG, "reparam_kl_bwd_dev: null (seed, offset) pointer");
+  return reparam_bwd(g_z, g_kl, mu, log_var, outer_host, mu_strides_host, lv_strides_host, D, 0, 0, seed_offset, g_mu, g_lv,
+                     stream);
 }
 
 extern "C" int vk_philox_normal(float* out, int64_t numel, uint64_t seed, uint64_t offset, void* stream) {

@@ -21,6 +21,8 @@ _SIGNATURES = {
     "vk_workspace_bytes": ([], _i64),
     "vk_reparam_kl_fwd": ([_p, _p, _p, _p, _p, _i64, _u64, _u64, _p, _p, _p, _p], _i),
     "vk_reparam_kl_bwd": ([_p, _p, _p, _p, _p, _p, _p, _i64, _u64, _u64, _p, _p, _p], _i),
+    "vk_reparam_kl_fwd_dev": ([_p, _p, _p, _p, _p, _i64, _p, _p, _p, _p, _p], _i),
+    "vk_reparam_kl_bwd_dev": ([_p, _p, _p, _p, _p, _p, _p, _i64, _p, _p, _p, _p], _i),
     "vk_philox_normal": ([_p, _i64, _u64, _u64, _p], _i),
     "vk_philox_normal_dev": ([_p, _i64, _p, _i64, _p], _i),
     "vk_philox_raw": ([_p, _i64, _u64, _u64, _p], _i),

@@ -4,7 +4,7 @@ import torch
 
 from . import _lib as L
 
-RECON_MSE_MEAN, RECON_MSE_SUM, RECON_LOGCOSH, RECON_MSE_L1_MEAN = 0, 1, 2, 3
+RECON_MSE_MEAN, RECON_MSE_SUM, RECON_LOGCOSH, RECON_MSE_L1_MEAN, RECON_BCE_MEAN, RECON_BCE_SUM = 0, 1, 2, 3, 4, 5
 COMBINE_NONE, COMBINE_LINEAR, COMBINE_ABS, COMBINE_SCALED = 0, 1, 2, 3
 
 
@@ -19,6 +19,56 @@ def next_philox(device, numel):
     quads = (int(numel) + 3) // 4
     gen.set_offset(offset + ((quads + 3) // 4) * 4)     # torch requires multiples of 4
     return seed & 0xFFFFFFFFFFFFFFFF, offset
+
+
+# (seed, offset) held ON THE DEVICE: the pair is no launch argument, so a CUDA graph that captured the noise kernels draws
+# fresh noise on every replay (vk_reparam_kl_fwd_dev / vk_philox_normal_dev).
+_DEVICE_KEYS = {}
+
+
+def make_rng_key(device):
+    """int64 CUDA tensor [2] = (seed, offset) taken from torch's CUDA generator for `device` (torch.manual_seed governs
+    it); create it OUTSIDE a graph capture."""
+    device = torch.device(device)
+    seed, offset = next_philox(device, 0)
+    if seed >= 1 << 63:
+        seed -= 1 << 64
+    return torch.tensor([seed, offset], dtype=torch.int64, device=device)
+
+
+class device_rng:
+    """`with device_rng(key):` -- every noise draw of reparam_kl / philox_normal inside the block reads (seed, offset)
+    from `key` on the device and advances key[1] there (two tiny captured torch ops per draw), instead of passing the
+    pair by value.  Capture a whole training step in a CUDA graph inside this block and every replay gets new noise."""
+
+    def __init__(self, key):
+        if key.dtype != torch.int64 or not key.is_cuda or key.numel() != 2:
+            raise RuntimeError("vaekit: rng key must be an int64 CUDA tensor with two elements (make_rng_key)")
+        self.key, self.index = key, key.device.index
+
+    def __enter__(self):
+        self.prev = _DEVICE_KEYS.get(self.index)
+        _DEVICE_KEYS[self.index] = self.key
+        return self.key
+
+    def __exit__(self, *exc):
+        if self.prev is None:
+            _DEVICE_KEYS.pop(self.index, None)
+        else:
+            _DEVICE_KEYS[self.index] = self.prev
+        return False
+
+
+def _draw_device_key(device, numel):
+    """Snapshot of the active device key for one draw of `numel` elements (None outside device_rng); the key advances by
+    the same multiple-of-4 quad count next_philox reserves on the host generator."""
+    key = _DEVICE_KEYS.get(device.index if device.index is not None else torch.cuda.current_device())
+    if key is None:
+        return None
+    snap = key.clone()
+    quads = (int(numel) + 3) // 4
+    key[1] += ((quads + 3) // 4) * 4
+    return snap
 
 
 def _row_layout(t):
@@ -52,8 +102,12 @@ class _ReparamKL(torch.autograd.Function):
         eps = torch.empty(mu.shape, dtype=torch.float32, device=dev) if want_eps else None
         if rows * D > 0:
             with L.on(dev):
-                L.call("reparam_kl_fwd", L.ptr(mu_v), L.ptr(lv_v), L.i64x3(outer), L.i64x3(ms), L.i64x3(ls), D,
-                                               seed, offset, L.ptr(z), L.ptr(kl), L.ptr(eps), L.stream_ptr())
+                if isinstance(seed, torch.Tensor):          # (seed, offset) on the device
+                    L.call("reparam_kl_fwd_dev", L.ptr(mu_v), L.ptr(lv_v), L.i64x3(outer), L.i64x3(ms), L.i64x3(ls), D,
+                           L.ptr(seed), L.ptr(z), L.ptr(kl), L.ptr(eps), L.stream_ptr())
+                else:
+                    L.call("reparam_kl_fwd", L.ptr(mu_v), L.ptr(lv_v), L.i64x3(outer), L.i64x3(ms), L.i64x3(ls), D,
+                           seed, offset, L.ptr(z), L.ptr(kl), L.ptr(eps), L.stream_ptr())
         ctx.save_for_backward(mu, log_var)
         ctx.rng = (seed, offset)
         ctx.had_z = want_z
@@ -76,9 +130,12 @@ class _ReparamKL(torch.autograd.Function):
             g_kl = g_kl.contiguous()
         if g_mu.numel() > 0:
             with L.on(dev):
-                L.call("reparam_kl_bwd", L.ptr(g_z), L.ptr(g_kl), L.ptr(mu_v), L.ptr(lv_v), L.i64x3(outer),
-                                               L.i64x3(ms), L.i64x3(ls), D, ctx.rng[0], ctx.rng[1], L.ptr(g_mu),
-                                               L.ptr(g_lv), L.stream_ptr())
+                if isinstance(ctx.rng[0], torch.Tensor):
+                    L.call("reparam_kl_bwd_dev", L.ptr(g_z), L.ptr(g_kl), L.ptr(mu_v), L.ptr(lv_v), L.i64x3(outer),
+                           L.i64x3(ms), L.i64x3(ls), D, L.ptr(ctx.rng[0]), L.ptr(g_mu), L.ptr(g_lv), L.stream_ptr())
+                else:
+                    L.call("reparam_kl_bwd", L.ptr(g_z), L.ptr(g_kl), L.ptr(mu_v), L.ptr(lv_v), L.i64x3(outer),
+                           L.i64x3(ms), L.i64x3(ls), D, ctx.rng[0], ctx.rng[1], L.ptr(g_mu), L.ptr(g_lv), L.stream_ptr())
         return g_mu, g_lv, None, None, None, None, None
 
 
@@ -86,7 +143,10 @@ def reparam_kl(mu, log_var, *, rng=None, want_kl=True, want_eps=False):
     """z = eps*exp(0.5*logvar)+mu with the KL rows as a fused second output.
     Returns (z, kl_rows, eps_or_None); rng = (seed, offset) or None to draw from torch's generator."""
     if rng is None:
-        rng = next_philox(mu.device, mu.numel())
+        key = _draw_device_key(mu.device, mu.numel()) if mu.is_cuda else None
+        rng = (key, 0) if key is not None else next_philox(mu.device, mu.numel())
+    elif isinstance(rng, torch.Tensor):
+        rng = (rng, 0)
     return _ReparamKL.apply(mu, log_var, rng[0], rng[1], True, want_kl, want_eps)
 
 
@@ -99,6 +159,9 @@ def philox_normal(shape, device, rng=None):
     """Standard normals from the contract stream (the prior_z draws of WAE / SWAE)."""
     out = torch.empty(shape, dtype=torch.float32, device=device)
     if rng is None:
+        key = _draw_device_key(out.device, out.numel()) if out.is_cuda else None
+        if key is not None:
+            return philox_normal_dev(shape, key)
         rng = next_philox(out.device, out.numel())
     with L.on(out.device):
         L.call("philox_normal", L.ptr(out), out.numel(), rng[0], rng[1], L.stream_ptr())
@@ -156,6 +219,8 @@ class _Elbo(torch.autograd.Function):
         recon_mode, alpha, combine_mode, w, C, kl_shape = ctx.cfg
         dev = r.device
         need_r, need_x, need_kl = ctx.needs_input_grad[0], ctx.needs_input_grad[1], ctx.needs_input_grad[2]
+        if need_x and recon_mode in (RECON_BCE_MEAN, RECON_BCE_SUM):
+            raise RuntimeError("vaekit: gradient w.r.t. the target image of the BCE term is not provided")
         g_rec = torch.empty_like(r) if (need_r or need_x) else None
         g_kl = torch.empty(kl_shape, dtype=torch.float32, device=dev) if (need_kl and kl_shape is not None) else None
         gs = [None if g is None else g.contiguous() for g in (g0, g1, g2, g3)]
@@ -770,6 +835,8 @@ def gumbel_softmax(q, temp, eps=1e-7, *, rng=None, uniforms=None, want_uniforms=
     """cat_vae.py:118-131 on logits [..., C]: softmax((q + gumbel) / temp, -1), same shape as q.  The uniforms come from the
     contract Philox stream (torch.manual_seed governs them) unless `uniforms` is given.  Returns (s, uniforms or None)."""
     if rng is None:
+        if q.is_cuda and uniforms is None and _DEVICE_KEYS.get(q.device.index) is not None:
+            raise RuntimeError("vaekit: gumbel_softmax has no device-key entry point yet; pass uniforms= inside device_rng()")
         rng = next_philox(q.device, q.numel()) if q.is_cuda and uniforms is None else (0, 0)
     return _GumbelSoftmax.apply(q, float(temp), float(eps), rng[0], rng[1], uniforms, bool(want_uniforms))
 

@@ -444,3 +444,89 @@ def test_iw_forward_contract_and_fixture(vk, name):
         assert tuple(s.shape) == (5, 3, 64, 64)
     finally:
         torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = tf32
+
+
+@pytest.mark.parametrize("reduction", ["mean", "sum"])
+def test_bce_reconstruction_mode(vk, reduction):
+    """North star kernel (1) "MSE/BCE": F.binary_cross_entropy semantics incl. the clamp of both logs at -100 (recons
+    exactly 0 / 1) and the 1e-12 floor of the backward's denominator; oracle = torch's own op (the reference has no BCE)."""
+    F, vae_models = vk
+    g = torch.Generator().manual_seed(77)
+    r = torch.sigmoid(2 * torch.randn(6, 3, 16, 16, generator=g)); x = torch.rand(6, 3, 16, 16, generator=g)
+    r.view(-1)[:4] = torch.tensor([0.0, 1.0, 1e-30, 1 - 1e-7])                    # clamp / floor cases
+    x.view(-1)[:2] = torch.tensor([1.0, 0.0])                                     # log(0) with a non-zero weight
+    mu = torch.randn(6, 16, generator=g); lv = 0.5 * torch.randn(6, 16, generator=g) - 1
+    rc, mc, vc = leaf(r), leaf(mu), leaf(lv)
+    ref = O.bce_vanilla_loss(rc, x, mc, vc, 0.005, reduction=reduction)
+    ref["loss"].backward()
+    rg, mg, vg = leaf(r.to(DEV)), leaf(mu.to(DEV)), leaf(lv.to(DEV))
+    mode = F.RECON_BCE_MEAN if reduction == "mean" else F.RECON_BCE_SUM
+    loss, rec, _, negkld = F.elbo(rg, x.to(DEV), F.kl_rows(mg, vg), recon_mode=mode, combine_mode=F.COMBINE_LINEAR, w=0.005)
+    loss.backward()
+    assert_close(loss, ref["loss"], TOL); assert_close(rec, ref["Reconstruction_Loss"], TOL); assert_close(negkld, ref["KLD"], TOL)
+    # the floor cases produce gradients of 1e12 magnitude: compare them element-wise relative, the rest in max norm
+    big = rc.grad.abs() > 1e3
+    assert torch.allclose(rg.grad.cpu()[big], rc.grad[big], rtol=1e-5)
+    assert_close(rg.grad.cpu()[~big], rc.grad[~big], TOL)
+    assert_close(mg.grad, mc.grad, TOL); assert_close(vg.grad, vc.grad, TOL)
+    if reduction == "mean":                                                       # through the drop-in model
+        m = vae_models["VanillaVAE"](3, 16, recons_loss="bce")
+        d = m.loss_function(r.to(DEV), x.to(DEV), mu.to(DEV), lv.to(DEV), M_N=0.005)
+        for k in d:
+            assert_close(d[k], ref[k], TOL, k)
+        with pytest.raises(ValueError):
+            vae_models["VanillaVAE"](3, 16, recons_loss="l7")
+
+
+def test_device_rng_key_and_graph_replay(vk):
+    """(seed, offset) read from device memory (vk_reparam_kl_fwd_dev / _bwd_dev).  Same stream as the
+    by-value entry points; a CUDA graph that captured reparameterize + loss + backward draws NEW noise on every replay
+    because the key advances on the device, and its backward regenerates the noise of its own forward."""
+    F, vae_models = vk
+    dev = torch.device(DEV)
+    g = torch.Generator(device=DEV).manual_seed(3)
+    B, D = 64, 128
+    mu = torch.randn(B, D, device=DEV, generator=g); lv = 0.5 * torch.randn(B, D, device=DEV, generator=g) - 1
+    key = torch.tensor([1265, 40], dtype=torch.int64, device=DEV)
+    z_val, _, e_val = F.reparam_kl(mu, lv, rng=(1265, 40), want_eps=True)
+    z_dev, _, e_dev = F.reparam_kl(mu, lv, rng=key.clone(), want_eps=True)
+    assert torch.equal(z_val, z_dev) and torch.equal(e_val, e_dev)
+    # graph: static inputs, the model's own reparameterize + loss + backward inside device_rng
+    m = vae_models["VanillaVAE"](3, D)
+    r = torch.tanh(torch.randn(B, 3, 64, 64, device=DEV, generator=g)); x = torch.rand(B, 3, 64, 64, device=DEV, generator=g)
+    mus, lvs = leaf(mu), leaf(lv)
+    gz = torch.randn(B, D, device=DEV, generator=g)
+    key = F.make_rng_key(dev)
+    key0 = key.clone()
+
+    def step():
+        mus.grad = lvs.grad = None
+        z = m.reparameterize(mus, lvs)
+        d = m.loss_function(r, x, mus, lvs, M_N=0.005)
+        torch.autograd.backward([d["loss"], z], [None, gz])
+        return z, d["loss"]
+
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s), F.device_rng(key):
+        for _ in range(2):
+            step()
+    torch.cuda.current_stream().wait_stream(s)
+    graph = torch.cuda.CUDAGraph()
+    mus.grad = lvs.grad = None
+    with F.device_rng(key):
+        with torch.cuda.graph(graph, stream=s):             # the warmed-up stream: its workspace already exists
+            z_out, loss_out = step()
+    zs, gls = [], []
+    for _ in range(3):
+        k_before = key.clone()
+        graph.replay()
+        torch.cuda.synchronize()
+        zs.append(z_out.clone()); gls.append(lvs.grad.clone())
+        # this replay's forward AND backward used the key as it stood before the replay
+        z_chk, _, eps = F.reparam_kl(mu, lv, rng=k_before, want_eps=True)
+        assert torch.equal(z_chk, z_out)
+        want_glv = gz * eps * 0.5 * torch.exp(0.5 * lv) - 0.5 * (0.005 / B) * (1 - torch.exp(lv))
+        assert_close(lvs.grad, want_glv, TOL)
+        assert int(key[1]) == int(k_before[1]) + B * D // 4 and int(key[0]) == int(key0[0])
+    assert not torch.equal(zs[0], zs[1]) and not torch.equal(zs[1], zs[2])
