@@ -1,17 +1,28 @@
 #!/usr/bin/env python
-"""Benchmark of the latent + loss hot path (BASELINE.json metric: samples/s fwd+bwd).
+"""Benchmark of the latent + loss hot path (BASELINE.json metric: samples/s fwd+bwd; % of HBM / tensor roofline).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload iwae|miwae|vanilla] [--impl reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload all|<name>] [--impl reference]
 
-Default workload = BASELINE.json configs[1]: IWAE K=5, batch 4096, latent 128, 64x64 RGB --
-reparameterize + importance-weighted bound, forward + backward, on synthetic tensors.
-One JSON line on stdout (rank 0).  Under torchrun each rank owns its own batch of 4096
-(weak scaling, no data-path collective: the op is batch-local).
+ONE invocation times every BASELINE.json config (and BetaTC) and prints ONE JSON line on stdout (rank 0):
+
+  top level   = BASELINE configs[2], the config the north star puts its multi-GPU target on: WAE-MMD RBF, z batch
+                65536 x 128, value + d/dz through the drop-in model API.  Under torchrun it is the row-sharded form
+                (all-gather of z, 128-aligned row blocks per rank): "scaling": "strong".
+  "workloads" = {name: {value, ms_per_step, roofline, cpu_baseline, e2e, clocks, ...}} for the other configs:
+                wae_mmd_imq, iwae, miwae (configs[1]), vanilla_b64 (configs[0] as BASELINE words it: full model(x) +
+                loss_function + backward at batch 64), vanilla (the same loss at streaming size), vq (configs[3]),
+                swae (configs[4]), betatc (SURVEY 8(d) extra).  Under torchrun: the strong-scaled sharded MMD / SWD /
+                BetaTC paths plus the batch-local ops as weak-scaled replicas.
+
+Every workload: W (>= 3) warm-up steps, K timed steps between two CUDA events on the launching stream (max over ranks),
+then the same K steps again with CUDA events around every library call for the roofline of the dominant call, then the
+end-to-end leg (pinned host inputs copied in and the loss read back every step), then -- rank 0, one GPU only -- the
+reference's CPU formulation (oracle port) on a bounded sample.  `--impl reference` times that CPU path for the top-level
+workload with the same K / W.
 """
 import argparse
 import json
 import os
-import subprocess
 import sys
 import threading
 import time
@@ -24,20 +35,30 @@ for p in (os.path.join(ROOT, "pytorch-vae_b200"),):
 import torch  # noqa: E402
 
 P_IMG = 3 * 64 * 64
-WORKLOADS = {
-    # name: (B, G, K, D, M_N)
-    "iwae": dict(B=4096, G=1, K=5, D=128, M_N=0.00025, desc="IWAE K=5, batch 4096, latent 128, 3x64x64 (BASELINE configs[1])"),
-    "miwae": dict(B=4096, G=3, K=5, D=128, M_N=0.00025, desc="MIWAE K=5 M=3, batch 4096, latent 128, 3x64x64 (BASELINE configs[1])"),
-    "vanilla": dict(B=65536, G=0, K=0, D=128, M_N=0.005, desc="VanillaVAE loss, batch 65536, latent 128, 3x64x64 (config 1 at streaming size)"),
-}
+METRIC = "latent+loss samples/s fwd+bwd"
+HEADLINE = "wae_mmd_rbf"
 
 
-def peaks():
+def _peaks_file():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
-            return float(json.load(f)["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (measured)"
+            return json.load(f)
     except Exception:
-        return 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
+        return None
+
+
+def hbm_peak():
+    pk = _peaks_file()
+    if pk and "hbm_gbs" in pk:
+        return float(pk["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (measured copy bandwidth)"
+    return 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
+
+
+def bf16_peak():
+    pk = _peaks_file()
+    if pk and "bf16_tflops_sustained" in pk:
+        return float(pk["bf16_tflops_sustained"]), "MEASURED_PEAKS.json bf16_tflops_sustained (kernel timed inside a long step)"
+    return 1400.0, "fallback 1.4 PFLOP/s sustained (B200_PROFILING.md)"
 
 
 class ClockSampler:
@@ -60,6 +81,7 @@ class ClockSampler:
             self.thread.start()
         except Exception as e:          # no NVML: report it rather than invent numbers
             self.err = repr(e)
+        return self
 
     def _run(self):
         nv = self.nv
@@ -92,351 +114,246 @@ class ClockSampler:
 
 
 def dist_env():
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    return rank, world, local
+    return int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
 
 
-# ---------------------------------------------------------------------------
+def oracle():
+    """The CPU oracle: test infrastructure, used here only for the cpu_baseline / --impl reference legs."""
+    p = os.path.join(ROOT, "oracle")
+    if p not in sys.path:
+        sys.path.insert(0, p)
+    import vae_oracle
+    return vae_oracle
+
+
+# =====================================================================================================================
 # workloads
-# ---------------------------------------------------------------------------
-def sample_shape(wl, B):
-    if wl["K"] == 0:
-        return (B,)
-    return (B, wl["G"], wl["K"]) if wl["G"] > 1 else (B, wl["K"])
-
-
-def make_host_inputs(wl, B, seed, pin):
-    g = torch.Generator().manual_seed(seed)
-    ss = sample_shape(wl, B)
-    t = {
-        "recons": torch.tanh(torch.randn(*ss, 3, 64, 64, generator=g)),       # decoder ends in Tanh
-        "input": torch.rand(B, 3, 64, 64, generator=g),                       # ToTensor range
-        "mu0": torch.randn(B, wl["D"], generator=g),
-        "lv0": 0.5 * torch.randn(B, wl["D"], generator=g) - 1.0,
-        "gz": 1e-3 * torch.randn(*ss, wl["D"], generator=g),                  # upstream grad of z (decoder bwd)
-    }
-    if pin:
-        t = {k: v.pin_memory() for k, v in t.items()}
-    return t
-
-
-def make_device_inputs(wl, B, seed, dev):
-    """Synthetic tensors generated on the device (fast for 1-3 GB), same distributions."""
-    g = torch.Generator(device=dev).manual_seed(seed)
-    ss = sample_shape(wl, B)
-    return {
-        "recons": torch.tanh(torch.randn(*ss, 3, 64, 64, device=dev, generator=g)),
-        "input": torch.rand(B, 3, 64, 64, device=dev, generator=g),
-        "mu0": torch.randn(B, wl["D"], device=dev, generator=g),
-        "lv0": 0.5 * torch.randn(B, wl["D"], device=dev, generator=g) - 1.0,
-        "gz": 1e-3 * torch.randn(*ss, wl["D"], device=dev, generator=g),
-    }
-
-
-def expand_latents(wl, mu0, lv0):
-    if wl["K"] == 0:
-        return mu0, lv0
-    if wl["G"] > 1:
-        shp = (-1, wl["G"], wl["K"], -1)
-        return mu0.view(mu0.size(0), 1, 1, -1).expand(*shp), lv0.view(lv0.size(0), 1, 1, -1).expand(*shp)
-    return mu0.unsqueeze(1).expand(-1, wl["K"], -1), lv0.unsqueeze(1).expand(-1, wl["K"], -1)
-
-
-def hot_path_step(model, wl, t):
-    """One pass of the hot path through the public model API: reparameterize -> loss_function -> backward."""
-    recons = t["recons"].requires_grad_(True)
-    mu0 = t["mu0"].requires_grad_(True)
-    lv0 = t["lv0"].requires_grad_(True)
-    recons.grad = mu0.grad = lv0.grad = None
-    mu, lv = expand_latents(wl, mu0, lv0)
-    z = model.reparameterize(mu, lv)
-    if wl["K"] == 0:
-        d = model.loss_function(recons, t["input"], mu, lv, M_N=wl["M_N"])
-    else:
-        d = model.loss_function(recons, t["input"], mu, lv, z, None, M_N=wl["M_N"])
-    torch.autograd.backward([d["loss"], z], [None, t["gz"]])
-    return d
-
-
-def algorithmic_bytes(wl, B):
-    """bytes one step must move (fp32)."""
-    D = wl["D"]
-    if wl["K"] == 0:
-        return B * (5 * P_IMG * 4 + 8 * D * 4)
-    GK = max(wl["G"], 1) * wl["K"]
-    recon = B * ((GK * P_IMG + P_IMG) * 4 * 2 + GK * P_IMG * 4)          # fwd read, bwd read + write g_recons
-    lat = B * (2 * D * 4 * 2 + GK * D * 4 * 4)                           # mu0/lv0 read twice; z, g_z, g_mu, g_lv rows
-    return recon + lat
-
-
-def build_model(name):
-    from vaekit.models import vae_models
-    if name == "iwae":
-        return vae_models["IWAE"](3, 128, num_samples=5)
-    if name == "miwae":
-        return vae_models["MIWAE"](3, 128, num_samples=5, num_estimates=3)
-    return vae_models["VanillaVAE"](3, 128)
-
-
-KERNEL_BYTES = {
-    # kernel -> algorithmic bytes per launch as a function of the workload (fp32), SURVEY.md 8(d) / DESIGN.md
-    "iw_bound_fwd": lambda B, GK, D: B * (GK * P_IMG + P_IMG) * 4 + B * GK * 8,
-    "iw_bound_bwd": lambda B, GK, D: B * (2 * GK * P_IMG + P_IMG) * 4 + B * GK * 12,
-    "elbo_fwd": lambda B, GK, D: B * 2 * P_IMG * 4 + B * 4,
-    "elbo_bwd": lambda B, GK, D: B * 3 * P_IMG * 4 + B * 4,
-    "reparam_kl_fwd": lambda B, GK, D: B * 2 * D * 4 + B * max(GK, 1) * (D * 4 + 4),
-    "reparam_kl_bwd": lambda B, GK, D: B * 2 * D * 4 + B * max(GK, 1) * (3 * D * 4 + 4),
-}
-
-
-# dram__bytes_read.sum + dram__bytes_write.sum per launch from `ncu --set full` captures of the SAME workload size
-# (profiles/): (kernel, B, G*K) -> bytes.  Anything not captured reports traffic = null.
-NCU_TRAFFIC = {
-    ("iw_bound_bwd", 4096, 5): (1.208158e9 + 952.969216e6, "profiles/ncu_iw_bound_r01a_summary.csv"),
-    ("iw_bound_fwd", 4096, 5): (1.208144e9 + 4.415744e6, "profiles/ncu_iw_bound_r01a_summary.csv"),
-}
-
-
-def roofline_from_events(wl, B, log):
-    """Per-kernel average duration from the CUDA events recorded around every libvaekit launch
-    inside the timed region (same stream), turned into achieved GB/s on algorithmic bytes."""
-    peak, peak_src = peaks()
-    GK = max(wl["G"], 1) * wl["K"]
-    acc = {}
-    for name, e0, e1 in log:
-        acc.setdefault(name, []).append(e0.elapsed_time(e1))
-    res, total = {}, 0.0
-    for name, ts in acc.items():
-        ms = sum(ts) / len(ts)
-        nbytes = KERNEL_BYTES[name](B, GK, wl["D"]) if name in KERNEL_BYTES else 0
-        res[name] = {"ms": round(ms, 4), "launches": len(ts), "bytes": nbytes, "GBps": round(nbytes / ms / 1e6, 1)}
-        total += ms
-    dom = max(res, key=lambda k: res[k]["ms"])
-    for k in res:
-        res[k]["share_of_kernel_time"] = round(res[k]["ms"] / total, 4)
-    d = res[dom]
-    traffic = NCU_TRAFFIC.get((dom, B, GK))
-    return {"bound": "hbm", "kernel": dom + "_kernel", "achieved": d["GBps"], "peak": peak, "unit": "GB/s",
-            "frac": round(d["GBps"] / peak, 4), "traffic": traffic[0] if traffic else None,
-            "traffic_source": traffic[1] if traffic else None, "peak_source": peak_src,
-            "algorithmic_bytes_per_launch": d["bytes"], "ms_per_launch": d["ms"], "kernels": res}
-
-
-# ---------------------------------------------------------------------------
-# CPU baseline: the oracle port of the reference's torch code, on the host cores
-# ---------------------------------------------------------------------------
-def cpu_reference_step(wl, t):
-    """reparameterize + loss_function + backward exactly as the reference composes them
-    (iwae.py:121-160 / miwae.py:124-164 / vanilla_vae.py:119-146), via oracle/vae_oracle.py."""
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))
-    import vae_oracle as O
-    recons = t["recons"].detach().requires_grad_(True)
-    mu0 = t["mu0"].detach().requires_grad_(True)
-    lv0 = t["lv0"].detach().requires_grad_(True)
-    if wl["K"] == 0:
-        mu, lv = mu0, lv0
-    elif wl["G"] > 1:
-        mu = mu0.repeat(wl["G"], wl["K"], 1, 1).permute(2, 0, 1, 3)
-        lv = lv0.repeat(wl["G"], wl["K"], 1, 1).permute(2, 0, 1, 3)
-    else:
-        mu = mu0.repeat(wl["K"], 1, 1).permute(1, 0, 2)
-        lv = lv0.repeat(wl["K"], 1, 1).permute(1, 0, 2)
-    z = O.reparameterize(mu, lv, torch.randn_like(mu))
-    if wl["K"] == 0:
-        d = O.vanilla_loss(recons, t["input"], mu, lv, wl["M_N"])
-    else:
-        d = O.iw_bound_loss(recons, t["input"], mu, lv, wl["M_N"])
-    torch.autograd.backward([d["loss"], z], [None, t["gz"]])
-    return d
-
-
-def cpu_baseline(wl, sample_B, iters, warmup=1):
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
-    t = make_host_inputs(wl, sample_B, 1265, pin=False)
-    for _ in range(warmup):
-        cpu_reference_step(wl, t)
-    ts = []
-    for _ in range(iters):
-        t0 = time.perf_counter()
-        cpu_reference_step(wl, t)
-        ts.append(time.perf_counter() - t0)
-    return ts, cores
-
-
-def run_reference_arm(args, wl):
-    """--impl reference: the reference's CPU path (oracle port of its torch code; the Python reference
-    itself cannot travel to the GPU box) on all host cores, bounded sample of the same workload."""
-    rank, world, _ = dist_env()
-    if rank != 0:
-        return
-    sample_B = args.cpu_sample or (1024 if wl["K"] else 4096)
-    ts, cores = cpu_baseline(wl, sample_B, args.steps, warmup=max(1, min(args.warmup, 2)))
-    total = sum(ts)
-    value = sample_B * len(ts) / total
-    line = {
-        "impl": "reference", "metric": "latent+loss samples/s fwd+bwd", "value": round(value, 2), "unit": "samples/s",
-        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(1e3 * total / len(ts), 3),
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": wl["desc"], "sample": "batch %d of %d per step" % (sample_B, wl["B"])},
-        "cpu_baseline": {"value": round(value, 2), "unit": "samples/s", "cores": cores, "kind": "port",
-                         "sample": "batch %d of the %d-sample workload per step, torch CPU %d threads" % (sample_B, wl["B"], cores)},
-        "e2e": {"value": round(value, 2), "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0,
-    }
-    print(json.dumps(line), flush=True)
-
-
-# ---------------------------------------------------------------------------
-# GPU arm
-# ---------------------------------------------------------------------------
-def run_gpu_arm(args, wl):
-    import torch.distributed as dist
-    rank, world, local = dist_env()
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-    import vaekit
-    from vaekit import _lib as L
-    vaekit.lib()
-    model = build_model(args.workload)
-    B = wl["B"]
-    t = make_device_inputs(wl, B, 1265 + rank, dev)
-    torch.manual_seed(1265)
-
-    def barrier():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-            torch.cuda.synchronize()
-
-    # ---- device-resident timing (value) ----
-    for _ in range(args.warmup):
-        hot_path_step(model, wl, t)
-    barrier()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
-    launches0 = L.LAUNCHES
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(args.steps):
-        d = hot_path_step(model, wl, t)
-    e1.record()
-    barrier()
-    launches = L.LAUNCHES - launches0
-    ms = e0.elapsed_time(e1)
-    # the same K steps again with CUDA events around every library call (launching stream): per-kernel durations for the
-    # roofline.  Kept out of the pass that gives `value`: two event records per call cost the host 20-60 us per call.
-    L.EVENT_LOG = []
-    for _ in range(args.steps):
-        hot_path_step(model, wl, t)
-    barrier()
-    log, L.EVENT_LOG = L.EVENT_LOG, None
-    clocks = sampler.stop() if rank == 0 else None
-    if world > 1:
-        tms = torch.tensor([ms], device=dev)
-        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
-        ms = tms.item()
-    value = world * B * args.steps / (ms / 1e3)
-    roof = roofline_from_events(wl, B, log)
-    loss_val = d["loss"].item()
-
-    # ---- end-to-end: pinned host tensors in, loss out, every step ----
-    host = make_host_inputs(wl, B, 99 + rank, pin=True) if not args.no_e2e else None
-    e2e = None
-    if host is not None:
-        h2d = sum(v.numel() * 4 for v in host.values())
-
-        def e2e_step():
-            td = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
-            dd = hot_path_step(model, wl, td)
-            return [dd[k].item() for k in dd]          # the caller's .item() per dict key (experiment.py:55)
-
-        for _ in range(min(args.warmup, 3)):
-            e2e_step()
-        barrier()
-        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        f0.record()
-        for _ in range(args.steps):
-            vals = e2e_step()
-        f1.record()
-        barrier()
-        ems = f0.elapsed_time(f1)
-        if world > 1:
-            tms = torch.tensor([ems], device=dev)
-            dist.all_reduce(tms, op=dist.ReduceOp.MAX)
-            ems = tms.item()
-        e2e = {"value": round(world * B * args.steps / (ems / 1e3), 1), "unit": "samples/s",
-               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4 * len(vals), "ms_per_step": round(ems / args.steps, 3)}
-
-    if rank == 0:
-        cpu = None
-        if world == 1 and not args.no_cpu:
-            sample_B = args.cpu_sample or (1024 if wl["K"] else 4096)
-            ts, cores = cpu_baseline(wl, sample_B, 3)
-            v = sample_B * len(ts) / sum(ts)
-            cpu = {"value": round(v, 2), "unit": "samples/s", "cores": cores, "kind": "port",
-                   "sample": "batch %d of the %d-sample workload, 3 iterations after 1 warm-up, torch CPU %d threads"
-                             % (sample_B, B, cores)}
-        alg = algorithmic_bytes(wl, B)
-        line = {
-            "metric": "latent+loss samples/s fwd+bwd", "value": round(value, 1), "unit": "samples/s",
-            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 4),
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": wl["desc"], "per_gpu_batch": B, "global_batch": B * world,
-                       "l2_policy": "inputs (%.2f GB/step) larger than L2, no flush" % (alg / 1e9),
-                       "parallelism": "batch-sharded, no data-path collective" if world > 1 else "single GPU",
-                       "step": "reparameterize + loss_function + backward through the drop-in model API",
-                       "timing": "value: K steps between two CUDA events; roofline: the same K steps repeated with CUDA "
-                                 "events around every library call"},
-            "step_GBps_algorithmic": round(alg / (ms / args.steps) / 1e6, 1),
-            "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
-            "loss": loss_val,
-        }
-        print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
-
-
-# ---------------------------------------------------------------------------
-# op workloads: the other BASELINE.json configs (WAE-MMD, VQ, SWAE) and BetaTC, through the drop-in model API
-# ---------------------------------------------------------------------------
-def bf16_peak():
-    try:
-        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
-            return float(json.load(f)["bf16_tflops_sustained"]), "MEASURED_PEAKS.json bf16_tflops_sustained (measured)"
-    except Exception:
-        return 1400.0, "fallback 1.4 PFLOP/s sustained (B200_PROFILING.md)"
-
-
-class OpWorkload:
+# =====================================================================================================================
+class Workload:
     """One hot-path op at a BASELINE.json size.  make() builds synthetic inputs, step() runs forward + backward through
-    the public model API, cpu_step() is the oracle port of the reference on a bounded sample."""
-    scaling = "weak"
+    the public (drop-in model) API, cpu_make() / cpu_step() are the oracle port of the reference's formulation on a
+    bounded sample."""
+    scaling = "weak"            # replicas: every rank owns its own batch, no data-path collective
+    bound = "hbm"
+    dominant = None             # library call whose roofline is reported; None = the call with the largest share
+    parallelism = "batch-local replicas, no data-path collective"
+    graphed = False
+    l2_policy = "inputs larger than L2, no flush"
+    ncu_traffic = {}
 
     def units(self, world):
         return self.N * (world if self.scaling == "weak" else 1)
 
+    def model(self, dev):
+        raise NotImplementedError
 
-class WaeMmd(OpWorkload):
+    def extras(self, model, t, args, dev):
+        return {}
+
+
+# ---- configs[1]: IWAE / MIWAE, configs[0] at streaming size -------------------------------------------------------
+class StreamWorkload(Workload):
+    """reparameterize + loss_function + backward on given tensors (K1 + K2 / K3)."""
+
+    def __init__(self, name):
+        cfg = {"iwae": dict(B=4096, G=1, K=5, M_N=0.00025,
+                            desc="IWAE K=5, batch 4096, latent 128, 3x64x64: reparameterize + importance-weighted bound (BASELINE configs[1])"),
+               "miwae": dict(B=4096, G=3, K=5, M_N=0.00025,
+                             desc="MIWAE K=5 M=3, batch 4096, latent 128, 3x64x64 (BASELINE configs[1])"),
+               "vanilla": dict(B=65536, G=0, K=0, M_N=0.005,
+                               desc="VanillaVAE reparameterize + loss_function on given tensors, batch 65536, latent 128, 3x64x64 "
+                                    "(BASELINE configs[0] at streaming size)")}[name]
+        self.name, self.N, self.G, self.K, self.M_N, self.desc, self.D = name, cfg["B"], cfg["G"], cfg["K"], cfg["M_N"], cfg["desc"], 128
+        self.cpu_sample = 1024 if self.K else 4096
+        self.ncu_traffic = {"iw_bound_bwd": (1.208158e9 + 952.969216e6, "profiles/ncu_iw_bound_r01a_summary.csv"),
+                            "iw_bound_fwd": (1.208144e9 + 4.415744e6, "profiles/ncu_iw_bound_r01a_summary.csv")} if name == "iwae" else {}
+
+    def model(self, dev):
+        from vaekit.models import vae_models
+        if self.name == "iwae":
+            return vae_models["IWAE"](3, self.D, num_samples=5)
+        if self.name == "miwae":
+            return vae_models["MIWAE"](3, self.D, num_samples=5, num_estimates=3)
+        return vae_models["VanillaVAE"](3, self.D)
+
+    def _ss(self, B):
+        if self.K == 0:
+            return (B,)
+        return (B, self.G, self.K) if self.G > 1 else (B, self.K)
+
+    def make(self, dev, rank, world, n=None):
+        B = n or self.N
+        g = torch.Generator(device=dev).manual_seed(1265 + rank)
+        ss = self._ss(B)
+        return {"recons": torch.tanh(torch.randn(*ss, 3, 64, 64, device=dev, generator=g)),     # decoder ends in Tanh
+                "input": torch.rand(B, 3, 64, 64, device=dev, generator=g),                       # ToTensor range
+                "mu0": torch.randn(B, self.D, device=dev, generator=g),
+                "lv0": 0.5 * torch.randn(B, self.D, device=dev, generator=g) - 1.0,
+                "gz": 1e-3 * torch.randn(*ss, self.D, device=dev, generator=g)}                   # upstream grad of z
+
+    def _expand(self, mu0, lv0):
+        if self.K == 0:
+            return mu0, lv0
+        if self.G > 1:
+            shp = (-1, self.G, self.K, -1)
+            return mu0.view(mu0.size(0), 1, 1, -1).expand(*shp), lv0.view(lv0.size(0), 1, 1, -1).expand(*shp)
+        return mu0.unsqueeze(1).expand(-1, self.K, -1), lv0.unsqueeze(1).expand(-1, self.K, -1)
+
+    def step(self, m, t, world=1):
+        recons = t["recons"].requires_grad_(True)
+        mu0 = t["mu0"].requires_grad_(True)
+        lv0 = t["lv0"].requires_grad_(True)
+        recons.grad = mu0.grad = lv0.grad = None
+        mu, lv = self._expand(mu0, lv0)
+        z = m.reparameterize(mu, lv)
+        if self.K == 0:
+            d = m.loss_function(recons, t["input"], mu, lv, M_N=self.M_N)
+        else:
+            d = m.loss_function(recons, t["input"], mu, lv, z, None, M_N=self.M_N)
+        torch.autograd.backward([d["loss"], z], [None, t["gz"]])
+        return d
+
+    def work(self, world):
+        B, D, GK = self.N, self.D, max(self.G, 1) * self.K
+        return {"iw_bound_fwd": B * (GK * P_IMG + P_IMG) * 4 + B * GK * 8,
+                "iw_bound_bwd": B * (2 * GK * P_IMG + P_IMG) * 4 + B * GK * 12,
+                "elbo_fwd": B * 2 * P_IMG * 4 + B * 4, "elbo_bwd": B * 3 * P_IMG * 4 + B * 4,
+                "reparam_kl_fwd": B * 2 * D * 4 + B * max(GK, 1) * (D * 4 + 4),
+                "reparam_kl_bwd": B * 2 * D * 4 + B * max(GK, 1) * (3 * D * 4 + 4)}, "GB/s"
+
+    def cpu_make(self):
+        return {k: v for k, v in self.make(torch.device("cpu"), 0, 1, n=self.cpu_sample).items()}, self.cpu_sample, \
+            "batch %d of the %d-sample workload (cost per sample does not depend on the batch)" % (self.cpu_sample, self.N)
+
+    def cpu_step(self, t):
+        """iwae.py:121-160 / miwae.py:124-164 / vanilla_vae.py:119-146 as the reference composes them."""
+        O = oracle()
+        recons = t["recons"].detach().requires_grad_(True)
+        mu0 = t["mu0"].detach().requires_grad_(True)
+        lv0 = t["lv0"].detach().requires_grad_(True)
+        if self.K == 0:
+            mu, lv = mu0, lv0
+        elif self.G > 1:
+            mu = mu0.repeat(self.G, self.K, 1, 1).permute(2, 0, 1, 3)
+            lv = lv0.repeat(self.G, self.K, 1, 1).permute(2, 0, 1, 3)
+        else:
+            mu = mu0.repeat(self.K, 1, 1).permute(1, 0, 2)
+            lv = lv0.repeat(self.K, 1, 1).permute(1, 0, 2)
+        z = O.reparameterize(mu, lv, torch.randn_like(mu))
+        if self.K == 0:
+            d = O.vanilla_loss(recons, t["input"], mu, lv, self.M_N)
+        else:
+            d = O.iw_bound_loss(recons, t["input"], mu, lv, self.M_N)
+        torch.autograd.backward([d["loss"], z], [None, t["gz"]])
+
+
+# ---- configs[0] as BASELINE.json words it ----------------------------------------------------------------------------
+class VanillaB64(Workload):
+    """tests/test_vae.py:11-28 + configs/vae/vae.yaml: VanillaVAE(3, 128), batch 64 of 64x64 RGB, the full model(x) +
+    loss_function + backward.  The hot path moves 16 MB per step (2.5 us of HBM time): the step is launch-latency-bound
+    (SURVEY 0.10), so it is reported as us/step and launches/step, eager and replayed from ONE CUDA graph (K1 reads its
+    Philox key from device memory, so the replay draws fresh noise)."""
+    graphed = True
+    l2_policy = "working set fits L2 by construction (16 MB): latency-bound config, reported as us/step"
+    dominant = "elbo_bwd"
+
+    def __init__(self):
+        self.name, self.N, self.D = "vanilla_b64", 64, 128
+        self.desc = ("VanillaVAE(3, 128) full model(x) + loss_function + backward, batch 64, 64x64 RGB (BASELINE configs[0]; "
+                     "encoder / decoder convs are torch modules, out of scope but inside the step)")
+
+    def model(self, dev):
+        from vaekit.models import vae_models
+        torch.manual_seed(1265)
+        return vae_models["VanillaVAE"](3, self.D).to(dev)
+
+    def make(self, dev, rank, world, n=None):
+        g = torch.Generator(device=dev).manual_seed(1265 + rank)
+        return {"x": torch.rand(n or self.N, 3, 64, 64, device=dev, generator=g)}
+
+    def step(self, m, t, world=1):
+        for p in m.parameters():
+            p.grad = None
+        out = m(t["x"])
+        d = m.loss_function(*out, M_N=0.005)
+        d["loss"].backward()
+        return {"loss": d["loss"]}
+
+    def work(self, world):
+        B, D = self.N, self.D
+        return {"elbo_fwd": B * 2 * P_IMG * 4, "elbo_bwd": B * 3 * P_IMG * 4, "reparam_kl_fwd": B * 3 * D * 4,
+                "reparam_kl_bwd": B * 5 * D * 4}, "GB/s"
+
+    def extras(self, m, t, args, dev):
+        """The hot path alone (reparameterize + loss_function + backward on given tensors, no convs), eager and graphed."""
+        from vaekit.graphs import GraphedStep
+        from vaekit import _lib as L
+        sw = StreamWorkload("vanilla")
+        sw.N = self.N
+        tt = sw.make(dev, 0, 1, n=self.N)
+        mm = sw.model(dev)
+
+        def timed(fn, steps):
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            n0 = L.LAUNCHES
+            e0.record()
+            for _ in range(steps):
+                fn()
+            e1.record()
+            torch.cuda.synchronize()
+            return e0.elapsed_time(e1) / steps, (L.LAUNCHES - n0) / steps
+
+        for _ in range(3):
+            sw.step(mm, tt)
+        eager_ms, launches = timed(lambda: sw.step(mm, tt), max(args.steps, 20))
+        gs = GraphedStep(lambda inp: sw.step(mm, inp)["loss"], tt, rng=True)
+        graph_ms, _ = timed(gs, max(args.steps, 20))
+        alg = B_bytes = self.N * (5 * P_IMG * 4 + 8 * self.D * 4)
+        peak, _ = hbm_peak()
+        return {"hot_path_only": {"what": "reparameterize + loss_function + backward on given [64, ...] tensors (no convs)",
+                                  "eager_us_per_step": round(1e3 * eager_ms, 2), "graph_us_per_step": round(1e3 * graph_ms, 2),
+                                  "vaekit_launches_per_step": launches, "algorithmic_bytes_per_step": B_bytes,
+                                  "graph_GBps": round(alg / graph_ms / 1e6, 1), "graph_frac_of_hbm": round(alg / graph_ms / 1e6 / peak, 4),
+                                  "hbm_time_us_at_peak": round(alg / peak / 1e3, 2)}}
+
+    def cpu_make(self):
+        torch.manual_seed(1265)
+        from vaekit.models import vae_models
+        m = vae_models["VanillaVAE"](3, self.D)                       # conv stacks are plain torch modules: they run on the CPU
+        return {"x": torch.rand(self.N, 3, 64, 64), "m": m}, self.N, "the full config: batch 64, model(x) + loss_function + backward"
+
+    def cpu_step(self, t):
+        """vanilla_vae.py:119-146 with the reference's torch ops: conv stacks + oracle reparameterize / loss."""
+        O = oracle()
+        m = t["m"]
+        for p in m.parameters():
+            p.grad = None
+        mu, lv = m.encode(t["x"])
+        z = O.reparameterize(mu, lv, torch.randn_like(mu))
+        O.vanilla_loss(m.decode(z), t["x"], mu, lv, 0.005)["loss"].backward()
+
+
+# ---- configs[2]: WAE-MMD ---------------------------------------------------------------------------------------------
+class WaeMmd(Workload):
     scaling = "strong"          # fixed global batch, rows sharded after an all-gather of z (SURVEY 8(e))
+    bound = "tensor"
+    dominant = "mmd_fwd"
+    parallelism = "row-sharded after an NCCL all-gather of z (33.5 MB), 128-aligned row block per rank, all-reduce of 3 float64 sums"
+    l2_policy = "tensor-bound: operand images (67 MB) are L2-resident by design; nothing to flush"
 
     def __init__(self, kt):
         self.kt, self.N, self.D = kt, 65536, 128
+        self.name = "wae_mmd_" + kt
         self.reg = 5000.0 if kt == "rbf" else 100.0
         self.desc = "WAE-MMD %s kernel, z batch 65536x128, value + d/dz in one tcgen05 Gram sweep (BASELINE configs[2])" % kt.upper()
-        self.cpu_sample, self.bound = 2048, "tensor"
-        self.dominant = "mmd_fwd"
+        self.cpu_rows = 8
 
-    def model(self):
+    def model(self, dev):
         from vaekit.models import vae_models
         return vae_models["WAE_MMD"](3, self.D, reg_weight=self.reg, kernel_type=self.kt)
 
-    def make(self, dev, rank, world, n=None, generator_device=None):
+    def make(self, dev, rank, world, n=None):
         n = n or self.N // world
         g = torch.Generator(device=dev).manual_seed(1265 + rank)
         return {"z": torch.randn(n, self.D, device=dev, generator=g) + 0.25}
@@ -457,26 +374,36 @@ class WaeMmd(OpWorkload):
     def work(self, world):
         return {"mmd_fwd": 10.0 * self.N * self.N * self.D / world}, "TFLOP/s"
 
+    def cpu_make(self):
+        t = self.make(torch.device("cpu"), 0, 1, n=self.N)
+        t["prior"] = torch.randn(self.N, self.D)
+        return t, self.cpu_rows, ("a block of %d rows x all 65536 columns of the three kernel matrices in the reference's own "
+                                  "broadcast formulation at the FULL N (cost = rows/N of the step; the full [N,N,D] temporaries "
+                                  "need 2.2 TB)" % self.cpu_rows)
+
     def cpu_step(self, t):
-        import vae_oracle as O
+        O = oracle()
         z = t["z"].detach().requires_grad_(True)
-        n = z.shape[0]
-        O.mmd(z, torch.randn_like(z), self.reg / (n * (n - 1)), self.kt, 2.0).backward()
+        O.mmd_row_block(z, t["prior"], self.cpu_rows, self.kt, 2.0).backward()
 
 
-class VqWorkload(OpWorkload):
+# ---- configs[3]: VQ --------------------------------------------------------------------------------------------------
+class VqWorkload(Workload):
+    dominant = "vq_fwd"
+    graphed = True
+
     def __init__(self):
-        self.N, self.D, self.K, self.H = 1024, 64, 512, 16
-        self.desc = "VQ-VAE VectorQuantizer, codebook 512x64, 16x16 latent grid, batch 1024 (BASELINE configs[3])"
-        self.cpu_sample, self.bound = 128, "hbm"
-        self.dominant = "vq_fwd"
+        self.name, self.N, self.D, self.K, self.H = "vq", 1024, 64, 512, 16
+        self.desc = "VQ-VAE VectorQuantizer, codebook 512x64, 16x16 latent grid, batch 1024: argmin + straight-through + commitment loss (BASELINE configs[3])"
+        self.cpu_sample = 128
 
-    def model(self):
+    def model(self, dev):
         from vaekit.models.vq_vae import VectorQuantizer
+        torch.manual_seed(1265)
         m = VectorQuantizer(self.K, self.D, 0.25)
         with torch.no_grad():
             m.embedding.weight.normal_()
-        return m
+        return m.to(dev)
 
     def make(self, dev, rank, world, n=None):
         n = n or self.N
@@ -498,27 +425,71 @@ class VqWorkload(OpWorkload):
         bwd = 4 * R * self.D * 4 + R * 4 + 2 * self.K * self.D * 4
         return {"vq_fwd": float(fwd), "vq_bwd": float(bwd)}, "GB/s"
 
+    def extras(self, m, t, args, dev):
+        """Index mismatch rate over all 262 144 rows by gap bucket (north star: bit-exact wherever the reference's fp32
+        distance gap exceeds 1e-5 relative; the rate is reported).  The checker is torch on the GPU: the reference's
+        own expression (vq_vae.py:32-37) in fp32 and in float64."""
+        from vaekit import functional as F
+        x, e = t["latents"].detach(), m.embedding.weight.detach()
+        _, _, idx = F.vector_quantize(x, e, 0.25)
+        flat = x.permute(0, 2, 3, 1).reshape(-1, self.D)
+        tf32 = torch.backends.cuda.matmul.allow_tf32
+        torch.backends.cuda.matmul.allow_tf32 = False
+        try:
+            d32 = torch.sum(flat ** 2, dim=1, keepdim=True) + torch.sum(e ** 2, dim=1) - 2 * torch.matmul(flat, e.t())
+        finally:
+            torch.backends.cuda.matmul.allow_tf32 = tf32
+        i32 = torch.argmin(d32, dim=1)
+        best2 = torch.topk(d32, 2, dim=1, largest=False).values
+        gap = (best2[:, 1] - best2[:, 0]) / best2[:, 1].abs().clamp_min(1e-30)
+        del d32
+        f64, e64 = flat.double(), e.double()
+        i64 = torch.argmin(torch.sum(f64 ** 2, dim=1, keepdim=True) + torch.sum(e64 ** 2, dim=1) - 2 * f64 @ e64.t(), dim=1)
+        ours = idx.long()
+        buckets = {}
+        for name, lo, hi in (("gap>1e-5", 1e-5, float("inf")), ("1e-6<gap<=1e-5", 1e-6, 1e-5), ("0<gap<=1e-6", 0.0, 1e-6),
+                             ("exact_tie", -1.0, 0.0)):
+            sel = (gap > lo) & (gap <= hi)
+            n = int(sel.sum())
+            buckets[name] = {"rows": n, "mismatch_vs_reference_fp32": int((ours[sel] != i32[sel]).sum()),
+                             "mismatch_vs_float64": int((ours[sel] != i64[sel]).sum()),
+                             "reference_fp32_vs_float64": int((i32[sel] != i64[sel]).sum())}
+        return {"index_mismatch": {"rows": int(ours.numel()), "overall_vs_reference_fp32": int((ours != i32).sum()),
+                                   "overall_vs_float64": int((ours != i64).sum()),
+                                   "reference_fp32_vs_float64": int((i32 != i64).sum()), "by_relative_gap": buckets,
+                                   "checker": "torch on the GPU: vq_vae.py:32-37 in fp32 (TF32 off) and in float64"}}
+
+    def cpu_make(self):
+        t = self.make(torch.device("cpu"), 0, 1, n=self.cpu_sample)
+        t["cb"] = torch.randn(self.K, self.D)
+        return t, self.cpu_sample, "batch %d of 1024 images (cost per image does not depend on the batch)" % self.cpu_sample
+
     def cpu_step(self, t):
-        import vae_oracle as O
+        O = oracle()
         x = t["latents"].detach().requires_grad_(True)
-        cb = torch.randn(self.K, self.D, requires_grad=True)
+        cb = t["cb"].detach().requires_grad_(True)
         q, l, _ = O.vq_forward(x, cb, 0.25)
         torch.autograd.backward([q, l], [t["gq"], None])
 
 
-class SwaeWorkload(OpWorkload):
-    scaling = "strong"          # fixed global batch, projections sharded across ranks
+# ---- configs[4]: SWAE ------------------------------------------------------------------------------------------------
+class SwaeWorkload(Workload):
+    scaling = "strong"          # fixed global batch, every stage sharded (SURVEY 8(e))
+    dominant = "swd_fwd"
+    dominant_sharded = "swd_segments_fwd"
+    l2_policy = "sort buffers (1.7 GB per pass) larger than L2, no flush"
 
     def __init__(self):
-        self.N, self.D, self.S = 1 << 20, 128, 200
-        self.desc = "SWAE sliced-Wasserstein, 200 projections, batch 1048576x128, projection GEMM + radix sort (BASELINE configs[4])"
-        self.cpu_sample, self.bound = 1 << 16, "hbm"
-        self.dominant, self.dominant_sharded = "swd_fwd", "swd_segments_fwd"
-        # dram__bytes_read.sum + dram__bytes_write.sum over the 19 kernels of one vk_swd_fwd call at this size
-        # (`ncu --set full`, r01v): 30.82 GB against the 28.76 GB of the traffic model
+        self.name, self.N, self.D, self.S = "swae", 1 << 20, 128, 200
+        self.desc = "SWAE sliced-Wasserstein, 200 projections, batch 1048576x128: projection GEMM + per-projection radix sort (BASELINE configs[4])"
+        self.cpu_proj = 20
+        # dram__bytes_read.sum + dram__bytes_write.sum over the 19 kernels of one vk_swd_fwd call at this size (r01v)
         self.ncu_traffic = {"swd_fwd": (30.822819e9, "profiles/ncu_swae_r01v_summary.txt")}
+        self.parallelism = ("rows and projections both sharded: every rank projects its rows on all 200 projections, sorts its "
+                            "200/world projections; both exchanges fused into the tcgen05 GEMMs over peer memory (%s)"
+                            % os.environ.get("VAEKIT_SWD_EXCHANGE", "auto"))
 
-    def model(self):
+    def model(self, dev):
         from vaekit.models import vae_models
         return vae_models["SWAE"](3, self.D, reg_weight=100, num_projections=self.S)
 
@@ -542,29 +513,43 @@ class SwaeWorkload(OpWorkload):
         return {"SWD": swd}
 
     def work(self, world):
-        # radix-sort traffic model of SURVEY 8(d); sharded (all-to-all) runs time the sort + loss stage on its own:
-        # 120 of the model's 132 bytes per (sample, projection) belong to it (key+index sort 68, key-only sort 36,
-        # loss read 8, gradient scatter 8)
-        return {"swd_fwd": 27424.0 * self.N / world,
-                "swd_segments_fwd": 120.0 * self.N * self.S / world}, "GB/s"
+        # radix-sort traffic model of SURVEY 8(d): 27 424 B/sample; sharded runs time the sort + loss stage on its own (120 of
+        # the model's 132 bytes per (sample, projection): key+index sort 68, key-only sort 36, loss read 8, scatter 8)
+        return {"swd_fwd": 27424.0 * self.N / world, "swd_segments_fwd": 120.0 * self.N * self.S / world}, "GB/s"
+
+    def extras(self, m, t, args, dev):
+        return {"compulsory_floor": {"bytes_per_sample": 1024, "what": "z read + g_z write only (SURVEY 8(d): everything else on chip)"}}
+
+    def cpu_make(self):
+        O = oracle()
+        t = self.make(torch.device("cpu"), 0, 1, n=self.N)
+        t["prior"] = torch.randn(self.N, self.D)
+        torch.manual_seed(1265)
+        t["proj"] = O.random_projections(self.D, self.S)[:self.cpu_proj].contiguous()
+        return t, self.N * self.cpu_proj / self.S, ("%d of the 200 projections at the FULL batch 1048576 (cost is linear in the "
+                                                    "projection count; the prior draw is outside the timed region)" % self.cpu_proj)
 
     def cpu_step(self, t):
-        import vae_oracle as O
+        O = oracle()
         z = t["z"].detach().requires_grad_(True)
         n = z.shape[0]
-        O.swd(z, torch.randn_like(z), O.random_projections(self.D, self.S), 2.0, 100.0 / (n * (n - 1))).backward()
+        O.swd(z, t["prior"], t["proj"], 2.0, 100.0 / (n * (n - 1))).backward()
 
 
-class BetaTcWorkload(OpWorkload):
+# ---- SURVEY 8(d) extra: BetaTC -----------------------------------------------------------------------------------------
+class BetaTcWorkload(Workload):
     scaling = "strong"          # fixed global batch, anchor rows sharded after an all-gather of z, mu, log_var
+    bound = "mufu"
+    dominant, dominant_sharded = "tc_bwd", "tc_bwd_rows"
+    parallelism = "anchor rows sharded after NCCL all-gathers of z, mu, log_var; all-reduce of the 4 batch means"
+    l2_policy = "MUFU-bound: operands (6 MB) are L2-resident by design"
 
     def __init__(self):
-        self.N, self.D = 4096, 128
-        self.desc = "BetaTC-VAE latent terms (log_q_z, per-dim LSE, MI/TC/KLD), batch 4096, latent 128 (SURVEY 8(d) extra)"
-        self.cpu_sample, self.bound = 1024, "mufu"
-        self.dominant, self.dominant_sharded = "tc_bwd", "tc_bwd_rows"
+        self.name, self.N, self.D = "betatc", 4096, 128
+        self.desc = "BetaTC-VAE latent terms (log_q_z, per-dimension LSE, MI / TC / KLD), batch 4096, latent 128 (SURVEY 8(d) extra)"
+        self.cpu_rows = 64
 
-    def model(self):
+    def model(self, dev):
         from vaekit.models import vae_models
         return vae_models["BetaTCVAE"](3, self.D).eval()
 
@@ -573,7 +558,7 @@ class BetaTcWorkload(OpWorkload):
         g = torch.Generator(device=dev).manual_seed(1265 + rank)
         mu = torch.randn(n, self.D, device=dev, generator=g)
         lv = 0.3 * torch.randn(n, self.D, device=dev, generator=g)
-        return {"mu": mu, "lv": lv, "eps": torch.randn(n, self.D, device=dev, generator=g)}
+        return {"mu": mu, "lv": lv}
 
     def step(self, m, t, world=1):
         from vaekit import functional as F
@@ -592,23 +577,34 @@ class BetaTcWorkload(OpWorkload):
         e = float(self.N) * self.N * self.D
         return {"tc_fwd": e, "tc_bwd": 2.0 * e, "tc_fwd_rows": e / world, "tc_bwd_rows": 2.0 * e / world}, "Gexp/s"
 
+    def cpu_make(self):
+        t = self.make(torch.device("cpu"), 0, 1, n=self.N)
+        t["eps"] = torch.randn(self.N, self.D)
+        return t, self.cpu_rows, ("%d anchor rows x all 4096 partners of the reference's [B,B,D] log-density tensor at the FULL "
+                                  "batch (cost = rows/B of the step; the full tensor is 8.6 GB per temporary)" % self.cpu_rows)
+
     def cpu_step(self, t):
-        import vae_oracle as O
+        O = oracle()
         mu, lv = t["mu"].detach().requires_grad_(True), t["lv"].detach().requires_grad_(True)
         z = O.reparameterize(mu, lv, t["eps"])
-        rz = torch.zeros(mu.shape[0], 1, 1, 1)
-        O.betatc_loss(rz, rz, mu, lv, z, 0.00025, alpha=1.0, beta=6.0, gamma=1.0, anneal_rate=1.0)["loss"].backward()
+        O.betatc_row_block(mu, lv, z, self.cpu_rows, 0.00025).backward()
 
 
-OP_WORKLOADS = {"wae_mmd_rbf": lambda: WaeMmd("rbf"), "wae_mmd_imq": lambda: WaeMmd("imq"), "vq": VqWorkload,
-                "swae": SwaeWorkload, "betatc": BetaTcWorkload}
+WORKLOADS = {"wae_mmd_rbf": lambda: WaeMmd("rbf"), "wae_mmd_imq": lambda: WaeMmd("imq"),
+             "iwae": lambda: StreamWorkload("iwae"), "miwae": lambda: StreamWorkload("miwae"),
+             "vanilla_b64": VanillaB64, "vanilla": lambda: StreamWorkload("vanilla"),
+             "vq": VqWorkload, "swae": SwaeWorkload, "betatc": BetaTcWorkload}
+ORDER_1GPU = ["wae_mmd_rbf", "wae_mmd_imq", "iwae", "miwae", "vanilla_b64", "vanilla", "vq", "swae", "betatc"]
+ORDER_NGPU = ["wae_mmd_rbf", "wae_mmd_imq", "swae", "betatc", "iwae", "vq"]
 
 
-def op_cpu_baseline(wl, iters, warmup=1):
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+# =====================================================================================================================
+# CPU arm: the reference's formulation (oracle port) on the host cores
+# =====================================================================================================================
+def cpu_time(wl, iters, warmup):
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    t = wl.make(torch.device("cpu"), 0, 1, n=wl.cpu_sample)
+    t, units, sample = wl.cpu_make()
     for _ in range(warmup):
         wl.cpu_step(t)
     ts = []
@@ -616,167 +612,256 @@ def op_cpu_baseline(wl, iters, warmup=1):
         t0 = time.perf_counter()
         wl.cpu_step(t)
         ts.append(time.perf_counter() - t0)
-    v = wl.cpu_sample * len(ts) / sum(ts)
-    return v, cores, ts
+    return units * len(ts) / sum(ts), cores, ts, sample, units
 
 
-def run_op_reference_arm(args, wl):
-    rank, _, _ = dist_env()
+def cpu_baseline(wl, budget_s=8.0):
+    """Bounded sample: one warm-up, then as many iterations as fit the budget (at least 2, at most 5)."""
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    t, units, sample = wl.cpu_make()
+    t0 = time.perf_counter()
+    wl.cpu_step(t)
+    first = time.perf_counter() - t0
+    iters = max(2, min(5, int(budget_s / max(first, 1e-3))))
+    ts = []
+    for _ in range(iters):
+        t0 = time.perf_counter()
+        wl.cpu_step(t)
+        ts.append(time.perf_counter() - t0)
+    v = units * len(ts) / sum(ts)
+    return {"value": round(v, 3), "unit": "samples/s", "cores": cores, "kind": "port",
+            "sample": "%s; %d iterations after 1 warm-up, torch CPU %d threads; oracle/vae_oracle.py = the reference's torch ops"
+                      % (sample, iters, cores), "s_per_iteration": round(sum(ts) / len(ts), 3)}
+
+
+def run_reference_arm(args):
+    """--impl reference: the reference's CPU formulation of the top-level workload (oracle port of its torch code -- the
+    Python reference itself cannot travel to the GPU box and has no native code to compile) on all host cores, each step
+    a bounded sample of that workload."""
+    rank, world, _ = dist_env()
     if rank != 0:
         return
-    v, cores, ts = op_cpu_baseline(wl, max(1, min(args.steps, 3)), warmup=1)
-    sample = "batch %d of the %d-sample workload per step (the reference's broadcast formulation at that size), torch CPU %d threads" % (
-        wl.cpu_sample, wl.N, cores)
-    line = {"impl": "reference", "metric": "latent+loss samples/s fwd+bwd", "value": round(v, 2), "unit": "samples/s",
-            "n_gpus": args.gpus, "steps": len(ts), "warmup": 1, "ms_per_step": round(1e3 * sum(ts) / len(ts), 3),
+    name = HEADLINE if args.workload == "all" else args.workload
+    wl = WORKLOADS[name]()
+    v, cores, ts, sample, units = cpu_time(wl, args.steps, max(1, min(args.warmup, 2)))
+    line = {"impl": "reference", "metric": METRIC, "value": round(v, 3), "unit": "samples/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(1e3 * sum(ts) / len(ts), 3),
             "higher_is_better": True, "scaling": wl.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": wl.desc, "sample": sample},
-            "cpu_baseline": {"value": round(v, 2), "unit": "samples/s", "cores": cores, "kind": "port", "sample": sample},
-            "e2e": {"value": round(v, 2), "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "config": {"workload": wl.desc, "sample": sample, "samples_per_step": units},
+            "cpu_baseline": {"value": round(v, 3), "unit": "samples/s", "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": round(v, 3), "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
 
 
-def run_op_gpu_arm(args, wl):
-    import torch.distributed as dist
-    rank, world, local = dist_env()
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-    import vaekit
-    from vaekit import _lib as L
-    vaekit.lib()
-    model = wl.model().to(dev)
-    t = wl.make(dev, rank, world)
-    torch.manual_seed(1265)
+# =====================================================================================================================
+# GPU arm
+# =====================================================================================================================
+class Ctx:
+    def __init__(self, args):
+        import torch.distributed as dist
+        self.dist = dist
+        self.rank, self.world, self.local = dist_env()
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device("cuda", self.local)
+        if self.world > 1:
+            dist.init_process_group("nccl", device_id=self.dev)
+        self.args = args
 
-    def barrier():
+    def barrier(self):
         torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
+        if self.world > 1:
+            self.dist.barrier()
             torch.cuda.synchronize()
 
-    def timed(fn, steps, log_events):
-        barrier()
-        if log_events:
-            L.EVENT_LOG = []
-        n0 = L.LAUNCHES
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(steps):
-            r = fn()
-        e1.record()
-        barrier()
-        log, L.EVENT_LOG = L.EVENT_LOG, None
-        ms = e0.elapsed_time(e1)
-        if world > 1:
-            tms = torch.tensor([ms], device=dev)
-            dist.all_reduce(tms, op=dist.ReduceOp.MAX)
-            ms = tms.item()
-        return ms, log, L.LAUNCHES - n0, r
+    def max_over_ranks(self, ms):
+        if self.world > 1:
+            t = torch.tensor([ms], device=self.dev)
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+            ms = t.item()
+        return ms
 
-    for _ in range(max(args.warmup, 3)):
-        wl.step(model, t, world)
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
-    ms, _, launches, d = timed(lambda: wl.step(model, t, world), args.steps, False)
-    # the same K steps again with CUDA events around every library call (launching stream): per-call durations for the
-    # roofline.  Kept out of the pass that gives `value`: two event records per call cost the host 20-60 us per call.
-    _, log, _, _ = timed(lambda: wl.step(model, t, world), args.steps, True)
-    clocks = sampler.stop() if rank == 0 else None
-    value = wl.units(world) * args.steps / (ms / 1e3)
-    # roofline of the dominant library call, from CUDA events around each call on the launching stream
+
+def timed(ctx, fn, steps, log_events=False):
+    """K calls of fn between two CUDA events on the launching stream, barrier + synchronize on both sides, max over ranks."""
+    from vaekit import _lib as L
+    ctx.barrier()
+    if log_events:
+        L.EVENT_LOG = []
+    n0 = L.LAUNCHES
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        r = fn()
+    e1.record()
+    ctx.barrier()
+    log, L.EVENT_LOG = L.EVENT_LOG, None
+    return ctx.max_over_ranks(e0.elapsed_time(e1)), log, L.LAUNCHES - n0, r
+
+
+def roofline(wl, world, log):
     work, unit = wl.work(world)
     acc = {}
     for name, a, b in log:
         acc.setdefault(name, []).append(a.elapsed_time(b))
-    kern = {k: {"ms": round(sum(v) / len(v), 4), "calls": len(v)} for k, v in acc.items()}
-    tot = sum(k["ms"] * k["calls"] for k in kern.values()) or 1.0
-    for k in kern:
-        kern[k]["share_of_library_time"] = round(kern[k]["ms"] * kern[k]["calls"] / tot, 4)
-    dom = wl.dominant if wl.dominant in kern else wl.dominant_sharded
-    dms = kern[dom]["ms"]
+    calls = {k: {"ms": round(sum(v) / len(v), 4), "calls": len(v)} for k, v in acc.items()}
+    tot = sum(k["ms"] * k["calls"] for k in calls.values()) or 1.0
+    for k in calls:
+        calls[k]["share_of_library_time"] = round(calls[k]["ms"] * calls[k]["calls"] / tot, 4)
+        if k in work:
+            calls[k]["algorithmic_work"] = work[k]
+    dom = wl.dominant if wl.dominant in calls else getattr(wl, "dominant_sharded", None)
+    if dom not in calls:
+        cand = [k for k in calls if k in work]
+        dom = max(cand, key=lambda k: calls[k]["ms"] * calls[k]["calls"]) if cand else None
+    if dom is None:
+        return {"bound": wl.bound, "error": "no library call with a work model was logged", "calls": calls}
+    dms = calls[dom]["ms"]
     if wl.bound == "tensor":
         peak, src = bf16_peak()
         ach = work[dom] / dms / 1e9
     elif wl.bound == "hbm":
-        peak, src = peaks()
+        peak, src = hbm_peak()
         ach = work[dom] / dms / 1e6
     else:
         peak, src = 148 * 16 * 1.965, "16 MUFU ops/clk/SM x 148 SMs x 1.965 GHz (nominal)"
         ach = work[dom] / dms / 1e6
-    ncu_t = getattr(wl, "ncu_traffic", {}).get(dom) if world == 1 else None
-    roof = {"bound": "tensor" if wl.bound == "tensor" else "hbm" if wl.bound == "hbm" else "mufu", "kernel": dom,
-            "achieved": round(ach, 2), "peak": round(peak, 1), "unit": unit, "frac": round(ach / peak, 4),
-            "traffic": ncu_t[0] if ncu_t else None, "traffic_source": ncu_t[1] if ncu_t else None,
-            "peak_source": src, "algorithmic_work_per_launch": work[dom], "ms_per_launch": dms, "calls": kern}
-    # end to end: host (pinned) inputs copied in and the loss read back every step
+    t = wl.ncu_traffic.get(dom) if world == 1 else None
+    return {"bound": wl.bound, "kernel": dom, "achieved": round(ach, 2), "peak": round(peak, 1), "unit": unit,
+            "frac": round(ach / peak, 4), "traffic": t[0] if t else None, "traffic_source": t[1] if t else None,
+            "peak_source": src, "algorithmic_work_per_launch": work[dom], "ms_per_launch": dms, "calls": calls}
+
+
+def free_memory():
+    import gc
+    gc.collect()
+    torch.cuda.empty_cache()
+    try:
+        torch._C._host_emptyCache()          # pinned host blocks of the previous workload's e2e leg
+    except Exception:
+        pass
+
+
+def measure(ctx, wl):
+    from vaekit import _lib as L
+    args, world, dev = ctx.args, ctx.world, ctx.dev
+    warm = max(args.warmup, 3)
+    model = wl.model(dev)
+    if isinstance(model, torch.nn.Module):
+        model = model.to(dev)
+    t = wl.make(dev, ctx.rank, world)
+    torch.manual_seed(1265)
+    for _ in range(warm):
+        wl.step(model, t, world)
+    sampler = ClockSampler(ctx.local).start() if ctx.rank == 0 else None
+    ms, _, launches, d = timed(ctx, lambda: wl.step(model, t, world), args.steps)
+    # the same K steps again with CUDA events around every library call (launching stream): per-call durations for the
+    # roofline.  Kept out of the pass that gives the step time: two event records per call cost the host 20-60 us.
+    _, log, _, _ = timed(ctx, lambda: wl.step(model, t, world), args.steps, log_events=True)
+    res = {"ms_per_step": round(ms / args.steps, 4), "api": "eager: forward + backward through the drop-in model API"}
+    step_ms = ms / args.steps
+    gs = None
+    if wl.graphed and world == 1:
+        # host-bound short steps: the same step captured once in a CUDA graph (vaekit.graphs.GraphedStep) and replayed
+        from vaekit.graphs import GraphedStep
+        gs = GraphedStep(lambda inp: wl.step(model, inp, world), t, rng=isinstance(wl, VanillaB64))
+        for _ in range(warm):
+            gs()
+        gms, _, _, _ = timed(ctx, gs, args.steps)
+        res.update({"eager_ms_per_step": res["ms_per_step"], "graph_ms_per_step": round(gms / args.steps, 4),
+                    "ms_per_step": round(gms / args.steps, 4), "vaekit_launches_per_step": launches / args.steps,
+                    "api": "vaekit.graphs.GraphedStep: forward + backward through the drop-in model API, captured once, replayed"})
+        step_ms = gms / args.steps
+    clocks = sampler.stop() if sampler else None
+    value = wl.units(world) * 1e3 / step_ms
+    roof = roofline(wl, world, log)
+    # end to end: pinned host inputs copied in and every returned loss read back, every step
     e2e = None
     if not args.no_e2e:
-        # detached: the workload marks its inputs requires_grad in place, and a host copy that stayed in the autograd
-        # graph would make every backward() end with a pageable device-to-host copy of the gradient (r01w and earlier
-        # ops-workload e2e numbers carry that artefact: 1.7-3.4 GB/s effective instead of the 54 GB/s of pinned copies)
-        host = {k: v.detach().cpu().pin_memory() for k, v in t.items()}
+        host = {k: v.detach().cpu().pin_memory() for k, v in t.items()}     # detached, like a data loader's batch
         h2d = sum(v.numel() * v.element_size() for v in host.values())
-
-        def e2e_step():
-            td = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
-            dd = wl.step(model, td, world)
-            return [v.item() for v in dd.values()]
-
+        if gs is not None:
+            def e2e_step():
+                out = gs(**host)
+                return [v.item() for v in out.values()]
+        else:
+            def e2e_step():
+                td = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
+                dd = wl.step(model, td, world)
+                return [v.item() for v in dd.values()]              # the caller's .item() per dict key (experiment.py:55)
         for _ in range(2):
             e2e_step()
-        ems, _, _, vals = timed(e2e_step, args.steps, False)
+        ems, _, _, vals = timed(ctx, e2e_step, args.steps)
         e2e = {"value": round(wl.units(world) * args.steps / (ems / 1e3), 1), "unit": "samples/s",
                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4 * len(vals), "ms_per_step": round(ems / args.steps, 3)}
-    if rank == 0:
-        cpu = None
-        if world == 1 and not args.no_cpu:
-            v, cores, ts = op_cpu_baseline(wl, 2)
-            cpu = {"value": round(v, 2), "unit": "samples/s", "cores": cores, "kind": "port",
-                   "sample": "batch %d of the %d-sample workload (the reference's formulation at that size), 2 iterations "
-                             "after 1 warm-up, torch CPU %d threads" % (wl.cpu_sample, wl.N, cores)}
-        line = {"metric": "latent+loss samples/s fwd+bwd", "value": round(value, 1), "unit": "samples/s", "n_gpus": world,
-                "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": round(ms / args.steps, 4),
-                "higher_is_better": True, "scaling": wl.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": wl.desc, "global_batch": wl.units(world),
-                           "l2_policy": "synthetic inputs regenerated never; working set (operand images / sort buffers) larger than L2 or tensor-bound",
-                           "parallelism": ("%s over %d ranks" % ("row-sharded after all-gather" if isinstance(wl, (WaeMmd, BetaTcWorkload)) else
-                                                                  "projection-sharded, exchange fused into the GEMMs over peer memory (%s)"
-                                                                  % os.environ.get("VAEKIT_SWD_EXCHANGE", "auto") if isinstance(wl, SwaeWorkload)
-                                                                  else "batch-sharded", world)) if world > 1 else "single GPU",
-                           "step": "forward + backward through the drop-in model API",
-                           "timing": "value: K steps between two CUDA events; roofline: the same K steps repeated with CUDA "
+        del host
+    extras = {}
+    if ctx.rank == 0 and world == 1 and not args.no_extras:
+        extras = wl.extras(model, t, args, dev)
+    loss = {k: float(v.item()) for k, v in d.items()}
+    del t, model, gs
+    free_memory()
+    cpu = None
+    if ctx.rank == 0 and world == 1 and not args.no_cpu:
+        cpu = cpu_baseline(wl)
+    res.update({"metric": METRIC, "value": round(value, 1), "unit": "samples/s", "scaling": wl.scaling,
+                "config": {"workload": wl.desc, "global_batch": wl.units(world), "l2_policy": wl.l2_policy,
+                           "parallelism": ("%s; %d ranks" % (wl.parallelism, world)) if world > 1 else "single GPU",
+                           "timing": "step: K steps between two CUDA events; roofline: the same K steps repeated with CUDA "
                                      "events around every library call"},
-                "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
-                "loss": {k: v.item() for k, v in d.items()}}
+                "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "loss": loss})
+    res.update(extras)
+    return res
+
+
+def run_gpu_arm(args):
+    ctx = Ctx(args)
+    import vaekit
+    vaekit.lib()                        # raises if libvaekit.so is missing: there is no fallback
+    if args.workload == "all":
+        names = ORDER_1GPU if ctx.world == 1 else ORDER_NGPU
+    else:
+        names = [args.workload]
+    results = {}
+    for name in names:
+        wl = WORKLOADS[name]()
+        if ctx.world > 1 or name == names[0]:
+            results[name] = measure(ctx, wl)            # a failure of the headline (or on any rank of a group) is fatal
+        else:
+            try:
+                results[name] = measure(ctx, wl)
+            except Exception as e:                      # keep the line: one broken workload must not hide the others
+                results[name] = {"error": "%s: %s" % (type(e).__name__, str(e)[:300])}
+                free_memory()
+    if ctx.rank == 0:
+        top = results[names[0]]
+        line = {"metric": METRIC, "value": top["value"], "unit": "samples/s", "n_gpus": ctx.world, "steps": args.steps,
+                "warmup": max(args.warmup, 3), "ms_per_step": top["ms_per_step"], "higher_is_better": True,
+                "scaling": top["scaling"], "vs_baseline": None, "dtype": "f32", "data": "synthetic"}
+        line.update({k: v for k, v in top.items() if k not in line})
+        line["headline_workload"] = names[0]
+        line["workloads"] = {n: results[n] for n in names[1:]}
         print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
+    if ctx.world > 1:
+        ctx.dist.destroy_process_group()
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--workload", default="iwae", choices=sorted(WORKLOADS) + sorted(OP_WORKLOADS))
+    ap.add_argument("--workload", default="all", choices=["all"] + sorted(WORKLOADS))
     ap.add_argument("--impl", default="vaekit", choices=["vaekit", "reference"])
-    ap.add_argument("--cpu-sample", type=int, default=0, help="batch of the bounded CPU-baseline sample")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-extras", action="store_true")
     args = ap.parse_args()
-    if args.workload in OP_WORKLOADS:
-        wl = OP_WORKLOADS[args.workload]()
-        (run_op_reference_arm if args.impl == "reference" else run_op_gpu_arm)(args, wl)
-        return
-    wl = WORKLOADS[args.workload]
     if args.impl == "reference":
-        run_reference_arm(args, wl)
+        run_reference_arm(args)
     else:
-        run_gpu_arm(args, wl)
+        run_gpu_arm(args)
 
 
 if __name__ == "__main__":

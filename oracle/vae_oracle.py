@@ -397,6 +397,20 @@ def mmd_terms_chunked(z: Tensor, prior_z: Tensor, kernel_type: str, z_var: float
         return term(prior_z, prior_z), term(z, z), term(prior_z, z)
 
 
+def mmd_row_block(z: Tensor, prior_z: Tensor, rows: int, kernel_type: str, z_var: float) -> Tensor:
+    """The first `rows` rows of the three kernel matrices of wae_mmd.py:193-204 in the reference's own broadcast
+    formulation (compute_kernel's expand() views, wae_mmd.py:140-141, cut to a row block): pp + zz - 2 pz of the block,
+    un-normalised.  The cost of a row block is exactly rows / N of the full N x N problem, which makes it the bounded
+    CPU timing sample of the benchmark at the full N = 65 536 (the full [N, N, D] temporaries would need 2.2 TB)."""
+    f = compute_rbf if kernel_type == "rbf" else compute_inv_mult_quad
+
+    def block(a, b):
+        x1 = a[:rows].unsqueeze(-2).expand(rows, b.size(0), a.size(1))
+        x2 = b.unsqueeze(-3).expand(rows, b.size(0), a.size(1))
+        return f(x1, x2, z_var).sum()
+    return block(prior_z, prior_z) + block(z, z) - 2 * block(prior_z, z)
+
+
 def wae_loss(recons: Tensor, input: Tensor, z: Tensor, prior_z: Tensor, *, reg_weight: float,
              kernel_type: str, z_var: float) -> Dict[str, Tensor]:
     """wae_mmd.py:107-123."""
@@ -453,6 +467,28 @@ def betatc_loss(recons: Tensor, input: Tensor, mu: Tensor, log_var: Tensor, z: T
     kld = (log_prod_q_z - log_p_z).mean()
     loss = recons_loss / bsz + alpha * mi + (beta * tc + anneal_rate * gamma * kld)
     return {"loss": loss, "Reconstruction_Loss": recons_loss, "KLD": kld, "TC_Loss": tc, "MI_Loss": mi}
+
+
+def betatc_row_block(mu: Tensor, log_var: Tensor, z: Tensor, rows: int, M_N: float) -> Tensor:
+    """betatc_vae.py:165-192 for the first `rows` anchor rows against all B partners (the [rows, B, D] slice of the
+    reference's [B, B, D] log-density tensor and both logsumexps over it): sum over the block of
+    mi + tc + kld.  rows / B of the full problem's cost: the bounded CPU timing sample at B = 4096, D = 128 (the full
+    tensor is 8.6 GB per temporary)."""
+    bsz, d = z.shape
+    log_q_zx = log_density_gaussian(z[:rows], mu[:rows], log_var[:rows]).sum(dim=1)
+    zeros = torch.zeros_like(z[:rows])
+    log_p_z = log_density_gaussian(z[:rows], zeros, zeros).sum(dim=1)
+    mat = log_density_gaussian(z[:rows].view(rows, 1, d), mu.view(1, bsz, d), log_var.view(1, bsz, d))
+    dataset_size = (1 / M_N) * bsz
+    strat = (dataset_size - bsz + 1) / (dataset_size * (bsz - 1))
+    w = torch.Tensor(bsz, bsz).fill_(1 / (bsz - 1))
+    w.view(-1)[::bsz] = 1 / dataset_size
+    w.view(-1)[1::bsz] = strat
+    w[bsz - 2, 0] = strat
+    mat = mat + w[:rows].log().to(mat.dtype).view(rows, bsz, 1)
+    log_q_z = torch.logsumexp(mat.sum(2), dim=1)
+    log_prod_q_z = torch.logsumexp(mat, dim=1).sum(1)
+    return ((log_q_zx - log_q_z) + (log_q_z - log_prod_q_z) + (log_prod_q_z - log_p_z)).sum()
 
 
 # --------------------------------------------------------------------------
