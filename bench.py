@@ -759,6 +759,8 @@ def measure(ctx, wl):
     # the same K steps again with CUDA events around every library call (launching stream): per-call durations for the
     # roofline.  Kept out of the pass that gives the step time: two event records per call cost the host 20-60 us.
     _, log, _, _ = timed(ctx, lambda: wl.step(model, t, world), args.steps, log_events=True)
+    loss = {k: float(v.item()) for k, v in d.items()}
+    del d       # frees the eager autograd graph: its AccumulateGrad nodes are bound to this stream and would break a capture
     res = {"ms_per_step": round(ms / args.steps, 4), "api": "eager: forward + backward through the drop-in model API"}
     step_ms = ms / args.steps
     gs = None
@@ -799,7 +801,6 @@ def measure(ctx, wl):
     extras = {}
     if ctx.rank == 0 and world == 1 and not args.no_extras:
         extras = wl.extras(model, t, args, dev)
-    loss = {k: float(v.item()) for k, v in d.items()}
     del t, model, gs
     free_memory()
     cpu = None
