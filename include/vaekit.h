@@ -197,8 +197,20 @@ int vk_vq_bwd(const float* g_q, const float* g_loss, const float* latents, const
  *   sums_out[3] (double, device) = { sum k(z_i,z_j), sum k(z_i,prior_j), sum k(prior_i,prior_j) } over the rows
  *   grad_unscaled [(row_end-row_begin), D]:  G_i = sum_j dk/dd^2(z_i,z_j) (z_i-z_j) - sum_j dk/dd^2(z_i,p_j) (z_i-p_j)
  *                 so that  d mmd / d z_i = 4 * reg * m * G_i,  m = 1/N^2 (rbf) or 1 (imq)
- * x.y runs on tcgen05 tensor cores: passes = 3 -> bf16 hi/lo split (hi*hi + lo*hi + hi*lo, ~2^-17 relative,
- * the parity mode), passes = 1 -> plain bf16 (reported separately; gradients lose ~3 digits).
+ * x.y runs on tcgen05 tensor cores in bf16 with fp32 accumulation; `passes` selects the precision of the two GEMMs
+ * (distance GEMM / gradient GEMM):
+ *   3  both in three passes of a bf16 hi/lo split (hi*hi + lo*hi + hi*lo, ~2^-17 relative): the parity sweep
+ *   2  distance GEMM three passes, gradient GEMM one pass
+ *   1  both in one plain bf16 pass
+ *   0  auto: the library picks (rbf at N >= 8192: one pass each; otherwise the parity sweep); a reduced-precision sweep
+ *      is CHECKED against a float64 SIMT evaluation of 32 sample rows over all columns, and when its error exceeds
+ *      4e-6 of max |grad| a device flag makes the parity sweep run behind it -- no host synchronisation either way.
+ * The data are centred on the device (distances are translation invariant) and the gradient GEMM accumulates CENTRED
+ * coefficients c - c0 (c0 = the coefficient at the mean squared distance; its share of the gradient is exact float64
+ * arithmetic on column sums), which is what keeps the tcgen05 accumulator's truncation out of the result.
+ * Latent dims > 128 take a SIMT kernel in the reference's literal (x - y)^2 form (slower, any D <= 2048).
+ * diag (device, 4 floats, may be NULL): { 10 * g1 + g2 passes of the sweep whose result stands, measured sample error /
+ * max |grad| (0 when nothing was checked), 1 if the parity sweep had to run, max |grad_unscaled| }.
  * vk_mmd_combine: out[4] = { reg*pp + reg*zz - 2*reg*pz, pp, zz, pz } with pp = mean (rbf) / sum (imq) of the
  * (all-reduced) sums, in the reference's fp32 association (wae_mmd.py:201-203).
  * -------------------------------------------------------------------------*/
@@ -206,7 +218,7 @@ enum { VK_KERNEL_RBF = 0, VK_KERNEL_IMQ = 1 };
 int64_t vk_mmd_workspace_bytes(int64_t N, int64_t D);
 int vk_mmd_fwd(const float* z, const float* prior, int64_t N, int64_t D, int kernel_type, float z_var, int passes,
                int64_t row_begin, int64_t row_end, double* sums_out /*[3]*/, float* grad_unscaled,
-               void* workspace, int64_t workspace_bytes, void* stream);
+               float* diag /*[4] or NULL*/, void* workspace, int64_t workspace_bytes, void* stream);
 int vk_mmd_combine(const double* sums /*[3]*/, int64_t N, int kernel_type, float reg_weight, float* out /*[4]*/, void* stream);
 /* out[i] = in[i] * (*g) * factor  (g may be NULL = 1): backward of an op whose gradient was produced in the forward sweep */
 int vk_scale_by_scalar(const float* in, const float* g, float factor, int64_t n, float* out, void* stream);

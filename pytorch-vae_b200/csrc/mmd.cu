@@ -4,23 +4,36 @@
 // The reference materialises x1.expand(N,N,D) - x2.expand(N,N,D) (2.2 TB per temporary at N = 65536).  Here the
 // pairwise squared distance is  |x|^2 + |y|^2 - 2 x.y  with x.y on tcgen05 tensor cores:
 //
-//   pack kernels    z, prior_z (fp32 [N,D]) -> bf16 hi/lo operand images, 128-row tiles in the UMMA no-swizzle
+//   stats kernels   column means of z and prior -> the common centre m (distances are translation invariant, so the
+//                   whole sweep runs on x - m: smaller norms, less cancellation in |x|^2 + |y|^2 - 2 x.y), column sums of
+//                   the centred data, and the coefficient offsets c0 (the coefficient at the mean squared distance)
+//   pack kernels    z - m, prior - m (fp32 [N,D]) -> bf16 hi/lo operand images, 64-row granules in the UMMA no-swizzle
 //                   canonical layout, + fp32 row norms.  The same image is a K-major operand (K = latent dim)
 //                   for the distance GEMM and an MN-major operand (K = sample index) for the gradient GEMM.
 //   main kernel     persistent, warp-specialised, one CTA per SM:
-//     TMA warp      1-D bulk copies (cp.async.bulk -> mbarrier) of the A row block and of 64-column B stages
-//     MMA warp      GEMM1  S[128,64]  = X_i . Y_j^T         (hi*hi + lo*hi + hi*lo, fp32 accumulate in TMEM)
-//                   GEMM2  O[128,D]  += C_ij . Y_j          (coefficient tile C written by the epilogue)
-//     epilogue (4w) tcgen05.ld S -> d^2 -> k (ex2 / rcp) -> running sum of k, c = dk/dd^2 (signed) ->
-//                   row sums of c, bf16 hi/lo of c into shared memory as the A operand of GEMM2
-//   finalize        dL/dz_i (unscaled) = z_i * sum_j c_ij - O_i ; per-CTA partial sums -> three kernel sums
+//     TMA warp      1-D bulk copies (cp.async.bulk -> mbarrier) of 64-column B stages
+//     MMA warp      GEMM1  S[128,64]  = X_i . Y_j^T         (G1P passes, fp32 accumulate in TMEM)
+//                   GEMM2  O[128,D]  += C'_ij . Y_j         (G2P passes; centred coefficient tile written by the epilogue)
+//     epilogue 16w  tcgen05.ld S -> d^2 -> k (ex2 / rcp) -> running sum of k, c' = dk/dd^2 - c0 (signed) ->
+//                   row sums of c', bf16 (hi / lo) of c' into tensor memory as the A operand of GEMM2
+//   finalize        dL/dz_i (unscaled) = z_i * sum_j c'_ij - O'_i + [c0 part from the column sums, float64];
+//                   per-CTA partial sums -> three kernel sums
+//   sample check    (auto mode, reduced passes) float64 SIMT gradient of 32 sample rows against all columns; if the
+//                   measured error of the tensor sweep exceeds the budget a device flag makes the parity sweep run
 //
-// Gradient identity:  sum_j c_ij (z_i - y_j) = z_i * (sum_j c_ij) - (C Y)_i.
+// Gradient identity:  sum_j c_ij (z_i - y_j) = z_i * (sum_j c_ij) - (C Y)_i,  with c = c' + c0:
+//   = z_i * sum_j c'_ij - (C' Y)_i + c0 * (n z_i - sum_j y_j).
+// The tcgen05 fp32 accumulator truncates; accumulating C' (values ~ the SPREAD of the kernel over the batch) instead of
+// C (values ~ the kernel itself) shrinks the accumulated magnitude -- and with it the truncation bias and the bf16
+// rounding of the coefficients -- by 1 / (relative spread): 2000x for the RBF at the benchmark size.
 // The prior-prior Gram needs no gradient: it is evaluated on a circulant half (each unordered tile pair once,
 // weight 2), which is also balanced when row blocks are sharded across GPUs.
 // Reference quirks kept: RBF = exp(-|x-y|^2 / (2 D^2 z_var)) averaged over the full N x N including the diagonal
 // (wae_mmd.py:164-167); IMQ = C / (1e-7 + C + |x-y|^2), C = 2 D z_var, summed with the diagonal removed from
 // all three terms, including k(prior_i, z_i) (wae_mmd.py:185-191).
+// Latent dims > 128 do not fit the tile kernel's tensor-memory map: they take the SIMT kernel at the end of this file
+// (the reference's literal (x - y)^2 form, float64 accumulation) -- slower, same results, no exception.
+#include <stdlib.h>
 #include <type_traits>
 #include "common.cuh"
 #include "tc.cuh"
@@ -45,20 +58,29 @@ constexpr int kEpiWarps = 16, kColGroups = kEpiWarps / 4, kTmaWarp = 16, kMmaWar
 constexpr int kEpiThreads = 32 * kEpiWarps;
 constexpr int kMmdThreads = 32 * 18;  // warps 0-15 epilogue, warp 16 TMA, warp 17 MMA
 // Column chunks per row block.  Two rules pick Q: enough gradient items for the static schedule to balance (up to
-// kBalanceQ), and a bound on how many 64-column tiles are accumulated into one gradient tile in tensor memory: the
-// tcgen05 fp32 accumulator truncates, a bias that grows with the length of the chain (measured at N = 65 536 with 683
-// tiles per chain: 2.3e-4 of the gradient's maximum against float64; 16-tile chains at N = 4096 stay below 2e-5).
-// Chains are therefore cut at kChainTiles and the partial tiles are summed in fp32 round-to-nearest by the finalize
-// kernel; kMaxGradItems bounds the workspace that costs (4 GiB of partial tiles at D = 128).
-constexpr int kMaxQ = 64, kBalanceQ = 8, kChainTiles = 32;
+// kBalanceQ), and -- when a chain limit is set -- a bound on how many 64-column tiles are accumulated into one gradient
+// tile in tensor memory: the tcgen05 fp32 accumulator truncates, a bias that grows with the length of the chain AND with
+// the magnitude of the accumulated values.  Round 1 accumulated the raw coefficients (|O| ~ N k |y|: 2.3e-4 of the
+// gradient's maximum at N = 65 536 with one 683-tile chain, 1.8e-5 with 32-tile chains at 17 ms per step).  Round 2
+// accumulates CENTRED coefficients (see the head of the file), so the RBF needs no chain limit at all; the partial tiles
+// of a limited chain are summed in fp32 round-to-nearest by the finalize kernel.
+constexpr int kMaxQ = 64, kBalanceQ = 8;
 constexpr int64_t kMaxGradItems = 65536;
-// -DVK_MMD_INNER_DRAIN=1 (NOT validated on a GPU yet): cut the chains INSIDE a scheduler item instead --
-// the MMA warp commits o_full every s.chain live tiles, the epilogue drains O into sub-slot (q * subs + sub) while the
-// distance GEMMs of the next tiles run, and the row block's A operand stays in tensor memory.  Q follows the balance
-// rule only.  With the switch off the preprocessed source is the validated r01z kernel, token for token.
-#ifndef VK_MMD_INNER_DRAIN
-#define VK_MMD_INNER_DRAIN 0
-#endif
+constexpr int kSampleRows = 32, kSampleSplits = 16;     // rows / column splits of the verification sample (auto mode)
+constexpr float kVerifyBudget = 4e-6f;                  // accepted sample error relative to max |grad| (north star: 1e-5)
+constexpr int64_t kAutoMinN = 8192;                     // below this the parity sweep costs < 0.3 ms: nothing to gain
+
+// Device-side per-call state at the start of the workspace (after the ticket header).
+struct MmdStats {
+  float m[128];             // centre of the data: mean of the z and prior column means
+  double Sz[128], Sp[128];  // column sums of the centred z / prior over all N rows
+  float c0[4];              // coefficient offsets of the zz and pz tiles ([2], [3] unused)
+  unsigned int gmax_bits;   // max |grad_unscaled| written by the last finalize (float bit pattern)
+  int flag;                 // 1: the sampled check of the reduced-precision sweep failed -> the parity sweep runs
+  float verify_rel;         // measured sample error / max |grad|
+  int mode_used;            // 10 * g1p + g2p of the sweep whose result stands
+  double gref[kSampleRows * 128];   // float64 SIMT gradient sums of the sample rows (before dk_scale)
+};
 
 struct MmdShape {
   int64_t N;
@@ -67,11 +89,8 @@ struct MmdShape {
   int lz;               // live 64-column tiles per side: ceil(N / 64)
   int rb0, rb1;         // row-block range owned by this call
   int Q;                // column chunks per row block (gradient items)
-#if VK_MMD_INNER_DRAIN
-  int subs, chain;      // partial-gradient sub-slots per item, live tiles per accumulation chain
-#endif
   int kernel_type;      // 0 rbf, 1 imq
-  int passes;           // 3 (hi/lo split, fp32-grade) or 1 (plain bf16)
+  int g1p, g2p;         // tensor passes of the distance GEMM / the gradient GEMM: 3 (bf16 hi/lo split, fp32-grade) or 1
   float a_exp;          // rbf: -log2(e) / (2 D^2 z_var)
   float dk_scale;       // dk/dd^2 = dk_scale * coefficient: rbf -1 / (2 D^2 z_var) (coef k) ; imq -C (coef (k/C)^2)
   float C, Ceps;        // imq: C, fl32(1e-7 + C)
@@ -81,13 +100,17 @@ __host__ __device__ inline int rup(int x, int m) { return (x + m - 1) / m * m; }
 __host__ __device__ inline uint32_t tile_img_bytes(int Dp) { return 2u * kRows * Dp * 2u; }   // hi + lo of 128 rows
 
 struct MmdWs {
-  size_t cta_sums, imgZb, imgPb, normZ, normP, Opart, rspart, total;
+  size_t stats, colpart, cta_sums, imgZb, imgPb, normZ, normP, Opart, rspart, total;
 };
+constexpr int kStatBlocks = 296;
 inline MmdWs mmd_ws(int64_t N, int D, int rows_local_blocks, int Q) {
   const int Dp = rup(D, 16);
   const int T = (int)((N + kRows - 1) / kRows);
   MmdWs w;
   size_t o = kWsHeader;
+  w.stats = o; o += sizeof(MmdStats);
+  o = (o + 255) & ~(size_t)255;
+  w.colpart = o; o += (size_t)kStatBlocks * 2 * 130 * sizeof(double);
   w.cta_sums = o; o += (size_t)256 * 3 * sizeof(double);
   o = (o + 255) & ~(size_t)255;
   w.imgZb = o; o += (size_t)T * tile_img_bytes(Dp);      // bf16 hi/lo images in 64-row granules (column stages: one bulk copy each)
@@ -105,49 +128,21 @@ inline int q_cap(int row_blocks) {
   if (c < kBalanceQ) c = kBalanceQ;
   return (int)c;
 }
-inline int pick_Q(int T, int row_blocks) {
+// chain_tiles: longest accumulation chain in 64-column tiles (0 = no limit)
+inline int pick_Q(int T, int row_blocks, int chain_tiles) {
   // aim for >= 8 gradient items per SM so the static round-robin schedule balances
-  int q = (148 * 8 + row_blocks - 1) / row_blocks;
+  int q = (sm_count() * 8 + row_blocks - 1) / row_blocks;
   if (q > kBalanceQ) q = kBalanceQ;
-  const int chain = (4 * T + kChainTiles - 1) / kChainTiles;      // accumulation chains of at most kChainTiles tiles
-  if (chain > q) q = chain;
+  if (chain_tiles > 0) {
+    const int chain = (4 * T + chain_tiles - 1) / chain_tiles;
+    if (chain > q) q = chain;
+  }
   if (q > q_cap(row_blocks)) q = q_cap(row_blocks);
   if (q > 4 * T) q = 4 * T;
   if (q < 1) q = 1;
   const int n = 4 * T, len = (n + q - 1) / q;
   return (n + len - 1) / len;                 // no empty chunk
 }
-#if VK_MMD_INNER_DRAIN
-inline int pick_Q_balance(int T, int row_blocks) {
-  int q = (148 * 8 + row_blocks - 1) / row_blocks;
-  if (q > kBalanceQ) q = kBalanceQ;
-  if (q > 4 * T) q = 4 * T;
-  if (q < 1) q = 1;
-  const int n = 4 * T, len = (n + q - 1) / q;
-  return (n + len - 1) / len;
-}
-// sub-slots per item and live tiles per chain: kChainTiles unless that needs more than kMaxGradItems partial tiles
-inline void pick_chain(int T, int row_blocks, int Q, int& subs, int& chain) {
-  const int n = 4 * T, len = (n + Q - 1) / Q;
-  int64_t per_rb = kMaxGradItems / (row_blocks > 0 ? row_blocks : 1);
-  if (per_rb < Q) per_rb = Q;
-  const int subs_cap = (int)(per_rb / Q);                        // >= 1
-  chain = kChainTiles;
-  subs = (len + chain - 1) / chain;
-  if (subs > subs_cap) {
-    chain = (len + subs_cap - 1) / subs_cap;
-    subs = (len + chain - 1) / chain;
-  }
-  if (subs < 1) subs = 1;
-}
-// bound of Q * subs * row_blocks over every row range: Q * subs <= T / 8 + 9, and never more than the cap allows
-inline int64_t max_grad_slots(int T) {
-  const int64_t a = (int64_t)T * (T / 8 + 9);
-  int64_t b = kMaxGradItems;
-  if (b < (int64_t)kBalanceQ * T) b = (int64_t)kBalanceQ * T;
-  return a < b ? a : b;
-}
-#endif
 // upper bound of Q * row_blocks over every row range of an N-row problem (what the workspace query must cover)
 inline int64_t max_grad_items(int T) {
   int64_t a = (int64_t)kMaxQ * T;
@@ -171,8 +166,91 @@ __host__ __device__ inline MmdSmem mmd_smem(int Dp) {
   return m;
 }
 
-// ---- pack: fp32 [N,D] -> image tiles [T][hi/lo][Dp/8][128][8] bf16 ; norms [T*128] fp32 ----------------------
-__global__ void mmd_pack_kernel(const float* __restrict__ X, int64_t N, int D, int Dp, uint8_t* __restrict__ imgB, int T) {
+// ---- stats: column sums and squared norms of z and prior (double), then centre, centred sums, c0 ---------------
+// part[block][mat][0..127] column sums, [128] sum of squared row norms; one warp per row, lanes over latent dims.
+__global__ void __launch_bounds__(256)
+mmd_colsum_kernel(const float* __restrict__ Z, const float* __restrict__ P, int64_t N, int D, double* __restrict__ part) {
+  __shared__ double sh[8][2][130];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  double az[4] = {0, 0, 0, 0}, ap[4] = {0, 0, 0, 0}, nz = 0.0, np = 0.0;
+  for (int64_t r = (int64_t)blockIdx.x * 8 + warp; r < N; r += (int64_t)gridDim.x * 8) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int d = lane + 32 * k;
+      if (d < D) {
+        const double a = (double)Z[r * D + d], b = (double)P[r * D + d];
+        az[k] += a; ap[k] += b; nz += a * a; np += b * b;
+      }
+    }
+  }
+  nz = warp_sum(nz); np = warp_sum(np);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) { sh[warp][0][lane + 32 * k] = az[k]; sh[warp][1][lane + 32 * k] = ap[k]; }
+  if (lane == 0) { sh[warp][0][128] = nz; sh[warp][1][128] = np; }
+  __syncthreads();
+  for (int t = threadIdx.x; t < 2 * 130; t += blockDim.x) {
+    const int mat = t / 130, c = t % 130;
+    double v = 0.0;
+    if (c <= 128) for (int w = 0; w < 8; ++w) v += sh[w][mat][c];
+    part[((size_t)blockIdx.x * 2 + mat) * 130 + c] = v;
+  }
+}
+
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+__global__ void __launch_bounds__(128)
+mmd_stats_finalize_kernel(const double* __restrict__ part, int blocks, int64_t N, int D, int kernel_type, float a_exp,
+                          float Ceps, MmdStats* __restrict__ st) {
+  __shared__ double red[4][128];
+  const int d = threadIdx.x;
+  double sz = 0.0, sp = 0.0;
+  if (d < D) for (int b = 0; b < blocks; ++b) { sz += part[((size_t)b * 2 + 0) * 130 + d]; sp += part[((size_t)b * 2 + 1) * 130 + d]; }
+  const double n = (double)N;
+  const float m = d < D ? (float)(0.5 * (sz / n + sp / n)) : 0.f;
+  st->m[d] = m;
+  const double szc = sz - n * (double)m, spc = sp - n * (double)m;     // column sums of the centred data
+  st->Sz[d] = d < D ? szc : 0.0;
+  st->Sp[d] = d < D ? spc : 0.0;
+  // per-dim pieces of  sum |x - m|^2 = sum |x|^2 - 2 m . sum x + n |m|^2  and of  mean(z - m) . mean(p - m)
+  red[0][d] = d < D ? -2.0 * (double)m * sz + n * (double)m * (double)m : 0.0;
+  red[1][d] = d < D ? -2.0 * (double)m * sp + n * (double)m * (double)m : 0.0;
+  red[2][d] = d < D ? (szc / n) * (szc / n) : 0.0;
+  red[3][d] = d < D ? (szc / n) * (spc / n) : 0.0;
+  for (int i = d; i < kSampleRows * 128; i += blockDim.x) st->gref[i] = 0.0;
+  __syncthreads();
+  if (d == 0) {
+    double nz = 0.0, np = 0.0, a = 0.0, b = 0.0, mz2 = 0.0, mzp = 0.0;
+    for (int blk = 0; blk < blocks; ++blk) { nz += part[((size_t)blk * 2 + 0) * 130 + 128]; np += part[((size_t)blk * 2 + 1) * 130 + 128]; }
+    for (int i = 0; i < 128; ++i) { a += red[0][i]; b += red[1][i]; mz2 += red[2][i]; mzp += red[3][i]; }
+    const double ez = (nz + a) / n, ep = (np + b) / n;            // mean squared norms of the centred rows
+    double dzz = 2.0 * (ez - mz2), dpz = ez + ep - 2.0 * mzp;    // mean squared distances z-z, z-prior
+    if (dzz < 0.0) dzz = 0.0;
+    if (dpz < 0.0) dpz = 0.0;
+    float c0zz, c0pz;
+    if (kernel_type == 0) {
+      // -log2(e) / (2 D^2 z_var) = a_exp: exp(-d^2 / (2 D^2 z_var)) = 2^(a_exp d^2)
+      c0zz = exp2f(a_exp * (float)dzz); c0pz = exp2f(a_exp * (float)dpz);
+    } else {
+      const float kz = 1.0f / (Ceps + (float)dzz), kp = 1.0f / (Ceps + (float)dpz);
+      c0zz = kz * kz; c0pz = kp * kp;
+    }
+    st->c0[0] = c0zz; st->c0[1] = c0pz; st->c0[2] = 0.f; st->c0[3] = 0.f;
+    st->gmax_bits = 0u; st->flag = 0; st->verify_rel = 0.f; st->mode_used = 0;
+  }
+}
+
+// ---- pack: fp32 [N,D] - m -> image tiles [T][hi/lo][Dp/8][128][8] bf16 ; norms [T*128] fp32 ---------------------
+__global__ void mmd_pack_kernel(const float* __restrict__ X, const MmdStats* __restrict__ st, int64_t N, int D, int Dp,
+                                uint8_t* __restrict__ imgB, int T) {
   const int nkc = Dp / 8;
   const int64_t total = (int64_t)T * kRows * nkc;
   for (int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (int64_t)gridDim.x * blockDim.x) {
@@ -182,7 +260,7 @@ __global__ void mmd_pack_kernel(const float* __restrict__ X, int64_t N, int D, i
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
       const int d = kc * 8 + e;
-      v[e] = (row < N && d < D) ? X[row * D + d] : 0.f;
+      v[e] = (row < N && d < D) ? X[row * D + d] - st->m[d] : 0.f;
     }
     uint32_t ph[4], pl[4];
 #pragma unroll
@@ -201,12 +279,13 @@ __global__ void mmd_pack_kernel(const float* __restrict__ X, int64_t N, int D, i
   }
 }
 // one warp per row, fixed summation order
-__global__ void mmd_norm_kernel(const float* __restrict__ X, int64_t N, int D, float scale, float* __restrict__ norms, int T) {
+__global__ void mmd_norm_kernel(const float* __restrict__ X, const MmdStats* __restrict__ st, int64_t N, int D, float scale,
+                                float* __restrict__ norms, int T) {
   const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (row >= (int64_t)T * kRows) return;
   float s = 0.f;
-  if (row < N) for (int d = lane; d < D; d += 32) { const float v = X[row * D + d]; s = fmaf(v, v, s); }
+  if (row < N) for (int d = lane; d < D; d += 32) { const float v = X[row * D + d] - st->m[d]; s = fmaf(v, v, s); }
   s = warp_sum(s);
   if (lane == 0) norms[row] = s * scale;                 // RBF: |x|^2 * a_exp (the epilogue's ex2 argument), IMQ: |x|^2
 }
@@ -265,25 +344,24 @@ __device__ __forceinline__ TileD get_tile(const MmdShape& s, const Item& it, int
   }
   return t;
 }
-__device__ __forceinline__ float ex2_approx(float x) {
-  float y;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
-__device__ __forceinline__ float rcp_approx(float x) {
-  float y;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
 __device__ __forceinline__ bool tile_live(const MmdShape& s, const TileD& t) { return t.jt < s.lz; }
+// two fp32 -> packed bf16 pair (round to nearest), no lo part
+__device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+  return r;
+}
 
 // ---- main kernel ----------------------------------------------------------------------------------------------
-template <int PASSES, int KT>
-__global__ void __launch_bounds__(kMmdThreads, 1)
+// G1P / G2P: tensor passes of the distance / gradient GEMM.  run_if >= 0: the kernel only runs when st->flag == run_if
+// (the parity sweep behind a failed sample check).
+template <int G1P, int G2P, int KT>
+__global__ void __maxnreg__(112)     // 18 warps x 112 registers = 64 512 of the 65 536: 96 (what __launch_bounds__ picks) spills 180 B in the epilogue
 mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, const uint8_t* __restrict__ imgZb,
                 const uint8_t* __restrict__ imgPb, const float* __restrict__ normZ,
                 const float* __restrict__ normP, MmdShape s, int n_items, float* __restrict__ Opart,
-                float* __restrict__ rspart, double* __restrict__ cta_sums) {
+                float* __restrict__ rspart, double* __restrict__ cta_sums, const MmdStats* __restrict__ st, int run_if) {
+  if (run_if >= 0 && st->flag != run_if) return;          // uniform over the grid: decided before the kernel started
   extern __shared__ __align__(128) uint8_t smem[];
   const MmdSmem L = mmd_smem(s.Dp);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -307,13 +385,14 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
   const uint32_t tmem = *tmem_slot;
   const uint32_t tmem_S = tmem + kTmS, tmem_O = tmem + kTmO;
   const uint32_t b_half = (uint32_t)kCols * s.Dp * 2u;      // one hi (or lo) image of a 64-row stage
+  constexpr bool kNeedLo = G1P == 3 || G2P == 3;             // the lo image of a column stage is read by some pass
+  const uint32_t b_bytes = kNeedLo ? 2u * b_half : b_half;
 
   if (warp == kTmaWarp) {
     // ===== TMA producer =====
     if (lane == 0) {
       uint32_t nb = 0;
-      int iter = 0;
-      for (int idx = blockIdx.x; idx < n_items; idx += gridDim.x, ++iter) {
+      for (int idx = blockIdx.x; idx < n_items; idx += gridDim.x) {
         const Item it = get_item(s, idx);
         for (int u = it.u0; u < it.u1; ++u) {
           const TileD t = get_tile(s, it, u);
@@ -322,8 +401,8 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
           if (nb >= kBStages) mbar_wait(bar(kBarBEmpty + slot), ((nb / kBStages) - 1) & 1);
           const uint8_t* bimg = (t.bm ? imgPb : imgZb) + (size_t)t.jt * (2 * b_half);
           const float* nrm = (t.bm ? normP : normZ) + (size_t)t.jt * kCols;
-          mbar_expect_tx(bar(kBarBFull + slot), 2 * b_half + kCols * 4);
-          bulk_g2s(sbase + L.B + slot * (2u * b_half), bimg, 2 * b_half, bar(kBarBFull + slot));      // hi + lo images of 64 rows, one copy
+          mbar_expect_tx(bar(kBarBFull + slot), b_bytes + kCols * 4);
+          bulk_g2s(sbase + L.B + slot * (2u * b_half), bimg, b_bytes, bar(kBarBFull + slot));      // hi (+ lo) image of 64 rows, one copy
           bulk_g2s(sbase + L.norms + (nb % kNormRing) * kCols * 4, nrm, kCols * 4, bar(kBarBFull + slot));
           ++nb;
         }
@@ -357,11 +436,11 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
         const uint64_t db_hi = smem_desc(b_hi, b_lbo, 128), db_lo = smem_desc(b_hi + b_half, b_lbo, 128);
         uint32_t acc = 0;
 #pragma unroll
-        for (int pass = 0; pass < PASSES; ++pass) {
+        for (int pass = 0; pass < G1P; ++pass) {
           // passes: lo*hi, hi*lo, then hi*hi LAST -- the tensor core's fp32 accumulation truncates (~2^-23 |acc| per
           // MMA), so the correction terms are summed while the accumulator is still small (gemm3x.cuh, measured 8x)
-          uint32_t ta = (PASSES == 3 && pass == 0) ? tmem_Alo : tmem_Ahi;   // operand from tensor memory: 8 columns per K=16
-          uint64_t db = (PASSES == 3 && pass == 1) ? db_lo : db_hi;
+          uint32_t ta = (G1P == 3 && pass == 0) ? tmem_Alo : tmem_Ahi;   // operand from tensor memory: 8 columns per K=16
+          uint64_t db = (G1P == 3 && pass == 1) ? db_lo : db_hi;
 #pragma unroll 4
           for (int k = 0; k < ksteps1; ++k) {
             mma_bf16_ts_if(leader, tmem_S + sb * kCols, ta, db, idesc1, acc);
@@ -390,9 +469,6 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
           ++nb;
         }
         uint32_t oacc = 0;
-#if VK_MMD_INNER_DRAIN
-        bool o_wait = true;                                  // the next G2 is the first one into a fresh accumulator
-#endif
         // live z-side tiles of this chunk come first (tile sequence: [z tiles | prior tiles], dead tiles = columns >= N)
         int nz_live = 0;
         if (it.grad) {
@@ -414,12 +490,7 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
             const uint32_t neg_a = j >= nz_live ? (1u << 13) : 0u;           // k(z, prior) enters with a minus sign
             PROF_LAP(3)
             mbar_wait(bar(kBarKFull + kb), (nk >> 1) & 1);
-#if VK_MMD_INNER_DRAIN
-            if (o_wait && n_grad_items > 0) mbar_wait(bar(kBarOEmpty), (n_grad_items - 1) & 1);
-            o_wait = false;
-#else
             if (j == 0 && n_grad_items > 0) mbar_wait(bar(kBarOEmpty), (n_grad_items - 1) & 1);
-#endif
             PROF_LAP(2)
             TRACE(2, nk)
             fence_after_sync();
@@ -428,9 +499,9 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
             // A: coefficient tile in tensor memory (K = column index) ; B: MN-major (N = latent dims, K = rows of the stage)
             const uint64_t db_hi = smem_desc(b_hi, 128, b_lbo), db_lo = smem_desc(b_hi + b_half, 128, b_lbo);
 #pragma unroll
-            for (int pass = 0; pass < PASSES; ++pass) {
-              uint32_t ta = (PASSES == 3 && pass == 0) ? tk_lo : tk_hi;
-              uint64_t db = (PASSES == 3 && pass == 1) ? db_lo : db_hi;
+            for (int pass = 0; pass < G2P; ++pass) {
+              uint32_t ta = (G2P == 3 && pass == 0) ? tk_lo : tk_hi;
+              uint64_t db = (G2P == 3 && pass == 1) ? db_lo : db_hi;
 #pragma unroll
               for (int k = 0; k < kCols / 16; ++k) {
                 mma_bf16_ts_if(leader, tmem_O, ta, db, idesc2 | neg_a, oacc);
@@ -443,14 +514,6 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
             mma_commit_if(leader, bar(kBarKEmpty + kb));
             TRACE(3, nk)
             ++nk;
-#if VK_MMD_INNER_DRAIN
-            if ((j + 1) % s.chain == 0 && j + 1 < live) {      // chain complete: hand O to the epilogue, start a new one
-              mma_commit_if(leader, bar(kBarOFull));
-              ++n_grad_items;
-              oacc = 0;
-              o_wait = true;
-            }
-#endif
           }
         }
         if (it.grad && live > 0) { mma_commit_if(leader, bar(kBarOFull)); ++n_grad_items; }
@@ -474,6 +537,7 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
     uint32_t ns = 0, nk = 0, nb = 0, n_grad_items = 0, item_iter = 0;
     // RBF: norms arrive pre-scaled by a_exp, so ex2's argument is one FADD + one FFMA; IMQ: t = C + eps + d^2
     const float s_coef = KT == 0 ? -2.f * s.a_exp : -2.f;
+    const float c0zz = st->c0[0], c0pz = st->c0[1];          // coefficient offsets (written by the stats kernel)
     PROF_DECL
     TRACE_DECL(3)
     for (int idx = blockIdx.x; idx < n_items; idx += gridDim.x) {
@@ -485,52 +549,13 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
       const float nx = (it.grad ? normZ : normP)[grow] + (KT == 1 ? s.Ceps : 0.f);
       float rs = 0.f;
       int live = 0;
-#if VK_MMD_INNER_DRAIN
-      const int q_item = idx % (s.Q + 1);
-      const size_t lrow_i = (size_t)(it.i - s.rb0) * kRows + t;
-      const size_t nloc_i = (size_t)(s.rb1 - s.rb0) * kRows;
-      int nlive = 0;
-      if (it.grad)
-        for (int u = it.u0; u < it.u1; ++u) nlive += tile_live(s, get_tile(s, it, u)) ? 1 : 0;
-      // partial slot (q * subs + sub) <- this warp's row sums of the chain and its 32 x 32 chunk of O (zeros when there
-      // is no accumulator to read); every epilogue warp calls it at the same live-tile count (.sync.aligned inside)
-      auto drain_o = [&](int sub, bool have_o) {
-        const size_t slot = (size_t)q_item * s.subs + sub;
-        float* op = Opart + (slot * nloc_i + lrow_i) * s.Dp;
-        rspart[(slot * kColGroups + cg) * nloc_i + lrow_i] = rs;
-        rs = 0.f;
-        const int c0 = cg * 32;
-        if (!have_o) {
-          for (int e = c0; e < c0 + 32 && e < s.Dp; ++e) op[e] = 0.f;
-          return;
-        }
-        mbar_wait(bar(kBarOFull), n_grad_items & 1);
-        fence_after_sync();
-        if (c0 < s.Dp) {
-          uint32_t o[32];
-          tmem_ld32(tmem_O + ((uint32_t)(ew * 32) << 16) + c0, o);
-          tmem_ld_wait();
-          if (c0 + 32 <= s.Dp) {
-#pragma unroll
-            for (int e = 0; e < 32; e += 4)
-              *reinterpret_cast<float4*>(op + c0 + e) = make_float4(__uint_as_float(o[e]), __uint_as_float(o[e + 1]),
-                                                                     __uint_as_float(o[e + 2]), __uint_as_float(o[e + 3]));
-          } else {
-#pragma unroll
-            for (int e = 0; e < 32; ++e) if (c0 + e < s.Dp) op[c0 + e] = __uint_as_float(o[e]);
-          }
-        }
-        fence_before_sync();
-        mbar_arrive(bar(kBarOEmpty));
-        ++n_grad_items;
-      };
-#endif
       {
-        // this row block's operand -> tensor memory: fp32 row slice [cg*32, cg*32+32) split into bf16 hi / lo, two per
-        // column.  The previous item's MMAs must be finished with the old block first.
+        // this row block's operand -> tensor memory: fp32 row slice [cg*32, cg*32+32) of x - m split into bf16 hi / lo,
+        // two per column.  The previous item's MMAs must be finished with the old block first.
         if (item_iter > 0) mbar_wait(bar(kBarAEmpty), (item_iter - 1) & 1);
         fence_after_sync();
         const float* xr = (it.grad ? Zf : Pf) + (int64_t)grow * s.D + cg * 32;
+        const float* mr = st->m + cg * 32;
         const uint32_t ta = tmem + ((uint32_t)(ew * 32) << 16) + cg * 16;
 #pragma unroll
         for (int j8 = 0; j8 < 16; j8 += 8) {
@@ -538,12 +563,13 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             const int d = cg * 32 + 2 * (j8 + j);
-            const float a = (rvalid && d < s.D) ? __ldg(xr + 2 * (j8 + j)) : 0.f;
-            const float b = (rvalid && d + 1 < s.D) ? __ldg(xr + 2 * (j8 + j) + 1) : 0.f;
-            split_pair(a, b, ah[j], al[j]);
+            const float a = (rvalid && d < s.D) ? __ldg(xr + 2 * (j8 + j)) - mr[2 * (j8 + j)] : 0.f;
+            const float b = (rvalid && d + 1 < s.D) ? __ldg(xr + 2 * (j8 + j) + 1) - mr[2 * (j8 + j) + 1] : 0.f;
+            if (G1P == 3) split_pair(a, b, ah[j], al[j]);
+            else ah[j] = pack_bf16x2(a, b);
           }
           tmem_st8(ta + kTmAhi + j8, ah);
-          tmem_st8(ta + kTmAlo + j8, al);
+          if (G1P == 3) tmem_st8(ta + kTmAlo + j8, al);
         }
         tmem_st_wait();
         fence_before_sync();
@@ -567,9 +593,10 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
           const int gcol0 = td.jt * kCols + h * 32;
           // uniform across the warp (the two instances below contain .sync.aligned tcgen05 instructions)
           const bool slow = td.diag || gcol0 + 32 > n32 || row_tail;
-          float ksum = 0.f, csum = 0.f;                       // sum of k (value) and of the coefficient (gradient)
+          float ksum = 0.f, csum = 0.f;                       // sum of k (value) and of the centred coefficient (gradient)
           const uint32_t tk = tmem + ((uint32_t)(ew * 32) << 16) + kTmK + (nk & 1) * 64 + h * 16;
           const bool diag_excl = KT == 1 && td.diag;
+          const float c0k = td.kind == 0 ? c0zz : c0pz;       // (unused by the prior-prior tiles)
           // interior tiles take the branch-free instance; diagonal / tail tiles the masked one
           auto tile_math = [&](auto masked_c, auto grad_c) {
             constexpr bool MASKED = decltype(masked_c)::value, GRAD = decltype(grad_c)::value;
@@ -595,10 +622,10 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
                 float k;
                 if (KT == 0) {
                   k = ex2_approx(arg);                        // exp(-d^2 / (2 D^2 z_var))
-                  cv[e] = k;                                  // dk/dd^2 = k * dk_scale: the constant is applied in finalize
+                  cv[e] = k - c0k;                            // dk/dd^2 = k * dk_scale: the constant is applied in finalize
                 } else {
                   k = rcp_approx(arg);                        // k / C = 1 / (C + eps + d^2)
-                  cv[e] = k * k;                              // dk/dd^2 = -C * (k/C)^2
+                  cv[e] = fmaf(k, k, -c0k);                   // dk/dd^2 = -C * (k/C)^2
                 }
                 if (MASKED) {                                 // diagonal exclusion, tail rows / columns
                   const bool ok = rvalid && (gcol0 + c < n32) && !(diag_excl && gcol0 + c == grow);
@@ -606,11 +633,14 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
                   cv[e] = ok ? cv[e] : 0.f;
                 }
                 ksum += k;
-                if (KT == 1) csum += cv[e];
+                if (GRAD) csum += cv[e];
               }
               if (GRAD) {
 #pragma unroll
-                for (int e = 0; e < 4; ++e) split_pair(cv[2 * e], cv[2 * e + 1], kh[(c8 >> 1) + e], kl[(c8 >> 1) + e]);
+                for (int e = 0; e < 4; ++e) {
+                  if (G2P == 3) split_pair(cv[2 * e], cv[2 * e + 1], kh[(c8 >> 1) + e], kl[(c8 >> 1) + e]);
+                  else kh[(c8 >> 1) + e] = pack_bf16x2(cv[2 * e], cv[2 * e + 1]);
+                }
               }
             }
             if (GRAD) {
@@ -621,7 +651,7 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
                 TRACE(1, ns)
               }
               tmem_st8(tk + hf * 8, kh);
-              tmem_st8(tk + 32 + hf * 8, kl);
+              if (G2P == 3) tmem_st8(tk + 32 + hf * 8, kl);
             }
           }
           };
@@ -630,7 +660,6 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
           } else {
             if (slow) tile_math(std::true_type{}, std::false_type{}); else tile_math(std::false_type{}, std::false_type{});
           }
-          if (KT == 0) csum = ksum;
           rs += td.kind == 1 ? -csum : csum;                  // GEMM2 applies the same sign with the negate-A bit
           if (td.kind != run_kind) {                          // (warp-uniform, once or twice per item)
             if (run_kind == 0) acc_zz += acc_run; else if (run_kind == 1) acc_pz += acc_run; else if (run_kind == 2) acc_pp += acc_run;
@@ -649,18 +678,8 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
         ++live;
         if (it.grad) ++nk;
         ++nb;
-#if VK_MMD_INNER_DRAIN
-        if (it.grad && live % s.chain == 0 && live < nlive) drain_o(live / s.chain - 1, true);
-#endif
       }
       PROF_LAP(1)
-#if VK_MMD_INNER_DRAIN
-      if (it.grad) {
-        const int last = live == 0 ? 0 : (live - 1) / s.chain;
-        drain_o(last, live > 0);
-        for (int sub = last + 1; sub < s.subs; ++sub) drain_o(sub, false);     // unused sub-slots of a short item
-      }
-#else
       if (it.grad) {
         const int q = (idx % (s.Q + 1));
         const size_t lrow = (size_t)(it.i - s.rb0) * kRows + t;
@@ -693,7 +712,6 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
         mbar_arrive(bar(kBarOEmpty));
         ++n_grad_items;
       }
-#endif
       PROF_LAP(3)
     }
     PROF_OUT("epilogue wait_s_full/work/wait_k_empty/item_end", threadIdx.x == 0)
@@ -716,34 +734,141 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
   if (warp == kMmaWarp) tmem_dealloc(tmem, 512);
 }
 
-// ---- finalize: G_i = z_i * sum_q rs - sum_q O ; the three kernel sums ----------------------------------------
-__global__ void mmd_finalize_kernel(const float* __restrict__ Z, MmdShape s, const float* __restrict__ Opart,
-                                    const float* __restrict__ rspart, const double* __restrict__ cta_sums, int grid_main,
-                                    float* __restrict__ grad, double* __restrict__ sums) {
+// ---- finalize: G_i = z_i * sum_q rs' - sum_q O' + c0 part ; the three kernel sums -----------------------------
+// The c0 part of the gradient, from the column sums (float64):  rbf (every column carries a coefficient)
+//   (c0zz - c0pz) N z_i - c0zz Sz + c0pz Sp ;  imq (column i carries none):
+//   (c0zz - c0pz) (N - 1) z_i - c0zz (Sz - z_i) + c0pz (Sp - p_i)         (z, p, Sz, Sp of the centred data)
+__global__ void mmd_finalize_kernel(const float* __restrict__ Z, const float* __restrict__ P, MmdShape s,
+                                    const float* __restrict__ Opart, const float* __restrict__ rspart,
+                                    const double* __restrict__ cta_sums, int grid_main, float* __restrict__ grad,
+                                    double* __restrict__ sums, MmdStats* __restrict__ st, int run_if) {
+  if (run_if >= 0 && st->flag != run_if) return;
   const int64_t row0 = (int64_t)s.rb0 * kRows;
   const int64_t nloc_pad = (int64_t)(s.rb1 - s.rb0) * kRows;
   int64_t nloc = s.N - row0;
   if (nloc > nloc_pad) nloc = nloc_pad;
   const int64_t total = nloc * s.D;
+  const double c0zz = (double)st->c0[0], c0pz = (double)st->c0[1];
+  const double n = (double)s.N;
+  float gmax = 0.f;
   for (int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (int64_t)gridDim.x * blockDim.x) {
     const int64_t r = g / s.D;
     const int d = (int)(g % s.D);
     float rs = 0.f, o = 0.f;
-#if VK_MMD_INNER_DRAIN
-    const int n_slots = s.Q * s.subs;
-#else
-    const int n_slots = s.Q;
-#endif
-    for (int q = 0; q < n_slots; ++q) {
+    for (int q = 0; q < s.Q; ++q) {
       for (int c = 0; c < kColGroups; ++c) rs += rspart[(size_t)(q * kColGroups + c) * nloc_pad + r];
       o += Opart[((size_t)q * nloc_pad + r) * s.Dp + d];
     }
-    grad[g] = s.dk_scale * fmaf(Z[(row0 + r) * s.D + d], rs, -o);     // dk/dd^2 constant: -1/(2 D^2 z_var) | -C
+    const float zc = Z[(row0 + r) * s.D + d] - st->m[d];
+    double ana;
+    if (s.kernel_type == 0) {
+      ana = (c0zz - c0pz) * n * (double)zc - c0zz * st->Sz[d] + c0pz * st->Sp[d];
+    } else {
+      const float pc = P[(row0 + r) * s.D + d] - st->m[d];
+      ana = (c0zz - c0pz) * (n - 1.0) * (double)zc - c0zz * (st->Sz[d] - (double)zc) + c0pz * (st->Sp[d] - (double)pc);
+    }
+    const float gv = s.dk_scale * (float)((double)fmaf(zc, rs, -o) + ana);     // dk/dd^2 constant: -1/(2 D^2 z_var) | -C
+    grad[g] = gv;
+    gmax = fmaxf(gmax, fabsf(gv));
   }
+  gmax = warp_max(gmax);
+  if ((threadIdx.x & 31) == 0 && gmax > 0.f) atomicMax(&st->gmax_bits, __float_as_uint(gmax));
   if (blockIdx.x == 0 && threadIdx.x < 3) {
     double t = 0.0;
     for (int c = 0; c < grid_main; ++c) t += cta_sums[c * 3 + threadIdx.x];
     sums[threadIdx.x] = t;                       // order: zz, pz, pp
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) st->mode_used = 10 * s.g1p + s.g2p;
+}
+
+// ---- SIMT rows: the reference's literal (x - y)^2 form, float64 accumulation --------------------------------------
+// One CTA (8 warps) per row; a warp takes one column at a time, lanes over latent dims.  Used (a) for the sampled check of
+// a reduced-precision tensor sweep (few rows, column range split over gridDim.y, atomics into MmdStats::gref) and (b) as
+// the whole path for latent dims > 128 (every row, gridDim.y == 1, deterministic).
+//   X rows, Y columns [N, D]; rows i = row0 + blockIdx.x * row_step; sign +1 / -1 of the gradient contribution;
+//   gacc [rows, D] float64 accumulators (NULL: no gradient), krow [rows]: each row's kernel sum (NULL: none; needs
+//   gridDim.y == 1).
+template <int KT>
+__global__ void __launch_bounds__(256)
+mmd_simt_rows_kernel(const float* __restrict__ X, const float* __restrict__ Y, int64_t N, int D, int64_t row0,
+                     int64_t row_step, int64_t n_rows, float a_exp, float Ceps, float C, double sign,
+                     double* __restrict__ gacc, bool g_atomic, double* __restrict__ krow) {
+  extern __shared__ double sh[];                 // [8][D] gradient partials | [8] k partials
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if ((int64_t)blockIdx.x >= n_rows) return;
+  const int64_t i = row0 + (int64_t)blockIdx.x * row_step;
+  const float* xi = X + i * D;
+  double* acc = sh + (size_t)warp * D;
+  for (int d = lane; d < D; d += 32) acc[d] = 0.0;
+  double ks = 0.0;
+  const int64_t span = (N + gridDim.y - 1) / gridDim.y;
+  const int64_t j0 = (int64_t)blockIdx.y * span, j1 = j0 + span < N ? j0 + span : N;
+  for (int64_t j = j0 + warp; j < j1; j += 8) {
+    const float* yj = Y + j * D;
+    float s2 = 0.f;
+    for (int d = lane; d < D; d += 32) { const float t = xi[d] - yj[d]; s2 = fmaf(t, t, s2); }
+    s2 = warp_sum(s2);
+    float k, coef;
+    if (KT == 0) { k = exp2f(a_exp * s2); coef = k; }
+    else { const float r = 1.0f / (Ceps + s2); k = C * r; coef = r * r; }
+    if (KT == 1 && j == i) continue;                           // imq: the diagonal is removed from every term
+    ks += (double)k;
+    if (gacc) for (int d = lane; d < D; d += 32) acc[d] += (double)(coef * (xi[d] - yj[d]));
+  }
+  __syncthreads();
+  double* kred = sh + (size_t)8 * D;
+  if (lane == 0) kred[warp] = ks;
+  __syncthreads();
+  if (gacc) {
+    for (int d = threadIdx.x; d < D; d += blockDim.x) {
+      double t = 0.0;
+      for (int w = 0; w < 8; ++w) t += sh[(size_t)w * D + d];
+      double* dst = gacc + (size_t)blockIdx.x * D + d;
+      if (g_atomic) atomicAdd(dst, sign * t); else *dst += sign * t;
+    }
+  }
+  if (krow && threadIdx.x == 0) {
+    double t = 0.0;
+    for (int w = 0; w < 8; ++w) t += kred[w];
+    krow[blockIdx.x] = t;
+  }
+}
+
+// sample check: max |grad - dk_scale * gref| over the sample rows against the budget -> st->flag
+__global__ void __launch_bounds__(256)
+mmd_verify_kernel(const float* __restrict__ grad, int D, int64_t row_step, int n_rows, float dk_scale, float budget,
+                  MmdStats* __restrict__ st) {
+  __shared__ float red[8];
+  float e = 0.f;
+  for (int t = threadIdx.x; t < n_rows * D; t += blockDim.x) {
+    const int r = t / D, d = t % D;
+    const float ref = dk_scale * (float)st->gref[(size_t)r * D + d];
+    e = fmaxf(e, fabsf(grad[(size_t)r * row_step * D + d] - ref));
+  }
+  e = warp_max(e);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = e;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < 8; ++w) e = fmaxf(e, red[w]);
+    const float gmax = __uint_as_float(st->gmax_bits);
+    const float rel = gmax > 0.f ? e / gmax : 0.f;
+    st->verify_rel = rel;
+    st->flag = (rel <= budget) ? 0 : 1;                       // NaN compares false: the parity sweep runs
+  }
+}
+
+// general-D path: float64 accumulators -> grad_unscaled; per-row kernel sums -> the three sums in a fixed order
+__global__ void __launch_bounds__(256)
+mmd_simt_finish_kernel(const double* __restrict__ gacc, int64_t count, float dk_scale, float* __restrict__ grad,
+                       const double* __restrict__ krow, int64_t rows, double* __restrict__ sums) {
+  __shared__ double red[3 * 8];
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (int64_t)gridDim.x * blockDim.x)
+    grad[i] = dk_scale * (float)gacc[i];
+  if (blockIdx.x == 0) {
+    double v[3] = {0.0, 0.0, 0.0};
+    for (int64_t r = threadIdx.x; r < rows; r += blockDim.x) { v[0] += krow[r]; v[1] += krow[rows + r]; v[2] += krow[2 * rows + r]; }
+    block_sum<3>(v, red);
+    if (threadIdx.x == 0) { sums[0] = v[0]; sums[1] = v[1]; sums[2] = v[2]; }
   }
 }
 
@@ -764,34 +889,78 @@ __global__ void scale_by_scalar_kernel(const float* __restrict__ in, const float
     out[i] = in[i] * f;
 }
 
-int make_shape(int64_t N, int64_t D, int kernel_type, float z_var, int passes, int64_t row_begin, int64_t row_end,
-               MmdShape& s) {
-  VK_REQUIRE(N >= 1 && D >= 1, VK_ERR_BAD_ARG, "mmd: empty z [%lld,%lld]", (long long)N, (long long)D);
-  VK_REQUIRE(D <= 128, VK_ERR_UNSUPPORTED, "mmd: latent dim %lld > 128 is not supported by the Gram tile kernel", (long long)D);
-  VK_REQUIRE(N <= (int64_t)1 << 24, VK_ERR_UNSUPPORTED, "mmd: N=%lld too large", (long long)N);
-  VK_REQUIRE(kernel_type == 0 || kernel_type == 1, VK_ERR_BAD_ARG, "mmd: unknown kernel type %d", kernel_type);
-  VK_REQUIRE(passes == 1 || passes == 3, VK_ERR_BAD_ARG, "mmd: passes must be 1 or 3");
-  VK_REQUIRE(row_begin >= 0 && row_begin < row_end && row_end <= N && row_begin % kRows == 0 &&
-             (row_end % kRows == 0 || row_end == N), VK_ERR_BAD_ARG,
-             "mmd: row range [%lld,%lld) must be 128-aligned inside [0,%lld)", (long long)row_begin, (long long)row_end, (long long)N);
+__global__ void mmd_diag_kernel(const MmdStats* __restrict__ st, float* __restrict__ diag) {
+  diag[0] = (float)st->mode_used;
+  diag[1] = st->verify_rel;
+  diag[2] = (float)st->flag;
+  diag[3] = __uint_as_float(st->gmax_bits);
+}
+
+int chain_limit(int kernel_type) {
+  // longest accumulation chain in 64-column tiles, 0 = none.  Centred coefficients make the RBF chain harmless; the IMQ
+  // coefficients spread ~8 % around c0 at the benchmark size, so its chains are still cut (VK_MMD_CHAIN overrides both).
+  static const int env = [] { const char* e = getenv("VK_MMD_CHAIN"); return e ? atoi(e) : -1; }();
+  if (env >= 0) return env;
+  return kernel_type == 0 ? 0 : 128;
+}
+
+void make_shape(int64_t N, int64_t D, int kernel_type, float z_var, int64_t row_begin, int64_t row_end, MmdShape& s) {
   s.N = N; s.D = (int)D; s.Dp = rup((int)D, 16); s.nkc = s.Dp / 8;
   s.T = (int)((N + kRows - 1) / kRows);
   s.lz = (int)((N + kCols - 1) / kCols);
   s.rb0 = (int)(row_begin / kRows);
   s.rb1 = (int)((row_end + kRows - 1) / kRows);
-#if VK_MMD_INNER_DRAIN
-  s.Q = pick_Q_balance(s.T, s.rb1 - s.rb0);
-  pick_chain(s.T, s.rb1 - s.rb0, s.Q, s.subs, s.chain);
-#else
-  s.Q = pick_Q(s.T, s.rb1 - s.rb0);
-#endif
-  s.kernel_type = kernel_type; s.passes = passes;
+  s.Q = pick_Q(s.T, s.rb1 - s.rb0, chain_limit(kernel_type));
+  s.kernel_type = kernel_type; s.g1p = 3; s.g2p = 3;
   const double sp = 2.0 * (double)D * (double)D * (double)z_var;
   s.a_exp = (float)(-1.4426950408889634 / sp);
   s.C = (float)(2.0 * (double)D * (double)z_var);
   s.Ceps = (float)(1e-7 + (double)s.C);
   s.dk_scale = kernel_type == 0 ? (float)(-1.0 / sp) : -s.C;      // applied once, in finalize
-  return VK_OK;
+}
+
+template <int G1P, int G2P>
+int launch_sweep(const float* z, const float* prior, const MmdShape& s, const MmdWs& w, uint8_t* ws, double* sums_out,
+                 float* grad_unscaled, int run_if, cudaStream_t st) {
+  const MmdSmem L = mmd_smem(s.Dp);
+  const int n_items = (s.rb1 - s.rb0) * (s.Q + 1);
+  const int grid = n_items < sm_count() ? n_items : sm_count();
+  auto kern = s.kernel_type == 0 ? mmd_main_kernel<G1P, G2P, 0> : mmd_main_kernel<G1P, G2P, 1>;
+  static bool attr_done[2] = {false, false};                  // once per instantiation and kernel type
+  if (!attr_done[s.kernel_type]) {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mmd_smem(128).total) != cudaSuccess)
+      return check_launch("mmd_fwd (shared memory attribute)");
+    attr_done[s.kernel_type] = true;
+  }
+  MmdStats* stats = (MmdStats*)(ws + w.stats);
+  kern<<<grid, kMmdThreads, L.total, st>>>(z, prior, ws + w.imgZb, ws + w.imgPb, (const float*)(ws + w.normZ),
+                                           (const float*)(ws + w.normP), s, n_items, (float*)(ws + w.Opart),
+                                           (float*)(ws + w.rspart), (double*)(ws + w.cta_sums), stats, run_if);
+  int rc = check_launch("mmd_main");
+  if (rc != VK_OK) return rc;
+  mmd_finalize_kernel<<<sm_count() * 4, 256, 0, st>>>(z, prior, s, (const float*)(ws + w.Opart), (const float*)(ws + w.rspart),
+                                                       (const double*)(ws + w.cta_sums), grid, grad_unscaled, sums_out, stats,
+                                                       run_if);
+  return check_launch("mmd_finalize");
+}
+
+int dispatch_sweep(int g1p, int g2p, const float* z, const float* prior, MmdShape s, const MmdWs& w, uint8_t* ws,
+                   double* sums_out, float* grad_unscaled, int run_if, cudaStream_t st) {
+  s.g1p = g1p; s.g2p = g2p;
+  if (g1p == 3 && g2p == 3) return launch_sweep<3, 3>(z, prior, s, w, ws, sums_out, grad_unscaled, run_if, st);
+  if (g1p == 3 && g2p == 1) return launch_sweep<3, 1>(z, prior, s, w, ws, sums_out, grad_unscaled, run_if, st);
+  return launch_sweep<1, 1>(z, prior, s, w, ws, sums_out, grad_unscaled, run_if, st);
+}
+
+struct SimtWs { size_t gacc, krow, total; };
+inline SimtWs simt_ws(int64_t rows, int64_t D) {
+  SimtWs w;
+  size_t o = kWsHeader;
+  w.krow = o; o += (size_t)3 * rows * sizeof(double);
+  o = (o + 255) & ~(size_t)255;
+  w.gacc = o; o += (size_t)rows * D * sizeof(double);
+  w.total = o;
+  return w;
 }
 
 }  // namespace
@@ -800,56 +969,105 @@ int make_shape(int64_t N, int64_t D, int kernel_type, float z_var, int passes, i
 using namespace vk;
 
 extern "C" int64_t vk_mmd_workspace_bytes(int64_t N, int64_t D) {
-  if (N < 1 || D < 1 || D > 128) return -1;
+  if (N < 1 || D < 1) return -1;
+  if (D > 128) return (int64_t)simt_ws(N, D).total;           // SIMT path: float64 gradient accumulators
   const int T = (int)((N + kRows - 1) / kRows);
-#if VK_MMD_INNER_DRAIN
-  const int64_t items = max_grad_slots(T);
-#else
   const int64_t items = max_grad_items(T);
-#endif
   VK_REQUIRE(items < (int64_t)1 << 31, -1, "mmd_workspace_bytes: N too large");
   return (int64_t)mmd_ws(N, (int)D, (int)items, 1).total;
 }
 
 extern "C" int vk_mmd_fwd(const float* z, const float* prior, int64_t N, int64_t D, int kernel_type, float z_var,
                           int passes, int64_t row_begin, int64_t row_end, double* sums_out, float* grad_unscaled,
-                          void* workspace, int64_t workspace_bytes, void* stream) {
+                          float* diag, void* workspace, int64_t workspace_bytes, void* stream) {
   VK_REQUIRE(z && prior && sums_out && grad_unscaled && workspace, VK_ERR_BAD_ARG, "mmd_fwd: null pointer");
-  MmdShape s;
-  int rc = make_shape(N, D, kernel_type, z_var, passes, row_begin, row_end, s);
-  if (rc != VK_OK) return rc;
-#if VK_MMD_INNER_DRAIN
-  const MmdWs w = mmd_ws(N, (int)D, s.rb1 - s.rb0, s.Q * s.subs);
-#else
-  const MmdWs w = mmd_ws(N, (int)D, s.rb1 - s.rb0, s.Q);
-#endif
-  VK_REQUIRE(workspace_bytes >= (int64_t)w.total, VK_ERR_WORKSPACE, "mmd_fwd: workspace %lld < %lld",
-             (long long)workspace_bytes, (long long)w.total);
+  VK_REQUIRE(N >= 1 && D >= 1, VK_ERR_BAD_ARG, "mmd: empty z [%lld,%lld]", (long long)N, (long long)D);
+  VK_REQUIRE(N <= (int64_t)1 << 24, VK_ERR_UNSUPPORTED, "mmd: N=%lld too large", (long long)N);
+  VK_REQUIRE(kernel_type == 0 || kernel_type == 1, VK_ERR_BAD_ARG, "mmd: unknown kernel type %d", kernel_type);
+  VK_REQUIRE(passes >= 0 && passes <= 3, VK_ERR_BAD_ARG, "mmd: passes must be 0 (auto), 1, 2 or 3");
+  VK_REQUIRE(row_begin >= 0 && row_begin < row_end && row_end <= N && row_begin % kRows == 0 &&
+             (row_end % kRows == 0 || row_end == N), VK_ERR_BAD_ARG,
+             "mmd: row range [%lld,%lld) must be 128-aligned inside [0,%lld)", (long long)row_begin, (long long)row_end, (long long)N);
   cudaStream_t st = (cudaStream_t)stream;
   uint8_t* ws = (uint8_t*)workspace;
+  MmdShape s;
+  make_shape(N, D, kernel_type, z_var, row_begin, row_end, s);
+  if (D > 128) {
+    // ---- general latent dim: SIMT rows, every term in the reference's (x - y)^2 form ----
+    const int64_t rows = row_end - row_begin;
+    const SimtWs w = simt_ws(rows, D);
+    VK_REQUIRE(workspace_bytes >= (int64_t)w.total, VK_ERR_WORKSPACE, "mmd_fwd: workspace %lld < %lld",
+               (long long)workspace_bytes, (long long)w.total);
+    VK_REQUIRE(D <= 2048, VK_ERR_UNSUPPORTED, "mmd: latent dim %lld > 2048", (long long)D);
+    double* ks = (double*)(ws + w.krow);
+    double* gacc = (double*)(ws + w.gacc);
+    cudaMemsetAsync(gacc, 0, (size_t)rows * D * sizeof(double), st);
+    const size_t shb = ((size_t)8 * D + 8) * sizeof(double);
+    auto kern = kernel_type == 0 ? mmd_simt_rows_kernel<0> : mmd_simt_rows_kernel<1>;
+    if (shb > 48 * 1024 && cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shb) != cudaSuccess)
+      return check_launch("mmd_fwd (SIMT shared memory attribute)");
+    const dim3 grid((unsigned)rows, 1);
+    kern<<<grid, 256, shb, st>>>(z, z, N, (int)D, row_begin, 1, rows, s.a_exp, s.Ceps, s.C, 1.0, gacc, false, ks);
+    kern<<<grid, 256, shb, st>>>(z, prior, N, (int)D, row_begin, 1, rows, s.a_exp, s.Ceps, s.C, -1.0, gacc, false, ks + rows);
+    kern<<<grid, 256, shb, st>>>(prior, prior, N, (int)D, row_begin, 1, rows, s.a_exp, s.Ceps, s.C, 0.0, nullptr, false, ks + 2 * rows);
+    int rc = check_launch("mmd_simt_rows");
+    if (rc != VK_OK) return rc;
+    mmd_simt_finish_kernel<<<sm_count() * 2, 256, 0, st>>>(gacc, rows * D, s.dk_scale, grad_unscaled, ks, rows, sums_out);
+    if (diag) cudaMemsetAsync(diag, 0, 4 * sizeof(float), st);
+    return check_launch("mmd_simt_finish");
+  }
+  const MmdWs w = mmd_ws(N, (int)D, s.rb1 - s.rb0, s.Q);
+  VK_REQUIRE(workspace_bytes >= (int64_t)w.total, VK_ERR_WORKSPACE, "mmd_fwd: workspace %lld < %lld",
+             (long long)workspace_bytes, (long long)w.total);
+  MmdStats* stats = (MmdStats*)(ws + w.stats);
+  double* colpart = (double*)(ws + w.colpart);
+  // ---- statistics, centre, operand images ----
+  const int sblocks = (int)((N + 7) / 8 < kStatBlocks ? (N + 7) / 8 : kStatBlocks);
+  mmd_colsum_kernel<<<sblocks, 256, 0, st>>>(z, prior, N, (int)D, colpart);
+  mmd_stats_finalize_kernel<<<1, 128, 0, st>>>(colpart, sblocks, N, (int)D, kernel_type, s.a_exp, s.Ceps, stats);
   const int64_t pack_work = (int64_t)s.T * kRows * s.nkc;
-  const int pack_blocks = (int)((pack_work + 255) / 256 < 148 * 16 ? (pack_work + 255) / 256 : 148 * 16);
+  const int64_t pack_cap = (int64_t)sm_count() * 16;
+  const int pack_blocks = (int)((pack_work + 255) / 256 < pack_cap ? (pack_work + 255) / 256 : pack_cap);
   const int norm_blocks = (int)(((int64_t)s.T * kRows * 32 + 255) / 256);
-  mmd_pack_kernel<<<pack_blocks, 256, 0, st>>>(z, N, (int)D, s.Dp, ws + w.imgZb, s.T);
-  mmd_pack_kernel<<<pack_blocks, 256, 0, st>>>(prior, N, (int)D, s.Dp, ws + w.imgPb, s.T);
+  mmd_pack_kernel<<<pack_blocks, 256, 0, st>>>(z, stats, N, (int)D, s.Dp, ws + w.imgZb, s.T);
+  mmd_pack_kernel<<<pack_blocks, 256, 0, st>>>(prior, stats, N, (int)D, s.Dp, ws + w.imgPb, s.T);
   const float nscale = kernel_type == 0 ? s.a_exp : 1.f;
-  mmd_norm_kernel<<<norm_blocks, 256, 0, st>>>(z, N, (int)D, nscale, (float*)(ws + w.normZ), s.T);
-  mmd_norm_kernel<<<norm_blocks, 256, 0, st>>>(prior, N, (int)D, nscale, (float*)(ws + w.normP), s.T);
-  const MmdSmem L = mmd_smem(s.Dp);
-  const int n_items = (s.rb1 - s.rb0) * (s.Q + 1);
-  const int grid = n_items < sm_count() ? n_items : sm_count();
-  auto kern = passes == 3 ? (kernel_type == 0 ? mmd_main_kernel<3, 0> : mmd_main_kernel<3, 1>)
-                          : (kernel_type == 0 ? mmd_main_kernel<1, 0> : mmd_main_kernel<1, 1>);
-  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total) != cudaSuccess)
-    return check_launch("mmd_fwd (shared memory attribute)");
-  kern<<<grid, kMmdThreads, L.total, st>>>(z, prior, ws + w.imgZb, ws + w.imgPb, (const float*)(ws + w.normZ),
-                                           (const float*)(ws + w.normP), s, n_items, (float*)(ws + w.Opart),
-                                           (float*)(ws + w.rspart), (double*)(ws + w.cta_sums));
-  rc = check_launch("mmd_main");
+  mmd_norm_kernel<<<norm_blocks, 256, 0, st>>>(z, stats, N, (int)D, nscale, (float*)(ws + w.normZ), s.T);
+  mmd_norm_kernel<<<norm_blocks, 256, 0, st>>>(prior, stats, N, (int)D, nscale, (float*)(ws + w.normP), s.T);
+  int rc = check_launch("mmd_pack");
   if (rc != VK_OK) return rc;
-  mmd_finalize_kernel<<<148 * 4, 256, 0, st>>>(z, s, (const float*)(ws + w.Opart), (const float*)(ws + w.rspart),
-                                               (const double*)(ws + w.cta_sums), grid, grad_unscaled, sums_out);
-  return check_launch("mmd_finalize");
+  // ---- precision policy ----
+  int g1p = 3, g2p = 3;
+  bool verify = false;
+  if (passes == 1) { g1p = 1; g2p = 1; }
+  else if (passes == 2) { g1p = 3; g2p = 1; }
+  else if (passes == 0 && N >= kAutoMinN && kernel_type == 0) {
+    // RBF at large N: |dk/dd^2| = k / (2 D^2 z_var) makes k insensitive to the bf16 rounding of x.y and the centred
+    // coefficients are tiny, so one pass per GEMM is enough -- when the data agree (checked below, not assumed)
+    g1p = 1; g2p = 1; verify = true;
+  }
+  rc = dispatch_sweep(g1p, g2p, z, prior, s, w, ws, sums_out, grad_unscaled, -1, st);
+  if (rc != VK_OK) return rc;
+  if (verify) {
+    const int64_t nloc = (row_end - row_begin);
+    const int n_rows = (int)(nloc < kSampleRows ? nloc : kSampleRows);
+    const int64_t row_step = nloc / n_rows;
+    const size_t shb = ((size_t)8 * D + 8) * sizeof(double);
+    auto kern = kernel_type == 0 ? mmd_simt_rows_kernel<0> : mmd_simt_rows_kernel<1>;
+    const dim3 grid((unsigned)n_rows, kSampleSplits);
+    kern<<<grid, 256, shb, st>>>(z, z, N, (int)D, row_begin, row_step, n_rows, s.a_exp, s.Ceps, s.C, 1.0, stats->gref, true, nullptr);
+    kern<<<grid, 256, shb, st>>>(z, prior, N, (int)D, row_begin, row_step, n_rows, s.a_exp, s.Ceps, s.C, -1.0, stats->gref, true, nullptr);
+    mmd_verify_kernel<<<1, 256, 0, st>>>(grad_unscaled, (int)D, row_step, n_rows, s.dk_scale, kVerifyBudget, stats);
+    rc = check_launch("mmd_verify");
+    if (rc != VK_OK) return rc;
+    rc = dispatch_sweep(3, 3, z, prior, s, w, ws, sums_out, grad_unscaled, 1, st);      // runs only if the check failed
+    if (rc != VK_OK) return rc;
+  }
+  if (diag) {
+    mmd_diag_kernel<<<1, 1, 0, st>>>(stats, diag);
+    return check_launch("mmd_diag");
+  }
+  return VK_OK;
 }
 
 extern "C" int vk_mmd_combine(const double* sums, int64_t N, int kernel_type, float reg_weight, float* out, void* stream) {
@@ -861,7 +1079,8 @@ extern "C" int vk_mmd_combine(const double* sums, int64_t N, int kernel_type, fl
 extern "C" int vk_scale_by_scalar(const float* in, const float* g, float factor, int64_t n, float* out, void* stream) {
   VK_REQUIRE(in && out && n >= 0, VK_ERR_BAD_ARG, "scale_by_scalar: bad argument");
   if (n == 0) return VK_OK;
-  const int blocks = (int)((n + 1023) / 1024 < 148 * 8 ? (n + 1023) / 1024 : 148 * 8);
+  const int64_t cap = (int64_t)sm_count() * 8;
+  const int blocks = (int)((n + 1023) / 1024 < cap ? (n + 1023) / 1024 : cap);
   scale_by_scalar_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(in, g, factor, n, out);
   return check_launch("scale_by_scalar");
 }

@@ -34,7 +34,7 @@ _SIGNATURES = {
     "vk_vq_fwd": ([_p, _p, _i64, _i64, _i64, _i64, _f, _p, _p, _p, _p, _i64, _p], _i),
     "vk_vq_bwd": ([_p, _p, _p, _p, _p, _i64, _i64, _i64, _i64, _f, _p, _p, _p], _i),
     "vk_mmd_workspace_bytes": ([_i64, _i64], _i64),
-    "vk_mmd_fwd": ([_p, _p, _i64, _i64, _i, _f, _i, _i64, _i64, _p, _p, _p, _i64, _p], _i),
+    "vk_mmd_fwd": ([_p, _p, _i64, _i64, _i, _f, _i, _i64, _i64, _p, _p, _p, _p, _i64, _p], _i),
     "vk_mmd_combine": ([_p, _i64, _i, _f, _p, _p], _i),
     "vk_scale_by_scalar": ([_p, _p, _f, _i64, _p, _p], _i),
     "vk_pair_kernel_fwd": ([_p, _p, _p, _p, _i64, _i64, _i64, _i, _f, _f, _p, _p, _p, _i64, _p], _i),

@@ -161,7 +161,7 @@ class _ShardedMmd(torch.autograd.Function):
         return F.scale_by_scalar(ctx.saved_tensors[0], g.contiguous(), ctx.factor), None, None, None, None, None
 
 
-def sharded_mmd(z_local, reg_weight, kernel_type, z_var, passes=3, group=None):
+def sharded_mmd(z_local, reg_weight, kernel_type, z_var, passes=0, group=None):
     """MMD of the GLOBAL batch (all ranks' z rows) against a shared prior sample; returns (mmd, terms[3]) identical
     on every rank; backward gives d mmd / d z_local."""
     from . import functional as F

@@ -377,9 +377,13 @@ def vector_quantize(latents, codebook, beta):
 KERNEL_TYPES = {'rbf': 0, 'imq': 1}
 
 
-def mmd_sweep(z_all, prior_all, kernel_type, z_var, row_begin, row_end, passes=3):
+MMD_DIAG = None      # set to a list to collect the [4] diagnostics tensor of every vk_mmd_fwd call (tests, bench)
+
+
+def mmd_sweep(z_all, prior_all, kernel_type, z_var, row_begin, row_end, passes=0):
     """One Gram sweep (vk_mmd_fwd) over rows [row_begin,row_end) of the N x N kernel matrices.
-    Returns (sums[3] float64 device tensor {zz, pz, pp}, grad_unscaled [rows, D])."""
+    passes: 0 auto (reduced-precision sweeps are sample-checked on the device and redone when they fail), 3 parity,
+    2 / 1 reduced.  Returns (sums[3] float64 device tensor {zz, pz, pp}, grad_unscaled [rows, D])."""
     L.require(z_all, "z", dims=(2,)); L.require(prior_all, "prior_z", dims=(2,))
     if z_all.shape != prior_all.shape:
         raise RuntimeError("vaekit: z %s and prior_z %s differ in shape" % (tuple(z_all.shape), tuple(prior_all.shape)))
@@ -388,13 +392,16 @@ def mmd_sweep(z_all, prior_all, kernel_type, z_var, row_begin, row_end, passes=3
     dev = z.device
     need = L.ws_bytes("mmd", N, D)
     if need < 0:
-        raise RuntimeError("vaekit: MMD shape N=%d D=%d is not supported (latent dim must be <= 128)" % (N, D))
+        raise RuntimeError("vaekit: MMD shape N=%d D=%d is not supported" % (N, D))
     ws = L.workspace(dev, need)
     sums = torch.empty(3, dtype=torch.float64, device=dev)
     grad = torch.empty((row_end - row_begin, D), dtype=torch.float32, device=dev)
+    diag = torch.empty(4, dtype=torch.float32, device=dev) if MMD_DIAG is not None else None
     with L.on(dev):
         L.call("mmd_fwd", L.ptr(z), L.ptr(p), N, D, kernel_type, z_var, passes, row_begin, row_end, L.ptr(sums),
-               L.ptr(grad), L.ptr(ws), ws.numel(), L.stream_ptr())
+               L.ptr(grad), L.ptr(diag), L.ptr(ws), ws.numel(), L.stream_ptr())
+    if diag is not None:
+        MMD_DIAG.append(diag)
     return sums, grad
 
 
@@ -433,7 +440,7 @@ class _Mmd(torch.autograd.Function):
         return scale_by_scalar(grad, g_mmd.contiguous(), ctx.factor), None, None, None, None, None
 
 
-def mmd(z, prior_z, reg_weight, kernel_type, z_var, passes=3):
+def mmd(z, prior_z, reg_weight, kernel_type, z_var, passes=0):
     """wae_mmd.py:193-204 with the prior sample given: returns (mmd, terms[3] = {pp, zz, pz} kernel means/sums).
     Value and d mmd/d z come out of one tcgen05 Gram sweep; backward only rescales the saved gradient."""
     if kernel_type not in KERNEL_TYPES:

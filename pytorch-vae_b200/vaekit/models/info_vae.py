@@ -21,7 +21,7 @@ class InfoVAE(KernelMatrixMixin, GaussianConvVAE):
         assert alpha <= 0, 'alpha must be negative or zero.'
         self.alpha = alpha
         self.beta = beta
-        self.mmd_passes = 3
+        self.mmd_passes = 0          # 0: auto (sample-checked reduced passes where safe), 3: parity sweep, 2 / 1: reduced
 
     def decode(self, z: Tensor) -> Tensor:
         h = self.decoder_input(z).view(-1, 512, 2, 2)          # hard-wired like info_vae.py:106

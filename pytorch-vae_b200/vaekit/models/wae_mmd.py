@@ -37,7 +37,7 @@ class WAE_MMD(KernelMatrixMixin, DeterministicConvAE):
         self.reg_weight = reg_weight
         self.kernel_type = kernel_type
         self.z_var = latent_var
-        self.mmd_passes = 3          # 3: bf16 hi/lo split (fp32-grade, parity mode); 1: plain bf16 tensor-core pass
+        self.mmd_passes = 0          # 0: auto (sample-checked reduced passes where safe), 3: parity sweep, 2 / 1: reduced
 
     def loss_function(self, *args, **kwargs) -> dict:
         """wae_mmd.py:107-123 (does not read M_N; raises ZeroDivisionError at batch size 1 like the reference)."""

@@ -112,7 +112,7 @@ def test_sharded_ops_match_single_gpu_and_oracle(tmp_path):
             assert abs(a - b) <= 1e-5 * abs(b), (kt, a, b)
         scale = 3.0 * max(abs(t.item()) for t in ref_terms)       # the statistic is a difference of these sums
         assert abs(one.item() - ref.item()) <= 1e-5 * scale, kt
-        assert ((g.double() - zo.grad).abs().max() / zo.grad.abs().max()).item() < 2e-5, kt
+        assert ((g.double() - zo.grad).abs().max() / zo.grad.abs().max()).item() < 1e-5, kt
 
     # Beta-TC: sharded == single-GPU kernels on the gathered batch (gradients flow into mu / log_var through z too)
     mu = torch.cat([parts[r]["tc"][4] for r in range(world)]).to(dev).requires_grad_(True)

@@ -50,7 +50,7 @@ def test_wae_golden(vk, name, kt):
     assert abs(mmd.item() - g["out_MMD"].item()) <= TOL * scale
     assert_close(recons_loss, g["out_Reconstruction_Loss"], TOL)
     assert_close(r.grad, g["grad_recons"], TOL)
-    assert_close(z.grad, g["grad_z"], 2e-5, "grad z")
+    assert_close(z.grad, g["grad_z"], TOL, "grad z")
 
 
 @pytest.mark.parametrize("kt", ["rbf", "imq"])
@@ -78,7 +78,7 @@ def test_mmd_vs_oracle(vk, kt, n, dim, shift):
     if n > 1:
         e = rel_err(zg.grad / 1.5, zc.grad)
         print("   grad rel err %.2e" % e)
-        assert e <= 2e-5
+        assert e <= TOL
 
 
 @pytest.mark.parametrize("kt", ["rbf", "imq"])
@@ -112,7 +112,7 @@ def test_mmd_large_vs_chunked_oracle(vk, kt):
     ref.backward()
     e = rel_err(zg.grad, zd.grad)
     print("%s N=4096 grad rel err vs fp64 %.2e; mmd %.6e vs fp64 %.6e" % (kt, e, mmd.item(), ref.item()))
-    assert e <= 2e-5
+    assert e <= TOL
 
 
 def test_mmd_row_sharded_sweeps_add_up(vk):
@@ -187,8 +187,8 @@ def test_infovae_golden(vk, name, kt, monkeypatch):
     assert_close(d["Reconstruction_Loss"], g["out_Reconstruction_Loss"], TOL)
     assert_close(d["KLD"], g["out_KLD"], TOL)
     assert_close(r.grad, g["grad_recons"], TOL)
-    assert_close(mu.grad, g["grad_mu"], 2e-5, "grad mu")
-    assert_close(lv.grad, g["grad_log_var"], 2e-5, "grad log_var")
+    assert_close(mu.grad, g["grad_mu"], TOL, "grad mu")
+    assert_close(lv.grad, g["grad_log_var"], TOL, "grad log_var")
 
 
 def test_infovae_model_contract(vk):
@@ -218,21 +218,10 @@ def test_infovae_model_contract(vk):
     assert m.sample(3, DEV).shape == (3, 3, 64, 64) and m.generate(x).shape == x.shape
 
 
-@pytest.mark.parametrize("kt", ["rbf", "imq"])
-def test_mmd_full_size_vs_fp64_blocks(vk, kt):
-    """BASELINE configs[2] at its full size (N = 65 536, D = 128; the reference cannot materialise it, SURVEY 0.6): the
-    three kernel terms and the whole gradient against a float64 row-blocked Gram-form restatement evaluated
-    with torch autograd on the GPU, block by block.  Same tolerances as at N = 4096."""
-    F, _ = vk
-    n, dim, z_var, blk = 65536, 128, 2.0, 4096
-    gen = torch.Generator(device=DEV).manual_seed(11)
-    z = torch.randn(n, dim, device=DEV, generator=gen) + 0.25
-    p = torch.randn(n, dim, device=DEV, generator=gen)
-    reg = (5000.0 if kt == "rbf" else 100.0) / (n * (n - 1))          # configs/vae/wae_mmd_{rbf,imq}.yaml
-    zg = leaf(z)
-    mmd, terms = F.mmd(zg, p, reg, kt, z_var)
-    mmd.backward()
-
+def fp64_blocks(z, p, kt, z_var, reg, blk=4096):
+    """wae_mmd.py:193-204 as a float64 row-blocked Gram-form restatement evaluated with torch autograd on
+    the GPU, block by block (torch is only the checker).  Returns (d mmd / dz float64, [pp, zz, pz] terms, mmd)."""
+    n, dim = z.shape
     zd, pd = z.double().requires_grad_(True), p.double()
     scale = 1.0 / (float(n) * n) if kt == "rbf" else 1.0               # .mean() of [N, N] vs of the imq scalar
 
@@ -241,7 +230,7 @@ def test_mmd_full_size_vs_fp64_blocks(vk, kt):
         if kt == "rbf":
             return torch.exp(-d2 / (2.0 * dim * dim * z_var)).sum()
         k = (2 * dim * z_var) / (1e-7 + 2 * dim * z_var + d2)
-        rows = torch.arange(a.shape[0], device=DEV)
+        rows = torch.arange(a.shape[0], device=a.device)
         return k.sum() - k[rows, rows + r0].sum()                      # wae_mmd.py:188-190: minus the diagonal
 
     tot = [0.0, 0.0, 0.0]
@@ -253,12 +242,103 @@ def test_mmd_full_size_vs_fp64_blocks(vk, kt):
         (reg * scale * zz - 2 * reg * scale * pz).backward()
         for i, t in enumerate((pp, zz, pz)):
             tot[i] += t.item() * scale
+    return zd.grad, tot, reg * tot[0] + reg * tot[1] - 2 * reg * tot[2]
+
+
+def run_mode(F, z, p, reg, kt, z_var, passes):
+    """One F.mmd call with the diagnostics of its vk_mmd_fwd: (mmd, terms, grad, diag[4] list)."""
+    F.MMD_DIAG = []
+    try:
+        zg = leaf(z)
+        mmd, terms = F.mmd(zg, p, reg, kt, z_var, passes=passes)
+        mmd.backward()
+        diag = F.MMD_DIAG[0].cpu().tolist()
+    finally:
+        F.MMD_DIAG = None
+    return mmd, terms, zg.grad, diag
+
+
+@pytest.mark.parametrize("kt", ["rbf", "imq"])
+def test_mmd_full_size_vs_fp64_blocks(vk, kt):
+    """BASELINE configs[2] at its full size (N = 65 536, D = 128; the reference cannot materialise it, SURVEY 0.6): the
+    three kernel terms and the whole gradient against the float64 restatement, 1e-5 -- in the DEFAULT (auto) mode, the
+    one bench.py times, and in every explicit precision mode (the per-mode error table of DESIGN.md)."""
+    F, _ = vk
+    n, dim, z_var = 65536, 128, 2.0
+    gen = torch.Generator(device=DEV).manual_seed(11)
+    z = torch.randn(n, dim, device=DEV, generator=gen) + 0.25
+    p = torch.randn(n, dim, device=DEV, generator=gen)
+    reg = (5000.0 if kt == "rbf" else 100.0) / (n * (n - 1))          # configs/vae/wae_mmd_{rbf,imq}.yaml
+    g64, tot, ref_mmd = fp64_blocks(z, p, kt, z_var, reg)
     ref_terms = [torch.tensor(t, dtype=torch.float64) for t in tot]
-    ref_mmd = reg * tot[0] + reg * tot[1] - 2 * reg * tot[2]
-    den = zd.grad.abs().max()
-    e = ((zg.grad.double() - zd.grad).abs().max() / den).item()
-    print("%s N=65536: grad rel err vs fp64 %.2e; terms %s vs %s; mmd %.6e vs %.6e"
-          % (kt, e, terms.cpu().tolist(), tot, mmd.item(), ref_mmd))
-    check_terms(terms, ref_terms, kt + " full size")
+    den = g64.abs().max()
+    for passes in (0, 3, 2, 1):
+        mmd, terms, grad, diag = run_mode(F, z, p, reg, kt, z_var, passes)
+        e = ((grad.double() - g64).abs().max() / den).item()
+        et = max(abs(a - b) / abs(b) for a, b in zip(terms.cpu().tolist(), tot))
+        print("%s N=65536 passes=%d: grad rel err vs fp64 %.2e; worst term rel err %.1e; mmd %.6e vs %.6e; sweep that stands "
+              "%d, sample check %.2e, fallback %d" % (kt, passes, e, et, mmd.item(), ref_mmd, diag[0], diag[1], diag[2]))
+        if passes in (0, 3) or kt == "rbf":
+            check_terms(terms, ref_terms, kt + " full size")
+            assert abs(mmd.item() - ref_mmd) <= TOL * reg * max(abs(t) for t in tot)
+            assert e <= TOL, (kt, passes, e)
+
+
+@pytest.mark.parametrize("kt", ["rbf", "imq"])
+@pytest.mark.parametrize("n,dim,shift,sig", [(8192, 128, 0.25, 1.0), (16384, 128, 0.0, 1.0), (8192, 16, 0.5, 1.0),
+                                             (12000, 64, 0.0, 1.0), (8200, 128, 0.25, 3.0), (9000, 2, 0.5, 1.0)])
+def test_mmd_auto_mode_is_checked_not_assumed(vk, kt, n, dim, shift, sig):
+    """The auto mode at sizes where it tries a reduced-precision sweep: whatever the data (narrow latent dims and wide
+    batches make the kernel values spread and one bf16 pass too coarse), the result meets 1e-5 because the sweep is
+    verified against float64 SIMT rows on the device and redone in parity mode when it fails.  Prints which way it went."""
+    F, _ = vk
+    gen = torch.Generator(device=DEV).manual_seed(n + dim)
+    z = sig * torch.randn(n, dim, device=DEV, generator=gen) + shift
+    p = torch.randn(n, dim, device=DEV, generator=gen)
+    reg = 100.0 / (n * (n - 1))
+    g64, tot, ref_mmd = fp64_blocks(z, p, kt, 2.0, reg, blk=2048)
+    mmd, terms, grad, diag = run_mode(F, z, p, reg, kt, 2.0, 0)
+    e = ((grad.double() - g64).abs().max() / g64.abs().max()).item()
+    print("%s N=%d D=%d shift=%.2f sigma=%.1f auto: grad rel err %.2e; sweep that stands %d, sample check %.2e, fallback %d"
+          % (kt, n, dim, shift, sig, e, diag[0], diag[1], diag[2]))
+    check_terms(terms, [torch.tensor(t, dtype=torch.float64) for t in tot], "%s auto n=%d d=%d" % (kt, n, dim))
     assert abs(mmd.item() - ref_mmd) <= TOL * reg * max(abs(t) for t in tot)
-    assert e <= 2e-5
+    assert e <= TOL
+    if diag[2] == 1:
+        assert diag[0] == 33                               # the parity sweep's result stands
+    # the explicit one-pass sweep on the same data, unchecked: reported, not asserted
+    _, _, g1, _ = run_mode(F, z, p, reg, kt, 2.0, 1)
+    print("   passes=1 unchecked: grad rel err %.2e" % ((g1.double() - g64).abs().max() / g64.abs().max()).item())
+
+
+@pytest.mark.parametrize("kt", ["rbf", "imq"])
+@pytest.mark.parametrize("n,dim", [(300, 160), (129, 256), (64, 1000)])
+def test_mmd_latent_dims_beyond_128(vk, kt, n, dim):
+    """wae_mmd.py:125-150 takes any latent dim; dims > 128 do not fit the tile kernel's tensor-memory map and run the SIMT
+    kernel (the reference's (x - y)^2 form) instead of raising."""
+    F, models = vk
+    gen = torch.Generator().manual_seed(dim)
+    z = torch.randn(n, dim, generator=gen) + 0.25
+    p = torch.randn(n, dim, generator=gen)
+    reg = 100.0 / (n * (n - 1))
+    zc = leaf(z.double())
+    ref = O.mmd(zc, p.double(), reg, kt, 2.0)
+    ref.backward()
+    ref_terms = O.mmd_terms(z.double(), p.double(), kt, 2.0)
+    zg = leaf(z.to(DEV))
+    mmd, terms = F.mmd(zg, p.to(DEV), reg, kt, 2.0)
+    mmd.backward()
+    check_terms(terms, ref_terms, "%s d=%d" % (kt, dim))
+    assert abs(mmd.item() - ref.item()) <= TOL * reg * max(abs(t.item()) for t in ref_terms)
+    assert_close(zg.grad, zc.grad, TOL, "grad d=%d" % dim)
+    # row shards add up (the multi-GPU decomposition of the same kernel)
+    ktn = F.KERNEL_TYPES[kt]
+    full_s, full_g = F.mmd_sweep(z.to(DEV), p.to(DEV), ktn, 2.0, 0, n)
+    if n > 128:
+        s1, g1 = F.mmd_sweep(z.to(DEV), p.to(DEV), ktn, 2.0, 0, 128)
+        s2, g2 = F.mmd_sweep(z.to(DEV), p.to(DEV), ktn, 2.0, 128, n)
+        assert_close(s1 + s2, full_s, 1e-12); assert torch.equal(torch.cat([g1, g2]), full_g)
+    if dim == 256 and kt == "imq":                          # through the drop-in model
+        m = models["WAE_MMD"](3, dim, reg_weight=100, kernel_type=kt)
+        out = m.compute_mmd(z.to(DEV), reg)
+        assert torch.isfinite(out)
