@@ -356,7 +356,9 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
 // G1P / G2P: tensor passes of the distance / gradient GEMM.  run_if >= 0: the kernel only runs when st->flag == run_if
 // (the parity sweep behind a failed sample check).
 template <int G1P, int G2P, int KT>
-__global__ void __maxnreg__(112)     // 18 warps x 112 registers = 64 512 of the 65 536: 96 (what __launch_bounds__ picks) spills 180 B in the epilogue
+// (18 warps = 5 on two of the four SM sub-partitions: 16 384 / 5 / 32 = 102 -> 96 registers per thread is the most a
+// 576-thread CTA can have; __maxnreg__(112) compiles with fewer spills but cannot launch)
+__global__ void __launch_bounds__(kMmdThreads, 1)
 mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, const uint8_t* __restrict__ imgZb,
                 const uint8_t* __restrict__ imgPb, const float* __restrict__ normZ,
                 const float* __restrict__ normP, MmdShape s, int n_items, float* __restrict__ Opart,

@@ -583,10 +583,140 @@ __global__ void zero_kernel(float* p, int64_t n) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = 0.f;
 }
 
+
+// ---- general shapes: SIMT kernels (any D, any K) -------------------------------------------------------------------
+// The tensor-core forward keeps the whole bf16 hi/lo image of the codebook resident in shared memory and the backward a
+// [K][D] fp32 accumulator tile; codebooks that do not fit (e.g. K = 1024, D = 128: 512 KB) take these kernels instead:
+// same results (fp32 dot products in the reference's association (|x|^2 + |e|^2) - 2 x.e, vq_vae.py:35-37; first index
+// wins ties), several times slower, no exception.
+constexpr int kSimtRows = 128, kSimtCodes = 32, kSimtDims = 128;   // thread = row; 32 codes x <= 128 dims staged per step
+
+__global__ void vq_code_norms_kernel(const float* __restrict__ E, int64_t K, int64_t D, float* __restrict__ ee) {
+  const int64_t k = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (k >= K) return;
+  float s = 0.f;
+  for (int64_t d = lane; d < D; d += 32) { const float v = E[k * D + d]; s = fmaf(v, v, s); }
+  s = warp_sum(s);
+  if (lane == 0) ee[k] = s;
+}
+
+__global__ void __launch_bounds__(kSimtRows)
+vq_fwd_simt_kernel(const float* __restrict__ X, const float* __restrict__ E, const float* __restrict__ ee, VqShape s,
+                   float beta, float* __restrict__ q_out, int32_t* __restrict__ idx_out, float* __restrict__ out,
+                   unsigned int* ticket, double* partials) {
+  __shared__ __align__(16) float es[kSimtCodes][kSimtDims];
+  __shared__ double red[kSimtRows / 32];
+  const int t = threadIdx.x;
+  const uint32_t hw32 = (uint32_t)s.HW;
+  const int D = (int)s.D;
+  double sq = 0.0;
+  for (int64_t tile = blockIdx.x; tile < s.tiles; tile += gridDim.x) {
+    const uint32_t r = (uint32_t)tile * kSimtRows + t;
+    const bool live = r < (uint32_t)s.R;
+    const uint32_t b = live ? r / hw32 : 0u, hw = live ? r - b * hw32 : 0u;
+    const float* xp = X + (size_t)b * D * hw32 + hw;
+    float xx = 0.f;
+    if (live) for (int d = 0; d < D; ++d) { const float v = __ldg(xp + (size_t)d * hw32); xx = fmaf(v, v, xx); }
+    float best = INFINITY;
+    int bi = 0;
+    for (int64_t k0 = 0; k0 < s.K; k0 += kSimtCodes) {
+      float dot[kSimtCodes];
+#pragma unroll
+      for (int c = 0; c < kSimtCodes; ++c) dot[c] = 0.f;
+      for (int d0 = 0; d0 < D; d0 += kSimtDims) {
+        const int dn = D - d0 < kSimtDims ? D - d0 : kSimtDims;
+        __syncthreads();
+        for (int i = t; i < kSimtCodes * kSimtDims; i += kSimtRows) {
+          const int c = i / kSimtDims, d = i % kSimtDims;
+          es[c][d] = (k0 + c < s.K && d < dn) ? __ldg(E + (size_t)(k0 + c) * D + d0 + d) : 0.f;
+        }
+        __syncthreads();
+        for (int dd = 0; dd < dn; dd += 4) {
+          float xv[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) xv[j] = (live && dd + j < dn) ? __ldg(xp + (size_t)(d0 + dd + j) * hw32) : 0.f;
+#pragma unroll
+          for (int c = 0; c < kSimtCodes; ++c) {
+            const float4 e4 = *reinterpret_cast<const float4*>(&es[c][dd]);
+            dot[c] = fmaf(xv[0], e4.x, dot[c]); dot[c] = fmaf(xv[1], e4.y, dot[c]);
+            dot[c] = fmaf(xv[2], e4.z, dot[c]); dot[c] = fmaf(xv[3], e4.w, dot[c]);
+          }
+        }
+      }
+#pragma unroll
+      for (int c = 0; c < kSimtCodes; ++c) {
+        if (k0 + c < s.K) {
+          const float dist = (xx + __ldg(ee + k0 + c)) - 2.f * dot[c];      // vq_vae.py:35-37
+          if (dist < best) { best = dist; bi = (int)(k0 + c); }             // strict: the first minimum wins
+        }
+      }
+    }
+    if (live) {
+      idx_out[r] = bi;
+      float* qp = q_out + (size_t)b * D * hw32 + hw;
+      const float* ep = E + (size_t)bi * D;
+      float acc = 0.f;
+      for (int d = 0; d < D; ++d) {
+        const float x = __ldg(xp + (size_t)d * hw32);
+        const float df = __ldg(ep + d) - x;
+        qp[(size_t)d * hw32] = x + df;                       // latents + (quantized - latents).detach()
+        acc = fmaf(df, df, acc);
+      }
+      sq += (double)acc;
+    }
+  }
+  sq = warp_sum(sq);
+  if ((t & 31) == 0) red[t >> 5] = sq;
+  __syncthreads();
+  if (t == 0) {
+    double tot = 0;
+    for (int i = 0; i < kSimtRows / 32; ++i) tot += red[i];
+    partials[blockIdx.x] = tot;
+    __threadfence();
+    const unsigned int tk = atomicAdd(ticket, 1u);
+    if (tk == gridDim.x - 1) {
+      __threadfence();
+      double all = 0;
+      for (unsigned int i = 0; i < gridDim.x; ++i) all += ((volatile double*)partials)[i];
+      const float m = (float)(all / ((double)s.R * (double)s.D));
+      out[0] = m * beta + m;
+      out[1] = m;
+      *ticket = 0u;
+    }
+  }
+}
+
+// g_x = g_q - cx (q - x);  g_E[idx] += ce (q - x) with global atomics (summation order varies run to run at rounding level)
+__global__ void __launch_bounds__(kSimtRows)
+vq_bwd_simt_kernel(const float* __restrict__ g_q, const float* __restrict__ g_loss, const float* __restrict__ X,
+                   const float* __restrict__ E, const int32_t* __restrict__ idx, VqShape s, float beta,
+                   float* __restrict__ g_x, float* __restrict__ g_E) {
+  const float gl = g_loss ? *g_loss : 0.f;
+  const float cx = gl * 2.f * beta / (float)((double)s.R * (double)s.D);
+  const float ce = gl * 2.f / (float)((double)s.R * (double)s.D);
+  const uint32_t hw32 = (uint32_t)s.HW;
+  const int D = (int)s.D;
+  for (int64_t tile = blockIdx.x; tile < s.tiles; tile += gridDim.x) {
+    const uint32_t r = (uint32_t)tile * kSimtRows + threadIdx.x;
+    if (r >= (uint32_t)s.R) continue;
+    const uint32_t b = r / hw32, hw = r - b * hw32;
+    const size_t base = (size_t)b * D * hw32 + hw;
+    const int k = __ldg(idx + r);
+    const float* ep = E + (size_t)k * D;
+    for (int d = 0; d < D; ++d) {
+      const size_t o = base + (size_t)d * hw32;
+      const float df = __ldg(ep + d) - __ldg(X + o);
+      if (g_x) g_x[o] = (g_q ? __ldg(g_q + o) : 0.f) - cx * df;
+      if (g_E && gl != 0.f) atomicAdd(g_E + (size_t)k * D + d, ce * df);
+    }
+  }
+}
+
 int make_shape(int64_t B, int64_t D, int64_t HW, int64_t K, VqShape& s) {
   VK_REQUIRE(B > 0 && D > 0 && HW > 0 && K > 0, VK_ERR_BAD_ARG, "vq: empty shape B=%lld D=%lld HW=%lld K=%lld",
              (long long)B, (long long)D, (long long)HW, (long long)K);
-  VK_REQUIRE(D <= 256 && K <= 4096, VK_ERR_UNSUPPORTED, "vq: D=%lld (max 256) or K=%lld (max 4096) too large",
+  VK_REQUIRE(D <= (1 << 20) && K <= (1 << 24), VK_ERR_UNSUPPORTED, "vq: D=%lld or K=%lld beyond the index math of the kernels",
              (long long)D, (long long)K);
   VK_REQUIRE(B * HW < (1ll << 31) - 128 && HW * D < (1ll << 31), VK_ERR_UNSUPPORTED,
              "vq: B*HW=%lld rows or D*HW=%lld beyond the 32-bit index math of the kernels", (long long)(B * HW),
@@ -605,6 +735,11 @@ int make_shape(int64_t B, int64_t D, int64_t HW, int64_t K, VqShape& s) {
 
 using namespace vk;
 
+// the tensor-core forward fits: codebook image + two x stages in shared memory, MMA N <= 256 per chunk
+static bool vq_tile_fwd_fits(const VqShape& s) {
+  return s.D <= 256 && s.K <= 4096 && vq_smem(s.Dp, s.Kp).total + 256 <= 227 * 1024;
+}
+
 extern "C" int64_t vk_vq_workspace_bytes(int64_t D, int64_t K) {
   VqShape s;
   if (make_shape(1, D, 1, K, s) != VK_OK) return -1;
@@ -621,11 +756,19 @@ extern "C" int vk_vq_fwd(const float* latents, const float* codebook, int64_t B,
   const VqWs w = vq_ws(s);
   VK_REQUIRE(workspace_bytes >= (int64_t)w.total, VK_ERR_WORKSPACE, "vq_fwd: workspace %lld < %lld",
              (long long)workspace_bytes, (long long)w.total);
-  const VqSmem L = vq_smem(s.Dp, s.Kp);
-  VK_REQUIRE(L.total + 256 <= 227 * 1024, VK_ERR_UNSUPPORTED,
-             "vq_fwd: codebook %lldx%lld needs %u bytes of shared memory (max 232192)", (long long)K, (long long)D, L.total);
   cudaStream_t st = (cudaStream_t)stream;
   uint8_t* ws = (uint8_t*)workspace;
+  if (!vq_tile_fwd_fits(s)) {
+    // codebook image beyond shared memory (or D / K beyond the tile kernel's map): SIMT kernel, same results
+    float* ee = (float*)(ws + w.ee);
+    vq_code_norms_kernel<<<(unsigned)((K * 32 + 255) / 256), 256, 0, st>>>(codebook, K, D, ee);
+    const int64_t cap = (int64_t)sm_count() * 8;
+    const int grid = (int)(s.tiles < cap ? s.tiles : cap);
+    vq_fwd_simt_kernel<<<grid, kSimtRows, 0, st>>>(latents, codebook, ee, s, beta, q_out, idx_out, out, (unsigned int*)ws,
+                                                    (double*)(ws + w.partials));
+    return check_launch("vq_fwd (SIMT)");
+  }
+  const VqSmem L = vq_smem(s.Dp, s.Kp);
   vq_pack_codebook_kernel<<<(s.Kp + 127) / 128, 128, 0, st>>>(codebook, (int)K, (int)D, s.Kp, s.Dp,
                                                               (__nv_bfloat16*)(ws + w.image), (float*)(ws + w.ee));
   if (cudaFuncSetAttribute(vq_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total) != cudaSuccess)
@@ -646,8 +789,14 @@ extern "C" int vk_vq_bwd(const float* g_q, const float* g_loss, const float* lat
   if (rc != VK_OK) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   const VqBwdSmem L = vq_bwd_smem(D, K, g_codebook != nullptr);
-  VK_REQUIRE(L.total <= 226 * 1024, VK_ERR_UNSUPPORTED, "vq_bwd: codebook gradient tile needs %u bytes of shared memory",
-             L.total);
+  if ((uint64_t)K * (uint64_t)D * 4 + (uint64_t)kTileRows * ((uint64_t)D + 1) * 4 + (uint64_t)K * 16 + 1024 > 226 * 1024) {
+    // the [K][D] accumulator tile does not fit shared memory: SIMT kernel with global atomics
+    if (g_codebook) zero_kernel<<<64, 256, 0, st>>>(g_codebook, K * D);
+    const int64_t cap = (int64_t)sm_count() * 8;
+    const int64_t blocks = s.tiles < cap ? s.tiles : cap;
+    vq_bwd_simt_kernel<<<(int)blocks, kSimtRows, 0, st>>>(g_q, g_loss, latents, codebook, idx, s, beta, g_latents, g_codebook);
+    return check_launch("vq_bwd (SIMT)");
+  }
   auto kern = D == 32 ? vq_bwd_kernel<4> : D == 64 ? vq_bwd_kernel<8> : D == 128 ? vq_bwd_kernel<16> : vq_bwd_kernel<0>;
   if (L.total > 48 * 1024 && cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total) != cudaSuccess)
     return check_launch("vq_bwd (shared memory attribute)");
