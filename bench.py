@@ -211,7 +211,7 @@ class StreamWorkload(Workload):
         else:
             d = m.loss_function(recons, t["input"], mu, lv, z, None, M_N=self.M_N)
         torch.autograd.backward([d["loss"], z], [None, t["gz"]])
-        return d
+        return {k: v.detach() for k, v in d.items()}
 
     def work(self, world):
         B, D, GK = self.N, self.D, max(self.G, 1) * self.K
@@ -277,7 +277,7 @@ class VanillaB64(Workload):
         out = m(t["x"])
         d = m.loss_function(*out, M_N=0.005)
         d["loss"].backward()
-        return {"loss": d["loss"]}
+        return {"loss": d["loss"].detach()}
 
     def work(self, world):
         B, D = self.N, self.D
@@ -369,7 +369,7 @@ class WaeMmd(Workload):
         else:
             mmd = m.compute_mmd(z, reg)
         mmd.backward()
-        return {"MMD": mmd}
+        return {"MMD": mmd.detach()}
 
     def work(self, world):
         return {"mmd_fwd": 10.0 * self.N * self.N * self.D / world}, "TFLOP/s"
@@ -417,7 +417,7 @@ class VqWorkload(Workload):
         m.embedding.weight.grad = None
         q, vq_loss = m(x)
         torch.autograd.backward([q, vq_loss], [t["gq"], None])
-        return {"VQ_Loss": vq_loss}
+        return {"VQ_Loss": vq_loss.detach()}
 
     def work(self, world):
         R = self.N * self.H * self.H
@@ -510,7 +510,7 @@ class SwaeWorkload(Workload):
         else:
             swd = m.compute_swd(z, m.p, reg)
         swd.backward()
-        return {"SWD": swd}
+        return {"SWD": swd.detach()}
 
     def work(self, world):
         # radix-sort traffic model of SURVEY 8(d): 27 424 B/sample; sharded runs time the sort + loss stage on its own (120 of
@@ -571,7 +571,7 @@ class BetaTcWorkload(Workload):
         else:
             latent, terms = F.betatc_terms(z, mu, lv, 0.00025, m.alpha, m.beta, m.gamma)
         latent.backward()
-        return {"latent": latent}
+        return {"latent": latent.detach()}
 
     def work(self, world):
         e = float(self.N) * self.N * self.D
@@ -758,9 +758,14 @@ def measure(ctx, wl):
     ms, _, launches, d = timed(ctx, lambda: wl.step(model, t, world), args.steps)
     # the same K steps again with CUDA events around every library call (launching stream): per-call durations for the
     # roofline.  Kept out of the pass that gives the step time: two event records per call cost the host 20-60 us.
-    _, log, _, _ = timed(ctx, lambda: wl.step(model, t, world), args.steps, log_events=True)
+    out2 = timed(ctx, lambda: wl.step(model, t, world), args.steps, log_events=True)
+    log = out2[1]
     loss = {k: float(v.item()) for k, v in d.items()}
-    del d       # frees the eager autograd graph: its AccumulateGrad nodes are bound to this stream and would break a capture
+    # free the eager autograd graphs (every reference to a returned loss): their AccumulateGrad nodes are bound to this
+    # stream and a live one makes the engine synchronise it with the capturing stream, which invalidates the capture
+    del d, out2
+    import gc
+    gc.collect()
     res = {"ms_per_step": round(ms / args.steps, 4), "api": "eager: forward + backward through the drop-in model API"}
     step_ms = ms / args.steps
     gs = None

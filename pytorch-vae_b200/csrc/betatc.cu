@@ -76,8 +76,8 @@ tc_fwd_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const f
   float* Ms = Zs + kW * Dpad;             // running max  [kW][Dpad]
   float* Ss = Ms + kW * Dpad;             // running sum  [kW][Dpad]
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int i = blockIdx.x * kW + w;
-  const bool alive = i < p.B;
+  const int i = p.r0 + blockIdx.x * kW + w;      // anchor rows [r0, r1): a rank's row block, [0, B) on one GPU
+  const bool alive = i < p.r1;
   for (int d = lane; d < Dpad; d += 32) {
     Zs[w * Dpad + d] = (alive && d < p.D) ? Z[(size_t)i * p.D + d] : 0.f;
     Ms[w * Dpad + d] = -INFINITY;
@@ -203,8 +203,8 @@ tc_bwd_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const f
   float* G1 = G0 + kW * Dpad;
   float* Tq = G1 + kW * Dpad;             // COLS: lqz of the partner rows [kPT]
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int a = blockIdx.x * kW + w;      // anchor index (row i or column j)
-  const bool alive = a < p.B;
+  const int a = p.r0 + blockIdx.x * kW + w;      // anchor index (row i or column j) inside [r0, r1)
+  const bool alive = a < p.r1;
   const float g = g_loss ? *g_loss : 1.f;
   const float invB = 1.f / (float)p.B;
   const float cq = (p.beta - p.alpha) * invB * g, cp = (p.gamma_anneal - p.beta) * invB * g;
@@ -338,8 +338,6 @@ static int tc_fwd_impl(const float* z, const float* mu, const float* log_var, in
   if (rc != VK_OK) return rc;
   VK_REQUIRE(0 <= row_begin && row_begin < row_end && row_end <= B, VK_ERR_BAD_ARG, "tc_fwd: bad row range [%lld, %lld) of %lld",
              (long long)row_begin, (long long)row_end, (long long)B);
-  VK_REQUIRE(D <= 128 || (row_begin == 0 && row_end == B), VK_ERR_UNSUPPORTED,
-             "tc_fwd: row ranges need latent dim <= 128 (got %lld)", (long long)D);
   p.r0 = (int)row_begin; p.r1 = (int)row_end;
   VK_REQUIRE(workspace_bytes >= vk_tc_workspace_bytes(B, D), VK_ERR_WORKSPACE, "tc_fwd: workspace too small");
   cudaStream_t st = (cudaStream_t)stream;
@@ -383,7 +381,9 @@ static int tc_fwd_impl(const float* z, const float* mu, const float* log_var, in
   const size_t sm = tc_smem_fwd((int)D);
   if (cudaFuncSetAttribute(tc_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm) != cudaSuccess)
     return check_launch("tc_fwd (shared memory attribute)");
-  tc_fwd_kernel<<<blocks, 32 * kW, sm, st>>>(z, mu, log_var, H, C0, p, lqz_out, lse_out, partials, (unsigned int*)ws, out);
+  // latent dims > 128: first-generation kernels (one anchor per warp, partners over lanes), anchors of the row range only
+  const int rblocks = (int)((p.r1 - p.r0 + kW - 1) / kW);
+  tc_fwd_kernel<<<rblocks, 32 * kW, sm, st>>>(z, mu, log_var, H, C0, p, lqz_out, lse_out, partials, (unsigned int*)ws, out);
   return check_launch("tc_fwd");
 }
 
@@ -411,8 +411,6 @@ static int tc_bwd_impl(const float* z, const float* mu, const float* log_var, co
   if (rc != VK_OK) return rc;
   VK_REQUIRE(0 <= row_begin && row_begin < row_end && row_end <= B, VK_ERR_BAD_ARG, "tc_bwd: bad row range [%lld, %lld) of %lld",
              (long long)row_begin, (long long)row_end, (long long)B);
-  VK_REQUIRE(D <= 128 || (row_begin == 0 && row_end == B), VK_ERR_UNSUPPORTED,
-             "tc_bwd: row ranges need latent dim <= 128 (got %lld)", (long long)D);
   p.r0 = (int)row_begin; p.r1 = (int)row_end;
   VK_REQUIRE(workspace_bytes >= vk_tc_workspace_bytes(B, D), VK_ERR_WORKSPACE, "tc_bwd: workspace too small");
   cudaStream_t st = (cudaStream_t)stream;
@@ -457,8 +455,9 @@ static int tc_bwd_impl(const float* z, const float* mu, const float* log_var, co
   if (cudaFuncSetAttribute(tc_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm) != cudaSuccess ||
       cudaFuncSetAttribute(tc_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm) != cudaSuccess)
     return check_launch("tc_bwd (shared memory attribute)");
-  tc_bwd_kernel<true><<<blocks, 32 * kW, sm, st>>>(z, mu, H, C0, lqz, lse, p, g_loss, g_z, g_mu, g_lv);
-  tc_bwd_kernel<false><<<blocks, 32 * kW, sm, st>>>(z, mu, H, C0, lqz, lse, p, g_loss, g_z, g_mu, g_lv);
+  const int rblocks = (int)((p.r1 - p.r0 + kW - 1) / kW);
+  tc_bwd_kernel<true><<<rblocks, 32 * kW, sm, st>>>(z, mu, H, C0, lqz, lse, p, g_loss, g_z, g_mu, g_lv);
+  tc_bwd_kernel<false><<<rblocks, 32 * kW, sm, st>>>(z, mu, H, C0, lqz, lse, p, g_loss, g_z, g_mu, g_lv);
   return check_launch("tc_bwd");
 }
 

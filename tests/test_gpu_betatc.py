@@ -106,7 +106,8 @@ def test_betatc_model_contract(vk):
     assert_close(ld, O.log_density_gaussian(out[4].cpu(), out[2].cpu(), out[3].cpu()), TOL)
 
 
-@pytest.mark.parametrize("B,D,cuts", [(256, 128, (0, 100, 256)), (130, 10, (0, 1, 64, 129, 130)), (96, 40, (0, 95, 96))])
+@pytest.mark.parametrize("B,D,cuts", [(256, 128, (0, 100, 256)), (130, 10, (0, 1, 64, 129, 130)), (96, 40, (0, 95, 96)),
+                                        (200, 160, (0, 7, 128, 200)), (64, 256, (0, 33, 64))])   # latent dims > 128: first-generation kernels
 def test_betatc_row_shards_add_up(vk, B, D, cuts):
     """Multi-GPU decomposition emulated on one GPU: anchor-row blocks swept separately (vk_tc_fwd_rows /
     vk_tc_bwd_rows) give per-row outputs identical to the full sweep, shares of the batch means that add up, and row
