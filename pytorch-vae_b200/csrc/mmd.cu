@@ -352,6 +352,29 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
   return r;
 }
 
+// packed fp32 pairs (sm_100: FADD2 / FFMA2 process two lanes per issue slot -- the epilogue is issue-bound)
+__device__ __forceinline__ uint64_t pk2(float a, float b) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+  return r;
+}
+__device__ __forceinline__ uint64_t pk2u(uint32_t a, uint32_t b) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(a), "r"(b));
+  return r;
+}
+__device__ __forceinline__ void upk2(uint64_t v, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
+__device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+
 // ---- main kernel ----------------------------------------------------------------------------------------------
 // G1P / G2P: tensor passes of the distance / gradient GEMM.  run_if >= 0: the kernel only runs when st->flag == run_if
 // (the parity sweep behind a failed sample check).
@@ -603,6 +626,9 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
           // interior tiles take the branch-free instance; diagonal / tail tiles the masked one
           auto tile_math = [&](auto masked_c, auto grad_c) {
             constexpr bool MASKED = decltype(masked_c)::value, GRAD = decltype(grad_c)::value;
+            // interior tiles: two elements per instruction (FADD2 / FFMA2), one running sum where one is enough
+            const uint64_t nx2 = pk2(nx, nx), sc2 = pk2(s_coef, s_coef), nc0 = pk2(-c0k, -c0k);
+            uint64_t ksum2 = pk2(0.f, 0.f), csum2 = pk2(0.f, 0.f);
 #pragma unroll
           for (int hf = 0; hf < 2; ++hf) {
             tmem_ld_wait16(rr[hf]);
@@ -616,27 +642,41 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
               float cv[8];
               const float4 n0 = *reinterpret_cast<const float4*>(ny + hf * 16 + c8);
               const float4 n1 = *reinterpret_cast<const float4*>(ny + hf * 16 + c8 + 4);
-              const float nyv[8] = {n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, n1.z, n1.w};
+              if constexpr (!MASKED) {
+                const uint64_t nyp[4] = {pk2(n0.x, n0.y), pk2(n0.z, n0.w), pk2(n1.x, n1.y), pk2(n1.z, n1.w)};
 #pragma unroll
-              for (int e = 0; e < 8; ++e) {
-                const int c = hf * 16 + c8 + e;
-                // no clamp of d^2 at 0: a rounding-level negative distance moves k by < 1e-9 relative
-                const float arg = fmaf(__uint_as_float(rr[hf][c8 + e]), s_coef, nx + nyv[e]);
-                float k;
-                if (KT == 0) {
-                  k = ex2_approx(arg);                        // exp(-d^2 / (2 D^2 z_var))
-                  cv[e] = k - c0k;                            // dk/dd^2 = k * dk_scale: the constant is applied in finalize
-                } else {
-                  k = rcp_approx(arg);                        // k / C = 1 / (C + eps + d^2)
-                  cv[e] = fmaf(k, k, -c0k);                   // dk/dd^2 = -C * (k/C)^2
+                for (int e = 0; e < 8; e += 2) {
+                  // no clamp of d^2 at 0: a rounding-level negative distance moves k by < 1e-9 relative
+                  const uint64_t a2 = fma2(pk2u(rr[hf][c8 + e], rr[hf][c8 + e + 1]), sc2, add2(nx2, nyp[e >> 1]));
+                  float a0, a1, k0, k1;
+                  upk2(a2, a0, a1);
+                  if (KT == 0) { k0 = ex2_approx(a0); k1 = ex2_approx(a1); }      // exp(-d^2 / (2 D^2 z_var))
+                  else { k0 = rcp_approx(a0); k1 = rcp_approx(a1); }              // k / C = 1 / (C + eps + d^2)
+                  const uint64_t k2 = pk2(k0, k1);
+                  if (GRAD) {
+                    // centred coefficient: rbf dk/dd^2 = k * dk_scale, imq -C (k/C)^2 (the constants are applied in finalize)
+                    const uint64_t c2 = KT == 0 ? add2(k2, nc0) : fma2(k2, k2, nc0);
+                    csum2 = add2(csum2, c2);
+                    upk2(c2, cv[e], cv[e + 1]);
+                  }
+                  if (!GRAD || KT == 1) ksum2 = add2(ksum2, k2);                  // rbf gradient tiles: sum k = sum c' + 32 c0
                 }
-                if (MASKED) {                                 // diagonal exclusion, tail rows / columns
+              } else {
+                const float nyv[8] = {n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, n1.z, n1.w};
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                  const int c = hf * 16 + c8 + e;
+                  const float arg = fmaf(__uint_as_float(rr[hf][c8 + e]), s_coef, nx + nyv[e]);
+                  float k;
+                  if (KT == 0) { k = ex2_approx(arg); cv[e] = k - c0k; }
+                  else { k = rcp_approx(arg); cv[e] = fmaf(k, k, -c0k); }
+                  // diagonal exclusion, tail rows / columns
                   const bool ok = rvalid && (gcol0 + c < n32) && !(diag_excl && gcol0 + c == grow);
                   k = ok ? k : 0.f;
                   cv[e] = ok ? cv[e] : 0.f;
+                  ksum += k;
+                  if (GRAD) csum += cv[e];
                 }
-                ksum += k;
-                if (GRAD) csum += cv[e];
               }
               if (GRAD) {
 #pragma unroll
@@ -657,6 +697,12 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
               if (G2P == 3) tmem_st8(tk + 32 + hf * 8, kl);
             }
           }
+            if constexpr (!MASKED) {
+              float a, b;
+              if (GRAD) { upk2(csum2, a, b); csum = a + b; }
+              if (GRAD && KT == 0) ksum = fmaf(32.f, c0k, csum);
+              else { upk2(ksum2, a, b); ksum = a + b; }
+            }
           };
           if (it.grad) {
             if (slow) tile_math(std::true_type{}, std::true_type{}); else tile_math(std::false_type{}, std::true_type{});
@@ -750,29 +796,30 @@ __global__ void mmd_finalize_kernel(const float* __restrict__ Z, const float* __
   const int64_t nloc_pad = (int64_t)(s.rb1 - s.rb0) * kRows;
   int64_t nloc = s.N - row0;
   if (nloc > nloc_pad) nloc = nloc_pad;
-  const int64_t total = nloc * s.D;
   const double c0zz = (double)st->c0[0], c0pz = (double)st->c0[1];
   const double n = (double)s.N;
+  const int lane = threadIdx.x & 31;
   float gmax = 0.f;
-  for (int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t r = g / s.D;
-    const int d = (int)(g % s.D);
-    float rs = 0.f, o = 0.f;
-    for (int q = 0; q < s.Q; ++q) {
-      for (int c = 0; c < kColGroups; ++c) rs += rspart[(size_t)(q * kColGroups + c) * nloc_pad + r];
-      o += Opart[((size_t)q * nloc_pad + r) * s.Dp + d];
+  // one warp per row: the lanes first sum the row's Q x 4 partial row sums (fixed order), then take latent dims
+  for (int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; r < nloc; r += ((int64_t)gridDim.x * blockDim.x) >> 5) {
+    float rs = 0.f;
+    for (int e = lane; e < s.Q * kColGroups; e += 32) rs += rspart[(size_t)e * nloc_pad + r];
+    rs = warp_sum(rs);
+    for (int d = lane; d < s.D; d += 32) {
+      float o = 0.f;
+      for (int q = 0; q < s.Q; ++q) o += Opart[((size_t)q * nloc_pad + r) * s.Dp + d];
+      const float zc = Z[(row0 + r) * s.D + d] - st->m[d];
+      double ana;
+      if (s.kernel_type == 0) {
+        ana = (c0zz - c0pz) * n * (double)zc - c0zz * st->Sz[d] + c0pz * st->Sp[d];
+      } else {
+        const float pc = P[(row0 + r) * s.D + d] - st->m[d];
+        ana = (c0zz - c0pz) * (n - 1.0) * (double)zc - c0zz * (st->Sz[d] - (double)zc) + c0pz * (st->Sp[d] - (double)pc);
+      }
+      const float gv = s.dk_scale * (float)((double)fmaf(zc, rs, -o) + ana);   // dk/dd^2 constant: -1/(2 D^2 z_var) | -C
+      grad[r * s.D + d] = gv;
+      gmax = fmaxf(gmax, fabsf(gv));
     }
-    const float zc = Z[(row0 + r) * s.D + d] - st->m[d];
-    double ana;
-    if (s.kernel_type == 0) {
-      ana = (c0zz - c0pz) * n * (double)zc - c0zz * st->Sz[d] + c0pz * st->Sp[d];
-    } else {
-      const float pc = P[(row0 + r) * s.D + d] - st->m[d];
-      ana = (c0zz - c0pz) * (n - 1.0) * (double)zc - c0zz * (st->Sz[d] - (double)zc) + c0pz * (st->Sp[d] - (double)pc);
-    }
-    const float gv = s.dk_scale * (float)((double)fmaf(zc, rs, -o) + ana);     // dk/dd^2 constant: -1/(2 D^2 z_var) | -C
-    grad[g] = gv;
-    gmax = fmaxf(gmax, fabsf(gv));
   }
   gmax = warp_max(gmax);
   if ((threadIdx.x & 31) == 0 && gmax > 0.f) atomicMax(&st->gmax_bits, __float_as_uint(gmax));
@@ -791,7 +838,7 @@ __global__ void mmd_finalize_kernel(const float* __restrict__ Z, const float* __
 //   X rows, Y columns [N, D]; rows i = row0 + blockIdx.x * row_step; sign +1 / -1 of the gradient contribution;
 //   gacc [rows, D] float64 accumulators (NULL: no gradient), krow [rows]: each row's kernel sum (NULL: none; needs
 //   gridDim.y == 1).
-template <int KT>
+template <int KT, bool REG>
 __global__ void __launch_bounds__(256)
 mmd_simt_rows_kernel(const float* __restrict__ X, const float* __restrict__ Y, int64_t N, int D, int64_t row0,
                      int64_t row_step, int64_t n_rows, float a_exp, float Ceps, float C, double sign,
@@ -802,21 +849,57 @@ mmd_simt_rows_kernel(const float* __restrict__ X, const float* __restrict__ Y, i
   const int64_t i = row0 + (int64_t)blockIdx.x * row_step;
   const float* xi = X + i * D;
   double* acc = sh + (size_t)warp * D;
-  for (int d = lane; d < D; d += 32) acc[d] = 0.0;
   double ks = 0.0;
   const int64_t span = (N + gridDim.y - 1) / gridDim.y;
   const int64_t j0 = (int64_t)blockIdx.y * span, j1 = j0 + span < N ? j0 + span : N;
-  for (int64_t j = j0 + warp; j < j1; j += 8) {
-    const float* yj = Y + j * D;
-    float s2 = 0.f;
-    for (int d = lane; d < D; d += 32) { const float t = xi[d] - yj[d]; s2 = fmaf(t, t, s2); }
-    s2 = warp_sum(s2);
-    float k, coef;
-    if (KT == 0) { k = exp2f(a_exp * s2); coef = k; }
-    else { const float r = 1.0f / (Ceps + s2); k = C * r; coef = r * r; }
-    if (KT == 1 && j == i) continue;                           // imq: the diagonal is removed from every term
-    ks += (double)k;
-    if (gacc) for (int d = lane; d < D; d += 32) acc[d] += (double)(coef * (xi[d] - yj[d]));
+  if (REG) {
+    // D <= 128: the row and four columns at a time live in registers (independent loads and reductions in flight)
+    float xr[4];
+    double ar[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) xr[k] = lane + 32 * k < D ? xi[lane + 32 * k] : 0.f;
+    for (int64_t j = j0 + warp * 4; j < j1; j += 32) {
+      float df[4][4], s2[4];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const bool ok = j + c < j1;
+        s2[c] = 0.f;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int d = lane + 32 * k;
+          df[c][k] = (ok && d < D) ? xr[k] - __ldg(Y + (j + c) * D + d) : 0.f;
+          s2[c] = fmaf(df[c][k], df[c][k], s2[c]);
+        }
+      }
+#pragma unroll
+      for (int c = 0; c < 4; ++c) s2[c] = warp_sum(s2[c]);
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        float k, coef;
+        if (KT == 0) { k = exp2f(a_exp * s2[c]); coef = k; }
+        else { const float r = 1.0f / (Ceps + s2[c]); k = C * r; coef = r * r; }
+        if (j + c >= j1 || (KT == 1 && j + c == i)) { k = 0.f; coef = 0.f; }     // imq: no diagonal in any term
+        ks += (double)k;
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) ar[kk] += (double)(coef * df[c][kk]);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) if (lane + 32 * k < D) acc[lane + 32 * k] = ar[k];
+  } else {
+    for (int d = lane; d < D; d += 32) acc[d] = 0.0;
+    for (int64_t j = j0 + warp; j < j1; j += 8) {
+      const float* yj = Y + j * D;
+      float s2 = 0.f;
+      for (int d = lane; d < D; d += 32) { const float t = xi[d] - yj[d]; s2 = fmaf(t, t, s2); }
+      s2 = warp_sum(s2);
+      float k, coef;
+      if (KT == 0) { k = exp2f(a_exp * s2); coef = k; }
+      else { const float r = 1.0f / (Ceps + s2); k = C * r; coef = r * r; }
+      if (KT == 1 && j == i) continue;                           // imq: the diagonal is removed from every term
+      ks += (double)k;
+      if (gacc) for (int d = lane; d < D; d += 32) acc[d] += (double)(coef * (xi[d] - yj[d]));
+    }
   }
   __syncthreads();
   double* kred = sh + (size_t)8 * D;
@@ -941,7 +1024,7 @@ int launch_sweep(const float* z, const float* prior, const MmdShape& s, const Mm
                                            (float*)(ws + w.rspart), (double*)(ws + w.cta_sums), stats, run_if);
   int rc = check_launch("mmd_main");
   if (rc != VK_OK) return rc;
-  mmd_finalize_kernel<<<sm_count() * 4, 256, 0, st>>>(z, prior, s, (const float*)(ws + w.Opart), (const float*)(ws + w.rspart),
+  mmd_finalize_kernel<<<sm_count() * 8, 256, 0, st>>>(z, prior, s, (const float*)(ws + w.Opart), (const float*)(ws + w.rspart),
                                                        (const double*)(ws + w.cta_sums), grid, grad_unscaled, sums_out, stats,
                                                        run_if);
   return check_launch("mmd_finalize");
@@ -1006,7 +1089,7 @@ extern "C" int vk_mmd_fwd(const float* z, const float* prior, int64_t N, int64_t
     double* gacc = (double*)(ws + w.gacc);
     cudaMemsetAsync(gacc, 0, (size_t)rows * D * sizeof(double), st);
     const size_t shb = ((size_t)8 * D + 8) * sizeof(double);
-    auto kern = kernel_type == 0 ? mmd_simt_rows_kernel<0> : mmd_simt_rows_kernel<1>;
+    auto kern = kernel_type == 0 ? mmd_simt_rows_kernel<0, false> : mmd_simt_rows_kernel<1, false>;
     if (shb > 48 * 1024 && cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shb) != cudaSuccess)
       return check_launch("mmd_fwd (SIMT shared memory attribute)");
     const dim3 grid((unsigned)rows, 1);
@@ -1060,7 +1143,7 @@ extern "C" int vk_mmd_fwd(const float* z, const float* prior, int64_t N, int64_t
     const int n_rows = (int)(nloc < kSampleRows ? nloc : kSampleRows);
     const int64_t row_step = nloc / n_rows;
     const size_t shb = ((size_t)8 * D + 8) * sizeof(double);
-    auto kern = kernel_type == 0 ? mmd_simt_rows_kernel<0> : mmd_simt_rows_kernel<1>;
+    auto kern = kernel_type == 0 ? mmd_simt_rows_kernel<0, true> : mmd_simt_rows_kernel<1, true>;
     const dim3 grid((unsigned)n_rows, kSampleSplits);
     kern<<<grid, 256, shb, st>>>(z, z, N, (int)D, row_begin, row_step, n_rows, s.a_exp, s.Ceps, s.C, 1.0, stats->gref, true, nullptr);
     kern<<<grid, 256, shb, st>>>(z, prior, N, (int)D, row_begin, row_step, n_rows, s.a_exp, s.Ceps, s.C, -1.0, stats->gref, true, nullptr);
