@@ -66,7 +66,8 @@ constexpr int kMmdThreads = 32 * 18;  // warps 0-15 epilogue, warp 16 TMA, warp 
 // of a limited chain are summed in fp32 round-to-nearest by the finalize kernel.
 constexpr int kMaxQ = 64, kBalanceQ = 8;
 constexpr int64_t kMaxGradItems = 65536;
-constexpr int kSampleRows = 32, kSampleSplits = 16;     // rows / column splits of the verification sample (auto mode)
+constexpr int kSampleRows = 32, kSampleSplits = 64;     // rows / column splits of the verification sample (auto mode): 2048 CTAs,
+                                                        // ~4.6 waves at 3 CTAs per SM (16 splits = 512 CTAs = 1.15 waves cost two)
 constexpr float kVerifyBudget = 4e-6f;                  // accepted sample error relative to max |grad| (north star: 1e-5)
 constexpr int64_t kAutoMinN = 8192;                     // below this the parity sweep costs < 0.3 ms: nothing to gain
 
