@@ -166,6 +166,23 @@ int vk_iw_bound_bwd(const float* recons, const float* input, const float* lp, co
                     const float* g_loss, const float* g_recon, const float* g_kld, const float* g_negkld,
                     float* g_recons /*[B,G,K,P] or NULL*/, float* g_kl /*[B*G*K] or NULL*/, void* stream);
 
+/* Allocation-free variant of vk_iw_bound_fwd.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments and results as vk_iw_bound_fwd without the workspace: the scratch (a
+ * 256-byte ticket header + 3 doubles per batch item) lives in a file-scope `static __device__` array of the library,
+ * 256 + 24 * VK_IW_STATIC_MAX_BATCH = 393 472 bytes, which every GPU that loads the library holds until the process
+ * exits.  The call allocates nothing (no cudaMalloc / cudaFree, no allocating library routine); it enqueues one
+ * 256-byte cudaMemsetAsync (the header must start at zero; the array keeps the previous call's contents) and the kernel.
+ *   B > VK_IW_STATIC_MAX_BATCH -> VK_ERR_UNSUPPORTED with a message naming the limit (use vk_iw_bound_fwd instead).
+ *   The array's device address is resolved with cudaGetSymbolAddress on the first call per device (that device current)
+ *   and cached: make that first call outside a stream capture.
+ *   Every call on a device shares the one array: calls that OVERLAP on the GPU (different streams or host threads)
+ *   race on it and give wrong results; calls on one stream are ordered and safe. */
+#define VK_IW_STATIC_MAX_BATCH 16384
+int vk_iw_bound_fwd_static(const float* recons, const float* input, const float* kl,
+                           int64_t B, int64_t G, int64_t K, int64_t P, float M_N,
+                           float* lp_out, float* out /*[4]*/, void* stream);
+
 /* ---------------------------------------------------------------------------
  * K7  VQ-VAE VectorQuantizer               (reference: models/vq_vae.py:24-55)
  *

@@ -270,3 +270,69 @@ extern "C" int vk_iw_bound_bwd(const float* recons, const float* input, const fl
   iw_bound_bwd_kernel<<<grid, 256, smem, s>>>(recons, input, lp, kl, p, chunk, g_loss, g_recon, g_kld, g_negkld, g_recons, g_kl);
   return check_launch("iw_bound_bwd");
 }
+
+// ---- allocation-free variant of the forward --------------------------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  vk_iw_bound_fwd takes its scratch (the
+// ticket header + 3 doubles per batch item) from a caller-provided workspace; this entry point keeps that scratch in a
+// file-scope device array instead, so the caller passes inputs and outputs only.  The array is 256 + 24 * 16384 = 393 472
+// bytes and every GPU that loads the library holds it until the process exits.
+//
+// In HOST code `g_iw_static_scratch` is only a stand-in for the symbol, not a device address (a kernel handed it would
+// fault, or silently use host memory where the GPU can reach it): the address is resolved with cudaGetSymbolAddress once
+// per device, with that device current, and cached.
+// Every call on a device shares the one array: calls that overlap on the GPU (two streams, two host threads) race on it.
+namespace vk {
+namespace {
+constexpr int64_t kIwStaticMaxB = VK_IW_STATIC_MAX_BATCH;
+constexpr int kIwStaticMaxDevices = 64;
+static __device__ __align__(256) unsigned char g_iw_static_scratch[kWsHeader + kIwStaticMaxB * 3 * sizeof(double)];
+
+// device address of the array on the CURRENT device (resolved on first use per device; no allocation involved)
+int iw_static_scratch(unsigned char** out) {
+  static void* cached[kIwStaticMaxDevices] = {nullptr};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return fail(VK_ERR_CUDA, "iw_bound_fwd_static: cudaGetDevice: %s", cudaGetErrorString(e));
+  VK_REQUIRE(dev >= 0 && dev < kIwStaticMaxDevices, VK_ERR_UNSUPPORTED, "iw_bound_fwd_static: device index %d out of range", dev);
+  void* p = __atomic_load_n(&cached[dev], __ATOMIC_ACQUIRE);
+  if (!p) {
+    e = cudaGetSymbolAddress(&p, g_iw_static_scratch);
+    if (e != cudaSuccess || !p) {
+      cudaGetLastError();
+      return fail(VK_ERR_CUDA, "iw_bound_fwd_static: cudaGetSymbolAddress on device %d: %s", dev, cudaGetErrorString(e));
+    }
+    __atomic_store_n(&cached[dev], p, __ATOMIC_RELEASE);      // the same value whichever thread resolves it first
+  }
+  *out = static_cast<unsigned char*>(p);
+  return VK_OK;
+}
+}  // namespace
+}  // namespace vk
+
+extern "C" int vk_iw_bound_fwd_static(const float* recons, const float* input, const float* kl, int64_t B, int64_t G,
+                                      int64_t K, int64_t P, float M_N, float* lp_out, float* out, void* stream) {
+  VK_REQUIRE(recons && input && kl && lp_out && out, VK_ERR_BAD_ARG, "iw_bound_fwd_static: null pointer");
+  VK_REQUIRE(B > 0 && G > 0 && K > 0 && P > 0, VK_ERR_BAD_ARG, "iw_bound_fwd_static: bad sizes");
+  VK_REQUIRE(B <= kIwStaticMaxB, VK_ERR_UNSUPPORTED,
+             "iw_bound_fwd_static: batch %lld exceeds the static scratch maximum of %lld (use vk_iw_bound_fwd with a workspace)",
+             (long long)B, (long long)kIwStaticMaxB);
+  const int64_t GK = G * K;
+  IwParams p{B, G, K, P, M_N};
+  const int64_t smem = (GK * 8 + GK) * 4;
+  VK_REQUIRE(smem <= kIwMaxSmem, VK_ERR_UNSUPPORTED, "iw_bound_fwd_static: G*K=%lld too large for shared memory", (long long)GK);
+  unsigned char* scratch = nullptr;
+  int rc = iw_static_scratch(&scratch);
+  if (rc != VK_OK) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  // the array keeps the last call's contents: the ticket header must start at zero (the kernel leaves it zeroed, but an
+  // aborted launch would not); the partials are fully rewritten for the B blocks of this call before they are read
+  cudaError_t e = cudaMemsetAsync(scratch, 0, kWsHeader, s);
+  if (e != cudaSuccess) return fail(VK_ERR_CUDA, "iw_bound_fwd_static: cudaMemsetAsync: %s", cudaGetErrorString(e));
+  if (smem > 48 * 1024)
+    cudaFuncSetAttribute(iw_bound_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  iw_bound_fwd_kernel<<<(unsigned)B, 256, smem, s>>>(recons, input, kl, p, lp_out, out,
+                                                     reinterpret_cast<unsigned int*>(scratch),
+                                                     reinterpret_cast<double*>(scratch + kWsHeader));
+  return check_launch("iw_bound_fwd_static");
+}

@@ -30,6 +30,7 @@ _SIGNATURES = {
     "vk_elbo_bwd": ([_p, _p, _i64, _i64, _i, _f, _i, _f, _f, _p, _p, _p, _p, _p, _p, _p, _p], _i),
     "vk_per_image_mse": ([_p, _p, _i64, _i64, _p, _p], _i),
     "vk_iw_bound_fwd": ([_p, _p, _p, _i64, _i64, _i64, _i64, _f, _p, _p, _p, _i64, _p], _i),
+    "vk_iw_bound_fwd_static": ([_p, _p, _p, _i64, _i64, _i64, _i64, _f, _p, _p, _p], _i),
     "vk_vq_workspace_bytes": ([_i64, _i64], _i64),
     "vk_vq_fwd": ([_p, _p, _i64, _i64, _i64, _i64, _f, _p, _p, _p, _p, _i64, _p], _i),
     "vk_vq_bwd": ([_p, _p, _p, _p, _p, _i64, _i64, _i64, _i64, _f, _p, _p, _p], _i),
