@@ -66,8 +66,12 @@ constexpr int kMmdThreads = 32 * 18;  // warps 0-15 epilogue, warp 16 TMA, warp 
 // of a limited chain are summed in fp32 round-to-nearest by the finalize kernel.
 constexpr int kMaxQ = 64, kBalanceQ = 8;
 constexpr int64_t kMaxGradItems = 65536;
-constexpr int kSampleRows = 32, kSampleSplits = 64;     // rows / column splits of the verification sample (auto mode): 2048 CTAs,
-                                                        // ~4.6 waves at 3 CTAs per SM (16 splits = 512 CTAs = 1.15 waves cost two)
+// rows / column splits of the verification sample (auto mode).  16 rows x 128 dims = 2048 gradient entries against all N
+// columns: the rounding error of a reduced-precision sweep is statistical and spread evenly over the rows (measured
+// r02b/r02g: the sample's error tracks the full gradient's within 2x on every data set tried), and the two SIMT passes
+// cost time in proportion to the rows (32 rows: 1.0 ms of an 8.3 ms call at N = 65 536).  16 x 128 splits = 2048 CTAs,
+// ~4.6 waves at 3 CTAs per SM (512 CTAs = 1.15 waves cost two).
+constexpr int kSampleRows = 16, kSampleSplits = 128;
 constexpr float kVerifyBudget = 4e-6f;                  // accepted sample error relative to max |grad| (north star: 1e-5)
 constexpr int64_t kAutoMinN = 8192;                     // below this the parity sweep costs < 0.3 ms: nothing to gain
 
