@@ -178,13 +178,27 @@ mmd_colsum_kernel(const float* __restrict__ Z, const float* __restrict__ P, int6
   __shared__ double sh[8][2][130];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   double az[4] = {0, 0, 0, 0}, ap[4] = {0, 0, 0, 0}, nz = 0.0, np = 0.0;
-  for (int64_t r = (int64_t)blockIdx.x * 8 + warp; r < N; r += (int64_t)gridDim.x * 8) {
+  // four rows in flight per warp (independent loads), fp32 -> double accumulation per element
+  const int64_t stride = (int64_t)gridDim.x * 8;
+  for (int64_t r0 = (int64_t)blockIdx.x * 8 + warp; r0 < N; r0 += 4 * stride) {
+    float a[4][4], b[4][4];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const int d = lane + 32 * k;
-      if (d < D) {
-        const double a = (double)Z[r * D + d], b = (double)P[r * D + d];
-        az[k] += a; ap[k] += b; nz += a * a; np += b * b;
+    for (int u = 0; u < 4; ++u) {
+      const int64_t r = r0 + u * stride;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int d = lane + 32 * k;
+        const bool ok = r < N && d < D;
+        a[u][k] = ok ? __ldg(Z + r * D + d) : 0.f;
+        b[u][k] = ok ? __ldg(P + r * D + d) : 0.f;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const double x = (double)a[u][k], y = (double)b[u][k];
+        az[k] += x; ap[k] += y; nz += x * x; np += y * y;
       }
     }
   }
@@ -212,13 +226,29 @@ __device__ __forceinline__ float rcp_approx(float x) {
   return y;
 }
 
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(1024)
 mmd_stats_finalize_kernel(const double* __restrict__ part, int blocks, int64_t N, int D, int kernel_type, float a_exp,
                           float Ceps, MmdStats* __restrict__ st) {
   __shared__ double red[4][128];
+  __shared__ double part_s[8][2][130];
+  // 8 slices of the block partials per column (fixed order inside a slice and across slices: deterministic)
+  {
+    const int c = threadIdx.x & 127, sl = threadIdx.x >> 7;
+    const int per = (blocks + 7) / 8, b0 = sl * per, b1 = b0 + per < blocks ? b0 + per : blocks;
+    double a0 = 0.0, a1 = 0.0, n0 = 0.0, n1 = 0.0;
+    for (int b = b0; b < b1; ++b) {
+      a0 += part[((size_t)b * 2 + 0) * 130 + c]; a1 += part[((size_t)b * 2 + 1) * 130 + c];
+      if (c == 0) { n0 += part[((size_t)b * 2 + 0) * 130 + 128]; n1 += part[((size_t)b * 2 + 1) * 130 + 128]; }
+    }
+    part_s[sl][0][c] = a0; part_s[sl][1][c] = a1;
+    if (c == 0) { part_s[sl][0][128] = n0; part_s[sl][1][128] = n1; }
+  }
+  __syncthreads();
+  if (threadIdx.x >= 128) return;
   const int d = threadIdx.x;
   double sz = 0.0, sp = 0.0;
-  if (d < D) for (int b = 0; b < blocks; ++b) { sz += part[((size_t)b * 2 + 0) * 130 + d]; sp += part[((size_t)b * 2 + 1) * 130 + d]; }
+  for (int sl = 0; sl < 8; ++sl) { sz += part_s[sl][0][d]; sp += part_s[sl][1][d]; }
+  if (d >= D) { sz = 0.0; sp = 0.0; }
   const double n = (double)N;
   const float m = d < D ? (float)(0.5 * (sz / n + sp / n)) : 0.f;
   st->m[d] = m;
@@ -230,11 +260,11 @@ mmd_stats_finalize_kernel(const double* __restrict__ part, int blocks, int64_t N
   red[1][d] = d < D ? -2.0 * (double)m * sp + n * (double)m * (double)m : 0.0;
   red[2][d] = d < D ? (szc / n) * (szc / n) : 0.0;
   red[3][d] = d < D ? (szc / n) * (spc / n) : 0.0;
-  for (int i = d; i < kSampleRows * 128; i += blockDim.x) st->gref[i] = 0.0;
-  __syncthreads();
+  for (int i = d; i < kSampleRows * 128; i += 128) st->gref[i] = 0.0;
+  asm volatile("bar.sync 1, 128;" ::: "memory");           // the first 128 threads only (the others have returned)
   if (d == 0) {
     double nz = 0.0, np = 0.0, a = 0.0, b = 0.0, mz2 = 0.0, mzp = 0.0;
-    for (int blk = 0; blk < blocks; ++blk) { nz += part[((size_t)blk * 2 + 0) * 130 + 128]; np += part[((size_t)blk * 2 + 1) * 130 + 128]; }
+    for (int sl = 0; sl < 8; ++sl) { nz += part_s[sl][0][128]; np += part_s[sl][1][128]; }
     for (int i = 0; i < 128; ++i) { a += red[0][i]; b += red[1][i]; mz2 += red[2][i]; mzp += red[3][i]; }
     const double ez = (nz + a) / n, ep = (np + b) / n;            // mean squared norms of the centred rows
     double dzz = 2.0 * (ez - mz2), dpz = ez + ep - 2.0 * mzp;    // mean squared distances z-z, z-prior
@@ -1115,7 +1145,7 @@ extern "C" int vk_mmd_fwd(const float* z, const float* prior, int64_t N, int64_t
   // ---- statistics, centre, operand images ----
   const int sblocks = (int)((N + 7) / 8 < kStatBlocks ? (N + 7) / 8 : kStatBlocks);
   mmd_colsum_kernel<<<sblocks, 256, 0, st>>>(z, prior, N, (int)D, colpart);
-  mmd_stats_finalize_kernel<<<1, 128, 0, st>>>(colpart, sblocks, N, (int)D, kernel_type, s.a_exp, s.Ceps, stats);
+  mmd_stats_finalize_kernel<<<1, 1024, 0, st>>>(colpart, sblocks, N, (int)D, kernel_type, s.a_exp, s.Ceps, stats);
   const int64_t pack_work = (int64_t)s.T * kRows * s.nkc;
   const int64_t pack_cap = (int64_t)sm_count() * 16;
   const int pack_blocks = (int)((pack_work + 255) / 256 < pack_cap ? (pack_work + 255) / 256 : pack_cap);
@@ -1145,7 +1175,12 @@ extern "C" int vk_mmd_fwd(const float* z, const float* prior, int64_t N, int64_t
   if (rc != VK_OK) return rc;
   if (verify) {
     const int64_t nloc = (row_end - row_begin);
-    const int n_rows = (int)(nloc < kSampleRows ? nloc : kSampleRows);
+    // a rank that sweeps 1/G of the rows checks 1/G of the sample (at least 2 rows): the SIMT passes cost rows x N and
+    // would otherwise be a fixed cost that does not shrink with the shard
+    int64_t want = (kSampleRows * nloc + N - 1) / N;
+    if (want < 2) want = 2;
+    if (want > kSampleRows) want = kSampleRows;
+    const int n_rows = (int)(nloc < want ? nloc : want);
     const int64_t row_step = nloc / n_rows;
     const size_t shb = ((size_t)8 * D + 8) * sizeof(double);
     auto kern = kernel_type == 0 ? mmd_simt_rows_kernel<0, true> : mmd_simt_rows_kernel<1, true>;
