@@ -284,45 +284,55 @@ mmd_stats_finalize_kernel(const double* __restrict__ part, int blocks, int64_t N
 }
 
 // ---- pack: fp32 [N,D] - m -> image tiles [T][hi/lo][Dp/8][128][8] bf16 ; norms [T*128] fp32 ---------------------
-__global__ void mmd_pack_kernel(const float* __restrict__ X, const MmdStats* __restrict__ st, int64_t N, int D, int Dp,
-                                uint8_t* __restrict__ imgB, int T) {
+// pack + norms of BOTH matrices in one launch (gridDim.y: 0 z, 1 prior): half a warp per row, lanes over the 8-element K
+// chunks.  Each lane centres its 8 values, adds its share of the row norm, writes the hi / lo image chunks; a 16-lane
+// shuffle reduction (fixed order) finishes the norm.  Replaces 2 pack + 2 norm launches: the fixed cost matters once the
+// sweep is sharded over 8 GPUs.
+__global__ void __launch_bounds__(256)
+mmd_pack_norm_kernel(const float* __restrict__ Z, const float* __restrict__ P, const MmdStats* __restrict__ st, int64_t N,
+                     int D, int Dp, float scale, uint8_t* __restrict__ imgZ, uint8_t* __restrict__ imgP,
+                     float* __restrict__ normZ, float* __restrict__ normP, int T) {
+  const float* X = blockIdx.y ? P : Z;
+  uint8_t* imgB = blockIdx.y ? imgP : imgZ;
+  float* norms = blockIdx.y ? normP : normZ;
   const int nkc = Dp / 8;
-  const int64_t total = (int64_t)T * kRows * nkc;
-  for (int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t row = g / nkc;
-    const int kc = (int)(g % nkc);
+  const int kc = threadIdx.x & 15;
+  const int64_t rows = (int64_t)T * kRows;
+  const bool vec = (D & 3) == 0 && (reinterpret_cast<uintptr_t>(X) & 15) == 0;
+  for (int64_t row = (int64_t)blockIdx.x * 16 + (threadIdx.x >> 4); row < rows; row += (int64_t)gridDim.x * 16) {
     float v[8];
 #pragma unroll
-    for (int e = 0; e < 8; ++e) {
-      const int d = kc * 8 + e;
-      v[e] = (row < N && d < D) ? X[row * D + d] - st->m[d] : 0.f;
-    }
-    uint32_t ph[4], pl[4];
+    for (int e = 0; e < 8; ++e) v[e] = 0.f;
+    if (row < N && kc < nkc) {
+      const int d0 = kc * 8;
+      if (vec && d0 + 8 <= D) {
+        const float4 a = __ldg(reinterpret_cast<const float4*>(X + row * D + d0));
+        const float4 b = __ldg(reinterpret_cast<const float4*>(X + row * D + d0 + 4));
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
 #pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      __nv_bfloat16 h0, l0, h1, l1;
-      split_bf16(v[2 * e], h0, l0);
-      split_bf16(v[2 * e + 1], h1, l1);
-      ph[e] = pack2(h0, h1);
-      pl[e] = pack2(l0, l1);
+        for (int e = 0; e < 8; ++e) v[e] -= st->m[d0 + e];
+      } else {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) if (d0 + e < D) v[e] = X[row * D + d0 + e] - st->m[d0 + e];
+      }
     }
-    // 64-row granules: [granule][hi/lo][Dp/8][64][8]
-    uint8_t* gb = imgB + (row / kCols) * (tile_img_bytes(Dp) / 2);
-    const int rb = (int)(row % kCols);
-    *reinterpret_cast<uint4*>(gb + ((size_t)kc * kCols + rb) * 16) = make_uint4(ph[0], ph[1], ph[2], ph[3]);
-    *reinterpret_cast<uint4*>(gb + ((size_t)(nkc + kc) * kCols + rb) * 16) = make_uint4(pl[0], pl[1], pl[2], pl[3]);
+    float sq = 0.f;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) sq = fmaf(v[e], v[e], sq);
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);      // stays inside the 16-lane half
+    if (kc == 0) norms[row] = sq * scale;              // RBF: |x|^2 * a_exp (the epilogue's ex2 argument), IMQ: |x|^2
+    if (kc < nkc) {
+      uint32_t ph[4], pl[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) split_pair(v[2 * e], v[2 * e + 1], ph[e], pl[e]);
+      // 64-row granules: [granule][hi/lo][Dp/8][64][8]
+      uint8_t* gb = imgB + (row / kCols) * (tile_img_bytes(Dp) / 2);
+      const int rb = (int)(row % kCols);
+      *reinterpret_cast<uint4*>(gb + ((size_t)kc * kCols + rb) * 16) = make_uint4(ph[0], ph[1], ph[2], ph[3]);
+      *reinterpret_cast<uint4*>(gb + ((size_t)(nkc + kc) * kCols + rb) * 16) = make_uint4(pl[0], pl[1], pl[2], pl[3]);
+    }
   }
-}
-// one warp per row, fixed summation order
-__global__ void mmd_norm_kernel(const float* __restrict__ X, const MmdStats* __restrict__ st, int64_t N, int D, float scale,
-                                float* __restrict__ norms, int T) {
-  const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
-  if (row >= (int64_t)T * kRows) return;
-  float s = 0.f;
-  if (row < N) for (int d = lane; d < D; d += 32) { const float v = X[row * D + d] - st->m[d]; s = fmaf(v, v, s); }
-  s = warp_sum(s);
-  if (lane == 0) norms[row] = s * scale;                 // RBF: |x|^2 * a_exp (the epilogue's ex2 argument), IMQ: |x|^2
 }
 
 // ---- work items ---------------------------------------------------------------------------------------------
@@ -1146,15 +1156,12 @@ extern "C" int vk_mmd_fwd(const float* z, const float* prior, int64_t N, int64_t
   const int sblocks = (int)((N + 7) / 8 < kStatBlocks ? (N + 7) / 8 : kStatBlocks);
   mmd_colsum_kernel<<<sblocks, 256, 0, st>>>(z, prior, N, (int)D, colpart);
   mmd_stats_finalize_kernel<<<1, 1024, 0, st>>>(colpart, sblocks, N, (int)D, kernel_type, s.a_exp, s.Ceps, stats);
-  const int64_t pack_work = (int64_t)s.T * kRows * s.nkc;
-  const int64_t pack_cap = (int64_t)sm_count() * 16;
-  const int pack_blocks = (int)((pack_work + 255) / 256 < pack_cap ? (pack_work + 255) / 256 : pack_cap);
-  const int norm_blocks = (int)(((int64_t)s.T * kRows * 32 + 255) / 256);
-  mmd_pack_kernel<<<pack_blocks, 256, 0, st>>>(z, stats, N, (int)D, s.Dp, ws + w.imgZb, s.T);
-  mmd_pack_kernel<<<pack_blocks, 256, 0, st>>>(prior, stats, N, (int)D, s.Dp, ws + w.imgPb, s.T);
+  const int64_t pack_rows = (int64_t)s.T * kRows;
+  const int64_t pack_cap = (int64_t)sm_count() * 8;
+  const int pack_blocks = (int)((pack_rows + 15) / 16 < pack_cap ? (pack_rows + 15) / 16 : pack_cap);
   const float nscale = kernel_type == 0 ? s.a_exp : 1.f;
-  mmd_norm_kernel<<<norm_blocks, 256, 0, st>>>(z, stats, N, (int)D, nscale, (float*)(ws + w.normZ), s.T);
-  mmd_norm_kernel<<<norm_blocks, 256, 0, st>>>(prior, stats, N, (int)D, nscale, (float*)(ws + w.normP), s.T);
+  mmd_pack_norm_kernel<<<dim3(pack_blocks, 2), 256, 0, st>>>(z, prior, stats, N, (int)D, s.Dp, nscale, ws + w.imgZb, ws + w.imgPb,
+                                                             (float*)(ws + w.normZ), (float*)(ws + w.normP), s.T);
   int rc = check_launch("mmd_pack");
   if (rc != VK_OK) return rc;
   // ---- precision policy ----

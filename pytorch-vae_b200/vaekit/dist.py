@@ -74,6 +74,17 @@ def gather_rows(x_local: torch.Tensor, group=None) -> torch.Tensor:
     return out
 
 
+def gather_rows_async(x_local: torch.Tensor, group=None):
+    """gather_rows started asynchronously: (output, work handle or None).  `handle.wait()` orders the CURRENT stream after
+    the collective; kernels enqueued before the wait run under it."""
+    if not _active(group):
+        return x_local.contiguous(), None
+    world = dist.get_world_size(group)
+    out = torch.empty((world * x_local.shape[0],) + tuple(x_local.shape[1:]), dtype=x_local.dtype, device=x_local.device)
+    work = dist.all_gather_into_tensor(out, x_local.contiguous(), group=group, async_op=True)
+    return out, work
+
+
 def reduce_sum_(t: torch.Tensor, group=None) -> torch.Tensor:
     if _active(group):
         dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
@@ -141,8 +152,11 @@ class _ShardedMmd(torch.autograd.Function):
         from . import functional as F
         world, rank = world_rank(group)
         N, r0, r1 = plan_rows(z_local.shape[0], world, rank)
-        z_all = gather_rows(z_local, group)
-        prior_all = F.philox_normal_dev(z_all.shape, shared_rng_key(z_local.device, z_all.numel(), group))
+        # the gather is started first and the prior (a pure function of the shared key, no traffic) is drawn under it
+        z_all, pending = gather_rows_async(z_local, group)
+        prior_all = F.philox_normal_dev((N, z_local.shape[1]), shared_rng_key(z_local.device, N * z_local.shape[1], group))
+        if pending is not None:
+            pending.wait()
         sums, grad = F.mmd_sweep(z_all, prior_all, kernel_type, z_var, r0, r1, passes)
         reduce_sum_(sums, group)
         out = F.mmd_combine(sums, N, kernel_type, reg_weight)
