@@ -7,15 +7,15 @@
 //   stats kernels   column means of z and prior -> the common centre m (distances are translation invariant, so the
 //                   whole sweep runs on x - m: smaller norms, less cancellation in |x|^2 + |y|^2 - 2 x.y), column sums of
 //                   the centred data, and the coefficient offsets c0 (the coefficient at the mean squared distance)
-//   pack kernels    z - m, prior - m (fp32 [N,D]) -> bf16 hi/lo operand images, 64-row granules in the UMMA no-swizzle
+//   pack kernels    z - m, prior - m (fp32 [N,D]) -> bf16 hi/lo operand images, 128-row blocks in the UMMA no-swizzle
 //                   canonical layout, + fp32 row norms.  The same image is a K-major operand (K = latent dim)
 //                   for the distance GEMM and an MN-major operand (K = sample index) for the gradient GEMM.
 //   main kernel     persistent, warp-specialised, one CTA per SM:
-//     TMA warp      1-D bulk copies (cp.async.bulk -> mbarrier) of 64-column B stages
-//     MMA warp      GEMM1  S[128,64]  = X_i . Y_j^T         (G1P passes, fp32 accumulate in TMEM)
+//     TMA warp      1-D bulk copies (cp.async.bulk -> mbarrier) of 128-column B stages
+//     MMA warp      GEMM1  S[128,128] = X_i . Y_j^T         (G1P passes, fp32 accumulate in TMEM)
 //                   GEMM2  O[128,D]  += C'_ij . Y_j         (G2P passes; centred coefficient tile written by the epilogue)
 //     epilogue 16w  tcgen05.ld S -> d^2 -> k (ex2 / rcp) -> running sum of k, c' = dk/dd^2 - c0 (signed) ->
-//                   row sums of c', bf16 (hi / lo) of c' into tensor memory as the A operand of GEMM2
+//                   row sums of c', bf16 (hi / lo) of c' back into the S columns just read = the A operand of GEMM2
 //   finalize        dL/dz_i (unscaled) = z_i * sum_j c'_ij - O'_i + [c0 part from the column sums, float64];
 //                   per-CTA partial sums -> three kernel sums
 //   sample check    (auto mode, reduced passes) float64 SIMT gradient of 32 sample rows against all columns; if the
@@ -44,21 +44,22 @@ using namespace tc;
 namespace {
 
 constexpr int kRows = 128;       // row block (MMA M)
-constexpr int kCols = 64;        // column tile (GEMM1 N, GEMM2 K)
-constexpr int kBStages = 4;
-constexpr int kNormRing = 8;
+constexpr int kCols = 128;       // column block (GEMM1 N, GEMM2 K): one B stage, one S buffer
+constexpr int kMaxBStages = 6;   // B ring: 6 hi-only stages, or 3 hi + lo stages when a pass reads the lo image
+constexpr int kNormRing = 8;     // >= B stages + 2 (prior-prior items free a stage before the epilogue has read its norms)
 // mbarriers
-constexpr int kBarAFull = 0, kBarAEmpty = 1, kBarBFull = 2, kBarBEmpty = kBarBFull + kBStages, kBarSFull = kBarBEmpty + kBStages,
-              kBarSEmpty = kBarSFull + 2, kBarKFull = kBarSEmpty + 2, kBarKEmpty = kBarKFull + 2, kBarOFull = kBarKEmpty + 2,
+constexpr int kBarAFull = 0, kBarAEmpty = 1, kBarBFull = 2, kBarBEmpty = kBarBFull + kMaxBStages,
+              kBarSFull = kBarBEmpty + kMaxBStages, kBarKFull = kBarSFull + 2, kBarOFull = kBarKFull + 2,
               kBarOEmpty = kBarOFull + 1, kNumBars = kBarOEmpty + 1;
-// tensor memory map (512 columns): S 2 x 64 | O <= 128 | row-block operand hi, lo (Dp/2 columns each, two bf16 per
-// column) | coefficient tile hi, lo (32 columns each), double-buffered
-constexpr uint32_t kTmS = 0, kTmO = 128, kTmAhi = 256, kTmAlo = 320, kTmK = 384;
+// tensor memory map (512 columns): S / coefficient buffers 2 x 128 | O <= 128 | row-block operand hi, lo (Dp/2 columns
+// each, two bf16 per column).  The coefficient block (bf16 hi [+ lo]: 16 [+ 16] columns per 32-column slice) overwrites
+// the S columns its warp has just read, so it needs no columns -- and no barriers -- of its own.
+constexpr uint32_t kTmS = 0, kTmO = 256, kTmAhi = 384, kTmAlo = 448;
 constexpr int kEpiWarps = 16, kColGroups = kEpiWarps / 4, kTmaWarp = 16, kMmaWarp = 17;
 constexpr int kEpiThreads = 32 * kEpiWarps;
 constexpr int kMmdThreads = 32 * 18;  // warps 0-15 epilogue, warp 16 TMA, warp 17 MMA
 // Column chunks per row block.  Two rules pick Q: enough gradient items for the static schedule to balance (up to
-// kBalanceQ), and -- when a chain limit is set -- a bound on how many 64-column tiles are accumulated into one gradient
+// kBalanceQ), and -- when a chain limit is set -- a bound on how many 128-column blocks are accumulated into one gradient
 // tile in tensor memory: the tcgen05 fp32 accumulator truncates, a bias that grows with the length of the chain AND with
 // the magnitude of the accumulated values.  Round 1 accumulated the raw coefficients (|O| ~ N k |y|: 2.3e-4 of the
 // gradient's maximum at N = 65 536 with one 683-tile chain, 1.8e-5 with 32-tile chains at 17 ms per step).  Round 2
@@ -91,7 +92,6 @@ struct MmdShape {
   int64_t N;
   int D, Dp, nkc;       // latent dim, padded to 16, number of 8-element K chunks
   int T;                // 128-row tiles of the full matrix
-  int lz;               // live 64-column tiles per side: ceil(N / 64)
   int rb0, rb1;         // row-block range owned by this call
   int Q;                // column chunks per row block (gradient items)
   int kernel_type;      // 0 rbf, 1 imq
@@ -118,7 +118,7 @@ inline MmdWs mmd_ws(int64_t N, int D, int rows_local_blocks, int Q) {
   w.colpart = o; o += (size_t)kStatBlocks * 2 * 130 * sizeof(double);
   w.cta_sums = o; o += (size_t)256 * 3 * sizeof(double);
   o = (o + 255) & ~(size_t)255;
-  w.imgZb = o; o += (size_t)T * tile_img_bytes(Dp);      // bf16 hi/lo images in 64-row granules (column stages: one bulk copy each)
+  w.imgZb = o; o += (size_t)T * tile_img_bytes(Dp);      // bf16 hi | lo images of 128-row blocks (column stages: one bulk copy each)
   w.imgPb = o; o += (size_t)T * tile_img_bytes(Dp);
   w.normZ = o; o += (size_t)T * kRows * 4;
   w.normP = o; o += (size_t)T * kRows * 4;
@@ -133,7 +133,8 @@ inline int q_cap(int row_blocks) {
   if (c < kBalanceQ) c = kBalanceQ;
   return (int)c;
 }
-// chain_tiles: longest accumulation chain in 64-column tiles (0 = no limit)
+// chain_tiles: longest accumulation chain in 64-column units (0 = no limit); the sequence of a gradient item is made of
+// 2 T blocks of 128 columns ([z blocks | prior blocks])
 inline int pick_Q(int T, int row_blocks, int chain_tiles) {
   // aim for >= 8 gradient items per SM so the static round-robin schedule balances
   int q = (sm_count() * 8 + row_blocks - 1) / row_blocks;
@@ -143,9 +144,9 @@ inline int pick_Q(int T, int row_blocks, int chain_tiles) {
     if (chain > q) q = chain;
   }
   if (q > q_cap(row_blocks)) q = q_cap(row_blocks);
-  if (q > 4 * T) q = 4 * T;
+  if (q > 2 * T) q = 2 * T;
   if (q < 1) q = 1;
-  const int n = 4 * T, len = (n + q - 1) / q;
+  const int n = 2 * T, len = (n + q - 1) / q;
   return (n + len - 1) / len;                 // no empty chunk
 }
 // upper bound of Q * row_blocks over every row range of an N-row problem (what the workspace query must cover)
@@ -162,7 +163,7 @@ struct MmdSmem {
 __host__ __device__ inline MmdSmem mmd_smem(int Dp) {
   MmdSmem m;
   uint32_t o = 0;
-  m.B = o; o += kBStages * 2u * kCols * Dp * 2u;             // column stages: hi + lo image of 64 rows each
+  m.B = o; o += 3u * 2u * kCols * Dp * 2u;                   // column stages: 3 x (hi + lo image of 128 rows) or 6 x hi
   m.norms = o; o += kNormRing * kCols * 4u;   // deeper than the B ring: read by the epilogue after b_empty may have fired
   m.bars = o; o += kNumBars * 8;
   m.tmem = o; o += 16;
@@ -326,8 +327,8 @@ mmd_pack_norm_kernel(const float* __restrict__ Z, const float* __restrict__ P, c
       uint32_t ph[4], pl[4];
 #pragma unroll
       for (int e = 0; e < 4; ++e) split_pair(v[2 * e], v[2 * e + 1], ph[e], pl[e]);
-      // 64-row granules: [granule][hi/lo][Dp/8][64][8]
-      uint8_t* gb = imgB + (row / kCols) * (tile_img_bytes(Dp) / 2);
+      // 128-row blocks: [block][hi/lo][Dp/8][128][8]
+      uint8_t* gb = imgB + (row / kCols) * tile_img_bytes(Dp);
       const int rb = (int)(row % kCols);
       *reinterpret_cast<uint4*>(gb + ((size_t)kc * kCols + rb) * 16) = make_uint4(ph[0], ph[1], ph[2], ph[3]);
       *reinterpret_cast<uint4*>(gb + ((size_t)(nkc + kc) * kCols + rb) * 16) = make_uint4(pl[0], pl[1], pl[2], pl[3]);
@@ -337,17 +338,19 @@ mmd_pack_norm_kernel(const float* __restrict__ Z, const float* __restrict__ P, c
 
 // ---- work items ---------------------------------------------------------------------------------------------
 // Item order: for each owned row block i: Q gradient items (i, q), then the prior-prior item of row block i.
+// The column sequence of an item is made of 128-column blocks; a block that reaches beyond N is not skipped but takes
+// the masked epilogue (its operand rows and norms are zero-filled by the pack kernel).
 struct Item {
   int i;          // row block (global index)
-  int grad;       // 1: rows = z, columns = [z tiles | prior tiles] chunk q ; 0: rows = prior, circulant half of prior
-  int u0, u1;     // tile sequence range
+  int grad;       // 1: rows = z, columns = [z blocks | prior blocks] chunk q ; 0: rows = prior, circulant half of prior
+  int u0, u1;     // block sequence range
 };
 struct TileD {
   int bm;         // column matrix: 0 z, 1 prior
-  int jt;         // 64-column tile index
+  int jb;         // 128-column block index
   int kind;       // 0 zz, 1 zp, 2 pp
   float weight;
-  int diag;       // tile touches the main diagonal
+  int diag;       // block on the main diagonal
 };
 __device__ __forceinline__ Item get_item(const MmdShape& s, int idx) {
   Item it;
@@ -356,40 +359,37 @@ __device__ __forceinline__ Item get_item(const MmdShape& s, int idx) {
   const int q = idx % per;
   if (q < s.Q) {
     it.grad = 1;
-    const int n = 4 * s.T, len = (n + s.Q - 1) / s.Q;
+    const int n = 2 * s.T, len = (n + s.Q - 1) / s.Q;
     it.u0 = q * len;
     it.u1 = it.u0 + len < n ? it.u0 + len : n;
     if (it.u0 > n) it.u0 = n;
   } else {
     it.grad = 0;
-    const int noff = (s.T % 2 == 0) ? s.T / 2 + 1 : (s.T + 1) / 2;
     it.u0 = 0;
-    it.u1 = 2 * noff;
+    it.u1 = (s.T % 2 == 0) ? s.T / 2 + 1 : (s.T + 1) / 2;
   }
   return it;
 }
 __device__ __forceinline__ TileD get_tile(const MmdShape& s, const Item& it, int u) {
   TileD t;
   if (it.grad) {
-    const bool zside = u < 2 * s.T;
+    const bool zside = u < s.T;
     t.bm = zside ? 0 : 1;
-    t.jt = zside ? u : u - 2 * s.T;
+    t.jb = zside ? u : u - s.T;
     t.kind = zside ? 0 : 1;
     t.weight = 1.f;
-    t.diag = (t.jt >> 1) == it.i;
+    t.diag = t.jb == it.i;
   } else {
-    const int o = u >> 1;
-    int j128 = it.i + o;                                  // o <= T/2 + 1: one conditional wrap instead of a modulo
-    if (j128 >= s.T) j128 -= s.T;
+    int jb = it.i + u;                                    // u <= T/2 + 1: one conditional wrap instead of a modulo
+    if (jb >= s.T) jb -= s.T;
     t.bm = 1;
-    t.jt = 2 * j128 + (u & 1);
+    t.jb = jb;
     t.kind = 2;
-    t.weight = (o == 0 || (s.T % 2 == 0 && o == s.T / 2)) ? 1.f : 2.f;
-    t.diag = o == 0;
+    t.weight = (u == 0 || (s.T % 2 == 0 && u == s.T / 2)) ? 1.f : 2.f;
+    t.diag = u == 0;
   }
   return t;
 }
-__device__ __forceinline__ bool tile_live(const MmdShape& s, const TileD& t) { return t.jt < s.lz; }
 // two fp32 -> packed bf16 pair (round to nearest), no lo part
 __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
   uint32_t r;
@@ -423,6 +423,18 @@ __device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
 // ---- main kernel ----------------------------------------------------------------------------------------------
 // G1P / G2P: tensor passes of the distance / gradient GEMM.  run_if >= 0: the kernel only runs when st->flag == run_if
 // (the parity sweep behind a failed sample check).
+//
+// Pipeline per 128-column block c (buffer sb = c & 1 of tensor memory):
+//   TMA   B stage c (hi [+ lo] image of the 128 column rows, their norms)            -> B_full[slot]
+//   MMA   G1(c): S[sb] = X_i . Y_c^T            (after B_full)                        -> S_full[sb]
+//   epi   S[sb] -> registers -> k, c' ; bf16 c' back INTO the S columns just read     -> K_full[sb]   (16 warp arrivals)
+//   MMA   G2(c): O += C'[sb] . Y_c              (after K_full)                        -> B_empty[slot]
+// The MMA warp issues G1(c+1) before it waits for K_full(c): the tensor pipe works on the next block's distances
+// while the epilogue is busy, and because tcgen05.mma executes in issue order, G1(c+2) -- issued after G2(c) -- may
+// overwrite buffer sb without another barrier (K_full(c) already says every warp has S(c) in registers).
+// Round 2 measurements behind this shape (profiles/role_prof_mmd_r02r.log, trace_mmd_r02r.log): with 64-column tiles
+// the MMA warp's own instruction stream (~250 uniform-datapath instructions per tile at ~5 cycles) took 1260 cycles per
+// tile against 768 cycles of tensor work, and every epilogue warp walked the loop header of both tile groups.
 template <int G1P, int G2P, int KT>
 // (18 warps = 5 on two of the four SM sub-partitions: 16 384 / 5 / 32 = 102 -> 96 registers per thread is the most a
 // 576-thread CTA can have; __maxnreg__(112) compiles with fewer spills but cannot launch)
@@ -438,14 +450,13 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
   const uint32_t sbase = smem_u32(smem);
   auto bar = [&](int i) { return sbase + L.bars + 8u * i; };
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + L.tmem);
+  constexpr bool kNeedLo = G1P == 3 || G2P == 3;             // the lo image of a column stage is read by some pass
+  constexpr uint32_t NST = kNeedLo ? 3u : 6u;                // B ring slots (same bytes either way)
   if (threadIdx.x == 0) {
-    mbar_init(bar(kBarAFull), kEpiThreads); mbar_init(bar(kBarAEmpty), 1);
-    for (int i = 0; i < kBStages; ++i) { mbar_init(bar(kBarBFull + i), 1); mbar_init(bar(kBarBEmpty + i), 1); }
-    for (int i = 0; i < 2; ++i) {
-      mbar_init(bar(kBarSFull + i), 1); mbar_init(bar(kBarSEmpty + i), kEpiThreads / 2);      // one tile group per S / Kmat buffer use
-      mbar_init(bar(kBarKFull + i), kEpiThreads / 2); mbar_init(bar(kBarKEmpty + i), 1);
-    }
-    mbar_init(bar(kBarOFull), 1); mbar_init(bar(kBarOEmpty), kEpiThreads);
+    mbar_init(bar(kBarAFull), kEpiWarps); mbar_init(bar(kBarAEmpty), 1);
+    for (int i = 0; i < kMaxBStages; ++i) { mbar_init(bar(kBarBFull + i), 1); mbar_init(bar(kBarBEmpty + i), 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(bar(kBarSFull + i), 1); mbar_init(bar(kBarKFull + i), kEpiWarps); }
+    mbar_init(bar(kBarOFull), 1); mbar_init(bar(kBarOEmpty), kEpiWarps);
     mbar_fence_init();
   }
   if (warp == kMmaWarp) tmem_alloc(smem_u32(tmem_slot), 512);
@@ -454,9 +465,8 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
   fence_after_sync();
   const uint32_t tmem = *tmem_slot;
   const uint32_t tmem_S = tmem + kTmS, tmem_O = tmem + kTmO;
-  const uint32_t b_half = (uint32_t)kCols * s.Dp * 2u;      // one hi (or lo) image of a 64-row stage
-  constexpr bool kNeedLo = G1P == 3 || G2P == 3;             // the lo image of a column stage is read by some pass
-  const uint32_t b_bytes = kNeedLo ? 2u * b_half : b_half;
+  const uint32_t b_half = (uint32_t)kCols * s.Dp * 2u;      // the hi (or lo) image of a 128-row stage
+  const uint32_t b_bytes = kNeedLo ? 2u * b_half : b_half;   // bytes of one ring slot = what one bulk copy brings
 
   if (warp == kTmaWarp) {
     // ===== TMA producer =====
@@ -464,17 +474,15 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
       uint32_t nb = 0;
       for (int idx = blockIdx.x; idx < n_items; idx += gridDim.x) {
         const Item it = get_item(s, idx);
-        for (int u = it.u0; u < it.u1; ++u) {
+        for (int u = it.u0; u < it.u1; ++u, ++nb) {
           const TileD t = get_tile(s, it, u);
-          if (!tile_live(s, t)) continue;
-          const uint32_t slot = nb % kBStages;
-          if (nb >= kBStages) mbar_wait(bar(kBarBEmpty + slot), ((nb / kBStages) - 1) & 1);
-          const uint8_t* bimg = (t.bm ? imgPb : imgZb) + (size_t)t.jt * (2 * b_half);
-          const float* nrm = (t.bm ? normP : normZ) + (size_t)t.jt * kCols;
+          const uint32_t slot = nb % NST;
+          if (nb >= NST) mbar_wait(bar(kBarBEmpty + slot), ((nb / NST) - 1) & 1);
+          const uint8_t* bimg = (t.bm ? imgPb : imgZb) + (size_t)t.jb * (2 * b_half);
+          const float* nrm = (t.bm ? normP : normZ) + (size_t)t.jb * kCols;
           mbar_expect_tx(bar(kBarBFull + slot), b_bytes + kCols * 4);
-          bulk_g2s(sbase + L.B + slot * (2u * b_half), bimg, b_bytes, bar(kBarBFull + slot));      // hi (+ lo) image of 64 rows, one copy
+          bulk_g2s(sbase + L.B + slot * b_bytes, bimg, b_bytes, bar(kBarBFull + slot));      // hi (+ lo) image, one copy
           bulk_g2s(sbase + L.norms + (nb % kNormRing) * kCols * 4, nrm, kCols * 4, bar(kBarBFull + slot));
-          ++nb;
         }
       }
     }
@@ -484,26 +492,25 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
     {
       const uint32_t leader = elect_one();
       const uint32_t idesc1 = idesc_bf16(kRows, kCols, 0, 0);       // S = A(K-major) . B(K-major)^T
-      const uint32_t idesc2 = idesc_bf16(kRows, s.Dp, 0, 1);        // O += Kmat(K-major) . B(MN-major)
+      const uint32_t idesc2 = idesc_bf16(kRows, s.Dp, 0, 1);        // O += Cmat(K-major) . B(MN-major)
       const uint32_t b_lbo = kCols * 16;
       const uint64_t b_step = (2u * b_lbo) >> 4, b2_step = 256u >> 4;
       const uint32_t tmem_Ahi = tmem + kTmAhi, tmem_Alo = tmem + kTmAlo;
       const int ksteps1 = s.Dp / 16;
-      uint32_t nb = 0, ns = 0, nk = 0, n_grad_items = 0;
+      uint32_t cnt = 0, n_grad_items = 0;                      // cnt: blocks whose G1 has been issued
       int iter = 0;
       PROF_DECL
       TRACE_DECL(4)
-      auto gemm1 = [&](uint32_t slot) {
-        TRACE(0, ns)
+      auto gemm1 = [&](bool release_b) {
+        const uint32_t slot = cnt % NST, sb = cnt & 1u;
+        TRACE(0, cnt)
         PROF_LAP(3)
-        mbar_wait(bar(kBarBFull + slot), (nb / kBStages) & 1);
+        mbar_wait(bar(kBarBFull + slot), (cnt / NST) & 1);
         PROF_LAP(0)
-        const uint32_t sb = ns & 1;
-        if (ns >= 2) mbar_wait(bar(kBarSEmpty + sb), ((ns >> 1) - 1) & 1);
-        PROF_LAP(1)
         fence_after_sync();
-        const uint32_t b_hi = sbase + L.B + slot * (2u * b_half);
-        const uint64_t db_hi = smem_desc(b_hi, b_lbo, 128), db_lo = smem_desc(b_hi + b_half, b_lbo, 128);
+        const uint32_t b_hi = sbase + L.B + slot * b_bytes;
+        const uint64_t db_hi = smem_desc(b_hi, b_lbo, 128), db_lo = smem_desc(b_hi + b_half, b_lbo, 128);   // lo: kNeedLo modes only
+        const uint32_t s_dst = tmem_S + sb * (uint32_t)kCols;
         uint32_t acc = 0;
 #pragma unroll
         for (int pass = 0; pass < G1P; ++pass) {
@@ -514,112 +521,100 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
           uint64_t db = (G1P == 3 && pass == 1) ? db_lo : db_hi;
 #pragma unroll 4
           for (int k = 0; k < ksteps1; ++k) {
-            mma_bf16_ts_if(leader, tmem_S + sb * kCols, ta, db, idesc1, acc);
+            mma_bf16_ts_if(leader, s_dst, ta, db, idesc1, acc);
             acc = 1;
             ta += 8;
             db += b_step;
           }
         }
         mma_commit_if(leader, bar(kBarSFull + sb));
-        TRACE(1, ns)
-        ++ns;
+        if (release_b) mma_commit_if(leader, bar(kBarBEmpty + slot));   // no gradient GEMM will read this stage
+        TRACE(1, cnt)
+        ++cnt;
       };
       for (int idx = blockIdx.x; idx < n_items; idx += gridDim.x, ++iter) {
         const Item it = get_item(s, idx);
         mbar_wait(bar(kBarAFull), iter & 1);
-        fence_after_sync();
-        // live tiles of this item, in order
-        int live = 0;
-        for (int u = it.u0; u < it.u1; ++u) live += tile_live(s, get_tile(s, it, u)) ? 1 : 0;
-        const uint32_t nb0 = nb;
-        // software pipeline: G1(0), G1(1), then for each j: G1(j+2), G2(j)
-        int issued1 = 0;
-        for (; issued1 < 2 && issued1 < live; ++issued1) {
-          gemm1((nb0 + issued1) % kBStages);
-          if (!it.grad) mma_commit_if(leader, bar(kBarBEmpty + (nb0 + issued1) % kBStages));
-          ++nb;
-        }
-        uint32_t oacc = 0;
-        // live z-side tiles of this chunk come first (tile sequence: [z tiles | prior tiles], dead tiles = columns >= N)
-        int nz_live = 0;
+        const int n = it.u1 - it.u0;
+        const uint32_t c0 = cnt;
+        // z-side blocks of this chunk come first (block sequence: [z blocks | prior blocks])
+        int nz = 0;
         if (it.grad) {
-          const int zend = it.u1 < 2 * s.T ? it.u1 : 2 * s.T;
-          const int hi = zend < s.lz ? zend : s.lz;
-          nz_live = hi > it.u0 ? hi - it.u0 : 0;
+          const int zend = it.u1 < s.T ? it.u1 : s.T;
+          nz = zend > it.u0 ? zend - it.u0 : 0;
         }
-        for (int j = 0; j < live; ++j) {
-          // G1(j+2) goes first: its S buffer was freed as soon as the epilogue had tile j in registers, so the distance
-          // GEMM of tile j+2 runs while the epilogue is still computing the coefficients G2(j) waits for
-          if (issued1 < live) {
-            gemm1((nb0 + issued1) % kBStages);
-            if (!it.grad) mma_commit_if(leader, bar(kBarBEmpty + (nb0 + issued1) % kBStages));
-            ++nb;
-            ++issued1;
-          }
+        if (n > 0) gemm1(!it.grad);
+        uint32_t oacc = 0;
+        for (int j = 0; j < n; ++j) {
+          // G1(j+1) goes first: the distance GEMM of the next block runs while the epilogue works on block j
+          if (j + 1 < n) gemm1(!it.grad);
+          const uint32_t c = c0 + (uint32_t)j, sb = c & 1u;
+          PROF_LAP(3)
+          mbar_wait(bar(kBarKFull + sb), (c >> 1) & 1);       // block j is in the epilogue's registers (+ coefficients written)
+          if (it.grad && j == 0 && n_grad_items > 0) mbar_wait(bar(kBarOEmpty), (n_grad_items - 1) & 1);
+          PROF_LAP(2)
           if (it.grad) {
-            const uint32_t slot = (nb0 + j) % kBStages, kb = nk & 1;
-            const uint32_t neg_a = j >= nz_live ? (1u << 13) : 0u;           // k(z, prior) enters with a minus sign
-            PROF_LAP(3)
-            mbar_wait(bar(kBarKFull + kb), (nk >> 1) & 1);
-            if (j == 0 && n_grad_items > 0) mbar_wait(bar(kBarOEmpty), (n_grad_items - 1) & 1);
-            PROF_LAP(2)
-            TRACE(2, nk)
+            TRACE(2, c)
             fence_after_sync();
-            const uint32_t tk_hi = tmem + kTmK + kb * 64, tk_lo = tk_hi + 32;
-            const uint32_t b_hi = sbase + L.B + slot * (2u * b_half);
-            // A: coefficient tile in tensor memory (K = column index) ; B: MN-major (N = latent dims, K = rows of the stage)
+            const uint32_t slot = c % NST;
+            const uint32_t neg_a = j >= nz ? (1u << 13) : 0u;             // k(z, prior) enters with a minus sign
+            // A: coefficient block in tensor memory, per 32-column slice 16 columns of bf16 pairs hi, then 16 lo (G2P == 3)
+            const uint32_t tk = tmem_S + sb * (uint32_t)kCols;
+            const uint32_t b_hi = sbase + L.B + slot * b_bytes;
+            // B: MN-major (N = latent dims, K = rows of the stage)
             const uint64_t db_hi = smem_desc(b_hi, 128, b_lbo), db_lo = smem_desc(b_hi + b_half, 128, b_lbo);
 #pragma unroll
             for (int pass = 0; pass < G2P; ++pass) {
-              uint32_t ta = (G2P == 3 && pass == 0) ? tk_lo : tk_hi;
+              const uint32_t lo_off = (G2P == 3 && pass == 0) ? 16u : 0u;
               uint64_t db = (G2P == 3 && pass == 1) ? db_lo : db_hi;
 #pragma unroll
               for (int k = 0; k < kCols / 16; ++k) {
-                mma_bf16_ts_if(leader, tmem_O, ta, db, idesc2 | neg_a, oacc);
+                mma_bf16_ts_if(leader, tmem_O, tk + (uint32_t)((k >> 1) * 32 + (k & 1) * 8) + lo_off, db, idesc2 | neg_a, oacc);
                 oacc = 1;
-                ta += 8;
                 db += b2_step;
               }
             }
             mma_commit_if(leader, bar(kBarBEmpty + slot));
-            mma_commit_if(leader, bar(kBarKEmpty + kb));
-            TRACE(3, nk)
-            ++nk;
+            TRACE(3, c)
           }
         }
-        if (it.grad && live > 0) { mma_commit_if(leader, bar(kBarOFull)); ++n_grad_items; }
+        if (it.grad && n > 0) { mma_commit_if(leader, bar(kBarOFull)); ++n_grad_items; }
         mma_commit_if(leader, bar(kBarAEmpty));
       }
       PROF_LAP(3)
-      PROF_OUT("mma wait_b/wait_s_empty/wait_k_full/issue", leader)
+      PROF_OUT("mma wait_b/-/wait_k_full/issue", leader)
       TRACE_OUT("mma g1_start/g1_issued/g2_kfull/g2_issued", 4, leader)
     }
   } else {
-    // ===== epilogue: 16 warps = 2 tile groups x 4 TMEM lane quadrants x 2 column halves.  Group g takes the tiles
-    // that land in S buffer g, so two tiles are in the epilogue at once (four warps per scheduler to hide the TMEM /
-    // MUFU / shared-memory latencies) while every warp still amortises its per-tile bookkeeping over 32 columns =====
+    // ===== epilogue: 16 warps = 4 TMEM lane quadrants x 4 slices of 32 columns; every warp takes its slice of every
+    // block (four warps per scheduler hide the TMEM / MUFU / shared-memory latencies) =====
     const int ew = warp & 3;                                  // TMEM lane quadrant (must equal warp id % 4)
-    const int h = (warp >> 2) & 1;                            // column half of the tile
-    const uint32_t grp = warp >> 3;                           // tile group == S buffer
-    const int cg = warp >> 2;                                 // slot of this warp's partial row sums / O chunk
+    const int cg = warp >> 2;                                 // 32-column slice of the block; slot of this warp's partial row sums / O chunk
     const int t = ew * 32 + lane;                             // row within the block
-    double acc_zz = 0.0, acc_pz = 0.0, acc_pp = 0.0, acc_run = 0.0;   // acc_run: sums of the term run_kind, not yet flushed
+    double acc_zz = 0.0, acc_pz = 0.0, acc_pp = 0.0;
+    // sum of the current term (run_kind) as a compensated fp32 pair: exact to ~2^-45 of the run, no conversion and no
+    // DADD per block (the DADD alone held 5 % of the r02g stall samples)
+    float run_hi = 0.f, run_lo = 0.f;
     int run_kind = -1;
-    uint32_t ns = 0, nk = 0, nb = 0, n_grad_items = 0, item_iter = 0;
+    auto flush_run = [&]() {
+      const double r = (double)run_hi + (double)run_lo;
+      if (run_kind == 0) acc_zz += r; else if (run_kind == 1) acc_pz += r; else if (run_kind == 2) acc_pp += r;
+      run_hi = 0.f; run_lo = 0.f;
+    };
+    uint32_t cnt = 0, n_grad_items = 0, item_iter = 0;
     // RBF: norms arrive pre-scaled by a_exp, so ex2's argument is one FADD + one FFMA; IMQ: t = C + eps + d^2
     const float s_coef = KT == 0 ? -2.f * s.a_exp : -2.f;
     const float c0zz = st->c0[0], c0pz = st->c0[1];          // coefficient offsets (written by the stats kernel)
+    const int n32 = (int)s.N;                                  // N <= 2^24: 32-bit index math in the block loop
     PROF_DECL
     TRACE_DECL(3)
     for (int idx = blockIdx.x; idx < n_items; idx += gridDim.x) {
       const Item it = get_item(s, idx);
-      const int n32 = (int)s.N;                                // N <= 2^24: 32-bit index math in the tile loop
       const int grow = it.i * kRows + t;
       const bool rvalid = grow < n32;
       const bool row_tail = (it.i + 1) * kRows > n32;     // this row block has rows beyond N
       const float nx = (it.grad ? normZ : normP)[grow] + (KT == 1 ? s.Ceps : 0.f);
       float rs = 0.f;
-      int live = 0;
       {
         // this row block's operand -> tensor memory: fp32 row slice [cg*32, cg*32+32) of x - m split into bf16 hi / lo,
         // two per column.  The previous item's MMAs must be finished with the old block first.
@@ -644,44 +639,46 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
         }
         tmem_st_wait();
         fence_before_sync();
-        mbar_arrive(bar(kBarAFull));
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar(kBarAFull));
         ++item_iter;
       }
-      for (int u = it.u0; u < it.u1; ++u) {
+      for (int u = it.u0; u < it.u1; ++u, ++cnt) {
         const TileD td = get_tile(s, it, u);
-        if (!tile_live(s, td)) continue;
-        if ((ns & 1) == grp) {
-          PROF_LAP(1)
-          mbar_wait(bar(kBarSFull + grp), (ns >> 1) & 1);
-          PROF_LAP(0)
-          TRACE(0, ns)
-          fence_after_sync();
-          uint32_t rr[2][16];
-          const uint32_t taddr = tmem_S + ((uint32_t)(ew * 32) << 16) + grp * kCols + h * 32;
-          tmem_ld16(taddr, rr[0]);
-          tmem_ld16(taddr + 16, rr[1]);
-          const float* ny = reinterpret_cast<const float*>(smem + L.norms + (nb % kNormRing) * kCols * 4) + h * 32;
-          const int gcol0 = td.jt * kCols + h * 32;
-          // uniform across the warp (the two instances below contain .sync.aligned tcgen05 instructions)
-          const bool slow = td.diag || gcol0 + 32 > n32 || row_tail;
-          float ksum = 0.f, csum = 0.f;                       // sum of k (value) and of the centred coefficient (gradient)
-          const uint32_t tk = tmem + ((uint32_t)(ew * 32) << 16) + kTmK + (nk & 1) * 64 + h * 16;
-          const bool diag_excl = KT == 1 && td.diag;
-          const float c0k = td.kind == 0 ? c0zz : c0pz;       // (unused by the prior-prior tiles)
-          // interior tiles take the branch-free instance; diagonal / tail tiles the masked one
-          auto tile_math = [&](auto masked_c, auto grad_c) {
-            constexpr bool MASKED = decltype(masked_c)::value, GRAD = decltype(grad_c)::value;
-            // interior tiles: two elements per instruction (FADD2 / FFMA2), one running sum where one is enough
-            const uint64_t nx2 = pk2(nx, nx), sc2 = pk2(s_coef, s_coef), nc0 = pk2(-c0k, -c0k);
-            uint64_t ksum2 = pk2(0.f, 0.f), csum2 = pk2(0.f, 0.f);
+        const uint32_t sb = cnt & 1u;
+        PROF_LAP(1)
+        mbar_wait(bar(kBarSFull + sb), (cnt >> 1) & 1);
+        PROF_LAP(0)
+        TRACE(0, cnt)
+        fence_after_sync();
+        uint32_t rr[2][16];
+        // this warp's 32 columns of S; its coefficients go back into the same columns (hi: +0..15, lo: +16..31)
+        const uint32_t taddr = tmem_S + ((uint32_t)(ew * 32) << 16) + sb * (uint32_t)kCols + cg * 32;
+        tmem_ld16(taddr, rr[0]);
+        tmem_ld16(taddr + 16, rr[1]);
+        const float* ny = reinterpret_cast<const float*>(smem + L.norms + (cnt % kNormRing) * kCols * 4) + cg * 32;
+        const int gcol0 = td.jb * kCols + cg * 32;
+        // IMQ leaves the diagonal out: only the slice that meets this warp's rows has diagonal elements
+        const bool diag_excl = KT == 1 && td.diag && cg == ew;
+        // uniform across the warp (the two instances below contain .sync.aligned tcgen05 instructions)
+        const bool slow = diag_excl || gcol0 + 32 > n32 || row_tail;
+        float ksum = 0.f, csum = 0.f;                       // sum of k (value) and of the centred coefficient (gradient)
+        const float c0k = td.kind == 0 ? c0zz : c0pz;       // (unused by the prior-prior blocks)
+        // interior slices take the branch-free instance; diagonal / tail slices the masked one
+        auto tile_math = [&](auto masked_c, auto grad_c) {
+          constexpr bool MASKED = decltype(masked_c)::value, GRAD = decltype(grad_c)::value;
+          // interior: two elements per instruction (FADD2 / FFMA2), one running sum where one is enough
+          const uint64_t nx2 = pk2(nx, nx), sc2 = pk2(s_coef, s_coef), nc0 = pk2(-c0k, -c0k);
+          uint64_t ksum2 = pk2(0.f, 0.f), csum2 = pk2(0.f, 0.f);
 #pragma unroll
           for (int hf = 0; hf < 2; ++hf) {
-            tmem_ld_wait16(rr[hf]);
-            if (hf == 1) {                                    // both halves are in registers: the next GEMM1 into this
-              fence_before_sync();                            // S buffer may start
-              mbar_arrive(bar(kBarSEmpty + grp));
+            tmem_ld_wait16(rr[hf]);                           // (tcgen05.wait::ld covers both loads: S is in registers)
+            if (!GRAD && hf == 1) {                           // no coefficients to write: the buffer is free already
+              fence_before_sync();
+              __syncwarp();
+              if (lane == 0) mbar_arrive(bar(kBarKFull + sb));
             }
-            uint32_t kh[8], kl[8];                            // 16 coefficients: 8 hi + 8 lo columns of the tile in TMEM
+            uint32_t kh[8], kl[8];                            // 16 coefficients: 8 hi + 8 lo columns of bf16 pairs
 #pragma unroll
             for (int c8 = 0; c8 < 16; c8 += 8) {
               float cv[8];
@@ -704,7 +701,7 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
                     csum2 = add2(csum2, c2);
                     upk2(c2, cv[e], cv[e + 1]);
                   }
-                  if (!GRAD || KT == 1) ksum2 = add2(ksum2, k2);                  // rbf gradient tiles: sum k = sum c' + 32 c0
+                  if (!GRAD || KT == 1) ksum2 = add2(ksum2, k2);                  // rbf gradient blocks: sum k = sum c' + 32 c0
                 }
               } else {
                 const float nyv[8] = {n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, n1.z, n1.w};
@@ -732,46 +729,37 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
               }
             }
             if (GRAD) {
-              if (hf == 0) {                                  // the coefficient buffer is needed only now: G2 of the tile
-                PROF_LAP(1)                                   // two back has had the first half of this tile's math to finish
-                if (nk >= 2) mbar_wait(bar(kBarKEmpty + (nk & 1)), ((nk >> 1) - 1) & 1);
-                PROF_LAP(2)
-                TRACE(1, ns)
-              }
-              tmem_st8(tk + hf * 8, kh);
-              if (G2P == 3) tmem_st8(tk + 32 + hf * 8, kl);
+              tmem_st8(taddr + hf * 8, kh);
+              if (G2P == 3) tmem_st8(taddr + 16 + hf * 8, kl);
             }
           }
-            if constexpr (!MASKED) {
-              float a, b;
-              if (GRAD) { upk2(csum2, a, b); csum = a + b; }
-              if (GRAD && KT == 0) ksum = fmaf(32.f, c0k, csum);
-              else { upk2(ksum2, a, b); ksum = a + b; }
-            }
-          };
-          if (it.grad) {
-            if (slow) tile_math(std::true_type{}, std::true_type{}); else tile_math(std::false_type{}, std::true_type{});
-          } else {
-            if (slow) tile_math(std::true_type{}, std::false_type{}); else tile_math(std::false_type{}, std::false_type{});
+          if constexpr (!MASKED) {
+            float a, b;
+            if (GRAD) { upk2(csum2, a, b); csum = a + b; }
+            if (GRAD && KT == 0) ksum = fmaf(32.f, c0k, csum);
+            else { upk2(ksum2, a, b); ksum = a + b; }
           }
-          rs += td.kind == 1 ? -csum : csum;                  // GEMM2 applies the same sign with the negate-A bit
-          if (td.kind != run_kind) {                          // (warp-uniform, once or twice per item)
-            if (run_kind == 0) acc_zz += acc_run; else if (run_kind == 1) acc_pz += acc_run; else if (run_kind == 2) acc_pp += acc_run;
-            acc_run = 0.0;
-            run_kind = td.kind;
-          }
-          acc_run += (double)(ksum * td.weight);
-          if (it.grad) {
-            tmem_st_wait();
-            fence_before_sync();
-            mbar_arrive(bar(kBarKFull + (nk & 1)));
-          }
-          TRACE(2, ns)
+        };
+        if (it.grad) {
+          if (slow) tile_math(std::true_type{}, std::true_type{}); else tile_math(std::false_type{}, std::true_type{});
+          tmem_st_wait();
+          fence_before_sync();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar(kBarKFull + sb));
+        } else {
+          if (slow) tile_math(std::true_type{}, std::false_type{}); else tile_math(std::false_type{}, std::false_type{});
         }
-        ++ns;
-        ++live;
-        if (it.grad) ++nk;
-        ++nb;
+        rs += td.kind == 1 ? -csum : csum;                  // GEMM2 applies the same sign with the negate-A bit
+        if (td.kind != run_kind) {                          // (warp-uniform, once or twice per item)
+          flush_run();
+          run_kind = td.kind;
+        }
+        {
+          const float x = ksum * td.weight, sum = run_hi + x, bp = sum - run_hi;      // TwoSum
+          run_lo += (run_hi - (sum - bp)) + (x - bp);
+          run_hi = sum;
+        }
+        TRACE(2, cnt)
       }
       PROF_LAP(1)
       if (it.grad) {
@@ -781,7 +769,7 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
         float* op = Opart + ((size_t)q * nloc + lrow) * s.Dp;
         rspart[((size_t)q * kColGroups + cg) * nloc + lrow] = rs;
         const int c0 = cg * 32;                               // this warp's 32-column chunk of O (Dp <= 128)
-        if (live == 0) {                                      // chunk made only of column tiles beyond N
+        if (it.u1 <= it.u0) {                                 // empty chunk (cannot happen with pick_Q's Q; kept safe)
           for (int e = c0; e < c0 + 32 && e < s.Dp; ++e) op[e] = 0.f;
           continue;
         }
@@ -803,14 +791,15 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
           }
         }
         fence_before_sync();
-        mbar_arrive(bar(kBarOEmpty));
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar(kBarOEmpty));
         ++n_grad_items;
       }
       PROF_LAP(3)
     }
-    PROF_OUT("epilogue wait_s_full/work/wait_k_empty/item_end", threadIdx.x == 0)
-    TRACE_OUT("epi s_full/k_empty/done", 3, threadIdx.x == 0 || threadIdx.x == 256)
-    if (run_kind == 0) acc_zz += acc_run; else if (run_kind == 1) acc_pz += acc_run; else if (run_kind == 2) acc_pp += acc_run;
+    PROF_OUT("epilogue wait_s_full/work/-/item_end", threadIdx.x == 0)
+    TRACE_OUT("epi s_full/-/done", 3, threadIdx.x == 0)
+    flush_run();
     if (KT == 1) { acc_zz *= (double)s.C; acc_pz *= (double)s.C; acc_pp *= (double)s.C; }   // IMQ sums were of k / C
     // per-CTA sums (fixed order) -> workspace
     double* red = reinterpret_cast<double*>(smem + L.red);
@@ -1028,7 +1017,7 @@ __global__ void mmd_diag_kernel(const MmdStats* __restrict__ st, float* __restri
 }
 
 int chain_limit(int kernel_type) {
-  // longest accumulation chain in 64-column tiles, 0 = none.  Centred coefficients make the RBF chain harmless; the IMQ
+  // longest accumulation chain in 64-column units (two per block), 0 = none.  Centred coefficients make the RBF chain harmless; the IMQ
   // coefficients spread ~8 % around c0 at the benchmark size, so its chains are still cut (VK_MMD_CHAIN overrides both).
   static const int env = [] { const char* e = getenv("VK_MMD_CHAIN"); return e ? atoi(e) : -1; }();
   if (env >= 0) return env;
@@ -1038,7 +1027,6 @@ int chain_limit(int kernel_type) {
 void make_shape(int64_t N, int64_t D, int kernel_type, float z_var, int64_t row_begin, int64_t row_end, MmdShape& s) {
   s.N = N; s.D = (int)D; s.Dp = rup((int)D, 16); s.nkc = s.Dp / 8;
   s.T = (int)((N + kRows - 1) / kRows);
-  s.lz = (int)((N + kCols - 1) / kCols);
   s.rb0 = (int)(row_begin / kRows);
   s.rb1 = (int)((row_end + kRows - 1) / kRows);
   s.Q = pick_Q(s.T, s.rb1 - s.rb0, chain_limit(kernel_type));
