@@ -94,6 +94,7 @@ struct MmdShape {
   int T;                // 128-row tiles of the full matrix
   int rb0, rb1;         // row-block range owned by this call
   int Q;                // column chunks per row block (gradient items)
+  int P;                // pieces of the prior-prior item of a row block
   int kernel_type;      // 0 rbf, 1 imq
   int g1p, g2p;         // tensor passes of the distance GEMM (3: both operands hi/lo, 2: row operand hi/lo, 1) / gradient GEMM (3, 1)
   float a_exp;          // rbf: -log2(e) / (2 D^2 z_var)
@@ -337,11 +338,12 @@ mmd_pack_norm_kernel(const float* __restrict__ Z, const float* __restrict__ P, c
 }
 
 // ---- work items ---------------------------------------------------------------------------------------------
-// Item order: for each owned row block i: Q gradient items (i, q), then the prior-prior item of row block i.
+// Item order: for each owned row block i: Q gradient items (i, q), then the P prior-prior pieces of row block i.
 // The column sequence of an item is made of 128-column blocks; a block that reaches beyond N is not skipped but takes
 // the masked epilogue (its operand rows and norms are zero-filled by the pack kernel).
 struct Item {
   int i;          // row block (global index)
+  int q;          // item index within the row block: [0, Q) gradient chunks, [Q, Q + P) prior-prior pieces
   int grad;       // 1: rows = z, columns = [z blocks | prior blocks] chunk q ; 0: rows = prior, circulant half of prior
   int u0, u1;     // block sequence range
 };
@@ -354,9 +356,10 @@ struct TileD {
 };
 __device__ __forceinline__ Item get_item(const MmdShape& s, int idx) {
   Item it;
-  const int per = s.Q + 1;
+  const int per = s.Q + s.P;
   it.i = s.rb0 + idx / per;
   const int q = idx % per;
+  it.q = q;
   if (q < s.Q) {
     it.grad = 1;
     const int n = 2 * s.T, len = (n + s.Q - 1) / s.Q;
@@ -364,9 +367,13 @@ __device__ __forceinline__ Item get_item(const MmdShape& s, int idx) {
     it.u1 = it.u0 + len < n ? it.u0 + len : n;
     if (it.u0 > n) it.u0 = n;
   } else {
+    // prior-prior: the circulant half of this row block, cut into P pieces about as long as a gradient item so that the
+    // static round-robin schedule deals equal work (one piece of T/2 + 1 blocks was twice a gradient item at Q = 8)
     it.grad = 0;
-    it.u0 = 0;
-    it.u1 = (s.T % 2 == 0) ? s.T / 2 + 1 : (s.T + 1) / 2;
+    const int noff = (s.T % 2 == 0) ? s.T / 2 + 1 : (s.T + 1) / 2, len = (noff + s.P - 1) / s.P;
+    it.u0 = (q - s.Q) * len;
+    it.u1 = it.u0 + len < noff ? it.u0 + len : noff;
+    if (it.u0 > noff) it.u0 = noff;
   }
   return it;
 }
@@ -565,7 +572,8 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
             const uint64_t db_hi = smem_desc(b_hi, 128, b_lbo), db_lo = smem_desc(b_hi + b_half, 128, b_lbo);
 #pragma unroll
             for (int pass = 0; pass < G2P; ++pass) {
-              const uint32_t lo_off = (G2P == 3 && pass == 0) ? 16u : 0u;
+              // G2P == 3: lo*hi, hi*lo, hi*hi ; G2P == 2: lo*hi, hi*hi (coefficient split, column operand plain bf16)
+              const uint32_t lo_off = (G2P >= 2 && pass == 0) ? 16u : 0u;
               uint64_t db = (G2P == 3 && pass == 1) ? db_lo : db_hi;
 #pragma unroll
               for (int k = 0; k < kCols / 16; ++k) {
@@ -723,14 +731,14 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
               if (GRAD) {
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
-                  if (G2P == 3) split_pair(cv[2 * e], cv[2 * e + 1], kh[(c8 >> 1) + e], kl[(c8 >> 1) + e]);
+                  if (G2P >= 2) split_pair(cv[2 * e], cv[2 * e + 1], kh[(c8 >> 1) + e], kl[(c8 >> 1) + e]);
                   else kh[(c8 >> 1) + e] = pack_bf16x2(cv[2 * e], cv[2 * e + 1]);
                 }
               }
             }
             if (GRAD) {
               tmem_st8(taddr + hf * 8, kh);
-              if (G2P == 3) tmem_st8(taddr + 16 + hf * 8, kl);
+              if (G2P >= 2) tmem_st8(taddr + 16 + hf * 8, kl);
             }
           }
           if constexpr (!MASKED) {
@@ -763,7 +771,7 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
       }
       PROF_LAP(1)
       if (it.grad) {
-        const int q = (idx % (s.Q + 1));
+        const int q = it.q;
         const size_t lrow = (size_t)(it.i - s.rb0) * kRows + t;
         const size_t nloc = (size_t)(s.rb1 - s.rb0) * kRows;
         float* op = Opart + ((size_t)q * nloc + lrow) * s.Dp;
@@ -1030,6 +1038,12 @@ void make_shape(int64_t N, int64_t D, int kernel_type, float z_var, int64_t row_
   s.rb0 = (int)(row_begin / kRows);
   s.rb1 = (int)((row_end + kRows - 1) / kRows);
   s.Q = pick_Q(s.T, s.rb1 - s.rb0, chain_limit(kernel_type));
+  {
+    const int len = (2 * s.T + s.Q - 1) / s.Q, noff = (s.T % 2 == 0) ? s.T / 2 + 1 : (s.T + 1) / 2;
+    s.P = (noff + len / 2) / len;                    // nearest number of gradient-item lengths
+    if (s.P < 1) s.P = 1;
+    if (s.P > noff) s.P = noff;
+  }
   s.kernel_type = kernel_type; s.g1p = 3; s.g2p = 3;
   const double sp = 2.0 * (double)D * (double)D * (double)z_var;
   s.a_exp = (float)(-1.4426950408889634 / sp);
@@ -1042,7 +1056,7 @@ template <int G1P, int G2P>
 int launch_sweep(const float* z, const float* prior, const MmdShape& s, const MmdWs& w, uint8_t* ws, double* sums_out,
                  float* grad_unscaled, int run_if, cudaStream_t st) {
   const MmdSmem L = mmd_smem(s.Dp);
-  const int n_items = (s.rb1 - s.rb0) * (s.Q + 1);
+  const int n_items = (s.rb1 - s.rb0) * (s.Q + s.P);
   const int grid = n_items < sm_count() ? n_items : sm_count();
   auto kern = s.kernel_type == 0 ? mmd_main_kernel<G1P, G2P, 0> : mmd_main_kernel<G1P, G2P, 1>;
   static bool attr_done[2] = {false, false};                  // once per instantiation and kernel type
@@ -1068,6 +1082,9 @@ int dispatch_sweep(int g1p, int g2p, const float* z, const float* prior, MmdShap
   s.g1p = g1p; s.g2p = g2p;
   if (g1p == 3 && g2p == 3) return launch_sweep<3, 3>(z, prior, s, w, ws, sums_out, grad_unscaled, run_if, st);
   if (g1p == 2 && g2p == 1) return launch_sweep<2, 1>(z, prior, s, w, ws, sums_out, grad_unscaled, run_if, st);
+  if (g1p == 2 && g2p == 2) return launch_sweep<2, 2>(z, prior, s, w, ws, sums_out, grad_unscaled, run_if, st);
+  if (g1p == 3 && g2p == 1) return launch_sweep<3, 1>(z, prior, s, w, ws, sums_out, grad_unscaled, run_if, st);
+  if (g1p == 3 && g2p == 2) return launch_sweep<3, 2>(z, prior, s, w, ws, sums_out, grad_unscaled, run_if, st);
   return launch_sweep<1, 1>(z, prior, s, w, ws, sums_out, grad_unscaled, run_if, st);
 }
 
@@ -1103,7 +1120,8 @@ extern "C" int vk_mmd_fwd(const float* z, const float* prior, int64_t N, int64_t
   VK_REQUIRE(N >= 1 && D >= 1, VK_ERR_BAD_ARG, "mmd: empty z [%lld,%lld]", (long long)N, (long long)D);
   VK_REQUIRE(N <= (int64_t)1 << 24, VK_ERR_UNSUPPORTED, "mmd: N=%lld too large", (long long)N);
   VK_REQUIRE(kernel_type == 0 || kernel_type == 1, VK_ERR_BAD_ARG, "mmd: unknown kernel type %d", kernel_type);
-  VK_REQUIRE(passes >= 0 && passes <= 3, VK_ERR_BAD_ARG, "mmd: passes must be 0 (auto), 1, 2 or 3");
+  VK_REQUIRE((passes >= 0 && passes <= 3) || passes == 22 || passes == 31 || passes == 32, VK_ERR_BAD_ARG,
+             "mmd: passes must be 0 (auto), 1, 2, 3 or one of the explicit pairs 22, 31, 32");
   VK_REQUIRE(row_begin >= 0 && row_begin < row_end && row_end <= N && row_begin % kRows == 0 &&
              (row_end % kRows == 0 || row_end == N), VK_ERR_BAD_ARG,
              "mmd: row range [%lld,%lld) must be 128-aligned inside [0,%lld)", (long long)row_begin, (long long)row_end, (long long)N);
@@ -1157,6 +1175,7 @@ extern "C" int vk_mmd_fwd(const float* z, const float* prior, int64_t N, int64_t
   bool verify = false;
   if (passes == 1) { g1p = 1; g2p = 1; }
   else if (passes == 2) { g1p = 2; g2p = 1; }
+  else if (passes > 3) { g1p = passes / 10; g2p = passes % 10; }
   else if (passes == 0 && N >= kAutoMinN && kernel_type == 0) {
     // RBF at large N: |dk/dd^2| = k / (2 D^2 z_var) makes k insensitive to the bf16 rounding of the COLUMN operand (an
     // error that is random over the columns and averages out of a row's gradient) and the centred coefficients are tiny,

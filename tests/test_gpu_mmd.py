@@ -272,7 +272,7 @@ def test_mmd_full_size_vs_fp64_blocks(vk, kt):
     g64, tot, ref_mmd = fp64_blocks(z, p, kt, z_var, reg)
     ref_terms = [torch.tensor(t, dtype=torch.float64) for t in tot]
     den = g64.abs().max()
-    for passes in (0, 3, 2, 1):
+    for passes in (0, 3, 2, 1, 22, 31, 32):       # two digits: explicit (distance GEMM, gradient GEMM) pass pair
         mmd, terms, grad, diag = run_mode(F, z, p, reg, kt, z_var, passes)
         e = ((grad.double() - g64).abs().max() / den).item()
         et = max(abs(a - b) / abs(b) for a, b in zip(terms.cpu().tolist(), tot))
