@@ -67,12 +67,11 @@ constexpr int kMmdThreads = 32 * 18;  // warps 0-15 epilogue, warp 16 TMA, warp 
 // of a limited chain are summed in fp32 round-to-nearest by the finalize kernel.
 constexpr int kMaxQ = 64, kBalanceQ = 8;
 constexpr int64_t kMaxGradItems = 65536;
-// rows / column splits of the verification sample (auto mode).  16 rows x 128 dims = 2048 gradient entries against all N
-// columns: the rounding error of a reduced-precision sweep is statistical and spread evenly over the rows (measured
-// r02b/r02g: the sample's error tracks the full gradient's within 2x on every data set tried), and the two SIMT passes
-// cost time in proportion to the rows (32 rows: 1.0 ms of an 8.3 ms call at N = 65 536).  16 x 128 splits = 2048 CTAs,
-// ~4.6 waves at 3 CTAs per SM (512 CTAs = 1.15 waves cost two).
-constexpr int kSampleRows = 16, kSampleSplits = 128;
+// rows of the verification sample (auto mode).  16 rows x 128 dims = 2048 gradient entries against all N columns: the
+// rounding error of a reduced-precision sweep is statistical and spread evenly over the rows (measured r02b/r02g: the
+// sample's error tracks the full gradient's within 2x on every data set tried).  mmd_sample_kernel takes them eight at a
+// time in registers (r02v: 2 x 248 us for the one-row-per-CTA version it replaced).
+constexpr int kSampleRows = 16;
 constexpr float kVerifyBudget = 4e-6f;                  // accepted sample error relative to max |grad| (north star: 1e-5)
 constexpr int64_t kAutoMinN = 8192;                     // below this the parity sweep costs < 0.3 ms: nothing to gain
 
@@ -874,13 +873,12 @@ __global__ void mmd_finalize_kernel(const float* __restrict__ Z, const float* __
 }
 
 // ---- SIMT rows: the reference's literal (x - y)^2 form, float64 accumulation --------------------------------------
-// One CTA (8 warps) per row; a warp takes one column at a time, lanes over latent dims.  Used (a) for the sampled check of
-// a reduced-precision tensor sweep (few rows, column range split over gridDim.y, atomics into MmdStats::gref) and (b) as
-// the whole path for latent dims > 128 (every row, gridDim.y == 1, deterministic).
+// One CTA (8 warps) per row; a warp takes one column at a time, lanes over latent dims.  The whole path for latent dims
+// > 128 (every row, gridDim.y == 1, deterministic); the sampled check of the tensor sweeps is mmd_sample_kernel below.
 //   X rows, Y columns [N, D]; rows i = row0 + blockIdx.x * row_step; sign +1 / -1 of the gradient contribution;
 //   gacc [rows, D] float64 accumulators (NULL: no gradient), krow [rows]: each row's kernel sum (NULL: none; needs
 //   gridDim.y == 1).
-template <int KT, bool REG>
+template <int KT>
 __global__ void __launch_bounds__(256)
 mmd_simt_rows_kernel(const float* __restrict__ X, const float* __restrict__ Y, int64_t N, int D, int64_t row0,
                      int64_t row_step, int64_t n_rows, float a_exp, float Ceps, float C, double sign,
@@ -894,41 +892,7 @@ mmd_simt_rows_kernel(const float* __restrict__ X, const float* __restrict__ Y, i
   double ks = 0.0;
   const int64_t span = (N + gridDim.y - 1) / gridDim.y;
   const int64_t j0 = (int64_t)blockIdx.y * span, j1 = j0 + span < N ? j0 + span : N;
-  if (REG) {
-    // D <= 128: the row and four columns at a time live in registers (independent loads and reductions in flight)
-    float xr[4];
-    double ar[4] = {0.0, 0.0, 0.0, 0.0};
-#pragma unroll
-    for (int k = 0; k < 4; ++k) xr[k] = lane + 32 * k < D ? xi[lane + 32 * k] : 0.f;
-    for (int64_t j = j0 + warp * 4; j < j1; j += 32) {
-      float df[4][4], s2[4];
-#pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        const bool ok = j + c < j1;
-        s2[c] = 0.f;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const int d = lane + 32 * k;
-          df[c][k] = (ok && d < D) ? xr[k] - __ldg(Y + (j + c) * D + d) : 0.f;
-          s2[c] = fmaf(df[c][k], df[c][k], s2[c]);
-        }
-      }
-#pragma unroll
-      for (int c = 0; c < 4; ++c) s2[c] = warp_sum(s2[c]);
-#pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        float k, coef;
-        if (KT == 0) { k = exp2f(a_exp * s2[c]); coef = k; }
-        else { const float r = 1.0f / (Ceps + s2[c]); k = C * r; coef = r * r; }
-        if (j + c >= j1 || (KT == 1 && j + c == i)) { k = 0.f; coef = 0.f; }     // imq: no diagonal in any term
-        ks += (double)k;
-#pragma unroll
-        for (int kk = 0; kk < 4; ++kk) ar[kk] += (double)(coef * df[c][kk]);
-      }
-    }
-#pragma unroll
-    for (int k = 0; k < 4; ++k) if (lane + 32 * k < D) acc[lane + 32 * k] = ar[k];
-  } else {
+  {
     for (int d = lane; d < D; d += 32) acc[d] = 0.0;
     for (int64_t j = j0 + warp; j < j1; j += 8) {
       const float* yj = Y + j * D;
@@ -959,6 +923,94 @@ mmd_simt_rows_kernel(const float* __restrict__ X, const float* __restrict__ Y, i
     double t = 0.0;
     for (int w = 0; w < 8; ++w) t += kred[w];
     krow[blockIdx.x] = t;
+  }
+}
+
+// ---- sampled check of a reduced-precision sweep: float64 gradient sums of a few rows against ALL columns -----------
+// A CTA keeps kSampleGroup sample rows in registers and walks a column range, so every column is read once per row group
+// (the first version gave a CTA one row: 16 x 33.5 MB of L2 reads per launch and 32 lanes computing the same exponential).
+// A warp takes four columns at a time, lanes over latent dims: the 8 x 4 squared distances of a step are summed with one
+// transposing butterfly (31 shuffles; lane q = 4 r + c ends with pair (row r, column c)), that lane alone evaluates the
+// kernel, and the coefficients go back to every lane by shuffle for the float64 accumulation of coef * (x - y).
+// Terms in fp32 exactly as the SIMT path computes them (literal (x - y)^2 form), sums in float64, atomics into gref.
+constexpr int kSampleGroup = 8;
+template <int KT>
+__global__ void __launch_bounds__(256)
+mmd_sample_kernel(const float* __restrict__ X, const float* __restrict__ Y, int64_t N, int D, int64_t row0,
+                  int64_t row_step, int n_rows, float a_exp, float Ceps, double sign, double* __restrict__ gref) {
+  constexpr int NR = kSampleGroup;
+  __shared__ double sh[NR][128];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int rbase = blockIdx.y * NR;
+  float xr[NR][4];
+  double ar[NR][4];
+#pragma unroll
+  for (int r = 0; r < NR; ++r) {
+    const bool rok = rbase + r < n_rows;
+    const float* xi = X + (row0 + (int64_t)(rbase + r) * row_step) * D;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      xr[r][k] = (rok && lane + 32 * k < D) ? xi[lane + 32 * k] : 0.f;
+      ar[r][k] = 0.0;
+    }
+  }
+  const int my_r = lane >> 2, my_c = lane & 3;                 // the pair this lane finishes
+  const bool my_rok = rbase + my_r < n_rows;
+  const int64_t my_i = row0 + (int64_t)(rbase + my_r) * row_step;
+  const int64_t span = (N + gridDim.x - 1) / gridDim.x;
+  const int64_t j0 = (int64_t)blockIdx.x * span, j1 = j0 + span < N ? j0 + span : N;
+  for (int64_t j = j0 + warp * 4; j < j1; j += 32) {
+    float y[4][4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c)
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        y[c][k] = (j + c < j1 && lane + 32 * k < D) ? __ldg(Y + (j + c) * D + lane + 32 * k) : 0.f;
+    float v[32];
+#pragma unroll
+    for (int r = 0; r < NR; ++r)
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        float s2 = 0.f;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { const float df = xr[r][k] - y[c][k]; s2 = fmaf(df, df, s2); }
+        v[r * 4 + c] = s2;
+      }
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) {
+      const bool up = lane & o;
+#pragma unroll
+      for (int t = 0; t < o; ++t) v[t] = (up ? v[t + o] : v[t]) + __shfl_xor_sync(0xFFFFFFFFu, up ? v[t] : v[t + o], o);
+    }
+    float coef;
+    if (KT == 0) coef = exp2f(a_exp * v[0]);
+    else { const float rr = 1.0f / (Ceps + v[0]); coef = rr * rr; }
+    if (!my_rok || j + my_c >= j1 || (KT == 1 && j + my_c == my_i)) coef = 0.f;      // imq: no diagonal in any term
+#pragma unroll
+    for (int r = 0; r < NR; ++r)
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const float cf = __shfl_sync(0xFFFFFFFFu, coef, r * 4 + c);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) ar[r][k] += (double)(cf * (xr[r][k] - y[c][k]));
+      }
+  }
+  // the eight warps add their sums in turn (fixed order), then one atomic per (row, dim) and CTA
+  for (int w = 0; w < 8; ++w) {
+    if (warp == w) {
+#pragma unroll
+      for (int r = 0; r < NR; ++r)
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          double* p = &sh[r][lane + 32 * k];
+          *p = (w == 0 ? 0.0 : *p) + ar[r][k];
+        }
+    }
+    __syncthreads();
+  }
+  for (int t = threadIdx.x; t < NR * 128; t += blockDim.x) {
+    const int r = t >> 7, d = t & 127;
+    if (rbase + r < n_rows && d < D) atomicAdd(gref + (size_t)(rbase + r) * D + d, sign * sh[r][d]);
   }
 }
 
@@ -1140,7 +1192,7 @@ extern "C" int vk_mmd_fwd(const float* z, const float* prior, int64_t N, int64_t
     double* gacc = (double*)(ws + w.gacc);
     cudaMemsetAsync(gacc, 0, (size_t)rows * D * sizeof(double), st);
     const size_t shb = ((size_t)8 * D + 8) * sizeof(double);
-    auto kern = kernel_type == 0 ? mmd_simt_rows_kernel<0, false> : mmd_simt_rows_kernel<1, false>;
+    auto kern = kernel_type == 0 ? mmd_simt_rows_kernel<0> : mmd_simt_rows_kernel<1>;
     if (shb > 48 * 1024 && cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shb) != cudaSuccess)
       return check_launch("mmd_fwd (SIMT shared memory attribute)");
     const dim3 grid((unsigned)rows, 1);
@@ -1196,11 +1248,10 @@ extern "C" int vk_mmd_fwd(const float* z, const float* prior, int64_t N, int64_t
     if (want > kSampleRows) want = kSampleRows;
     const int n_rows = (int)(nloc < want ? nloc : want);
     const int64_t row_step = nloc / n_rows;
-    const size_t shb = ((size_t)8 * D + 8) * sizeof(double);
-    auto kern = kernel_type == 0 ? mmd_simt_rows_kernel<0, true> : mmd_simt_rows_kernel<1, true>;
-    const dim3 grid((unsigned)n_rows, kSampleSplits);
-    kern<<<grid, 256, shb, st>>>(z, z, N, (int)D, row_begin, row_step, n_rows, s.a_exp, s.Ceps, s.C, 1.0, stats->gref, true, nullptr);
-    kern<<<grid, 256, shb, st>>>(z, prior, N, (int)D, row_begin, row_step, n_rows, s.a_exp, s.Ceps, s.C, -1.0, stats->gref, true, nullptr);
+    auto kern = kernel_type == 0 ? mmd_sample_kernel<0> : mmd_sample_kernel<1>;
+    const dim3 grid((unsigned)(sm_count() * 2), (unsigned)((n_rows + kSampleGroup - 1) / kSampleGroup));
+    kern<<<grid, 256, 0, st>>>(z, z, N, (int)D, row_begin, row_step, n_rows, s.a_exp, s.Ceps, 1.0, stats->gref);
+    kern<<<grid, 256, 0, st>>>(z, prior, N, (int)D, row_begin, row_step, n_rows, s.a_exp, s.Ceps, -1.0, stats->gref);
     mmd_verify_kernel<<<1, 256, 0, st>>>(grad_unscaled, (int)D, row_step, n_rows, s.dk_scale, kVerifyBudget, stats);
     rc = check_launch("mmd_verify");
     if (rc != VK_OK) return rc;
