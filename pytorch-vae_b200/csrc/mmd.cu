@@ -65,7 +65,7 @@ constexpr int kMmdThreads = 32 * 18;  // warps 0-15 epilogue, warp 16 TMA, warp 
 // gradient's maximum at N = 65 536 with one 683-tile chain, 1.8e-5 with 32-tile chains at 17 ms per step).  Round 2
 // accumulates CENTRED coefficients (see the head of the file), so the RBF needs no chain limit at all; the partial tiles
 // of a limited chain are summed in fp32 round-to-nearest by the finalize kernel.
-constexpr int kMaxQ = 64, kBalanceQ = 8;
+constexpr int kMaxQ = 64, kBalanceQ = 16;
 constexpr int64_t kMaxGradItems = 65536;
 // rows of the verification sample (auto mode).  16 rows x 128 dims = 2048 gradient entries against all N columns: the
 // rounding error of a reduced-precision sweep is statistical and spread evenly over the rows (measured r02b/r02g: the
@@ -94,6 +94,7 @@ struct MmdShape {
   int rb0, rb1;         // row-block range owned by this call
   int Q;                // column chunks per row block (gradient items)
   int P;                // pieces of the prior-prior item of a row block
+  int qmajor;           // item enumeration: 1 q-major, 0 row-block-major
   int kernel_type;      // 0 rbf, 1 imq
   int g1p, g2p;         // tensor passes of the distance GEMM (3: both operands hi/lo, 2: row operand hi/lo, 1) / gradient GEMM (3, 1)
   float a_exp;          // rbf: -log2(e) / (2 D^2 z_var)
@@ -133,19 +134,67 @@ inline int q_cap(int row_blocks) {
   if (c < kBalanceQ) c = kBalanceQ;
   return (int)c;
 }
-// chain_tiles: longest accumulation chain in 64-column units (0 = no limit); the sequence of a gradient item is made of
-// 2 T blocks of 128 columns ([z blocks | prior blocks])
-inline int pick_Q(int T, int row_blocks, int chain_tiles) {
-  // aim for >= 8 gradient items per SM so the static round-robin schedule balances
-  int q = (sm_count() * 8 + row_blocks - 1) / row_blocks;
-  if (q > kBalanceQ) q = kBalanceQ;
-  if (chain_tiles > 0) {
-    const int chain = (4 * T + chain_tiles - 1) / chain_tiles;
-    if (chain > q) q = chain;
+// pieces of a row block's prior-prior item: the nearest number of gradient-item lengths
+inline int pick_P(int T, int Q) {
+  const int len = (2 * T + Q - 1) / Q, noff = (T % 2 == 0) ? T / 2 + 1 : (T + 1) / 2;
+  int P = (noff + len / 2) / len;
+  if (P < 1) P = 1;
+  if (P > noff) P = noff;
+  return P;
+}
+// Makespan (in 128-column blocks) of the static schedule: items enumerated q-major, dealt round-robin to the grid.  An
+// item boundary costs about as much as kItemCost blocks (row operand refill, O read-out, pipeline drain and restart:
+// r02x sweep, ~18k cycles), a prior-prior block ~3/4 of a gradient block (no gradient GEMM).
+constexpr int kItemCost = 10;
+inline int64_t schedule_makespan(int T, int row_blocks, int Q) {
+  const int P = pick_P(T, Q), n = 2 * T, len = (n + Q - 1) / Q;
+  const int noff = (T % 2 == 0) ? T / 2 + 1 : (T + 1) / 2, plen = (noff + P - 1) / P;
+  const int64_t items = (int64_t)row_blocks * (Q + P);
+  const int grid = (int)(items < sm_count() ? items : sm_count());
+  int64_t worst = 0;
+  for (int b = 0; b < grid; ++b) {
+    int64_t load = 0;
+    for (int64_t idx = b; idx < items; idx += grid) {
+      const int q = (int)(idx / row_blocks);
+      int blocks;
+      if (q < Q) { const int u0 = q * len; blocks = (u0 + len < n ? u0 + len : n) - u0; if (blocks < 0) blocks = 0; load += 4 * (blocks + kItemCost); }
+      else { const int u0 = (q - Q) * plen; blocks = (u0 + plen < noff ? u0 + plen : noff) - u0; if (blocks < 0) blocks = 0; load += 3 * blocks + 4 * kItemCost; }
+    }
+    if (load > worst) worst = load;
   }
-  if (q > q_cap(row_blocks)) q = q_cap(row_blocks);
-  if (q > 2 * T) q = 2 * T;
-  if (q < 1) q = 1;
+  return worst;
+}
+// chain_tiles: longest accumulation chain in 64-column units (0 = no limit); the sequence of a gradient item is made of
+// 2 T blocks of 128 columns ([z blocks | prior blocks]).  Q = the chunk count in [chain bound, kBalanceQ] whose static
+// schedule has the shortest makespan (one GPU, N = 65 536: every Q from 3 to 12 measures the same within noise; a shard
+// of 64 row blocks on 148 SMs is where the quantisation bites: 640 items are 5 for some CTAs and 4 for others).
+inline int pick_Q(int T, int row_blocks, int chain_tiles) {
+  static const int q_env = [] { const char* e = getenv("VK_MMD_Q"); return e ? atoi(e) : 0; }();
+  int qmin = 1, qmax = kBalanceQ;
+  if (chain_tiles > 0) {
+    qmin = (4 * T + chain_tiles - 1) / chain_tiles;
+    if (qmin > q_cap(row_blocks)) qmin = q_cap(row_blocks);
+    if (qmax < qmin) qmax = qmin;
+  }
+  if (qmax > 2 * T) qmax = 2 * T;
+  if (qmin > qmax) qmin = qmax;
+  if (qmin < 1) qmin = 1;
+  // one-entry memo: a training loop calls with the same shape every step
+  static thread_local int mT = -1, mR = -1, mC = -1, mQ = 1;
+  int q;
+  if (q_env > 0) q = q_env < qmin ? qmin : q_env;
+  else if (mT == T && mR == row_blocks && mC == chain_tiles) q = mQ;
+  else {
+    q = qmin;
+    int64_t best = -1;
+    for (int c = qmin; c <= qmax; ++c) {
+      const int len = (2 * T + c - 1) / c;
+      if ((2 * T + len - 1) / len != c) continue;           // would leave an empty chunk
+      const int64_t m = schedule_makespan(T, row_blocks, c);
+      if (best < 0 || m < best) { best = m; q = c; }
+    }
+    mT = T; mR = row_blocks; mC = chain_tiles; mQ = q;
+  }
   const int n = 2 * T, len = (n + q - 1) / q;
   return (n + len - 1) / len;                 // no empty chunk
 }
@@ -337,7 +386,7 @@ mmd_pack_norm_kernel(const float* __restrict__ Z, const float* __restrict__ P, c
 }
 
 // ---- work items ---------------------------------------------------------------------------------------------
-// Item order: for each owned row block i: Q gradient items (i, q), then the P prior-prior pieces of row block i.
+// Items: Q gradient chunks and P prior-prior pieces per owned row block, enumerated q-major (see get_item).
 // The column sequence of an item is made of 128-column blocks; a block that reaches beyond N is not skipped but takes
 // the masked epilogue (its operand rows and norms are zero-filled by the pack kernel).
 struct Item {
@@ -355,9 +404,13 @@ struct TileD {
 };
 __device__ __forceinline__ Item get_item(const MmdShape& s, int idx) {
   Item it;
-  const int per = s.Q + s.P;
-  it.i = s.rb0 + idx / per;
-  const int q = idx % per;
+  // q-major: consecutive items are the same column chunk of consecutive row blocks, so (a) a CTA's items, a grid stride
+  // apart, run through every chunk kind in proportion -- with the row-block-major order and a grid that is a multiple
+  // of Q + P every CTA drew one kind only (r02w: 8 % imbalance at one GPU, 16 % at eight) -- and (b) the CTAs of a
+  // wave read the same column stages (L2); the cheaper prior-prior pieces come last
+  const int nrb = s.rb1 - s.rb0;
+  const int q = s.qmajor ? idx / nrb : idx % (s.Q + s.P);
+  it.i = s.rb0 + (s.qmajor ? idx % nrb : idx / (s.Q + s.P));
   it.q = q;
   if (q < s.Q) {
     it.grad = 1;
@@ -1076,26 +1129,29 @@ __global__ void mmd_diag_kernel(const MmdStats* __restrict__ st, float* __restri
   diag[3] = __uint_as_float(st->gmax_bits);
 }
 
-int chain_limit(int kernel_type) {
-  // longest accumulation chain in 64-column units (two per block), 0 = none.  Centred coefficients make the RBF chain harmless; the IMQ
-  // coefficients spread ~8 % around c0 at the benchmark size, so its chains are still cut (VK_MMD_CHAIN overrides both).
+int chain_limit(int kernel_type, int64_t D) {
+  // longest accumulation chain in 64-column units (two per block), 0 = none.  The tcgen05 accumulator truncates, a bias
+  // ~ chain length x magnitude of the accumulated CENTRED coefficients, i.e. x the relative spread of the kernel over the
+  // batch: IMQ ~8 % at the benchmark size -> 128; RBF ~ sqrt(2) / (D^1.5 z_var): 1/2000 at D = 128 (no limit needed),
+  // but 1 % at D = 16 and 25 % at D = 2 (N = 9000, D = 2 in the parity sweep: 6.4e-6 with 36-unit chains, 1.5e-5 with
+  // 142) -> narrow latent dims get short chains.  VK_MMD_CHAIN overrides.
   static const int env = [] { const char* e = getenv("VK_MMD_CHAIN"); return e ? atoi(e) : -1; }();
   if (env >= 0) return env;
-  return kernel_type == 0 ? 0 : 128;
+  // (IMQ: the spread of d^2 relative to C + d^2 goes like sqrt(2 / D): N = 9000, D = 2 measures 6.9e-6 with 36-unit
+  // chains and 1.55e-5 with 95)
+  if (kernel_type != 0) return D <= 4 ? 16 : D <= 16 ? 32 : D <= 64 ? 64 : 128;
+  return D <= 4 ? 16 : D <= 16 ? 64 : D <= 32 ? 128 : 0;
 }
+constexpr int kFallbackChain = 32;      // the parity sweep behind a failed sample check: short chains, it is the slow path anyway
 
 void make_shape(int64_t N, int64_t D, int kernel_type, float z_var, int64_t row_begin, int64_t row_end, MmdShape& s) {
   s.N = N; s.D = (int)D; s.Dp = rup((int)D, 16); s.nkc = s.Dp / 8;
   s.T = (int)((N + kRows - 1) / kRows);
   s.rb0 = (int)(row_begin / kRows);
   s.rb1 = (int)((row_end + kRows - 1) / kRows);
-  s.Q = pick_Q(s.T, s.rb1 - s.rb0, chain_limit(kernel_type));
-  {
-    const int len = (2 * s.T + s.Q - 1) / s.Q, noff = (s.T % 2 == 0) ? s.T / 2 + 1 : (s.T + 1) / 2;
-    s.P = (noff + len / 2) / len;                    // nearest number of gradient-item lengths
-    if (s.P < 1) s.P = 1;
-    if (s.P > noff) s.P = noff;
-  }
+  s.Q = pick_Q(s.T, s.rb1 - s.rb0, chain_limit(kernel_type, D));
+  { static const int qm = [] { const char* e = getenv("VK_MMD_QMAJOR"); return e ? atoi(e) : 1; }(); s.qmajor = qm; }
+  s.P = pick_P(s.T, s.Q);
   s.kernel_type = kernel_type; s.g1p = 3; s.g2p = 3;
   const double sp = 2.0 * (double)D * (double)D * (double)z_var;
   s.a_exp = (float)(-1.4426950408889634 / sp);
@@ -1255,7 +1311,14 @@ extern "C" int vk_mmd_fwd(const float* z, const float* prior, int64_t N, int64_t
     mmd_verify_kernel<<<1, 256, 0, st>>>(grad_unscaled, (int)D, row_step, n_rows, s.dk_scale, kVerifyBudget, stats);
     rc = check_launch("mmd_verify");
     if (rc != VK_OK) return rc;
-    rc = dispatch_sweep(3, 3, z, prior, s, w, ws, sums_out, grad_unscaled, 1, st);      // runs only if the check failed
+    MmdShape sf = s;                                      // the parity sweep that runs only if the check failed
+    const int ch = chain_limit(kernel_type, D);
+    sf.Q = pick_Q(s.T, s.rb1 - s.rb0, ch > 0 && ch < kFallbackChain ? ch : kFallbackChain);
+    sf.P = pick_P(s.T, sf.Q);
+    const MmdWs wf = mmd_ws(N, (int)D, s.rb1 - s.rb0, sf.Q);
+    VK_REQUIRE(workspace_bytes >= (int64_t)wf.total, VK_ERR_WORKSPACE, "mmd_fwd: workspace %lld < %lld (parity sweep)",
+               (long long)workspace_bytes, (long long)wf.total);
+    rc = dispatch_sweep(3, 3, z, prior, sf, wf, ws, sums_out, grad_unscaled, 1, st);
     if (rc != VK_OK) return rc;
   }
   if (diag) {
