@@ -676,26 +676,35 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
       const float nx = (it.grad ? normZ : normP)[grow] + (KT == 1 ? s.Ceps : 0.f);
       float rs = 0.f;
       {
-        // this row block's operand -> tensor memory: fp32 row slice [cg*32, cg*32+32) of x - m split into bf16 hi / lo,
-        // two per column.  The previous item's MMAs must be finished with the old block first.
+        // this row block's operand -> tensor memory: dims [cg*32, cg*32+32) of row t as bf16 hi / lo pairs, two per
+        // column.  The previous item's MMAs must be finished with the old block first.
         if (item_iter > 0) mbar_wait(bar(kBarAEmpty), (item_iter - 1) & 1);
         fence_after_sync();
-        const float* xr = (it.grad ? Zf : Pf) + (int64_t)grow * s.D + cg * 32;
-        const float* mr = st->m + cg * 32;
+        // The pack kernel has already split x - m into the bf16 hi / lo images ([block][hi/lo][Dp/8][128 rows][8]): chunk
+        // kc of this row is 16 bytes, and the 32 lanes of a warp (32 consecutive rows) read 512 contiguous bytes -- four
+        // coalesced 16-byte loads per image instead of the fp32 row (lanes on 32 different rows: ~16k LSU cycles per
+        // item with scalar loads, r02y / r02z role counters).  Rows >= N and padded dims are zero in the image.
+        const uint8_t* img = (it.grad ? imgZb : imgPb) + (size_t)it.i * (2 * b_half);
         const uint32_t ta = tmem + ((uint32_t)(ew * 32) << 16) + cg * 16;
+        uint32_t ah[16], al[16];
+#pragma unroll
+        for (int m = 0; m < 4; ++m) {
+          const int kc = cg * 4 + m;
+          uint4 h = make_uint4(0u, 0u, 0u, 0u), l = h;
+          if (kc < s.nkc) {
+            h = __ldg(reinterpret_cast<const uint4*>(img + ((size_t)kc * kRows + t) * 16));
+            if (G1P >= 2) l = __ldg(reinterpret_cast<const uint4*>(img + b_half + ((size_t)kc * kRows + t) * 16));
+          }
+          ah[4 * m] = h.x; ah[4 * m + 1] = h.y; ah[4 * m + 2] = h.z; ah[4 * m + 3] = h.w;
+          al[4 * m] = l.x; al[4 * m + 1] = l.y; al[4 * m + 2] = l.z; al[4 * m + 3] = l.w;
+        }
 #pragma unroll
         for (int j8 = 0; j8 < 16; j8 += 8) {
-          uint32_t ah[8], al[8];
+          uint32_t h8[8], l8[8];
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const int d = cg * 32 + 2 * (j8 + j);
-            const float a = (rvalid && d < s.D) ? __ldg(xr + 2 * (j8 + j)) - mr[2 * (j8 + j)] : 0.f;
-            const float b = (rvalid && d + 1 < s.D) ? __ldg(xr + 2 * (j8 + j) + 1) - mr[2 * (j8 + j) + 1] : 0.f;
-            if (G1P >= 2) split_pair(a, b, ah[j], al[j]);
-            else ah[j] = pack_bf16x2(a, b);
-          }
-          tmem_st8(ta + kTmAhi + j8, ah);
-          if (G1P >= 2) tmem_st8(ta + kTmAlo + j8, al);
+          for (int j = 0; j < 8; ++j) { h8[j] = ah[j8 + j]; l8[j] = al[j8 + j]; }
+          tmem_st8(ta + kTmAhi + j8, h8);
+          if (G1P >= 2) tmem_st8(ta + kTmAlo + j8, l8);
         }
         tmem_st_wait();
         fence_before_sync();
