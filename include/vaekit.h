@@ -219,8 +219,9 @@ int vk_vq_bwd(const float* g_q, const float* g_loss, const float* latents, const
  *   3  both in three passes of a bf16 hi/lo split (hi*hi + lo*hi + hi*lo, ~2^-17 relative): the parity sweep
  *   2  distance GEMM two passes (row operand hi/lo, column operand plain bf16), gradient GEMM one pass
  *   1  both in one plain bf16 pass
+ *   22, 31, 32  an explicit (distance GEMM, gradient GEMM) pair; a two-pass gradient GEMM splits the coefficients only
  *   0  auto: the library picks (rbf at N >= 8192: mode 2; otherwise the parity sweep); a reduced-precision sweep
- *      is CHECKED against a float64 SIMT evaluation of 32 sample rows over all columns, and when its error exceeds
+ *      is CHECKED against a float64 SIMT evaluation of 16 sample rows over all columns, and when its error exceeds
  *      4e-6 of max |grad| a device flag makes the parity sweep run behind it -- no host synchronisation either way.
  * The data are centred on the device (distances are translation invariant) and the gradient GEMM accumulates CENTRED
  * coefficients c - c0 (c0 = the coefficient at the mean squared distance; its share of the gradient is exact float64
