@@ -348,6 +348,8 @@ class WaeMmd(Workload):
         self.reg = 5000.0 if kt == "rbf" else 100.0
         self.desc = "WAE-MMD %s kernel, z batch 65536x128, value + d/dz in one tcgen05 Gram sweep (BASELINE configs[2])" % kt.upper()
         self.cpu_rows = 8
+        if kt == "rbf":      # dram__bytes_read + write of mmd_main_kernel<2,1,0>, the launch that is 91 % of the call
+            self.ncu_traffic = {"mmd_fwd": (74.697472e6 + 39.711232e6, "profiles/ncu_mmd_rbf_r02z_summary.txt")}
 
     def model(self, dev):
         from vaekit.models import vae_models
