@@ -795,9 +795,20 @@ def measure(ctx, wl):
                 out = gs(**host)
                 return [v.item() for v in out.values()]
         else:
+            # the copy of batch t+1 runs on a side stream while step t computes (vaekit.io.DevicePrefetcher: the pinned-memory
+            # DataLoader of dataset.py:172-178 with its copy taken off the critical path); every timed step still issues
+            # one full host -> device copy of its inputs and reads every returned loss back
+            from vaekit.io import DevicePrefetcher
+            pf = DevicePrefetcher(dev)
+            pf.submit(host)
+
             def e2e_step():
-                td = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
-                dd = wl.step(model, td, world)
+                td = pf.get()
+                dd = wl.step(model, td, world)                      # enqueues the step (asynchronous)
+                # the next batch's copy goes in AFTER the step's own launches: a step may start with a small host -> device
+                # copy of its own (SWAE's projection matrix is drawn on the CPU like the reference's, swae.py:135-149), and
+                # that would queue behind a 537 MB prefetch in the copy engine (scripts/probe_prefetch*.py, r02z)
+                pf.submit(host)
                 return [v.item() for v in dd.values()]              # the caller's .item() per dict key (experiment.py:55)
         for _ in range(2):
             e2e_step()
