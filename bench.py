@@ -660,11 +660,34 @@ def run_reference_arm(args):
 # =====================================================================================================================
 # GPU arm
 # =====================================================================================================================
+def bind_to_gpu_numa_node(local_rank):
+    """Pins this rank's process to the CPUs NVML reports as local to its GPU BEFORE any pinned host memory is allocated
+    (first touch puts the pages on that node): on an 8-GPU box the ranks otherwise pull their batches through one
+    socket's memory and the inter-socket link.  Best effort: returns the CPU count it bound to, or None."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        idx = int(vis.split(",")[local_rank]) if vis and vis.split(",")[local_rank].isdigit() else local_rank
+        h = pynvml.nvmlDeviceGetHandleByIndex(idx)
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = {64 * w + b for w, m in enumerate(mask) for b in range(64) if (m >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return len(cpus)
+    except Exception:
+        pass
+    return None
+
+
 class Ctx:
     def __init__(self, args):
         import torch.distributed as dist
         self.dist = dist
         self.rank, self.world, self.local = dist_env()
+        self.numa = bind_to_gpu_numa_node(self.local) if self.world > 1 else None
         torch.cuda.set_device(self.local)
         self.dev = torch.device("cuda", self.local)
         if self.world > 1:
@@ -828,7 +851,10 @@ def measure(ctx, wl):
                 "config": {"workload": wl.desc, "global_batch": wl.units(world), "l2_policy": wl.l2_policy,
                            "parallelism": ("%s; %d ranks" % (wl.parallelism, world)) if world > 1 else "single GPU",
                            "timing": "step: K steps between two CUDA events; roofline: the same K steps repeated with CUDA "
-                                     "events around every library call"},
+                                     "events around every library call",
+                           "e2e_pipeline": "vaekit.io.DevicePrefetcher: batch t+1 copied from pinned memory on a side stream "
+                                           "during step t; every step copies its inputs and reads its losses back",
+                           "numa_cpus_bound": ctx.numa},
                 "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "loss": loss})
     res.update(extras)
     return res

@@ -24,6 +24,9 @@ namespace tiled {
 #define VK_TC_TW 4
 #define VK_TC_MINB 2
 #endif
+#ifndef VK_TC_MINB_COLS
+#define VK_TC_MINB_COLS 2      // (3 CTAs per SM fit the packed column sweep at 168 registers; measured r02z: 2.81 ms against 2.58)
+#endif
 constexpr int kR = VK_TC_R;    // anchors per warp
 constexpr int kPSh = VK_TC_PSH;   // log2 kP
 constexpr int kP = 1 << kPSh;  // partners per step
@@ -467,7 +470,7 @@ bwd_rows_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
 // ---- backward, column sweep: d/dmu_j, d/dlog_var_j -------------------------------------------------------------------
 //   d ld_ijd / d mu_jd = 2 h_jd (z_id - mu_jd) ;  d ld_ijd / d lv_jd = h_jd (z_id - mu_jd)^2 - 1/2
 template <int KD, int NS>
-__global__ void __launch_bounds__(kThreads, VK_TC_MINB)
+__global__ void __launch_bounds__(kThreads, VK_TC_MINB_COLS)
 bwd_cols_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const float* __restrict__ LV,
                 const float* __restrict__ Hs, const float* __restrict__ Cs, const double* __restrict__ Cb,
                 const float* __restrict__ lqz, const float* __restrict__ lse, TcParams p, const float* __restrict__ g_loss,
@@ -484,19 +487,29 @@ bwd_cols_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
   const float g = g_loss ? *g_loss : 1.f;
   const float invB = 1.f / (float)p.B;
   const float cq = (p.beta - p.alpha) * invB * g, cp = (p.gamma_anneal - p.beta) * invB * g;
-  float mu[kR][KD], hs[kR][KD], cs[kR][KD], g0[kR][KD], g1[kR][KD];
+  // Anchor columns are carried in PAIRS (r = 2 rp, 2 rp + 1) as packed fp32 (FADD2 / FMUL2 / FFMA2: one issue slot for the
+  // two anchors that share a staged partner value): 6 packed + 1 MUFU instead of 12 + 1 instructions per density.  Signs
+  // are folded into the operands (-mu, -h; -g0 accumulated) so every element sees exactly the scalar version's operations.
+  static_assert(kR % 2 == 0, "anchor pairs");
+  constexpr int RP = kR / 2;
+  uint64_t nmu2[RP][KD], nhs2[RP][KD], cs2[RP][KD], g0n2[RP][KD], g12[RP][KD];
 #pragma unroll
-  for (int r = 0; r < kR; ++r)
+  for (int rp = 0; rp < RP; ++rp)
 #pragma unroll
     for (int k = 0; k < KD; ++k) {
       const int d = dbase + lane + 32 * k;
-      const bool ok = c0 + r < p.r1 && d < p.D;
-      const size_t o = (size_t)(c0 + r) * p.D + d;
-      mu[r][k] = ok ? MU[o] : 0.f;
-      hs[r][k] = ok ? Hs[o] : 0.f;
-      cs[r][k] = ok ? Cs[o] : 0.f;
-      g0[r][k] = 0.f; g1[r][k] = 0.f;
+      float m_[2], h_[2], c_[2];
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int r = 2 * rp + e;
+        const bool ok = c0 + r < p.r1 && d < p.D;
+        const size_t o = (size_t)(c0 + r) * p.D + d;
+        m_[e] = ok ? MU[o] : 0.f; h_[e] = ok ? Hs[o] : 0.f; c_[e] = ok ? Cs[o] : 0.f;
+      }
+      nmu2[rp][k] = pk2(-m_[0], -m_[1]); nhs2[rp][k] = pk2(-h_[0], -h_[1]); cs2[rp][k] = pk2(c_[0], c_[1]);
+      g0n2[rp][k] = pk2(0.f, 0.f); g12[rp][k] = pk2(0.f, 0.f);
     }
+  const uint64_t cp2 = pk2(cp, cp), log2e2 = pk2(kLog2e, kLog2e), nln2_2 = pk2(-kLn2, -kLn2), nhalf2 = pk2(-0.5f, -0.5f);
   const float dcorr = (p.lw_strat - p.lw_ds) * kLog2e;
   const int pq = (lane >> 1) & (kP - 1);                    // partner slot of this lane's pair
   const bool anchor_dead = c0 + (lane >> (kPSh + 1)) >= p.r1;
@@ -528,49 +541,60 @@ bwd_cols_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
       const int pp_special = p.B - 2 - (i0 + ib);     // partner slot of row B-2 in this step (if in [0, kP))
       auto step = [&](auto special_c) {
         constexpr bool SPECIAL = decltype(special_c)::value;
-        float a[kR][kP];
+        uint64_t an2[RP][kP];                                        // MINUS the quadratic part of the pair sums
 #pragma unroll
-        for (int r = 0; r < kR; ++r)
+        for (int rp = 0; rp < RP; ++rp)
 #pragma unroll
-          for (int pp = 0; pp < kP; ++pp) a[r][pp] = 0.f;
+          for (int pp = 0; pp < kP; ++pp) an2[rp][pp] = pk2(0.f, 0.f);
 #pragma unroll
         for (int k = 0; k < KD; ++k) {
 #pragma unroll
           for (int pp = 0; pp < kP; ++pp) {
             const float pz = Tz[(ib + pp) * DP + dbase + lane + 32 * k];
+            const uint64_t pz2 = pk2(pz, pz);
 #pragma unroll
-            for (int r = 0; r < kR; ++r) {
-              const float df = pz - mu[r][k];
-              a[r][pp] = fmaf(df * df, hs[r][k], a[r][pp]);          // quadratic part of the pair sum
+            for (int rp = 0; rp < RP; ++rp) {
+              const uint64_t df2 = add2(pz2, nmu2[rp][k]);
+              an2[rp][pp] = fma2(mul2(df2, df2), nhs2[rp][k], an2[rp][pp]);
             }
           }
         }
-        double x = (cbq - (double)pair_sum<NS>(a, lane, grp, w % NS, xch, step_no)) -
+        float a[kR][kP];
+#pragma unroll
+        for (int rp = 0; rp < RP; ++rp)
+#pragma unroll
+          for (int pp = 0; pp < kP; ++pp) upk2(an2[rp][pp], a[2 * rp][pp], a[2 * rp + 1][pp]);
+        // (the sum of the negated values is the negated sum, bit for bit)
+        double x = (cbq + (double)pair_sum<NS>(a, lane, grp, w % NS, xch, step_no)) -
                    ((double)Tq[ib + pq] + (double)Tq[kTR + ib + pq]) * 1.4426950408889634;
         if (SPECIAL && (lane >> (kPSh + 1)) == 0 && pq == pp_special) x += (double)p.D * (double)dcorr;
         const float wq = anchor_dead ? 0.f : cq * ex2f((float)x);
-        float cqp[kR][kP];
+        uint64_t cqp2[RP][kP];
 #pragma unroll
-        for (int r = 0; r < kR; ++r)
+        for (int rp = 0; rp < RP; ++rp)
 #pragma unroll
-          for (int pp = 0; pp < kP; ++pp) cqp[r][pp] = __shfl_sync(0xFFFFFFFFu, wq, 2 * (r * kP + pp));
+          for (int pp = 0; pp < kP; ++pp)
+            cqp2[rp][pp] = pk2(__shfl_sync(0xFFFFFFFFu, wq, 2 * (2 * rp * kP + pp)), __shfl_sync(0xFFFFFFFFu, wq, 2 * ((2 * rp + 1) * kP + pp)));
 #pragma unroll
         for (int k = 0; k < KD; ++k)
 #pragma unroll
           for (int pp = 0; pp < kP; ++pp) {
             const int o = (ib + pp) * DP + dbase + lane + 32 * k;
             const float pz = Tz[o], pl = Tl[o];
+            const uint64_t pz2 = pk2(pz, pz), npl2 = pk2(-pl, -pl);
 #pragma unroll
-            for (int r = 0; r < kR; ++r) {
-              const float df = pz - mu[r][k];
-              const float t = hs[r][k] * df;                         // h (z - mu) log2e
-              const float u = df * t;                                // h (z - mu)^2 log2e
-              float e = cs[r][k] - u;
-              if (SPECIAL && r == 0 && pp == pp_special && dbase + lane + 32 * k < p.D) e += dcorr;
-              const float rr = ex2f(fmaf(-pl, kLog2e, e));           // softmax weight inside LSE_j[i, d]
-              const float cf = fmaf(cp, rr, cqp[r][pp]);             // dL / d ld_ijd
-              g0[r][k] = fmaf(cf, t, g0[r][k]);
-              g1[r][k] = fmaf(cf, fmaf(u, kLn2, -0.5f), g1[r][k]);   // h (z - mu)^2 - 1/2
+            for (int rp = 0; rp < RP; ++rp) {
+              const uint64_t df2 = add2(pz2, nmu2[rp][k]);
+              const uint64_t tn2 = mul2(nhs2[rp][k], df2);           // -h (z - mu) log2e
+              const uint64_t w2 = mul2(df2, tn2);                    // -h (z - mu)^2 log2e
+              uint64_t e2 = add2(cs2[rp][k], w2);
+              if (SPECIAL && rp == 0 && pp == pp_special && dbase + lane + 32 * k < p.D) e2 = add2(e2, pk2(dcorr, 0.f));
+              float a0, a1;
+              upk2(fma2(npl2, log2e2, e2), a0, a1);
+              const uint64_t rr2 = pk2(ex2f(a0), ex2f(a1));          // softmax weights inside LSE_j[i, d]
+              const uint64_t cf2 = fma2(cp2, rr2, cqp2[rp][pp]);     // dL / d ld_ijd
+              g0n2[rp][k] = fma2(cf2, tn2, g0n2[rp][k]);
+              g12[rp][k] = fma2(cf2, fma2(w2, nln2_2, nhalf2), g12[rp][k]);   // h (z - mu)^2 - 1/2
             }
           }
       };
@@ -584,6 +608,13 @@ bwd_cols_kernel(const float* __restrict__ Z, const float* __restrict__ MU, const
   for (int r = 0; r < kR; ++r)
 #pragma unroll
     for (int k = 0; k < KD; ++k) {
+      float mu[kR][KD], g0[kR][KD], g1[kR][KD];                    // (this element only; the compiler keeps the pairs)
+      {
+        float q0, q1;
+        upk2(nmu2[r / 2][k], q0, q1); mu[r][k] = -((r & 1) ? q1 : q0);
+        upk2(g0n2[r / 2][k], q0, q1); g0[r][k] = -((r & 1) ? q1 : q0);
+        upk2(g12[r / 2][k], q0, q1); g1[r][k] = (r & 1) ? q1 : q0;
+      }
       const int j = c0 + r, d = dbase + lane + 32 * k;
       if (gridDim.y > 1) {
         if (j < p.r1 && d < p.D) {
