@@ -836,7 +836,7 @@ mmd_main_kernel(const float* __restrict__ Zf, const float* __restrict__ Pf, cons
         if (c0 < s.Dp) {
           uint32_t o[32];
           tmem_ld32(tmem_O + ((uint32_t)(ew * 32) << 16) + c0, o);
-          tmem_ld_wait();
+          tmem_ld_wait32(o);
           if (c0 + 32 <= s.Dp) {
 #pragma unroll
             for (int e = 0; e < 32; e += 4)

@@ -270,11 +270,11 @@ vq_fwd_kernel(const float* __restrict__ X, const float* __restrict__ E, const ui
         mbar_wait(bar(5 + buf), (c >> 1) & 1);
         PROF_LAP(0)
         fence_after_sync();
-        // 16-column halves of this part's 32-column blocks, TMEM loads ping-ponged against the compares
+        // this part's 32-column blocks, one tcgen05.ld.x32 each: tcgen05.wait::ld waits for EVERY outstanding load, so two
+        // ping-ponged x16 loads never were two loads in flight -- one x32 per wait halves the exposed waits
         const uint32_t tbase = tmem + ((uint32_t)(ew * 32) << 16) + buf * 256;
-        const int nh = 2 * ((nblk - part + kParts - 1) / kParts);
-        auto col_of = [&](int h) { return ((part + (h >> 1) * kParts) << 5) + ((h & 1) << 4); };
-        auto consume = [&](const uint32_t (&r)[16], int kb) {
+        const int nb32 = (nblk - part + kParts - 1) / kParts;
+        auto consume = [&](const uint32_t* r, int kb) {       // 16 distances
           float ee[16];
 #pragma unroll
           for (int i = 0; i < 16; i += 4)
@@ -298,15 +298,13 @@ vq_fwd_kernel(const float* __restrict__ X, const float* __restrict__ E, const ui
             }
           }
         };
-        uint32_t ra[16], rb[16];
-        tmem_ld16(tbase + col_of(0), ra);
-        for (int h = 0; h < nh; h += 2) {
-          tmem_ld_wait16(ra);
-          tmem_ld16(tbase + col_of(h + 1), rb);
-          consume(ra, ch * s.NC + col_of(h));
-          tmem_ld_wait16(rb);
-          if (h + 2 < nh) tmem_ld16(tbase + col_of(h + 2), ra);
-          consume(rb, ch * s.NC + col_of(h + 1));
+        uint32_t ra[32];
+        for (int b = 0; b < nb32; ++b) {
+          const int col = (part + b * kParts) << 5;
+          tmem_ld32(tbase + col, ra);
+          tmem_ld_wait32(ra);
+          consume(ra, ch * s.NC + col);
+          consume(ra + 16, ch * s.NC + col + 16);
         }
         fence_before_sync();
         mbar_arrive(bar(7 + buf));
