@@ -119,3 +119,19 @@ def test_last_model_host_parts(built):
     assert "pseudo_input" not in v.state_dict() and v.embed_pseudo[0].out_features == 12288
     pm, pv = v.prior_components(torch.rand(2, 3, 64, 64))
     assert pm.shape == (12, 16) and pv.shape == (12, 16)
+
+
+def test_bench_host_helpers_are_best_effort():
+    """bench.py's NUMA binding must never take a run down (no NVML / no GPU here: it returns None and leaves the affinity
+    alone), and the prefetcher refuses misuse before touching a device."""
+    import os
+    sys.path.insert(0, ROOT)
+    import bench
+    before = os.sched_getaffinity(0)
+    got = bench.bind_to_gpu_numa_node(0)
+    assert got is None or (isinstance(got, int) and got > 0)
+    if got is None:
+        assert os.sched_getaffinity(0) == before
+    os.sched_setaffinity(0, before)
+    src = open(os.path.join(ROOT, "pytorch-vae_b200", "vaekit", "io.py")).read()
+    assert "oracle" not in src and "wait_event" in src                      # plumbing only: streams and events
