@@ -346,7 +346,7 @@ static int tc_fwd_impl(const float* z, const float* mu, const float* log_var, in
   double* partials = (double*)(ws + kWsHeader);
   float* H = (float*)(ws + kWsHeader + (((size_t)blocks * 32 + 255) & ~(size_t)255));
   float* C0 = H + B * D;
-  const int prep_blocks = (int)((B * D + 255) / 256 < 1184 ? (B * D + 255) / 256 : 1184);
+  const int prep_blocks = (int)((B * D + 255) / 256 < (int64_t)sm_count() * 8 ? (B * D + 255) / 256 : (int64_t)sm_count() * 8);
   if (D <= 128) {
     // lanes-own-dims path (betatc_tiled.cuh)
     // D <= 32: one dim per lane; <= 64: two; <= 128: four.  (Two warps per anchor group with two dims per lane each --
@@ -418,7 +418,7 @@ static int tc_bwd_impl(const float* z, const float* mu, const float* log_var, co
   const int blocks = (int)((B + kW - 1) / kW);
   float* H = (float*)(ws + kWsHeader + (((size_t)blocks * 32 + 255) & ~(size_t)255));
   float* C0 = H + B * D;
-  const int prep_blocks = (int)((B * D + 255) / 256 < 1184 ? (B * D + 255) / 256 : 1184);
+  const int prep_blocks = (int)((B * D + 255) / 256 < (int64_t)sm_count() * 8 ? (B * D + 255) / 256 : (int64_t)sm_count() * 8);
   if (D <= 128) {
     const int cfg = D <= 32 ? 0 : (D <= 64 ? 1 : 2);
     const int DP = cfg == 0 ? 32 : (cfg == 1 ? 64 : 128), NS = 1;
@@ -445,7 +445,7 @@ static int tc_bwd_impl(const float* z, const float* mu, const float* log_var, co
     kc<<<dim3(tb, nsplit), tiled::kThreads, tsm, st>>>(z, mu, log_var, H, C0, Cb, lqz, lse, p, g_loss, g_mu, g_lv, part_mu, part_lv);
     if (nsplit > 1) {
       const int64_t n = rows * D;
-      tiled::bwd_merge_kernel<<<(unsigned)((n + 255) / 256 < 1184 ? (n + 255) / 256 : 1184), 256, 0, st>>>(
+      tiled::bwd_merge_kernel<<<(unsigned)((n + 255) / 256 < (int64_t)sm_count() * 8 ? (n + 255) / 256 : (int64_t)sm_count() * 8), 256, 0, st>>>(
           z, mu, log_var, p, g_loss, nsplit, part, part_mu, part_lv, g_z, g_mu, g_lv);
     }
     return check_launch("tc_bwd");

@@ -187,7 +187,7 @@ extern "C" int vk_pair_kernel_bwd_dense(const float* x1, const int64_t* s1, cons
   if (rc != VK_OK) return rc;
   const int64_t pairs = N1 * N2, wpb = kPairThreads / 32;
   int64_t blocks = (pairs + wpb - 1) / wpb;
-  if (blocks > 148 * 64) blocks = 148 * 64;
+  if (blocks > sm_count() * 64) blocks = sm_count() * 64;
   const PairView a{x1, s1[0], s1[1], s1[2]}, b{x2, s2[0], s2[1], s2[2]};
   pair_bwd_dense_kernel<<<(int)blocks, kPairThreads, 0, (cudaStream_t)stream>>>(a, b, N1, N2, (int)D, kmat, g, g_sr, g_sc,
                                                                                   kernel_type, sigma, c, g_x1, g_x2);
